@@ -1,0 +1,235 @@
+/*
+ * vllm_b200.h -- C ABI of libvllm_b200.so: the B200-native (sm_100a) implementation of vLLM's
+ * decode hot path.  Plain pointers and sizes only; no torch types.  Every entry point is the
+ * device-side body of ONE reference operator; the reference-side binding a maintainer would add
+ * (a TORCH_LIBRARY shim that unwraps at::Tensor into these arguments) is in INTEGRATION.md, and
+ * vllm_b200/torch_shim.cpp is that shim.
+ *
+ * Conventions (mirror the reference operator contract):
+ *   - all data pointers are DEVICE pointers on the current CUDA device; the caller owns every
+ *     buffer (outputs, workspaces); nothing is retained after the call returns;
+ *   - `stream` is a cudaStream_t (passed as void*); kernels are launched on it, no host sync,
+ *     CUDA-graph-capturable;
+ *   - scales (k_scale, v_scale, a_scales, ...) are DEVICE fp32 pointers dereferenced in-kernel
+ *     (reference: csrc/attention/attention_kernels.cuh:283);
+ *   - return value: 0 on success, non-zero on error; vb200_last_error() gives the message of the
+ *     last failure on this thread (the Python host raises RuntimeError with it, matching the
+ *     reference's TORCH_CHECK -> c10::Error -> RuntimeError convention).
+ *
+ * All citations are relative to /root/reference.
+ */
+#ifndef VLLM_B200_H_
+#define VLLM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* element types */
+enum {
+  VB200_F32 = 0,
+  VB200_F16 = 1,
+  VB200_BF16 = 2,
+  VB200_FP8_E4M3 = 3,
+  VB200_I32 = 4,
+  VB200_I64 = 5,
+  VB200_U32 = 6
+};
+
+/* kv_cache_dtype strings of the reference ("auto", "fp8"/"fp8_e4m3";
+ * csrc/quantization/fp8/nvidia/quant_utils.cuh:532-569) */
+enum { VB200_KV_AUTO = 0, VB200_KV_FP8_E4M3 = 1 };
+
+typedef void* vb200_stream_t;
+
+const char* vb200_last_error(void);
+/* library / build identification: "vllm_b200 <ver> sm_100a" */
+const char* vb200_version(void);
+
+/* ------------------------------------------------------------------------------------------ */
+/* KV-cache scatter                                                                            */
+/* ------------------------------------------------------------------------------------------ */
+
+/* reshape_and_cache: csrc/cache_kernels.cu:369-395 (kernel :210-262), schema
+ * csrc/torch_bindings.cpp:676-681.
+ *   key/value  [num_tokens, num_heads, head_size] of `src_dtype`, row strides key_stride /
+ *              value_stride (elements);
+ *   key_cache  [num_blocks, num_heads, head_size/x, block_size, x]; value_cache
+ *              [num_blocks, num_heads, head_size, block_size]; contiguous; element type is
+ *              src_dtype (kv_dtype AUTO) or fp8 e4m3 bytes (kv_dtype FP8_E4M3, quantised as
+ *              fp8_satfinite(float(v) / *scale), quant_utils.cuh:466-479);
+ *   slot_mapping int64 [num_tokens]; negative slots are skipped. */
+int vb200_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                            const int64_t* slot_mapping, int num_tokens, int num_heads,
+                            int head_size, int block_size, int x, int64_t key_stride,
+                            int64_t value_stride, int src_dtype, int kv_dtype,
+                            const float* k_scale, const float* v_scale, vb200_stream_t stream);
+
+/* reshape_and_cache_flash: csrc/cache_kernels.cu:412-450 (kernel :264-306), schema
+ * csrc/torch_bindings.cpp:685-691.  Cache [num_blocks, block_size, num_heads, head_size] addressed
+ * through runtime strides (elements) so NHD and HND-permuted views both work; the key and value
+ * caches share the same strides (the reference passes key_cache's).  num_tokens =
+ * slot_mapping.size(0) may be smaller than key.size(0) (:421-431). */
+int vb200_reshape_and_cache_flash(const void* key, const void* value, void* key_cache,
+                                  void* value_cache, const int64_t* slot_mapping, int num_tokens,
+                                  int num_heads, int head_size, int block_size,
+                                  int64_t block_stride, int64_t page_stride, int64_t head_stride,
+                                  int64_t key_stride, int64_t value_stride, int src_dtype,
+                                  int kv_dtype, const float* k_scale, const float* v_scale,
+                                  vb200_stream_t stream);
+
+/* convert_fp8 (test helper of the reference): csrc/cache_kernels.cu:526-571, schema
+ * csrc/torch_bindings.cpp:705-707.  Flat element-wise conversion of `numel` elements:
+ *   src 16/32-bit -> dst fp8:   fp8_satfinite(float(src) / scale)
+ *   src fp8 -> dst 16/32-bit:   dst_t(float(half(fp8)) * scale)        (quant_utils.cuh:348-359) */
+int vb200_convert_fp8(void* dst, const void* src, int64_t numel, int dst_dtype, int src_dtype,
+                      float scale, vb200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* Paged-attention decode                                                                      */
+/* ------------------------------------------------------------------------------------------ */
+
+/* paged_attention_v2: csrc/attention/paged_attention_v2.cu:167-192, kernels
+ * csrc/attention/attention_kernels.cuh:524-664, schema csrc/torch_bindings.cpp:58-68.
+ *   out        [num_seqs, num_heads, head_size]  q_dtype
+ *   exp_sums, max_logits  fp32 [num_seqs, num_heads, max_num_partitions]
+ *   tmp_out    [num_seqs, num_heads, max_num_partitions, head_size]  q_dtype
+ *   query      [num_seqs, num_heads, head_size], row stride q_stride (elements)
+ *   key_cache / value_cache in the paged layout above, strides kv_block_stride / kv_head_stride
+ *   block_tables int32 [num_seqs, max_num_blocks_per_seq]; seq_lens int32 [num_seqs]
+ *   partition_size: tokens per split-K partition (the reference fixes 512,
+ *   paged_attention_v2.cu:29); max_num_partitions = ceil(max_seq_len / partition_size).
+ * Same per-partition outputs as the reference: tmp_out holds the partition's NORMALISED output,
+ * exp_sums the un-normalised sum at the partition max, max_logits the partition max. */
+int vb200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                             const void* query, const void* key_cache, const void* value_cache,
+                             int num_seqs, int num_heads, int head_size, int num_kv_heads,
+                             float scale, const int32_t* block_tables, const int32_t* seq_lens,
+                             int block_size, int max_seq_len, int max_num_blocks_per_seq,
+                             const float* alibi_slopes, int q_dtype, int kv_dtype,
+                             const float* k_scale, const float* v_scale, int64_t q_stride,
+                             int64_t kv_block_stride, int64_t kv_head_stride, int partition_size,
+                             vb200_stream_t stream);
+
+/* paged_attention_v1: csrc/attention/paged_attention_v1.cu:160-182, kernel
+ * attention_kernels.cuh:494-522, schema csrc/torch_bindings.cpp:45-54.  Same math without
+ * caller-visible partials.  The B200 kernel is split-K by design: when `workspace` is non-NULL it
+ * is used for the partials ( vb200_paged_attention_v1_workspace_size() bytes, any alignment of
+ * 16 ) and `partition_size` (0 = library heuristic) selects the split; with workspace == NULL the
+ * whole sequence is processed by one CTA per (sequence, kv-head group). */
+size_t vb200_paged_attention_v1_workspace_size(int num_seqs, int num_heads, int head_size,
+                                               int max_seq_len, int q_dtype, int partition_size);
+int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads, int num_kv_heads,
+                                            int max_seq_len, int block_size);
+int vb200_paged_attention_v1(void* out, const void* query, const void* key_cache,
+                             const void* value_cache, int num_seqs, int num_heads, int head_size,
+                             int num_kv_heads, float scale, const int32_t* block_tables,
+                             const int32_t* seq_lens, int block_size, int max_seq_len,
+                             int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype,
+                             int kv_dtype, const float* k_scale, const float* v_scale,
+                             int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+                             int partition_size, void* workspace, size_t workspace_bytes,
+                             vb200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* FP8 activation quantisation + activation                                                    */
+/* ------------------------------------------------------------------------------------------ */
+
+/* static_scaled_fp8_quant: csrc/quantization/fp8/common.cu:87-111 (kernel :14-26):
+ * out = fp8(clamp(x * (1 / *scale), +-448)).  input [num_tokens, hidden] contiguous. */
+int vb200_static_scaled_fp8_quant(void* out, const void* input, const float* scale,
+                                  int64_t num_tokens, int hidden_size, int in_dtype,
+                                  vb200_stream_t stream);
+/* dynamic_scaled_fp8_quant: common.cu:113-141: *scale = max(*scale, amax(|x|)/448) through an
+ * atomic max (scale must be pre-zeroed, vllm/_custom_ops.py:1297), then the static kernel. */
+int vb200_dynamic_scaled_fp8_quant(void* out, const void* input, float* scale, int64_t num_tokens,
+                                   int hidden_size, int in_dtype, vb200_stream_t stream);
+/* dynamic_per_token_scaled_fp8_quant: common.cu:143-171 (kernel :28-83): per row
+ * s = max(min(amax, *scale_ub) / 448, 1/(448*512)); out = fp8(clamp(x / s, +-448)); scales[row]=s */
+int vb200_dynamic_per_token_scaled_fp8_quant(void* out, const void* input, float* scales,
+                                             const float* scale_ub, int64_t num_tokens,
+                                             int hidden_size, int in_dtype, vb200_stream_t stream);
+/* silu_and_mul: csrc/activation_kernels.cu:129-136 (kernel :26-39):
+ * out[t,i] = T(silu_f32(x[t,i])) *_T x[t,d+i]; input [num_tokens, 2d], out [num_tokens, d]. */
+int vb200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, int dtype,
+                       vb200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* FP8 w8a8 linear                                                                             */
+/* ------------------------------------------------------------------------------------------ */
+
+/* cutlass_scaled_mm (fp8 e4m3 path): csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:169-240,
+ * epilogue csrc/cutlass_extensions/epilogue/scaled_mm_epilogues_c3x.hpp:137-216, schema
+ * csrc/torch_bindings.cpp:422-426.
+ *   out[m,n] = OutT( a_scales[m|0] * ( b_scales[n|0] * sum_k a[m,k]*b[k,n] ) (+ bias[n]) )
+ *   a  fp8 [M,K] row-major, row stride lda (elements);  b fp8 [K,N] COLUMN-major, i.e. the
+ *   [N,K] weight, row stride ldb;  out [M,N] of out_dtype (bf16/f16), row stride ldc;
+ *   a_scales fp32, numel 1 or M;  b_scales fp32, numel 1 or N;  bias NULL or [N] of out_dtype.
+ * Requires K % 16 == 0 and N % 16 == 0 (vllm/_custom_ops.py:732-736).
+ * The tcgen05/TMA kernel needs TMA descriptors built on the host per call (driver entry point
+ * resolved at load time; no allocation, graph-capturable). */
+int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b, const float* a_scales,
+                            const float* b_scales, const void* bias, int M, int N, int K,
+                            int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
+                            int b_scales_numel, int out_dtype, vb200_stream_t stream);
+/* cutlass_scaled_mm_supports_fp8(cuda_device_capability): torch_bindings.cpp:441 */
+int vb200_cutlass_scaled_mm_supports_fp8(int cuda_device_capability);
+
+/* ------------------------------------------------------------------------------------------ */
+/* Fused MoE                                                                                   */
+/* ------------------------------------------------------------------------------------------ */
+
+/* topk_softmax: csrc/moe/topk_softmax_kernels.cu:499-556, schema csrc/moe/torch_bindings.cpp:6-8.
+ * gating_output fp32 [num_tokens, num_experts]; topk_weights fp32 [num_tokens, topk];
+ * topk_indices [num_tokens, topk] of indices_dtype (I32 / U32 / I64); token_expert_indices int32
+ * [num_tokens, topk] = k_idx * num_tokens + row (:373).  Lowest-index tie-break (:336-358). */
+int vb200_topk_softmax(float* topk_weights, void* topk_indices, int32_t* token_expert_indices,
+                       const float* gating_output, int num_tokens, int num_experts, int topk,
+                       int indices_dtype, vb200_stream_t stream);
+
+/* moe_align_block_size: csrc/moe/moe_align_sum_kernels.cu:204-275, schema
+ * csrc/moe/torch_bindings.cpp:18-22.  topk_ids int32 [numel]; sorted_token_ids int32
+ * [numel + num_experts*(block_size-1)] (caller may pre-fill; this call writes every entry:
+ * padding = numel); expert_ids int32 [ceil(max_padded/block_size)] (trailing blocks 0);
+ * num_tokens_post_pad int32 [1].  Order inside an expert is the STABLE order (ascending flat
+ * index) -- deterministic, equal to the reference test's golden.
+ * workspace: int32 scratch of vb200_moe_align_workspace_size() bytes. */
+size_t vb200_moe_align_workspace_size(int numel, int num_experts);
+int vb200_moe_align_block_size(const int32_t* topk_ids, int numel, int num_experts, int block_size,
+                               int32_t* sorted_token_ids, int sorted_capacity, int32_t* expert_ids,
+                               int expert_ids_capacity, int32_t* num_tokens_post_pad,
+                               void* workspace, size_t workspace_bytes, vb200_stream_t stream);
+
+/* moe_sum: csrc/moe/moe_align_sum_kernels.cu:277-318 (kernel :109-123):
+ * out[t,:] = sum_j in[t,j,:], accumulated in the tensor dtype in j order. */
+int vb200_moe_sum(void* out, const void* input, int num_tokens, int topk, int hidden, int dtype,
+                  vb200_stream_t stream);
+
+/* Grouped FP8 GEMM of fused_experts (the work of invoke_fused_moe_kernel,
+ * vllm/model_executor/layers/fused_moe/fused_moe.py:478-647, Triton kernel :267-475), driven by
+ * moe_align_block_size's outputs with block_size == VB200_MOE_BLOCK_M:
+ *   for M-block p: expert e = expert_ids[p]; rows = sorted_token_ids[p*BM : (p+1)*BM]
+ *   (entries >= num_valid_tokens are padding); A row = token_id / top_k;
+ *   C[token_id, n] = OutT( (sum_k A[row,k] * B[e,n,k]) * [topk_weights[token_id]] * a_scale * b_scale[e] )
+ *   (routed weight multiplied BEFORE the scales, in fp32: fused_moe.py:455-468).
+ *   a  fp8 [num_a_rows, K];  b fp8 [E, N, K] (K contiguous);  c [num_valid_tokens, N] out_dtype.
+ *   a_scales: fp32, 1 (per-tensor) or num_a_rows (per-token); b_scales: fp32 [E] (per-tensor per
+ *   expert) or [E, N] (per-channel), selected by b_scales_per_channel. */
+#define VB200_MOE_BLOCK_M 128
+int vb200_moe_grouped_gemm_fp8(void* c, const void* a, const void* b, const float* a_scales,
+                               const float* b_scales, const float* topk_weights,
+                               const int32_t* sorted_token_ids, const int32_t* expert_ids,
+                               const int32_t* num_tokens_post_pad, int num_valid_tokens,
+                               int num_a_rows, int top_k, int E, int N, int K,
+                               int sorted_capacity, int a_scales_per_token,
+                               int b_scales_per_channel, int mul_routed_weight, int out_dtype,
+                               void* workspace, size_t workspace_bytes, vb200_stream_t stream);
+size_t vb200_moe_grouped_gemm_workspace_size(int sorted_capacity, int K);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VLLM_B200_H_ */

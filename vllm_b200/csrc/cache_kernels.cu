@@ -1,0 +1,287 @@
+// KV-cache scatter kernels for sm_100a: reshape_and_cache (paged layout), reshape_and_cache_flash
+// (flash layout through runtime strides) and the convert_fp8 test helper.
+// Semantics follow /root/reference/csrc/cache_kernels.cu:210-306,369-450,526-571; the kernels are
+// a fresh design: one CTA per token, 16-byte vector loads of the source row, 16-byte stores of the
+// x-element K runs / flash rows, bit-exact copy (AUTO) or reference-exact fp8 quantisation.
+#include "common.cuh"
+
+namespace vb200 {
+
+template <typename T>
+struct Vec16 {  // 16 bytes of T
+  static constexpr int N = 16 / sizeof(T);
+  T v[N];
+};
+
+// ---------------------------------------------------------------------------------------------
+// Paged layout.  K: [blk, h, d/x, off, x]   V: [blk, h, d, off]
+// ---------------------------------------------------------------------------------------------
+template <typename scalar_t, bool FP8>
+__global__ void __launch_bounds__(256) reshape_and_cache_kernel(
+    const scalar_t* __restrict__ key, const scalar_t* __restrict__ value,
+    void* __restrict__ key_cache_, void* __restrict__ value_cache_,
+    const int64_t* __restrict__ slot_mapping, int64_t key_stride, int64_t value_stride,
+    int num_heads, int head_size, int block_size, int x, const float* __restrict__ k_scale_p,
+    const float* __restrict__ v_scale_p, bool vec_ok) {
+  using cache_t = typename std::conditional<FP8, uint8_t, scalar_t>::type;
+  cache_t* key_cache = reinterpret_cast<cache_t*>(key_cache_);
+  cache_t* value_cache = reinterpret_cast<cache_t*>(value_cache_);
+  const int64_t token_idx = blockIdx.x;
+  const int64_t slot_idx = slot_mapping[token_idx];
+  if (slot_idx < 0) return;  // padding token
+  const int64_t block_idx = slot_idx / block_size;
+  const int64_t block_offset = slot_idx % block_size;
+  const int n = num_heads * head_size;
+  float k_scale = 1.f, v_scale = 1.f;
+  if (FP8) {
+    k_scale = *k_scale_p;
+    v_scale = *v_scale_p;
+  }
+  const scalar_t* ksrc = key + token_idx * key_stride;
+  const scalar_t* vsrc = value + token_idx * value_stride;
+  cache_t* kdst = key_cache + block_idx * (int64_t)n * block_size;
+  cache_t* vdst = value_cache + block_idx * (int64_t)n * block_size + block_offset;
+
+  if (vec_ok) {
+    // K: one x-run (x * sizeof(cache_t) == 16 bytes) per thread-iteration.
+    const int runs = n / x;
+    const int runs_per_head = head_size / x;
+    for (int r = threadIdx.x; r < runs; r += blockDim.x) {
+      const int h = r / runs_per_head;
+      const int xi = r - h * runs_per_head;
+      const scalar_t* s = ksrc + (int64_t)r * x;
+      cache_t* d = kdst + ((int64_t)(h * runs_per_head + xi) * block_size + block_offset) * x;
+      if (!FP8) {
+        *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(s);
+      } else {
+        // x == 16 source elements -> 16 fp8 bytes
+        union { uint4 u; uint8_t b[16]; } o;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o.b[j] = float_to_e4m3(to_float<scalar_t>(s[j]) / k_scale);
+        *reinterpret_cast<uint4*>(d) = o.u;
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const int h = i / head_size;
+      const int ho = i - h * head_size;
+      const int xi = ho / x, xo = ho - xi * x;
+      const int64_t t =
+          ((int64_t)(h * (head_size / x) + xi) * block_size + block_offset) * x + xo;
+      if (!FP8) {
+        kdst[t] = *reinterpret_cast<const cache_t*>(&ksrc[i]);
+      } else {
+        reinterpret_cast<uint8_t*>(kdst)[t] = float_to_e4m3(to_float<scalar_t>(ksrc[i]) / k_scale);
+      }
+    }
+  }
+  // V: element (h, d) lands at stride block_size -- inherent to the layout.
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (!FP8) {
+      vdst[(int64_t)i * block_size] = *reinterpret_cast<const cache_t*>(&vsrc[i]);
+    } else {
+      reinterpret_cast<uint8_t*>(vdst)[(int64_t)i * block_size] =
+          float_to_e4m3(to_float<scalar_t>(vsrc[i]) / v_scale);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Flash layout through runtime strides: cache[blk*block_stride + off*page_stride + h*head_stride + d]
+// ---------------------------------------------------------------------------------------------
+template <typename scalar_t, bool FP8>
+__global__ void __launch_bounds__(256) reshape_and_cache_flash_kernel(
+    const scalar_t* __restrict__ key, const scalar_t* __restrict__ value,
+    void* __restrict__ key_cache_, void* __restrict__ value_cache_,
+    const int64_t* __restrict__ slot_mapping, int64_t block_stride, int64_t page_stride,
+    int64_t head_stride, int64_t key_stride, int64_t value_stride, int num_heads, int head_size,
+    int block_size, const float* __restrict__ k_scale_p, const float* __restrict__ v_scale_p,
+    bool vec_ok) {
+  using cache_t = typename std::conditional<FP8, uint8_t, scalar_t>::type;
+  cache_t* key_cache = reinterpret_cast<cache_t*>(key_cache_);
+  cache_t* value_cache = reinterpret_cast<cache_t*>(value_cache_);
+  const int64_t token_idx = blockIdx.x;
+  const int64_t slot_idx = slot_mapping[token_idx];
+  if (slot_idx < 0) return;
+  const int64_t block_idx = slot_idx / block_size;
+  const int64_t block_offset = slot_idx % block_size;
+  float k_scale = 1.f, v_scale = 1.f;
+  if (FP8) {
+    k_scale = *k_scale_p;
+    v_scale = *v_scale_p;
+  }
+  const scalar_t* ksrc = key + token_idx * key_stride;
+  const scalar_t* vsrc = value + token_idx * value_stride;
+  const int64_t base = block_idx * block_stride + block_offset * page_stride;
+  const int n = num_heads * head_size;
+  if (vec_ok) {
+    constexpr int VE = FP8 ? 16 : (int)(16 / sizeof(scalar_t));  // elements per thread-iteration
+    const int vec_per_head = head_size / VE;
+    const int nvec = num_heads * vec_per_head;
+    for (int r = threadIdx.x; r < 2 * nvec; r += blockDim.x) {
+      const bool is_v = r >= nvec;
+      const int rr = is_v ? r - nvec : r;
+      const int h = rr / vec_per_head;
+      const int ho = (rr - h * vec_per_head) * VE;
+      const scalar_t* s = (is_v ? vsrc : ksrc) + h * head_size + ho;
+      cache_t* d = (is_v ? value_cache : key_cache) + base + h * head_stride + ho;
+      if (!FP8) {
+        *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(s);
+      } else {
+        const float sc = is_v ? v_scale : k_scale;
+        union { uint4 u; uint8_t b[16]; } o;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) o.b[j] = float_to_e4m3(to_float<scalar_t>(s[j]) / sc);
+        *reinterpret_cast<uint4*>(d) = o.u;
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const int h = i / head_size;
+      const int ho = i - h * head_size;
+      const int64_t t = base + h * head_stride + ho;
+      if (!FP8) {
+        key_cache[t] = *reinterpret_cast<const cache_t*>(&ksrc[i]);
+        value_cache[t] = *reinterpret_cast<const cache_t*>(&vsrc[i]);
+      } else {
+        reinterpret_cast<uint8_t*>(key_cache)[t] =
+            float_to_e4m3(to_float<scalar_t>(ksrc[i]) / k_scale);
+        reinterpret_cast<uint8_t*>(value_cache)[t] =
+            float_to_e4m3(to_float<scalar_t>(vsrc[i]) / v_scale);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// convert_fp8: flat conversion, both directions
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void to_fp8_kernel(uint8_t* __restrict__ dst, const T* __restrict__ src, int64_t n,
+                              float scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = float_to_e4m3(to_float<T>(src[i]) / scale);
+}
+template <typename T>
+__global__ void from_fp8_kernel(T* __restrict__ dst, const uint8_t* __restrict__ src, int64_t n,
+                                float scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = from_float<T>(e4m3_to_float(src[i]) * scale);
+}
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace vb200
+
+using namespace vb200;
+
+#define DISPATCH_SRC(dt, ...)                                   \
+  switch (dt) {                                                 \
+    case VB200_F32: { using scalar_t = float; __VA_ARGS__; break; }         \
+    case VB200_F16: { using scalar_t = __half; __VA_ARGS__; break; }        \
+    case VB200_BF16: { using scalar_t = __nv_bfloat16; __VA_ARGS__; break; } \
+    default: VB_CHECK(false, "unsupported source dtype %d", dt);  \
+  }
+
+extern "C" int vb200_reshape_and_cache(const void* key, const void* value, void* key_cache,
+                                       void* value_cache, const int64_t* slot_mapping,
+                                       int num_tokens, int num_heads, int head_size,
+                                       int block_size, int x, int64_t key_stride,
+                                       int64_t value_stride, int src_dtype, int kv_dtype,
+                                       const float* k_scale, const float* v_scale,
+                                       vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3,
+           "Unsupported data type of kv cache: %d", kv_dtype);
+  VB_CHECK(x > 0 && head_size % x == 0, "head_size %d must be a multiple of x %d", head_size, x);
+  if (num_tokens <= 0) return 0;
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (k_scale && v_scale), "fp8 kv cache needs k_scale and v_scale");
+  const int src_size = src_dtype == VB200_F32 ? 4 : 2;
+  const int cache_elt = fp8 ? 1 : src_size;
+  // vector path: an x-run is exactly 16 bytes of cache, source rows 16-byte aligned.
+  bool vec_ok = (x * cache_elt == 16) && aligned16(key) && aligned16(key_cache) &&
+                ((key_stride * src_size) % 16 == 0);
+  if (fp8) vec_ok = vec_ok && (x == 16);
+  const int n = num_heads * head_size;
+  const int threads = n >= 1024 ? 256 : (n >= 256 ? 128 : 64);
+  DISPATCH_SRC(src_dtype, {
+    if (fp8)
+      reshape_and_cache_kernel<scalar_t, true><<<num_tokens, threads, 0, stream>>>(
+          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
+    else
+      reshape_and_cache_kernel<scalar_t, false><<<num_tokens, threads, 0, stream>>>(
+          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_reshape_and_cache_flash(const void* key, const void* value, void* key_cache,
+                                             void* value_cache, const int64_t* slot_mapping,
+                                             int num_tokens, int num_heads, int head_size,
+                                             int block_size, int64_t block_stride,
+                                             int64_t page_stride, int64_t head_stride,
+                                             int64_t key_stride, int64_t value_stride,
+                                             int src_dtype, int kv_dtype, const float* k_scale,
+                                             const float* v_scale, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3,
+           "Unsupported data type of kv cache: %d", kv_dtype);
+  if (num_tokens <= 0) return 0;
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (k_scale && v_scale), "fp8 kv cache needs k_scale and v_scale");
+  const int src_size = src_dtype == VB200_F32 ? 4 : 2;
+  const int cache_elt = fp8 ? 1 : src_size;
+  const int ve = fp8 ? 16 : 16 / src_size;
+  const bool vec_ok = (head_size % ve == 0) && aligned16(key) && aligned16(value) &&
+                      aligned16(key_cache) && aligned16(value_cache) &&
+                      ((key_stride * src_size) % 16 == 0) && ((value_stride * src_size) % 16 == 0) &&
+                      ((block_stride * cache_elt) % 16 == 0) &&
+                      ((page_stride * cache_elt) % 16 == 0) && ((head_stride * cache_elt) % 16 == 0);
+  const int n = num_heads * head_size;
+  const int threads = n >= 1024 ? 256 : (n >= 256 ? 128 : 64);
+  DISPATCH_SRC(src_dtype, {
+    if (fp8)
+      reshape_and_cache_flash_kernel<scalar_t, true><<<num_tokens, threads, 0, stream>>>(
+          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          block_stride, page_stride, head_stride, key_stride, value_stride, num_heads, head_size,
+          block_size, k_scale, v_scale, vec_ok);
+    else
+      reshape_and_cache_flash_kernel<scalar_t, false><<<num_tokens, threads, 0, stream>>>(
+          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          block_stride, page_stride, head_stride, key_stride, value_stride, num_heads, head_size,
+          block_size, k_scale, v_scale, vec_ok);
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_convert_fp8(void* dst, const void* src, int64_t numel, int dst_dtype,
+                                 int src_dtype, float scale, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (numel <= 0) return 0;
+  const int threads = 256;
+  const int blocks = (int)((numel + threads - 1) / threads < 148 * 16
+                               ? (numel + threads - 1) / threads
+                               : 148 * 16);
+  if (dst_dtype == VB200_FP8_E4M3) {
+    DISPATCH_SRC(src_dtype, {
+      to_fp8_kernel<scalar_t>
+          <<<blocks, threads, 0, stream>>>((uint8_t*)dst, (const scalar_t*)src, numel, scale);
+    });
+  } else {
+    VB_CHECK(src_dtype == VB200_FP8_E4M3, "convert_fp8: one side must be fp8 (src %d dst %d)",
+             src_dtype, dst_dtype);
+    DISPATCH_SRC(dst_dtype, {
+      from_fp8_kernel<scalar_t>
+          <<<blocks, threads, 0, stream>>>((scalar_t*)dst, (const uint8_t*)src, numel, scale);
+    });
+  }
+  VB_LAUNCH_CHECK();
+  return 0;
+}

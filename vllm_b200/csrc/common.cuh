@@ -1,0 +1,123 @@
+// Shared helpers for libvllm_b200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <type_traits>
+
+#include "../../include/vllm_b200.h"
+
+namespace vb200 {
+
+// ---- error reporting (thread-local message, non-zero return) ---------------------------------
+void set_error(const char* fmt, ...);
+
+#define VB_CHECK(cond, ...)            \
+  do {                                 \
+    if (!(cond)) {                     \
+      ::vb200::set_error(__VA_ARGS__); \
+      return 1;                        \
+    }                                  \
+  } while (0)
+
+#define VB_CUDA_CHECK(expr)                                                             \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      ::vb200::set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, \
+                         __LINE__, cudaGetErrorString(_e));                             \
+      return 2;                                                                         \
+    }                                                                                   \
+  } while (0)
+
+#define VB_LAUNCH_CHECK() VB_CUDA_CHECK(cudaPeekAtLastError())
+
+inline int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+// ---- scalar conversions ----------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ float to_float(T v);
+template <>
+__device__ __forceinline__ float to_float<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_float<__half>(__half v) { return __half2float(v); }
+template <>
+__device__ __forceinline__ float to_float<__nv_bfloat16>(__nv_bfloat16 v) {
+  return __bfloat162float(v);
+}
+
+template <typename T>
+__device__ __forceinline__ T from_float(float v);
+template <>
+__device__ __forceinline__ float from_float<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __half from_float<__half>(float v) { return __float2half_rn(v); }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+
+// fp8 e4m3 quantisation exactly as the reference: __nv_cvt_float_to_fp8(v, SATFINITE, E4M3)
+// (csrc/quantization/fp8/nvidia/quant_utils.cuh:466-479).
+__device__ __forceinline__ uint8_t float_to_e4m3(float v) {
+  return (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3);
+}
+// fp8 e4m3 -> float through half, as the reference (quant_utils.cuh:348-359).
+__device__ __forceinline__ float e4m3_to_float(uint8_t v) {
+  __half_raw h = __nv_cvt_fp8_to_halfraw(v, __NV_E4M3);
+  return __half2float(*reinterpret_cast<__half*>(&h));
+}
+
+// two e4m3 (low byte first) -> f16x2
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint16_t v) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"(v));
+  return r;
+}
+
+// ---- streaming (read-once / write-once) global accesses ---------------------------------------
+__device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ldg_stream_v2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];"
+               : "=r"(r.x), "=r"(r.y)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint32_t ldg_stream_u32(const void* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace vb200

@@ -1,0 +1,315 @@
+// MoE routing kernels for sm_100a: topk_softmax, moe_align_block_size (stable counting sort),
+// moe_sum.  Semantics: /root/reference/csrc/moe/topk_softmax_kernels.cu:53-391,499-556 and
+// /root/reference/csrc/moe/moe_align_sum_kernels.cu:17-123,204-318.  These are latency-bound at
+// decode sizes (a few KB), so each is ONE launch (topk: one warp per token row; align: a single
+// CTA that keeps histogram, offsets and per-warp ranks in shared memory; sum: one CTA per token).
+#include <float.h>
+
+#include "common.cuh"
+
+namespace vb200 {
+
+// ---------------------------------------------------------------------------------------------
+// topk_softmax: one warp per row; lane l holds experts l, l+32, ...
+// ---------------------------------------------------------------------------------------------
+template <int VPT, typename IndT>
+__global__ void __launch_bounds__(128) topk_softmax_kernel(
+    float* __restrict__ topk_weights, IndT* __restrict__ topk_indices,
+    int* __restrict__ token_expert_indices, const float* __restrict__ gating, int num_tokens,
+    int num_experts, int topk) {
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= num_tokens) return;
+  const int lane = threadIdx.x & 31;
+  const float* g = gating + (int64_t)row * num_experts;
+  float v[VPT];
+  float mx = -FLT_MAX;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int e = lane + 32 * i;
+    v[i] = e < num_experts ? g[e] : -FLT_MAX;
+    mx = fmaxf(mx, v[i]);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int e = lane + 32 * i;
+    v[i] = e < num_experts ? expf(v[i] - mx) : 0.f;
+    sum += v[i];
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.f / sum;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int e = lane + 32 * i;
+    v[i] = e < num_experts ? v[i] * inv : -1.f;  // probabilities are >= 0; -1 never wins
+  }
+  // k rounds of arg-max, lowest index wins ties (topk_softmax_kernels.cu:336-358)
+  for (int k = 0; k < topk; ++k) {
+    float best = -2.f;
+    int bidx = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int e = lane + 32 * i;
+      if (v[i] > best) {  // ascending e inside a lane: strict > keeps the lowest index
+        best = v[i];
+        bidx = e;
+      }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, bidx, off);
+      if (ob > best || (ob == best && oi < bidx)) {
+        best = ob;
+        bidx = oi;
+      }
+    }
+    if (lane == 0) {
+      const int64_t o = (int64_t)row * topk + k;
+      topk_weights[o] = best;
+      topk_indices[o] = (IndT)bidx;
+      token_expert_indices[o] = k * num_tokens + row;  // :373
+    }
+    // mask the winner
+    if ((bidx & 31) == lane) {
+#pragma unroll
+      for (int i = 0; i < VPT; ++i)
+        if (lane + 32 * i == bidx) v[i] = -1.f;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// moe_align_block_size: single CTA, stable order inside every expert.
+//   smem: hist[E] | start[E+1] | run[E] | warp_cnt[NW][E]
+// ---------------------------------------------------------------------------------------------
+constexpr int kAlignThreads = 1024;
+constexpr int kAlignWarps = kAlignThreads / 32;
+
+__global__ void __launch_bounds__(kAlignThreads) moe_align_kernel(
+    const int* __restrict__ topk_ids, int numel, int num_experts, int block_size,
+    int* __restrict__ sorted_token_ids, int sorted_capacity, int* __restrict__ expert_ids,
+    int expert_ids_capacity, int* __restrict__ num_tokens_post_pad) {
+  extern __shared__ int sm[];
+  int* hist = sm;                          // [E]
+  int* start = hist + num_experts;         // [E + 1] padded exclusive prefix
+  int* run = start + num_experts + 1;      // [E] tokens placed so far
+  int* warp_cnt = run + num_experts;       // [NW][E]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  for (int i = tid; i < num_experts; i += kAlignThreads) {
+    hist[i] = 0;
+    run[i] = 0;
+  }
+  for (int i = tid; i < kAlignWarps * num_experts; i += kAlignThreads) warp_cnt[i] = 0;
+  __syncthreads();
+  // pass 1: histogram (ids outside [0, E) are ignored, like the reference's expert_map = -1 rows)
+  for (int i = tid; i < numel; i += kAlignThreads) {
+    const int e = topk_ids[i];
+    if (e >= 0 && e < num_experts) atomicAdd(&hist[e], 1);
+  }
+  __syncthreads();
+  // padded exclusive scan over experts (E <= 1024: one element per thread, warp-shuffle scan)
+  {
+    __shared__ int wsum[kAlignWarps];
+    const int cnt = tid < num_experts ? (hist[tid] + block_size - 1) / block_size * block_size : 0;
+    int incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = wsum[lane];
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, w, off);
+        if (lane >= off) w += t;
+      }
+      wsum[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const int base = warp > 0 ? wsum[warp - 1] : 0;
+    if (tid < num_experts) start[tid] = base + incl - cnt;
+    if (tid == num_experts - 1 || (num_experts > kAlignThreads && tid == kAlignThreads - 1))
+      start[num_experts] = base + incl;
+  }
+  __syncthreads();
+  const int total = start[num_experts];
+  if (tid == 0) *num_tokens_post_pad = total;
+  // expert id of every M-block; blocks past the padded total are 0 (reference: zero-initialised)
+  for (int b = tid; b < expert_ids_capacity; b += kAlignThreads) {
+    const int pos = b * block_size;
+    int e = 0;
+    if (pos < total) {
+      // binary search: last expert with start[e] <= pos
+      int lo = 0, hi = num_experts - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (start[mid] <= pos) lo = mid; else hi = mid - 1;
+      }
+      e = lo;
+    }
+    expert_ids[b] = e;
+  }
+  // padding sentinel everywhere first (entries are then overwritten by real tokens)
+  for (int i = tid; i < sorted_capacity; i += kAlignThreads) sorted_token_ids[i] = numel;
+  __syncthreads();
+  // pass 2: stable scatter, 1024 tokens per tile in flat-index order
+  for (int base = 0; base < numel; base += kAlignThreads) {
+    const int i = base + tid;
+    int e = -1;
+    if (i < numel) {
+      e = topk_ids[i];
+      if (e < 0 || e >= num_experts) e = -1;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, e);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const bool leader = rank == 0 && e >= 0;
+    if (leader) warp_cnt[warp * num_experts + e] = __popc(peers);
+    __syncthreads();
+    int pos = -1;
+    if (e >= 0) {
+      int before = 0;
+      for (int w = 0; w < warp; ++w) before += warp_cnt[w * num_experts + e];
+      pos = start[e] + run[e] + before + rank;
+    }
+    __syncthreads();
+    if (leader) {
+      atomicAdd(&run[e], __popc(peers));
+      warp_cnt[warp * num_experts + e] = 0;
+    }
+    if (pos >= 0 && pos < sorted_capacity) sorted_token_ids[pos] = i;
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// moe_sum
+// ---------------------------------------------------------------------------------------------
+template <typename T, int TOPK>
+__global__ void __launch_bounds__(256) moe_sum_kernel(T* __restrict__ out,
+                                                      const T* __restrict__ in, int topk, int d) {
+  const int64_t t = blockIdx.x;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    if (TOPK > 0) {
+      // accumulate in T, in j order, starting from 0 (moe_align_sum_kernels.cu:116-121)
+      T x = from_float<T>(0.f);
+#pragma unroll
+      for (int k = 0; k < TOPK; ++k)
+        x = from_float<T>(to_float<T>(x) + to_float<T>(in[(t * TOPK + k) * d + i]));
+      out[t * d + i] = x;
+    } else {
+      // other top-k: at::sum_out (fp32 accumulation, one rounding)
+      float x = 0.f;
+      for (int k = 0; k < topk; ++k) x += to_float<T>(in[(t * topk + k) * d + i]);
+      out[t * d + i] = from_float<T>(x);
+    }
+  }
+}
+
+}  // namespace vb200
+
+using namespace vb200;
+
+template <typename IndT>
+static int launch_topk(float* w, void* idx, int* tei, const float* g, int T, int E, int k,
+                       cudaStream_t s) {
+  const int grid = (T + 3) / 4;
+  const int vpt = (E + 31) / 32;
+#define TOPK_CASE(V)                                                                      \
+  if (vpt <= V) {                                                                         \
+    topk_softmax_kernel<V, IndT><<<grid, 128, 0, s>>>(w, (IndT*)idx, tei, g, T, E, k);    \
+    VB_LAUNCH_CHECK();                                                                    \
+    return 0;                                                                             \
+  }
+  TOPK_CASE(1) TOPK_CASE(2) TOPK_CASE(4) TOPK_CASE(8) TOPK_CASE(16) TOPK_CASE(32)
+#undef TOPK_CASE
+  VB_CHECK(false, "topk_softmax: num_experts %d > 1024 not supported", E);
+  return 0;
+}
+
+extern "C" int vb200_topk_softmax(float* topk_weights, void* topk_indices,
+                                  int32_t* token_expert_indices, const float* gating_output,
+                                  int num_tokens, int num_experts, int topk, int indices_dtype,
+                                  vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(topk >= 1 && topk <= num_experts, "topk %d must be in [1, num_experts %d]", topk,
+           num_experts);
+  if (num_tokens <= 0) return 0;
+  switch (indices_dtype) {
+    case VB200_I32:
+      return launch_topk<int32_t>(topk_weights, topk_indices, token_expert_indices, gating_output,
+                                  num_tokens, num_experts, topk, stream);
+    case VB200_U32:
+      return launch_topk<uint32_t>(topk_weights, topk_indices, token_expert_indices,
+                                   gating_output, num_tokens, num_experts, topk, stream);
+    case VB200_I64:
+      return launch_topk<int64_t>(topk_weights, topk_indices, token_expert_indices, gating_output,
+                                  num_tokens, num_experts, topk, stream);
+    default:
+      VB_CHECK(false, "topk_softmax: indices must be int32, uint32 or int64");
+  }
+  return 0;
+}
+
+extern "C" size_t vb200_moe_align_workspace_size(int numel, int num_experts) {
+  (void)numel;
+  (void)num_experts;
+  return 0;  // everything lives in shared memory
+}
+
+extern "C" int vb200_moe_align_block_size(const int32_t* topk_ids, int numel, int num_experts,
+                                          int block_size, int32_t* sorted_token_ids,
+                                          int sorted_capacity, int32_t* expert_ids,
+                                          int expert_ids_capacity, int32_t* num_tokens_post_pad,
+                                          void* workspace, size_t workspace_bytes,
+                                          vb200_stream_t stream_) {
+  (void)workspace;
+  (void)workspace_bytes;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(num_experts >= 1 && num_experts <= 1024,
+           "moe_align_block_size: num_experts %d must be in [1, 1024]", num_experts);
+  VB_CHECK(block_size >= 1, "moe_align_block_size: bad block_size %d", block_size);
+  const size_t smem = ((size_t)num_experts * 3 + 1 + (size_t)kAlignWarps * num_experts) * 4;
+  if (smem > 48 * 1024) {
+    VB_CUDA_CHECK(cudaFuncSetAttribute(moe_align_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  moe_align_kernel<<<1, kAlignThreads, smem, stream>>>(topk_ids, numel, num_experts, block_size,
+                                                       sorted_token_ids, sorted_capacity,
+                                                       expert_ids, expert_ids_capacity,
+                                                       num_tokens_post_pad);
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+#define DISPATCH_T(dt, ...)                                                 \
+  switch (dt) {                                                             \
+    case VB200_F32: { using scalar_t = float; __VA_ARGS__; break; }         \
+    case VB200_F16: { using scalar_t = __half; __VA_ARGS__; break; }        \
+    case VB200_BF16: { using scalar_t = __nv_bfloat16; __VA_ARGS__; break; } \
+    default: VB_CHECK(false, "unsupported dtype %d", dt);                   \
+  }
+
+extern "C" int vb200_moe_sum(void* out, const void* input, int num_tokens, int topk, int hidden,
+                             int dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (num_tokens <= 0 || hidden <= 0) return 0;
+  const int threads = hidden >= 256 ? 256 : 64;
+  DISPATCH_T(dtype, {
+    scalar_t* o = (scalar_t*)out;
+    const scalar_t* in = (const scalar_t*)input;
+    switch (topk) {
+      case 2: moe_sum_kernel<scalar_t, 2><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
+      case 3: moe_sum_kernel<scalar_t, 3><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
+      case 4: moe_sum_kernel<scalar_t, 4><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
+      default: moe_sum_kernel<scalar_t, 0><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
+    }
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}

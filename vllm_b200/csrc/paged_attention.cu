@@ -1,0 +1,667 @@
+// Paged-attention decode for sm_100a (paged_attention_v1 / v2 semantics of
+// /root/reference/csrc/attention/attention_kernels.cuh:81-664), designed for HBM streaming:
+//
+//  * one CTA per (sequence, kv-head [x group of 8 query heads], split-K partition): all query
+//    heads of a GQA group share ONE pass over the KV bytes (the reference re-reads K/V once per
+//    query head);
+//  * K/V go HBM -> registers with 16-byte / 8-byte streaming loads issued one 16-token tile ahead
+//    of the math (register double buffer), several CTAs per SM keep >= 64 KB in flight per SM;
+//  * QK^T and PV run on the warp-level tensor-core path (mma.sync m16n8k16, fp32 accumulate) with
+//    tokens on the M side and the (<= 8) query heads on the N side, so there is no padding waste
+//    for GQA-8 and the fp8 -> f16 dequant (cvt.f16x2.e4m3x2) is the only ALU work per byte;
+//    k_scale / v_scale are folded into the fp32 logits / output (exact products, one rounding
+//    fewer than the reference's bf16(k * scale));
+//  * the vLLM cache layouts are consumed as-is: a K "x-run" [token][x] is one 16-byte load, a V
+//    row [d][tokens] gives 4 consecutive tokens per load; a fixed permutation of the token and
+//    head-dim order inside a tile (legal because both are summed over) makes those loads line up
+//    with the MMA fragment layouts without any shared-memory transpose;
+//  * online softmax in the exp2 domain, per-warp (m, l, O) merged through shared memory, then
+//    either the final output or the v2 partials (normalised tmp_out, exp_sums, max_logits) with
+//    the reference's +1e-6 normalisers (attention_kernels.cuh:337,647).
+#include "common.cuh"
+
+namespace vb200 {
+
+struct PagedAttnParams {
+  void* out;          // [num_seqs, num_heads, head_size]
+  float* exp_sums;    // [num_seqs, num_heads, max_num_partitions]   (partitioned only)
+  float* max_logits;  // same
+  void* tmp_out;      // [num_seqs, num_heads, max_num_partitions, head_size]
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int* block_tables;
+  const int* seq_lens;
+  const float* alibi_slopes;
+  const float* k_scale;
+  const float* v_scale;
+  int num_heads, num_kv_heads, max_num_blocks_per_seq;
+  int partition_size;      // tokens; multiple of 16 and of BLOCK_SIZE
+  int max_num_partitions;  // 1 => write `out` directly
+  int64_t q_stride, kv_block_stride, kv_head_stride;
+  float scale;
+};
+
+template <typename T>
+struct MmaType;
+template <>
+struct MmaType<__half> {
+  static __device__ __forceinline__ void mma(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                             uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+        "{%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+template <>
+struct MmaType<__nv_bfloat16> {
+  static __device__ __forceinline__ void mma(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                             uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t v) {
+  uint32_t r;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// QT: query/output element type (__half / __nv_bfloat16).  FP8: cache holds e4m3 bytes (x = 16),
+// otherwise the cache element type is QT (x = 8).
+template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32, (HEAD_SIZE <= 128 ? (FP8 ? 3 : 2) : 1))
+    paged_attention_kernel(const PagedAttnParams p) {
+  using MT = typename std::conditional<FP8, __half, QT>::type;  // tensor-core operand type
+  using M = MmaType<MT>;
+  constexpr int X = FP8 ? 16 : 8;                 // elements per 16-byte K run
+  constexpr int CE = FP8 ? 1 : 2;                 // cache element bytes
+  constexpr int NCHUNK = HEAD_SIZE / X;           // K runs per token
+  constexpr int KI = (NCHUNK + 3) / 4;            // runs per thread (chunk = c + 4 i)
+  constexpr int KJ = X / 4;                       // MMAs per run
+  constexpr int NJ = (HEAD_SIZE + 15) / 16;       // 16-row d tiles for PV
+  constexpr int VW = FP8 ? 1 : 2;                 // 32-bit words per V load (4 tokens)
+  static_assert(HEAD_SIZE % X == 0, "head size must be a multiple of the K run");
+  static_assert(BLOCK_SIZE % 4 == 0, "block size must be a multiple of 4");
+
+  const int seq_idx = blockIdx.y;
+  const int part_idx = blockIdx.z;
+  const int num_q_per_kv = p.num_heads / p.num_kv_heads;
+  const int groups_per_kv = (num_q_per_kv + 7) >> 3;
+  const int kv_head = blockIdx.x / groups_per_kv;
+  const int hgroup = blockIdx.x - kv_head * groups_per_kv;
+  const int head0 = kv_head * num_q_per_kv + hgroup * 8;      // first query head of this CTA
+  const int nheads = min(8, num_q_per_kv - hgroup * 8);       // valid heads in this CTA
+
+  const int seq_len = p.seq_lens[seq_idx];
+  const int tok_begin = part_idx * p.partition_size;
+  if (tok_begin >= seq_len && !(seq_len <= 0 && part_idx == 0)) return;
+  const int tok_end = min(tok_begin + p.partition_size, seq_len);
+  const int ntok = max(tok_end - tok_begin, 0);
+  const int ntiles = (ntok + 15) >> 4;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int r = lane >> 2;  // 0..7
+  const int c = lane & 3;   // 0..3
+
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // layout: [NWARPS][8][HEAD_SIZE] fp32 O | [NWARPS][8] m | [NWARPS][8] l | block table ints
+  float* sm_o = reinterpret_cast<float*>(smem_raw);
+  float* sm_m = sm_o + NWARPS * 8 * HEAD_SIZE;
+  float* sm_l = sm_m + NWARPS * 8;
+  int* sm_bt = reinterpret_cast<int*>(sm_l + NWARPS * 8);
+
+  // ---- stage this partition's slice of the block table ---------------------------------------
+  const int* bt = p.block_tables + (int64_t)seq_idx * p.max_num_blocks_per_seq;
+  const int blk_begin = tok_begin / BLOCK_SIZE;
+  const int nblk = (ntok + BLOCK_SIZE - 1) / BLOCK_SIZE;
+  for (int i = tid; i < nblk; i += NWARPS * 32) sm_bt[i] = bt[blk_begin + i];
+
+  // ---- query fragments (B operand of QK^T): thread (r, c) holds head r, runs c + 4i ----------
+  uint32_t qf[KI][KJ][2];
+  {
+    const QT* qp = reinterpret_cast<const QT*>(p.q) + (int64_t)seq_idx * p.q_stride +
+                   (int64_t)(head0 + r) * HEAD_SIZE;
+    const bool hvalid = r < nheads;
+#pragma unroll
+    for (int i = 0; i < KI; ++i) {
+      const int chunk = c + 4 * i;
+#pragma unroll
+      for (int j = 0; j < KJ; ++j) {
+        uint32_t w0 = 0, w1 = 0;
+        if (hvalid && chunk < NCHUNK) {
+          const QT* e = qp + chunk * X + 4 * j;
+          if (std::is_same<QT, MT>::value) {
+            uint2 v = *reinterpret_cast<const uint2*>(e);
+            w0 = v.x;
+            w1 = v.y;
+          } else {
+            w0 = M::pack(to_float<QT>(e[0]), to_float<QT>(e[1]));
+            w1 = M::pack(to_float<QT>(e[2]), to_float<QT>(e[3]));
+          }
+        }
+        qf[i][j][0] = w0;
+        qf[i][j][1] = w1;
+      }
+    }
+  }
+
+  // logits are kept in the log2 domain: s2 = (q.k) * scale * k_scale * log2(e) (+ alibi * log2e)
+  float sl2 = p.scale * kLog2e;
+  if (FP8) sl2 *= *p.k_scale;
+  float alibi2[2] = {0.f, 0.f};
+  if (p.alibi_slopes != nullptr) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      if (2 * c + h < nheads) alibi2[h] = p.alibi_slopes[head0 + 2 * c + h] * kLog2e;
+  }
+
+  const unsigned char* kbase = reinterpret_cast<const unsigned char*>(p.k_cache) +
+                               (int64_t)kv_head * p.kv_head_stride * CE;
+  const unsigned char* vbase = reinterpret_cast<const unsigned char*>(p.v_cache) +
+                               (int64_t)kv_head * p.kv_head_stride * CE;
+  const int64_t blk_stride_b = p.kv_block_stride * CE;
+
+  // per-thread token slots inside a 16-token tile (see header comment):
+  //   QK^T rows: slot r <-> token t0 = 4*(r/2) + (r&1); slot r+8 <-> t0 + 2
+  //   PV k-slots of lane c <-> tokens 4c .. 4c+3
+  const int t0 = ((r >> 1) << 2) + (r & 1);
+
+  __syncthreads();  // block table staged
+
+  struct Tile {
+    uint4 ka[KI], kb[KI];
+    uint32_t va[NJ][VW], vb[NJ][VW];
+  };
+
+  auto load_tile = [&](Tile& t, int tile) {
+    const int T0 = tile << 4;  // token offset inside the partition
+    // K rows
+    const int ta = T0 + t0, tb = ta + 2;
+    const bool va_ok = ta < ntok, vb_ok = tb < ntok;
+    const int64_t pba = va_ok ? sm_bt[ta / BLOCK_SIZE] : 0;
+    const unsigned char* ka = kbase + pba * blk_stride_b + ((ta % BLOCK_SIZE) << 4);
+    const unsigned char* kb = ka + 32;  // tb = ta + 2 is in the same block (BLOCK_SIZE % 4 == 0)
+#pragma unroll
+    for (int i = 0; i < KI; ++i) {
+      const int chunk = c + 4 * i;
+      const bool cok = chunk < NCHUNK;
+      t.ka[i] = (va_ok && cok) ? ldg_stream_v4(ka + chunk * (BLOCK_SIZE * 16)) : make_uint4(0, 0, 0, 0);
+      t.kb[i] = (vb_ok && cok) ? ldg_stream_v4(kb + chunk * (BLOCK_SIZE * 16)) : make_uint4(0, 0, 0, 0);
+    }
+    // V rows: tokens T0 + 4c .. +3 of rows d = 16 j + r and + 8
+    const int tv = T0 + 4 * c;
+    const bool v_ok = tv < ntok;
+    const int64_t pbv = v_ok ? sm_bt[tv / BLOCK_SIZE] : 0;
+    const unsigned char* vp = vbase + pbv * blk_stride_b + (tv % BLOCK_SIZE) * CE;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int da = 16 * j + r, db = da + 8;
+      if (VW == 2) {
+        uint2 a = (v_ok && da < HEAD_SIZE) ? ldg_stream_v2(vp + da * (BLOCK_SIZE * CE)) : make_uint2(0, 0);
+        uint2 b = (v_ok && db < HEAD_SIZE) ? ldg_stream_v2(vp + db * (BLOCK_SIZE * CE)) : make_uint2(0, 0);
+        t.va[j][0] = a.x;
+        t.va[j][VW - 1] = a.y;
+        t.vb[j][0] = b.x;
+        t.vb[j][VW - 1] = b.y;
+      } else {
+        t.va[j][0] = (v_ok && da < HEAD_SIZE) ? ldg_stream_u32(vp + da * (BLOCK_SIZE * CE)) : 0u;
+        t.vb[j][0] = (v_ok && db < HEAD_SIZE) ? ldg_stream_u32(vp + db * (BLOCK_SIZE * CE)) : 0u;
+      }
+    }
+  };
+
+  float o[NJ][4];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY};  // running max (log2 domain) of heads 2c, 2c+1
+  float l_run[2] = {0.f, 0.f};              // this thread's partial sums
+
+  auto compute_tile = [&](Tile& t, int tile) {
+    const int T0 = tile << 4;
+    // ---- S^T = K Q^T ---------------------------------------------------------------------------
+    float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < KI; ++i) {
+      const uint32_t kaw[4] = {t.ka[i].x, t.ka[i].y, t.ka[i].z, t.ka[i].w};
+      const uint32_t kbw[4] = {t.kb[i].x, t.kb[i].y, t.kb[i].z, t.kb[i].w};
+#pragma unroll
+      for (int j = 0; j < KJ; ++j) {
+        uint32_t a0, a1, a2, a3;
+        if (FP8) {
+          a0 = e4m3x2_to_f16x2((uint16_t)(kaw[j] & 0xffffu));
+          a2 = e4m3x2_to_f16x2((uint16_t)(kaw[j] >> 16));
+          a1 = e4m3x2_to_f16x2((uint16_t)(kbw[j] & 0xffffu));
+          a3 = e4m3x2_to_f16x2((uint16_t)(kbw[j] >> 16));
+        } else {
+          a0 = kaw[2 * j];
+          a2 = kaw[2 * j + 1];
+          a1 = kbw[2 * j];
+          a3 = kbw[2 * j + 1];
+        }
+        M::mma(s, a0, a1, a2, a3, qf[i][j][0], qf[i][j][1]);
+      }
+    }
+    // ---- scale, alibi, mask --------------------------------------------------------------------
+    const int tok_a = T0 + t0, tok_b = tok_a + 2;  // partition-relative
+    {
+      const float pa = (float)(tok_begin + tok_a - seq_len + 1);
+      const float pb = (float)(tok_begin + tok_b - seq_len + 1);
+      s[0] = (tok_a < ntok) ? fmaf(s[0], sl2, alibi2[0] * pa) : -INFINITY;
+      s[1] = (tok_a < ntok) ? fmaf(s[1], sl2, alibi2[1] * pa) : -INFINITY;
+      s[2] = (tok_b < ntok) ? fmaf(s[2], sl2, alibi2[0] * pb) : -INFINITY;
+      s[3] = (tok_b < ntok) ? fmaf(s[3], sl2, alibi2[1] * pb) : -INFINITY;
+    }
+    // ---- online softmax: max over the 16 token rows (8 r-lanes x 2) ------------------------------
+    float mx0 = fmaxf(s[0], s[2]), mx1 = fmaxf(s[1], s[3]);
+#pragma unroll
+    for (int off = 4; off < 32; off <<= 1) {
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, off));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
+    }
+    const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+    const float corr0 = fast_exp2(m_run[0] - mn0), corr1 = fast_exp2(m_run[1] - mn1);
+    m_run[0] = mn0;
+    m_run[1] = mn1;
+    const float p0 = fast_exp2(s[0] - mn0), p1 = fast_exp2(s[1] - mn1);
+    const float p2 = fast_exp2(s[2] - mn0), p3 = fast_exp2(s[3] - mn1);
+    l_run[0] = fmaf(l_run[0], corr0, p0 + p2);
+    l_run[1] = fmaf(l_run[1], corr1, p1 + p3);
+    // P^T as B fragments: transpose the (token-slot x head) 8x8 blocks across the warp
+    const uint32_t b0 = movmatrix_trans(M::pack(p0, p1));
+    const uint32_t b1 = movmatrix_trans(M::pack(p2, p3));
+    // ---- O^T += V^T P^T ------------------------------------------------------------------------
+    // zero V of tokens past the end (they may hold NaN/Inf garbage)
+    uint32_t vmask0 = 0xffffffffu, vmask1 = 0xffffffffu;
+    if (T0 + 16 > ntok) {
+      const int nv = min(max(ntok - (T0 + 4 * c), 0), 4);
+      if (FP8) {
+        vmask0 = nv >= 4 ? 0xffffffffu : ((1u << (8 * nv)) - 1u);
+      } else {
+        vmask0 = nv >= 2 ? 0xffffffffu : (nv == 1 ? 0x0000ffffu : 0u);
+        vmask1 = nv >= 4 ? 0xffffffffu : (nv == 3 ? 0x0000ffffu : 0u);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      o[j][0] *= corr0;
+      o[j][1] *= corr1;
+      o[j][2] *= corr0;
+      o[j][3] *= corr1;
+      uint32_t a0, a1, a2, a3;
+      if (FP8) {
+        const uint32_t wa = t.va[j][0] & vmask0, wb = t.vb[j][0] & vmask0;
+        a0 = e4m3x2_to_f16x2((uint16_t)(wa & 0xffffu));
+        a2 = e4m3x2_to_f16x2((uint16_t)(wa >> 16));
+        a1 = e4m3x2_to_f16x2((uint16_t)(wb & 0xffffu));
+        a3 = e4m3x2_to_f16x2((uint16_t)(wb >> 16));
+      } else {
+        a0 = t.va[j][0] & vmask0;
+        a2 = t.va[j][VW - 1] & vmask1;
+        a1 = t.vb[j][0] & vmask0;
+        a3 = t.vb[j][VW - 1] & vmask1;
+      }
+      M::mma(o[j], a0, a1, a2, a3, b0, b1);
+    }
+  };
+
+  // ---- main loop: register double buffer, tiles strided over the warps -------------------------
+  {
+    Tile ta, tb;
+    int tile = warp;
+    if (tile < ntiles) load_tile(ta, tile);
+    while (tile < ntiles) {
+      const int n1 = tile + NWARPS;
+      if (n1 < ntiles) load_tile(tb, n1);
+      compute_tile(ta, tile);
+      if (n1 >= ntiles) break;
+      const int n2 = n1 + NWARPS;
+      if (n2 < ntiles) load_tile(ta, n2);
+      compute_tile(tb, n1);
+      tile = n2;
+    }
+  }
+
+  // ---- per-warp totals -> shared memory ---------------------------------------------------------
+#pragma unroll
+  for (int off = 4; off < 32; off <<= 1) {
+    l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], off);
+    l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], off);
+  }
+  if (r == 0) {
+    sm_m[warp * 8 + 2 * c] = m_run[0];
+    sm_m[warp * 8 + 2 * c + 1] = m_run[1];
+    sm_l[warp * 8 + 2 * c] = l_run[0];
+    sm_l[warp * 8 + 2 * c + 1] = l_run[1];
+  }
+  {
+    float* so = sm_o + warp * 8 * HEAD_SIZE;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int da = 16 * j + r, db = da + 8;
+      if (da < HEAD_SIZE) {
+        so[(2 * c) * HEAD_SIZE + da] = o[j][0];
+        so[(2 * c + 1) * HEAD_SIZE + da] = o[j][1];
+      }
+      if (db < HEAD_SIZE) {
+        so[(2 * c) * HEAD_SIZE + db] = o[j][2];
+        so[(2 * c + 1) * HEAD_SIZE + db] = o[j][3];
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- merge warps, normalise, write --------------------------------------------------------------
+  const float v_scale = FP8 ? *p.v_scale : 1.f;
+  const bool partitioned = p.max_num_partitions > 1;
+  for (int idx = tid; idx < nheads * HEAD_SIZE; idx += NWARPS * 32) {
+    const int h = idx / HEAD_SIZE;
+    const int d = idx - h * HEAD_SIZE;
+    float mg = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < NWARPS; ++w) mg = fmaxf(mg, sm_m[w * 8 + h]);
+    float lsum = 0.f, acc = 0.f;
+#pragma unroll
+    for (int w = 0; w < NWARPS; ++w) {
+      const float f = (sm_m[w * 8 + h] == -INFINITY) ? 0.f : fast_exp2(sm_m[w * 8 + h] - mg);
+      lsum = fmaf(sm_l[w * 8 + h], f, lsum);
+      acc = fmaf(sm_o[(w * 8 + h) * HEAD_SIZE + d], f, acc);
+    }
+    const float res = acc * v_scale * __fdividef(1.f, lsum + 1e-6f);
+    const int head = head0 + h;
+    if (partitioned) {
+      QT* dst = reinterpret_cast<QT*>(p.tmp_out) +
+                (((int64_t)seq_idx * p.num_heads + head) * p.max_num_partitions + part_idx) *
+                    HEAD_SIZE;
+      dst[d] = from_float<QT>(res);
+      if (d == 0) {
+        const int64_t o2 = ((int64_t)seq_idx * p.num_heads + head) * p.max_num_partitions + part_idx;
+        p.exp_sums[o2] = lsum;
+        p.max_logits[o2] = mg * kLn2;  // back to natural-log units, as the reference stores
+      }
+    } else {
+      QT* dst = reinterpret_cast<QT*>(p.out) + ((int64_t)seq_idx * p.num_heads + head) * HEAD_SIZE;
+      dst[d] = from_float<QT>(res);
+    }
+  }
+}
+
+// v2 reduce (attention_kernels.cuh:559-664): one warp per (seq, head).
+template <typename QT, int HEAD_SIZE>
+__global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
+    QT* __restrict__ out, const float* __restrict__ exp_sums, const float* __restrict__ max_logits,
+    const QT* __restrict__ tmp_out, const int* __restrict__ seq_lens, int num_heads,
+    int max_num_partitions, int partition_size, int total_rows) {
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);  // seq * num_heads + head
+  if (row >= total_rows) return;
+  const int lane = threadIdx.x & 31;
+  const int seq_idx = row / num_heads;
+  const int seq_len = seq_lens[seq_idx];
+  const int np = max(1, (seq_len + partition_size - 1) / partition_size);
+  const float* ml = max_logits + (int64_t)row * max_num_partitions;
+  const float* es = exp_sums + (int64_t)row * max_num_partitions;
+  const QT* tp = tmp_out + (int64_t)row * max_num_partitions * HEAD_SIZE;
+  QT* op = out + (int64_t)row * HEAD_SIZE;
+  if (np == 1) {  // copy (attention_kernels.cuh:577-589)
+    for (int d = lane; d < HEAD_SIZE; d += 32) op[d] = tp[d];
+    return;
+  }
+  float mg = -INFINITY;
+  for (int j = lane; j < np; j += 32) mg = fmaxf(mg, ml[j]);
+  mg = warp_max(mg);
+  float gsum = 0.f;
+  for (int j = lane; j < np; j += 32) gsum += es[j] * __expf(ml[j] - mg);
+  gsum = warp_sum(gsum);
+  const float inv = __fdividef(1.f, gsum + 1e-6f);
+  constexpr int PER = (HEAD_SIZE + 31) / 32;
+  float acc[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) acc[i] = 0.f;
+  for (int j = 0; j < np; ++j) {
+    const float w = es[j] * __expf(ml[j] - mg) * inv;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int d = lane + 32 * i;
+      if (d < HEAD_SIZE) acc[i] = fmaf(to_float<QT>(tp[(int64_t)j * HEAD_SIZE + d]), w, acc[i]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int d = lane + 32 * i;
+    if (d < HEAD_SIZE) op[d] = from_float<QT>(acc[i]);
+  }
+}
+
+constexpr int kWarps = 4;
+
+template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE>
+static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
+                     cudaStream_t stream) {
+  auto kern = paged_attention_kernel<QT, FP8, HEAD_SIZE, BLOCK_SIZE, kWarps>;
+  const int nblk = (p.partition_size + BLOCK_SIZE - 1) / BLOCK_SIZE;
+  const size_t smem = (size_t)kWarps * 8 * HEAD_SIZE * 4 + 2 * kWarps * 8 * 4 + (size_t)nblk * 4;
+  if (smem > 48 * 1024) {
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  const int q_per_kv = p.num_heads / p.num_kv_heads;
+  const int groups = (q_per_kv + 7) / 8;
+  dim3 grid(p.num_kv_heads * groups, num_seqs, num_partitions);
+  kern<<<grid, kWarps * 32, smem, stream>>>(p);
+  VB_LAUNCH_CHECK();
+  if (p.max_num_partitions > 1) {
+    const int rows = num_seqs * p.num_heads;
+    paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
+        (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
+        p.max_num_partitions, p.partition_size, rows);
+    VB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+template <typename QT, bool FP8, int HEAD_SIZE>
+static int dispatch_block(const PagedAttnParams& p, int block_size, int num_seqs, int np,
+                          cudaStream_t s) {
+  switch (block_size) {
+    case 8: return launch_pa<QT, FP8, HEAD_SIZE, 8>(p, num_seqs, np, s);
+    case 16: return launch_pa<QT, FP8, HEAD_SIZE, 16>(p, num_seqs, np, s);
+    case 32: return launch_pa<QT, FP8, HEAD_SIZE, 32>(p, num_seqs, np, s);
+    default: VB_CHECK(false, "Unsupported block size: %d", block_size);
+  }
+  return 0;
+}
+
+template <typename QT, bool FP8>
+static int dispatch_head(const PagedAttnParams& p, int head_size, int block_size, int num_seqs,
+                         int np, cudaStream_t s) {
+  switch (head_size) {
+    case 32: return dispatch_block<QT, FP8, 32>(p, block_size, num_seqs, np, s);
+    case 64: return dispatch_block<QT, FP8, 64>(p, block_size, num_seqs, np, s);
+    case 80: return dispatch_block<QT, FP8, 80>(p, block_size, num_seqs, np, s);
+    case 96: return dispatch_block<QT, FP8, 96>(p, block_size, num_seqs, np, s);
+    case 112: return dispatch_block<QT, FP8, 112>(p, block_size, num_seqs, np, s);
+    case 128: return dispatch_block<QT, FP8, 128>(p, block_size, num_seqs, np, s);
+    case 192: return dispatch_block<QT, FP8, 192>(p, block_size, num_seqs, np, s);
+    case 256: return dispatch_block<QT, FP8, 256>(p, block_size, num_seqs, np, s);
+    default: break;
+  }
+  if (!FP8 && head_size == 120) {
+    // 120 is not a multiple of the fp8 run (16); the reference's fp8 tests skip it as well.
+    return dispatch_block<QT, false, 120>(p, block_size, num_seqs, np, s);
+  }
+  VB_CHECK(false, "Unsupported head size: %d", head_size);
+  return 0;
+}
+
+static int run_paged_attention(PagedAttnParams& p, int num_seqs, int head_size, int block_size,
+                               int max_seq_len, int q_dtype, int kv_dtype, cudaStream_t stream) {
+  VB_CHECK(q_dtype == VB200_F16 || q_dtype == VB200_BF16,
+           "paged attention: query dtype must be f16 or bf16 (got %d)", q_dtype);
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3,
+           "Unsupported data type of kv cache: %d", kv_dtype);
+  VB_CHECK(p.num_kv_heads > 0 && p.num_heads % p.num_kv_heads == 0,
+           "num_heads %d must be a multiple of num_kv_heads %d", p.num_heads, p.num_kv_heads);
+  VB_CHECK(p.partition_size % 16 == 0 && p.partition_size % block_size == 0,
+           "partition size %d must be a multiple of 16 and of the block size", p.partition_size);
+  if (num_seqs <= 0) return 0;
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (p.k_scale && p.v_scale), "fp8 kv cache needs k_scale and v_scale");
+  (void)max_seq_len;
+  const int np = p.max_num_partitions;
+  if (q_dtype == VB200_F16) {
+    return fp8 ? dispatch_head<__half, true>(p, head_size, block_size, num_seqs, np, stream)
+               : dispatch_head<__half, false>(p, head_size, block_size, num_seqs, np, stream);
+  }
+  return fp8 ? dispatch_head<__nv_bfloat16, true>(p, head_size, block_size, num_seqs, np, stream)
+             : dispatch_head<__nv_bfloat16, false>(p, head_size, block_size, num_seqs, np, stream);
+}
+
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+}  // namespace vb200
+
+using namespace vb200;
+
+extern "C" int vb200_paged_attention_v2(
+    void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
+    const void* key_cache, const void* value_cache, int num_seqs, int num_heads, int head_size,
+    int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens,
+    int block_size, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes,
+    int q_dtype, int kv_dtype, const float* k_scale, const float* v_scale, int64_t q_stride,
+    int64_t kv_block_stride, int64_t kv_head_stride, int partition_size, vb200_stream_t stream) {
+  VB_CHECK(partition_size > 0, "partition_size must be positive");
+  PagedAttnParams p;
+  p.out = out;
+  p.exp_sums = exp_sums;
+  p.max_logits = max_logits;
+  p.tmp_out = tmp_out;
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  p.partition_size = partition_size;
+  p.max_num_partitions = (max_seq_len + partition_size - 1) / partition_size;
+  if (p.max_num_partitions < 1) p.max_num_partitions = 1;
+  p.q_stride = q_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  p.scale = scale;
+  // With a single partition the kernel writes `out` directly (the reference's reduce kernel
+  // would copy tmp_out -> out; same result), and leaves the partial buffers untouched.
+  return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
+                             (cudaStream_t)stream);
+}
+
+extern "C" int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads,
+                                                       int num_kv_heads, int max_seq_len,
+                                                       int block_size) {
+  // Split-K so that the grid covers the 148 SMs x 4 resident CTAs at least ~4 times while a
+  // partition stays >= 256 tokens (8 tiles per warp amortise the prologue / merge).
+  if (num_seqs <= 0 || num_kv_heads <= 0) return 0;
+  const int q_per_kv = num_heads / num_kv_heads;
+  const int groups = (q_per_kv + 7) / 8;
+  const long base_ctas = (long)num_seqs * num_kv_heads * groups;
+  const long target = 4L * num_sms() * 4;
+  int part = round_up(max_seq_len > 0 ? max_seq_len : 16, 32);
+  if (part < block_size) part = block_size;
+  while (part > 256 && base_ctas * ((max_seq_len + part - 1) / part) < target) part = round_up(part / 2, 32);
+  if (part > 8192) part = 8192;
+  return part;
+}
+
+extern "C" size_t vb200_paged_attention_v1_workspace_size(int num_seqs, int num_heads,
+                                                          int head_size, int max_seq_len,
+                                                          int q_dtype, int partition_size) {
+  (void)q_dtype;
+  if (partition_size <= 0 || max_seq_len <= partition_size) return 0;
+  const size_t np = (size_t)(max_seq_len + partition_size - 1) / partition_size;
+  const size_t rows = (size_t)num_seqs * num_heads * np;
+  return rows * 4 * 2 + rows * head_size * 2 + 64;
+}
+
+extern "C" int vb200_paged_attention_v1(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs,
+    int num_heads, int head_size, int num_kv_heads, float scale, const int32_t* block_tables,
+    const int32_t* seq_lens, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+    const float* alibi_slopes, int q_dtype, int kv_dtype, const float* k_scale,
+    const float* v_scale, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int partition_size, void* workspace, size_t workspace_bytes, vb200_stream_t stream) {
+  int part = partition_size;
+  if (workspace == nullptr) {
+    part = 0;
+  } else if (part <= 0) {
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, max_seq_len,
+                                                   block_size);
+  }
+  int np = 1;
+  if (part > 0 && max_seq_len > part) np = (max_seq_len + part - 1) / part;
+  if (np == 1) {
+    part = round_up(max_seq_len > 0 ? max_seq_len : 16, 32);
+    if (part % block_size) part = round_up(part, block_size);
+  }
+  PagedAttnParams p;
+  p.out = out;
+  p.exp_sums = nullptr;
+  p.max_logits = nullptr;
+  p.tmp_out = nullptr;
+  if (np > 1) {
+    const size_t need = vb200_paged_attention_v1_workspace_size(num_seqs, num_heads, head_size,
+                                                                max_seq_len, q_dtype, part);
+    VB_CHECK(workspace_bytes >= need, "paged_attention_v1 workspace too small: %zu < %zu",
+             workspace_bytes, need);
+    const size_t rows = (size_t)num_seqs * num_heads * np;
+    p.exp_sums = reinterpret_cast<float*>(workspace);
+    p.max_logits = p.exp_sums + rows;
+    p.tmp_out = reinterpret_cast<void*>(p.max_logits + rows);
+  }
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  p.partition_size = part;
+  p.max_num_partitions = np;
+  p.q_stride = q_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  p.scale = scale;
+  return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
+                             (cudaStream_t)stream);
+}
