@@ -1,0 +1,128 @@
+#!/usr/bin/env python3
+"""Micro-benchmark of paged-attention decode at the BASELINE configs: achieved HBM GB/s (algorithmic bytes,
+SURVEY.md 8d) vs the measured copy peak, next to the reference's own CUDA kernel (torch.ops._ref_C, test infra).
+Inputs are larger than L2 (126 MB) and block tables are random permutations, so every iteration streams from HBM.
+Usage: python benchmarks/bench_paged_attention.py [--cfg 2|3|5|all] [--iters 20] [--partition N] [--no-ref]"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+CFGS = {
+    "2": dict(num_seqs=64, ctx=2048, H=32, Hkv=8, D=128, kvd="auto"),
+    "3": dict(num_seqs=256, ctx=4096, H=32, Hkv=8, D=128, kvd="fp8"),
+    "5": dict(num_seqs=128, ctx=8192, H=8, Hkv=1, D=128, kvd="fp8"),
+    "2r": dict(num_seqs=64, ctx=2048, H=32, Hkv=8, D=128, kvd="auto", ragged=True),
+}
+
+
+def peak_gbs():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def make(cfg, dev="cuda"):
+    torch.manual_seed(0)
+    S, ctx, H, Hkv, D = cfg["num_seqs"], cfg["ctx"], cfg["H"], cfg["Hkv"], cfg["D"]
+    bs = 16
+    fp8 = cfg["kvd"] == "fp8"
+    x = 16 if fp8 else 8
+    blocks_per_seq = ctx // bs
+    nb = S * blocks_per_seq + 1024
+    if fp8:
+        kc = torch.randint(0, 120, (nb, Hkv, D // x, bs, x), dtype=torch.uint8, device=dev)  # finite e4m3 codes
+        vc = torch.randint(0, 120, (nb, Hkv, D, bs), dtype=torch.uint8, device=dev)
+        kc |= (torch.randint(0, 2, kc.shape, dtype=torch.uint8, device=dev) << 7)
+        vc |= (torch.randint(0, 2, vc.shape, dtype=torch.uint8, device=dev) << 7)
+        sc = 0.01
+    else:
+        kc = torch.empty(nb, Hkv, D // x, bs, x, dtype=torch.bfloat16, device=dev).normal_()
+        vc = torch.empty(nb, Hkv, D, bs, dtype=torch.bfloat16, device=dev).normal_()
+        sc = 1.0
+    q = (torch.randn(S, H, D, device=dev) * 0.3).bfloat16()
+    bt = torch.randperm(nb, device=dev)[: S * blocks_per_seq].to(torch.int32).reshape(S, blocks_per_seq)
+    if cfg.get("ragged"):
+        sl = torch.randint(ctx // 2 + 1, ctx + 1, (S,), dtype=torch.int32, device=dev)
+    else:
+        sl = torch.full((S,), ctx, dtype=torch.int32, device=dev)
+    scale_t = torch.full((1,), sc, device=dev)
+    return q, kc, vc, bt, sl, scale_t
+
+
+def algo_bytes(cfg, sl):
+    ce = 1 if cfg["kvd"] == "fp8" else 2
+    tot = int(sl.sum().item())
+    kv = tot * cfg["Hkv"] * cfg["D"] * 2 * ce
+    qo = 2 * cfg["num_seqs"] * cfg["H"] * cfg["D"] * 2
+    btb = int(((sl + 15) // 16).sum().item()) * 4 + 4 * cfg["num_seqs"]
+    return kv + qo + btb
+
+
+def timeit(fn, iters, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        ts.append(a.elapsed_time(b) * 1e-3)
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cfg", default="all")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--partition", type=int, default=0)
+    ap.add_argument("--no-ref", action="store_true")
+    a = ap.parse_args()
+    from vllm_b200 import _custom_ops as ops
+    from parity_utils import load_ref_cuda
+    ref = None if a.no_ref else load_ref_cuda()
+    peak, how = peak_gbs()
+    names = list(CFGS) if a.cfg == "all" else a.cfg.split(",")
+    for name in names:
+        cfg = CFGS[name]
+        q, kc, vc, bt, sl, sc = make(cfg)
+        out = torch.empty_like(q)
+        nbytes = algo_bytes(cfg, sl)
+        max_len = int(sl.max())
+        scale = cfg["D"] ** -0.5
+
+        def ours():
+            ops.paged_attention_v1(out, q, kc, vc, cfg["Hkv"], scale, bt, sl, 16, max_len, None, cfg["kvd"], sc, sc,
+                                   partition_size=a.partition)
+        med, best = timeit(ours, a.iters)
+        row = {"cfg": name, **{k: v for k, v in cfg.items()}, "algo_MB": round(nbytes / 1e6, 2),
+               "ours_us": round(med * 1e6, 1), "ours_best_us": round(best * 1e6, 1),
+               "ours_GBs": round(nbytes / med / 1e9, 1), "frac_of_%s_peak" % how: round(nbytes / med / 1e9 / peak, 3)}
+        if ref is not None:
+            out_r = torch.empty_like(q)
+
+            def theirs():
+                ref.paged_attention_v1(out_r, q, kc, vc, cfg["Hkv"], scale, bt, sl, 16, max_len, None, cfg["kvd"], sc, sc,
+                                       0, 0, 0, 64, 0)
+            medr, _ = timeit(theirs, max(3, a.iters // 4))
+            row.update(ref_v1_us=round(medr * 1e6, 1), ref_v1_GBs=round(nbytes / medr / 1e9, 1),
+                       speedup_vs_ref=round(medr / med, 2),
+                       max_abs_diff_vs_ref=float((out.float() - out_r.float()).abs().max()))
+        print(json.dumps(row), flush=True)
+        del q, kc, vc, bt, sl
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()

@@ -229,3 +229,184 @@ def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0,
         check(load().vb200_convert_fp8(ptr(output), ptr(input), input.numel(),
                                        dtype_enum(output.dtype), dtype_enum(input.dtype),
                                        float(scale), stream()))
+
+
+# ------------------------------------------------------------------------------------------------
+# fp8 activation quantisation + activation  (reference: vllm/_custom_ops.py:1244-1304, :111)
+# ------------------------------------------------------------------------------------------------
+FP8_DTYPE = torch.float8_e4m3fn
+
+
+def _quant_in(input: torch.Tensor, output: torch.Tensor):
+    require_cuda(input, output)
+    if input.dim() != 2 or not input.is_contiguous() or not output.is_contiguous():
+        raise RuntimeError("fp8 quant: input and output must be contiguous 2-D tensors")
+    if output.element_size() != 1 or output.shape[1] != input.shape[1] or output.shape[0] < input.shape[0]:
+        raise RuntimeError("fp8 quant: output must be a 1-byte tensor of (at least) the input's shape")
+    return input.shape[0], input.shape[1], dtype_enum(input.dtype)
+
+
+def static_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor) -> None:
+    """torch.ops._C.static_scaled_fp8_quant (csrc/torch_bindings.cpp:575-577)."""
+    m, k, dt = _quant_in(input, result)
+    require_cuda(scale)
+    with _device_of(input):
+        check(load().vb200_static_scaled_fp8_quant(ptr(result), ptr(input), ptr(scale), m, k, dt, stream()))
+
+
+def dynamic_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor) -> None:
+    """torch.ops._C.dynamic_scaled_fp8_quant (csrc/torch_bindings.cpp:581-584); `scale` must be
+    pre-zeroed by the caller (vllm/_custom_ops.py:1297)."""
+    m, k, dt = _quant_in(input, result)
+    require_cuda(scale)
+    with _device_of(input):
+        check(load().vb200_dynamic_scaled_fp8_quant(ptr(result), ptr(input), ptr(scale), m, k, dt, stream()))
+
+
+def dynamic_per_token_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor,
+                                       scale_ub: Optional[torch.Tensor] = None) -> None:
+    """torch.ops._C.dynamic_per_token_scaled_fp8_quant (csrc/torch_bindings.cpp:588-591)."""
+    m, k, dt = _quant_in(input, result)
+    require_cuda(scale, scale_ub)
+    if scale.numel() < m or not scale.is_contiguous():
+        raise RuntimeError("per-token quant: scale must be a contiguous fp32 tensor with one entry per row")
+    with _device_of(input):
+        check(load().vb200_dynamic_per_token_scaled_fp8_quant(ptr(result), ptr(input), ptr(scale),
+                                                              ptr(scale_ub), m, k, dt, stream()))
+
+
+def scaled_fp8_quant(
+    input: torch.Tensor,
+    scale: Optional[torch.Tensor] = None,
+    num_token_padding: Optional[int] = None,
+    scale_ub: Optional[torch.Tensor] = None,
+    use_per_token_if_dynamic: bool = False,
+    output: Optional[torch.Tensor] = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """vllm/_custom_ops.py:1244-1304, same allocation and dispatch rules."""
+    assert input.ndim == 2
+    shape = input.shape
+    if num_token_padding:
+        shape = (max(num_token_padding, input.shape[0]), shape[1])
+    if output is None:
+        output = torch.empty(shape, device=input.device, dtype=FP8_DTYPE)
+    else:
+        assert num_token_padding is None, "padding not supported if output passed in"
+        assert output.dtype == FP8_DTYPE
+    if scale is None:
+        if use_per_token_if_dynamic:
+            scale = torch.empty((shape[0], 1), device=input.device, dtype=torch.float32)
+            dynamic_per_token_scaled_fp8_quant(output, input.contiguous(), scale, scale_ub)
+        else:
+            scale = torch.zeros(1, device=input.device, dtype=torch.float32)
+            dynamic_scaled_fp8_quant(output, input.contiguous(), scale)
+    else:
+        assert scale.numel() == 1, f"{scale.shape}"
+        static_scaled_fp8_quant(output, input.contiguous(), scale)
+    return output, scale
+
+
+def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    """torch.ops._C.silu_and_mul (csrc/torch_bindings.cpp:111): x [..., 2d] -> out [..., d]."""
+    require_cuda(out, x)
+    d = x.shape[-1] // 2
+    if not (x.is_contiguous() and out.is_contiguous()) or out.shape[-1] != d or out.dtype != x.dtype:
+        raise RuntimeError("silu_and_mul: contiguous x [..., 2d] and out [..., d] of one dtype")
+    n = x.numel() // max(x.shape[-1], 1)
+    with _device_of(x):
+        check(load().vb200_silu_and_mul(ptr(out), ptr(x), n, d, dtype_enum(x.dtype), stream()))
+
+
+# ------------------------------------------------------------------------------------------------
+# fp8 w8a8 linear  (reference: vllm/_custom_ops.py:688-741)
+# ------------------------------------------------------------------------------------------------
+def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
+    return bool(load().vb200_cutlass_scaled_mm_supports_fp8(int(cuda_device_capability)))
+
+
+def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor,
+                          scale_b: torch.Tensor, bias: Optional[torch.Tensor] = None) -> None:
+    """torch.ops._C.cutlass_scaled_mm (csrc/torch_bindings.cpp:422-426) with the checks of
+    csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:169-187."""
+    require_cuda(out, a, b, scale_a, scale_b, bias)
+    if a.dim() != 2 or b.dim() != 2 or out.dim() != 2:
+        raise RuntimeError("cutlass_scaled_mm: a, b, out must be 2-D")
+    m, k = a.shape
+    n = b.shape[1]
+    if out.shape[0] != m or b.shape[0] != k or out.shape[1] != n:
+        raise RuntimeError("cutlass_scaled_mm: shape mismatch")
+    if a.stride(1) != 1 or out.stride(1) != 1 or b.stride(0) != 1:
+        raise RuntimeError("cutlass_scaled_mm: a/out must be row-major and b column-major")
+    if out.stride(0) % 16 or b.stride(1) % 16:
+        raise RuntimeError("cutlass_scaled_mm: out.stride(0) and b.stride(1) must be multiples of 16")
+    if a.dtype != FP8_DTYPE or b.dtype != FP8_DTYPE:
+        raise RuntimeError("cutlass_scaled_mm: only the fp8 e4m3 path is built (a and b must be float8_e4m3fn)")
+    if scale_a.dtype != torch.float32 or scale_b.dtype != torch.float32:
+        raise RuntimeError("cutlass_scaled_mm: scales must be fp32")
+    if scale_a.numel() not in (1, m) or scale_b.numel() not in (1, n):
+        raise RuntimeError("cutlass_scaled_mm: scale_a must have 1 or M entries, scale_b 1 or N")
+    if not (scale_a.is_contiguous() and scale_b.is_contiguous()):
+        raise RuntimeError("cutlass_scaled_mm: scales must be contiguous")
+    if bias is not None and (bias.numel() != n or not bias.is_contiguous() or bias.dtype != out.dtype):
+        raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of the output dtype")
+    with _device_of(a):
+        check(load().vb200_cutlass_scaled_mm(
+            ptr(out), ptr(a), ptr(b), ptr(scale_a), ptr(scale_b), ptr(bias), m, n, k, a.stride(0),
+            b.stride(1), out.stride(0), scale_a.numel(), scale_b.numel(), dtype_enum(out.dtype), stream()))
+
+
+def cutlass_scaled_mm(a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor, scale_b: torch.Tensor,
+                      out_dtype: torch.dtype, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """vllm/_custom_ops.py:697-741 (no Triton fallback: incompatible shapes raise)."""
+    assert out_dtype is torch.bfloat16 or out_dtype is torch.float16
+    assert bias is None or bias.shape[0] == b.shape[1] and bias.dtype == out_dtype
+    if b.shape[0] % 16 or b.shape[1] % 16:
+        raise RuntimeError("cutlass_scaled_mm: K and N must be multiples of 16")
+    out = torch.empty((a.shape[0], b.shape[1]), dtype=out_dtype, device=a.device)
+    cutlass_scaled_mm_out(out, a, b, scale_a, scale_b, bias)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# MoE routing  (reference: vllm/_custom_ops.py:1512-1548)
+# ------------------------------------------------------------------------------------------------
+def topk_softmax(topk_weights: torch.Tensor, topk_ids: torch.Tensor, token_expert_indices: torch.Tensor,
+                 gating_output: torch.Tensor) -> None:
+    """torch.ops._moe_C.topk_softmax (csrc/moe/torch_bindings.cpp:6-8)."""
+    require_cuda(topk_weights, topk_ids, token_expert_indices, gating_output)
+    if gating_output.dtype != torch.float32 or not gating_output.is_contiguous():
+        raise RuntimeError("topk_softmax: gating_output must be contiguous fp32")
+    if topk_weights.dtype != torch.float32 or token_expert_indices.dtype != torch.int32:
+        raise RuntimeError("topk_softmax: topk_weights fp32, token_expert_indices int32")
+    num_experts = gating_output.shape[-1]
+    num_tokens = gating_output.numel() // num_experts
+    topk = topk_weights.shape[-1]
+    with _device_of(gating_output):
+        check(load().vb200_topk_softmax(ptr(topk_weights), ptr(topk_ids), ptr(token_expert_indices),
+                                        ptr(gating_output), num_tokens, num_experts, topk,
+                                        dtype_enum(topk_ids.dtype), stream()))
+
+
+def moe_align_block_size(topk_ids: torch.Tensor, num_experts: int, block_size: int,
+                         sorted_token_ids: torch.Tensor, experts_ids: torch.Tensor,
+                         num_tokens_post_pad: torch.Tensor) -> None:
+    """torch.ops._moe_C.moe_align_block_size (csrc/moe/torch_bindings.cpp:18-22)."""
+    require_cuda(topk_ids, sorted_token_ids, experts_ids, num_tokens_post_pad)
+    for t in (topk_ids, sorted_token_ids, experts_ids, num_tokens_post_pad):
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise RuntimeError("moe_align_block_size: all tensors must be contiguous int32")
+    with _device_of(topk_ids):
+        check(load().vb200_moe_align_block_size(
+            ptr(topk_ids), topk_ids.numel(), num_experts, block_size, ptr(sorted_token_ids),
+            sorted_token_ids.numel(), ptr(experts_ids), experts_ids.numel(), ptr(num_tokens_post_pad),
+            None, 0, stream()))
+
+
+def moe_sum(input: torch.Tensor, output: torch.Tensor) -> None:
+    """torch.ops._moe_C.moe_sum (csrc/moe/torch_bindings.cpp:13): input [T, k, H] -> output [T, H]."""
+    require_cuda(input, output)
+    if input.dim() != 3 or not (input.is_contiguous() and output.is_contiguous()):
+        raise RuntimeError("moe_sum: contiguous input [T, k, H] and output [T, H]")
+    t, k, h = input.shape
+    with _device_of(input):
+        check(load().vb200_moe_sum(ptr(output), ptr(input), t, k, h, dtype_enum(input.dtype), stream()))
