@@ -123,7 +123,8 @@ int vb200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void
 size_t vb200_paged_attention_v1_workspace_size(int num_seqs, int num_heads, int head_size,
                                                int max_seq_len, int q_dtype, int partition_size);
 int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads, int num_kv_heads,
-                                            int max_seq_len, int block_size);
+                                            int head_size, int max_seq_len, int block_size,
+                                            int kv_dtype);
 int vb200_paged_attention_v1(void* out, const void* query, const void* key_cache,
                              const void* value_cache, int num_seqs, int num_heads, int head_size,
                              int num_kv_heads, float scale, const int32_t* block_tables,

@@ -91,7 +91,7 @@ def paged_attention_v1(
         if partition_size >= 0:
             if partition_size == 0:
                 partition_size = lib.vb200_paged_attention_v1_partition_size(
-                    num_seqs, num_heads, num_kv_heads, max_seq_len, block_size)
+                    num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size, kvd)
             ws_bytes = lib.vb200_paged_attention_v1_workspace_size(
                 num_seqs, num_heads, head_size, max_seq_len, qd, partition_size)
             if ws_bytes > 0:

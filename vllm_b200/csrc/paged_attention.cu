@@ -458,6 +458,7 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
 }
 
 constexpr int kWarps = 4;
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE>
 static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
@@ -540,8 +541,6 @@ static int run_paged_attention(PagedAttnParams& p, int num_seqs, int head_size, 
              : dispatch_head<__nv_bfloat16, false>(p, head_size, block_size, num_seqs, np, stream);
 }
 
-static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
-
 }  // namespace vb200
 
 using namespace vb200;
@@ -583,21 +582,40 @@ extern "C" int vb200_paged_attention_v2(
                              (cudaStream_t)stream);
 }
 
+// resident CTAs per SM of the main kernel (its __launch_bounds__ minimum)
+static inline int pa_ctas_per_sm(int head_size, int kv_dtype) {
+  return head_size <= 128 ? (kv_dtype == VB200_KV_FP8_E4M3 ? 3 : 2) : 1;
+}
+
 extern "C" int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads,
-                                                       int num_kv_heads, int max_seq_len,
-                                                       int block_size) {
-  // Split-K so that the grid covers the 148 SMs x 4 resident CTAs at least ~4 times while a
-  // partition stays >= 256 tokens (8 tiles per warp amortise the prologue / merge).
+                                                       int num_kv_heads, int head_size,
+                                                       int max_seq_len, int block_size,
+                                                       int kv_dtype) {
+  // Split-K cost model: time ~ waves(np) * (tokens per partition + fixed per-CTA overhead), where
+  // a wave is num_sms x resident CTAs.  Picks the np (not only powers of two) that fills whole
+  // waves; no split when the unsplit grid already covers the machine.
   if (num_seqs <= 0 || num_kv_heads <= 0) return 0;
   const int q_per_kv = num_heads / num_kv_heads;
   const int groups = (q_per_kv + 7) / 8;
   const long base_ctas = (long)num_seqs * num_kv_heads * groups;
-  const long target = 4L * num_sms() * 4;
-  int part = round_up(max_seq_len > 0 ? max_seq_len : 16, 32);
-  if (part < block_size) part = block_size;
-  while (part > 256 && base_ctas * ((max_seq_len + part - 1) / part) < target) part = round_up(part / 2, 32);
-  if (part > 8192) part = 8192;
-  return part;
+  const long resident = (long)num_sms() * pa_ctas_per_sm(head_size, kv_dtype);
+  const int align = block_size > 32 ? block_size : 32;
+  const int len = max_seq_len > 0 ? max_seq_len : 16;
+  const long kOverheadTokens = 256;
+  long best_cost = -1;
+  int best_part = round_up(len, align);
+  for (int np = 1; np <= 64; ++np) {
+    const int part = round_up((len + np - 1) / np, align);
+    if (np > 1 && part < 128) break;
+    const int np_eff = (len + part - 1) / part;
+    const long waves = (base_ctas * np_eff + resident - 1) / resident;
+    const long cost = waves * (part + kOverheadTokens) + (np_eff > 1 ? 64 : 0);
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best_part = part;
+    }
+  }
+  return best_part;
 }
 
 extern "C" size_t vb200_paged_attention_v1_workspace_size(int num_seqs, int num_heads,
@@ -621,8 +639,8 @@ extern "C" int vb200_paged_attention_v1(
   if (workspace == nullptr) {
     part = 0;
   } else if (part <= 0) {
-    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, max_seq_len,
-                                                   block_size);
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size,
+                                                   max_seq_len, block_size, kv_dtype);
   }
   int np = 1;
   if (part > 0 && max_seq_len > part) np = (max_seq_len + part - 1) / part;

@@ -80,9 +80,9 @@ __device__ __forceinline__ float block_max_256(float v, float* sm) {
   v = warp_max(v);
   if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
   __syncthreads();
-  float r = (threadIdx.x < (blockDim.x >> 5)) ? sm[threadIdx.x] : 0.f;
-  r = warp_max(r);
-  return __shfl_sync(0xffffffffu, r, 0);
+  // every warp reduces the per-warp maxima itself, so all threads return the block maximum
+  float r = ((threadIdx.x & 31) < (blockDim.x >> 5)) ? sm[threadIdx.x & 31] : 0.f;
+  return warp_max(r);
 }
 
 // per-tensor absmax / 448 -> atomic max into *scale (pre-zeroed by the caller), common.cuh:64-99
