@@ -170,12 +170,17 @@ int vb200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, 
  *   [N,K] weight, row stride ldb;  out [M,N] of out_dtype (bf16/f16), row stride ldc;
  *   a_scales fp32, numel 1 or M;  b_scales fp32, numel 1 or N;  bias NULL or [N] of out_dtype.
  * Requires K % 16 == 0 and N % 16 == 0 (vllm/_custom_ops.py:732-736).
- * The tcgen05/TMA kernel needs TMA descriptors built on the host per call (driver entry point
- * resolved at load time; no allocation, graph-capturable). */
+ * The tcgen05/TMA kernel builds its TMA descriptors on the host per call (driver entry point
+ * resolved at load time; no allocation, graph-capturable).  `workspace`: device scratch of
+ * vb200_cutlass_scaled_mm_workspace_size(M, N, K) bytes whose first 16 KiB (split-K tickets) must
+ * be ZERO on first use; every launch leaves them zero.  May be NULL when the size query returns
+ * the ticket region only and the problem needs no K split. */
+size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K);
 int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b, const float* a_scales,
                             const float* b_scales, const void* bias, int M, int N, int K,
                             int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
-                            int b_scales_numel, int out_dtype, vb200_stream_t stream);
+                            int b_scales_numel, int out_dtype, void* workspace,
+                            size_t workspace_bytes, vb200_stream_t stream);
 /* cutlass_scaled_mm_supports_fp8(cuda_device_capability): torch_bindings.cpp:441 */
 int vb200_cutlass_scaled_mm_supports_fp8(int cuda_device_capability);
 

@@ -324,6 +324,24 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     return bool(load().vb200_cutlass_scaled_mm_supports_fp8(int(cuda_device_capability)))
 
 
+_GEMM_WS = {}       # device index -> zero-initialised workspace (split-K tickets + partials)
+_GEMM_WS_KEEP = []  # superseded buffers stay alive: captured CUDA graphs may still point at them
+
+
+def _gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Per-device scratch for the tcgen05 GEMMs.  The first 16 KiB (tickets) must be zero on first
+    use and are left zero by every launch, so the buffer is allocated once with torch.zeros and only
+    ever grown.  One workspace per device: GEMMs are assumed to run on one stream at a time (as in
+    vLLM's worker); warm up before CUDA-graph capture so that no growth happens while capturing."""
+    ws = _GEMM_WS.get(device.index)
+    if ws is None or ws.numel() < nbytes:
+        if ws is not None:
+            _GEMM_WS_KEEP.append(ws)
+        ws = torch.zeros(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
+        _GEMM_WS[device.index] = ws
+    return ws
+
+
 def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor,
                           scale_b: torch.Tensor, bias: Optional[torch.Tensor] = None) -> None:
     """torch.ops._C.cutlass_scaled_mm (csrc/torch_bindings.cpp:422-426) with the checks of
@@ -350,9 +368,12 @@ def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, s
     if bias is not None and (bias.numel() != n or not bias.is_contiguous() or bias.dtype != out.dtype):
         raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of the output dtype")
     with _device_of(a):
-        check(load().vb200_cutlass_scaled_mm(
+        lib = load()
+        ws = _gemm_workspace(a.device, lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k))
+        check(lib.vb200_cutlass_scaled_mm(
             ptr(out), ptr(a), ptr(b), ptr(scale_a), ptr(scale_b), ptr(bias), m, n, k, a.stride(0),
-            b.stride(1), out.stride(0), scale_a.numel(), scale_b.numel(), dtype_enum(out.dtype), stream()))
+            b.stride(1), out.stride(0), scale_a.numel(), scale_b.numel(), dtype_enum(out.dtype),
+            ptr(ws), ws.numel(), stream()))
 
 
 def cutlass_scaled_mm(a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor, scale_b: torch.Tensor,

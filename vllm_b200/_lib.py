@@ -61,8 +61,9 @@ SIGNATURES = {
     "vb200_dynamic_scaled_fp8_quant": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_dynamic_per_token_scaled_fp8_quant": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_silu_and_mul": (c_int, [_P, _P, c_int64, c_int, c_int, _P]),
+    "vb200_cutlass_scaled_mm_workspace_size": (c_size_t, [c_int, c_int, c_int]),
     "vb200_cutlass_scaled_mm": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int64, c_int64,
-                                        c_int64, c_int, c_int, c_int, _P]),
+                                        c_int64, c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_cutlass_scaled_mm_supports_fp8": (c_int, [c_int]),
     "vb200_topk_softmax": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_moe_align_workspace_size": (c_size_t, [c_int, c_int]),

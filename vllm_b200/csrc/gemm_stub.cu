@@ -1,13 +1,6 @@
 // Temporary: entry points of the tcgen05 GEMMs until scaled_mm.cu / moe_gemm.cu land.
 #include "common.cuh"
 using namespace vb200;
-extern "C" int vb200_cutlass_scaled_mm(void*, const void*, const void*, const float*, const float*,
-                                       const void*, int, int, int, int64_t, int64_t, int64_t, int,
-                                       int, int, vb200_stream_t) {
-  VB_CHECK(false, "vb200_cutlass_scaled_mm: not built yet");
-  return 1;
-}
-extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
 extern "C" int vb200_moe_grouped_gemm_fp8(void*, const void*, const void*, const float*,
                                           const float*, const float*, const int32_t*,
                                           const int32_t*, const int32_t*, int, int, int, int, int,

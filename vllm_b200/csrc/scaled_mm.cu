@@ -1,0 +1,332 @@
+// FP8 w8a8 linear (cutlass_scaled_mm semantics,
+// /root/reference/csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:169-240, epilogue
+// /root/reference/csrc/cutlass_extensions/epilogue/scaled_mm_epilogues_c3x.hpp:137-216) as a
+// hand-written tcgen05 / TMEM / TMA kernel for sm_100a.
+//
+// Decode-shaped design ("swap-AB"): the WEIGHT rows are the UMMA M side (128 TMEM lanes), the
+// tokens are the UMMA N side (any multiple of 16 up to 256), so
+//   * a batch of <= 256 tokens is ONE token tile: every weight byte is read from HBM exactly once;
+//   * small batches waste nothing (N = 16 / 32 / ... instead of a padded 128-row M tile);
+//   * the accumulator D^T[n, token] lives in TMEM (128 lanes x <= 256 fp32 columns).
+// Pipeline: warp 0 = TMA producer (128-byte-swizzled [rows x 128 B] boxes of W and A into a ring of
+// stages, mbarrier complete_tx), warp 1 = single-thread tcgen05.mma issuer (4 x K=32 per stage,
+// tcgen05.commit frees the stage), warps 2-5 = epilogue (tcgen05.ld -> a_scale * (b_scale * acc)
+// (+ bias) -> bf16/f16 -> global).  Small-N problems are split along K so the grid covers the SMs:
+// partial tiles go to an fp32 workspace and the last-arriving CTA of a tile (atomic ticket) sums
+// them in split order and runs the epilogue -- one launch, deterministic.
+#include "tc_common.cuh"
+
+namespace vb200 {
+using namespace tc;
+
+constexpr int kBlockN = 128;   // weight rows per CTA (UMMA M)
+constexpr int kBlockK = 128;   // fp8 elements (= bytes) of K per stage: one 128-byte swizzle row
+constexpr int kUmmaK = 32;     // K per tcgen05.mma for 8-bit inputs
+constexpr int kMaxTokTile = 256;
+constexpr int kMaxStages = 8;
+constexpr int kGemmThreads = 192;
+constexpr int kTmemCols = 256;
+constexpr int kWTileBytes = kBlockN * kBlockK;  // 16 KiB
+
+struct GemmParams {
+  void* out;              // [M, N] out_t, row stride ldc
+  const float* a_scales;  // 1 or M
+  const float* b_scales;  // 1 or N
+  const void* bias;       // nullptr or [N] out_t
+  float* ws;              // split-K partials: [tile][split][tok_tile][128] fp32
+  int* tickets;           // [tiles] zero between launches
+  int M, N, K;
+  int64_t ldc;
+  int a_per_token, b_per_channel;
+  int tok_tile;   // tokens per CTA tile (multiple of 16, <= 256)
+  int stages;     // pipeline depth
+  int splits;     // K splits
+  int kb_per_split;  // k-blocks per split
+  int num_kb;     // total k-blocks
+};
+
+template <typename OutT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+    scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                     const __grid_constant__ CUtensorMap tmap_a, const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [stages][W tile 16 KiB | A tile tok_tile*128] | barriers | tmem ptr | a_scale[256]
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int a_tile_bytes = p.tok_tile * kBlockK;
+  const int stage_bytes = kWTileBytes + a_tile_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* acc_bar = empty_bar + kMaxStages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_bar + 1);
+  int* last_flag = reinterpret_cast<int*>(tmem_ptr + 1);
+  float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x;
+  const int split = blockIdx.y;
+  const int m_tile = blockIdx.z;
+  const int n0 = n_tile * kBlockN;
+  const int tok0 = m_tile * p.tok_tile;
+  const int kb0 = split * p.kb_per_split;
+  const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
+  const int nkb = kb1 - kb0;  // >= 1 by construction
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_w);
+    prefetch_tensormap(&tmap_a);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
+  if (warp >= 2) {
+    // per-token scales of this tile -> smem (scalar scale broadcast)
+    for (int i = threadIdx.x - 64; i < p.tok_tile; i += 128) {
+      const int t = tok0 + i;
+      s_ascale[i] = p.a_per_token ? (t < p.M ? p.a_scales[t] : 0.f) : p.a_scales[0];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sw = smem + (size_t)stage * stage_bytes;
+        uint8_t* sa = sw + kWTileBytes;
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+        tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * kBlockK, n0, kEvictFirst);
+        tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBlockK, tok0, kEvictLast);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_f8(kBlockN, p.tok_tile);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sw = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint64_t adesc = make_smem_desc_sw128(sw);
+        const uint64_t bdesc = make_smem_desc_sw128(sw + kWTileBytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advance both descriptors by 32 bytes of K inside the swizzle row (address field >> 4)
+          umma_f8(tmem_base, adesc + (uint64_t)(k * (kUmmaK >> 4)),
+                  bdesc + (uint64_t)(k * (kUmmaK >> 4)), idesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[stage]);  // frees the stage when these MMAs have read it
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(acc_bar);  // accumulator complete
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+    const int q = warp & 3;
+    const int n = n0 + q * 32 + lane;  // weight row / output column of this thread
+    const bool n_ok = n < p.N;
+    mbar_wait(acc_bar, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int ep_tid = threadIdx.x - 64;  // 0..127
+    bool do_epilogue = true;
+    const int tile_id = m_tile * gridDim.x + n_tile;
+    float* ws_tile = p.ws + (size_t)tile_id * p.splits * p.tok_tile * kBlockN;
+    if (p.splits > 1) {
+      // publish this split's partial tile: ws[tile][split][token][128 n]
+      float* dst = ws_tile + (size_t)split * p.tok_tile * kBlockN + q * 32 + lane;
+      for (int c = 0; c < p.tok_tile; c += 16) {
+        uint32_t r[16];
+        tmem_ld_x16(taddr + c, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) __stcg(dst + (size_t)(c + j) * kBlockN, __uint_as_float(r[j]));
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (ep_tid == 0) {
+        const int t = atomicAdd(&p.tickets[tile_id], 1);
+        const int last = (t == p.splits - 1);
+        if (last) p.tickets[tile_id] = 0;  // ready for the next launch
+        *last_flag = last;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      do_epilogue = (*last_flag != 0);
+      if (do_epilogue) __threadfence();
+    }
+    if (do_epilogue) {
+      const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[n] : 0.f) : p.b_scales[0];
+      float biasf = 0.f;
+      if (p.bias != nullptr && n_ok) biasf = to_float<OutT>(reinterpret_cast<const OutT*>(p.bias)[n]);
+      OutT* outp = reinterpret_cast<OutT*>(p.out);
+      for (int c = 0; c < p.tok_tile; c += 16) {
+        float acc[16];
+        if (p.splits > 1) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+          for (int s = 0; s < p.splits; ++s) {
+            const float* src = ws_tile + (size_t)s * p.tok_tile * kBlockN + q * 32 + lane;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] += __ldcg(src + (size_t)(c + j) * kBlockN);
+          }
+        } else {
+          uint32_t r[16];
+          tmem_ld_x16(taddr + c, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(r[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int t = tok0 + c + j;
+          if (n_ok && t < p.M) {
+            // a_scale * (b_scale * acc) [+ bias]  (ScaledEpilogue / ScaledEpilogueBias)
+            const float v = p.bias != nullptr ? fmaf(s_ascale[c + j], bsc * acc[j], biasf)
+                                              : s_ascale[c + j] * (bsc * acc[j]);
+            outp[(int64_t)t * p.ldc + n] = from_float<OutT>(v);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+struct GemmPlan {
+  int tok_tile, m_tiles, n_tiles, stages, splits, kb_per_split, num_kb;
+  size_t smem, ws_bytes, ticket_bytes;
+};
+
+static GemmPlan plan_gemm(int M, int N, int K) {
+  GemmPlan g;
+  g.m_tiles = ceil_div(M, kMaxTokTile);
+  g.tok_tile = (ceil_div(M, g.m_tiles) + 15) / 16 * 16;
+  g.n_tiles = ceil_div(N, kBlockN);
+  g.num_kb = ceil_div(K, kBlockK);
+  const int stage_bytes = kWTileBytes + g.tok_tile * kBlockK;
+  const int budget = 227 * 1024 - 1024 /*align*/ - 2048 /*barriers + scales*/;
+  g.stages = budget / stage_bytes;
+  if (g.stages > kMaxStages) g.stages = kMaxStages;
+  // split K until the grid covers the SMs (each split keeps >= 8 k-blocks to amortise the ramp)
+  const int tiles = g.n_tiles * g.m_tiles;
+  int splits = 1;
+  const int sms = num_sms();
+  while (tiles * splits * 2 <= sms + sms / 4 && g.num_kb / (splits * 2) >= 8 && splits < 16) splits *= 2;
+  if (tiles * splits < sms && g.num_kb / (splits + 1) >= 8) {
+    // finer choice: the split count that gets closest to one full wave
+    int best = splits;
+    for (int s = splits; s <= 16 && g.num_kb / s >= 8; ++s)
+      if (tiles * s <= sms) best = s;
+    splits = best;
+  }
+  g.kb_per_split = ceil_div(g.num_kb, splits);
+  g.splits = ceil_div(g.num_kb, g.kb_per_split);
+  if (g.stages > g.kb_per_split) g.stages = g.kb_per_split < 2 ? 2 : g.kb_per_split;
+  g.smem = 1024 + (size_t)g.stages * stage_bytes + 2048;
+  g.ws_bytes = g.splits > 1 ? (size_t)tiles * g.splits * g.tok_tile * kBlockN * sizeof(float) : 0;
+  g.ticket_bytes = (size_t)tiles * sizeof(int);
+  return g;
+}
+
+}  // namespace vb200
+
+using namespace vb200;
+
+extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
+
+// workspace layout: [tickets: 4 KiB-aligned int32 region, must be ZERO on first use and is left
+// zero by every launch][fp32 split-K partials].
+static constexpr size_t kTicketRegion = 16384;  // up to 4096 tiles
+
+extern "C" size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return kTicketRegion;
+  const GemmPlan g = plan_gemm(M, N, K);
+  return kTicketRegion + g.ws_bytes;
+}
+
+extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
+                                       const float* a_scales, const float* b_scales,
+                                       const void* bias, int M, int N, int K, int64_t lda,
+                                       int64_t ldb, int64_t ldc, int a_scales_numel,
+                                       int b_scales_numel, int out_dtype, void* workspace,
+                                       size_t workspace_bytes, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(out_dtype == VB200_BF16 || out_dtype == VB200_F16,
+           "cutlass_scaled_mm: out dtype must be bf16 or f16");
+  VB_CHECK(K % 16 == 0 && N % 16 == 0, "cutlass_scaled_mm: K (%d) and N (%d) must be multiples of 16",
+           K, N);
+  VB_CHECK(a_scales_numel == 1 || a_scales_numel == M, "a_scales must have 1 or M entries");
+  VB_CHECK(b_scales_numel == 1 || b_scales_numel == N, "b_scales must have 1 or N entries");
+  if (M <= 0 || N <= 0) return 0;
+  VB_CHECK(K > 0, "cutlass_scaled_mm: K must be positive");
+  GemmPlan g = plan_gemm(M, N, K);
+  VB_CHECK((size_t)g.n_tiles * g.m_tiles * sizeof(int) <= kTicketRegion,
+           "cutlass_scaled_mm: too many tiles for the ticket region");
+  if (g.splits > 1) {
+    VB_CHECK(workspace != nullptr && workspace_bytes >= kTicketRegion + g.ws_bytes,
+             "cutlass_scaled_mm: workspace too small (%zu < %zu)", workspace_bytes,
+             kTicketRegion + g.ws_bytes);
+  }
+  CUtensorMap tw, ta;
+  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kBlockN)) return 1;
+  if (tc::make_tmap_2d_u8(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, (uint32_t)g.tok_tile))
+    return 1;
+  GemmParams p;
+  p.out = out;
+  p.a_scales = a_scales;
+  p.b_scales = b_scales;
+  p.bias = bias;
+  p.tickets = reinterpret_cast<int*>(workspace);
+  p.ws = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kTicketRegion)
+                   : nullptr;
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.ldc = ldc;
+  p.a_per_token = a_scales_numel > 1 ? 1 : 0;
+  p.b_per_channel = b_scales_numel > 1 ? 1 : 0;
+  p.tok_tile = g.tok_tile;
+  p.stages = g.stages;
+  p.splits = g.splits;
+  p.kb_per_split = g.kb_per_split;
+  p.num_kb = g.num_kb;
+  dim3 grid(g.n_tiles, g.splits, g.m_tiles);
+  if (out_dtype == VB200_BF16) {
+    auto kern = scaled_mm_kernel<__nv_bfloat16>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kGemmThreads, g.smem, stream>>>(tw, ta, p);
+  } else {
+    auto kern = scaled_mm_kernel<__half>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kGemmThreads, g.smem, stream>>>(tw, ta, p);
+  }
+  VB_LAUNCH_CHECK();
+  return 0;
+}
