@@ -1,0 +1,468 @@
+#!/usr/bin/env python3
+"""bench.py -- decode throughput of the hot path on BASELINE.json's metric
+("decode tokens/s/GPU Llama-3.1-8B FP8; paged-attn HBM GB/s vs peak").
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--config cfg3|cfg2|tiny]
+
+One "step" = one decode step (all 32 layers + lm_head + greedy arg-max) of Llama-3.1-8B, FP8 w8a8 scaled_mm
+(dynamic per-token activation scales, per-channel weight scales) + fp8_e4m3 paged KV cache (block 16), batch 256
+at 4k context (BASELINE configs[2], the configuration the metric is quoted on), synthetic token ids, dummy
+weights, random cache contents.  N > 1 = tensor parallel over N ranks (heads / columns sharded, NCCL all-reduce
+after the row-parallel GEMMs), same global batch => "strong" scaling.  Printed keys: see the task contract;
+  value     tokens/s with the step's inputs resident in HBM (CUDA-graph replay, CUDA-event timed, max over ranks)
+  e2e       tokens/s through the public API with HOST inputs: per step pinned-host -> device copies of
+            token ids / positions / slot mapping / seq lens / block tables, the step, device -> host copy of the
+            sampled token ids, host waits for them (the next step's input depends on them)
+  roofline  the dominant kernel (paged_attention_kernel): algorithmic bytes / its CUDA-event duration measured
+            live in an eager replay of the same step right after the timed region, vs MEASURED_PEAKS.json
+  cpu_baseline  the reference's own CPU kernels (oracle/_ref: csrc/cpu attention + cache) + oneDNN bf16 GEMMs
+            on a bounded sample of the same step, timed on this box's host cores (N=1, rank 0 only)
+`--impl reference` times that CPU implementation as the measured arm.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "decode tokens/s Llama-3.1-8B FP8 (w8a8 scaled_mm + fp8_e4m3 paged KV, batch 256 @ 4k ctx)"
+
+WORKLOADS = {
+    # name: (model, batch, ctx, quant, kv_cache_dtype)
+    "cfg3": ("Llama-3.1-8B", 256, 4096, "fp8", "fp8"),
+    "cfg2": ("Llama-3.1-8B", 64, 2048, "bf16", "auto"),
+    "tiny": ("tiny-llama", 8, 256, "fp8", "fp8"),
+}
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own CPU kernels on a bounded sample of the same step
+# ---------------------------------------------------------------------------------------------------
+def cpu_reference_step_sample(workload: str, budget_s: float = 12.0, max_reps: int = 8):
+    """Times ONE decoder layer of the workload on the host cores for a sample of the batch:
+      reshape_and_cache + paged_attention_v1 = the reference's csrc/cpu/{cache,attention}.cpp compiled into
+      oracle/_ref/libvllm_ref_cpu.so (kind "reference"; bf16 KV -- that kernel has no fp8 path), or the oracle's
+      torch restatement when the .so is absent (kind "port");
+      the four projections = torch bf16 matmul (oneDNN / MKL-DNN inside torch: the reference's CPU fp8 GEMM does
+      not exist, its CPU w8a8 path is int8 oneDNN).
+    tokens/s = sample_seqs / (num_layers * t_layer).  Returns (tokens_per_s, info dict, seconds per rep)."""
+    from vllm_b200.decode_step import CONFIGS
+    model, batch, ctx, _, _ = WORKLOADS[workload]
+    cfg = CONFIGS[model]
+    S = min(batch, 64)
+    bs, D, Hkv, H = 16, cfg.head_dim, cfg.num_kv_heads, cfg.num_heads
+    ref, kind = None, "port"
+    so = os.path.join(ROOT, "oracle", "_ref", "libvllm_ref_cpu.so")
+    if os.path.exists(so):
+        try:
+            torch.ops.load_library(so)
+            ref, kind = torch.ops._ref_cpu, "reference"
+        except Exception:
+            ref = None
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    dt = torch.bfloat16
+    blocks_per_seq = (ctx + bs - 1) // bs
+    nb = S * blocks_per_seq
+    g = torch.Generator().manual_seed(0)
+    tile = torch.empty(1 << 22, dtype=dt).uniform_(-1, 1, generator=g)          # 8 MiB of random bf16, tiled
+    def big(shape):
+        n = 1
+        for s in shape:
+            n *= s
+        return tile.repeat((n + tile.numel() - 1) // tile.numel())[:n].reshape(shape).contiguous()
+    kc = big((nb, Hkv, D // 8, bs, 8))
+    vc = big((nb, Hkv, D, bs))
+    bt = torch.randperm(nb, generator=g).to(torch.int32).reshape(S, blocks_per_seq)
+    sl = torch.full((S,), ctx, dtype=torch.int32)
+    slots = (bt[:, (ctx - 1) // bs].to(torch.int64) * bs + (ctx - 1) % bs)
+    hid, inter = cfg.hidden_size, cfg.intermediate_size
+    w_qkv = big(((H + 2 * Hkv) * D, hid)) * 0.02
+    w_o = big((hid, H * D)) * 0.02
+    w_gu = big((2 * inter, hid)) * 0.02
+    w_dn = big((hid, inter)) * 0.02
+    x = torch.randn(S, hid, generator=g).to(dt)
+    one = torch.tensor(1.0)
+    scale = D ** -0.5
+
+    def layer():
+        qkv = x @ w_qkv.t()
+        q = qkv[:, :H * D].reshape(S, H, D).contiguous()
+        k = qkv[:, H * D:(H + Hkv) * D].reshape(S, Hkv, D).contiguous()
+        v = qkv[:, (H + Hkv) * D:].reshape(S, Hkv, D).contiguous()
+        out = torch.empty_like(q)
+        if ref is not None:
+            ref.reshape_and_cache(k, v, kc, vc, slots, "auto", one, one)
+            ref.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, bs, ctx, None, "auto", one, one, 0, 0, 0, 64, 0)
+        else:
+            from oracle import attention as oattn
+            from oracle import cache as ocache
+            ocache.reshape_and_cache(k, v, kc, vc, slots)
+            out = oattn.paged_attention(q, kc, vc, Hkv, scale, bt, sl)
+        h = out.reshape(S, H * D) @ w_o.t()
+        gu = h @ w_gu.t()
+        act = torch.nn.functional.silu(gu[:, :inter]) * gu[:, inter:]
+        return act @ w_dn.t()
+
+    layer()  # warm-up (page-in, thread pool)
+    ts = []
+    t_start = time.perf_counter()
+    while len(ts) < max_reps and (time.perf_counter() - t_start) < budget_s:
+        t0 = time.perf_counter()
+        layer()
+        ts.append(time.perf_counter() - t0)
+    t_layer = statistics.median(ts)
+    tps = S / (cfg.num_layers * t_layer)
+    info = {"value": round(tps, 3), "unit": "tokens/s", "cores": cores, "kind": kind,
+            "sample": (f"1 of {cfg.num_layers} layers x {S} of {batch} sequences at ctx {ctx}: reference csrc/cpu "
+                       f"reshape_and_cache + paged_attention_v1 (bf16 KV; the CPU kernel has no fp8 path) + 4 "
+                       f"projections as torch bf16 matmul (oneDNN); {len(ts)} reps, median {t_layer * 1e3:.1f} ms/layer; "
+                       f"tokens/s = {S} / ({cfg.num_layers} x t_layer)")}
+    return tps, info, t_layer
+
+
+def run_reference_arm(args, rank: int):
+    """bench.py --impl reference: the CPU implementation is the measured arm (rank 0 only)."""
+    if rank != 0:
+        return
+    model, batch, ctx, quant, kvd = WORKLOADS[args.config]
+    for _ in range(max(args.warmup, 0) and 1):
+        cpu_reference_step_sample(args.config, budget_s=2.0, max_reps=1)
+    vals, t_layers = [], []
+    for _ in range(max(args.steps, 1)):
+        tps, info, t_layer = cpu_reference_step_sample(args.config, budget_s=6.0, max_reps=3)
+        vals.append(tps)
+        t_layers.append(t_layer)
+        if sum(t_layers) * 4 > 150:   # keep the whole run within a few minutes
+            break
+    v = statistics.median(vals)
+    from vllm_b200.decode_step import CONFIGS
+    nl = CONFIGS[model].num_layers
+    info["value"] = round(v, 3)
+    line = {"impl": "reference", "metric": METRIC if args.config == "cfg3" else f"decode tokens/s ({args.config})",
+            "value": round(v, 3), "unit": "tokens/s", "n_gpus": args.gpus,
+            "steps": len(vals), "warmup": args.warmup,
+            "ms_per_step": round(statistics.median(t_layers) * nl * batch / min(batch, 64) * 1e3, 1),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 (CPU reference path)",
+            "data": "synthetic", "config": workload_config(args.config, 1),
+            "cpu_baseline": info,
+            "e2e": {"value": round(v, 3), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(name: str, n_gpus: int):
+    model, batch, ctx, quant, kvd = WORKLOADS[name]
+    return {"workload": f"BASELINE configs[{ {'cfg3': 2, 'cfg2': 1}.get(name, 0) }]: {model} {quant} "
+                        f"{'w8a8 scaled_mm ' if quant == 'fp8' else ''}+ {'fp8_e4m3' if kvd == 'fp8' else 'bf16'} "
+                        f"paged KV block 16, batch {batch} decode at {ctx} context",
+            "global_batch": batch, "context_len": ctx, "block_size": 16, "parallelism": f"tp{n_gpus}",
+            "weights": "dummy (random)", "l2": "inputs larger than L2 (KV cache + weights >> 126 MB per step)",
+            "context": "fixed per step (every step writes slot ctx-1 and attends over ctx tokens)"}
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+class StepInputs:
+    """Host (pinned) and device copies of one decode step's inputs + the algorithmic byte count of its attention."""
+
+    def __init__(self, batch, ctx, block_size, num_blocks, vocab, device):
+        g = torch.Generator().manual_seed(0)
+        bps = (ctx + block_size - 1) // block_size
+        self.h_ids = torch.randint(0, vocab, (batch,), generator=g, dtype=torch.int64).pin_memory()
+        self.h_pos = torch.full((batch,), ctx - 1, dtype=torch.int64).pin_memory()
+        self.h_sl = torch.full((batch,), ctx, dtype=torch.int32).pin_memory()
+        self.h_bt = torch.randperm(num_blocks, generator=g)[:batch * bps].to(torch.int32).reshape(batch, bps).pin_memory()
+        self.h_slots = (self.h_bt[:, (ctx - 1) // block_size].to(torch.int64) * block_size +
+                        (ctx - 1) % block_size).pin_memory()
+        self.h_out = torch.empty(batch, dtype=torch.int64).pin_memory()
+        self.d_ids, self.d_pos, self.d_sl = (t.to(device) for t in (self.h_ids, self.h_pos, self.h_sl))
+        self.d_bt, self.d_slots = self.h_bt.to(device), self.h_slots.to(device)
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_ids, self.h_pos, self.h_sl, self.h_bt, self.h_slots))
+        self.d2h_bytes = self.h_out.numel() * self.h_out.element_size()
+        self.batch, self.ctx = batch, ctx
+
+    def upload(self):
+        self.d_ids.copy_(self.h_ids, non_blocking=True)
+        self.d_pos.copy_(self.h_pos, non_blocking=True)
+        self.d_sl.copy_(self.h_sl, non_blocking=True)
+        self.d_bt.copy_(self.h_bt, non_blocking=True)
+        self.d_slots.copy_(self.h_slots, non_blocking=True)
+
+
+def attention_algorithmic_bytes(batch, ctx, H, Hkv, D, cache_bytes, q_bytes=2, block_size=16):
+    """K and V read once + q in + out + block table + seq_lens."""
+    kv = batch * ctx * Hkv * D * 2 * cache_bytes
+    qo = 2 * batch * H * D * q_bytes
+    bt = batch * ((ctx + block_size - 1) // block_size) * 4 + 4 * batch
+    return kv + qo + bt
+
+
+def run_gpu_arm(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200 import _lib
+    from vllm_b200.attention import B200PagedAttentionMetadata
+    from vllm_b200.decode_step import CONFIGS, Decoder
+    from vllm_b200.distributed import init_tensor_parallel
+    _lib.load()  # fail loudly when the CUDA library is missing
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    init_tensor_parallel()
+    model, batch, ctx, quant, kvd = WORKLOADS[args.config]
+    cfg = CONFIGS[model]
+    bs = 16
+    bps = (ctx + bs - 1) // bs
+    num_blocks = batch * bps + 64
+    dec = Decoder(cfg, num_blocks, bs, kvd, quant, device=dev)
+    dec.fill_kv_cache_random()
+    inp = StepInputs(batch, ctx, bs, num_blocks, cfg.vocab_size, dev)
+    meta = B200PagedAttentionMetadata(seq_lens_tensor=inp.d_sl, max_decode_seq_len=ctx, block_tables=inp.d_bt,
+                                      num_decode_tokens=batch, slot_mapping=inp.d_slots)
+    d_next = torch.empty(batch, dtype=torch.int64, device=dev)
+
+    # ---- count launches of OUR kernels in one step (host-side counter around the C ABI) -------------
+    lib = _lib.load()
+    counter = {"n": 0}
+    per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_dynamic_scaled_fp8_quant": 2}
+    wrapped = {}
+    for name in _lib.SIGNATURES:
+        if name.startswith("vb200_") and not any(s in name for s in ("size", "error", "version", "supports")):
+            fn = getattr(lib, name)
+            wrapped[name] = fn
+
+            def mk(fn, name):
+                def w(*a):
+                    counter["n"] += per_call.get(name, 1)
+                    return fn(*a)
+                return w
+            setattr(lib, name, mk(fn, name))
+
+    def step():
+        d_next.copy_(dec.greedy_step(inp.d_ids, inp.d_pos, meta))
+
+    # eager warm-up (allocator, workspaces, NCCL), then capture the step in a CUDA graph
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        counter["n"] = 0
+        step()
+        launches_per_step = counter["n"]
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    for name, fn in wrapped.items():
+        setattr(lib, name, fn)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident inputs, graph replay ------------------------------------------------
+    for _ in range(args.warmup):
+        graph.replay()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if args.profile_window:   # ncu --profile-from-start off: only the timed steps are profiled
+        torch.cuda.profiler.start()
+    e0.record()
+    for _ in range(args.steps):
+        graph.replay()
+    e1.record()
+    barrier()
+    if args.profile_window:
+        torch.cuda.profiler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    # ---- e2e: host inputs every step, sampled ids back to the host every step -------------------------
+    for _ in range(min(args.warmup, 3)):
+        inp.upload(); graph.replay(); inp.h_out.copy_(d_next, non_blocking=True); torch.cuda.current_stream().synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        inp.upload()
+        graph.replay()
+        inp.h_out.copy_(d_next, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+
+    # ---- roofline of the dominant kernel: eager replay of the step with events around every attention call ----
+    layer0 = dec.layers[0]
+    attn_ms = []
+    real_fd = __import__("vllm_b200.attention.paged_attn", fromlist=["PagedAttention"]).PagedAttention
+    orig = real_fd.forward_decode
+    evs = []
+
+    def timed_forward_decode(*a, **k):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        r = orig(*a, **k)
+        e.record()
+        evs.append((s, e))
+        return r
+    real_fd.forward_decode = staticmethod(timed_forward_decode)
+    try:
+        for _ in range(max(2, min(args.steps, 5))):
+            step()
+        torch.cuda.synchronize()
+    finally:
+        real_fd.forward_decode = staticmethod(orig)
+    attn_ms = [s.elapsed_time(e) for s, e in evs[len(dec.layers):]]  # drop the first step
+    attn_s = statistics.mean(attn_ms) * 1e-3
+    cache_bytes = 1 if kvd != "auto" else 2
+    algo = attention_algorithmic_bytes(batch, ctx, layer0.nh, layer0.nkv, cfg.head_dim, cache_bytes)
+    peak, peak_src = peaks()
+    achieved = algo / attn_s / 1e9
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    tps = batch / (ms * 1e-3)
+    line = {
+        "metric": METRIC if args.config == "cfg3" else f"decode tokens/s ({args.config})",
+        "value": round(tps, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "fp8_e4m3 x fp8_e4m3 -> f32 accumulate (GEMMs), bf16 activations, fp8_e4m3 KV" if quant == "fp8" else "bf16",
+        "data": "synthetic", "config": workload_config(args.config, world),
+        "tokens_per_s_per_gpu": round(tps / world, 1),
+        "e2e": {"value": round(batch / e2e_s, 1), "unit": "tokens/s", "h2d_bytes_per_step": inp.h2d_bytes,
+                "d2h_bytes_per_step": inp.d2h_bytes, "ms_per_step": round(e2e_s * 1e3, 4)},
+        "gpu_launches": launches_per_step * args.steps,
+        "gpu_launches_per_step": launches_per_step,
+        "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel (+ split-K reduce)",
+                     "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": algo, "avg_launch_us": round(attn_s * 1e6, 2),
+                     "launches_timed": len(attn_ms),
+                     "share_of_step": round(attn_s * 1e3 * len(dec.layers) / ms, 4),
+                     "how": "CUDA events around each layer's paged_attention call in an eager replay of the same "
+                            "step right after the timed region (the timed region itself is one CUDA graph)"},
+        "clocks": clk,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        del dec
+        torch.cuda.empty_cache()
+        try:
+            _, info, _ = cpu_reference_step_sample(args.config)
+            line["cpu_baseline"] = info
+        except Exception as ex:  # the CPU leg must not lose the GPU numbers
+            line["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"failed: {type(ex).__name__}: {ex}"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg3", choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-window", action="store_true",
+                    help="cudaProfilerStart/Stop around the timed steps (for ncu --profile-from-start off)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback); use --impl reference "
+                         "for the CPU arm")
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit(f"bench.py --gpus {args.gpus}: launch with torchrun --nproc-per-node {args.gpus}")
+    run_gpu_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

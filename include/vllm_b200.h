@@ -159,6 +159,43 @@ int vb200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, 
                        vb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------ */
+/* Per-token glue between the contractions                         */
+/* ------------------------------------------------------------------------------------------ */
+
+/* rms_norm: csrc/layernorm_kernels.cu:16-100, schema csrc/torch_bindings.cpp:171-173.
+ * out[t,:] = T(T(x[t,:] * rsqrt(mean(x^2) + eps)) * weight); input rows input_stride apart. */
+int vb200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
+                   int num_tokens, int hidden_size, int64_t input_stride, int dtype,
+                   vb200_stream_t stream);
+/* fused_add_rms_norm: csrc/layernorm_kernels.cu:102-200, schema torch_bindings.cpp:177-179.
+ * In place: residual = T(input + residual); input = rms_norm(residual). */
+int vb200_fused_add_rms_norm(void* input, void* residual, const void* weight, float epsilon,
+                             int num_tokens, int hidden_size, int64_t input_stride, int dtype,
+                             vb200_stream_t stream);
+/* rms_norm_dynamic_per_token_quant: csrc/quantization/fused_kernels/
+ * fused_layernorm_dynamic_per_token_quant.cu:9-43,100-170, schema torch_bindings.cpp:207-211.
+ * z = input (+ residual, fp32 sum; residual <- T(z) when given); y = T(T(z*inv_rms)*weight);
+ * scales[t] = max(min(amax|y|, *scale_ub)/448, 1/(448*512)); out = fp8(clamp(y / scales[t])). */
+int vb200_rms_norm_dynamic_per_token_quant(void* out, const void* input, const void* weight,
+                                           float* scales, float epsilon, const float* scale_ub,
+                                           void* residual, int num_tokens, int hidden_size,
+                                           int dtype, vb200_stream_t stream);
+/* rotary_embedding: csrc/pos_encoding_kernels.cu:10-98,130-178, schema torch_bindings.cpp:216-219.
+ * In place on query [num_tokens, num_heads, head_size] and key (may be NULL); positions int64;
+ * cos_sin_cache [max_position, rot_dim] = cos | sin halves; strides in elements. */
+int vb200_rotary_embedding(const int64_t* positions, void* query, void* key, int num_tokens,
+                           int num_heads, int num_kv_heads, int head_size, int rot_dim,
+                           const void* cos_sin_cache, int is_neox, int64_t query_stride,
+                           int64_t key_stride, int64_t head_stride, int dtype,
+                           vb200_stream_t stream);
+/* silu_and_mul followed by dynamic_per_token_scaled_fp8_quant in one pass (bit-identical to the
+ * two reference ops run back to back: csrc/activation_kernels.cu:26-63 then
+ * csrc/quantization/fp8/common.cu:28-83).  input [num_tokens, 2d] -> out fp8 [num_tokens, d]. */
+int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scales, const void* input,
+                                               const float* scale_ub, int num_tokens, int d,
+                                               int dtype, vb200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------ */
 /* FP8 w8a8 linear                                                                             */
 /* ------------------------------------------------------------------------------------------ */
 

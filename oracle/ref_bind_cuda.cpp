@@ -3,7 +3,7 @@
 // -- nothing is copied) under the private torch library name `_ref_C`, so that the GPU
 // parity tests can call THE reference op next to ours on the same inputs.
 // Schemas: /root/reference/csrc/torch_bindings.cpp:45-69 (attention), :111 (silu_and_mul),
-// :575-591 (fp8 quant), :676-707 (cache ops); /root/reference/csrc/moe/torch_bindings.cpp:6-22.
+// :171-219 (norms, rope), :575-591 (fp8 quant), :676-707 (cache ops); /root/reference/csrc/moe/torch_bindings.cpp:6-22.
 #include <torch/all.h>
 #include <torch/library.h>
 #include "ops.h"
@@ -47,6 +47,18 @@ TORCH_LIBRARY(_ref_C, m) {
       " Tensor? scale_ub) -> ()");
   m.impl("dynamic_per_token_scaled_fp8_quant", torch::kCUDA,
          &dynamic_per_token_scaled_fp8_quant);
+  m.def("rms_norm(Tensor! result, Tensor input, Tensor weight, float epsilon) -> ()");
+  m.impl("rms_norm", torch::kCUDA, &rms_norm);
+  m.def("fused_add_rms_norm(Tensor! input, Tensor! residual, Tensor weight, float epsilon) -> ()");
+  m.impl("fused_add_rms_norm", torch::kCUDA, &fused_add_rms_norm);
+  m.def(
+      "rms_norm_dynamic_per_token_quant(Tensor! result, Tensor input, Tensor weight, Tensor! scale,"
+      " float epsilon, Tensor? scale_ub, Tensor!? residual) -> ()");
+  m.impl("rms_norm_dynamic_per_token_quant", torch::kCUDA, &rms_norm_dynamic_per_token_quant);
+  m.def(
+      "rotary_embedding(Tensor positions, Tensor! query, Tensor!? key, int head_size,"
+      " Tensor cos_sin_cache, bool is_neox) -> ()");
+  m.impl("rotary_embedding", torch::kCUDA, &rotary_embedding);
   m.def(
       "topk_softmax(Tensor! topk_weights, Tensor! topk_indices, Tensor! token_expert_indices,"
       " Tensor gating_output) -> ()");

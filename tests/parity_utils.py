@@ -74,3 +74,18 @@ def make_block_tables(num_seqs, seq_lens, block_size, num_blocks, shared=False):
         perm = torch.randperm(num_blocks)[:need].to(torch.int32)
         bt = perm.reshape(num_seqs, max_blocks)
     return bt
+
+
+REF_CUTLASS_SO = os.path.join(ROOT, "oracle", "_ref", "libvllm_ref_cutlass.so")
+
+
+def load_ref_cutlass():
+    """torch.ops._ref_cutlass (the reference's own sm100 CUTLASS kernels: cutlass_scaled_mm, cutlass_moe_mm,
+    get_cutlass_moe_mm_data) or None when not built / not loadable (needs libcuda.so.1)."""
+    if "cutlass" not in _loaded:
+        try:
+            torch.ops.load_library(REF_CUTLASS_SO)
+            _loaded["cutlass"] = torch.ops._ref_cutlass
+        except Exception:
+            _loaded["cutlass"] = None
+    return _loaded["cutlass"]

@@ -431,3 +431,100 @@ def moe_sum(input: torch.Tensor, output: torch.Tensor) -> None:
     t, k, h = input.shape
     with _device_of(input):
         check(load().vb200_moe_sum(ptr(output), ptr(input), t, k, h, dtype_enum(input.dtype), stream()))
+
+
+# ------------------------------------------------------------------------------------------------
+# per-token glue between the contractions  (reference: vllm/_custom_ops.py:248-281, 368-384)
+# ------------------------------------------------------------------------------------------------
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: Optional[torch.Tensor], head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    """torch.ops._C.rotary_embedding (csrc/torch_bindings.cpp:216-219), launcher checks of
+    csrc/pos_encoding_kernels.cu:133-185.  In place on query / key ([T, H*D] or [T, H, D])."""
+    require_cuda(positions, query, key, cos_sin_cache)
+    if positions.dtype != torch.int64 or positions.dim() != 1 or not positions.is_contiguous():
+        raise RuntimeError("positions must have shape [num_tokens] (contiguous int64)")
+    num_tokens = positions.numel()
+    if query.shape[0] != num_tokens or (key is not None and key.shape[0] != num_tokens):
+        raise RuntimeError("query, key and positions must have the same number of tokens")
+    qh = query.numel() // max(num_tokens, 1)
+    kh = key.numel() // max(num_tokens, 1) if key is not None else 0
+    if qh % head_size or kh % head_size:
+        raise RuntimeError("rotary_embedding: hidden sizes must be multiples of head_size")
+    num_heads = qh // head_size
+    num_kv_heads = kh // head_size if key is not None else num_heads
+    if num_heads % num_kv_heads:
+        raise RuntimeError("rotary_embedding: num_heads must be a multiple of num_kv_heads")
+    if cos_sin_cache.dtype != query.dtype or not cos_sin_cache.is_contiguous():
+        raise RuntimeError("rotary_embedding: cos_sin_cache must be contiguous and of the query dtype")
+    head_stride = query.stride(-2) if query.dim() == 3 else head_size
+    if query.stride(-1) != 1 or (key is not None and key.stride(-1) != 1):
+        raise RuntimeError("rotary_embedding: head dim must be contiguous")
+    with _device_of(query):
+        check(load().vb200_rotary_embedding(
+            ptr(positions), ptr(query), ptr(key), num_tokens, num_heads, num_kv_heads, head_size,
+            cos_sin_cache.shape[1], ptr(cos_sin_cache), int(bool(is_neox)), query.stride(0),
+            key.stride(0) if key is not None else 0, head_stride, dtype_enum(query.dtype), stream()))
+
+
+def _norm_rows(op: str, input: torch.Tensor, weight: torch.Tensor):
+    require_cuda(input, weight)
+    hidden = input.shape[-1]
+    if input.stride(-1) != 1 or weight.numel() != hidden or weight.dtype != input.dtype or not weight.is_contiguous():
+        raise RuntimeError(f"{op}: contiguous rows and a [hidden] weight of the input dtype are required")
+    return input.numel() // max(hidden, 1), hidden
+
+
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    """torch.ops._C.rms_norm (csrc/torch_bindings.cpp:171-173)."""
+    input = input.contiguous()
+    n, hidden = _norm_rows("rms_norm", input, weight)
+    if not out.is_contiguous() or out.shape != input.shape or out.dtype != input.dtype:
+        raise RuntimeError("rms_norm: out must be contiguous with the input's shape and dtype")
+    with _device_of(input):
+        check(load().vb200_rms_norm(ptr(out), ptr(input), ptr(weight), float(epsilon), n, hidden, hidden,
+                                    dtype_enum(input.dtype), stream()))
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    """torch.ops._C.fused_add_rms_norm (csrc/torch_bindings.cpp:177-179); both tensors updated in place."""
+    n, hidden = _norm_rows("fused_add_rms_norm", input, weight)
+    if input.dim() != 2 or not residual.is_contiguous() or residual.shape != input.shape or residual.dtype != input.dtype:
+        raise RuntimeError("fused_add_rms_norm: 2-D input and a contiguous residual of the same shape/dtype")
+    with _device_of(input):
+        check(load().vb200_fused_add_rms_norm(ptr(input), ptr(residual), ptr(weight), float(epsilon), n, hidden,
+                                              input.stride(0), dtype_enum(input.dtype), stream()))
+
+
+def rms_norm_dynamic_per_token_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float,
+                                     quant_dtype: torch.dtype, scale_ub: Optional[torch.Tensor] = None,
+                                     residual: Optional[torch.Tensor] = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """vllm/_custom_ops.py:368-384 (fp8 e4m3 output only; the int8 variant is outside the path)."""
+    if quant_dtype != FP8_DTYPE:
+        raise RuntimeError("rms_norm_dynamic_per_token_quant: only float8_e4m3fn output is built")
+    n, hidden = _norm_rows("rms_norm_dynamic_per_token_quant", input, weight)
+    if not input.is_contiguous() or (residual is not None and (not residual.is_contiguous() or residual.shape != input.shape)):
+        raise RuntimeError("rms_norm_dynamic_per_token_quant: input and residual must be contiguous")
+    require_cuda(scale_ub, residual)
+    output = torch.empty_like(input, dtype=quant_dtype)
+    scales = torch.empty((n, 1), device=input.device, dtype=torch.float32)
+    with _device_of(input):
+        check(load().vb200_rms_norm_dynamic_per_token_quant(
+            ptr(output), ptr(input), ptr(weight), ptr(scales), float(epsilon), ptr(scale_ub), ptr(residual), n,
+            hidden, dtype_enum(input.dtype), stream()))
+    return output, scales
+
+
+def silu_and_mul_dynamic_per_token_quant(x: torch.Tensor, scale_ub: Optional[torch.Tensor] = None
+                                         ) -> tuple[torch.Tensor, torch.Tensor]:
+    """silu_and_mul + scaled_fp8_quant(use_per_token_if_dynamic=True) in one kernel (SURVEY.md 8f row 1);
+    bit-identical to the two reference ops run back to back.  x [T, 2d] -> (fp8 [T, d], fp32 [T, 1])."""
+    require_cuda(x, scale_ub)
+    if x.dim() != 2 or not x.is_contiguous():
+        raise RuntimeError("silu_and_mul_dynamic_per_token_quant: contiguous 2-D input")
+    t, d = x.shape[0], x.shape[1] // 2
+    out = torch.empty((t, d), device=x.device, dtype=FP8_DTYPE)
+    scales = torch.empty((t, 1), device=x.device, dtype=torch.float32)
+    with _device_of(x):
+        check(load().vb200_silu_and_mul_dynamic_per_token_quant(ptr(out), ptr(scales), ptr(x), ptr(scale_ub), t, d,
+                                                                dtype_enum(x.dtype), stream()))
+    return out, scales

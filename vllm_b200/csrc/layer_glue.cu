@@ -1,0 +1,306 @@
+// The small per-token kernels that sit between the contractions of one decode layer: RMSNorm
+// (plain / fused residual add / fused with the dynamic per-token fp8 quant that feeds the next
+// scaled_mm), rotary embedding, and silu_and_mul fused with the per-token fp8 quant.
+//
+// Arithmetic follows the reference operation for operation, including every rounding point:
+//   rms_norm, fused_add_rms_norm        /root/reference/csrc/layernorm_kernels.cu:16-160
+//   rms_norm_dynamic_per_token_quant    /root/reference/csrc/quantization/fused_kernels/
+//                                       layernorm_utils.cuh:19-125 + fused_layernorm_dynamic_per_token_quant.cu:9-43
+//   rotary_embedding                    /root/reference/csrc/pos_encoding_kernels.cu:10-98
+//   silu_and_mul (+ per-token quant)    /root/reference/csrc/activation_kernels.cu:26-63 followed by
+//                                       /root/reference/csrc/quantization/fp8/common.cu:28-83
+// One CTA per token; the row is read with 16-byte loads and kept in registers between the
+// reduction pass and the write pass (one HBM read per element instead of the reference's two or
+// three), which is what makes these launch-latency-bound rather than bandwidth-bound at decode
+// batch sizes.
+#include "common.cuh"
+
+namespace vb200 {
+
+constexpr float kFp8MaxG = 448.f;
+constexpr int kGlueThreads = 256;
+constexpr int kMaxVecPerThread = 8;  // rows up to 256 * 8 * 8 = 16384 16-bit elements stay in registers
+
+__device__ __forceinline__ uint8_t quant_clamped_g(float x) {
+  return float_to_e4m3(fmaxf(-kFp8MaxG, fminf(x, kFp8MaxG)));
+}
+
+template <bool IS_MAX>
+__device__ __forceinline__ float block_reduce(float v, float* sm) {
+  v = IS_MAX ? warp_max(v) : warp_sum(v);
+  __syncthreads();  // sm may still be read from a previous reduction
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = ((threadIdx.x & 31) < (blockDim.x >> 5)) ? sm[threadIdx.x & 31] : 0.f;
+  return IS_MAX ? warp_max(r) : warp_sum(r);
+}
+
+template <typename T>
+union Vec8 {
+  uint4 u;
+  T e[8];
+};
+
+// MODE 0: rms_norm            out = T(T(x * inv) * w)
+// MODE 1: fused_add_rms_norm  z = T(x + r); residual = z; input = T(T(z * inv) * w)   (in place)
+// MODE 2: rms_norm_dynamic_per_token_quant (optional residual): z = float(x) + float(r) unrounded,
+//         residual = T(z); y = T(T(z * inv) * w); s = max(min(amax|y|, ub) / 448, 1/(448*512));
+//         out = fp8(clamp(y / s)); scales[token] = s
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
+    void* __restrict__ out_, T* __restrict__ input, T* __restrict__ residual,
+    const T* __restrict__ weight, float* __restrict__ scales, const float* __restrict__ scale_ub,
+    float eps, int hidden, int64_t input_stride) {
+  __shared__ float sm[8];
+  const int64_t row = blockIdx.x;
+  T* in = input + row * input_stride;
+  T* res = residual ? residual + row * hidden : nullptr;
+  const int nvec = hidden >> 3;
+  float zf[kMaxVecPerThread][8];  // the (residual-added) row, fp32
+  float ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < kMaxVecPerThread; ++k) {
+    const int i = threadIdx.x + k * kGlueThreads;
+    if (i < nvec) {
+      Vec8<T> a;
+      a.u = *reinterpret_cast<const uint4*>(in + i * 8);
+      if (res != nullptr) {
+        Vec8<T> b, z;
+        b.u = *reinterpret_cast<const uint4*>(res + i * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float s = to_float<T>(a.e[j]) + to_float<T>(b.e[j]);
+          z.e[j] = from_float<T>(s);
+          zf[k][j] = (MODE == 1) ? to_float<T>(z.e[j]) : s;
+        }
+        *reinterpret_cast<uint4*>(res + i * 8) = z.u;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) zf[k][j] = to_float<T>(a.e[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(zf[k][j], zf[k][j], ss);
+    }
+  }
+  ss = block_reduce<false>(ss, sm);
+  const float inv = rsqrtf(ss / (float)hidden + eps);
+  float amax = 0.f;
+#pragma unroll
+  for (int k = 0; k < kMaxVecPerThread; ++k) {
+    const int i = threadIdx.x + k * kGlueThreads;
+    if (i < nvec) {
+      Vec8<T> w, y;
+      w.u = *reinterpret_cast<const uint4*>(weight + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const T n = from_float<T>(zf[k][j] * inv);
+        y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(w.e[j]));
+        if (MODE == 2) {
+          zf[k][j] = to_float<T>(y.e[j]);
+          amax = fmaxf(amax, fabsf(zf[k][j]));
+        }
+      }
+      if (MODE == 0) *reinterpret_cast<uint4*>(reinterpret_cast<T*>(out_) + row * hidden + i * 8) = y.u;
+      if (MODE == 1) *reinterpret_cast<uint4*>(in + i * 8) = y.u;
+    }
+  }
+  if (MODE == 2) {
+    amax = block_reduce<true>(amax, sm);
+    float s = scale_ub ? fminf(amax, *scale_ub) : amax;
+    s = fmaxf(s / kFp8MaxG, 1.0f / (kFp8MaxG * 512.0f));
+    if (threadIdx.x == 0) scales[row] = s;
+    uint8_t* o = reinterpret_cast<uint8_t*>(out_) + row * hidden;
+#pragma unroll
+    for (int k = 0; k < kMaxVecPerThread; ++k) {
+      const int i = threadIdx.x + k * kGlueThreads;
+      if (i < nvec) {
+        union { uint2 u; uint8_t b[8]; } q;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q.b[j] = quant_clamped_g(zf[k][j] / s);
+        *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+      }
+    }
+  }
+}
+
+// rotary_embedding: one CTA per token, q and k heads rotated in place.  T arithmetic with a
+// rounding after every operation (x*cos, y*sin and the sum are each rounded to T), as the
+// reference's scalar_t expression does.
+template <typename T, bool NEOX>
+__global__ void __launch_bounds__(256) rotary_kernel(
+    const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
+    const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
+    int64_t head_stride, int num_heads, int num_kv_heads) {
+  const int token = blockIdx.x;
+  const int64_t pos = positions[token];
+  const T* cache = cos_sin_cache + pos * rot_dim;
+  const int embed = rot_dim >> 1;
+  const int total = (num_heads + (key ? num_kv_heads : 0)) * embed;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int head = i / embed;
+    const int off = i - head * embed;
+    T* arr = head < num_heads ? query + token * query_stride + head * head_stride
+                              : key + token * key_stride + (head - num_heads) * head_stride;
+    const int xi = NEOX ? off : 2 * off;
+    const int yi = NEOX ? embed + off : 2 * off + 1;
+    const float c = to_float<T>(cache[off]);
+    const float s = to_float<T>(cache[embed + off]);
+    const float x = to_float<T>(arr[xi]);
+    const float y = to_float<T>(arr[yi]);
+    const float xc = to_float<T>(from_float<T>(x * c)), ys = to_float<T>(from_float<T>(y * s));
+    const float yc = to_float<T>(from_float<T>(y * c)), xs = to_float<T>(from_float<T>(x * s));
+    arr[xi] = from_float<T>(xc - ys);
+    arr[yi] = from_float<T>(yc + xs);
+  }
+}
+
+// silu_and_mul followed by dynamic per-token fp8 quant in ONE pass: act = T(T(silu(x)) * y) is
+// kept in registers, amax reduced, then quantised with the true division of common.cu:74.
+// Bit-identical to silu_and_mul -> dynamic_per_token_scaled_fp8_quant run back to back.
+template <typename T>
+__global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
+    uint8_t* __restrict__ out, float* __restrict__ scales, const T* __restrict__ in,
+    const float* __restrict__ scale_ub, int d) {
+  __shared__ float sm[8];
+  const int64_t row = blockIdx.x;
+  const T* x = in + row * 2 * d;
+  const T* y = x + d;
+  const int nvec = d >> 3;
+  float act[kMaxVecPerThread][8];
+  float amax = 0.f;
+#pragma unroll
+  for (int k = 0; k < kMaxVecPerThread; ++k) {
+    const int i = threadIdx.x + k * kGlueThreads;
+    if (i < nvec) {
+      Vec8<T> a, b;
+      a.u = ldg_stream_v4(x + i * 8);
+      b.u = ldg_stream_v4(y + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xf = to_float<T>(a.e[j]);
+        const T sl = from_float<T>(xf / (1.0f + expf(-xf)));
+        act[k][j] = to_float<T>(from_float<T>(to_float<T>(sl) * to_float<T>(b.e[j])));
+        amax = fmaxf(amax, fabsf(act[k][j]));
+      }
+    }
+  }
+  amax = block_reduce<true>(amax, sm);
+  float s = scale_ub ? fminf(amax, *scale_ub) : amax;
+  s = fmaxf(s / kFp8MaxG, 1.0f / (kFp8MaxG * 512.0f));
+  if (threadIdx.x == 0) scales[row] = s;
+  uint8_t* o = out + row * d;
+#pragma unroll
+  for (int k = 0; k < kMaxVecPerThread; ++k) {
+    const int i = threadIdx.x + k * kGlueThreads;
+    if (i < nvec) {
+      union { uint2 u; uint8_t b[8]; } q;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) q.b[j] = quant_clamped_g(act[k][j] / s);
+      *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+    }
+  }
+}
+
+static int check_row(const char* op, int hidden, int dtype, const void* p0, const void* p1) {
+  VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "%s: dtype must be f16 or bf16", op);
+  VB_CHECK(hidden > 0 && hidden % 8 == 0 && hidden <= kGlueThreads * kMaxVecPerThread * 8,
+           "%s: hidden size %d must be a multiple of 8 and <= %d", op, hidden,
+           kGlueThreads * kMaxVecPerThread * 8);
+  VB_CHECK(((reinterpret_cast<uintptr_t>(p0) | reinterpret_cast<uintptr_t>(p1)) & 15) == 0,
+           "%s: tensors must be 16-byte aligned", op);
+  return 0;
+}
+
+}  // namespace vb200
+
+using namespace vb200;
+
+#define DISPATCH_16(dt, ...)                                     \
+  if ((dt) == VB200_F16) {                                       \
+    using scalar_t = __half;                                     \
+    __VA_ARGS__;                                                 \
+  } else {                                                       \
+    using scalar_t = __nv_bfloat16;                              \
+    __VA_ARGS__;                                                 \
+  }
+
+extern "C" int vb200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
+                              int num_tokens, int hidden_size, int64_t input_stride, int dtype,
+                              vb200_stream_t stream) {
+  if (num_tokens <= 0) return 0;
+  if (check_row("rms_norm", hidden_size, dtype, out, input)) return 1;
+  VB_CHECK(input_stride % 8 == 0, "rms_norm: input stride must be a multiple of 8");
+  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 0><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
+                         out, (scalar_t*)input, nullptr, (const scalar_t*)weight, nullptr, nullptr,
+                         epsilon, hidden_size, input_stride)));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_fused_add_rms_norm(void* input, void* residual, const void* weight,
+                                        float epsilon, int num_tokens, int hidden_size,
+                                        int64_t input_stride, int dtype, vb200_stream_t stream) {
+  if (num_tokens <= 0) return 0;
+  if (check_row("fused_add_rms_norm", hidden_size, dtype, input, residual)) return 1;
+  VB_CHECK(input_stride % 8 == 0, "fused_add_rms_norm: input stride must be a multiple of 8");
+  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 1><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
+                         nullptr, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight,
+                         nullptr, nullptr, epsilon, hidden_size, input_stride)));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_rms_norm_dynamic_per_token_quant(void* out, const void* input,
+                                                      const void* weight, float* scales,
+                                                      float epsilon, const float* scale_ub,
+                                                      void* residual, int num_tokens,
+                                                      int hidden_size, int dtype,
+                                                      vb200_stream_t stream) {
+  if (num_tokens <= 0) return 0;
+  if (check_row("rms_norm_dynamic_per_token_quant", hidden_size, dtype, input, residual)) return 1;
+  VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "rms_norm_dynamic_per_token_quant: out must be 8-byte aligned");
+  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 2><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
+                         out, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, scales,
+                         scale_ub, epsilon, hidden_size, (int64_t)hidden_size)));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_rotary_embedding(const int64_t* positions, void* query, void* key,
+                                      int num_tokens, int num_heads, int num_kv_heads,
+                                      int head_size, int rot_dim, const void* cos_sin_cache,
+                                      int is_neox, int64_t query_stride, int64_t key_stride,
+                                      int64_t head_stride, int dtype, vb200_stream_t stream) {
+  if (num_tokens <= 0) return 0;
+  VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "rotary_embedding: dtype must be f16 or bf16");
+  VB_CHECK(rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_size,
+           "rotary_embedding: rot_dim %d must be even and <= head_size %d", rot_dim, head_size);
+  const int work = (num_heads + (key ? num_kv_heads : 0)) * rot_dim / 2;
+  const int threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
+  DISPATCH_16(dtype, {
+    if (is_neox)
+      rotary_kernel<scalar_t, true><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
+          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
+          query_stride, key_stride, head_stride, num_heads, num_kv_heads);
+    else
+      rotary_kernel<scalar_t, false><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
+          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
+          query_stride, key_stride, head_stride, num_heads, num_kv_heads);
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scales,
+                                                          const void* input,
+                                                          const float* scale_ub, int num_tokens,
+                                                          int d, int dtype,
+                                                          vb200_stream_t stream) {
+  if (num_tokens <= 0) return 0;
+  if (check_row("silu_and_mul_dynamic_per_token_quant", d, dtype, input, input)) return 1;
+  VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "silu_and_mul_dynamic_per_token_quant: out must be 8-byte aligned");
+  DISPATCH_16(dtype, (silu_mul_quant_kernel<scalar_t><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
+                         (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, d)));
+  VB_LAUNCH_CHECK();
+  return 0;
+}

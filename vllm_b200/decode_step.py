@@ -1,0 +1,236 @@
+"""Dummy-weight decode-step driver: one forward pass of a Llama-style decoder for a batch of single-token
+(decode) requests over a paged KV cache, built ONLY from the hot-path ops of this package.  It stands where the
+reference's model definition + model runner stand (/root/reference/vllm/model_executor/models/llama.py:98-330,
+/root/reference/vllm/v1/worker/gpu_model_runner.py:1417) -- those are host orchestration and out of scope; this
+is the minimum of them needed to measure the path end to end.
+
+Per layer (FP8 w8a8, dynamic per-token activation scales, per-channel weight scales):
+  rms_norm_dynamic_per_token_quant(+residual) -> cutlass_scaled_mm (qkv, column-parallel) -> rotary_embedding ->
+  AttentionImpl.forward (reshape_and_cache + paged_attention) -> scaled_fp8_quant -> cutlass_scaled_mm (o,
+  row-parallel) -> all-reduce -> rms_norm_dynamic_per_token_quant(+residual) -> cutlass_scaled_mm (gate_up) ->
+  silu_and_mul_dynamic_per_token_quant -> cutlass_scaled_mm (down, row-parallel) -> all-reduce
+or, for Mixtral layers, the MoE block: router GEMM -> fused_topk -> fused_experts -> all-reduce.
+Tensor parallelism: heads / columns / expert-intermediate shards, one all-reduce per row-parallel GEMM
+(/root/reference/vllm/model_executor/layers/linear.py:1389).  The bf16 variant (BASELINE config 2) uses the
+library GEMM (torch.matmul -> cuBLAS) for the projections: only its attention/cache path is ours.
+"""
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from . import _custom_ops as ops
+from .attention import B200PagedAttentionBackend, B200PagedAttentionMetadata
+from .distributed import (get_tensor_model_parallel_rank, get_tensor_model_parallel_world_size,
+                          tensor_model_parallel_all_reduce)
+
+FP8 = torch.float8_e4m3fn
+
+
+@dataclass
+class DecoderConfig:
+    name: str
+    hidden_size: int
+    num_layers: int
+    num_heads: int
+    num_kv_heads: int
+    head_dim: int
+    intermediate_size: int
+    vocab_size: int
+    rope_theta: float = 500000.0
+    rms_eps: float = 1e-5
+    max_position: int = 131072
+    num_experts: int = 0     # > 0: Mixtral-style MoE MLP
+    top_k: int = 0
+
+
+LLAMA_3_1_8B = DecoderConfig("Llama-3.1-8B", 4096, 32, 32, 8, 128, 14336, 128256)
+LLAMA_3_1_70B = DecoderConfig("Llama-3.1-70B", 8192, 80, 64, 8, 128, 28672, 128256)
+MIXTRAL_8X7B = DecoderConfig("Mixtral-8x7B", 4096, 32, 32, 8, 128, 14336, 32000, rope_theta=1e6, num_experts=8,
+                             top_k=2)
+TINY = DecoderConfig("tiny-llama", 256, 2, 8, 2, 32, 512, 1024, rope_theta=10000.0, max_position=4096)
+TINY_MOE = DecoderConfig("tiny-mixtral", 256, 2, 8, 2, 32, 512, 1024, rope_theta=10000.0, max_position=4096,
+                         num_experts=4, top_k=2)
+CONFIGS = {c.name: c for c in (LLAMA_3_1_8B, LLAMA_3_1_70B, MIXTRAL_8X7B, TINY, TINY_MOE)}
+
+
+def _dummy_fp8_weight(n: int, k: int, device, gen: torch.Generator, std: float = 0.02):
+    """Random [N, K] weight quantised per output channel: returns (fp8 [N, K], fp32 scale [N, 1])."""
+    w = torch.empty(n, k, device=device, dtype=torch.bfloat16).normal_(0.0, std, generator=gen)
+    amax = w.abs().amax(dim=1, keepdim=True).float().clamp_(min=1e-8)
+    scale = amax / 448.0
+    q = (w.float() / scale).clamp_(-448.0, 448.0).to(FP8)
+    return q, scale
+
+
+def make_cos_sin_cache(rot_dim: int, max_position: int, base: float, dtype, device) -> torch.Tensor:
+    """RotaryEmbedding._compute_cos_sin_cache (vllm/model_executor/layers/rotary_embedding.py): [max_pos, rot_dim]."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rot_dim, 2, dtype=torch.float32, device=device) / rot_dim))
+    t = torch.arange(max_position, dtype=torch.float32, device=device)
+    freqs = torch.outer(t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype)
+
+
+class _KVScales:
+    """What an `Attention` layer object supplies to AttentionImpl.forward (abstract.py:240-247)."""
+
+    def __init__(self, device, k_scale: float = 1.0, v_scale: float = 1.0):
+        self._k_scale = torch.tensor(k_scale, dtype=torch.float32, device=device)
+        self._v_scale = torch.tensor(v_scale, dtype=torch.float32, device=device)
+
+
+class DecoderLayer:
+    def __init__(self, cfg: DecoderConfig, tp: int, device, dtype, quant: str, kv_cache_dtype: str,
+                 gen: torch.Generator):
+        self.cfg, self.tp, self.quant, self.dtype = cfg, tp, quant, dtype
+        H, D = cfg.hidden_size, cfg.head_dim
+        self.nh = cfg.num_heads // tp
+        self.nkv = max(cfg.num_kv_heads // tp, 1)   # kv heads are replicated when tp > num_kv_heads
+        self.q_size, self.kv_size = self.nh * D, self.nkv * D
+        self.inter = cfg.intermediate_size // tp
+        self.input_ln = torch.ones(H, device=device, dtype=dtype)
+        self.post_ln = torch.ones(H, device=device, dtype=dtype)
+        mk = (lambda n, k: _dummy_fp8_weight(n, k, device, gen)) if quant == "fp8" else (
+            lambda n, k: (torch.empty(n, k, device=device, dtype=dtype).normal_(0.0, 0.02, generator=gen), None))
+        self.w_qkv, self.s_qkv = mk(self.q_size + 2 * self.kv_size, H)
+        self.w_o, self.s_o = mk(H, self.q_size)
+        if cfg.num_experts:
+            from .fused_moe import make_dummy_experts
+            self.w_gate = torch.empty(cfg.num_experts, H, device=device, dtype=dtype).normal_(0.0, 0.02, generator=gen)
+            self.experts = make_dummy_experts(cfg.num_experts, H, self.inter, device, dtype, quant, gen)
+        else:
+            self.w_gate_up, self.s_gate_up = mk(2 * self.inter, H)
+            self.w_down, self.s_down = mk(H, self.inter)
+        impl_cls = B200PagedAttentionBackend.get_impl_cls()
+        self.attn = impl_cls(self.nh, D, D ** -0.5, self.nkv, None, None, kv_cache_dtype)
+        self.kv_scales = _KVScales(device, 0.05 if kv_cache_dtype != "auto" else 1.0,
+                                   0.05 if kv_cache_dtype != "auto" else 1.0)
+
+    # ---- linear helpers -------------------------------------------------------------------------------
+    def _linear_q(self, xq, xs, w, ws):
+        return ops.cutlass_scaled_mm(xq, w.t(), xs, ws.view(1, -1), self.dtype)
+
+    def forward(self, positions, hidden, residual, kv_cache, meta: B200PagedAttentionMetadata, cos_sin):
+        cfg, eps = self.cfg, self.cfg.rms_eps
+        fp8 = self.quant == "fp8"
+        # ---- attention block ----
+        if fp8:
+            if residual is None:
+                residual = hidden.clone()
+                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.input_ln, eps, FP8)
+            else:
+                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.input_ln, eps, FP8, None, residual)
+            qkv = self._linear_q(xq, xs, self.w_qkv, self.s_qkv)
+        else:
+            if residual is None:
+                residual = hidden.clone()
+                x = torch.empty_like(hidden)
+                ops.rms_norm(x, hidden, self.input_ln, eps)
+            else:
+                ops.fused_add_rms_norm(hidden, residual, self.input_ln, eps)
+                x = hidden
+            qkv = torch.matmul(x, self.w_qkv.t())
+        q = qkv[:, :self.q_size]
+        k = qkv[:, self.q_size:self.q_size + self.kv_size]
+        v = qkv[:, self.q_size + self.kv_size:]
+        ops.rotary_embedding(positions, q, k, cfg.head_dim, cos_sin, True)
+        attn_out = self.attn.forward(self.kv_scales, q, k, v, kv_cache, meta)
+        if fp8:
+            aq, a_s = ops.scaled_fp8_quant(attn_out, use_per_token_if_dynamic=True)
+            hidden = self._linear_q(aq, a_s, self.w_o, self.s_o)
+        else:
+            hidden = torch.matmul(attn_out, self.w_o.t())
+        hidden = tensor_model_parallel_all_reduce(hidden)
+        # ---- MLP block ----
+        if cfg.num_experts:
+            ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
+            from .fused_moe import moe_forward
+            hidden = moe_forward(hidden, self.w_gate, self.experts, cfg.top_k, renormalize=True)
+        elif fp8:
+            xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.post_ln, eps, FP8, None, residual)
+            gu = self._linear_q(xq, xs, self.w_gate_up, self.s_gate_up)
+            hq, hs = ops.silu_and_mul_dynamic_per_token_quant(gu)
+            hidden = self._linear_q(hq, hs, self.w_down, self.s_down)
+        else:
+            ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
+            gu = torch.matmul(hidden, self.w_gate_up.t())
+            act = torch.empty(gu.shape[0], self.inter, device=gu.device, dtype=gu.dtype)
+            ops.silu_and_mul(act, gu)
+            hidden = torch.matmul(act, self.w_down.t())
+        hidden = tensor_model_parallel_all_reduce(hidden)
+        return hidden, residual
+
+
+class Decoder:
+    """Dummy-weight decoder + paged KV cache for one tensor-parallel rank."""
+
+    def __init__(self, cfg: DecoderConfig, num_blocks: int, block_size: int = 16, kv_cache_dtype: str = "auto",
+                 quant: str = "fp8", dtype=torch.bfloat16, device="cuda", seed: int = 0,
+                 num_layers: Optional[int] = None):
+        self.cfg, self.block_size, self.kv_cache_dtype = cfg, block_size, kv_cache_dtype
+        self.device, self.dtype, self.quant = torch.device(device), dtype, quant
+        tp = get_tensor_model_parallel_world_size()
+        self.tp, self.tp_rank = tp, get_tensor_model_parallel_rank()
+        assert cfg.num_heads % tp == 0 and cfg.intermediate_size % tp == 0
+        gen = torch.Generator(device=self.device)
+        gen.manual_seed(seed + 1000 * self.tp_rank)
+        self.num_layers = cfg.num_layers if num_layers is None else num_layers
+        self.layers: List[DecoderLayer] = [DecoderLayer(cfg, tp, self.device, dtype, quant, kv_cache_dtype, gen)
+                                           for _ in range(self.num_layers)]
+        gen_rep = torch.Generator(device=self.device)
+        gen_rep.manual_seed(seed)  # replicated tensors: identical on every rank
+        self.embed = torch.empty(cfg.vocab_size, cfg.hidden_size, device=self.device, dtype=dtype).normal_(
+            0.0, 0.5, generator=gen_rep)
+        self.final_ln = torch.ones(cfg.hidden_size, device=self.device, dtype=dtype)
+        assert cfg.vocab_size % tp == 0
+        self.vocab_shard = cfg.vocab_size // tp
+        self.lm_head = torch.empty(self.vocab_shard, cfg.hidden_size, device=self.device, dtype=dtype).normal_(
+            0.0, 0.02, generator=gen)
+        self.cos_sin = make_cos_sin_cache(cfg.head_dim, cfg.max_position, cfg.rope_theta, dtype, self.device)
+        nkv = self.layers[0].nkv
+        shape = B200PagedAttentionBackend.get_kv_cache_shape(num_blocks, block_size, nkv, cfg.head_dim)
+        cache_dtype = torch.uint8 if kv_cache_dtype != "auto" else dtype
+        self.kv_caches = [torch.zeros(shape, dtype=cache_dtype, device=self.device) for _ in range(self.num_layers)]
+
+    def fill_kv_cache_random(self, seed: int = 1) -> None:
+        """Synthetic cache contents (finite values only), so that attention reads realistic bytes."""
+        gen = torch.Generator(device=self.device)
+        gen.manual_seed(seed + self.tp_rank)
+        for kv in self.kv_caches:
+            if kv.dtype == torch.uint8:
+                flat = kv.view(-1)
+                step = 1 << 28
+                for o in range(0, flat.numel(), step):
+                    part = flat[o:o + step]
+                    part.random_(0, 120, generator=gen)                     # finite e4m3 magnitudes
+                    sign = torch.empty_like(part).random_(0, 2, generator=gen)
+                    part.bitwise_or_(sign.bitwise_left_shift_(7))
+            else:
+                kv.normal_(0.0, 1.0, generator=gen)
+
+    def hidden_states(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
+        hidden = self.embed.index_select(0, input_ids)
+        residual = None
+        for layer, kv in zip(self.layers, self.kv_caches):
+            hidden, residual = layer.forward(positions, hidden, residual, kv, meta, self.cos_sin)
+        ops.fused_add_rms_norm(hidden, residual, self.final_ln, self.cfg.rms_eps)
+        return hidden
+
+    def forward(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
+        """Returns the logits of this rank's vocabulary shard, [T, vocab/tp] (library GEMM: lm_head is not fp8)."""
+        return torch.matmul(self.hidden_states(input_ids, positions, meta), self.lm_head.t())
+
+    def greedy_step(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
+        """One decode step with greedy sampling: next token ids [T] int64 (vocab-parallel arg-max)."""
+        logits = self.forward(input_ids, positions, meta).float()
+        val, idx = logits.max(dim=-1)
+        idx = idx + self.tp_rank * self.vocab_shard
+        if self.tp == 1:
+            return idx
+        import torch.distributed as dist
+        vals = [torch.empty_like(val) for _ in range(self.tp)]
+        idxs = [torch.empty_like(idx) for _ in range(self.tp)]
+        dist.all_gather(vals, val)
+        dist.all_gather(idxs, idx)
+        best = torch.stack(vals).argmax(dim=0, keepdim=True)
+        return torch.stack(idxs).gather(0, best).squeeze(0)

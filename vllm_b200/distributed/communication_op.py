@@ -1,0 +1,40 @@
+"""One process per GPU; torch.distributed (NCCL over NVLink/NVSwitch on the GPU box, gloo in the CPU tests) is
+the plumbing.  Mirrors the call site of /root/reference/vllm/distributed/communication_op.py:12-14 and the
+GroupCoordinator.all_reduce contract (parallel_state.py: world size 1 bypasses, the result is the summed tensor).
+The all-reduce is issued on the current stream so it is captured inside the decode CUDA graph, as pynccl does in
+the reference (device_communicators/cuda_communicator.py:93-118)."""
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+_TP_GROUP: Optional["dist.ProcessGroup"] = None
+_TP_WORLD = 1
+_TP_RANK = 0
+
+
+def init_tensor_parallel(group: Optional["dist.ProcessGroup"] = None) -> None:
+    """Use `group` (default: the world group, if torch.distributed is initialised) as the TP group."""
+    global _TP_GROUP, _TP_WORLD, _TP_RANK
+    if group is None and not (dist.is_available() and dist.is_initialized()):
+        _TP_GROUP, _TP_WORLD, _TP_RANK = None, 1, 0
+        return
+    _TP_GROUP = group if group is not None else dist.group.WORLD
+    _TP_WORLD = dist.get_world_size(_TP_GROUP)
+    _TP_RANK = dist.get_rank(_TP_GROUP)
+
+
+def get_tensor_model_parallel_world_size() -> int:
+    return _TP_WORLD
+
+
+def get_tensor_model_parallel_rank() -> int:
+    return _TP_RANK
+
+
+def tensor_model_parallel_all_reduce(input_: torch.Tensor) -> torch.Tensor:
+    """All-reduce (sum) across the tensor-parallel group; in place, returns its argument."""
+    if _TP_WORLD == 1:
+        return input_
+    dist.all_reduce(input_, op=dist.ReduceOp.SUM, group=_TP_GROUP)
+    return input_
