@@ -17,16 +17,28 @@ SHAPES = {"qkv": (6144, 4096), "o": (4096, 4096), "gate_up": (28672, 4096), "dow
 
 
 def timeit(fn, iters, warmup=3):
-    for i in range(warmup):
-        fn(i)
+    """Kernel time without host launch overhead: `iters` calls (rotating weight pools) captured in ONE CUDA graph,
+    replayed 3 times after a warm-up replay; CUDA events around the replays."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(warmup):
+            fn(i)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            fn(i)
+    g.replay()
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for i in range(iters):
-        fn(i)
+    for _ in range(3):
+        g.replay()
     b.record()
     b.synchronize()
-    return a.elapsed_time(b) * 1e-3 / iters
+    return a.elapsed_time(b) * 1e-3 / (3 * iters)
 
 
 def main():

@@ -253,24 +253,27 @@ int vb200_moe_sum(void* out, const void* input, int num_tokens, int topk, int hi
 
 /* Grouped FP8 GEMM of fused_experts (the work of invoke_fused_moe_kernel,
  * vllm/model_executor/layers/fused_moe/fused_moe.py:478-647, Triton kernel :267-475), driven by
- * moe_align_block_size's outputs with block_size == VB200_MOE_BLOCK_M:
- *   for M-block p: expert e = expert_ids[p]; rows = sorted_token_ids[p*BM : (p+1)*BM]
- *   (entries >= num_valid_tokens are padding); A row = token_id / top_k;
- *   C[token_id, n] = OutT( (sum_k A[row,k] * B[e,n,k]) * [topk_weights[token_id]] * a_scale * b_scale[e] )
+ * moe_align_block_size's outputs computed with block_size == block_m:
+ *   for M-block p: expert e = expert_ids[p] (e < 0: the block's rows of C are zeroed, :370-377);
+ *   rows = sorted_token_ids[p*block_m : (p+1)*block_m] (entries >= num_valid_tokens are padding);
+ *   A row = token_id / top_k;
+ *   C[token_id, n] = OutT( ((sum_k A[row,k] * B[e,n,k]) * [topk_weights[token_id]]) * a_scale * b_scale )
  *   (routed weight multiplied BEFORE the scales, in fp32: fused_moe.py:455-468).
- *   a  fp8 [num_a_rows, K];  b fp8 [E, N, K] (K contiguous);  c [num_valid_tokens, N] out_dtype.
- *   a_scales: fp32, 1 (per-tensor) or num_a_rows (per-token); b_scales: fp32 [E] (per-tensor per
- *   expert) or [E, N] (per-channel), selected by b_scales_per_channel. */
-#define VB200_MOE_BLOCK_M 128
+ *   a  fp8 [num_a_rows, K] contiguous;  b fp8 [E, N, K] contiguous;  c [num_valid_tokens, N] out_dtype.
+ *   a_scales: fp32, 1 (per-tensor) or num_a_rows (per-token, a_scales_per_token);
+ *   b_scales: fp32 [E] (per-tensor per expert) or [E, N] (per-channel, b_scales_per_channel).
+ *   block_m: multiple of 16 in [16, 256]; K % 16 == 0.
+ *   workspace: vb200_moe_grouped_gemm_workspace_size(sorted_capacity, K) bytes of device scratch
+ *   (the activation rows gathered in sorted order); no initialisation needed. */
+size_t vb200_moe_grouped_gemm_workspace_size(int sorted_capacity, int K);
 int vb200_moe_grouped_gemm_fp8(void* c, const void* a, const void* b, const float* a_scales,
                                const float* b_scales, const float* topk_weights,
                                const int32_t* sorted_token_ids, const int32_t* expert_ids,
                                const int32_t* num_tokens_post_pad, int num_valid_tokens,
-                               int num_a_rows, int top_k, int E, int N, int K,
+                               int num_a_rows, int top_k, int E, int N, int K, int block_m,
                                int sorted_capacity, int a_scales_per_token,
                                int b_scales_per_channel, int mul_routed_weight, int out_dtype,
                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
-size_t vb200_moe_grouped_gemm_workspace_size(int sorted_capacity, int K);
 
 #ifdef __cplusplus
 }

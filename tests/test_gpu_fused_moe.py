@@ -1,0 +1,131 @@
+"""GPU parity: the fused-MoE grouped FP8 GEMM (invoke_fused_moe_kernel) and fused_experts / fused_moe through the
+C ABI vs the oracle (oracle/moe.py, which follows fused_moe.py:455-468's operation order and torch_experts,
+/root/reference/tests/kernels/utils.py:1060-1152).  Tolerance (north_star): 1e-2 rel / 2e-2 abs against the
+reference's dequantised result.  Modelled on /root/reference/tests/kernels/moe/test_moe.py:60-160."""
+import pytest
+import torch
+
+from oracle import moe as omoe
+from oracle import quant as oq
+from parity_utils import seed_all
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+FP8 = torch.float8_e4m3fn
+RTOL, ATOL = 1e-2, 2e-2
+
+
+def _fp8_weights(E, N, K, per_channel):
+    w = torch.randn(E, N, K) / 10
+    if per_channel:
+        s = w.abs().amax(dim=2).clamp(min=1e-6) / 448.0          # [E, N]
+        q = (w / s[:, :, None]).clamp(-448, 448).to(FP8)
+    else:
+        s = w.abs().amax(dim=(1, 2)).clamp(min=1e-6) / 448.0      # [E]
+        q = (w / s[:, None, None]).clamp(-448, 448).to(FP8)
+    return q, s.float()
+
+
+@pytest.mark.parametrize("T,k,E,N,K,block_m", [
+    (1, 2, 8, 256, 128, 16), (33, 2, 8, 512, 256, 16), (128, 2, 8, 1024, 512, 64), (128, 2, 8, 384, 4096, 32),
+    (64, 6, 64, 256, 512, 16), (300, 2, 4, 256, 256, 128), (700, 2, 2, 128, 128, 256), (17, 1, 3, 144, 272, 16)])
+@pytest.mark.parametrize("per_channel", [False, True])
+@pytest.mark.parametrize("mul_w", [False, True])
+def test_grouped_gemm(T, k, E, N, K, block_m, per_channel, mul_w):
+    from vllm_b200.fused_moe import invoke_fused_moe_kernel, moe_align_block_size
+    seed_all(T + N)
+    wq, ws = _fp8_weights(E, N, K, per_channel)
+    a = torch.randn(T, K)
+    if per_channel:
+        aq, a_s = oq.dynamic_per_token_scaled_fp8_quant(a.bfloat16())
+    else:
+        aq, a_s = oq.dynamic_scaled_fp8_quant(a.bfloat16())
+        a_s = a_s.reshape(1, 1)
+    ids = torch.stack([torch.randperm(E)[:k] for _ in range(T)]).to(torch.int32)
+    tw = torch.rand(T, k) + 0.1
+    want = omoe.grouped_gemm_fp8(aq, a_s, wq, ws, ids, k, tw if mul_w else None, torch.bfloat16)
+    sorted_ids, expert_ids, npost = moe_align_block_size(ids.to(DEV), block_m, E)
+    c = torch.full((T, k, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    invoke_fused_moe_kernel(aq.to(DEV), wq.to(DEV), c, a_s.to(DEV).reshape(-1), ws.to(DEV), tw.to(DEV) if mul_w else None,
+                            sorted_ids, expert_ids, npost, mul_w, k, block_m, True, per_channel)
+    torch.cuda.synchronize()
+    got = c.view(T * k, N).cpu().float()
+    assert torch.isfinite(got).all(), "every (token, expert) row must be written"
+    torch.testing.assert_close(got, want.float(), rtol=RTOL, atol=ATOL)
+    # the fp32 accumulation is exact for fp8 x fp8 products of this size: only the final bf16 rounding may differ
+    assert (got - want.float()).abs().max() <= 2.0 ** -7 * want.float().abs().max() + 1e-6
+
+
+def test_grouped_gemm_expert_map_zeros():
+    """Blocks whose expert is mapped to -1 (expert parallel) are written as zeros (fused_moe.py:370-377)."""
+    from vllm_b200.fused_moe import invoke_fused_moe_kernel, moe_align_block_size
+    seed_all(3)
+    T, k, E, N, K, bm = 40, 2, 4, 256, 256, 16
+    wq, ws = _fp8_weights(E, N, K, False)
+    aq, a_s = oq.dynamic_scaled_fp8_quant(torch.randn(T, K).bfloat16())
+    ids = torch.stack([torch.randperm(E)[:k] for _ in range(T)]).to(torch.int32)
+    emap = torch.tensor([0, -1, 1, -1], dtype=torch.int32)          # experts 0 and 2 live here as local 0, 1
+    sorted_ids, expert_ids, npost = moe_align_block_size(ids.to(DEV), bm, E, emap.to(DEV))
+    local_w, local_s = wq[[0, 2]], ws[[0, 2]]
+    c = torch.full((T, k, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    invoke_fused_moe_kernel(aq.to(DEV), local_w.to(DEV), c, a_s.to(DEV), local_s.to(DEV), None, sorted_ids, expert_ids,
+                            npost, False, k, bm)
+    got = c.view(T * k, N).cpu().float()
+    want = omoe.grouped_gemm_fp8(aq, a_s.reshape(1, 1), wq, ws, ids, k, None, torch.bfloat16).float()
+    dead = ((ids.flatten() == 1) | (ids.flatten() == 3))
+    assert (got[dead] == 0).all()
+    torch.testing.assert_close(got[~dead], want[~dead], rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("T,k,E,H,I", [(1, 2, 8, 256, 512), (128, 2, 8, 512, 1024), (33, 6, 64, 256, 256),
+                                        (222, 2, 8, 1024, 896)])
+@pytest.mark.parametrize("per_channel", [False, True])
+def test_fused_experts_fp8(T, k, E, H, I, per_channel):
+    from vllm_b200.fused_moe import fused_experts, fused_topk
+    seed_all(T + H)
+    w1q, w1s = _fp8_weights(E, 2 * I, H, per_channel)
+    w2q, w2s = _fp8_weights(E, H, I, per_channel)
+    x = (torch.randn(T, H) / 2).bfloat16()
+    gate = torch.randn(T, E)
+    tw_o, ids_o, _ = omoe.topk_softmax(gate, k)
+    tw_o = tw_o / tw_o.sum(-1, keepdim=True)
+    want = omoe.fused_experts_fp8(x, w1q, w2q, w1s, w2s, tw_o, ids_o, per_channel_quant=per_channel)
+    tw, ids, _ = fused_topk(x.to(DEV), gate.to(DEV), k, True)
+    assert torch.equal(ids.cpu(), ids_o), "top-k ids must be bit-exact"
+    w1s_d = w1s.to(DEV).reshape(E, -1, 1) if per_channel else w1s.to(DEV)
+    w2s_d = w2s.to(DEV).reshape(E, -1, 1) if per_channel else w2s.to(DEV)
+    out = fused_experts(x.to(DEV), w1q.to(DEV), w2q.to(DEV), tw, ids, use_fp8_w8a8=True, per_channel_quant=per_channel,
+                        w1_scale=w1s_d, w2_scale=w2s_d)
+    torch.cuda.synchronize()
+    # intermediate fp8 re-quantisation makes single elements flip by one fp8 step: compare with the reference
+    # tests' own bound for fp8 MoE (test_moe.py: atol 2e-2 / rtol 1e-2 scaled by the output magnitude)
+    got, w = out.cpu().float(), want.float()
+    scale = w.abs().max().item()
+    torch.testing.assert_close(got, w, rtol=2e-2, atol=2e-2 * max(scale, 1.0))
+    assert (got - w).abs().mean().item() <= 3e-3 * max(scale, 1.0)
+
+
+def test_fused_experts_cuda_graph():
+    """Capturable in a CUDA graph (tests/kernels/moe/test_moe.py:93-107 does the same)."""
+    from vllm_b200.fused_moe import fused_moe
+    seed_all(1)
+    T, k, E, H, I = 64, 2, 8, 256, 512
+    w1q, w1s = _fp8_weights(E, 2 * I, H, False)
+    w2q, w2s = _fp8_weights(E, H, I, False)
+    x = (torch.randn(T, H) / 2).bfloat16().to(DEV)
+    gate = torch.randn(T, E).to(DEV)
+    args = (x, w1q.to(DEV), w2q.to(DEV), gate, k, True)
+    kw = dict(use_fp8_w8a8=True, w1_scale=w1s.to(DEV), w2_scale=w2s.to(DEV))
+    eager = fused_moe(*args, **kw)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        fused_moe(*args, **kw)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        out = fused_moe(*args, **kw)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, eager)

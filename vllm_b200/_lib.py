@@ -77,7 +77,7 @@ SIGNATURES = {
                                            c_size_t, _P]),
     "vb200_moe_sum": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_moe_grouped_gemm_fp8": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
-                                           c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t,
+                                           c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t,
                                            _P]),
     "vb200_moe_grouped_gemm_workspace_size": (c_size_t, [c_int, c_int]),
 }

@@ -1,0 +1,317 @@
+// Fused-MoE grouped FP8 GEMM for sm_100a: the work of invoke_fused_moe_kernel
+// (/root/reference/vllm/model_executor/layers/fused_moe/fused_moe.py:478-647; Triton kernel :267-475)
+// as a tcgen05 / TMEM / TMA kernel driven by moe_align_block_size's outputs.
+//
+// Decode-shaped design (same "swap-AB" mapping as scaled_mm.cu): an expert's WEIGHT rows are the
+// UMMA M side (128 TMEM lanes per CTA), the tokens routed to that expert are the UMMA N side.  The
+// N extent of every MMA is trimmed to the number of valid rows of the M-block (rounded up to 16),
+// so the padding moe_align_block_size adds costs no tensor work, and a decode batch (tens of tokens
+// per expert) reads every expert weight byte exactly once: the kernel is a pure HBM stream of the
+// expert weights (1.4 GB / layer for Mixtral-8x7B at TP 1).
+//   grid = (ceil(N/128), max M-blocks); CTA (n_tile, p): expert e = expert_ids[p]
+//   warp 0: TMA producer  (W tile [128 x 128 B] of expert e, A tile [block_m x 128 B] of the
+//           gathered activations, 128-byte swizzle, mbarrier complete_tx)
+//   warp 1: tcgen05.mma issuer (one thread), accumulator in TMEM
+//   warps 2-5: epilogue: tcgen05.ld -> (acc * routed_weight) * a_scale * b_scale -> out dtype ->
+//           C[token_id, n]  (routed weight BEFORE the scales, fused_moe.py:455-468)
+// Two CTAs are resident per SM (<= 113 KB of shared memory each), so one CTA's prologue/epilogue
+// overlaps the other's weight stream.
+// The activation rows of a block are not contiguous in A (row = token_id / top_k): a small gather
+// kernel first writes them in sorted order into the workspace, so the GEMM loads A with plain TMA.
+#include "tc_common.cuh"
+
+namespace vb200 {
+using namespace tc;
+
+constexpr int kMoeBlockN = 128;   // weight rows per CTA (UMMA M)
+constexpr int kMoeBlockK = 128;   // K bytes per stage
+constexpr int kMoeUmmaK = 32;
+constexpr int kMoeThreads = 192;
+constexpr int kMoeMaxStages = 8;
+constexpr int kMoeMaxBlockM = 256;
+constexpr int kMoeWTile = kMoeBlockN * kMoeBlockK;
+
+struct MoeParams {
+  void* c;
+  const float* a_scales;
+  const float* b_scales;
+  const float* topk_weights;  // nullptr: no routed-weight multiply
+  const int32_t* sorted_token_ids;
+  const int32_t* expert_ids;
+  const int32_t* num_tokens_post_pad;
+  int num_valid_tokens, top_k, E, N, K, block_m;
+  int a_per_token, b_per_channel;
+  int stages, num_kb, tmem_cols;
+};
+
+// A_sorted[r, :] = A[sorted_token_ids[r] / top_k, :] for valid r < num_tokens_post_pad (16-byte
+// vectors; padding rows are left untouched: their accumulator columns are never written out).
+__global__ void __launch_bounds__(256) moe_gather_rows_kernel(
+    uint8_t* __restrict__ a_sorted, const uint8_t* __restrict__ a,
+    const int32_t* __restrict__ sorted_token_ids, const int32_t* __restrict__ num_tokens_post_pad,
+    int num_valid_tokens, int top_k, int K, int sorted_capacity) {
+  const int npost = min(*num_tokens_post_pad, sorted_capacity);
+  const int vec_per_row = K >> 4;
+  for (int r = blockIdx.x; r < npost; r += gridDim.x) {
+    const int tok = sorted_token_ids[r];
+    if (tok >= num_valid_tokens || tok < 0) continue;
+    const uint4* src = reinterpret_cast<const uint4*>(a + (int64_t)(tok / top_k) * K);
+    uint4* dst = reinterpret_cast<uint4*>(a_sorted + (int64_t)r * K);
+    for (int i = threadIdx.x; i < vec_per_row; i += blockDim.x) dst[i] = src[i];
+  }
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(kMoeThreads, 2)
+    moe_grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                            const __grid_constant__ CUtensorMap tmap_a, const MoeParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int a_tile_bytes = p.block_m * kMoeBlockK;
+  const int stage_bytes = kMoeWTile + a_tile_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + kMoeMaxStages;
+  uint64_t* acc_bar = empty_bar + kMoeMaxStages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_bar + 1);
+  int* s_nvalid = reinterpret_cast<int*>(tmem_ptr + 1);
+  int* s_tok = reinterpret_cast<int*>(tmem_ptr + 4);          // [block_m] token ids of this block
+  float* s_rowscale = reinterpret_cast<float*>(s_tok + kMoeMaxBlockM);  // [block_m] routed_w, a_scale
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x;
+  const int pblk = blockIdx.y;
+  const int row0 = pblk * p.block_m;
+  if (row0 >= *p.num_tokens_post_pad) return;  // uniform across the CTA
+  const int expert = p.expert_ids[pblk];
+  const int n0 = n_tile * kMoeBlockN;
+
+  // ---- block metadata: token ids, valid count -----------------------------------------------------
+  if (threadIdx.x == 0) *s_nvalid = 0;
+  __syncthreads();
+  {
+    int cnt = 0;
+    for (int i = threadIdx.x; i < p.block_m; i += kMoeThreads) {
+      const int tok = p.sorted_token_ids[row0 + i];
+      s_tok[i] = tok;
+      if (tok >= 0 && tok < p.num_valid_tokens) cnt = max(cnt, i + 1);
+    }
+    if (cnt) atomicMax(s_nvalid, cnt);
+  }
+  __syncthreads();
+  const int nvalid = *s_nvalid;                    // valid rows are a prefix of the block
+  if (nvalid == 0) return;
+  const int umma_n = max(16, (nvalid + 15) & ~15);  // <= block_m (multiple of 16)
+
+  if (expert < 0 || expert >= p.E) {
+    // expert not on this rank (expert_map -> -1): write zeros (fused_moe.py:370-377)
+    OutT* outp = reinterpret_cast<OutT*>(p.c);
+    for (int i = 0; i < nvalid; ++i) {
+      const int tok = s_tok[i];
+      if (tok < 0 || tok >= p.num_valid_tokens) continue;
+      for (int n = n0 + threadIdx.x; n < min(n0 + kMoeBlockN, p.N); n += kMoeThreads)
+        outp[(int64_t)tok * p.N + n] = from_float<OutT>(0.f);
+    }
+    return;
+  }
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_w);
+    prefetch_tensormap(&tmap_a);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, (uint32_t)p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int wrow = expert * p.N + n0;  // row of the [E*N, K] weight matrix
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sw = smem + (size_t)stage * stage_bytes;
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+        tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * kMoeBlockK, wrow, kEvictFirst);
+        tma_load_2d(sw + kMoeWTile, &tmap_a, &full_bar[stage], kb * kMoeBlockK, row0, kEvictLast);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_f8(kMoeBlockN, umma_n);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sw = smem_u32(smem + (size_t)stage * stage_bytes);
+        const uint64_t adesc = make_smem_desc_sw128(sw);
+        const uint64_t bdesc = make_smem_desc_sw128(sw + kMoeWTile);
+#pragma unroll
+        for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
+          umma_f8(tmem_base, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+                  bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+        umma_commit(&empty_bar[stage]);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(acc_bar);
+    }
+  } else {
+    // ===== epilogue warps 2..5 =====
+    const int q = warp & 3;
+    const int ep_tid = threadIdx.x - 64;
+    // per-row factors: routed weight and per-token activation scale, staged while the GEMM runs
+    for (int i = ep_tid; i < umma_n; i += 128) {
+      const int tok = s_tok[i];
+      const bool ok = tok >= 0 && tok < p.num_valid_tokens;
+      s_rowscale[i] = (ok && p.topk_weights) ? p.topk_weights[tok] : 1.f;
+      s_rowscale[kMoeMaxBlockM + i] =
+          p.a_per_token ? (ok ? p.a_scales[tok / p.top_k] : 0.f) : p.a_scales[0];
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int nl = q * 32 + lane;
+    const int n = n0 + nl;
+    const bool n_ok = n < p.N;
+    const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[(int64_t)expert * p.N + n] : 0.f)
+                                      : p.b_scales[expert];
+    const bool mul_w = p.topk_weights != nullptr;
+    mbar_wait(acc_bar, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    OutT* outp = reinterpret_cast<OutT*>(p.c);
+    for (int c = 0; c < umma_n; c += 16) {
+      uint32_t r[16];
+      tmem_ld_x16(taddr + c, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int i = c + j;
+        if (i < nvalid && n_ok) {
+          const int tok = s_tok[i];
+          if (tok >= 0 && tok < p.num_valid_tokens) {
+            float v = __uint_as_float(r[j]);
+            if (mul_w) v = v * s_rowscale[i];
+            v = (v * s_rowscale[kMoeMaxBlockM + i]) * bsc;
+            outp[(int64_t)tok * p.N + n] = from_float<OutT>(v);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  }
+}
+
+}  // namespace vb200
+
+using namespace vb200;
+
+extern "C" size_t vb200_moe_grouped_gemm_workspace_size(int sorted_capacity, int K) {
+  if (sorted_capacity <= 0 || K <= 0) return 0;
+  // gathered activations + one extra M-block of slack so a TMA box never leaves the allocation
+  return ((size_t)sorted_capacity + kMoeMaxBlockM) * (size_t)K + 256;
+}
+
+extern "C" int vb200_moe_grouped_gemm_fp8(
+    void* c, const void* a, const void* b, const float* a_scales, const float* b_scales,
+    const float* topk_weights, const int32_t* sorted_token_ids, const int32_t* expert_ids,
+    const int32_t* num_tokens_post_pad, int num_valid_tokens, int num_a_rows, int top_k, int E,
+    int N, int K, int block_m, int sorted_capacity, int a_scales_per_token,
+    int b_scales_per_channel, int mul_routed_weight, int out_dtype, void* workspace,
+    size_t workspace_bytes, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(out_dtype == VB200_BF16 || out_dtype == VB200_F16,
+           "moe_grouped_gemm_fp8: out dtype must be bf16 or f16");
+  VB_CHECK(K > 0 && K % 16 == 0, "moe_grouped_gemm_fp8: K (%d) must be a positive multiple of 16", K);
+  VB_CHECK(block_m >= 16 && block_m <= kMoeMaxBlockM && block_m % 16 == 0,
+           "moe_grouped_gemm_fp8: block_m (%d) must be a multiple of 16 in [16, 256]", block_m);
+  VB_CHECK(top_k >= 1 && E >= 1 && N >= 1, "moe_grouped_gemm_fp8: bad top_k / E / N");
+  VB_CHECK(!mul_routed_weight || topk_weights != nullptr,
+           "moe_grouped_gemm_fp8: mul_routed_weight needs topk_weights");
+  (void)num_a_rows;
+  if (num_valid_tokens <= 0 || sorted_capacity <= 0) return 0;
+  const size_t need = vb200_moe_grouped_gemm_workspace_size(sorted_capacity, K);
+  VB_CHECK(workspace != nullptr && workspace_bytes >= need,
+           "moe_grouped_gemm_fp8: workspace too small (%zu < %zu)", workspace_bytes, need);
+  uint8_t* a_sorted = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(workspace) + 255) & ~static_cast<uintptr_t>(255));
+  VB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0, "moe_grouped_gemm_fp8: A must be 16-byte aligned");
+  {
+    int grid = sorted_capacity < num_sms() * 8 ? sorted_capacity : num_sms() * 8;
+    moe_gather_rows_kernel<<<grid, K >= 4096 ? 256 : 128, 0, stream>>>(
+        a_sorted, reinterpret_cast<const uint8_t*>(a), sorted_token_ids, num_tokens_post_pad,
+        num_valid_tokens, top_k, K, sorted_capacity);
+    VB_LAUNCH_CHECK();
+  }
+  const int m_blocks = (sorted_capacity + block_m - 1) / block_m;
+  CUtensorMap tw, ta;
+  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)K, (uint64_t)K, kMoeBlockN)) return 1;
+  if (tc::make_tmap_2d_u8(&ta, a_sorted, (uint64_t)m_blocks * block_m, (uint64_t)K, (uint64_t)K,
+                          (uint32_t)block_m))
+    return 1;
+  MoeParams p;
+  p.c = c;
+  p.a_scales = a_scales;
+  p.b_scales = b_scales;
+  p.topk_weights = mul_routed_weight ? topk_weights : nullptr;
+  p.sorted_token_ids = sorted_token_ids;
+  p.expert_ids = expert_ids;
+  p.num_tokens_post_pad = num_tokens_post_pad;
+  p.num_valid_tokens = num_valid_tokens;
+  p.top_k = top_k;
+  p.E = E;
+  p.N = N;
+  p.K = K;
+  p.block_m = block_m;
+  p.a_per_token = a_scales_per_token ? 1 : 0;
+  p.b_per_channel = b_scales_per_channel ? 1 : 0;
+  p.num_kb = (K + kMoeBlockK - 1) / kMoeBlockK;
+  const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
+  const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
+  // two CTAs per SM when the stages fit in half of the shared memory, else one
+  int budget = (227 * 1024) / 2 - 1024 - meta;
+  int stages = budget / stage_bytes;
+  if (stages < 3) {
+    budget = 227 * 1024 - 1024 - meta;
+    stages = budget / stage_bytes;
+  }
+  if (stages > kMoeMaxStages) stages = kMoeMaxStages;
+  if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
+  p.stages = stages;
+  int cols = 32;
+  while (cols < block_m) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
+  dim3 grid((N + kMoeBlockN - 1) / kMoeBlockN, m_blocks);
+  if (out_dtype == VB200_BF16) {
+    auto kern = moe_grouped_gemm_kernel<__nv_bfloat16>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+  } else {
+    auto kern = moe_grouped_gemm_kernel<__half>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+  }
+  VB_LAUNCH_CHECK();
+  return 0;
+}

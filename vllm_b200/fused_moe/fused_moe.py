@@ -1,0 +1,162 @@
+"""Mirror of the decode-relevant part of /root/reference/vllm/model_executor/layers/fused_moe/fused_moe.py:
+fused_topk (:882-915), invoke_fused_moe_kernel (:478-647, the Triton kernel :267-475 replaced by the tcgen05
+grouped GEMM), fused_experts / fused_experts_impl (:1253-1346, :1349-1563), fused_moe (:1566-1670).
+FP8 w8a8 experts only (per-tensor or per-channel weight scales; static / dynamic per-tensor / per-token
+activation scales): that is what BASELINE config 4 (Mixtral-8x7B FP8) runs."""
+from typing import Optional
+
+import torch
+
+from .. import _custom_ops as ops
+from .._lib import check, dtype_enum, load, ptr, stream
+from .moe_align_block_size import moe_align_block_size
+
+FP8 = torch.float8_e4m3fn
+
+
+def fused_topk(hidden_states: torch.Tensor, gating_output: torch.Tensor, topk: int, renormalize: bool,
+               indices_type: Optional[torch.dtype] = None) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """fused_moe.py:882-915 (+ vllm_topk_softmax :866-879): fp32 softmax, top-k with lowest-index ties,
+    optional renormalisation w /= w.sum(-1)."""
+    assert hidden_states.size(0) == gating_output.size(0), "Number of tokens mismatch"
+    M = hidden_states.size(0)
+    dev = hidden_states.device
+    topk_weights = torch.empty(M, topk, dtype=torch.float32, device=dev)
+    topk_ids = torch.empty(M, topk, dtype=torch.int32 if indices_type is None else indices_type, device=dev)
+    token_expert_indices = torch.empty(M, topk, dtype=torch.int32, device=dev)
+    ops.topk_softmax(topk_weights, topk_ids, token_expert_indices, gating_output.float().contiguous())
+    if renormalize:
+        topk_weights = topk_weights / topk_weights.sum(dim=-1, keepdim=True)
+    return topk_weights, topk_ids, token_expert_indices
+
+
+def get_block_m(num_pairs: int, num_experts: int) -> int:
+    """M-block (tokens per grouped-GEMM tile) for the tcgen05 kernel: tokens sit on the UMMA N side, whose size
+    the kernel trims to the block's valid rows, so padding costs no math -- pick the block so that an average
+    expert fits in one (stands where get_default_config's BLOCK_SIZE_M stands, fused_moe.py:766-824)."""
+    avg = max(1, num_pairs // max(num_experts, 1))
+    for bm in (16, 32, 64, 128):
+        if avg * 3 <= bm * 2:
+            return bm
+    return 256 if avg > 192 else 128
+
+
+_MOE_WS = {}
+
+
+def _moe_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    ws = _MOE_WS.get(device.index)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 16 << 20), dtype=torch.uint8, device=device)
+        _MOE_WS[device.index] = ws
+    return ws
+
+
+def invoke_fused_moe_kernel(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, A_scale: Optional[torch.Tensor],
+                            B_scale: Optional[torch.Tensor], topk_weights: Optional[torch.Tensor],
+                            sorted_token_ids: torch.Tensor, expert_ids: torch.Tensor,
+                            num_tokens_post_padded: torch.Tensor, mul_routed_weight: bool, top_k: int,
+                            block_m: int, use_fp8_w8a8: bool = True, per_channel_quant: bool = False) -> None:
+    """fused_moe.py:478-647.  A fp8 [rows, K] (row = token_id // top_k); B fp8 [E, N, K]; C [num_pairs, N]
+    (any leading shape, contiguous); A_scale [1] or [rows, 1]; B_scale [E] or [E, N(,1)]."""
+    if not use_fp8_w8a8 or A.dtype != FP8 or B.dtype != FP8:
+        raise RuntimeError("invoke_fused_moe_kernel: only the fp8 w8a8 grouped GEMM is built")
+    assert sorted_token_ids.stride(0) == 1 and B.stride(-1) == 1 and A.stride(-1) == 1
+    assert A.is_contiguous() and B.is_contiguous() and C.is_contiguous()
+    E, N, K = B.shape
+    num_pairs = C.numel() // N
+    lib = load()
+    ws_bytes = lib.vb200_moe_grouped_gemm_workspace_size(sorted_token_ids.numel(), K)
+    ws = _moe_workspace(A.device, ws_bytes)
+    a_per_token = 1 if A_scale.numel() > 1 else 0
+    b_per_channel = 1 if B_scale.numel() > E else 0
+    if a_per_token and A_scale.numel() != A.shape[0]:
+        raise RuntimeError("invoke_fused_moe_kernel: per-token A_scale needs one entry per row of A")
+    check(lib.vb200_moe_grouped_gemm_fp8(
+        ptr(C), ptr(A), ptr(B), ptr(A_scale), ptr(B_scale), ptr(topk_weights) if mul_routed_weight else None,
+        ptr(sorted_token_ids), ptr(expert_ids), ptr(num_tokens_post_padded), num_pairs, A.shape[0], top_k, E, N, K,
+        block_m, sorted_token_ids.numel(), a_per_token, b_per_channel, int(bool(mul_routed_weight)),
+        dtype_enum(C.dtype), ptr(ws), ws.numel(), stream()))
+
+
+def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tensor, topk_weights: torch.Tensor,
+                  topk_ids: torch.Tensor, inplace: bool = False, activation: str = "silu",
+                  is_act_and_mul: bool = True, apply_router_weight_on_input: bool = False,
+                  use_fp8_w8a8: bool = False, use_int8_w8a8: bool = False, use_int8_w8a16: bool = False,
+                  use_int4_w4a16: bool = False, use_mxfp4_w4a4: bool = False, per_channel_quant: bool = False,
+                  global_num_experts: int = -1, expert_map: Optional[torch.Tensor] = None,
+                  w1_scale: Optional[torch.Tensor] = None, w2_scale: Optional[torch.Tensor] = None,
+                  w1_zp=None, w2_zp=None, a1_scale: Optional[torch.Tensor] = None,
+                  a2_scale: Optional[torch.Tensor] = None, block_shape=None, allow_deep_gemm: bool = False,
+                  allow_cutlass_block_scaled_grouped_gemm: bool = False) -> torch.Tensor:
+    """fused_moe.py:1253-1346 / fused_experts_impl :1349-1563 for use_fp8_w8a8 (Mixtral FP8):
+      quant(hidden) -> align -> GEMM1 [T, k, 2I] -> silu_and_mul -> quant -> GEMM2 (x routed weight) [T, k, H]
+      -> moe_sum.  w1 [E, 2I, H], w2 [E, H, I] fp8 with K contiguous."""
+    if not use_fp8_w8a8 or use_int8_w8a8 or use_int8_w8a16 or use_int4_w4a16 or use_mxfp4_w4a4:
+        raise RuntimeError("fused_experts: only use_fp8_w8a8=True is built in vllm_b200")
+    if activation != "silu" or not is_act_and_mul or apply_router_weight_on_input or block_shape is not None:
+        raise RuntimeError("fused_experts: only silu-and-mul experts with per-tensor / per-channel scales are built")
+    assert hidden_states.size(1) == w1.size(2), f"Hidden size mismatch {hidden_states.size(1)} != {w1.size(2)}"
+    assert topk_weights.size() == topk_ids.size(), "topk shape mismatch"
+    assert hidden_states.is_contiguous(), "Hidden_states must be contiguous"
+    assert w1.stride(-1) == 1 and w2.stride(-1) == 1, "Stride of last dimension must be 1"
+    assert hidden_states.dtype in (torch.float16, torch.bfloat16)
+    assert w1_scale is not None and w2_scale is not None
+    T, H = hidden_states.shape
+    E, N, _ = w1.shape
+    if global_num_experts == -1:
+        global_num_experts = E
+    k = topk_ids.size(1)
+    dev, dt = hidden_states.device, hidden_states.dtype
+    if topk_ids.dtype != torch.int32:
+        topk_ids = topk_ids.to(torch.int32)
+    # activation quant: per-token when per_channel_quant, static when a scale is given, else dynamic per-tensor
+    # (moe_kernel_quantize_input, fused_moe/utils.py)
+    a1q, a1s = ops.scaled_fp8_quant(hidden_states, a1_scale, use_per_token_if_dynamic=per_channel_quant)
+    block_m = get_block_m(T * k, global_num_experts)
+    sorted_ids, expert_ids, num_post = moe_align_block_size(topk_ids, block_m, global_num_experts, expert_map)
+    cache1 = torch.empty((T, k, N), device=dev, dtype=dt)
+    invoke_fused_moe_kernel(a1q, w1, cache1, a1s, w1_scale, None, sorted_ids, expert_ids, num_post, False, k,
+                            block_m, True, per_channel_quant)
+    if per_channel_quant and a2_scale is None:
+        a2q, a2s = ops.silu_and_mul_dynamic_per_token_quant(cache1.view(T * k, N))
+    else:
+        cache2 = torch.empty((T * k, N // 2), device=dev, dtype=dt)
+        ops.silu_and_mul(cache2, cache1.view(T * k, N))
+        a2q, a2s = ops.scaled_fp8_quant(cache2, a2_scale, use_per_token_if_dynamic=per_channel_quant)
+    cache3 = torch.empty((T, k, w2.shape[1]), device=dev, dtype=dt)
+    invoke_fused_moe_kernel(a2q, w2, cache3, a2s, w2_scale, topk_weights.contiguous(), sorted_ids, expert_ids,
+                            num_post, True, 1, block_m, True, per_channel_quant)
+    out = hidden_states if inplace else torch.empty_like(hidden_states)
+    ops.moe_sum(cache3, out)
+    return out
+
+
+def fused_moe(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tensor, gating_output: torch.Tensor,
+              topk: int, renormalize: bool, inplace: bool = False, **kwargs) -> torch.Tensor:
+    """fused_moe.py:1566-1670: routing + experts."""
+    topk_weights, topk_ids, _ = fused_topk(hidden_states, gating_output, topk, renormalize)
+    return fused_experts(hidden_states, w1, w2, topk_weights, topk_ids, inplace=inplace, **kwargs)
+
+
+# ---- dummy-weight helpers for the decode-step driver ---------------------------------------------------
+def make_dummy_experts(E: int, hidden: int, inter: int, device, dtype, quant: str, gen: torch.Generator):
+    """Random fp8 expert weights with per-tensor (per-expert) scales, as Mixtral FP8 checkpoints carry."""
+    if quant != "fp8":
+        raise RuntimeError("the MoE path is built for fp8 w8a8 experts")
+    def mk(n, k):
+        w = torch.empty(E, n, k, device=device, dtype=torch.bfloat16).normal_(0.0, 0.02, generator=gen)
+        amax = w.abs().amax(dim=(1, 2)).float().clamp_(min=1e-8)
+        scale = amax / 448.0
+        return (w.float() / scale.view(E, 1, 1)).clamp_(-448.0, 448.0).to(FP8), scale
+    w13, s13 = mk(2 * inter, hidden)
+    w2, s2 = mk(hidden, inter)
+    return {"w13": w13, "w13_scale": s13, "w2": w2, "w2_scale": s2}
+
+
+def moe_forward(hidden: torch.Tensor, w_gate: torch.Tensor, experts: dict, top_k: int, renormalize: bool = True):
+    """FusedMoE.forward_impl (fused_moe/layer.py:1482-1533) minus the all-reduce (done by the caller):
+    router logits via the library GEMM (replicated, unquantised gate), then fused_moe."""
+    router_logits = torch.matmul(hidden, w_gate.t())
+    return fused_moe(hidden, experts["w13"], experts["w2"], router_logits, top_k, renormalize,
+                     use_fp8_w8a8=True, w1_scale=experts["w13_scale"], w2_scale=experts["w2_scale"])
