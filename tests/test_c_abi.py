@@ -70,3 +70,46 @@ def test_cpu_tensors_are_rejected():
     one = torch.ones(1)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.reshape_and_cache(k, k, kc, vc, torch.zeros(2, dtype=torch.int64), "auto", one, one)
+
+
+def test_torch_shim_registers_reference_schemas():
+    """The TORCH_LIBRARY shim loads without a GPU and registers the ops under the reference's schema strings
+    (csrc/torch_bindings.cpp:45-69, 422-426, 676-691; csrc/moe/torch_bindings.cpp:6-22)."""
+    import torch
+    from vllm_b200 import torch_bindings
+    if not os.path.exists(torch_bindings.SHIM_PATH):
+        pytest.skip("libvllm_b200_torch.so not built")
+    torch_bindings.load_torch_ops()
+    s = str(torch.ops._b200_C.paged_attention_v1.default._schema)
+    assert "!" in s.split("out")[0] and "str kv_cache_dtype" in s and "int blocksparse_head_sliding_step" in s
+    s = str(torch.ops._b200_C.cutlass_scaled_mm.default._schema)
+    assert "out, Tensor a, Tensor b, Tensor a_scales, Tensor b_scales, Tensor? bias) -> ()" in s
+    s = str(torch.ops._b200_C_cache_ops.reshape_and_cache_flash.default._schema)
+    assert s.count("!") == 2 and "key_cache" in s and "Tensor slot_mapping" in s
+    s = str(torch.ops._b200_moe_C.moe_align_block_size.default._schema)
+    assert "int num_experts, int block_size" in s
+    assert torch.ops._b200_C.cutlass_scaled_mm_supports_fp8(100) and not torch.ops._b200_C.cutlass_scaled_mm_supports_fp8(89)
+
+
+def test_glue_mirrors_reference_names():
+    """fused_moe / attention / quantization glue keeps the reference's callables and argument names."""
+    from vllm_b200.attention import B200PagedAttentionBackend, PagedAttention
+    from vllm_b200.fused_moe import fused_experts, fused_topk, moe_align_block_size
+    from vllm_b200.quantization import Fp8LinearOp
+    assert list(inspect.signature(fused_topk).parameters) == ["hidden_states", "gating_output", "topk", "renormalize",
+                                                              "indices_type"]
+    fe = list(inspect.signature(fused_experts).parameters)
+    assert fe[:6] == ["hidden_states", "w1", "w2", "topk_weights", "topk_ids", "inplace"]
+    for name in ("use_fp8_w8a8", "per_channel_quant", "global_num_experts", "expert_map", "w1_scale", "w2_scale",
+                 "a1_scale", "a2_scale"):
+        assert name in fe
+    assert list(inspect.signature(moe_align_block_size).parameters) == ["topk_ids", "block_size", "num_experts",
+                                                                        "expert_map", "pad_sorted_ids"]
+    assert list(inspect.signature(Fp8LinearOp.apply).parameters)[1:] == ["input", "weight", "weight_scale", "out_dtype",
+                                                                         "input_scale", "input_scale_ub", "bias"]
+    assert PagedAttention.get_kv_cache_shape(4, 16, 8, 128) == (2, 4, 16 * 8 * 128)
+    for m in ("get_name", "get_impl_cls", "get_metadata_cls", "get_builder_cls", "get_kv_cache_shape", "swap_blocks",
+              "copy_blocks", "get_supported_head_sizes"):
+        assert hasattr(B200PagedAttentionBackend, m)
+    fwd = list(inspect.signature(B200PagedAttentionBackend.get_impl_cls().forward).parameters)
+    assert fwd == ["self", "layer", "query", "key", "value", "kv_cache", "attn_metadata", "output", "output_scale"]

@@ -62,5 +62,33 @@ def build(verbose=False, jobs=None):
     return so
 
 
+def build_torch_shim(names=("_b200_C", "_b200_C_cache_ops", "_b200_moe_C"), out_name="libvllm_b200_torch.so"):
+    """Compiles vllm_b200/torch_shim.cpp (TORCH_LIBRARY registrations under the reference's schemas, no kernels)
+    against the installed torch and links it to libvllm_b200.so.  `names` are the three library names
+    (pass ("_C", "_C_cache_ops", "_moe_C") for a drop-in build)."""
+    import sysconfig
+    import torch
+    tdir = os.path.dirname(torch.__file__)
+    src = os.path.join(HERE, "torch_shim.cpp")
+    so = os.path.join(LIB, out_name)
+    core = build()
+    if not _stale(so, [src, core, os.path.join(HERE, "..", "include", "vllm_b200.h")]):
+        return so
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cmd = [cxx, "-std=c++17", "-O1", "-fPIC", "-shared", f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "-DUSE_CUDA",
+           f"-DVB200_LIB_C={names[0]}", f"-DVB200_LIB_CACHE={names[1]}", f"-DVB200_LIB_MOE={names[2]}",
+           src, "-o", so, "-isystem", f"{tdir}/include", "-isystem", f"{tdir}/include/torch/csrc/api/include",
+           "-isystem", "/usr/local/cuda/include", "-isystem", sysconfig.get_paths()["include"],
+           f"-L{tdir}/lib", "-lc10", "-ltorch_cpu", "-ltorch", "-ltorch_cuda", "-lc10_cuda", f"-L{LIB}", "-lvllm_b200",
+           "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{tdir}/lib"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"torch shim build failed:\n{r.stdout}\n{r.stderr}")
+    return so
+
+
 if __name__ == "__main__":
     print(build(verbose="-v" in sys.argv))
+    if "--shim" in sys.argv:
+        print(build_torch_shim())
