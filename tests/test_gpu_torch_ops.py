@@ -78,8 +78,9 @@ def test_linear_quant_norm_ops(tops):
     tops._b200_C.cutlass_scaled_mm(o2, q1, w.t(), s1, ws, None)
     assert torch.equal(o1, o2)
     assert tops._b200_C.cutlass_scaled_mm_supports_fp8(100)
+    # (test_schema is skipped for this op: torch's schema checker multiplies its inputs, which fp8 tensors lack)
     torch.library.opcheck(tops._b200_C.cutlass_scaled_mm, (o2, q1, w.t(), s1, ws, None),
-                          test_utils=("test_schema", "test_faketensor"))
+                          test_utils=("test_faketensor",))
     wn = torch.randn(K, device=DEV).bfloat16()
     n1, n2 = torch.empty_like(x), torch.empty_like(x)
     ops.rms_norm(n1, x, wn, 1e-5)

@@ -369,11 +369,12 @@ def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, s
         raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of the output dtype")
     with _device_of(a):
         lib = load()
-        ws = _gemm_workspace(a.device, lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k))
+        ws_bytes = lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k)   # 0: split-K reduces through DSMEM
+        ws = _gemm_workspace(a.device, ws_bytes) if ws_bytes else None
         check(lib.vb200_cutlass_scaled_mm(
             ptr(out), ptr(a), ptr(b), ptr(scale_a), ptr(scale_b), ptr(bias), m, n, k, a.stride(0),
             b.stride(1), out.stride(0), scale_a.numel(), scale_b.numel(), dtype_enum(out.dtype),
-            ptr(ws), ws.numel(), stream()))
+            ptr(ws), ws.numel() if ws is not None else 0, stream()))
 
 
 def cutlass_scaled_mm(a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor, scale_b: torch.Tensor,

@@ -11,9 +11,14 @@
 // Pipeline: warp 0 = TMA producer (128-byte-swizzled [rows x 128 B] boxes of W and A into a ring of
 // stages, mbarrier complete_tx), warp 1 = single-thread tcgen05.mma issuer (4 x K=32 per stage,
 // tcgen05.commit frees the stage), warps 2-5 = epilogue (tcgen05.ld -> a_scale * (b_scale * acc)
-// (+ bias) -> bf16/f16 -> global).  Small-N problems are split along K so the grid covers the SMs:
-// partial tiles go to an fp32 workspace and the last-arriving CTA of a tile (atomic ticket) sums
-// them in split order and runs the epilogue -- one launch, deterministic.
+// (+ bias) -> bf16/f16 -> global).
+// Split-K for small N (the decode projections have 32-48 weight tiles for 148 SMs): the R CTAs that
+// share an output tile form a THREAD-BLOCK CLUSTER (1 x R x 1); each accumulates its K slice in
+// TMEM, then the partial tiles are exchanged through DISTRIBUTED SHARED MEMORY: CTA r owns 1/R of
+// the token columns, every CTA pushes its partial of those columns into r's shared memory
+// (st.shared::cluster, the pipeline stages are free by then), and after a cluster barrier each CTA
+// sums its R slices in rank order (deterministic) and runs the epilogue for its columns.  No
+// global-memory partials, no atomics, one launch.
 #include "tc_common.cuh"
 
 namespace vb200 {
@@ -25,24 +30,24 @@ constexpr int kUmmaK = 32;     // K per tcgen05.mma for 8-bit inputs
 constexpr int kMaxTokTile = 256;
 constexpr int kMaxStages = 8;
 constexpr int kGemmThreads = 192;
-constexpr int kTmemCols = 256;
 constexpr int kWTileBytes = kBlockN * kBlockK;  // 16 KiB
+constexpr int kMaxSplits = 8;                   // portable cluster size
 
 struct GemmParams {
   void* out;              // [M, N] out_t, row stride ldc
   const float* a_scales;  // 1 or M
   const float* b_scales;  // 1 or N
   const void* bias;       // nullptr or [N] out_t
-  float* ws;              // split-K partials: [tile][split][tok_tile][128] fp32
-  int* tickets;           // [tiles] zero between launches
   int M, N, K;
   int64_t ldc;
   int a_per_token, b_per_channel;
-  int tok_tile;   // tokens per CTA tile (multiple of 16, <= 256)
-  int stages;     // pipeline depth
-  int splits;     // K splits
+  int tok_tile;      // tokens per CTA tile (multiple of 16, <= 256)
+  int stages;        // pipeline depth
+  int splits;        // K splits == cluster size along y
   int kb_per_split;  // k-blocks per split
-  int num_kb;     // total k-blocks
+  int num_kb;        // total k-blocks
+  int col_chunk;     // split-K: token columns owned by one CTA of the cluster (multiple of 16)
+  int tmem_cols;     // TMEM columns to allocate (power of two >= tok_tile, >= 32)
 };
 
 template <typename OutT>
@@ -50,22 +55,25 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_w,
                      const __grid_constant__ CUtensorMap tmap_a, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: [stages][W tile 16 KiB | A tile tok_tile*128] | barriers | tmem ptr | a_scale[256]
+  // carve: [stages][W tile 16 KiB | A tile tok_tile*128]  (re-used as the split-K receive buffer)
+  //        | barriers | tmem ptr | a_scale[256]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   const int a_tile_bytes = p.tok_tile * kBlockK;
   const int stage_bytes = kWTileBytes + a_tile_bytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+  size_t main_bytes = (size_t)p.stages * stage_bytes;
+  const size_t recv_bytes = p.splits > 1 ? (size_t)p.splits * p.col_chunk * kBlockN * 4 : 0;
+  if (recv_bytes > main_bytes) main_bytes = (recv_bytes + 1023) & ~(size_t)1023;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + main_bytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* acc_bar = empty_bar + kMaxStages;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_bar + 1);
-  int* last_flag = reinterpret_cast<int*>(tmem_ptr + 1);
   float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int n_tile = blockIdx.x;
-  const int split = blockIdx.y;
+  const int split = blockIdx.y;  // == rank in the (1, splits, 1) cluster
   const int m_tile = blockIdx.z;
   const int n0 = n_tile * kBlockN;
   const int tok0 = m_tile * p.tok_tile;
@@ -83,7 +91,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     mbar_init(acc_bar, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
+  if (warp == 1) tmem_alloc(tmem_ptr, (uint32_t)p.tmem_cols);
   if (warp >= 2) {
     // per-token scales of this tile -> smem (scalar scale broadcast)
     for (int i = threadIdx.x - 64; i < p.tok_tile; i += 128) {
@@ -114,6 +122,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
         }
       }
     }
+    __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
@@ -140,69 +149,83 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       }
       umma_commit(acc_bar);  // accumulator complete
     }
-  } else {
-    // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-    const int q = warp & 3;
-    const int n = n0 + q * 32 + lane;  // weight row / output column of this thread
-    const bool n_ok = n < p.N;
-    mbar_wait(acc_bar, 0);
-    tc_fence_after();
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const int ep_tid = threadIdx.x - 64;  // 0..127
-    bool do_epilogue = true;
-    const int tile_id = m_tile * gridDim.x + n_tile;
-    float* ws_tile = p.ws + (size_t)tile_id * p.splits * p.tok_tile * kBlockN;
-    if (p.splits > 1) {
-      // publish this split's partial tile: ws[tile][split][token][128 n]
-      float* dst = ws_tile + (size_t)split * p.tok_tile * kBlockN + q * 32 + lane;
+    __syncwarp();
+  }
+
+  // epilogue warps 2..5: TMEM lane quarter = warp % 4
+  const int q = warp & 3;
+  const int nl = q * 32 + lane;  // weight row inside the tile
+  const int n = n0 + nl;         // output column of this thread
+  const bool n_ok = n < p.N;
+  const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+  OutT* outp = reinterpret_cast<OutT*>(p.out);
+
+  if (p.splits == 1) {
+    if (warp >= 2) {
+      const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[n] : 0.f) : p.b_scales[0];
+      float biasf = 0.f;
+      if (p.bias != nullptr && n_ok) biasf = to_float<OutT>(reinterpret_cast<const OutT*>(p.bias)[n]);
+      mbar_wait(acc_bar, 0);
+      tc_fence_after();
       for (int c = 0; c < p.tok_tile; c += 16) {
         uint32_t r[16];
         tmem_ld_x16(taddr + c, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) __stcg(dst + (size_t)(c + j) * kBlockN, __uint_as_float(r[j]));
-      }
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (ep_tid == 0) {
-        const int t = atomicAdd(&p.tickets[tile_id], 1);
-        const int last = (t == p.splits - 1);
-        if (last) p.tickets[tile_id] = 0;  // ready for the next launch
-        *last_flag = last;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      do_epilogue = (*last_flag != 0);
-      if (do_epilogue) __threadfence();
-    }
-    if (do_epilogue) {
-      const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[n] : 0.f) : p.b_scales[0];
-      float biasf = 0.f;
-      if (p.bias != nullptr && n_ok) biasf = to_float<OutT>(reinterpret_cast<const OutT*>(p.bias)[n]);
-      OutT* outp = reinterpret_cast<OutT*>(p.out);
-      for (int c = 0; c < p.tok_tile; c += 16) {
-        float acc[16];
-        if (p.splits > 1) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-          for (int s = 0; s < p.splits; ++s) {
-            const float* src = ws_tile + (size_t)s * p.tok_tile * kBlockN + q * 32 + lane;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) acc[j] += __ldcg(src + (size_t)(c + j) * kBlockN);
-          }
-        } else {
-          uint32_t r[16];
-          tmem_ld_x16(taddr + c, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(r[j]);
-        }
-#pragma unroll
         for (int j = 0; j < 16; ++j) {
           const int t = tok0 + c + j;
           if (n_ok && t < p.M) {
             // a_scale * (b_scale * acc) [+ bias]  (ScaledEpilogue / ScaledEpilogueBias)
-            const float v = p.bias != nullptr ? fmaf(s_ascale[c + j], bsc * acc[j], biasf)
-                                              : s_ascale[c + j] * (bsc * acc[j]);
+            const float acc = __uint_as_float(r[j]);
+            const float v = p.bias != nullptr ? fmaf(s_ascale[c + j], bsc * acc, biasf)
+                                              : s_ascale[c + j] * (bsc * acc);
+            outp[(int64_t)t * p.ldc + n] = from_float<OutT>(v);
+          }
+        }
+      }
+    }
+  } else {
+    // ===== cluster split-K: exchange partial tiles through distributed shared memory =====
+    const int cw = p.col_chunk;
+    if (warp >= 2) {
+      mbar_wait(acc_bar, 0);  // this CTA's MMAs are done: its stages are free, its TMEM is final
+      tc_fence_after();
+    }
+    cluster_sync_all();  // every CTA of the cluster is past its main loop
+    if (warp >= 2) {
+      const uint32_t recv_local = smem_u32(smem);
+      for (int owner = 0; owner < p.splits; ++owner) {
+        const int c_begin = owner * cw;
+        const int c_end = min(c_begin + cw, p.tok_tile);
+        if (c_begin >= c_end) break;
+        const uint32_t remote = map_to_cta(recv_local, (uint32_t)owner) +
+                                (uint32_t)(((split * cw) * kBlockN + nl) * 4);
+        for (int c = c_begin; c < c_end; c += 16) {
+          uint32_t r[16];
+          tmem_ld_x16(taddr + c, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            st_cluster_f32(remote + (uint32_t)((c - c_begin + j) * kBlockN * 4), __uint_as_float(r[j]));
+        }
+      }
+    }
+    cluster_sync_all();  // all partials have landed (release/acquire at cluster scope)
+    if (warp >= 2) {
+      const int c_begin = split * cw;
+      const int c_end = min(c_begin + cw, p.tok_tile);
+      if (c_begin < c_end) {
+        const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[n] : 0.f) : p.b_scales[0];
+        float biasf = 0.f;
+        if (p.bias != nullptr && n_ok) biasf = to_float<OutT>(reinterpret_cast<const OutT*>(p.bias)[n]);
+        const float* recv = reinterpret_cast<const float*>(smem);
+        for (int c = c_begin; c < c_end; ++c) {
+          float acc = 0.f;
+          for (int r = 0; r < p.splits; ++r) acc += recv[((r * cw) + (c - c_begin)) * kBlockN + nl];
+          const int t = tok0 + c;
+          if (n_ok && t < p.M) {
+            const float v = p.bias != nullptr ? fmaf(s_ascale[c], bsc * acc, biasf)
+                                              : s_ascale[c] * (bsc * acc);
             outp[(int64_t)t * p.ldc + n] = from_float<OutT>(v);
           }
         }
@@ -213,15 +236,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
   }
 }
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 struct GemmPlan {
-  int tok_tile, m_tiles, n_tiles, stages, splits, kb_per_split, num_kb;
-  size_t smem, ws_bytes, ticket_bytes;
+  int tok_tile, m_tiles, n_tiles, stages, splits, kb_per_split, num_kb, col_chunk, tmem_cols;
+  size_t smem;
 };
 
 static GemmPlan plan_gemm(int M, int N, int K) {
@@ -234,25 +257,44 @@ static GemmPlan plan_gemm(int M, int N, int K) {
   const int budget = 227 * 1024 - 1024 /*align*/ - 2048 /*barriers + scales*/;
   g.stages = budget / stage_bytes;
   if (g.stages > kMaxStages) g.stages = kMaxStages;
-  // split K until the grid covers the SMs (each split keeps >= 8 k-blocks to amortise the ramp)
+  // cluster split-K: the largest R <= 8 whose grid still fits one wave, keeping >= 4 k-blocks per split
   const int tiles = g.n_tiles * g.m_tiles;
-  int splits = 1;
   const int sms = num_sms();
-  while (tiles * splits * 2 <= sms + sms / 4 && g.num_kb / (splits * 2) >= 8 && splits < 16) splits *= 2;
-  if (tiles * splits < sms && g.num_kb / (splits + 1) >= 8) {
-    // finer choice: the split count that gets closest to one full wave
-    int best = splits;
-    for (int s = splits; s <= 16 && g.num_kb / s >= 8; ++s)
-      if (tiles * s <= sms) best = s;
-    splits = best;
-  }
+  int splits = 1;
+  for (int r = 2; r <= kMaxSplits; ++r)
+    if (tiles * r <= sms && g.num_kb / r >= 4) splits = r;
   g.kb_per_split = ceil_div(g.num_kb, splits);
   g.splits = ceil_div(g.num_kb, g.kb_per_split);
   if (g.stages > g.kb_per_split) g.stages = g.kb_per_split < 2 ? 2 : g.kb_per_split;
-  g.smem = 1024 + (size_t)g.stages * stage_bytes + 2048;
-  g.ws_bytes = g.splits > 1 ? (size_t)tiles * g.splits * g.tok_tile * kBlockN * sizeof(float) : 0;
-  g.ticket_bytes = (size_t)tiles * sizeof(int);
+  g.col_chunk = (ceil_div(g.tok_tile, g.splits) + 15) / 16 * 16;
+  size_t main_bytes = (size_t)g.stages * stage_bytes;
+  const size_t recv = g.splits > 1 ? (size_t)g.splits * g.col_chunk * kBlockN * 4 : 0;
+  if (recv > main_bytes) main_bytes = (recv + 1023) & ~(size_t)1023;
+  g.smem = 1024 + main_bytes + 2048;
+  g.tmem_cols = 32;
+  while (g.tmem_cols < g.tok_tile) g.tmem_cols <<= 1;
   return g;
+}
+
+template <typename OutT>
+static int launch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& ta,
+                       const GemmParams& p, cudaStream_t stream) {
+  auto kern = scaled_mm_kernel<OutT>;
+  VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(g.n_tiles, g.splits, g.m_tiles);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = g.smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = g.splits;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  VB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tw, ta, p));
+  return 0;
 }
 
 }  // namespace vb200
@@ -261,14 +303,11 @@ using namespace vb200;
 
 extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
 
-// workspace layout: [tickets: 4 KiB-aligned int32 region, must be ZERO on first use and is left
-// zero by every launch][fp32 split-K partials].
-static constexpr size_t kTicketRegion = 16384;  // up to 4096 tiles
-
+// Earlier versions kept split-K tickets and partials in a caller workspace; the cluster/DSMEM reduction needs
+// none.  The query stays in the ABI (callers may pass NULL / 0).
 extern "C" size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K) {
-  if (M <= 0 || N <= 0 || K <= 0) return kTicketRegion;
-  const GemmPlan g = plan_gemm(M, N, K);
-  return kTicketRegion + g.ws_bytes;
+  (void)M; (void)N; (void)K;
+  return 0;
 }
 
 extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
@@ -278,6 +317,8 @@ extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
                                        int b_scales_numel, int out_dtype, void* workspace,
                                        size_t workspace_bytes, vb200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  (void)workspace;
+  (void)workspace_bytes;
   VB_CHECK(out_dtype == VB200_BF16 || out_dtype == VB200_F16,
            "cutlass_scaled_mm: out dtype must be bf16 or f16");
   VB_CHECK(K % 16 == 0 && N % 16 == 0, "cutlass_scaled_mm: K (%d) and N (%d) must be multiples of 16",
@@ -287,13 +328,7 @@ extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
   if (M <= 0 || N <= 0) return 0;
   VB_CHECK(K > 0, "cutlass_scaled_mm: K must be positive");
   GemmPlan g = plan_gemm(M, N, K);
-  VB_CHECK((size_t)g.n_tiles * g.m_tiles * sizeof(int) <= kTicketRegion,
-           "cutlass_scaled_mm: too many tiles for the ticket region");
-  if (g.splits > 1) {
-    VB_CHECK(workspace != nullptr && workspace_bytes >= kTicketRegion + g.ws_bytes,
-             "cutlass_scaled_mm: workspace too small (%zu < %zu)", workspace_bytes,
-             kTicketRegion + g.ws_bytes);
-  }
+  VB_CHECK(g.m_tiles <= 65535, "cutlass_scaled_mm: M too large");
   CUtensorMap tw, ta;
   if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kBlockN)) return 1;
   if (tc::make_tmap_2d_u8(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, (uint32_t)g.tok_tile))
@@ -303,9 +338,6 @@ extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
   p.a_scales = a_scales;
   p.b_scales = b_scales;
   p.bias = bias;
-  p.tickets = reinterpret_cast<int*>(workspace);
-  p.ws = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kTicketRegion)
-                   : nullptr;
   p.M = M;
   p.N = N;
   p.K = K;
@@ -317,16 +349,8 @@ extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
   p.splits = g.splits;
   p.kb_per_split = g.kb_per_split;
   p.num_kb = g.num_kb;
-  dim3 grid(g.n_tiles, g.splits, g.m_tiles);
-  if (out_dtype == VB200_BF16) {
-    auto kern = scaled_mm_kernel<__nv_bfloat16>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kGemmThreads, g.smem, stream>>>(tw, ta, p);
-  } else {
-    auto kern = scaled_mm_kernel<__half>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kGemmThreads, g.smem, stream>>>(tw, ta, p);
-  }
-  VB_LAUNCH_CHECK();
-  return 0;
+  p.col_chunk = g.col_chunk;
+  p.tmem_cols = g.tmem_cols;
+  if (out_dtype == VB200_BF16) return launch_gemm<__nv_bfloat16>(g, tw, ta, p, stream);
+  return launch_gemm<__half>(g, tw, ta, p, stream);
 }

@@ -144,6 +144,28 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---- thread-block clusters / distributed shared memory ---------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// full cluster barrier (all threads of all CTAs), release/acquire: orders DSMEM stores before later loads
+__device__ __forceinline__ void cluster_sync_all() {
+  __syncwarp();
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address -> shared::cluster address of the same offset in CTA `rank`
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
 // ---- host: tensor maps ----------------------------------------------------------------------------
 // 2-D row-major byte matrix [rows, cols] with row pitch `ld` bytes; box = {128 bytes, box_rows};
 // 128-byte swizzle; out-of-bounds elements read as zero.  Returns 0 on success.

@@ -71,6 +71,40 @@ def make_cos_sin_cache(rot_dim: int, max_position: int, base: float, dtype, devi
     return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype)
 
 
+def tp_shard(cfg: DecoderConfig, tp: int, rank: int):
+    """Tensor-parallel partition of one decoder layer (reference: QKVParallelLinear / MergedColumnParallelLinear /
+    RowParallelLinear, vllm/model_executor/layers/linear.py): rank r owns q heads [r*H/tp, (r+1)*H/tp), the kv heads
+    of those q heads (replicated when tp > num_kv_heads), and intermediate columns [r*I/tp, (r+1)*I/tp).
+    Returns dict of index ranges into the UNSHARDED weights."""
+    assert cfg.num_heads % tp == 0 and cfg.intermediate_size % tp == 0
+    nh = cfg.num_heads // tp
+    if tp <= cfg.num_kv_heads:
+        assert cfg.num_kv_heads % tp == 0
+        nkv = cfg.num_kv_heads // tp
+        kv0 = rank * nkv
+    else:
+        assert tp % cfg.num_kv_heads == 0
+        nkv = 1
+        kv0 = rank // (tp // cfg.num_kv_heads)
+    inter = cfg.intermediate_size // tp
+    return {"q_heads": (rank * nh, (rank + 1) * nh), "kv_heads": (kv0, kv0 + nkv),
+            "inter": (rank * inter, (rank + 1) * inter), "num_heads": nh, "num_kv_heads": nkv, "inter_size": inter}
+
+
+def merge_vocab_parallel_argmax(val: torch.Tensor, idx: torch.Tensor, tp: int, group=None) -> torch.Tensor:
+    """Global arg-max from per-rank (max value, global index) pairs of a vocab-parallel lm_head: all-gather the
+    pairs, take the rank with the largest value (lowest rank wins ties, i.e. the lowest token id)."""
+    if tp == 1:
+        return idx
+    import torch.distributed as dist
+    vals = [torch.empty_like(val) for _ in range(tp)]
+    idxs = [torch.empty_like(idx) for _ in range(tp)]
+    dist.all_gather(vals, val, group=group)
+    dist.all_gather(idxs, idx, group=group)
+    best = torch.stack(vals).argmax(dim=0, keepdim=True)
+    return torch.stack(idxs).gather(0, best).squeeze(0)
+
+
 class _KVScales:
     """What an `Attention` layer object supplies to AttentionImpl.forward (abstract.py:240-247)."""
 
@@ -84,10 +118,10 @@ class DecoderLayer:
                  gen: torch.Generator):
         self.cfg, self.tp, self.quant, self.dtype = cfg, tp, quant, dtype
         H, D = cfg.hidden_size, cfg.head_dim
-        self.nh = cfg.num_heads // tp
-        self.nkv = max(cfg.num_kv_heads // tp, 1)   # kv heads are replicated when tp > num_kv_heads
+        shard = tp_shard(cfg, tp, get_tensor_model_parallel_rank())
+        self.nh, self.nkv = shard["num_heads"], shard["num_kv_heads"]   # kv heads replicated when tp > num_kv_heads
         self.q_size, self.kv_size = self.nh * D, self.nkv * D
-        self.inter = cfg.intermediate_size // tp
+        self.inter = shard["inter_size"]
         self.input_ln = torch.ones(H, device=device, dtype=dtype)
         self.post_ln = torch.ones(H, device=device, dtype=dtype)
         mk = (lambda n, k: _dummy_fp8_weight(n, k, device, gen)) if quant == "fp8" else (
@@ -225,12 +259,4 @@ class Decoder:
         logits = self.forward(input_ids, positions, meta).float()
         val, idx = logits.max(dim=-1)
         idx = idx + self.tp_rank * self.vocab_shard
-        if self.tp == 1:
-            return idx
-        import torch.distributed as dist
-        vals = [torch.empty_like(val) for _ in range(self.tp)]
-        idxs = [torch.empty_like(idx) for _ in range(self.tp)]
-        dist.all_gather(vals, val)
-        dist.all_gather(idxs, idx)
-        best = torch.stack(vals).argmax(dim=0, keepdim=True)
-        return torch.stack(idxs).gather(0, best).squeeze(0)
+        return merge_vocab_parallel_argmax(val, idx, self.tp)

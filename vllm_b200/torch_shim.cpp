@@ -160,11 +160,18 @@ void cutlass_scaled_mm(Tensor& out, const Tensor& a, const Tensor& b, const Tens
   if (bias) TORCH_CHECK(bias->numel() == b.size(1) && bias->is_contiguous() && bias->dim() == 1);
   const at::cuda::OptionalCUDAGuard guard(device_of(a));
   const int M = a.size(0), N = b.size(1), K = a.size(1);
-  at::Tensor& ws = gemm_workspace(a, vb200_cutlass_scaled_mm_workspace_size(M, N, K));
+  const size_t ws_bytes = vb200_cutlass_scaled_mm_workspace_size(M, N, K);  // 0: split-K reduces through DSMEM
+  void* ws_ptr = nullptr;
+  size_t ws_len = 0;
+  if (ws_bytes) {
+    at::Tensor& ws = gemm_workspace(a, ws_bytes);
+    ws_ptr = ws.data_ptr();
+    ws_len = ws.numel();
+  }
   vb_check(vb200_cutlass_scaled_mm(out.data_ptr(), a.const_data_ptr(), b.const_data_ptr(),
                                    a_scales.const_data_ptr<float>(), b_scales.const_data_ptr<float>(), optptr(bias), M,
                                    N, K, a.stride(0), b.stride(1), out.stride(0), a_scales.numel(), b_scales.numel(),
-                                   dt(out), ws.data_ptr(), ws.numel(), stream_of(a)));
+                                   dt(out), ws_ptr, ws_len, stream_of(a)));
 }
 
 bool cutlass_scaled_mm_supports_fp8(int64_t cuda_device_capability) {
