@@ -78,6 +78,53 @@ def test_scaled_mm_full_size_linearity():
     assert torch.equal(o1, ops.cutlass_scaled_mm(a, b, sa, sb, torch.bfloat16))
 
 
+def _gpu_reference(a, b, sa, sb):
+    """fp32 torch matmul of the exactly dequantised operands on the GPU (sizes the CPU oracle cannot finish)."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        return sa * (sb * (a.float() @ b.float()))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+@pytest.mark.parametrize("M,N,K", [(2048, 16384, 512), (1000, 6144 + 16, 1024 + 16), (300, 28672, 256)])
+def test_scaled_mm_persistent_many_tiles(M, N, K):
+    """More tiles than CTA pairs: every pair walks several tiles, both TMEM accumulator stages and the
+    shared-memory ring wrap their mbarrier phases several times; ragged M / N / K tails included."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(M + K)
+    a = to_fp8(torch.randn(M, K, device=DEV))
+    b = to_fp8(torch.randn(N, K, device=DEV)).t()
+    sa = torch.rand(M, 1, device=DEV) * 0.1 + 0.01
+    sb = torch.rand(1, N, device=DEV) * 0.1 + 0.01
+    got = ops.cutlass_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    want = _gpu_reference(a, b, sa, sb)
+    torch.testing.assert_close(got.float(), want, rtol=1e-2, atol=2e-2 * max(1.0, float(want.abs().mean())))
+
+
+@pytest.mark.parametrize("M", [16, 100, 256])
+@pytest.mark.parametrize("N,K", [(4096, 4096), (6144, 4096), (4096, 14336), (512, 8192)])
+def test_scaled_mm_split_k_repeated(M, N, K):
+    """Decode shapes that take the split-K path: repeated launches re-arm the arrival counters, results are
+    bit-identical run to run and match the fp32 reference."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(N + M)
+    a = to_fp8(torch.randn(M, K, device=DEV))
+    b = to_fp8(torch.randn(N, K, device=DEV)).t()
+    sa = torch.rand(M, 1, device=DEV) * 0.1 + 0.01
+    sb = torch.rand(1, N, device=DEV) * 0.1 + 0.01
+    want = _gpu_reference(a, b, sa, sb)
+    first = None
+    for _ in range(5):
+        got = ops.cutlass_scaled_mm(a, b, sa, sb, torch.bfloat16)
+        if first is None:
+            first = got
+            torch.testing.assert_close(got.float(), want, rtol=1e-2, atol=2e-2 * max(1.0, float(want.abs().mean())))
+        else:
+            assert torch.equal(first, got)
+
+
 def test_scaled_mm_rejects_bad_inputs():
     from vllm_b200 import _custom_ops as ops
     a = torch.zeros(4, 64, device=DEV).to(FP8)
