@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
   uint64_t* acc_bar = empty_bar + kMoeMaxStages;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_bar + 1);
   int* s_nvalid = reinterpret_cast<int*>(tmem_ptr + 1);
-  int* s_tok = reinterpret_cast<int*>(tmem_ptr + 4);          // [block_m] token ids of this block
+  int* s_tok = reinterpret_cast<int*>(tmem_ptr + 6);          // [block_m] token ids of this block (16-byte aligned)
   float* s_rowscale = reinterpret_cast<float*>(s_tok + kMoeMaxBlockM);  // [block_m] routed_w, a_scale
 
   const int warp = threadIdx.x >> 5;
@@ -195,21 +195,51 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     OutT* outp = reinterpret_cast<OutT*>(p.c);
+    // token ids and the two per-row factors are read with explicit ld.shared, 16 columns at a time, BEFORE the
+    // stores of those columns: a generic load would be ordered behind every earlier global store and serialise
+    // the loop on the shared-memory latency
+    const uint32_t tok_u32 = smem_u32(s_tok), rs_u32 = smem_u32(s_rowscale);
     for (int c = 0; c < umma_n; c += 16) {
       uint32_t r[16];
       tmem_ld_x16(taddr + c, r);
+      int tk[16];
+      float rw[16], as_[16];
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        uint32_t t0_, t1_, t2_, t3_;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(t0_), "=r"(t1_), "=r"(t2_), "=r"(t3_)
+                     : "r"(tok_u32 + 4 * (c + 4 * q4)));
+        tk[4 * q4] = (int)t0_;
+        tk[4 * q4 + 1] = (int)t1_;
+        tk[4 * q4 + 2] = (int)t2_;
+        tk[4 * q4 + 3] = (int)t3_;
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "r"(rs_u32 + 4 * (c + 4 * q4)));
+        rw[4 * q4] = v.x;
+        rw[4 * q4 + 1] = v.y;
+        rw[4 * q4 + 2] = v.z;
+        rw[4 * q4 + 3] = v.w;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "r"(rs_u32 + 4 * (kMoeMaxBlockM + c + 4 * q4)));
+        as_[4 * q4] = v.x;
+        as_[4 * q4 + 1] = v.y;
+        as_[4 * q4 + 2] = v.z;
+        as_[4 * q4 + 3] = v.w;
+      }
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const int i = c + j;
-        if (i < nvalid && n_ok) {
-          const int tok = s_tok[i];
-          if (tok >= 0 && tok < p.num_valid_tokens) {
-            float v = __uint_as_float(r[j]);
-            if (mul_w) v = v * s_rowscale[i];
-            v = (v * s_rowscale[kMoeMaxBlockM + i]) * bsc;
-            outp[(int64_t)tok * p.N + n] = from_float<OutT>(v);
-          }
+        const int tok = tk[j];
+        if (i < nvalid && n_ok && tok >= 0 && tok < p.num_valid_tokens) {
+          float v = __uint_as_float(r[j]);
+          if (mul_w) v = v * rw[j];
+          v = (v * as_[j]) * bsc;
+          outp[(int64_t)tok * p.N + n] = from_float<OutT>(v);
         }
       }
     }

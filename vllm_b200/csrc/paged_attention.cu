@@ -18,6 +18,8 @@
 //  * online softmax in the exp2 domain, per-warp (m, l, O) merged through shared memory, then
 //    either the final output or the v2 partials (normalised tmp_out, exp_sums, max_logits) with
 //    the reference's +1e-6 normalisers (attention_kernels.cuh:337,647).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace vb200 {
@@ -40,6 +42,7 @@ struct PagedAttnParams {
   int max_num_partitions;  // 1 => write `out` directly
   int64_t q_stride, kv_block_stride, kv_head_stride;
   float scale;
+  int prefetch_dist;  // tiles (per warp) ahead of the register double buffer that are pulled into L2; 0 = off
 };
 
 template <typename T>
@@ -236,6 +239,36 @@ __global__ void __launch_bounds__(NWARPS * 32, (HEAD_SIZE <= 128 ? (FP8 ? 3 : 2)
     }
   };
 
+  // L2 prefetch of a whole 16-token tile (K rows and V rows of this kv head): the tile's bytes are
+  // HEAD_SIZE * 16 * CE of K (contiguous in one cache block when BLOCK_SIZE == 16, else strided
+  // runs) + the same of V; one 128-byte line per lane and per round.  It raises the bytes in flight
+  // per SM beyond what the register double buffer holds, at no register cost.
+  auto prefetch_tile = [&](int tile) {
+    const int T0 = tile << 4;
+    if (T0 >= ntok) return;
+    const int64_t pb = sm_bt[T0 / BLOCK_SIZE];
+    const int tin = T0 % BLOCK_SIZE;
+    constexpr int kRowBytes = BLOCK_SIZE * 16;              // one K run-row [BLOCK_SIZE][x] in bytes
+    constexpr int kKLines = (NCHUNK * 16 * 16 + 127) / 128;  // 128-byte lines of K in a 16-token tile
+    constexpr int kVLines = (HEAD_SIZE * 16 * CE + 127) / 128;
+    const unsigned char* kb_ = kbase + pb * blk_stride_b;
+    const unsigned char* vb_ = vbase + pb * blk_stride_b;
+    for (int l = lane; l < kKLines + kVLines; l += 32) {
+      const unsigned char* a;
+      if (l < kKLines) {
+        // line l covers bytes [128 l, 128 l + 128) of the tile's K, laid out chunk-major: 256 bytes per chunk
+        const int chunk = (l * 128) / 256, within = (l * 128) % 256;
+        a = kb_ + chunk * kRowBytes + tin * 16 + within;
+      } else {
+        const int lv = l - kKLines;
+        // V rows are [d][BLOCK_SIZE] elements: 16 tokens of row d = 16 * CE bytes
+        const int d = (lv * 128) / (16 * CE), within = (lv * 128) % (16 * CE);
+        a = vb_ + (d * BLOCK_SIZE + tin) * CE + within;
+      }
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+    }
+  };
+
   float o[NJ][4];
 #pragma unroll
   for (int j = 0; j < NJ; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
@@ -334,13 +367,19 @@ __global__ void __launch_bounds__(NWARPS * 32, (HEAD_SIZE <= 128 ? (FP8 ? 3 : 2)
   {
     Tile ta, tb;
     int tile = warp;
+    const int pf = p.prefetch_dist * NWARPS;
+    if (pf > 0) {
+      for (int t = tile + NWARPS; t < tile + pf && t < ntiles; t += NWARPS) prefetch_tile(t);
+    }
     if (tile < ntiles) load_tile(ta, tile);
     while (tile < ntiles) {
       const int n1 = tile + NWARPS;
+      if (pf > 0 && tile + pf < ntiles) prefetch_tile(tile + pf);
       if (n1 < ntiles) load_tile(tb, n1);
       compute_tile(ta, tile);
       if (n1 >= ntiles) break;
       const int n2 = n1 + NWARPS;
+      if (pf > 0 && n1 + pf < ntiles) prefetch_tile(n1 + pf);
       if (n2 < ntiles) load_tile(ta, n2);
       compute_tile(tb, n1);
       tile = n2;
@@ -457,12 +496,68 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
   }
 }
 
+}  // namespace vb200
+#include "paged_attention_tma.cuh"
+namespace vb200 {
+
 constexpr int kWarps = 4;
 static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+// bulk-copy load path (block size 16, head size % 16 == 0) unless VB200_PA_TMA=0
+static bool pa_use_tma() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("VB200_PA_TMA");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+// resident CTAs per SM the bulk-copy kernel is compiled for: bandwidth no longer depends on the warp count, so
+// more (smaller) CTAs only make the waves finer; 96 registers/thread allow 4 CTAs of 160 threads up to head 128
+static inline int pa_tma_ctas_per_sm(int head_size) { return head_size <= 128 ? 4 : 2; }
+// ring depth: fill the shared memory of an SM shared by `ctas` CTAs.  MUST be a multiple of the consumer warp
+// count: then a stage is always consumed by the same warp, whose program order guarantees it never waits on a
+// full barrier that is still one phase behind (parity aliasing).
+template <int HEAD_SIZE>
+static inline int pa_tma_stages(int cache_elem_bytes, int partition_tokens) {
+  const int stage = 2 * HEAD_SIZE * 16 * cache_elem_bytes;
+  const int fixed = 2 * kPaMaxStages * 8 + ((partition_tokens + 15) / 16) * 4 + 1024 /* per-CTA reservation */ + 128;
+  int budget = (227 * 1024) / pa_tma_ctas_per_sm(HEAD_SIZE) - fixed;
+  int st = budget / stage;
+  const char* e = getenv("VB200_PA_STAGES");
+  if (e && atoi(e) > 0) st = atoi(e);
+  if (st > kPaMaxStages) st = kPaMaxStages;
+  st = st / kWarps * kWarps;
+  if (st < kWarps) st = kWarps;
+  return st;
+}
 
 template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE>
 static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
                      cudaStream_t stream) {
+  const int q_per_kv_ = p.num_heads / p.num_kv_heads;
+  if (BLOCK_SIZE == 16 && HEAD_SIZE % 16 == 0 && pa_use_tma()) {
+    constexpr int HS = HEAD_SIZE % 16 == 0 ? HEAD_SIZE : 128;  // (only instantiated for multiples of 16)
+    auto kt = paged_attention_tma_kernel<QT, FP8, HS, kWarps, (HS <= 128 ? 4 : 2)>;
+    const int ce = FP8 ? 1 : 2;
+    const int stages = pa_tma_stages<HS>(ce, p.partition_size);
+    const size_t smem_t = pa_tma_smem_bytes<HS, kWarps>(stages, ce, p.partition_size);
+    VB_CHECK(smem_t <= 227 * 1024, "paged attention: partition of %d tokens needs too much shared memory",
+             p.partition_size);
+    if (smem_t > 48 * 1024)
+      VB_CUDA_CHECK(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
+    dim3 grid_t(p.num_kv_heads * ((q_per_kv_ + 7) / 8), num_seqs, num_partitions);
+    kt<<<grid_t, (kWarps + 1) * 32, smem_t, stream>>>(p, stages);
+    VB_LAUNCH_CHECK();
+    if (p.max_num_partitions > 1) {
+      const int rows = num_seqs * p.num_heads;
+      paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
+          (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
+          p.max_num_partitions, p.partition_size, rows);
+      VB_LAUNCH_CHECK();
+    }
+    return 0;
+  }
   auto kern = paged_attention_kernel<QT, FP8, HEAD_SIZE, BLOCK_SIZE, kWarps>;
   const int nblk = (p.partition_size + BLOCK_SIZE - 1) / BLOCK_SIZE;
   const size_t smem = (size_t)kWarps * 8 * HEAD_SIZE * 4 + 2 * kWarps * 8 * 4 + (size_t)nblk * 4;
@@ -545,6 +640,18 @@ static int run_paged_attention(PagedAttnParams& p, int num_seqs, int head_size, 
 
 using namespace vb200;
 
+// tuning knob (tiles per warp prefetched into L2 ahead of the register pipeline); VB200_PA_PREFETCH overrides
+static int pa_prefetch_dist() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("VB200_PA_PREFETCH");
+    v = e ? atoi(e) : 0;
+    if (v < 0) v = 0;
+    if (v > 64) v = 64;
+  }
+  return v;
+}
+
 extern "C" int vb200_paged_attention_v2(
     void* out, float* exp_sums, float* max_logits, void* tmp_out, const void* query,
     const void* key_cache, const void* value_cache, int num_seqs, int num_heads, int head_size,
@@ -576,6 +683,7 @@ extern "C" int vb200_paged_attention_v2(
   p.kv_block_stride = kv_block_stride;
   p.kv_head_stride = kv_head_stride;
   p.scale = scale;
+  p.prefetch_dist = pa_prefetch_dist();
   // With a single partition the kernel writes `out` directly (the reference's reduce kernel
   // would copy tmp_out -> out; same result), and leaves the partial buffers untouched.
   return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
@@ -598,7 +706,8 @@ extern "C" int vb200_paged_attention_v1_partition_size(int num_seqs, int num_hea
   const int q_per_kv = num_heads / num_kv_heads;
   const int groups = (q_per_kv + 7) / 8;
   const long base_ctas = (long)num_seqs * num_kv_heads * groups;
-  const long resident = (long)num_sms() * pa_ctas_per_sm(head_size, kv_dtype);
+  const bool tma = block_size == 16 && head_size % 16 == 0 && pa_use_tma();
+  const long resident = (long)num_sms() * (tma ? pa_tma_ctas_per_sm(head_size) : pa_ctas_per_sm(head_size, kv_dtype));
   const int align = block_size > 32 ? block_size : 32;
   const int len = max_seq_len > 0 ? max_seq_len : 16;
   const long kOverheadTokens = 256;
@@ -680,6 +789,7 @@ extern "C" int vb200_paged_attention_v1(
   p.kv_block_stride = kv_block_stride;
   p.kv_head_stride = kv_head_stride;
   p.scale = scale;
+  p.prefetch_dist = pa_prefetch_dist();
   return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
                              (cudaStream_t)stream);
 }

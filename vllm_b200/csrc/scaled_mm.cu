@@ -51,7 +51,7 @@ struct Params {
   const float* a_scales;  // 1 or M
   const float* b_scales;  // 1 or N
   const void* bias;       // nullptr or [N] out_t
-  uint32_t* counters;     // split-K: arrive[2 * tiles] then depart[2 * tiles], zero between launches
+  uint32_t* counters;     // split-K: arrive[2 * tiles], zero between launches (self re-arming)
   float* partials;        // split-K: [tiles * 2][owner][source slice][col_chunk / 4][128][4] fp32
   int M, N, K;
   int64_t ldc;
@@ -68,14 +68,45 @@ struct Params {
   int units;         // tiles * splits
   uint32_t main_bytes;  // bytes of the stage ring (barriers follow)
   uint64_t hint_w, hint_a;
+  unsigned long long* trace;  // debug: [grid][16] %globaltimer stamps (nullptr = off)
 };
 
+__device__ __forceinline__ void stamp(const Params& p, int slot) {
+  if (p.trace != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[(size_t)blockIdx.x * 16 + slot] = t;
+  }
+}
+
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+
+// Epilogue of 16 consecutive token columns of one weight row: out[t0 + j][n] = a_scale[j] * (b_scale * acc[j])
+// (+ bias)  (ScaledEpilogue / ScaledEpilogueBias).  The 16 a_scales are read from shared memory with explicit
+// ld.shared (a generic load here would be ordered after every preceding global store and serialise the loop).
 template <typename OutT>
-__device__ __forceinline__ void store_scaled(OutT* outp, int64_t ldc, int t, int n, float acc,
-                                             float asc, float bsc, float biasf, bool has_bias) {
-  // a_scale * (b_scale * acc) [+ bias]  (ScaledEpilogue / ScaledEpilogueBias)
-  const float v = has_bias ? fmaf(asc, bsc * acc, biasf) : asc * (bsc * acc);
-  outp[(int64_t)t * ldc + n] = from_float<OutT>(v);
+__device__ __forceinline__ void store_chunk16(OutT* orow, int64_t ldc, const float (&acc)[16], uint32_t asc_smem,
+                                              float bsc, float biasf, bool has_bias, int nvalid) {
+  float a[16];
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) {
+    const float4 v = lds_f4(asc_smem + 16 * q4);
+    a[4 * q4] = v.x;
+    a[4 * q4 + 1] = v.y;
+    a[4 * q4 + 2] = v.z;
+    a[4 * q4 + 3] = v.w;
+  }
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float sv = bsc * acc[j];
+    const float v = has_bias ? fmaf(a[j], sv, biasf) : a[j] * sv;
+    if (j < nvalid) *orow = from_float<OutT>(v);
+    orow += ldc;
+  }
 }
 
 template <typename OutT>
@@ -93,7 +124,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint64_t* acc_empty = acc_full + 2;           // [2] accumulator stage drained (leader's is used)
   uint64_t* red_bar = acc_empty + 2;             // split-K: bulk fetch of the foreign partials
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(red_bar + 1);
-  float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 4);  // [2][256]
+  float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 6);  // [2][256], 16-byte aligned (offset 256 past the ring)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -101,6 +132,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   const int pair = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
   const int tok_half = p.tok_tile >> 1;
+  if (threadIdx.x == 0) stamp(p, 0);
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmap_w);
@@ -121,6 +153,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   cluster_sync_all();  // barrier inits + TMEM allocation visible in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  if (threadIdx.x == 0) stamp(p, 1);
 
   if (warp == 0) {
     // ===== TMA producer (both CTAs; one thread) =====
@@ -145,6 +178,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t bar = map_to_cta(smem_u32(&full_bar[stage]), 0);
           tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
           tma_load_2d_2cta(sa, &tmap_a, bar, kb * kBlockK, tok0, p.hint_a);
+          if (it == 0) stamp(p, 2);
         }
       }
       // tail: every stage this CTA filled has been released, i.e. all multicast arrivals aimed at
@@ -175,6 +209,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t phase = (it / p.stages) & 1;
           mbar_wait(&full_bar[stage], phase);  // both CTAs' boxes have landed
           tc_fence_after();
+          if (it == 0) stamp(p, 3);
           const uint32_t sw = smem_u32(smem + (size_t)stage * p.stage_bytes);
           const uint64_t adesc = make_smem_desc_sw128(sw);
           const uint64_t bdesc = make_smem_desc_sw128(sw + kWTileBytes);
@@ -187,6 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           umma_commit_2cta(&empty_bar[stage], 0x3);  // frees the stage in both CTAs
         }
         umma_commit_2cta(&acc_full[as], 0x3);  // accumulator complete, both CTAs' epilogues may read
+        stamp(p, 4);
       }
     }
     __syncwarp();
@@ -220,30 +256,36 @@ __global__ void __launch_bounds__(kThreads, 1)
       named_bar_sync(kEpiBarrier, 128);  // a_scale tile staged (and the previous use of `asc` is over)
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
+      if (tid_e == 0) stamp(p, 5);
       const uint32_t taddr = lane_addr + as * kAccStride;
       const int ncols = min(p.tok_tile, p.M - tok0);  // valid token columns of this tile
 
+      const uint32_t asc_u32 = smem_u32(asc);
+      // 16 accumulator columns (registers r[off .. off+15]) -> scaled, converted, stored
+      auto emit16 = [&](const uint32_t* r, int c) {
+        float f[16];
+#pragma unroll
+        for (int jx = 0; jx < 16; ++jx) f[jx] = __uint_as_float(r[jx]);
+        if (n_ok)
+          store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
+                        ncols - c);
+      };
       if (p.splits == 1) {
-        for (int c = 0; c < ncols; c += 32) {
-          uint32_t r0[16], r1[16];
-          tmem_ld_x16(taddr + c, r0);
-          const bool second = c + 16 < ncols;
-          if (second) tmem_ld_x16(taddr + c + 16, r1);
+        // tcgen05.ld is warp-collective (never under a per-lane predicate) and asynchronous: the load of the
+        // next 32 columns is in flight while the current 32 are converted and stored
+        uint32_t ra[32], rb[32];
+        tmem_ld_x32(taddr, ra);
+        for (int c = 0; c < ncols; c += 64) {
           tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int t = tok0 + c + j;
-            if (n_ok && t < p.M)
-              store_scaled(outp, p.ldc, t, n, __uint_as_float(r0[j]), asc[c + j], bsc, biasf, has_bias);
-          }
-          if (second) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int t = tok0 + c + 16 + j;
-              if (n_ok && t < p.M)
-                store_scaled(outp, p.ldc, t, n, __uint_as_float(r1[j]), asc[c + 16 + j], bsc, biasf,
-                             has_bias);
-            }
+          const bool more1 = c + 32 < ncols;
+          if (more1) tmem_ld_x32(taddr + c + 32, rb);
+          emit16(ra, c);
+          if (c + 16 < ncols) emit16(ra + 16, c + 16);
+          if (more1) {
+            tmem_ld_wait();
+            if (c + 64 < ncols) tmem_ld_x32(taddr + c + 64, ra);
+            emit16(rb, c + 32);
+            if (c + 48 < ncols) emit16(rb + 16, c + 48);
           }
         }
       } else {
@@ -252,30 +294,53 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int cw = p.col_chunk, S = p.splits;
         const size_t R = (size_t)cw * kCtaRows;  // floats per (owner, source) region
         float* base = p.partials + (size_t)(tile * 2 + (int)rank) * S * S * R;
-        for (int o = 0; o < S; ++o) {
-          if (o == split) continue;
-          const int c_begin = o * cw, c_end = min(c_begin + cw, p.tok_tile);
-          float4* dst = reinterpret_cast<float4*>(base + ((size_t)o * S + split) * R);
-          for (int c = c_begin; c < c_end; c += 16) {
-            uint32_t r0[16];
-            tmem_ld_x16(taddr + c, r0);
-            tmem_ld_wait();
+        const int tpc = p.tok_tile >> 4;  // 16-column chunks of the tile
+        auto next_foreign = [&](int jc) {
+          while (jc < tpc && (jc << 4) / cw == split) ++jc;
+          return jc;
+        };
+        auto park16 = [&](const uint32_t* r, int jc) {
+          const int c = jc << 4, o = c / cw;
+          float4* dst = reinterpret_cast<float4*>(base + ((size_t)o * S + split) * R) +
+                        (size_t)((c - o * cw) >> 2) * kCtaRows + row;
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-              __stcg(dst + (size_t)(((c - c_begin) >> 2) + jj) * kCtaRows + row,
-                     make_float4(__uint_as_float(r0[4 * jj]), __uint_as_float(r0[4 * jj + 1]),
-                                 __uint_as_float(r0[4 * jj + 2]), __uint_as_float(r0[4 * jj + 3])));
+          for (int jj = 0; jj < 4; ++jj)
+            __stcg(dst + (size_t)jj * kCtaRows,
+                   make_float4(__uint_as_float(r[4 * jj]), __uint_as_float(r[4 * jj + 1]),
+                               __uint_as_float(r[4 * jj + 2]), __uint_as_float(r[4 * jj + 3])));
+        };
+        {
+          uint32_t ra[16], rb[16];
+          int j0 = next_foreign(0);
+          if (j0 < tpc) tmem_ld_x16(taddr + (j0 << 4), ra);
+          while (j0 < tpc) {
+            const int j1 = next_foreign(j0 + 1);
+            tmem_ld_wait();
+            if (j1 < tpc) tmem_ld_x16(taddr + (j1 << 4), rb);
+            park16(ra, j0);
+            if (j1 >= tpc) break;
+            const int j2 = next_foreign(j1 + 1);
+            tmem_ld_wait();
+            if (j2 < tpc) tmem_ld_x16(taddr + (j2 << 4), ra);
+            park16(rb, j1);
+            j0 = j2;
           }
         }
         __threadfence();
+        if (tid_e == 0) stamp(p, 6);
         named_bar_sync(kEpiBarrier, 128);
+        // arrival counter that re-arms itself: atomicInc wraps to 0 on the S-th arrival, and 0 is what every
+        // waiter (who has incremented it itself) waits for; it is 0 again for the next launch
         uint32_t* arrive = p.counters + tile * 2 + (int)rank;
-        uint32_t* depart = p.counters + 2 * p.tiles + tile * 2 + (int)rank;
         const int nc = min(cw, p.tok_tile - split * cw);  // columns this slice reduces and writes
+        const int c_own = split * cw;
+        uint32_t ra[16], rb[16];
+        if (nc > 0) tmem_ld_x16(taddr + c_own, ra);  // own columns: in flight during the wait below
         if (tid_e == 0) {
-          atomicAdd(arrive, 1u);
-          while (ld_acquire_gpu(arrive) < (uint32_t)S) {
+          atomicInc(arrive, (uint32_t)S - 1u);
+          while (ld_acquire_gpu(arrive) != 0u) {
           }
+          stamp(p, 7);
           if (nc > 0) {
             // every slice's partials are visible: pull the S-1 foreign regions of my columns into the
             // (now idle) pipeline stages with two bulk copies (the regions left and right of my own)
@@ -289,43 +354,42 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
         if (nc > 0) {
           mbar_wait(red_bar, 0);
-          const float4* sp = reinterpret_cast<const float4*>(smem);
+          if (tid_e == 0) stamp(p, 8);
+          const uint32_t sp = smem_u32(smem) + (uint32_t)row * 16u;
           const int cq = cw >> 2;
-          for (int c = 0; c < nc; c += 16) {
-            uint32_t r0[16];
-            tmem_ld_x16(taddr + split * cw + c, r0);
-            tmem_ld_wait();
+          auto reduce16 = [&](const uint32_t* r, int c) {  // c: column offset inside my chunk
+            float f[16];
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              float4 acc = make_float4(__uint_as_float(r0[4 * jj]), __uint_as_float(r0[4 * jj + 1]),
-                                       __uint_as_float(r0[4 * jj + 2]), __uint_as_float(r0[4 * jj + 3]));
-              for (int s2 = 0; s2 < S - 1; ++s2) {  // own slice first, then the others in slice order
-                const float4 v = sp[(size_t)(s2 * cq + (c >> 2) + jj) * kCtaRows + row];
-                acc.x += v.x;
-                acc.y += v.y;
-                acc.z += v.z;
-                acc.w += v.w;
+            for (int jx = 0; jx < 16; ++jx) f[jx] = __uint_as_float(r[jx]);
+            for (int s2 = 0; s2 < S - 1; ++s2) {  // own slice first, then the others in slice order
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                const float4 v = lds_f4(sp + (uint32_t)((s2 * cq + (c >> 2) + jj) * kCtaRows * 16));
+                f[4 * jj] += v.x;
+                f[4 * jj + 1] += v.y;
+                f[4 * jj + 2] += v.z;
+                f[4 * jj + 3] += v.w;
               }
-              const int cc = split * cw + c + 4 * jj;
-              const int t = tok0 + cc;
-              if (n_ok) {
-                if (t < p.M) store_scaled(outp, p.ldc, t, n, acc.x, asc[cc], bsc, biasf, has_bias);
-                if (t + 1 < p.M) store_scaled(outp, p.ldc, t + 1, n, acc.y, asc[cc + 1], bsc, biasf, has_bias);
-                if (t + 2 < p.M) store_scaled(outp, p.ldc, t + 2, n, acc.z, asc[cc + 2], bsc, biasf, has_bias);
-                if (t + 3 < p.M) store_scaled(outp, p.ldc, t + 3, n, acc.w, asc[cc + 3], bsc, biasf, has_bias);
-              }
+            }
+            const int cc = c_own + c;
+            if (n_ok)
+              store_chunk16(outp + (int64_t)(tok0 + cc) * p.ldc + n, p.ldc, f, asc_u32 + 4 * cc, bsc, biasf, has_bias,
+                            p.M - tok0 - cc);
+          };
+          for (int c = 0; c < nc; c += 32) {
+            tmem_ld_wait();
+            const bool more1 = c + 16 < nc;
+            if (more1) tmem_ld_x16(taddr + c_own + c + 16, rb);
+            reduce16(ra, c);
+            if (more1) {
+              tmem_ld_wait();
+              if (c + 32 < nc) tmem_ld_x16(taddr + c_own + c + 32, ra);
+              reduce16(rb, c + 16);
             }
           }
         }
-        named_bar_sync(kEpiBarrier, 128);
-        if (tid_e == 0) {
-          // the last slice to leave re-arms the counters for the next launch
-          if (atomicAdd(depart, 1u) == (uint32_t)S - 1u) {
-            atomicExch(arrive, 0u);
-            atomicExch(depart, 0u);
-          }
-        }
       }
+      if (tid_e == 0) stamp(p, 9);
       // accumulator stage drained: tell the leader's MMA thread
       tc_fence_before();
       __syncwarp();
@@ -340,9 +404,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     tc_fence_after();
     tmem_dealloc_2cta(tmem_base, kTmemCols);
   }
+  if (threadIdx.x == 0) stamp(p, 10);
 }
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+static unsigned long long* g_trace = nullptr;  // set through vb200_debug_scaled_mm_trace()
 
 struct Plan {
   int tok_tile, m_tiles, n_ptiles, tiles, stages, stage_bytes, splits, kb_per_split, num_kb, col_chunk,
@@ -359,7 +426,7 @@ static Plan make_plan(int M, int N, int K) {
   g.num_kb = ceil_div(K, kBlockK);
   const int a_bytes = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
   g.stage_bytes = kWTileBytes + a_bytes;
-  const int tail = 2 * kMaxStages * 8 + 5 * 8 + 16 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
+  const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
   const int budget = 227 * 1024 - 1024 /*alignment slack*/ - tail;
   g.stages = budget / g.stage_bytes;
   if (g.stages > kMaxStages) g.stages = kMaxStages;
@@ -451,6 +518,7 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
   // weights are streamed once when there is a single token tile; otherwise they are re-read from L2
   p.hint_w = g.m_tiles == 1 ? kEvictFirst : kEvictNormal;
   p.hint_a = g.m_tiles == 1 ? kEvictLast : kEvictNormal;
+  p.trace = g_trace;
   if (out_dtype == VB200_BF16) return launch<__nv_bfloat16>(g, tw, ta, p, stream);
   return launch<__half>(g, tw, ta, p, stream);
 }
@@ -459,6 +527,12 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
 }  // namespace vb200
 
 using namespace vb200;
+
+// Debug / profiling hook (not part of the drop-in surface): when `buf` is non-NULL every CTA of the following
+// cutlass_scaled_mm launches writes 16 %globaltimer stamps (ns) at buf[blockIdx.x * 16 + i]:
+// 0 entry, 1 set-up done, 2 first TMA issued, 3 first stage landed, 4 last MMA committed, 5 accumulator ready,
+// 6 split-K partials parked, 7 all slices arrived, 8 foreign partials fetched, 9 epilogue done, 10 exit.
+extern "C" void vb200_debug_scaled_mm_trace(void* buf) { v2::g_trace = (unsigned long long*)buf; }
 
 extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
 
