@@ -2,7 +2,7 @@
 """bench.py -- decode throughput of the hot path on BASELINE.json's metric
 ("decode tokens/s/GPU Llama-3.1-8B FP8; paged-attn HBM GB/s vs peak").
 
-    python bench.py --gpus N --steps K --warmup W [--impl reference] [--config cfg3|cfg2|tiny]
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--config cfg3|cfg2|cfg4|tiny]
 
 One "step" = one decode step (all 32 layers + lm_head + greedy arg-max) of Llama-3.1-8B, FP8 w8a8 scaled_mm
 (dynamic per-token activation scales, per-channel weight scales) + fp8_e4m3 paged KV cache (block 16), batch 256
@@ -40,6 +40,7 @@ WORKLOADS = {
     # name: (model, batch, ctx, quant, kv_cache_dtype)
     "cfg3": ("Llama-3.1-8B", 256, 4096, "fp8", "fp8"),
     "cfg2": ("Llama-3.1-8B", 64, 2048, "bf16", "auto"),
+    "cfg4": ("Mixtral-8x7B", 128, 2048, "fp8", "fp8"),   # BASELINE configs[3] (context not named there: 2k)
     "tiny": ("tiny-llama", 8, 256, "fp8", "fp8"),
 }
 
@@ -50,6 +51,18 @@ def peaks():
         return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_traffic(config, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from the committed
+    `ncu --set full` capture of this command (profiles/r01_kernel_traffic.json); None when no capture exists for
+    the configuration (ncu cannot run inside a timed bench)."""
+    if world != 1:
+        return None
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")))[config]["traffic"]
+    except Exception:
+        return None
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -221,7 +234,7 @@ def run_reference_arm(args, rank: int):
 
 def workload_config(name: str, n_gpus: int):
     model, batch, ctx, quant, kvd = WORKLOADS[name]
-    return {"workload": f"BASELINE configs[{ {'cfg3': 2, 'cfg2': 1}.get(name, 0) }]: {model} {quant} "
+    return {"workload": f"BASELINE configs[{ {'cfg3': 2, 'cfg2': 1, 'cfg4': 3}.get(name, 0) }]: {model} {quant} "
                         f"{'w8a8 scaled_mm ' if quant == 'fp8' else ''}+ {'fp8_e4m3' if kvd == 'fp8' else 'bf16'} "
                         f"paged KV block 16, batch {batch} decode at {ctx} context",
             "global_batch": batch, "context_len": ctx, "block_size": 16, "parallelism": f"tp{n_gpus}",
@@ -295,7 +308,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     # ---- count launches of OUR kernels in one step (host-side counter around the C ABI) -------------
     lib = _lib.load()
     counter = {"n": 0}
-    per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_dynamic_scaled_fp8_quant": 2}
+    per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_dynamic_scaled_fp8_quant": 2,
+                "vb200_moe_grouped_gemm_fp8": 2}
     wrapped = {}
     for name in _lib.SIGNATURES:
         if name.startswith("vb200_") and not any(s in name for s in ("size", "error", "version", "supports")):
@@ -415,7 +429,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         "gpu_launches_per_step": launches_per_step,
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel (+ split-K reduce)",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": kernel_traffic(args.config, world), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo, "avg_launch_us": round(attn_s * 1e6, 2),
                      "launches_timed": len(attn_ms),
                      "share_of_step": round(attn_s * 1e3 * len(dec.layers) / ms, 4),

@@ -275,6 +275,47 @@ int vb200_moe_grouped_gemm_fp8(void* c, const void* a, const void* b, const floa
                                int b_scales_per_channel, int mul_routed_weight, int out_dtype,
                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
 
+/* ---- CUTLASS-style fused-MoE API ----------------------------------------- */
+
+/* get_cutlass_moe_mm_data: csrc/quantization/cutlass_w8a8/moe/moe_data.cu:103-159, schema
+ * csrc/torch_bindings.cpp:465-471.  topk_ids int32 [num_tokens, topk] (-1 = expert not on this rank);
+ * expert_offsets int32 [num_experts + 1]; problem_sizes1/2 int32 [num_experts, 3] = (m_e, 2n, k) / (m_e, k, n),
+ * first two entries swapped when num_tokens*topk <= 64 and blockscale_offsets == NULL (:9,121-122);
+ * input_permutation int32 [num_tokens*topk]: sorted row -> source token (flat index / topk);
+ * output_permutation int32 [num_tokens*topk]: flat index -> sorted row (ids == -1 -> total routed rows);
+ * blockscale_offsets: NULL or int32 [num_experts + 1], rows rounded up to 128 per expert (:61-79).
+ * Order inside an expert is the stable one (the reference's is scheduling-dependent). */
+int vb200_get_cutlass_moe_mm_data(const int32_t* topk_ids, int num_tokens, int topk,
+                                  int32_t* expert_offsets, int32_t* problem_sizes1,
+                                  int32_t* problem_sizes2, int32_t* input_permutation,
+                                  int32_t* output_permutation, int num_experts, int n, int k,
+                                  int32_t* blockscale_offsets, vb200_stream_t stream);
+
+/* get_cutlass_pplx_moe_mm_data: moe_data.cu:161-195 (batched-experts format: expert e starts at e*padded_m). */
+int vb200_get_cutlass_pplx_moe_mm_data(int32_t* expert_offsets, int32_t* problem_sizes1,
+                                       int32_t* problem_sizes2, const int32_t* expert_num_tokens,
+                                       int num_local_experts, int padded_m, int n, int k,
+                                       vb200_stream_t stream);
+
+/* shuffle_rows: vllm/_custom_ops.py:912-922.  out[r, :] = in[dst2src_map[r], :]; rows are row_bytes bytes. */
+int vb200_shuffle_rows(void* out, const void* in, const int32_t* dst2src_map, int num_dst_rows,
+                       int num_src_rows, int64_t row_bytes, vb200_stream_t stream);
+
+/* cutlass_moe_mm: csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:242-270, schema
+ * csrc/torch_bindings.cpp:450-456.  For every expert e with m_e rows (problem_sizes[e] = (m_e, N, K),
+ * or (N, m_e, K) as get_cutlass_moe_mm_data writes it for <= 64 routed rows; the kernel accepts either):
+ *   out[off_e : off_e + m_e, :] = OutT( (A[off_e : off_e + m_e, :] @ B[e]^T) * a_scale * b_scale ),
+ *   off_e = expert_offsets[e] (int32 [E]).
+ * a fp8 [num_rows, K] contiguous; b fp8 [E, N, K] contiguous (the reference's column-major B per expert, stride K);
+ * out [num_rows, N] bf16/f16 contiguous; a_scales fp32 [num_rows] (per_act_token) or [1]; b_scales fp32 [E, N]
+ * (per_out_ch) or [E].  Rows owned by no expert are left untouched.  The a/b/c stride tensors of the reference
+ * schema must describe these contiguous layouts (its only caller passes K, K, N: cutlass_moe.py:153-168).
+ */
+int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, const float* a_scales,
+                         const float* b_scales, const int32_t* expert_offsets,
+                         const int32_t* problem_sizes, int num_rows, int E, int N, int K,
+                         int per_act_token, int per_out_ch, int out_dtype, vb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

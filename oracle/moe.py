@@ -126,3 +126,90 @@ def fused_experts_bf16(hidden, w1, w2, topk_weights, topk_ids):
         acc = t2.to(_f32) @ w2[e].to(_f32).t()
         c3[sel] = (acc * topk_weights.flatten()[sel].to(_f32)[:, None]).to(hidden.dtype)
     return moe_sum(c3.reshape(T, k, H))
+
+
+# ---- CUTLASS-style fused-MoE API ------------------------------------------------------------
+def get_cutlass_moe_mm_data(topk_ids: torch.Tensor, num_experts: int, n: int, k: int, blockscale: bool = False):
+    """csrc/quantization/cutlass_w8a8/moe/moe_data.cu:11-159.  Returns (expert_offsets [E+1], problem_sizes1 [E,3],
+    problem_sizes2 [E,3], input_permutation, output_permutation[, blockscale_offsets]) as int32 tensors; the
+    permutation is the stable member of the reference's (atomics-ordered) family; ids == -1 map to row `total`
+    (:92-99); the first two problem-size entries are swapped for <= 64 routed rows unless blockscale (:9,121-122)."""
+    flat = topk_ids.flatten().long()
+    numel, topk = flat.numel(), topk_ids.shape[1]
+    swap = (not blockscale) and numel <= 64
+    counts = torch.zeros(num_experts, dtype=torch.int64)
+    for e in flat.tolist():
+        if 0 <= e < num_experts:
+            counts[e] += 1
+    offs = torch.zeros(num_experts + 1, dtype=torch.int64)
+    offs[1:] = torch.cumsum(counts, 0)
+    ps1 = torch.zeros(num_experts, 3, dtype=torch.int32)
+    ps2 = torch.zeros(num_experts, 3, dtype=torch.int32)
+    for e in range(num_experts):
+        m = int(counts[e])
+        ps1[e] = torch.tensor([2 * n, m, k] if swap else [m, 2 * n, k], dtype=torch.int32)
+        ps2[e] = torch.tensor([k, m, n] if swap else [m, k, n], dtype=torch.int32)
+    total = int(offs[-1])
+    a_map = torch.zeros(numel, dtype=torch.int32)
+    c_map = torch.zeros(numel, dtype=torch.int32)
+    nxt = offs[:-1].clone()
+    for i, e in enumerate(flat.tolist()):
+        if 0 <= e < num_experts:
+            a_map[int(nxt[e])] = i // topk
+            c_map[i] = int(nxt[e])
+            nxt[e] += 1
+        elif e == -1:
+            c_map[i] = total
+    out = (offs.to(torch.int32), ps1, ps2, a_map, c_map)
+    if blockscale:
+        bo = torch.zeros(num_experts + 1, dtype=torch.int64)
+        bo[1:] = torch.cumsum((counts + 127) // 128 * 128, 0)
+        out = out + (bo.to(torch.int32),)
+    return out
+
+
+def cutlass_moe_mm(a_q, b_q, a_scales, b_scales, expert_offsets, rows_per_expert, out_dtype=torch.bfloat16,
+                   out=None):
+    """cutlass_moe_mm (scaled_mm_entry.cu:242-270; ScaledEpilogueArray: D = a_scale * (b_scale * acc), the scale
+    granularity inferred from the element counts, moe/get_group_starts.cuh:24-31,58-59).  a_q fp8 [rows, K];
+    b_q fp8 [E, N, K]; rows of expert e = [expert_offsets[e], +rows_per_expert[e]).  Rows owned by no expert keep
+    the contents of `out` (zeros when not given)."""
+    E, N, K = b_q.shape
+    c = torch.zeros(a_q.shape[0], N, dtype=out_dtype) if out is None else out.clone()
+    per_tok = a_scales.numel() != 1
+    per_ch = b_scales.numel() != E
+    for e in range(E):
+        m, o = int(rows_per_expert[e]), int(expert_offsets[e])
+        if m == 0:
+            continue
+        acc = (a_q[o:o + m].to(torch.float64) @ b_q[e].to(torch.float64).t()).to(_f32)
+        sa = a_scales.flatten()[o:o + m].to(_f32)[:, None] if per_tok else a_scales.flatten()[0].to(_f32)
+        sb = b_scales.reshape(E, -1)[e].to(_f32).reshape(1, -1) if per_ch else b_scales.flatten()[e].to(_f32)
+        c[o:o + m] = (sa * (sb * acc)).to(out_dtype)
+    return c
+
+
+def cutlass_moe_fp8(a, w1_q, w2_q, topk_weights, topk_ids, w1_scale, w2_scale, per_act_token, a1_scale=None,
+                    a2_scale=None, expert_map=None):
+    """cutlass_moe_fp8 (fused_moe/cutlass_moe.py:324-409 = MoEPrepareAndFinalizeNoEP + run_cutlass_moe_fp8 :25-215 +
+    TopKWeightAndReduceContiguous): quantise, permute, GEMM1, silu_and_mul, quantise, GEMM2, un-permute, multiply by
+    the routing weights (fp32 product rounded once), moe_sum."""
+    M, K = a.shape
+    E, _, N = w2_q.shape
+    topk = topk_ids.shape[1]
+    num_experts = expert_map.numel() if expert_map is not None else E
+    local = topk_ids.long()
+    if expert_map is not None:
+        local = torch.where(expert_map[local] != -1, expert_map[local], -1)
+    a1q, a1s = _quant_act(a, a1_scale, per_act_token)
+    offs, ps1, _, a_map, c_map = get_cutlass_moe_mm_data(local, num_experts, N, K)[:5]
+    counts = (offs[1:] - offs[:-1])[:E]
+    ap = a1q[a_map.long()]
+    asp = a1s.reshape(-1)[a_map.long()] if per_act_token else a1s
+    c1 = cutlass_moe_mm(ap, w1_q, asp, w1_scale, offs[:E], counts, a.dtype)
+    c2 = silu_and_mul(c1)
+    a2q, a2s = _quant_act(c2, a2_scale, per_act_token)
+    c3 = cutlass_moe_mm(a2q, w2_q, a2s, w2_scale, offs[:E], counts, a.dtype)
+    out = c3[c_map.long()].view(M, topk, K)
+    out = (out.to(_f32) * topk_weights.view(M, topk, 1).to(_f32)).to(a.dtype)   # topk_weight_and_reduce.py:89
+    return moe_sum(out)

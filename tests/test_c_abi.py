@@ -89,6 +89,18 @@ def test_torch_shim_registers_reference_schemas():
     s = str(torch.ops._b200_moe_C.moe_align_block_size.default._schema)
     assert "int num_experts, int block_size" in s
     assert torch.ops._b200_C.cutlass_scaled_mm_supports_fp8(100) and not torch.ops._b200_C.cutlass_scaled_mm_supports_fp8(89)
+    # CUTLASS-style MoE API (csrc/torch_bindings.cpp:446-488, csrc/moe/torch_bindings.cpp:75-78)
+    s = str(torch.ops._b200_C.cutlass_moe_mm.default._schema)
+    assert "out_tensors, Tensor a_tensors, Tensor b_tensors, Tensor a_scales, Tensor b_scales, Tensor expert_offsets, " \
+           "Tensor problem_sizes, Tensor a_strides, Tensor b_strides, Tensor c_strides, bool per_act_token, " \
+           "bool per_out_ch) -> ()" in s
+    s = str(torch.ops._b200_C.get_cutlass_moe_mm_data.default._schema)
+    assert s.count("!") == 5 and "int num_experts, int n, int k, Tensor? blockscale_offsets) -> ()" in s
+    s = str(torch.ops._b200_C.get_cutlass_pplx_moe_mm_data.default._schema)
+    assert s.count("!") == 3 and "int num_local_experts, int padded_m, int n, int k) -> ()" in s
+    s = str(torch.ops._b200_moe_C.shuffle_rows.default._schema)
+    assert "Tensor input_tensor, Tensor dst2src_map, Tensor(" in s and s.count("!") == 1 and "output_tensor) -> ()" in s
+    assert torch.ops._b200_C.cutlass_group_gemm_supported(100) and not torch.ops._b200_C.cutlass_group_gemm_supported(90)
 
 
 def test_glue_mirrors_reference_names():
@@ -108,6 +120,21 @@ def test_glue_mirrors_reference_names():
     assert list(inspect.signature(Fp8LinearOp.apply).parameters)[1:] == ["input", "weight", "weight_scale", "out_dtype",
                                                                          "input_scale", "input_scale_ub", "bias"]
     assert PagedAttention.get_kv_cache_shape(4, 16, 8, 128) == (2, 4, 16 * 8 * 128)
+    # CUTLASS-style MoE (vllm/_custom_ops.py:871-969, fused_moe/cutlass_moe.py:25-45, 324-339)
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.fused_moe import cutlass_moe_fp8, run_cutlass_moe_fp8
+    assert list(inspect.signature(ops.get_cutlass_moe_mm_data).parameters) == [
+        "topk_ids", "expert_offsets", "problem_sizes1", "problem_sizes2", "input_permutation", "output_permutation",
+        "num_experts", "n", "k", "blockscale_offsets"]
+    assert list(inspect.signature(ops.cutlass_moe_mm).parameters) == [
+        "out_tensors", "a_tensors", "b_tensors", "a_scales", "b_scales", "expert_offsets", "problem_sizes", "a_strides",
+        "b_strides", "c_strides", "per_act_token", "per_out_ch"]
+    assert list(inspect.signature(ops.shuffle_rows).parameters) == ["input_tensor", "dst2src_map"]
+    assert list(inspect.signature(cutlass_moe_fp8).parameters) == [
+        "a", "w1_q", "w2_q", "topk_weights", "topk_ids", "w1_scale", "w2_scale", "per_act_token", "activation",
+        "a1_scale", "a2_scale", "expert_map", "apply_router_weight_on_input", "global_num_experts"]
+    assert list(inspect.signature(run_cutlass_moe_fp8).parameters)[:8] == [
+        "output", "hidden_states", "w1", "w2", "topk_ids", "activation_callable", "global_num_experts", "expert_map"]
     for m in ("get_name", "get_impl_cls", "get_metadata_cls", "get_builder_cls", "get_kv_cache_shape", "swap_blocks",
               "copy_blocks", "get_supported_head_sizes"):
         assert hasattr(B200PagedAttentionBackend, m)

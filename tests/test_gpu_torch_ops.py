@@ -119,3 +119,40 @@ def test_moe_ops(tops):
     ops.moe_sum(x, o1)
     tops._b200_moe_C.moe_sum(x, o2)
     assert torch.equal(o1, o2)
+
+
+def test_cutlass_moe_ops(tops):
+    """get_cutlass_moe_mm_data / shuffle_rows / cutlass_moe_mm through torch.ops == the ctypes host path, bit for bit."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(3)
+    T, k, E, N, K = 70, 2, 8, 256, 256
+    ids = torch.stack([torch.randperm(E)[:k] for _ in range(T)]).to(torch.int32).to(DEV)
+
+    def bufs():
+        return (torch.empty(E + 1, dtype=torch.int32, device=DEV), torch.empty(E, 3, dtype=torch.int32, device=DEV),
+                torch.empty(E, 3, dtype=torch.int32, device=DEV), torch.empty(T * k, dtype=torch.int32, device=DEV),
+                torch.empty(T * k, dtype=torch.int32, device=DEV))
+    b1, b2 = bufs(), bufs()
+    ops.get_cutlass_moe_mm_data(ids, *b1, E, N // 2, K)
+    tops._b200_C.get_cutlass_moe_mm_data(ids, *b2, E, N // 2, K, None)
+    for x, y in zip(b1, b2):
+        assert torch.equal(x, y)
+    eo, ps1, _, a_map, c_map = b1
+    a = (torch.randn(T, K, device=DEV)).to(FP8)
+    ap = ops.shuffle_rows(a, a_map)
+    ap2 = torch.empty_like(ap)
+    tops._b200_moe_C.shuffle_rows(a, a_map, ap2)
+    assert torch.equal(ap.view(torch.uint8), ap2.view(torch.uint8))
+    w = (torch.randn(E, N, K, device=DEV) / 4).to(FP8)
+    sa = torch.rand(T * k, 1, device=DEV) + 0.5
+    sb = torch.rand(E, N, device=DEV) + 0.5
+    st = torch.full((E,), K, dtype=torch.int64, device=DEV)
+    cst = torch.full((E,), N, dtype=torch.int64, device=DEV)
+    o1 = torch.zeros(T * k, N, dtype=torch.bfloat16, device=DEV)
+    o2 = torch.zeros_like(o1)
+    ops.cutlass_moe_mm(o1, ap, w, sa, sb, eo[:-1], ps1, st, st, cst, True, True)
+    tops._b200_C.cutlass_moe_mm(o2, ap, w, sa, sb, eo[:-1], ps1, st, st, cst, True, True)
+    assert torch.equal(o1, o2) and bool(o1.abs().sum() > 0)
+    assert tops._b200_C.cutlass_group_gemm_supported(100)
+    torch.library.opcheck(tops._b200_C.get_cutlass_moe_mm_data.default, (ids, *bufs(), E, N // 2, K, None),
+                          test_utils=("test_schema", "test_faketensor"))

@@ -151,3 +151,32 @@ def test_moe_sum_and_experts_oracle_consistency():
             h2 = oquant.silu_and_mul(h1[None])[0]
             ref[t] += w[t, j] * (h2.float() @ w2[e].float().t())
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+def test_cutlass_moe_data_oracle_known_answer():
+    """oracle.moe.get_cutlass_moe_mm_data on the routing example of the reference docstring
+    (fused_moe/moe_align_block_size.py:52-66, experts numbered 1..4): offsets = exclusive prefix of the per-expert
+    counts, a_map/c_map are inverse permutations, swapped problem sizes for <= 64 routed rows (moe_data.cu:9,30-44),
+    and the grouped-GEMM oracle equals per-expert dense matmuls of the dequantised operands."""
+    import torch
+    from oracle import moe as omoe
+    ids = torch.tensor([[2, 3, 4], [1, 2, 4], [1, 3, 4], [1, 2, 3]], dtype=torch.int32)
+    eo, ps1, ps2, a_map, c_map = omoe.get_cutlass_moe_mm_data(ids, 5, 8, 16)
+    assert eo.tolist() == [0, 0, 3, 6, 9, 12]
+    assert ps1.tolist() == [[16, 0, 16]] + [[16, 3, 16]] * 4 and ps2.tolist() == [[16, 0, 8]] + [[16, 3, 8]] * 4
+    assert c_map.tolist() == [3, 6, 9, 0, 4, 10, 1, 7, 11, 2, 5, 8]
+    assert a_map[c_map.long()].tolist() == [i // 3 for i in range(12)]
+    big = torch.randint(0, 5, (40, 2), dtype=torch.int32)          # 80 rows > 64: not swapped
+    assert omoe.get_cutlass_moe_mm_data(big, 5, 8, 16)[1][:, 1].tolist() == [16] * 5
+    # grouped GEMM oracle == dequantised per-expert matmul
+    torch.manual_seed(0)
+    E, N, K, rows = 3, 32, 64, 10
+    a = torch.randn(rows, K).to(torch.float8_e4m3fn)
+    b = torch.randn(E, N, K).to(torch.float8_e4m3fn)
+    sa, sb = torch.rand(rows) + 0.5, torch.rand(E, N) + 0.5
+    off, cnt = torch.tensor([0, 4, 4]), torch.tensor([4, 0, 6])
+    got = omoe.cutlass_moe_mm(a, b, sa, sb, off, cnt, torch.float32)
+    for e in range(E):
+        o, m = int(off[e]), int(cnt[e])
+        want = (a[o:o + m].float() * sa[o:o + m, None]) @ (b[e].float() * sb[e][:, None]).t()
+        torch.testing.assert_close(got[o:o + m], want, rtol=1e-5, atol=1e-5)

@@ -434,6 +434,117 @@ def moe_sum(input: torch.Tensor, output: torch.Tensor) -> None:
         check(load().vb200_moe_sum(ptr(output), ptr(input), t, k, h, dtype_enum(input.dtype), stream()))
 
 
+# ---------------------------------------------------------------------------------------------------
+# CUTLASS-style fused-MoE API (vllm/_custom_ops.py:858-969)
+# ---------------------------------------------------------------------------------------------------
+def cutlass_group_gemm_supported(cuda_device_capability: int) -> bool:
+    """torch.ops._C.cutlass_group_gemm_supported (csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:131-159):
+    this build carries exactly one target, sm_100."""
+    return int(cuda_device_capability) == 100
+
+
+def _i32c(name: str, *ts) -> None:
+    for t in ts:
+        if t is not None and (t.dtype != torch.int32 or not t.is_contiguous()):
+            raise RuntimeError(f"{name}: index tensors must be contiguous int32")
+
+
+def get_cutlass_moe_mm_data(topk_ids: torch.Tensor, expert_offsets: torch.Tensor, problem_sizes1: torch.Tensor,
+                            problem_sizes2: torch.Tensor, input_permutation: torch.Tensor,
+                            output_permutation: torch.Tensor, num_experts: int, n: int, k: int,
+                            blockscale_offsets: Optional[torch.Tensor] = None) -> None:
+    """torch.ops._C.get_cutlass_moe_mm_data (vllm/_custom_ops.py:871-909; csrc/.../moe/moe_data.cu:103-159)."""
+    require_cuda(topk_ids, expert_offsets, problem_sizes1, problem_sizes2, input_permutation, output_permutation,
+                 blockscale_offsets)
+    _i32c("get_cutlass_moe_mm_data", topk_ids, expert_offsets, problem_sizes1, problem_sizes2, input_permutation,
+          output_permutation, blockscale_offsets)
+    if topk_ids.dim() != 2:
+        raise RuntimeError("get_cutlass_moe_mm_data: topk_ids must be [num_tokens, topk]")
+    if expert_offsets.numel() < num_experts + 1 or problem_sizes1.numel() < 3 * num_experts or \
+            problem_sizes2.numel() < 3 * num_experts or input_permutation.numel() < topk_ids.numel() or \
+            output_permutation.numel() < topk_ids.numel():
+        raise RuntimeError("get_cutlass_moe_mm_data: output tensors too small")
+    if blockscale_offsets is not None and blockscale_offsets.numel() < num_experts + 1:
+        raise RuntimeError("get_cutlass_moe_mm_data: blockscale_offsets too small")
+    with _device_of(topk_ids):
+        check(load().vb200_get_cutlass_moe_mm_data(
+            ptr(topk_ids), topk_ids.size(0), topk_ids.size(1), ptr(expert_offsets), ptr(problem_sizes1),
+            ptr(problem_sizes2), ptr(input_permutation), ptr(output_permutation), num_experts, n, k,
+            ptr(blockscale_offsets), stream()))
+
+
+def get_cutlass_pplx_moe_mm_data(expert_offsets: torch.Tensor, problem_sizes1: torch.Tensor,
+                                 problem_sizes2: torch.Tensor, expert_num_tokens: torch.Tensor,
+                                 num_local_experts: int, padded_m: int, n: int, k: int) -> None:
+    """torch.ops._C.get_cutlass_pplx_moe_mm_data (vllm/_custom_ops.py:925-946; moe_data.cu:161-195)."""
+    require_cuda(expert_offsets, problem_sizes1, problem_sizes2, expert_num_tokens)
+    _i32c("get_cutlass_pplx_moe_mm_data", expert_offsets, problem_sizes1, problem_sizes2, expert_num_tokens)
+    with _device_of(expert_offsets):
+        check(load().vb200_get_cutlass_pplx_moe_mm_data(
+            ptr(expert_offsets), ptr(problem_sizes1), ptr(problem_sizes2), ptr(expert_num_tokens),
+            num_local_experts, padded_m, n, k, stream()))
+
+
+def shuffle_rows(input_tensor: torch.Tensor, dst2src_map: torch.Tensor) -> torch.Tensor:
+    """vllm/_custom_ops.py:912-922: output[r] = input[dst2src_map[r]] (allocates the output like the reference)."""
+    require_cuda(input_tensor, dst2src_map)
+    _i32c("shuffle_rows", dst2src_map)
+    if input_tensor.dim() != 2 or not input_tensor.is_contiguous():
+        raise RuntimeError("shuffle_rows: input must be a contiguous 2-D tensor")
+    out = torch.empty((dst2src_map.shape[0], input_tensor.shape[1]), device=input_tensor.device,
+                      dtype=input_tensor.dtype)
+    with _device_of(input_tensor):
+        check(load().vb200_shuffle_rows(ptr(out), ptr(input_tensor), ptr(dst2src_map), out.size(0),
+                                        input_tensor.size(0), input_tensor.size(1) * input_tensor.element_size(),
+                                        stream()))
+    return out
+
+
+def cutlass_moe_mm(out_tensors: torch.Tensor, a_tensors: torch.Tensor, b_tensors: torch.Tensor,
+                   a_scales: torch.Tensor, b_scales: torch.Tensor, expert_offsets: torch.Tensor,
+                   problem_sizes: torch.Tensor, a_strides: torch.Tensor, b_strides: torch.Tensor,
+                   c_strides: torch.Tensor, per_act_token: bool, per_out_ch: bool) -> None:
+    """torch.ops._C.cutlass_moe_mm (vllm/_custom_ops.py:949-969; scaled_mm_entry.cu:242-270): for each expert e,
+    out[off_e:off_e+m_e] = (a[off_e:off_e+m_e] @ b[e].T) * a_scale * b_scale.  b_tensors [E, N, K] (K contiguous)."""
+    require_cuda(out_tensors, a_tensors, b_tensors, a_scales, b_scales, expert_offsets, problem_sizes)
+    if a_tensors.size(0) == 0:
+        raise RuntimeError("No input A tensors provided.")
+    if b_tensors.size(0) == 0:
+        raise RuntimeError("No input B tensors provided.")
+    if out_tensors.size(0) == 0:
+        raise RuntimeError("No output tensors provided.")
+    if a_tensors.dtype != torch.float8_e4m3fn:
+        raise RuntimeError("A tensors must be of type float8_e4m3fn.")
+    if b_tensors.dtype != torch.float8_e4m3fn:
+        raise RuntimeError("B tensors must be of type float8_e4m3fn.")
+    if out_tensors.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("Invalid output type (must be float16 or bfloat16)")
+    if a_scales.dtype != torch.float32 or b_scales.dtype != torch.float32:
+        raise RuntimeError("cutlass_moe_mm: scales must be float32")
+    _i32c("cutlass_moe_mm", expert_offsets, problem_sizes)
+    E, N, K = b_tensors.shape
+    if a_tensors.dim() != 2 or a_tensors.size(1) != K or out_tensors.size(1) != N or \
+            out_tensors.size(0) != a_tensors.size(0):
+        raise RuntimeError("cutlass_moe_mm: shape mismatch between a, b and out")
+    if not (a_tensors.is_contiguous() and b_tensors.is_contiguous() and out_tensors.is_contiguous()):
+        raise RuntimeError("cutlass_moe_mm: a, b ([E, N, K]) and out must be contiguous")
+    if expert_offsets.numel() < E or problem_sizes.numel() < 3 * E:
+        raise RuntimeError("cutlass_moe_mm: expert_offsets / problem_sizes too small")
+    # get_group_starts.cuh:58-59: scale granularity is inferred from the element counts
+    per_act_token = a_scales.numel() != 1
+    per_out_ch = b_scales.numel() != E
+    if per_act_token and a_scales.numel() < a_tensors.size(0):
+        raise RuntimeError("cutlass_moe_mm: per-token a_scales need one entry per row of a")
+    if per_out_ch and b_scales.numel() != E * N:
+        raise RuntimeError("cutlass_moe_mm: per-channel b_scales must be [E, N]")
+    with _device_of(a_tensors):
+        check(load().vb200_cutlass_moe_mm(
+            ptr(out_tensors), ptr(a_tensors), ptr(b_tensors), ptr(a_scales.contiguous()), ptr(b_scales.contiguous()),
+            ptr(expert_offsets), ptr(problem_sizes), a_tensors.size(0), E, N, K, int(per_act_token),
+            int(per_out_ch), dtype_enum(out_tensors.dtype), stream()))
+
+
+
 # ------------------------------------------------------------------------------------------------
 # per-token glue between the contractions  (reference: vllm/_custom_ops.py:248-281, 368-384)
 # ------------------------------------------------------------------------------------------------

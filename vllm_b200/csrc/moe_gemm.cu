@@ -42,6 +42,11 @@ struct MoeParams {
   int num_valid_tokens, top_k, E, N, K, block_m;
   int a_per_token, b_per_channel;
   int stages, num_kb, tmem_cols;
+  // ragged ("CUTLASS-style") mode: experts own contiguous row ranges of A / C given by expert_offsets and
+  // problem_sizes (csrc/quantization/cutlass_w8a8/moe/get_group_starts.cuh:11-31); no sorted_token_ids
+  const int32_t* expert_offsets;   // [E] first row of expert e
+  const int32_t* problem_sizes;    // [E, 3] = (m_e, N, K), or (N, m_e, K) when the producer swapped A/B
+  int ragged;
 };
 
 // A_sorted[r, :] = A[sorted_token_ids[r] / top_k, :] for valid r < num_tokens_post_pad (16-byte
@@ -82,15 +87,38 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
   const int lane = threadIdx.x & 31;
   const int n_tile = blockIdx.x;
   const int pblk = blockIdx.y;
-  const int row0 = pblk * p.block_m;
-  if (row0 >= *p.num_tokens_post_pad) return;  // uniform across the CTA
-  const int expert = p.expert_ids[pblk];
   const int n0 = n_tile * kMoeBlockN;
-
-  // ---- block metadata: token ids, valid count -----------------------------------------------------
-  if (threadIdx.x == 0) *s_nvalid = 0;
-  __syncthreads();
-  {
+  int row0, expert;
+  if (p.ragged) {
+    // linear M-block id -> (expert, block inside the expert's row range): experts are walked in order, each owning
+    // ceil(m_e / block_m) blocks; the walk is E <= 1024 L2-resident loads by one thread
+    if (threadIdx.x == 0) {
+      int e = 0, blk = pblk, m_e = 0;
+      for (; e < p.E; ++e) {
+        // one of the first two entries is N, the other m_e (moe_data.cu:30-44 writes either order)
+        const int s0 = p.problem_sizes[e * 3], s1 = p.problem_sizes[e * 3 + 1];
+        m_e = s1 == p.N ? s0 : s1;
+        const int nb = (m_e + p.block_m - 1) / p.block_m;
+        if (blk < nb) break;
+        blk -= nb;
+      }
+      s_nvalid[1] = e < p.E ? e : -1;
+      s_nvalid[2] = e < p.E ? p.expert_offsets[e] + blk * p.block_m : 0;
+      s_nvalid[0] = e < p.E ? min(p.block_m, m_e - blk * p.block_m) : 0;
+    }
+    __syncthreads();
+    expert = s_nvalid[1];
+    row0 = s_nvalid[2];
+    const int nv = s_nvalid[0];
+    if (nv <= 0) return;  // uniform across the CTA
+    for (int i = threadIdx.x; i < p.block_m; i += kMoeThreads) s_tok[i] = i < nv ? row0 + i : -1;
+  } else {
+    row0 = pblk * p.block_m;
+    if (row0 >= *p.num_tokens_post_pad) return;  // uniform across the CTA
+    expert = p.expert_ids[pblk];
+    // ---- block metadata: token ids, valid count ---------------------------------------------------
+    if (threadIdx.x == 0) *s_nvalid = 0;
+    __syncthreads();
     int cnt = 0;
     for (int i = threadIdx.x; i < p.block_m; i += kMoeThreads) {
       const int tok = p.sorted_token_ids[row0 + i];
@@ -256,6 +284,41 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
 
 using namespace vb200;
 
+// stage count / TMEM columns / launch shared by the two entry points
+static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap& ta, int m_blocks,
+                           int out_dtype, cudaStream_t stream) {
+  const int N = p.N, K = p.K, block_m = p.block_m;
+  p.num_kb = (K + kMoeBlockK - 1) / kMoeBlockK;
+  const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
+  const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
+  // two CTAs per SM when the stages fit in half of the shared memory, else one
+  int budget = (227 * 1024) / 2 - 1024 - meta;
+  int stages = budget / stage_bytes;
+  if (stages < 3) {
+    budget = 227 * 1024 - 1024 - meta;
+    stages = budget / stage_bytes;
+  }
+  if (stages > kMoeMaxStages) stages = kMoeMaxStages;
+  if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
+  p.stages = stages;
+  int cols = 32;
+  while (cols < block_m) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
+  dim3 grid((N + kMoeBlockN - 1) / kMoeBlockN, m_blocks);
+  if (out_dtype == VB200_BF16) {
+    auto kern = moe_grouped_gemm_kernel<__nv_bfloat16>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+  } else {
+    auto kern = moe_grouped_gemm_kernel<__half>;
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+  }
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" size_t vb200_moe_grouped_gemm_workspace_size(int sorted_capacity, int K) {
   if (sorted_capacity <= 0 || K <= 0) return 0;
   // gathered activations + one extra M-block of slack so a TMA box never leaves the allocation
@@ -315,33 +378,58 @@ extern "C" int vb200_moe_grouped_gemm_fp8(
   p.block_m = block_m;
   p.a_per_token = a_scales_per_token ? 1 : 0;
   p.b_per_channel = b_scales_per_channel ? 1 : 0;
-  p.num_kb = (K + kMoeBlockK - 1) / kMoeBlockK;
-  const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
-  const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
-  // two CTAs per SM when the stages fit in half of the shared memory, else one
-  int budget = (227 * 1024) / 2 - 1024 - meta;
-  int stages = budget / stage_bytes;
-  if (stages < 3) {
-    budget = 227 * 1024 - 1024 - meta;
-    stages = budget / stage_bytes;
-  }
-  if (stages > kMoeMaxStages) stages = kMoeMaxStages;
-  if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
-  p.stages = stages;
-  int cols = 32;
-  while (cols < block_m) cols <<= 1;
-  p.tmem_cols = cols;
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
-  dim3 grid((N + kMoeBlockN - 1) / kMoeBlockN, m_blocks);
-  if (out_dtype == VB200_BF16) {
-    auto kern = moe_grouped_gemm_kernel<__nv_bfloat16>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
-  } else {
-    auto kern = moe_grouped_gemm_kernel<__half>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
-  }
-  VB_LAUNCH_CHECK();
-  return 0;
+  p.expert_offsets = nullptr;
+  p.problem_sizes = nullptr;
+  p.ragged = 0;
+  return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
+}
+
+
+// cutlass_moe_mm: csrc/quantization/cutlass_w8a8/scaled_mm_entry.cu:242-270 (sm100:
+// moe/grouped_mm_c3x_sm100.cu:64-140; pointer arrays moe/get_group_starts.cuh:11-31).  Expert e multiplies the
+// rows [expert_offsets[e], +m_e) of A with its own weight matrix; here that is the same tcgen05 kernel as
+// fused_experts' grouped GEMM in ragged mode: no gather, no pointer arrays, one launch.
+extern "C" int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, const float* a_scales,
+                                    const float* b_scales, const int32_t* expert_offsets,
+                                    const int32_t* problem_sizes, int num_rows, int E, int N, int K,
+                                    int per_act_token, int per_out_ch, int out_dtype,
+                                    vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(out_dtype == VB200_BF16 || out_dtype == VB200_F16,
+           "cutlass_moe_mm: Invalid output type (must be float16 or bfloat16)");
+  VB_CHECK(num_rows > 0, "cutlass_moe_mm: No input A tensors provided.");
+  VB_CHECK(E > 0 && N > 0, "cutlass_moe_mm: No input B tensors provided.");
+  VB_CHECK(K > 0 && K % 16 == 0, "cutlass_moe_mm: K (%d) must be a positive multiple of 16", K);
+  VB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0,
+           "cutlass_moe_mm: A and B must be 16-byte aligned");
+  // rows per M-block: about twice the mean rows per expert (skewed routing then still reads an expert's weights
+  // once or twice), multiple of 16
+  int block_m = (2 * ((num_rows + E - 1) / E) + 15) & ~15;
+  if (block_m < 16) block_m = 16;
+  if (block_m > kMoeMaxBlockM) block_m = kMoeMaxBlockM;
+  const int m_blocks = E + num_rows / block_m;  // >= sum_e ceil(m_e / block_m)
+  CUtensorMap tw, ta;
+  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)K, (uint64_t)K, kMoeBlockN)) return 1;
+  // rows past num_rows are filled with zeros by the TMA unit (and never stored)
+  if (tc::make_tmap_2d_u8(&ta, a, (uint64_t)num_rows, (uint64_t)K, (uint64_t)K, (uint32_t)block_m)) return 1;
+  MoeParams p;
+  p.c = out;
+  p.a_scales = a_scales;
+  p.b_scales = b_scales;
+  p.topk_weights = nullptr;
+  p.sorted_token_ids = nullptr;
+  p.expert_ids = nullptr;
+  p.num_tokens_post_pad = nullptr;
+  p.num_valid_tokens = num_rows;
+  p.top_k = 1;
+  p.E = E;
+  p.N = N;
+  p.K = K;
+  p.block_m = block_m;
+  p.a_per_token = per_act_token ? 1 : 0;
+  p.b_per_channel = per_out_ch ? 1 : 0;
+  p.expert_offsets = expert_offsets;
+  p.problem_sizes = problem_sizes;
+  p.ragged = 1;
+  return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
 }

@@ -274,6 +274,58 @@ void moe_align_block_size(Tensor topk_ids, int64_t num_experts, int64_t block_si
                                       num_tokens_post_pad.data_ptr<int32_t>(), nullptr, 0, stream_of(topk_ids)));
 }
 
+// ---- CUTLASS-style fused-MoE API (csrc/ops.h:237-262, csrc/moe/moe_ops.h shuffle_rows) ----
+bool cutlass_group_gemm_supported(int64_t cuda_device_capability) { return cuda_device_capability == 100; }
+void cutlass_moe_mm(Tensor& out_tensors, const Tensor& a_tensors, const Tensor& b_tensors, const Tensor& a_scales,
+                    const Tensor& b_scales, const Tensor& expert_offsets, const Tensor& problem_sizes,
+                    const Tensor& a_strides, const Tensor& b_strides, const Tensor& c_strides, bool per_act_token,
+                    bool per_out_ch) {
+  (void)a_strides; (void)b_strides; (void)c_strides; (void)per_act_token; (void)per_out_ch;
+  TORCH_CHECK(a_tensors.size(0) > 0, "No input A tensors provided.");
+  TORCH_CHECK(b_tensors.size(0) > 0, "No input B tensors provided.");
+  TORCH_CHECK(out_tensors.size(0) > 0, "No output tensors provided.");
+  TORCH_CHECK(a_tensors.dtype() == at::kFloat8_e4m3fn, "A tensors must be of type float8_e4m3fn.");
+  TORCH_CHECK(b_tensors.dtype() == at::kFloat8_e4m3fn, "B tensors must be of type float8_e4m3fn.");
+  TORCH_CHECK(a_tensors.is_contiguous() && b_tensors.is_contiguous() && out_tensors.is_contiguous());
+  const int64_t E = b_tensors.size(0), N = b_tensors.size(1), K = b_tensors.size(2);
+  TORCH_CHECK(a_tensors.size(1) == K && out_tensors.size(1) == N && out_tensors.size(0) == a_tensors.size(0));
+  const at::cuda::OptionalCUDAGuard guard(device_of(a_tensors));
+  // scale granularity from the element counts (moe/get_group_starts.cuh:58-59)
+  vb_check(vb200_cutlass_moe_mm(out_tensors.data_ptr(), a_tensors.const_data_ptr(), b_tensors.const_data_ptr(),
+                                a_scales.const_data_ptr<float>(), b_scales.const_data_ptr<float>(),
+                                expert_offsets.const_data_ptr<int32_t>(), problem_sizes.const_data_ptr<int32_t>(),
+                                a_tensors.size(0), E, N, K, a_scales.numel() != 1, b_scales.numel() != E,
+                                dt(out_tensors), stream_of(a_tensors)));
+}
+void get_cutlass_moe_mm_data(const Tensor& topk_ids, Tensor& expert_offsets, Tensor& problem_sizes1,
+                             Tensor& problem_sizes2, Tensor& input_permutation, Tensor& output_permutation,
+                             int64_t num_experts, int64_t n, int64_t k, const OptTensor& blockscale_offsets) {
+  TORCH_CHECK(topk_ids.dtype() == at::kInt && topk_ids.dim() == 2 && topk_ids.is_contiguous());
+  const at::cuda::OptionalCUDAGuard guard(device_of(topk_ids));
+  vb_check(vb200_get_cutlass_moe_mm_data(
+      topk_ids.const_data_ptr<int32_t>(), topk_ids.size(0), topk_ids.size(1), expert_offsets.data_ptr<int32_t>(),
+      problem_sizes1.data_ptr<int32_t>(), problem_sizes2.data_ptr<int32_t>(), input_permutation.data_ptr<int32_t>(),
+      output_permutation.data_ptr<int32_t>(), num_experts, n, k,
+      blockscale_offsets.has_value() ? blockscale_offsets->data_ptr<int32_t>() : nullptr, stream_of(topk_ids)));
+}
+void get_cutlass_pplx_moe_mm_data(Tensor& expert_offsets, Tensor& problem_sizes1, Tensor& problem_sizes2,
+                                  const Tensor& expert_num_tokens, int64_t num_local_experts, int64_t padded_m,
+                                  int64_t n, int64_t k) {
+  const at::cuda::OptionalCUDAGuard guard(device_of(expert_offsets));
+  vb_check(vb200_get_cutlass_pplx_moe_mm_data(expert_offsets.data_ptr<int32_t>(), problem_sizes1.data_ptr<int32_t>(),
+                                              problem_sizes2.data_ptr<int32_t>(),
+                                              expert_num_tokens.const_data_ptr<int32_t>(), num_local_experts,
+                                              padded_m, n, k, stream_of(expert_offsets)));
+}
+void shuffle_rows(const Tensor& input_tensor, const Tensor& dst2src_map, Tensor& output_tensor) {
+  TORCH_CHECK(input_tensor.dim() == 2 && input_tensor.is_contiguous() && output_tensor.is_contiguous());
+  TORCH_CHECK(dst2src_map.dtype() == at::kInt && dst2src_map.is_contiguous());
+  const at::cuda::OptionalCUDAGuard guard(device_of(input_tensor));
+  vb_check(vb200_shuffle_rows(output_tensor.data_ptr(), input_tensor.const_data_ptr(),
+                              dst2src_map.const_data_ptr<int32_t>(), dst2src_map.size(0), input_tensor.size(0),
+                              input_tensor.size(1) * input_tensor.element_size(), stream_of(input_tensor)));
+}
+
 }  // namespace
 
 #define VB_CAT_(a, b) a##b
@@ -318,6 +370,22 @@ TORCH_LIBRARY(VB200_LIB_C, ops) {
   ops.impl("dynamic_scaled_fp8_quant", torch::kCUDA, &dynamic_scaled_fp8_quant);
   ops.def("dynamic_per_token_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale, Tensor? scale_ub) -> ()");
   ops.impl("dynamic_per_token_scaled_fp8_quant", torch::kCUDA, &dynamic_per_token_scaled_fp8_quant);
+  ops.def("cutlass_group_gemm_supported(int cuda_device_capability) -> bool");
+  ops.impl("cutlass_group_gemm_supported", &cutlass_group_gemm_supported);
+  ops.def(
+      "cutlass_moe_mm(Tensor! out_tensors, Tensor a_tensors, Tensor b_tensors, Tensor a_scales, Tensor b_scales,"
+      " Tensor expert_offsets, Tensor problem_sizes, Tensor a_strides, Tensor b_strides, Tensor c_strides,"
+      " bool per_act_token, bool per_out_ch) -> ()");
+  ops.impl("cutlass_moe_mm", torch::kCUDA, &cutlass_moe_mm);
+  ops.def(
+      "get_cutlass_moe_mm_data(Tensor topk_ids, Tensor! expert_offsets, Tensor! problem_sizes1,"
+      " Tensor! problem_sizes2, Tensor! input_permutation, Tensor! output_permutation, int num_experts, int n,"
+      " int k, Tensor? blockscale_offsets) -> ()");
+  ops.impl("get_cutlass_moe_mm_data", torch::kCUDA, &get_cutlass_moe_mm_data);
+  ops.def(
+      "get_cutlass_pplx_moe_mm_data(Tensor! expert_offsets, Tensor! problem_sizes1, Tensor! problem_sizes2,"
+      " Tensor expert_num_tokens, int num_local_experts, int padded_m, int n, int k) -> ()");
+  ops.impl("get_cutlass_pplx_moe_mm_data", torch::kCUDA, &get_cutlass_pplx_moe_mm_data);
 }
 
 TORCH_LIBRARY(VB200_LIB_CACHE, ops) {
@@ -344,4 +412,6 @@ TORCH_LIBRARY(VB200_LIB_MOE, ops) {
       "moe_align_block_size(Tensor topk_ids, int num_experts, int block_size, Tensor! sorted_token_ids,"
       " Tensor! experts_ids, Tensor! num_tokens_post_pad) -> ()");
   ops.impl("moe_align_block_size", torch::kCUDA, &moe_align_block_size);
+  ops.def("shuffle_rows(Tensor input_tensor, Tensor dst2src_map, Tensor! output_tensor) -> ()");
+  ops.impl("shuffle_rows", torch::kCUDA, &shuffle_rows);
 }
