@@ -280,6 +280,23 @@ def attention_algorithmic_bytes(batch, ctx, H, Hkv, D, cache_bytes, q_bytes=2, b
     return kv + qo + bt
 
 
+def _finish_multi_rank(world):
+    """N > 1: leave without tearing NCCL down.  The captured CUDA graph holds NCCL kernels; destroying the
+    communicator under it (explicitly or from interpreter shutdown) can block for minutes waiting on the peer, which
+    keeps torchrun -- and the box -- alive long after the JSON line is out.  All ranks meet at a barrier (so nobody
+    exits while a peer still needs the communicator), flush, and exit 0 directly."""
+    if world <= 1:
+        return
+    import torch.distributed as dist
+    try:
+        dist.barrier()
+        torch.cuda.synchronize()
+    finally:
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
+
+
 def run_gpu_arm(args, rank, world, local_rank):
     import torch.distributed as dist
     from vllm_b200 import _custom_ops as ops
@@ -412,8 +429,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     peak, peak_src = peaks()
     achieved = algo / attn_s / 1e9
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish_multi_rank(world)
         return
     tps = batch / (ms * 1e-3)
     line = {
@@ -447,6 +463,7 @@ def run_gpu_arm(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"failed: {type(ex).__name__}: {ex}"}
     print(json.dumps(line), flush=True)
+    _finish_multi_rank(world)
     if world > 1:
         dist.destroy_process_group()
 

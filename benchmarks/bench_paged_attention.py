@@ -48,7 +48,10 @@ def make(cfg, dev="cuda"):
         vc = torch.empty(nb, Hkv, D, bs, dtype=torch.bfloat16, device=dev).normal_()
         sc = 1.0
     q = (torch.randn(S, H, D, device=dev) * 0.3).bfloat16()
-    bt = torch.randperm(nb, device=dev)[: S * blocks_per_seq].to(torch.int32).reshape(S, blocks_per_seq)
+    if os.environ.get("PA_SEQ_BLOCKS") == "1":   # experiment: physically consecutive blocks per sequence
+        bt = torch.arange(S * blocks_per_seq, device=dev, dtype=torch.int32).reshape(S, blocks_per_seq)
+    else:
+        bt = torch.randperm(nb, device=dev)[: S * blocks_per_seq].to(torch.int32).reshape(S, blocks_per_seq)
     if cfg.get("ragged"):
         sl = torch.randint(ctx // 2 + 1, ctx + 1, (S,), dtype=torch.int32, device=dev)
     else:

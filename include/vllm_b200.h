@@ -316,6 +316,27 @@ int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, const float* a
                          const int32_t* problem_sizes, int num_rows, int E, int N, int K,
                          int per_act_token, int per_out_ch, int out_dtype, vb200_stream_t stream);
 
+/* ---- callers either side of the path --------------------------------- */
+
+/* advance_step_flashattn: csrc/prepare_inputs/advance_step.cu:176-232 (kernel :13-65), schema
+ * csrc/torch_bindings.cpp:150-155.  For i < num_queries: input_tokens[i] = sampled_token_ids[i];
+ * seq_lens[i] += 1; input_positions[i] = seq_lens[i] - 1; slot_mapping[i] = block_tables[i][pos / block_size] *
+ * block_size + pos % block_size.  Rows num_queries..num_seqs-1 (CUDA-graph padding): tokens/positions 0, slot -1.
+ * input_tokens / input_positions / slot_mapping / sampled_token_ids int64; seq_lens / block_tables int32;
+ * block_tables_stride in elements. */
+int vb200_advance_step_flashattn(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                                 const int64_t* sampled_token_ids, int64_t* input_positions,
+                                 int32_t* seq_lens, int64_t* slot_mapping, const int32_t* block_tables,
+                                 int64_t block_tables_stride, vb200_stream_t stream);
+
+/* merge_attn_states: csrc/attention/merge_attn_states.cu:121-178 (kernel :12-89), schema
+ * csrc/torch_bindings.cpp:75-83.  output/prefix_output/suffix_output [num_tokens, num_heads, head_size] of
+ * `dtype` (F32/F16/BF16), contiguous; *_lse fp32 [num_heads, num_tokens]; output_lse may be NULL.
+ * out = p * e^(p_lse-m)/(e^(p_lse-m)+e^(s_lse-m)) + s * (...), infinities in an lse count as -inf. */
+int vb200_merge_attn_states(void* output, float* output_lse, const void* prefix_output,
+                            const float* prefix_lse, const void* suffix_output, const float* suffix_lse,
+                            int num_tokens, int num_heads, int head_size, int dtype, vb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -38,7 +38,7 @@ def _check(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0, scale=1
     assert rel <= 2 * ulp, f"max rel err vs exact-order oracle {rel}"
 
 
-@pytest.mark.parametrize("M", [1, 16, 33, 64, 128, 256, 257, 512, 1000])
+@pytest.mark.parametrize("M", [1, 16, 33, 64, 128, 129, 200, 256, 257, 512, 1000])
 @pytest.mark.parametrize("N,K", [(128, 128), (256, 512), (4096, 4096), (6144, 4096), (1280, 8192), (4096, 14336)])
 def test_scaled_mm_shapes(M, N, K):
     if M > 300 and N * K > 4096 * 4096:

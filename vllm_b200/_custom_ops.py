@@ -640,3 +640,55 @@ def silu_and_mul_dynamic_per_token_quant(x: torch.Tensor, scale_ub: Optional[tor
         check(load().vb200_silu_and_mul_dynamic_per_token_quant(ptr(out), ptr(scales), ptr(x), ptr(scale_ub), t, d,
                                                                 dtype_enum(x.dtype), stream()))
     return out, scales
+
+
+# ---------------------------------------------------------------------------------------------------
+# callers either side of the path (vllm/_custom_ops.py:142-149, 335-346)
+# ---------------------------------------------------------------------------------------------------
+def _verify_tensor(name: str, t: torch.Tensor, size_0: int, size_1: int, dtype: torch.dtype) -> None:
+    """advance_step.cu:67-89."""
+    ok = (size_0 == -1 or t.size(0) == size_0) and (size_1 == -1 or (t.dim() > 1 and t.size(1) == size_1)) and \
+        t.is_contiguous() and t.dtype == dtype
+    if not ok:
+        raise RuntimeError(f"tensor: name = {name}, shape = {list(t.shape)} is_cont = {t.is_contiguous()}, type = "
+                           f"{t.dtype} is not as expected: shape = [{size_0}, {size_1}], type = {dtype}")
+
+
+def advance_step_flashattn(num_seqs: int, num_queries: int, block_size: int, input_tokens: torch.Tensor,
+                           sampled_token_ids: torch.Tensor, input_positions: torch.Tensor, seq_lens: torch.Tensor,
+                           slot_mapping: torch.Tensor, block_tables: torch.Tensor) -> None:
+    """torch.ops._C.advance_step_flashattn (csrc/prepare_inputs/advance_step.cu:176-232): advance the decode inputs
+    one step on the device."""
+    require_cuda(input_tokens, sampled_token_ids, input_positions, seq_lens, slot_mapping, block_tables)
+    _verify_tensor("input_tokens", input_tokens, num_seqs, -1, torch.int64)
+    _verify_tensor("sampled_token_ids", sampled_token_ids, num_queries, 1, torch.int64)
+    _verify_tensor("input_positions", input_positions, num_seqs, -1, torch.int64)
+    _verify_tensor("seq_lens", seq_lens, num_seqs, -1, torch.int32)
+    _verify_tensor("slot_mapping", slot_mapping, num_seqs, -1, torch.int64)
+    _verify_tensor("block_tables", block_tables, num_seqs, -1, torch.int32)
+    with _device_of(sampled_token_ids):
+        check(load().vb200_advance_step_flashattn(
+            num_seqs, num_queries, block_size, ptr(input_tokens), ptr(sampled_token_ids), ptr(input_positions),
+            ptr(seq_lens), ptr(slot_mapping), ptr(block_tables), block_tables.stride(0), stream()))
+
+
+def merge_attn_states(output: torch.Tensor, prefix_output: torch.Tensor, prefix_lse: torch.Tensor,
+                      suffix_output: torch.Tensor, suffix_lse: torch.Tensor,
+                      output_lse: Optional[torch.Tensor] = None) -> None:
+    """torch.ops._C.merge_attn_states (vllm/_custom_ops.py:142-149; csrc/attention/merge_attn_states.cu:121-178)."""
+    require_cuda(output, prefix_output, prefix_lse, suffix_output, suffix_lse, output_lse)
+    if output.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+        raise RuntimeError(f"Unsupported data type of O: {output.dtype}")
+    if output.dim() != 3 or prefix_output.shape != output.shape or suffix_output.shape != output.shape:
+        raise RuntimeError("merge_attn_states: outputs must be [num_tokens, num_heads, head_size]")
+    t, h, d = output.shape
+    for x in (output, prefix_output, suffix_output):
+        if x.dtype != output.dtype or not x.is_contiguous():
+            raise RuntimeError("merge_attn_states: outputs must be contiguous and of one dtype")
+    for x in (prefix_lse, suffix_lse, output_lse):
+        if x is not None and (x.dtype != torch.float32 or tuple(x.shape) != (h, t) or not x.is_contiguous()):
+            raise RuntimeError("merge_attn_states: lse tensors must be contiguous fp32 [num_heads, num_tokens]")
+    with _device_of(output):
+        check(load().vb200_merge_attn_states(ptr(output), ptr(output_lse), ptr(prefix_output), ptr(prefix_lse),
+                                             ptr(suffix_output), ptr(suffix_lse), t, h, d, dtype_enum(output.dtype),
+                                             stream()))

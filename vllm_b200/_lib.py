@@ -83,6 +83,8 @@ SIGNATURES = {
     "vb200_get_cutlass_moe_mm_data": (c_int, [_P, c_int, c_int, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P]),
     "vb200_get_cutlass_pplx_moe_mm_data": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_shuffle_rows": (c_int, [_P, _P, _P, c_int, c_int, c_int64, _P]),
+    "vb200_advance_step_flashattn": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int64, _P]),
+    "vb200_merge_attn_states": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_cutlass_moe_mm": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_int, _P]),
 }

@@ -417,24 +417,55 @@ struct Plan {
   size_t smem, ws_bytes, main_bytes;
 };
 
+// Cost model (microseconds) of one (token tiles, K splits) choice for a problem whose units are all co-resident
+// or run in whole rounds.  Constants are read off the per-phase trace (benchmarks/trace_scaled_mm.py,
+// profiles/r01_scaled_mm_trace_s18.txt): a CTA pulls ~90 GB/s from L2, a pair retires one 256 x 256 x 128 k-block
+// in 0.28 us, the split-K exchange (park partials in L2, wait, fetch, store) costs ~9 us per 256 token columns and
+// the plain epilogue ~2.6 us, HBM streams the weights at ~6.4 TB/s.
+static float plan_cost(int tok_tile, int tiles, int splits, int num_kb, int max_pairs, double w_bytes) {
+  const int kbps = ceil_div(num_kb, splits);
+  const int rounds = ceil_div(tiles * splits, max_pairs);
+  const float feed = kbps * (kWTileBytes + tok_tile / 2 * kBlockK) / 90e3f;
+  const float mma = kbps * tok_tile * 0.0011f;
+  const float hbm = (float)(w_bytes / 6.4e6);
+  const float main_us = fmaxf(rounds * fmaxf(feed, mma), hbm);
+  return main_us + (splits > 1 ? 0.035f : 0.010f) * tok_tile;
+}
+
 static Plan make_plan(int M, int N, int K) {
   Plan g;
   g.m_tiles = ceil_div(M, kMaxTokTile);
-  g.tok_tile = (ceil_div(M, g.m_tiles) + 15) / 16 * 16;
   g.n_ptiles = ceil_div(N, kPairRows);
-  g.tiles = g.m_tiles * g.n_ptiles;
   g.num_kb = ceil_div(K, kBlockK);
+  const int max_pairs = num_sms() / 2;
+  // split-K only when every unit gets its own CTA pair (co-residency makes the in-kernel wait safe)
+  int splits = 1;
+  for (int s = 2; s <= kMaxSplits; ++s)
+    if (g.m_tiles * g.n_ptiles * s <= max_pairs && g.num_kb / s >= 4) splits = s;
+  if (M > 128 && M <= kMaxTokTile && 2 * g.n_ptiles <= max_pairs) {
+    // one token tile of 129..256 columns: splitting the TOKENS over two pairs (weights re-read from L2, no
+    // partial-sum traffic) can beat splitting K, whose exchange moves M x N x 4 bytes per slice through L2
+    const double w_bytes = (double)N * K;
+    float best = plan_cost((M + 15) / 16 * 16, g.n_ptiles, splits, g.num_kb, max_pairs, w_bytes);
+    const int tok2 = (ceil_div(M, 2) + 15) / 16 * 16;
+    for (int s = 1; s <= kMaxSplits; ++s) {
+      if (s > 1 && !(2 * g.n_ptiles * s <= max_pairs && g.num_kb / s >= 4)) break;
+      const float c = plan_cost(tok2, 2 * g.n_ptiles, s, g.num_kb, max_pairs, w_bytes);
+      if (c < best * 0.95f) {
+        best = c;
+        g.m_tiles = 2;
+        splits = s;
+      }
+    }
+  }
+  g.tok_tile = (ceil_div(M, g.m_tiles) + 15) / 16 * 16;
+  g.tiles = g.m_tiles * g.n_ptiles;
   const int a_bytes = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
   g.stage_bytes = kWTileBytes + a_bytes;
   const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
   const int budget = 227 * 1024 - 1024 /*alignment slack*/ - tail;
   g.stages = budget / g.stage_bytes;
   if (g.stages > kMaxStages) g.stages = kMaxStages;
-  const int max_pairs = num_sms() / 2;
-  // split-K only when every unit gets its own CTA pair (co-residency makes the in-kernel wait safe)
-  int splits = 1;
-  for (int s = 2; s <= kMaxSplits; ++s)
-    if (g.tiles * s <= max_pairs && g.num_kb / s >= 4) splits = s;
   g.kb_per_split = ceil_div(g.num_kb, splits);
   g.splits = ceil_div(g.num_kb, g.kb_per_split);
   g.col_chunk = (ceil_div(g.tok_tile, g.splits) + 15) / 16 * 16;

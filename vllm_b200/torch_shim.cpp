@@ -326,6 +326,33 @@ void shuffle_rows(const Tensor& input_tensor, const Tensor& dst2src_map, Tensor&
                               input_tensor.size(1) * input_tensor.element_size(), stream_of(input_tensor)));
 }
 
+// ---- callers either side of the path (csrc/ops.h advance_step_flashattn, merge_attn_states) ----
+void advance_step_flashattn(int64_t num_seqs, int64_t num_queries, int64_t block_size, Tensor& input_tokens,
+                            Tensor& sampled_token_ids, Tensor& input_positions, Tensor& seq_lens,
+                            Tensor& slot_mapping, Tensor& block_tables) {
+  TORCH_CHECK(input_tokens.dtype() == at::kLong && sampled_token_ids.dtype() == at::kLong &&
+              input_positions.dtype() == at::kLong && slot_mapping.dtype() == at::kLong &&
+              seq_lens.dtype() == at::kInt && block_tables.dtype() == at::kInt);
+  TORCH_CHECK(input_tokens.size(0) == num_seqs && sampled_token_ids.size(0) == num_queries &&
+              seq_lens.size(0) == num_seqs && slot_mapping.size(0) == num_seqs && block_tables.size(0) == num_seqs);
+  const at::cuda::OptionalCUDAGuard guard(device_of(sampled_token_ids));
+  vb_check(vb200_advance_step_flashattn(num_seqs, num_queries, block_size, input_tokens.data_ptr<int64_t>(),
+                                        sampled_token_ids.const_data_ptr<int64_t>(),
+                                        input_positions.data_ptr<int64_t>(), seq_lens.data_ptr<int32_t>(),
+                                        slot_mapping.data_ptr<int64_t>(), block_tables.const_data_ptr<int32_t>(),
+                                        block_tables.stride(0), stream_of(sampled_token_ids)));
+}
+void merge_attn_states(Tensor& output, OptTensor output_lse, const Tensor& prefix_output, const Tensor& prefix_lse,
+                       const Tensor& suffix_output, const Tensor& suffix_lse) {
+  TORCH_CHECK(output.dim() == 3 && output.is_contiguous() && prefix_output.is_contiguous() &&
+              suffix_output.is_contiguous());
+  const at::cuda::OptionalCUDAGuard guard(device_of(output));
+  vb_check(vb200_merge_attn_states(output.data_ptr(), output_lse.has_value() ? output_lse->data_ptr<float>() : nullptr,
+                                   prefix_output.const_data_ptr(), prefix_lse.const_data_ptr<float>(),
+                                   suffix_output.const_data_ptr(), suffix_lse.const_data_ptr<float>(), output.size(0),
+                                   output.size(1), output.size(2), dt(output), stream_of(output)));
+}
+
 }  // namespace
 
 #define VB_CAT_(a, b) a##b
@@ -370,6 +397,15 @@ TORCH_LIBRARY(VB200_LIB_C, ops) {
   ops.impl("dynamic_scaled_fp8_quant", torch::kCUDA, &dynamic_scaled_fp8_quant);
   ops.def("dynamic_per_token_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale, Tensor? scale_ub) -> ()");
   ops.impl("dynamic_per_token_scaled_fp8_quant", torch::kCUDA, &dynamic_per_token_scaled_fp8_quant);
+  ops.def(
+      "advance_step_flashattn(int num_seqs, int num_queries, int block_size, Tensor! input_tokens,"
+      " Tensor sampled_token_ids, Tensor! input_positions, Tensor! seq_lens, Tensor! slot_mapping,"
+      " Tensor block_tables) -> ()");
+  ops.impl("advance_step_flashattn", torch::kCUDA, &advance_step_flashattn);
+  ops.def(
+      "merge_attn_states(Tensor! output, Tensor!? output_lse, Tensor prefix_output, Tensor prefix_lse,"
+      " Tensor suffix_output, Tensor suffix_lse) -> ()");
+  ops.impl("merge_attn_states", torch::kCUDA, &merge_attn_states);
   ops.def("cutlass_group_gemm_supported(int cuda_device_capability) -> bool");
   ops.impl("cutlass_group_gemm_supported", &cutlass_group_gemm_supported);
   ops.def(
