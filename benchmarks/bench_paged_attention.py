@@ -70,19 +70,24 @@ def algo_bytes(cfg, sl):
 
 
 def timeit(fn, iters, warmup=3):
+    """(mean, best-batch mean) seconds per call.  Calls are enqueued back to back between two events, `iters` per
+    batch, 3 batches: a per-call event pair with a host sync in between would add the host's launch path (ctypes +
+    allocator, ~20-40 us) to every sample, which is comparable to the kernel itself at the smaller shapes.  The KV
+    working set of every config is larger than L2 (126 MB), so consecutive calls still stream from HBM."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
-    ts = []
-    for _ in range(iters):
+    means = []
+    for _ in range(3):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        fn()
+        for _ in range(iters):
+            fn()
         b.record()
         b.synchronize()
-        ts.append(a.elapsed_time(b) * 1e-3)
-    ts.sort()
-    return ts[len(ts) // 2], ts[0]
+        means.append(a.elapsed_time(b) * 1e-3 / iters)
+    means.sort()
+    return means[1], means[0]
 
 
 def main():
