@@ -303,13 +303,16 @@ def run_gpu_arm(args, rank, world, local_rank):
     from vllm_b200 import _lib
     from vllm_b200.attention import B200PagedAttentionMetadata
     from vllm_b200.decode_step import CONFIGS, Decoder
-    from vllm_b200.distributed import init_tensor_parallel
+    from vllm_b200.distributed import init_peer_allreduce, init_tensor_parallel
     _lib.load()  # fail loudly when the CUDA library is missing
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     init_tensor_parallel()
+    # N > 1: row-parallel all-reduces go over NVLink peer memory, fused with the norm that consumes them
+    # (csrc/peer_allreduce.cu); VB200_PEER_AR=0 keeps NCCL for every all-reduce
+    peer_ar = init_peer_allreduce(dev) if world > 1 else None
     model, batch, ctx, quant, kvd = WORKLOADS[args.config]
     cfg = CONFIGS[model]
     bs = 16

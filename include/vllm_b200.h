@@ -337,6 +337,32 @@ int vb200_merge_attn_states(void* output, float* output_lse, const void* prefix_
                             const float* prefix_lse, const void* suffix_output, const float* suffix_lse,
                             int num_tokens, int num_heads, int head_size, int dtype, vb200_stream_t stream);
 
+/* ---- row-parallel all-reduce over NVLink peer memory, fused with its consumer ---- */
+
+/* The reference's analogues: csrc/custom_all_reduce.cuh:297-314 (one-shot P2P all-reduce, flag barriers :184-260)
+ * and vllm/compilation/collective_fusion.py (all-reduce + residual add + RMSNorm fusion).
+ * peer_data / peer_signals are HOST arrays of `world` device pointers: this process's mappings (CUDA IPC) of every
+ * rank's partial-sum buffer ([rows, hidden] contiguous, 16-byte aligned) and signal block
+ * (vb200_peer_allreduce_signal_bytes() bytes, zero-initialised once); entry `rank` is this rank's own.
+ *   mode 0: out = T(sum_r data_r)                                  (out: T [rows, hidden])
+ *   mode 1: + fused_add_rms_norm: residual = T(sum + residual); out = rmsnorm(residual) * weight
+ *   mode 2: + rms_norm_dynamic_per_token_quant: residual = T(sum + residual); out = fp8 [rows, hidden],
+ *           scales[rows] fp32 (scale_ub optional)                  (layernorm_utils.cuh:19-125 arithmetic)
+ * The sum is taken in rank order in fp32 on every rank (bitwise identical everywhere).  world in {2, 4, 8}; every
+ * rank must issue the same sequence of calls with the same shapes (the barrier is per CTA index). */
+size_t vb200_peer_allreduce_signal_bytes(void);
+/* Peer-visible device buffers (csrc/custom_all_reduce.cu allocate_shared_buffer_and_handle / open_mem_handle):
+ * alloc = cudaMalloc + zero fill + cudaIpcGetMemHandle (64-byte handle to send to the peers); open =
+ * cudaIpcOpenMemHandle with lazy peer access on the CALLER's current device; close / free undo them. */
+int vb200_peer_buffer_alloc(size_t bytes, void** ptr, void* handle64);
+int vb200_peer_buffer_open(const void* handle64, void** ptr);
+int vb200_peer_buffer_close(void* ptr);
+int vb200_peer_buffer_free(void* ptr);
+int vb200_peer_allreduce(int mode, void* out, const void* const* peer_data, void* const* peer_signals,
+                         int rank, int world, int rows, int hidden, int dtype, void* residual,
+                         const void* weight, float epsilon, float* scales, const float* scale_ub,
+                         vb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

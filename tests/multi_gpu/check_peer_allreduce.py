@@ -1,0 +1,185 @@
+"""Run under torchrun (>= 2 GPUs of one node): parity of the NVLink peer-memory all-reduce (csrc/peer_allreduce.cu)
+against NCCL + the unfused ops, eagerly and under CUDA-graph replay, then a tiny decode step with the fused path on
+vs off.  Exits non-zero on any mismatch.  Launched by tests/test_gpu_peer_allreduce.py and scripts/gpu_run*.sh:
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tests/multi_gpu/check_peer_allreduce.py
+"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+FP8 = torch.float8_e4m3fn
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.distributed import init_peer_allreduce, init_tensor_parallel
+    init_tensor_parallel()
+    par = init_peer_allreduce(dev)
+    assert par is not None, "peer all-reduce did not initialise"
+    fails = []
+
+    def check(name, cond):
+        if not cond:
+            fails.append(name)
+            print(f"[rank {rank}] FAIL {name}", flush=True)
+
+    gen = torch.Generator(device=dev)
+    for it, (T, H, dtype) in enumerate([(1, 256, torch.bfloat16), (256, 4096, torch.bfloat16), (37, 8192, torch.float16),
+                                        (300, 4096, torch.bfloat16), (256, 4096, torch.bfloat16), (8, 16384, torch.bfloat16)]):
+        gen.manual_seed(100 * it + rank)
+        x = torch.empty(T, H, device=dev, dtype=dtype).normal_(0, 1, generator=gen)
+        gen.manual_seed(7 + it)            # replicated tensors: same on every rank
+        res = torch.empty(T, H, device=dev, dtype=dtype).normal_(0, 1, generator=gen)
+        w = (torch.empty(H, device=dev, dtype=dtype).normal_(0, 0.1, generator=gen) + 1)
+        ref = x.clone()
+        dist.all_reduce(ref)
+        # mode 0: for 2 ranks one rounding of an exact fp32 sum == NCCL bit for bit; more ranks: fp32 rank-order sum
+        st = par.staging(T, H, dtype)
+        st.copy_(x)
+        got = par.all_reduce(st)
+        if world == 2:
+            check(f"mode0 bit-exact {T}x{H}", torch.equal(got, ref))
+        else:
+            torch.testing.assert_close(got.float(), ref.float(), rtol=1e-2, atol=2e-2)
+        # every rank holds identical bits
+        gathered = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(gathered, got)
+        check(f"mode0 identical across ranks {T}x{H}", all(torch.equal(g, gathered[0]) for g in gathered))
+        # mode 1 vs all_reduce -> fused_add_rms_norm
+        r1, r2 = res.clone(), res.clone()
+        h = got.clone()
+        ops.fused_add_rms_norm(h, r1, w, 1e-5)
+        st.copy_(x)
+        o = par.all_reduce_add_rms_norm(st, r2, w, 1e-5)
+        check(f"mode1 residual bit-exact {T}x{H}", torch.equal(r1, r2))
+        torch.testing.assert_close(o.float(), h.float(), rtol=1e-2, atol=2e-2)
+        check(f"mode1 >= 99.9% identical {T}x{H}", (o == h).float().mean().item() >= 0.999)
+        # mode 2 vs all_reduce -> rms_norm_dynamic_per_token_quant
+        r1, r2 = res.clone(), res.clone()
+        q1, s1 = ops.rms_norm_dynamic_per_token_quant(got.clone(), w, 1e-5, FP8, None, r1)
+        st.copy_(x)
+        q2, s2 = par.all_reduce_add_rms_norm_quant(st, r2, w, 1e-5)
+        check(f"mode2 residual bit-exact {T}x{H}", torch.equal(r1, r2))
+        torch.testing.assert_close(s2, s1.view_as(s2), rtol=1e-2, atol=0)
+        d1, d2 = q1.float() * s1.view(-1, 1), q2.float() * s2.view(-1, 1)
+        torch.testing.assert_close(d2, d1, rtol=0.13, atol=2e-2)      # one e4m3 step at most
+        check(f"mode2 >= 99.5% identical codes {T}x{H}", (q1.view(torch.uint8) == q2.view(torch.uint8)).float().mean().item() >= 0.995)
+    # graph replay: 3 fused all-reduces per replay, 50 replays, the input changes between replays
+    T, H = 256, 4096
+    x = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
+    w = torch.ones(H, device=dev, dtype=torch.bfloat16)
+    res = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
+    out = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
+
+    def body():
+        for _ in range(3):
+            st = par.staging(T, H, torch.bfloat16)
+            st.copy_(x)
+            out.copy_(par.all_reduce(st))
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        body()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            body()
+    torch.cuda.synchronize()
+    ok = True
+    for it in range(50):
+        gen.manual_seed(1000 + 10 * it + rank)
+        x.normal_(0, 1, generator=gen)
+        ref = x.clone()
+        dist.all_reduce(ref)
+        g.replay()
+        torch.cuda.synchronize()
+        ok = ok and (torch.equal(out, ref) if world == 2 else torch.allclose(out.float(), ref.float(), rtol=1e-2, atol=2e-2))
+    check("graph replay x50", ok)
+    # timing (CUDA graph of 20 back-to-back ops, 10 replays): NCCL all_reduce + fused_add-rmsnorm-quant kernel vs the
+    # one fused peer kernel, [256, 4096] bf16 (the Llama-3.1-8B config-3 message, 2 MiB)
+    if os.environ.get("PEER_AR_TIMING", "1") == "1":
+        xs = torch.randn(T, H, device=dev).bfloat16()
+        res2 = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
+
+        def nccl_path():
+            for _ in range(20):
+                y = xs.clone()
+                dist.all_reduce(y)
+                ops.rms_norm_dynamic_per_token_quant(y, w, 1e-5, FP8, None, res2)
+
+        def clone_only():
+            for _ in range(20):
+                xs.clone()
+
+        def peer_path():
+            for _ in range(20):
+                st = par.staging(T, H, torch.bfloat16)
+                st.copy_(xs)
+                par.all_reduce_add_rms_norm_quant(st, res2, w, 1e-5)
+        times = {}
+        for name, fn in (("copy_only", clone_only), ("nccl_plus_norm_quant", nccl_path), ("peer_fused", peer_path)):
+            with torch.cuda.stream(s):
+                fn()
+                gg = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gg, stream=s):
+                    fn()
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                gg.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            times[name] = e0.elapsed_time(e1) * 1e3 / 200
+        if rank == 0:
+            print("[timing] us per op, [256 x 4096] bf16, world %d: %s (each path includes one 2 MiB device copy)" % (
+                world, {k: round(v, 2) for k, v in times.items()}), flush=True)
+    # decode step: fused path on vs off -> same greedy tokens, close logits
+    from vllm_b200.attention import B200PagedAttentionMetadata
+    from vllm_b200.decode_step import CONFIGS, Decoder
+    from vllm_b200.distributed import communication_op as co
+    cfg = CONFIGS["tiny-llama"]
+    B, bs, ctx = 8, 16, 100
+    bps = ctx // bs + 1
+    nb = B * bps + 4
+    gcpu = torch.Generator().manual_seed(3)
+    bt = torch.randperm(nb, generator=gcpu)[:B * bps].to(torch.int32).reshape(B, bps).to(dev)
+    ids = torch.randint(0, cfg.vocab_size, (B,), generator=gcpu).to(dev)
+    sl = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    pos = (sl - 1).to(torch.int64)
+    slots = bt[torch.arange(B), (ctx - 1) // bs].to(torch.int64) * bs + (ctx - 1) % bs
+    meta = B200PagedAttentionMetadata(seq_lens_tensor=sl, max_decode_seq_len=ctx, block_tables=bt, num_decode_tokens=B,
+                                      slot_mapping=slots)
+    outs = []
+    for use in (True, False):
+        co._PEER_AR = par if use else None
+        dec = Decoder(cfg, nb, bs, "fp8", "fp8", device=dev, seed=3)
+        dec.fill_kv_cache_random(seed=5)
+        outs.append(dec.hidden_states(ids, pos, meta).float())
+    co._PEER_AR = par
+    torch.testing.assert_close(outs[0], outs[1], rtol=5e-2, atol=5e-2)
+    check("decode hidden states fused vs NCCL (mean abs diff)", (outs[0] - outs[1]).abs().mean().item() < 5e-3)
+    dist.barrier()
+    torch.cuda.synchronize()
+    print(f"[rank {rank}] peer all-reduce check: {'OK' if not fails else 'FAILED ' + str(fails)}", flush=True)
+    sys.stdout.flush()
+    os._exit(1 if fails else 0)
+
+
+if __name__ == "__main__":
+    try:
+        main()
+    except Exception:  # noqa: BLE001
+        import traceback
+        traceback.print_exc()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(2)

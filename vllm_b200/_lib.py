@@ -85,6 +85,13 @@ SIGNATURES = {
     "vb200_shuffle_rows": (c_int, [_P, _P, _P, c_int, c_int, c_int64, _P]),
     "vb200_advance_step_flashattn": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int64, _P]),
     "vb200_merge_attn_states": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
+    "vb200_peer_allreduce_signal_bytes": (c_size_t, []),
+    "vb200_peer_buffer_alloc": (c_int, [c_size_t, _P, _P]),
+    "vb200_peer_buffer_open": (c_int, [_P, _P]),
+    "vb200_peer_buffer_close": (c_int, [_P]),
+    "vb200_peer_buffer_free": (c_int, [_P]),
+    "vb200_peer_allreduce": (c_int, [c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_float, _P, _P,
+                                     _P]),
     "vb200_cutlass_moe_mm": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_int, _P]),
 }

@@ -21,8 +21,8 @@ import torch
 
 from . import _custom_ops as ops
 from .attention import B200PagedAttentionBackend, B200PagedAttentionMetadata
-from .distributed import (get_tensor_model_parallel_rank, get_tensor_model_parallel_world_size,
-                          tensor_model_parallel_all_reduce)
+from .distributed import (get_peer_allreduce, get_tensor_model_parallel_rank,
+                          get_tensor_model_parallel_world_size, tensor_model_parallel_all_reduce)
 
 FP8 = torch.float8_e4m3fn
 
@@ -141,14 +141,31 @@ class DecoderLayer:
                                    0.05 if kv_cache_dtype != "auto" else 1.0)
 
     # ---- linear helpers -------------------------------------------------------------------------------
-    def _linear_q(self, xq, xs, w, ws):
-        return ops.cutlass_scaled_mm(xq, w.t(), xs, ws.view(1, -1), self.dtype)
+    def _linear_q(self, xq, xs, w, ws, out=None):
+        if out is None:
+            return ops.cutlass_scaled_mm(xq, w.t(), xs, ws.view(1, -1), self.dtype)
+        ops.cutlass_scaled_mm_out(out, xq, w.t(), xs, ws.view(1, -1))
+        return out
 
-    def forward(self, positions, hidden, residual, kv_cache, meta: B200PagedAttentionMetadata, cos_sin):
+    def _peer_ar(self, rows):
+        """The peer-memory all-reduce when it is set up and the message fits its staging buffer, else None (NCCL)."""
+        par = get_peer_allreduce()
+        return par if par is not None and par.fits(rows, self.cfg.hidden_size, self.dtype) else None
+
+    def forward(self, positions, hidden, residual, kv_cache, meta: B200PagedAttentionMetadata, cos_sin,
+                pending: bool = False):
+        """`pending`: `hidden` is this rank's PARTIAL sum of the previous layer's row-parallel GEMM, sitting in the
+        peer all-reduce staging buffer; the all-reduce is fused into the first norm of this layer.  Returns
+        (hidden, residual, pending) with the same meaning for the caller."""
         cfg, eps = self.cfg, self.cfg.rms_eps
         fp8 = self.quant == "fp8"
+        par = self._peer_ar(hidden.shape[0])
         # ---- attention block ----
-        if fp8:
+        if pending:
+            assert fp8 and par is not None and residual is not None
+            xq, xs = par.all_reduce_add_rms_norm_quant(hidden, residual, self.input_ln, eps)
+            qkv = self._linear_q(xq, xs, self.w_qkv, self.s_qkv)
+        elif fp8:
             if residual is None:
                 residual = hidden.clone()
                 xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.input_ln, eps, FP8)
@@ -169,21 +186,34 @@ class DecoderLayer:
         v = qkv[:, self.q_size + self.kv_size:]
         ops.rotary_embedding(positions, q, k, cfg.head_dim, cos_sin, True)
         attn_out = self.attn.forward(self.kv_scales, q, k, v, kv_cache, meta)
+        T = attn_out.shape[0]
+        fused_ar = fp8 and par is not None   # o_proj's all-reduce is fused into the post-attention norm
         if fp8:
             aq, a_s = ops.scaled_fp8_quant(attn_out, use_per_token_if_dynamic=True)
-            hidden = self._linear_q(aq, a_s, self.w_o, self.s_o)
+            hidden = self._linear_q(aq, a_s, self.w_o, self.s_o,
+                                    par.staging(T, cfg.hidden_size, self.dtype) if fused_ar else None)
         else:
             hidden = torch.matmul(attn_out, self.w_o.t())
-        hidden = tensor_model_parallel_all_reduce(hidden)
+        if not fused_ar:
+            hidden = tensor_model_parallel_all_reduce(hidden)
         # ---- MLP block ----
         if cfg.num_experts:
-            ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
+            if fused_ar:
+                hidden = par.all_reduce_add_rms_norm(hidden, residual, self.post_ln, eps)
+            else:
+                ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
             from .fused_moe import moe_forward
             hidden = moe_forward(hidden, self.w_gate, self.experts, cfg.top_k, renormalize=True)
         elif fp8:
-            xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.post_ln, eps, FP8, None, residual)
+            if fused_ar:
+                xq, xs = par.all_reduce_add_rms_norm_quant(hidden, residual, self.post_ln, eps)
+            else:
+                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, self.post_ln, eps, FP8, None, residual)
             gu = self._linear_q(xq, xs, self.w_gate_up, self.s_gate_up)
             hq, hs = ops.silu_and_mul_dynamic_per_token_quant(gu)
+            if fused_ar:   # leave the partial sum in the staging buffer: the next norm pulls and reduces it
+                hidden = self._linear_q(hq, hs, self.w_down, self.s_down, par.staging(T, cfg.hidden_size, self.dtype))
+                return hidden, residual, True
             hidden = self._linear_q(hq, hs, self.w_down, self.s_down)
         else:
             ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
@@ -192,7 +222,7 @@ class DecoderLayer:
             ops.silu_and_mul(act, gu)
             hidden = torch.matmul(act, self.w_down.t())
         hidden = tensor_model_parallel_all_reduce(hidden)
-        return hidden, residual
+        return hidden, residual, False
 
 
 class Decoder:
@@ -244,9 +274,11 @@ class Decoder:
 
     def hidden_states(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
         hidden = self.embed.index_select(0, input_ids)
-        residual = None
+        residual, pending = None, False
         for layer, kv in zip(self.layers, self.kv_caches):
-            hidden, residual = layer.forward(positions, hidden, residual, kv, meta, self.cos_sin)
+            hidden, residual, pending = layer.forward(positions, hidden, residual, kv, meta, self.cos_sin, pending)
+        if pending:   # the last down_proj's all-reduce, fused with the final norm
+            return get_peer_allreduce().all_reduce_add_rms_norm(hidden, residual, self.final_ln, self.cfg.rms_eps)
         ops.fused_add_rms_norm(hidden, residual, self.final_ln, self.cfg.rms_eps)
         return hidden
 

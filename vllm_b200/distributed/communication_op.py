@@ -11,6 +11,7 @@ import torch.distributed as dist
 _TP_GROUP: Optional["dist.ProcessGroup"] = None
 _TP_WORLD = 1
 _TP_RANK = 0
+_PEER_AR = None   # PeerAllReduce (NVLink peer-memory all-reduce fused with its consumer) or None
 
 
 def init_tensor_parallel(group: Optional["dist.ProcessGroup"] = None) -> None:
@@ -22,6 +23,28 @@ def init_tensor_parallel(group: Optional["dist.ProcessGroup"] = None) -> None:
     _TP_GROUP = group if group is not None else dist.group.WORLD
     _TP_WORLD = dist.get_world_size(_TP_GROUP)
     _TP_RANK = dist.get_rank(_TP_GROUP)
+
+
+def init_peer_allreduce(device, max_bytes: int = 8 << 20):
+    """Set up the peer-memory all-reduce for the TP group (CUDA devices of ONE node, world size 2/4/8, NCCL group
+    already initialised).  Returns the PeerAllReduce or None when it does not apply (world 1, unsupported size, or
+    VB200_PEER_AR=0)."""
+    global _PEER_AR
+    import os
+    _PEER_AR = None
+    if _TP_WORLD in (2, 4, 8) and os.environ.get("VB200_PEER_AR", "1") != "0" and torch.device(device).type == "cuda":
+        from .peer_allreduce import PeerAllReduce
+        try:
+            _PEER_AR = PeerAllReduce(_TP_GROUP, device, max_bytes)
+        except RuntimeError as e:   # raised on EVERY rank together (see PeerAllReduce.__init__): NCCL carries on
+            import sys
+            print(f"[vllm_b200] peer all-reduce unavailable, using NCCL: {e}", file=sys.stderr, flush=True)
+            _PEER_AR = None
+    return _PEER_AR
+
+
+def get_peer_allreduce():
+    return _PEER_AR
 
 
 def get_tensor_model_parallel_world_size() -> int:
