@@ -122,8 +122,17 @@ def main():
                 st = par.staging(T, H, torch.bfloat16)
                 st.copy_(xs)
                 par.all_reduce_add_rms_norm_quant(st, res2, w, 1e-5)
+        from vllm_b200 import _lib
+        import ctypes
+        tune = _lib.load().vb200_debug_peer_allreduce_tune
+        tune.restype, tune.argtypes = None, [ctypes.c_int, ctypes.c_int]
         times = {}
-        for name, fn in (("copy_only", clone_only), ("nccl_plus_norm_quant", nccl_path), ("peer_fused", peer_path)):
+        variants = [("copy_only", clone_only, None), ("nccl_plus_norm_quant", nccl_path, None)]
+        for blocks, staged in ((32, 1), (64, 1), (96, 1), (148, 1), (64, 0), (148, 0)):
+            variants.append((f"peer_fused_b{blocks}_{'staged' if staged else 'direct'}", peer_path, (blocks, staged)))
+        for name, fn, cfg_ in variants:
+            if cfg_ is not None:
+                tune(*cfg_)
             with torch.cuda.stream(s):
                 fn()
                 gg = torch.cuda.CUDAGraph()
@@ -139,6 +148,7 @@ def main():
             e1.record()
             torch.cuda.synchronize()
             times[name] = e0.elapsed_time(e1) * 1e3 / 200
+        tune(0, 1)
         if rank == 0:
             print("[timing] us per op, [256 x 4096] bf16, world %d: %s (each path includes one 2 MiB device copy)" % (
                 world, {k: round(v, 2) for k, v in times.items()}), flush=True)

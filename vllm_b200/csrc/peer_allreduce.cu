@@ -14,8 +14,8 @@
 //   MODE 2: x = T(sum); z = x + res (fp32); res = T(z); y = T(T(z * inv) * w); s = max(amax|y| / 448, 1/(448*512));
 //           out = fp8(clamp(y / s)); scales[row] = s                              (rms_norm_dynamic_per_token_quant)
 // Barrier: per CTA index, a monotonically increasing counter kept in device memory (graph-replay safe); CTA b of
-// rank r stores the counter into slot [b][r] of every peer's signal block (st.release.sys after a system fence)
-// and spins (ld.acquire.sys) until all peers' counters show up in its own block.  A second barrier at the end keeps
+// rank r stores the counter into slot [b][r] of every peer's signal block (volatile store over NVLink) and spins
+// (volatile loads of its own block) until all peers' counters show up.  A second barrier at the end keeps
 // a rank from overwriting its buffer (next GEMM) while a peer is still reading it.
 #include <cstring>
 
@@ -24,9 +24,11 @@
 namespace vb200 {
 
 constexpr int kArMaxRanks = 8;
-constexpr int kArMaxBlocks = 320;
-constexpr int kArThreads = 256;
-constexpr int kArMaxVec = 8;   // rows up to 256 * 8 * 8 = 16384 elements stay in registers
+constexpr int kArMaxBlocks = 160;
+constexpr int kArThreads = 512;
+constexpr int kArMaxVec = 4;   // rows up to 512 * 4 * 8 = 16384 elements stay in registers
+constexpr int kArStages = 3;   // staged kernel: rows in flight per CTA (cp.async ring in shared memory)
+constexpr int kArMaxStageBytes = 64 * 1024;
 constexpr float kFp8MaxA = 448.f;
 
 struct ArSignal {
@@ -47,12 +49,17 @@ struct ArParams {
   int rows, hidden;
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// Flag traffic is volatile (relaxed, system-visible) stores and loads WITHOUT fences, as in the reference's first /
+// final barriers (custom_all_reduce.cuh:196-240): the data a flag announces was written by the PREVIOUS kernel on
+// the stream (complete at this kernel's start), and the end barrier only has to order "my loads of your buffer have
+// returned" (their values were consumed before the bar.sync) before "you may overwrite it".  A fenced version
+// (fence.sys + st.release.sys / ld.acquire.sys in the spin) cost ~9 us per barrier.
+__device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+__device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
   uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
@@ -63,22 +70,32 @@ __device__ __forceinline__ void ar_barrier(const ArParams& p) {
     ArSignal* self = p.signals[p.rank];
     const uint32_t flag = self->self_counter[blockIdx.x][threadIdx.x] + 1;
     self->self_counter[blockIdx.x][threadIdx.x] = flag;
-    __threadfence_system();  // this rank's earlier writes (the GEMM output, via the kernel boundary) before the flag
-    st_release_sys(&p.signals[threadIdx.x]->peer_counter[flag & 1][blockIdx.x][p.rank], flag);
+    st_flag(&p.signals[threadIdx.x]->peer_counter[flag & 1][blockIdx.x][p.rank], flag);
     const uint32_t* mine = &self->peer_counter[flag & 1][blockIdx.x][threadIdx.x];
-    while (ld_acquire_sys(mine) != flag) {
+    while (ld_flag(mine) != flag) {
     }
   }
   __syncthreads();
 }
 
+// Peer data is read with plain (weak) 16-byte loads that do not allocate in L1: every address is read once per
+// kernel, after the barrier (bar.sync after the acquiring threads orders the CTA's loads behind it), and L1 does not
+// survive a kernel boundary, so no stale line can be hit.  (Strong .sys loads here cost 2x in the first version.)
 __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
-  uint4 v;  // peer memory is written by another GPU: no non-coherent (.nc) path, no L1 allocation
-  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p)
                : "memory");
   return v;
+}
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* g) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 template <typename T>
@@ -113,7 +130,7 @@ __device__ __forceinline__ void ar_sum8(const ArParams& p, int64_t off, float (&
 }
 
 template <typename T, int N, int MODE>
-__global__ void __launch_bounds__(kArThreads, 2) peer_allreduce_kernel(const ArParams p) {
+__global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_kernel(const ArParams p) {
   __shared__ float sm[kArThreads / 32];
   ar_barrier<N>(p);
   if (MODE == 0) {
@@ -196,8 +213,129 @@ __global__ void __launch_bounds__(kArThreads, 2) peer_allreduce_kernel(const ArP
   ar_barrier<N>(p);
 }
 
+// Staged variant of MODE 1 / 2 (the decode path's shape): a CTA owns rows blockIdx.x, blockIdx.x + grid, ... and
+// keeps kArStages rows in flight -- all N peers' copies of a row are fetched with cp.async (16 bytes, L2-only) into a
+// shared-memory ring, so the NVLink round trip of the next rows overlaps the reduction / norm / quant of this one and
+// far fewer CTAs (each one pays two system-scope barriers) cover the batch.
+template <typename T, int N, int MODE>
+__global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_staged_kernel(const ArParams p) {
+  extern __shared__ __align__(16) uint8_t ring[];
+  __shared__ float sm[kArThreads / 32];
+  const int nvec = p.hidden >> 3;
+  const int row_bytes = p.hidden * (int)sizeof(T);
+  const int stage_bytes = N * row_bytes;
+  const T* weight = reinterpret_cast<const T*>(p.weight);
+  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
+  ar_barrier<N>(p);
+  auto issue = [&](int k) {
+    const int row = blockIdx.x + k * gridDim.x;
+    if (row < p.rows) {
+      const uint32_t dst = ring_u32 + (uint32_t)((k % kArStages) * stage_bytes);
+#pragma unroll
+      for (int r = 0; r < N; ++r) {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.data[r]) + (int64_t)row * row_bytes;
+        for (int i = threadIdx.x; i < nvec; i += kArThreads) cp_async16(dst + r * row_bytes + i * 16, src + i * 16);
+      }
+    }
+    cp_async_commit();   // always: keeps the group count in step with k
+  };
+#pragma unroll
+  for (int k = 0; k < kArStages - 1; ++k) issue(k);
+  for (int k = 0;; ++k) {
+    const int row = blockIdx.x + k * gridDim.x;
+    if (row >= p.rows) break;
+    issue(k + kArStages - 1);
+    cp_async_wait<kArStages - 1>();
+    __syncthreads();
+    const uint8_t* st = ring + (size_t)(k % kArStages) * stage_bytes;
+    T* res = reinterpret_cast<T*>(p.residual) + (int64_t)row * p.hidden;
+    float zf[kArMaxVec][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < kArMaxVec; ++kk) {
+      const int i = threadIdx.x + kk * kArThreads;
+      if (i < nvec) {
+        ArVec8<T> v[N], b, z;
+#pragma unroll
+        for (int r = 0; r < N; ++r) v[r].u = *reinterpret_cast<const uint4*>(st + r * row_bytes + i * 16);
+        b.u = *reinterpret_cast<const uint4*>(res + i * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = to_float<T>(v[0].e[j]);
+#pragma unroll
+          for (int r = 1; r < N; ++r) a += to_float<T>(v[r].e[j]);
+          const float s = to_float<T>(from_float<T>(a)) + to_float<T>(b.e[j]);
+          z.e[j] = from_float<T>(s);
+          zf[kk][j] = (MODE == 1) ? to_float<T>(z.e[j]) : s;
+          ss = fmaf(zf[kk][j], zf[kk][j], ss);
+        }
+        *reinterpret_cast<uint4*>(res + i * 8) = z.u;
+      }
+    }
+    ss = ar_block_reduce<false>(ss, sm);   // its barriers also fence this stage's reads from the refill two rows on
+    const float inv = rsqrtf(ss / (float)p.hidden + p.eps);
+    float amax = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < kArMaxVec; ++kk) {
+      const int i = threadIdx.x + kk * kArThreads;
+      if (i < nvec) {
+        ArVec8<T> w, y;
+        w.u = *reinterpret_cast<const uint4*>(weight + i * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const T n = from_float<T>(zf[kk][j] * inv);
+          y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(w.e[j]));
+          if (MODE == 2) {
+            zf[kk][j] = to_float<T>(y.e[j]);
+            amax = fmaxf(amax, fabsf(zf[kk][j]));
+          }
+        }
+        if (MODE == 1)
+          *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.out) + (int64_t)row * p.hidden + i * 8) = y.u;
+      }
+    }
+    if (MODE == 2) {
+      amax = ar_block_reduce<true>(amax, sm);
+      float s = p.scale_ub ? fminf(amax, *p.scale_ub) : amax;
+      s = fmaxf(s / kFp8MaxA, 1.0f / (kFp8MaxA * 512.0f));
+      if (threadIdx.x == 0) p.scales[row] = s;
+      uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + (int64_t)row * p.hidden;
+#pragma unroll
+      for (int kk = 0; kk < kArMaxVec; ++kk) {
+        const int i = threadIdx.x + kk * kArThreads;
+        if (i < nvec) {
+          union { uint2 u; uint8_t b[8]; } q;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) q.b[j] = float_to_e4m3(fmaxf(-kFp8MaxA, fminf(zf[kk][j] / s, kFp8MaxA)));
+          *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+  ar_barrier<N>(p);
+}
+
+static int g_ar_blocks = 0;       // 0 = default; debug / tuning hook below
+static int g_ar_staged = 1;
+
 template <typename T, int N>
 static int launch_mode(int mode, int grid, const ArParams& p, cudaStream_t stream) {
+  const int stage_bytes = N * p.hidden * (int)sizeof(T);
+  if (mode != 0 && g_ar_staged && stage_bytes <= kArMaxStageBytes) {
+    const size_t smem = (size_t)kArStages * stage_bytes;
+    if (mode == 1) {
+      auto kern = peer_allreduce_staged_kernel<T, N, 1>;
+      VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kArStages * kArMaxStageBytes));
+      kern<<<grid, kArThreads, smem, stream>>>(p);
+    } else {
+      auto kern = peer_allreduce_staged_kernel<T, N, 2>;
+      VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kArStages * kArMaxStageBytes));
+      kern<<<grid, kArThreads, smem, stream>>>(p);
+    }
+    VB_LAUNCH_CHECK();
+    return 0;
+  }
   if (mode == 0) peer_allreduce_kernel<T, N, 0><<<grid, kArThreads, 0, stream>>>(p);
   else if (mode == 1) peer_allreduce_kernel<T, N, 1><<<grid, kArThreads, 0, stream>>>(p);
   else peer_allreduce_kernel<T, N, 2><<<grid, kArThreads, 0, stream>>>(p);
@@ -254,6 +392,11 @@ extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer
   p.eps = epsilon;
   p.rows = rows;
   p.hidden = hidden;
+  // Grid: every CTA pays two system-scope barriers, and the same-index CTAs of all ranks must be co-resident
+  // (1 CTA/SM, grid <= #SMs).  More CTAs = fewer rows per CTA = fewer serialised NVLink round trips (measured).
+  int cap = g_ar_blocks > 0 ? g_ar_blocks : num_sms();
+  if (cap > num_sms()) cap = num_sms();
+  if (cap > kArMaxBlocks) cap = kArMaxBlocks;
   int grid;
   if (mode == 0) {
     const int64_t nvec = (int64_t)rows * hidden / 8;
@@ -261,8 +404,6 @@ extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer
   } else {
     grid = rows;
   }
-  // every CTA must be co-resident with its same-index CTA on the peers: two 256-thread CTAs per SM at most
-  const int cap = 2 * num_sms() < kArMaxBlocks ? 2 * num_sms() : kArMaxBlocks;
   if (grid > cap) grid = cap;
   if (dtype == VB200_BF16) return launch_ranks<__nv_bfloat16>(world, mode, grid, p, stream);
   return launch_ranks<__half>(world, mode, grid, p, stream);
@@ -304,4 +445,12 @@ extern "C" int vb200_peer_buffer_close(void* ptr) {
 extern "C" int vb200_peer_buffer_free(void* ptr) {
   if (ptr) VB_CUDA_CHECK(cudaFree(ptr));
   return 0;
+}
+
+
+// Debug / tuning hook (not part of the drop-in surface): CTAs per launch (0 = default 64) and whether the fused modes
+// use the cp.async-staged kernel (default) or the direct-load kernel; CTAs 0 = one per SM.  Must be set identically on every rank.
+extern "C" void vb200_debug_peer_allreduce_tune(int blocks, int staged) {
+  g_ar_blocks = blocks;
+  g_ar_staged = staged;
 }
