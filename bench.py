@@ -2,7 +2,7 @@
 """bench.py -- decode throughput of the hot path on BASELINE.json's metric
 ("decode tokens/s/GPU Llama-3.1-8B FP8; paged-attn HBM GB/s vs peak").
 
-    python bench.py --gpus N --steps K --warmup W [--impl reference] [--config cfg3|cfg2|cfg4|tiny]
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--config cfg3|cfg2|cfg4|cfg5|tiny]
 
 One "step" = one decode step (all 32 layers + lm_head + greedy arg-max) of Llama-3.1-8B, FP8 w8a8 scaled_mm
 (dynamic per-token activation scales, per-channel weight scales) + fp8_e4m3 paged KV cache (block 16), batch 256
@@ -41,6 +41,7 @@ WORKLOADS = {
     "cfg3": ("Llama-3.1-8B", 256, 4096, "fp8", "fp8"),
     "cfg2": ("Llama-3.1-8B", 64, 2048, "bf16", "auto"),
     "cfg4": ("Mixtral-8x7B", 128, 2048, "fp8", "fp8"),   # BASELINE configs[3] (context not named there: 2k)
+    "cfg5": ("Llama-3.1-70B", 128, 8192, "fp8", "fp8"),  # BASELINE configs[4]: needs TP >= 4 (242 GB of weights + KV)
     "tiny": ("tiny-llama", 8, 256, "fp8", "fp8"),
 }
 
@@ -234,7 +235,7 @@ def run_reference_arm(args, rank: int):
 
 def workload_config(name: str, n_gpus: int):
     model, batch, ctx, quant, kvd = WORKLOADS[name]
-    return {"workload": f"BASELINE configs[{ {'cfg3': 2, 'cfg2': 1, 'cfg4': 3}.get(name, 0) }]: {model} {quant} "
+    return {"workload": f"BASELINE configs[{ {'cfg3': 2, 'cfg2': 1, 'cfg4': 3, 'cfg5': 4}.get(name, 0) }]: {model} {quant} "
                         f"{'w8a8 scaled_mm ' if quant == 'fp8' else ''}+ {'fp8_e4m3' if kvd == 'fp8' else 'bf16'} "
                         f"paged KV block 16, batch {batch} decode at {ctx} context",
             "global_batch": batch, "context_len": ctx, "block_size": 16, "parallelism": f"tp{n_gpus}",

@@ -48,7 +48,15 @@ def main():
         if world == 2:
             check(f"mode0 bit-exact {T}x{H}", torch.equal(got, ref))
         else:
-            torch.testing.assert_close(got.float(), ref.float(), rtol=1e-2, atol=2e-2)
+            # > 2 ranks: NCCL rounds partial sums to the 16-bit dtype on the way (ring / tree / in-switch), this kernel
+            # sums all ranks in fp32 and rounds once -- compare with the fp32 all-reduce rounded once (<= 1 ulp apart
+            # from a different fp32 summation order), and only loosely with NCCL's 16-bit result
+            ref32 = x.float()
+            dist.all_reduce(ref32)
+            torch.testing.assert_close(got.float(), ref32.to(dtype).float(), rtol=1e-2, atol=1e-3)
+            check(f"mode0 >= 99.9% identical to the rounded fp32 sum {T}x{H}",
+                  (got == ref32.to(dtype)).float().mean().item() >= 0.999)
+            torch.testing.assert_close(got.float(), ref.float(), rtol=5e-2, atol=5e-2 * world)
         # every rank holds identical bits
         gathered = [torch.empty_like(got) for _ in range(world)]
         dist.all_gather(gathered, got)
@@ -95,11 +103,12 @@ def main():
     for it in range(50):
         gen.manual_seed(1000 + 10 * it + rank)
         x.normal_(0, 1, generator=gen)
-        ref = x.clone()
+        ref = x.clone() if world == 2 else x.float()
         dist.all_reduce(ref)
         g.replay()
         torch.cuda.synchronize()
-        ok = ok and (torch.equal(out, ref) if world == 2 else torch.allclose(out.float(), ref.float(), rtol=1e-2, atol=2e-2))
+        ok = ok and (torch.equal(out, ref) if world == 2 else
+                     torch.allclose(out.float(), ref.bfloat16().float(), rtol=1e-2, atol=1e-3))
     check("graph replay x50", ok)
     # timing (CUDA graph of 20 back-to-back ops, 10 replays): NCCL all_reduce + fused_add-rmsnorm-quant kernel vs the
     # one fused peer kernel, [256, 4096] bf16 (the Llama-3.1-8B config-3 message, 2 MiB)
@@ -152,7 +161,14 @@ def main():
         if rank == 0:
             print("[timing] us per op, [256 x 4096] bf16, world %d: %s (each path includes one 2 MiB device copy)" % (
                 world, {k: round(v, 2) for k, v in times.items()}), flush=True)
-    # decode step: fused path on vs off -> same greedy tokens, close logits
+    # decode step: fused path on vs off -> close hidden states (tiny model: only sharded 2 ways -- at 4/8 ranks its
+    # per-rank K drops below one GEMM k-block; bench.py covers TP 4 / 8 at the real sizes)
+    if world > 2:
+        dist.barrier()
+        torch.cuda.synchronize()
+        print(f"[rank {rank}] peer all-reduce check: {'OK' if not fails else 'FAILED ' + str(fails)}", flush=True)
+        sys.stdout.flush()
+        os._exit(1 if fails else 0)
     from vllm_b200.attention import B200PagedAttentionMetadata
     from vllm_b200.decode_step import CONFIGS, Decoder
     from vllm_b200.distributed import communication_op as co
