@@ -204,6 +204,10 @@ class DecoderLayer:
                 ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
             from .fused_moe import moe_forward
             hidden = moe_forward(hidden, self.w_gate, self.experts, cfg.top_k, renormalize=True)
+            if fused_ar:   # park the partial sum (one 2 MiB copy) so that the next norm pulls and reduces it
+                st = par.staging(T, cfg.hidden_size, self.dtype)
+                st.copy_(hidden)
+                return st, residual, True
         elif fp8:
             if fused_ar:
                 xq, xs = par.all_reduce_add_rms_norm_quant(hidden, residual, self.post_ln, eps)
