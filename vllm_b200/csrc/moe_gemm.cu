@@ -406,7 +406,10 @@ extern "C" int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, con
   // once or twice), multiple of 16
   int block_m = (2 * ((num_rows + E - 1) / E) + 15) & ~15;
   if (block_m < 16) block_m = 16;
-  if (block_m > kMoeMaxBlockM) block_m = kMoeMaxBlockM;
+  // Short K (w13: K = hidden): <= 128 rows per block keeps two CTAs per SM, whose prologue / epilogue overlap is worth
+  // more than reading an expert's weights once (batch 512: 272 -> 259 us); long K (w2) prefers the 256-row block
+  // (113 vs 134 us) -- profiles/r01_moe_gemm_sweep_s16.jsonl, r01_moe_gemm_sweep_s31.jsonl
+  if (block_m > 128 && K <= 8192) block_m = 128;
   const int m_blocks = E + num_rows / block_m;  // >= sum_e ceil(m_e / block_m)
   CUtensorMap tw, ta;
   if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)K, (uint64_t)K, kMoeBlockN)) return 1;
