@@ -161,7 +161,8 @@ def _grouped_problem(T, k, E, N, K, per_act_token, per_out_ch, skew=False):
 
 @pytest.mark.parametrize("T,k,E,N,K", [
     (1, 2, 8, 256, 128), (16, 2, 8, 512, 256), (33, 2, 8, 512, 256), (128, 2, 8, 1024, 512), (128, 2, 8, 384, 4096),
-    (64, 6, 64, 256, 512), (300, 2, 4, 256, 256), (700, 2, 2, 128, 128), (17, 1, 3, 144, 272), (2048, 2, 8, 256, 384)])
+    (64, 6, 64, 256, 512), (300, 2, 4, 256, 256), (700, 2, 2, 128, 128), (17, 1, 3, 144, 272), (2048, 2, 8, 256, 384),
+    (2048, 2, 8, 128, 14336)])   # long K (> 8192) with > 128 rows per expert: the block_m clamp of the ragged launcher
 @pytest.mark.parametrize("per_act_token,per_out_ch", [(False, False), (True, True), (True, False)])
 @pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float16])
 def test_cutlass_moe_mm(T, k, E, N, K, per_act_token, per_out_ch, out_dtype):

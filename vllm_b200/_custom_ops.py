@@ -324,21 +324,23 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     return bool(load().vb200_cutlass_scaled_mm_supports_fp8(int(cuda_device_capability)))
 
 
-_GEMM_WS = {}       # device index -> zero-initialised workspace (split-K tickets + partials)
+_GEMM_WS = {}       # (device index, stream handle) -> zero-initialised workspace (split-K tickets + partials)
 _GEMM_WS_KEEP = []  # superseded buffers stay alive: captured CUDA graphs may still point at them
 
 
 def _gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Per-device scratch for the tcgen05 GEMMs.  The first 16 KiB (tickets) must be zero on first
-    use and are left zero by every launch, so the buffer is allocated once with torch.zeros and only
-    ever grown.  One workspace per device: GEMMs are assumed to run on one stream at a time (as in
-    vLLM's worker); warm up before CUDA-graph capture so that no growth happens while capturing."""
-    ws = _GEMM_WS.get(device.index)
+    """Scratch of the tcgen05 GEMMs (split-K arrival tickets + fp32 partials).  The first 16 KiB (tickets) must be
+    zero on first use and are left zero by every launch, so a buffer is allocated once with torch.zeros and only
+    ever grown.  One workspace per (device, stream): launches on ONE stream are ordered, so they may share it;
+    launches on different streams (or a graph replay on a side stream next to eager work) get different buffers.
+    include/vllm_b200.h states the same rule for direct callers of the C ABI."""
+    key = (device.index, stream())
+    ws = _GEMM_WS.get(key)
     if ws is None or ws.numel() < nbytes:
         if ws is not None:
             _GEMM_WS_KEEP.append(ws)
         ws = torch.zeros(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
-        _GEMM_WS[device.index] = ws
+        _GEMM_WS[key] = ws
     return ws
 
 

@@ -288,6 +288,8 @@ using namespace vb200;
 static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap& ta, int m_blocks,
                            int out_dtype, cudaStream_t stream) {
   const int N = p.N, K = p.K, block_m = p.block_m;
+  VB_CHECK(block_m >= 16 && block_m <= kMoeMaxBlockM && block_m % 16 == 0,
+           "moe grouped GEMM: block_m (%d) must be a multiple of 16 in [16, %d]", block_m, kMoeMaxBlockM);
   p.num_kb = (K + kMoeBlockK - 1) / kMoeBlockK;
   const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
   const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
@@ -410,6 +412,7 @@ extern "C" int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, con
   // more than reading an expert's weights once (batch 512: 272 -> 259 us); long K (w2) prefers the 256-row block
   // (113 vs 134 us) -- profiles/r01_moe_gemm_sweep_s16.jsonl, r01_moe_gemm_sweep_s31.jsonl
   if (block_m > 128 && K <= 8192) block_m = 128;
+  if (block_m > kMoeMaxBlockM) block_m = kMoeMaxBlockM;  // s_tok / s_rowscale / TMEM columns / UMMA N all end at 256
   const int m_blocks = E + num_rows / block_m;  // >= sum_e ceil(m_e / block_m)
   CUtensorMap tw, ta;
   if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)K, (uint64_t)K, kMoeBlockN)) return 1;

@@ -39,7 +39,8 @@ struct PagedAttnParams {
   const float* v_scale;
   int num_heads, num_kv_heads, max_num_blocks_per_seq;
   int partition_size;      // tokens; multiple of 16 and of BLOCK_SIZE
-  int max_num_partitions;  // 1 => write `out` directly
+  int max_num_partitions;  // 1 => write `out` directly (unless force_partials)
+  int force_partials = 0;  // paged_attention_v2: the caller's partial buffers are always filled, as the reference does
   int64_t q_stride, kv_block_stride, kv_head_stride;
   float scale;
   int prefetch_dist;  // tiles (per warp) ahead of the register double buffer that are pulled into L2; 0 = off
@@ -417,7 +418,7 @@ __global__ void __launch_bounds__(NWARPS * 32, (HEAD_SIZE <= 128 ? (FP8 ? 3 : 2)
 
   // ---- merge warps, normalise, write --------------------------------------------------------------
   const float v_scale = FP8 ? *p.v_scale : 1.f;
-  const bool partitioned = p.max_num_partitions > 1;
+  const bool partitioned = p.max_num_partitions > 1 || p.force_partials;
   for (int idx = tid; idx < nheads * HEAD_SIZE; idx += NWARPS * 32) {
     const int h = idx / HEAD_SIZE;
     const int d = idx - h * HEAD_SIZE;
@@ -461,7 +462,9 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
   const int lane = threadIdx.x & 31;
   const int seq_idx = row / num_heads;
   const int seq_len = seq_lens[seq_idx];
-  const int np = max(1, (seq_len + partition_size - 1) / partition_size);
+  // seq_len is read on the device and may have grown past the max_seq_len the buffers were sized from (a replayed
+  // graph whose seq_lens advance on device): never walk past the row's max_num_partitions entries
+  const int np = min(max(1, (seq_len + partition_size - 1) / partition_size), max_num_partitions);
   const float* ml = max_logits + (int64_t)row * max_num_partitions;
   const float* es = exp_sums + (int64_t)row * max_num_partitions;
   const QT* tp = tmp_out + (int64_t)row * max_num_partitions * HEAD_SIZE;
@@ -549,7 +552,7 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     dim3 grid_t(p.num_kv_heads * ((q_per_kv_ + 7) / 8), num_seqs, num_partitions);
     kt<<<grid_t, (kWarps + 1) * 32, smem_t, stream>>>(p, stages);
     VB_LAUNCH_CHECK();
-    if (p.max_num_partitions > 1) {
+    if (p.max_num_partitions > 1 || p.force_partials) {
       const int rows = num_seqs * p.num_heads;
       paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
           (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
@@ -569,7 +572,7 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
   dim3 grid(p.num_kv_heads * groups, num_seqs, num_partitions);
   kern<<<grid, kWarps * 32, smem, stream>>>(p);
   VB_LAUNCH_CHECK();
-  if (p.max_num_partitions > 1) {
+  if (p.max_num_partitions > 1 || p.force_partials) {
     const int rows = num_seqs * p.num_heads;
     paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
         (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
@@ -684,8 +687,9 @@ extern "C" int vb200_paged_attention_v2(
   p.kv_head_stride = kv_head_stride;
   p.scale = scale;
   p.prefetch_dist = pa_prefetch_dist();
-  // With a single partition the kernel writes `out` directly (the reference's reduce kernel
-  // would copy tmp_out -> out; same result), and leaves the partial buffers untouched.
+  // exp_sums / max_logits / tmp_out are always written, also with a single partition (the reference's v2 kernel
+  // fills them and its reduce kernel copies tmp_out -> out, attention_kernels.cuh:337,577-589,647)
+  p.force_partials = 1;
   return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
                              (cudaStream_t)stream);
 }

@@ -329,7 +329,7 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
 
   // ---- merge warps, normalise, write (identical to the register-staged kernel) ------------------------------
   const float v_scale = FP8 ? *p.v_scale : 1.f;
-  const bool partitioned = p.max_num_partitions > 1;
+  const bool partitioned = p.max_num_partitions > 1 || p.force_partials;
   for (int idx = tid; idx < nheads * HEAD_SIZE; idx += (NWARPS + 1) * 32) {
     const int h = idx / HEAD_SIZE;
     const int d = idx - h * HEAD_SIZE;

@@ -41,15 +41,11 @@ def get_block_m(num_pairs: int, num_experts: int) -> int:
     return 256 if avg > 192 else 128
 
 
-_MOE_WS = {}
-
-
 def _moe_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    ws = _MOE_WS.get(device.index)
-    if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 16 << 20), dtype=torch.uint8, device=device)
-        _MOE_WS[device.index] = ws
-    return ws
+    """Scratch for the sorted-order activation gather: taken per call from torch's caching allocator (as
+    paged_attention_v1 does for its partials), so it is stream-ordered, never shared between streams, and inside
+    a CUDA-graph capture it comes from -- and lives as long as -- the graph's private pool."""
+    return torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
 
 
 def invoke_fused_moe_kernel(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, A_scale: Optional[torch.Tensor],
