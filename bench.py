@@ -196,10 +196,13 @@ def cpu_reference_step_sample(workload: str, budget_s: float = 12.0, max_reps: i
     t_layer = statistics.median(ts)
     tps = S / (cfg.num_layers * t_layer)
     info = {"value": round(tps, 3), "unit": "tokens/s", "cores": cores, "kind": kind,
-            "sample": (f"1 of {cfg.num_layers} layers x {S} of {batch} sequences at ctx {ctx}: reference csrc/cpu "
-                       f"reshape_and_cache + paged_attention_v1 (bf16 KV; the CPU kernel has no fp8 path) + 4 "
-                       f"projections as torch bf16 matmul (oneDNN); {len(ts)} reps, median {t_layer * 1e3:.1f} ms/layer; "
-                       f"tokens/s = {S} / ({cfg.num_layers} x t_layer)")}
+            "sample": (f"PARTIAL LAYER, extrapolated: 1 of {cfg.num_layers} layers x {S} of {batch} sequences at ctx "
+                       f"{ctx}: reference csrc/cpu reshape_and_cache + paged_attention_v1 (bf16 KV; the CPU kernel has "
+                       f"no fp8 path) + the 4 projections as torch bf16 matmul (oneDNN) + silu-mul; norms, RoPE, "
+                       f"activation quant, lm_head and sampling are NOT in the sample (they would only slow it "
+                       f"further); {len(ts)} reps, median {t_layer * 1e3:.1f} ms/layer; tokens/s = {S} / "
+                       f"({cfg.num_layers} x t_layer)"),
+            "sample_wall_s": round(sum(ts), 2)}
     return tps, info, t_layer
 
 
@@ -210,21 +213,27 @@ def run_reference_arm(args, rank: int):
     model, batch, ctx, quant, kvd = WORKLOADS[args.config]
     for _ in range(max(args.warmup, 0) and 1):
         cpu_reference_step_sample(args.config, budget_s=2.0, max_reps=1)
-    vals, t_layers = [], []
+    vals, t_layers, walls = [], [], []
+    t_run = time.perf_counter()
     for _ in range(max(args.steps, 1)):
+        t_s = time.perf_counter()
         tps, info, t_layer = cpu_reference_step_sample(args.config, budget_s=6.0, max_reps=3)
+        walls.append(time.perf_counter() - t_s)
         vals.append(tps)
         t_layers.append(t_layer)
-        if sum(t_layers) * 4 > 150:   # keep the whole run within a few minutes
+        if time.perf_counter() - t_run > 150:   # keep the whole run within a few minutes
             break
     v = statistics.median(vals)
     from vllm_b200.decode_step import CONFIGS
     nl = CONFIGS[model].num_layers
     info["value"] = round(v, 3)
+    # ms_per_step is what one step of THIS arm really took (a bounded sample: set-up + up to 3 reps of one layer on
+    # 64 sequences), so steps x ms_per_step is the arm's wall time; the full-step figure behind `value` is separate
     line = {"impl": "reference", "metric": METRIC if args.config == "cfg3" else f"decode tokens/s ({args.config})",
             "value": round(v, 3), "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": len(vals), "warmup": args.warmup,
-            "ms_per_step": round(statistics.median(t_layers) * nl * batch / min(batch, 64) * 1e3, 1),
+            "ms_per_step": round(statistics.mean(walls) * 1e3, 1),
+            "extrapolated_full_step_ms": round(statistics.median(t_layers) * nl * batch / min(batch, 64) * 1e3, 1),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16 (CPU reference path)",
             "data": "synthetic", "config": workload_config(args.config, 1),
             "cpu_baseline": info,
@@ -240,30 +249,43 @@ def workload_config(name: str, n_gpus: int):
                         f"paged KV block 16, batch {batch} decode at {ctx} context",
             "global_batch": batch, "context_len": ctx, "block_size": 16, "parallelism": f"tp{n_gpus}",
             "weights": "dummy (random)", "l2": "inputs larger than L2 (KV cache + weights >> 126 MB per step)",
-            "context": "fixed per step (every step writes slot ctx-1 and attends over ctx tokens)"}
+            "context": "advances on the device: every step writes its token's K/V, attends over all tokens so far and "
+                       "advance_step_flashattn (inside the captured graph) moves ids / positions / seq_lens / slots on; "
+                       f"{ctx} tokens at the first step"}
 
 
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
 class StepInputs:
-    """Host (pinned) and device copies of one decode step's inputs + the algorithmic byte count of its attention."""
+    """Host (pinned) and device copies of the decode inputs.  The context ADVANCES: every step appends one token per
+    sequence (device side: advance_step_flashattn inside the captured graph; host side: `advance_host` for the e2e
+    leg, which uploads the step's inputs), starting at `ctx` tokens; block tables hold `headroom` extra tokens."""
 
-    def __init__(self, batch, ctx, block_size, num_blocks, vocab, device):
+    def __init__(self, batch, ctx, block_size, num_blocks, vocab, device, headroom):
         g = torch.Generator().manual_seed(0)
-        bps = (ctx + block_size - 1) // block_size
+        bps = (ctx + headroom + block_size - 1) // block_size
+        self.bs, self.bps = block_size, bps
         self.h_ids = torch.randint(0, vocab, (batch,), generator=g, dtype=torch.int64).pin_memory()
-        self.h_pos = torch.full((batch,), ctx - 1, dtype=torch.int64).pin_memory()
-        self.h_sl = torch.full((batch,), ctx, dtype=torch.int32).pin_memory()
+        self.h_pos = torch.empty((batch,), dtype=torch.int64).pin_memory()
+        self.h_sl = torch.empty((batch,), dtype=torch.int32).pin_memory()
         self.h_bt = torch.randperm(num_blocks, generator=g)[:batch * bps].to(torch.int32).reshape(batch, bps).pin_memory()
-        self.h_slots = (self.h_bt[:, (ctx - 1) // block_size].to(torch.int64) * block_size +
-                        (ctx - 1) % block_size).pin_memory()
+        self.h_slots = torch.empty((batch,), dtype=torch.int64).pin_memory()
         self.h_out = torch.empty(batch, dtype=torch.int64).pin_memory()
+        self.batch, self.ctx, self.max_len = batch, ctx, ctx + headroom
+        self.set_host_context(ctx)
         self.d_ids, self.d_pos, self.d_sl = (t.to(device) for t in (self.h_ids, self.h_pos, self.h_sl))
         self.d_bt, self.d_slots = self.h_bt.to(device), self.h_slots.to(device)
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_ids, self.h_pos, self.h_sl, self.h_bt, self.h_slots))
         self.d2h_bytes = self.h_out.numel() * self.h_out.element_size()
-        self.batch, self.ctx = batch, ctx
+
+    def set_host_context(self, seq_len):
+        """Host copies for a step whose sequences hold `seq_len` tokens (the last one is the token being decoded)."""
+        assert seq_len <= self.max_len, "bench context outgrew the block tables"
+        self.cur = seq_len
+        self.h_pos.fill_(seq_len - 1)
+        self.h_sl.fill_(seq_len)
+        self.h_slots.copy_(self.h_bt[:, (seq_len - 1) // self.bs].to(torch.int64) * self.bs + (seq_len - 1) % self.bs)
 
     def upload(self):
         self.d_ids.copy_(self.h_ids, non_blocking=True)
@@ -279,6 +301,63 @@ def attention_algorithmic_bytes(batch, ctx, H, Hkv, D, cache_bytes, q_bytes=2, b
     qo = 2 * batch * H * D * q_bytes
     bt = batch * ((ctx + block_size - 1) // block_size) * 4 + 4 * batch
     return kv + qo + bt
+
+
+def gemm_rooflines(dec, batch, hbm_peak, hbm_src):
+    """Second roofline block: the four FP8 scaled_mm GEMMs of one layer at this batch, each timed live with CUDA events
+    over one back-to-back pass through ALL layers' weights (every launch streams a different weight matrix from HBM:
+    layers x bytes >> L2), per-launch average.  Two roofs per GEMM: HBM (weights + activations + output bytes) against
+    the measured copy bandwidth, tensor (2 M N K) against 2 x the measured dense bf16 peak (MEASURED_PEAKS.json has no
+    fp8 entry; cuBLASLt fp8 8192^3 measured 3.14 PF on this pool, profiles/r01_fp8_peak_probe_s30.json)."""
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        tensor_peak, tensor_src = 2.0 * float(pk["bf16_tflops"]), "2 x measured dense bf16 burst (MEASURED_PEAKS.json)"
+    except Exception:
+        tensor_peak, tensor_src = 4500.0, "fallback (nominal fp8 dense)"
+    from vllm_b200 import _custom_ops as ops
+    layers = dec.layers
+    if not hasattr(layers[0], "w_gate_up") or layers[0].quant != "fp8":
+        return None
+    dev = layers[0].w_qkv.device
+    out = []
+    for name, wattr, sattr in (("qkv_proj", "w_qkv", "s_qkv"), ("o_proj", "w_o", "s_o"),
+                               ("gate_up_proj", "w_gate_up", "s_gate_up"), ("down_proj", "w_down", "s_down")):
+        w0 = getattr(layers[0], wattr)
+        N, K = w0.shape
+        a = torch.randn(batch, K, device=dev).clamp_(-3, 3).to(torch.float8_e4m3fn)
+        a_s = torch.rand(batch, 1, device=dev) + 0.5
+        c = torch.empty(batch, N, device=dev, dtype=torch.bfloat16)
+
+        def sweep():
+            for l in layers:
+                ops.cutlass_scaled_mm_out(c, a, getattr(l, wattr).t(), a_s, getattr(l, sattr).view(1, -1))
+        sweep()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            sweep()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (3 * len(layers))
+        byts = N * K + batch * K + batch * N * 2 + 4 * (batch + N)
+        flops = 2.0 * batch * N * K
+        gbs, tfs = byts / us / 1e3, flops / us / 1e6
+        bound = "hbm" if byts / hbm_peak / 1e3 >= flops / tensor_peak / 1e6 else "tensor"
+        out.append({"kernel": f"scaled_mm_kernel {name} [M={batch}, N={N}, K={K}]", "bound": bound,
+                    "avg_launch_us": round(us, 2), "launches_timed": 3 * len(layers),
+                    "achieved": round(gbs if bound == "hbm" else tfs, 1),
+                    "peak": hbm_peak if bound == "hbm" else tensor_peak,
+                    "unit": "GB/s" if bound == "hbm" else "TFLOP/s",
+                    "frac": round((gbs / hbm_peak) if bound == "hbm" else (tfs / tensor_peak), 4),
+                    "hbm_GBs": round(gbs, 1), "hbm_frac": round(gbs / hbm_peak, 4), "tensor_TFLOPs": round(tfs, 1),
+                    "tensor_frac": round(tfs / tensor_peak, 4), "algorithmic_bytes_per_launch": byts,
+                    "flops_per_launch": flops, "traffic": None})
+    return {"gemms": out, "sum_us_per_layer": round(sum(g["avg_launch_us"] for g in out), 2),
+            "hbm_peak_source": hbm_src, "tensor_peak_source": tensor_src,
+            "how": "CUDA events around 3 passes of back-to-back launches over all layers' weights (PDL on, as in the "
+                   "captured step), per-launch average"}
+
 
 
 def _finish_multi_rank(world):
@@ -317,14 +396,18 @@ def run_gpu_arm(args, rank, world, local_rank):
     model, batch, ctx, quant, kvd = WORKLOADS[args.config]
     cfg = CONFIGS[model]
     bs = 16
-    bps = (ctx + bs - 1) // bs
+    # the context advances one token per step: room for every step this run makes (eager warm-up, graph warm-up,
+    # the timed steps, the e2e leg, the eager roofline replay) plus slack
+    headroom = ((args.warmup + 2 * args.steps + 24 + bs - 1) // bs + 1) * bs
+    bps = (ctx + headroom + bs - 1) // bs
     num_blocks = batch * bps + 64
     dec = Decoder(cfg, num_blocks, bs, kvd, quant, device=dev)
     dec.fill_kv_cache_random()
-    inp = StepInputs(batch, ctx, bs, num_blocks, cfg.vocab_size, dev)
-    meta = B200PagedAttentionMetadata(seq_lens_tensor=inp.d_sl, max_decode_seq_len=ctx, block_tables=inp.d_bt,
-                                      num_decode_tokens=batch, slot_mapping=inp.d_slots)
-    d_next = torch.empty(batch, dtype=torch.int64, device=dev)
+    inp = StepInputs(batch, ctx, bs, num_blocks, cfg.vocab_size, dev, headroom)
+    # max_decode_seq_len bounds EVERY replayed step (it sizes the split-K grid and partial buffers at capture)
+    meta = B200PagedAttentionMetadata(seq_lens_tensor=inp.d_sl, max_decode_seq_len=ctx + headroom,
+                                      block_tables=inp.d_bt, num_decode_tokens=batch, slot_mapping=inp.d_slots)
+    d_next = torch.empty(batch, 1, dtype=torch.int64, device=dev)
 
     # ---- count launches of OUR kernels in one step (host-side counter around the C ABI) -------------
     lib = _lib.load()
@@ -345,7 +428,10 @@ def run_gpu_arm(args, rank, world, local_rank):
             setattr(lib, name, mk(fn, name))
 
     def step():
-        d_next.copy_(dec.greedy_step(inp.d_ids, inp.d_pos, meta))
+        """One decode step + the on-device advance to the next one (sampled ids become the next input ids,
+        positions / seq_lens += 1, slots follow the block tables): replaying this graph IS the decode loop."""
+        d_next.copy_(dec.greedy_step(inp.d_ids, inp.d_pos, meta).view(batch, 1))
+        ops.advance_step_flashattn(batch, batch, bs, inp.d_ids, d_next, inp.d_pos, inp.d_sl, inp.d_slots, inp.d_bt)
 
     # eager warm-up (allocator, workspaces, NCCL), then capture the step in a CUDA graph
     side = torch.cuda.Stream(device=dev)
@@ -359,6 +445,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     torch.cuda.synchronize()
     for name, fn in wrapped.items():
         setattr(lib, name, fn)
+    inp.set_host_context(ctx)   # the two eager steps advanced the device state: start the captured loop at `ctx`
+    inp.upload()
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.graph(graph):
         step()
@@ -388,15 +476,20 @@ def run_gpu_arm(args, rank, world, local_rank):
         torch.cuda.profiler.stop()
     ms = e0.elapsed_time(e1) / args.steps
     # ---- e2e: host inputs every step, sampled ids back to the host every step -------------------------
+    def e2e_step():
+        inp.upload()                       # H2D: ids, positions, seq_lens, block tables, slots of THIS step
+        graph.replay()
+        inp.h_out.copy_(d_next.view(-1), non_blocking=True)   # D2H: sampled ids
+        torch.cuda.current_stream().synchronize()
+        inp.h_ids.copy_(inp.h_out)         # the host owns the loop: next ids / context from what came back
+        inp.set_host_context(inp.cur + 1)
+    inp.set_host_context(ctx + args.warmup + args.steps)   # carry on where the device loop stopped
     for _ in range(min(args.warmup, 3)):
-        inp.upload(); graph.replay(); inp.h_out.copy_(d_next, non_blocking=True); torch.cuda.current_stream().synchronize()
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        inp.upload()
-        graph.replay()
-        inp.h_out.copy_(d_next, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        e2e_step()
     e2e_s = (time.perf_counter() - t0) / args.steps
     barrier()
     clk = clocks.stop() if rank == 0 else None
@@ -421,6 +514,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         return r
     real_fd.forward_decode = staticmethod(timed_forward_decode)
     try:
+        inp.upload()
         for _ in range(max(2, min(args.steps, 5))):
             step()
         torch.cuda.synchronize()
@@ -429,9 +523,12 @@ def run_gpu_arm(args, rank, world, local_rank):
     attn_ms = [s.elapsed_time(e) for s, e in evs[len(dec.layers):]]  # drop the first step
     attn_s = statistics.mean(attn_ms) * 1e-3
     cache_bytes = 1 if kvd != "auto" else 2
-    algo = attention_algorithmic_bytes(batch, ctx, layer0.nh, layer0.nkv, cfg.head_dim, cache_bytes)
+    n_eager = len(evs) // len(dec.layers)
+    ctx_eager = inp.cur + (1 + n_eager - 1) / 2.0   # mean context of the timed eager steps (first one dropped)
+    algo = int(attention_algorithmic_bytes(batch, ctx_eager, layer0.nh, layer0.nkv, cfg.head_dim, cache_bytes))
     peak, peak_src = peaks()
     achieved = algo / attn_s / 1e9
+    gemm_rf = gemm_rooflines(dec, batch, peak, peak_src) if rank == 0 else None
     if rank != 0:
         _finish_multi_rank(world)
         return
@@ -457,6 +554,11 @@ def run_gpu_arm(args, rank, world, local_rank):
                             "step right after the timed region (the timed region itself is one CUDA graph)"},
         "clocks": clk,
     }
+    if gemm_rf is not None:
+        line["roofline_gemm"] = gemm_rf
+    line["config"]["allreduce"] = ("none" if world == 1 else "nccl" if peer_ar is None else
+                                   peer_ar.algo_name(batch, cfg.hidden_size, torch.bfloat16))
+    line["config"]["pdl"] = os.environ.get("VB200_PDL", "1") != "0"
     if world == 1 and not args.no_cpu_baseline:
         del dec
         torch.cuda.empty_cache()

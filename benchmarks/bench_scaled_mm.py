@@ -43,11 +43,14 @@ def timeit(fn, iters, warmup=3):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--M", default="16,64,128,256,1024,4096")
-    ap.add_argument("--shapes", default="qkv,o,gate_up,down")
+    ap.add_argument("--M", default="16,64,128,256")
+    ap.add_argument("--shapes", default="qkv,o,gate_up,down,70b_qkv,70b_o,70b_gate_up,70b_down")
     ap.add_argument("--iters", type=int, default=30)
     a = ap.parse_args()
     from vllm_b200 import _custom_ops as ops
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity_utils import load_ref_cutlass
+    ref = load_ref_cutlass()   # the reference's own sm100 CUTLASS kernel (scaled_mm_sm100_fp8_dispatch.cuh), or None
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     fp8_peak = 2 * peaks["bf16_tflops"]  # derived: fp8 dense = 2 x measured bf16 burst
     for name in a.shapes.split(","):
@@ -60,12 +63,18 @@ def main():
             sb = torch.rand(1, N, device="cuda") * 0.1 + 0.01
             t = timeit(lambda i: ops.cutlass_scaled_mm(x, ws[i % npool].t(), sa, sb, torch.bfloat16), a.iters)
             t2 = timeit(lambda i: torch._scaled_mm(x, ws[i % npool].t(), sa, sb, out_dtype=torch.bfloat16), a.iters)
+            t3 = None
+            if ref is not None:
+                o3 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+                t3 = timeit(lambda i: ref.cutlass_scaled_mm(o3, x, ws[i % npool].t(), sa, sb, None), a.iters)
             flops = 2.0 * M * N * K
             byts = M * K + N * K + 2 * M * N
             print(json.dumps({"shape": name, "M": M, "N": N, "K": K, "us": round(t * 1e6, 1),
                               "TFLOPs": round(flops / t / 1e12, 1), "frac_fp8_peak(2x_bf16_measured)": round(flops / t / 1e12 / fp8_peak, 3),
                               "GBs": round(byts / t / 1e9, 1), "frac_hbm": round(byts / t / 1e9 / peaks["hbm_gbs"], 3),
-                              "cublaslt_us": round(t2 * 1e6, 1), "speedup_vs_cublaslt": round(t2 / t, 2)}), flush=True)
+                              "cublaslt_us": round(t2 * 1e6, 1), "speedup_vs_cublaslt": round(t2 / t, 2),
+                              "ref_sm100_cutlass_us": None if t3 is None else round(t3 * 1e6, 1),
+                              "speedup_vs_ref_cutlass": None if t3 is None else round(t3 / t, 2)}), flush=True)
 
 
 if __name__ == "__main__":

@@ -81,6 +81,17 @@ int vb200_reshape_and_cache_flash(const void* key, const void* value, void* key_
                                   int kv_dtype, const float* k_scale, const float* v_scale,
                                   vb200_stream_t stream);
 
+/* RoPE + KV-cache write in one launch: exactly rotary_embedding(positions, query, key, head_size,
+ * cos_sin_cache, is_neox) (csrc/pos_encoding_kernels.cu:77-101,133-185) followed by reshape_and_cache(key, value, ...)
+ * (csrc/cache_kernels.cu:210-262) -- same bits in query, key and both caches as the two ops run back to back.
+ * query [T, num_heads*head_size], key / value [T, num_kv_heads*head_size] with the given token strides (elements),
+ * heads contiguous; paged cache layout as vb200_reshape_and_cache. */
+int vb200_rotary_embedding_reshape_and_cache(
+    const int64_t* positions, void* query, void* key, const void* value, const void* cos_sin_cache, void* key_cache,
+    void* value_cache, const int64_t* slot_mapping, int num_tokens, int num_heads, int num_kv_heads, int head_size,
+    int rot_dim, int is_neox, int block_size, int x, int64_t query_stride, int64_t key_stride, int64_t value_stride,
+    int src_dtype, int kv_dtype, const float* k_scale, const float* v_scale, vb200_stream_t stream);
+
 /* convert_fp8 (test helper of the reference): csrc/cache_kernels.cu:526-571, schema
  * csrc/torch_bindings.cpp:705-707.  Flat element-wise conversion of `numel` elements:
  *   src 16/32-bit -> dst fp8:   fp8_satfinite(float(src) / scale)
@@ -362,6 +373,16 @@ int vb200_peer_allreduce(int mode, void* out, const void* const* peer_data, void
                          int rank, int world, int rows, int hidden, int dtype, void* residual,
                          const void* weight, float epsilon, float* scales, const float* scale_ub,
                          vb200_stream_t stream);
+/* Two-shot variant (reference: cross_device_reduce_2stage, csrc/custom_all_reduce.cuh:320-360, chosen above
+ * 256 KB at 8 ranks / 512 KB at 4 ranks, :560-572): rank r reduces only its shard of rows into its GATHER buffer
+ * (peer_gather: HOST array of `world` device pointers, each at least rows*hidden elements, 16-byte aligned,
+ * peer-visible like peer_data), then every rank reads each row once from its owner and applies the same fused
+ * consumer.  Per GPU 2(N-1)/N of the tensor crosses NVLink instead of (N-1).  Same results bit for bit as
+ * vb200_peer_allreduce (the sum of a row is taken once, in rank order, by its owner). */
+int vb200_peer_allreduce_2shot(int mode, void* out, const void* const* peer_data, void* const* peer_gather,
+                               void* const* peer_signals, int rank, int world, int rows, int hidden, int dtype,
+                               void* residual, const void* weight, float epsilon, float* scales,
+                               const float* scale_ub, vb200_stream_t stream);
 
 #ifdef __cplusplus
 }

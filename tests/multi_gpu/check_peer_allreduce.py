@@ -32,8 +32,11 @@ def main():
             print(f"[rank {rank}] FAIL {name}", flush=True)
 
     gen = torch.Generator(device=dev)
-    for it, (T, H, dtype) in enumerate([(1, 256, torch.bfloat16), (256, 4096, torch.bfloat16), (37, 8192, torch.float16),
-                                        (300, 4096, torch.bfloat16), (256, 4096, torch.bfloat16), (8, 16384, torch.bfloat16)]):
+    cases = [(algo, c) for algo in ("1shot", "2shot") for c in [(1, 256, torch.bfloat16), (256, 4096, torch.bfloat16), (37, 8192, torch.float16),
+                                        (300, 4096, torch.bfloat16), (256, 4096, torch.bfloat16), (8, 16384, torch.bfloat16),
+                                                                (3, 512, torch.float16)]]
+    for it, (algo, (T, H, dtype)) in enumerate(cases):
+        par.algo = algo     # both kernels on every shape (one-shot and reduce-scatter + all-gather), interleaved below
         gen.manual_seed(100 * it + rank)
         x = torch.empty(T, H, device=dev, dtype=dtype).normal_(0, 1, generator=gen)
         gen.manual_seed(7 + it)            # replicated tensors: same on every rank
@@ -80,6 +83,18 @@ def main():
         d1, d2 = q1.float() * s1.view(-1, 1), q2.float() * s2.view(-1, 1)
         torch.testing.assert_close(d2, d1, rtol=0.13, atol=2e-2)      # one e4m3 step at most
         check(f"mode2 >= 99.5% identical codes {T}x{H}", (q1.view(torch.uint8) == q2.view(torch.uint8)).float().mean().item() >= 0.995)
+        if algo == "2shot":
+            # the two kernels sum in the same (rank) order and round at the same points: bit-identical results
+            par.algo = "1shot"
+            st.copy_(x)
+            g1 = par.all_reduce(st)
+            r3 = res.clone()
+            st.copy_(x)
+            q3, s3 = par.all_reduce_add_rms_norm_quant(st, r3, w, 1e-5)
+            check(f"2shot == 1shot bit for bit {T}x{H}", torch.equal(g1, got) and torch.equal(r3, r2) and torch.equal(s3, s2)
+                  and torch.equal(q3.view(torch.uint8), q2.view(torch.uint8)))
+            par.algo = "2shot"
+    par.algo = "auto"
     # graph replay: 3 fused all-reduces per replay, 50 replays, the input changes between replays
     T, H = 256, 4096
     x = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
@@ -88,10 +103,12 @@ def main():
     out = torch.zeros(T, H, device=dev, dtype=torch.bfloat16)
 
     def body():
-        for _ in range(3):
+        for i in range(4):
+            par.algo = "2shot" if i % 2 else "1shot"
             st = par.staging(T, H, torch.bfloat16)
             st.copy_(x)
             out.copy_(par.all_reduce(st))
+        par.algo = "auto"
     s = torch.cuda.Stream()
     with torch.cuda.stream(s):
         body()
@@ -131,6 +148,12 @@ def main():
                 st = par.staging(T, H, torch.bfloat16)
                 st.copy_(xs)
                 par.all_reduce_add_rms_norm_quant(st, res2, w, 1e-5)
+
+        def peer_path_2shot():
+            par.algo = "2shot"
+            peer_path()
+            par.algo = "1shot"
+        par.algo = "1shot"
         from vllm_b200 import _lib
         import ctypes
         tune = _lib.load().vb200_debug_peer_allreduce_tune
@@ -139,6 +162,8 @@ def main():
         variants = [("copy_only", clone_only, None), ("nccl_plus_norm_quant", nccl_path, None)]
         for blocks, staged in ((32, 1), (64, 1), (96, 1), (148, 1), (64, 0), (148, 0)):
             variants.append((f"peer_fused_b{blocks}_{'staged' if staged else 'direct'}", peer_path, (blocks, staged)))
+        for blocks in (64, 96, 148):
+            variants.append((f"peer_fused_2shot_b{blocks}", peer_path_2shot, (blocks, 0)))
         for name, fn, cfg_ in variants:
             if cfg_ is not None:
                 tune(*cfg_)
@@ -158,6 +183,7 @@ def main():
             torch.cuda.synchronize()
             times[name] = e0.elapsed_time(e1) * 1e3 / 200
         tune(0, 0)
+        par.algo = "auto"
         if rank == 0:
             print("[timing] us per op, [256 x 4096] bf16, world %d: %s (each path includes one 2 MiB device copy)" % (
                 world, {k: round(v, 2) for k, v in times.items()}), flush=True)

@@ -110,3 +110,20 @@ def test_attention_backend_interface():
     assert m.num_decode_tokens == 2 and m.max_decode_seq_len == 17 and m.prefill_metadata is None
     assert m.slot_mapping.tolist() == [9 * 16 + 0, 2 * 16 + 2]
     assert m.block_tables.tolist() == [[5, 9], [2, 0]] and m.seq_lens_tensor.tolist() == [17, 3]
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_tp_decode_matches_tp1_on_one_gpu(world):
+    """TP-N decode == TP-1 decode on the same (sharded) weights with N ranks sharing THIS GPU and a gloo all-reduce on
+    the host (tests/multi_gpu/check_tp_parity.py, TP_PARITY_BACKEND=gloo): the multi-rank correctness check a 1-GPU
+    box can run.  The NVLink / peer-kernel variants of the same script need >= 2 GPUs (test_gpu_peer_allreduce.py)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TP_PARITY_BACKEND="gloo", GLOO_SOCKET_IFNAME="lo")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
+           "127.0.0.1", "--master-port", str(29540 + world), os.path.join(root, "tests", "multi_gpu", "check_tp_parity.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "tp parity check: OK" in r.stdout

@@ -138,7 +138,8 @@ def test_rotary_embedding(dtype, neox, T, H, Hkv, D, rot):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("T,d", [(1, 14336), (256, 14336), (7, 1792), (5, 128), (3, 16384)])
+@pytest.mark.parametrize("T,d", [(1, 14336), (256, 14336), (7, 1792), (5, 128), (3, 16384), (64, 14336), (130, 7168),
+                                 (2048, 2048), (33, 3584)])
 def test_silu_and_mul_per_token_quant(dtype, T, d):
     """Bit-identical to silu_and_mul -> dynamic_per_token_scaled_fp8_quant run back to back (ours and the oracle)."""
     from vllm_b200 import _custom_ops as ops
@@ -154,3 +155,51 @@ def test_silu_and_mul_per_token_quant(dtype, T, d):
     wq, ws = oq.dynamic_per_token_scaled_fp8_quant(oq.silu_and_mul(x))
     torch.testing.assert_close(s.cpu(), ws, rtol=2.0 ** -7, atol=0)
     _fp8_close(q.cpu(), wq, frac=0.02)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("neox", [True, False])
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
+@pytest.mark.parametrize("T,H,Hkv,D,rot,bs", [(1, 32, 8, 128, 128, 16), (256, 32, 8, 128, 128, 16), (37, 12, 12, 64, 64, 32),
+                                              (9, 8, 2, 80, 32, 16), (4, 8, 1, 256, 128, 8)])
+def test_rotary_embedding_reshape_and_cache(dtype, neox, kv_cache_dtype, T, H, Hkv, D, rot, bs):
+    """The fused RoPE + KV-cache-write launch == rotary_embedding followed by reshape_and_cache, bit for bit, in q, k
+    and both caches (ours back to back, and the oracle); padding tokens (slot -1) are rotated but not cached."""
+    from oracle import cache as ocache
+    from vllm_b200 import _custom_ops as ops
+    fp8 = kv_cache_dtype == "fp8"
+    seed_all(T + H + D + bs)
+    cache = oln.make_cos_sin_cache(D, rot, 8192, 10000.0, dtype)
+    pos = torch.randint(0, 8192, (T,), dtype=torch.int64)
+    qkv = torch.randn(T, (H + 2 * Hkv) * D).to(dtype)
+    x = 16 if fp8 else 8
+    nb = (T + bs - 1) // bs + 3
+    cdt = torch.uint8 if fp8 else dtype
+    kc = torch.zeros(nb, Hkv, D // x, bs, x, dtype=cdt)
+    vc = torch.zeros(nb, Hkv, D, bs, dtype=cdt)
+    slots = torch.randperm(nb * bs)[:T].to(torch.int64)
+    if T > 4:
+        slots[2] = -1
+    ks, vs = torch.tensor(0.037 if fp8 else 1.0), torch.tensor(0.051 if fp8 else 1.0)
+    sl_q, sl_k, sl_v = slice(0, H * D), slice(H * D, (H + Hkv) * D), slice((H + Hkv) * D, (H + 2 * Hkv) * D)
+    # two launches
+    a = qkv.to(DEV)
+    kc_a, vc_a = kc.to(DEV), vc.to(DEV)
+    ops.rotary_embedding(pos.to(DEV), a[:, sl_q], a[:, sl_k], D, cache.to(DEV), neox)
+    ops.reshape_and_cache(a[:, sl_k].view(T, Hkv, D), a[:, sl_v].view(T, Hkv, D), kc_a, vc_a, slots.to(DEV),
+                          kv_cache_dtype, ks.to(DEV), vs.to(DEV))
+    # one launch
+    b = qkv.to(DEV)
+    kc_b, vc_b = kc.to(DEV), vc.to(DEV)
+    ops.rotary_embedding_reshape_and_cache(pos.to(DEV), b[:, sl_q], b[:, sl_k], b[:, sl_v], D, cache.to(DEV), neox,
+                                           kc_b, vc_b, slots.to(DEV), kv_cache_dtype, ks.to(DEV), vs.to(DEV))
+    torch.cuda.synchronize()
+    bits = (lambda t: t.view(torch.uint8)) if fp8 else (lambda t: t.view(torch.int16))
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16)), "q / k / v after the fused launch differ"
+    assert torch.equal(bits(kc_a), bits(kc_b)) and torch.equal(bits(vc_a), bits(vc_b)), "caches differ"
+    # oracle: rope then scatter on the CPU
+    wq, wk = oln.rotary_embedding(pos, qkv[:, sl_q], qkv[:, sl_k], D, cache, neox)
+    kc_o, vc_o = kc.clone(), vc.clone()
+    ocache.reshape_and_cache(wk.reshape(T, Hkv, D), qkv[:, sl_v].reshape(T, Hkv, D), kc_o, vc_o, slots, kv_cache_dtype, ks, vs)
+    assert torch.equal(b[:, sl_q].cpu().view(torch.int16), wq.contiguous().view(torch.int16))
+    assert torch.equal(bits(kc_b.cpu()), bits(kc_o)) and torch.equal(bits(vc_b.cpu()), bits(vc_o))

@@ -136,3 +136,33 @@ def test_scaled_mm_rejects_bad_inputs():
     with pytest.raises(RuntimeError, match="column-major"):
         ops.cutlass_scaled_mm(a, b2, s, s, torch.bfloat16)
     assert ops.cutlass_scaled_mm_supports_fp8(100) and not ops.cutlass_scaled_mm_supports_fp8(89)
+
+
+@pytest.mark.parametrize("M", [16, 64, 128, 256])
+@pytest.mark.parametrize("N,K", [(6144, 4096), (4096, 4096), (28672, 4096), (4096, 14336),      # Llama-3.1-8B
+                                 (1280, 8192), (8192, 1024), (7168, 8192), (8192, 3584)])       # Llama-3.1-70B / TP 8
+def test_scaled_mm_vs_reference_sm100_cutlass(M, N, K):
+    """Against the kernel SURVEY.md calls "the Blackwell kernel to beat": the reference's own sm100 CUTLASS
+    cutlass_scaled_mm (csrc/quantization/cutlass_w8a8/c3x/scaled_mm_sm100_fp8_dispatch.cuh:17-135) compiled from
+    /root/reference into oracle/_ref/libvllm_ref_cutlass.so, same inputs, at the decode batch sizes.  Both kernels
+    accumulate the same fp8 products in fp32 (in different orders) and round once to bf16: north_star bound
+    1e-2 rel / 2e-2 abs, and at least 99 % of the outputs identical to one bf16 ulp."""
+    from parity_utils import load_ref_cutlass
+    from vllm_b200 import _custom_ops as ops
+    ref = load_ref_cutlass()
+    if ref is None:
+        pytest.skip("oracle/_ref/libvllm_ref_cutlass.so not built / not loadable")
+    seed_all(M + N + K)
+    a = to_fp8(torch.randn(M, K, device=DEV))
+    b = to_fp8(torch.randn(N, K, device=DEV)).t()
+    sa = torch.rand(M, 1, device=DEV) * 0.1 + 0.01
+    sb = torch.rand(1, N, device=DEV) * 0.1 + 0.01
+    bias = (torch.rand(N, device=DEV) * 4).to(torch.bfloat16)
+    for use_bias in (False, True):
+        got = ops.cutlass_scaled_mm(a, b, sa, sb, torch.bfloat16, bias if use_bias else None)
+        want = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        ref.cutlass_scaled_mm(want, a, b, sa, sb, bias if use_bias else None)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(got.float(), want.float(), rtol=1e-2, atol=2e-2 * max(1.0, float(want.float().abs().mean())))
+        rel = (got.float() - want.float()).abs() / want.float().abs().clamp(min=1e-2)
+        assert (rel <= 2.0 ** -7).float().mean().item() >= 0.99

@@ -580,6 +580,45 @@ def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: Optional
             key.stride(0) if key is not None else 0, head_stride, dtype_enum(query.dtype), stream()))
 
 
+def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                                       value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool,
+                                       key_cache: torch.Tensor, value_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                                       kv_cache_dtype: str, k_scale: torch.Tensor, v_scale: torch.Tensor) -> None:
+    """One launch for `rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)` followed by
+    `reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale)` -- same
+    results bit for bit (reference kernels csrc/pos_encoding_kernels.cu:77-101 and
+    csrc/cache_kernels.cu:210-262).  query [T, H*D], key / value [T, Hkv*D] (or [T, heads, D]), heads contiguous."""
+    require_cuda(positions, query, key, value, cos_sin_cache, key_cache, value_cache, slot_mapping)
+    if positions.dtype != torch.int64 or positions.dim() != 1 or not positions.is_contiguous():
+        raise RuntimeError("positions must have shape [num_tokens] (contiguous int64)")
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape[0] != positions.numel():
+        raise RuntimeError("slot_mapping must be int64 with one entry per token")
+    T = positions.numel()
+    if query.shape[0] != T or key.shape[0] != T or value.shape[0] != T:
+        raise RuntimeError("query, key, value and positions must have the same number of tokens")
+    qh, kh = query.numel() // max(T, 1), key.numel() // max(T, 1)
+    if qh % head_size or kh % head_size or value.numel() // max(T, 1) != kh:
+        raise RuntimeError("rotary_embedding_reshape_and_cache: hidden sizes must be multiples of head_size")
+    num_heads, num_kv_heads = qh // head_size, kh // head_size
+    if cos_sin_cache.dtype != query.dtype or not cos_sin_cache.is_contiguous() or key.dtype != query.dtype \
+            or value.dtype != query.dtype:
+        raise RuntimeError("rotary_embedding_reshape_and_cache: query / key / value / cos_sin_cache dtypes differ")
+    for t in (query, key, value):
+        if t.stride(-1) != 1 or (t.dim() == 3 and t.stride(1) != head_size):
+            raise RuntimeError("rotary_embedding_reshape_and_cache: heads must be contiguous")
+    if not (key_cache.is_contiguous() and value_cache.is_contiguous()):
+        raise RuntimeError("rotary_embedding_reshape_and_cache: caches must be contiguous")
+    if key_cache.shape[1] != num_kv_heads or key_cache.shape[2] * key_cache.shape[4] != head_size:
+        raise RuntimeError("rotary_embedding_reshape_and_cache: key_cache shape does not match key")
+    block_size, x = key_cache.shape[3], key_cache.shape[4]
+    with _device_of(query):
+        check(load().vb200_rotary_embedding_reshape_and_cache(
+            ptr(positions), ptr(query), ptr(key), ptr(value), ptr(cos_sin_cache), ptr(key_cache), ptr(value_cache),
+            ptr(slot_mapping), T, num_heads, num_kv_heads, head_size, cos_sin_cache.shape[1], int(bool(is_neox)),
+            block_size, x, query.stride(0), key.stride(0), value.stride(0), dtype_enum(query.dtype),
+            kv_dtype_enum(kv_cache_dtype), ptr(k_scale), ptr(v_scale), stream()))
+
+
 def _norm_rows(op: str, input: torch.Tensor, weight: torch.Tensor):
     require_cuda(input, weight)
     hidden = input.shape[-1]

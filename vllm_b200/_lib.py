@@ -48,6 +48,9 @@ SIGNATURES = {
                                         c_int64, c_int, c_int, _P, _P, _P]),
     "vb200_reshape_and_cache_flash": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int64,
                                               c_int64, c_int64, c_int64, c_int64, c_int, c_int, _P, _P, _P]),
+    "vb200_rotary_embedding_reshape_and_cache": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
+                                                         c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int,
+                                                         c_int, _P, _P, _P]),
     "vb200_convert_fp8": (c_int, [_P, _P, c_int64, c_int, c_int, c_float, _P]),
     "vb200_paged_attention_v2": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float,
                                          _P, _P, c_int, c_int, c_int, _P, c_int, c_int, _P, _P, c_int64,
@@ -92,6 +95,8 @@ SIGNATURES = {
     "vb200_peer_buffer_free": (c_int, [_P]),
     "vb200_peer_allreduce": (c_int, [c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_float, _P, _P,
                                      _P]),
+    "vb200_peer_allreduce_2shot": (c_int, [c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_float, _P,
+                                           _P, _P]),
     "vb200_cutlass_moe_mm": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_int, _P]),
 }

@@ -4,6 +4,7 @@
 // a fresh design: one CTA per token, 16-byte vector loads of the source row, 16-byte stores of the
 // x-element K runs / flash rows, bit-exact copy (AUTO) or reference-exact fp8 quantisation.
 #include "common.cuh"
+#include "token_ops.cuh"
 
 namespace vb200 {
 
@@ -23,67 +24,48 @@ __global__ void __launch_bounds__(256) reshape_and_cache_kernel(
     const int64_t* __restrict__ slot_mapping, int64_t key_stride, int64_t value_stride,
     int num_heads, int head_size, int block_size, int x, const float* __restrict__ k_scale_p,
     const float* __restrict__ v_scale_p, bool vec_ok) {
-  using cache_t = typename std::conditional<FP8, uint8_t, scalar_t>::type;
-  cache_t* key_cache = reinterpret_cast<cache_t*>(key_cache_);
-  cache_t* value_cache = reinterpret_cast<cache_t*>(value_cache_);
+  pdl_wait();
+  pdl_trigger();
   const int64_t token_idx = blockIdx.x;
   const int64_t slot_idx = slot_mapping[token_idx];
   if (slot_idx < 0) return;  // padding token
-  const int64_t block_idx = slot_idx / block_size;
-  const int64_t block_offset = slot_idx % block_size;
-  const int n = num_heads * head_size;
   float k_scale = 1.f, v_scale = 1.f;
   if (FP8) {
     k_scale = *k_scale_p;
     v_scale = *v_scale_p;
   }
-  const scalar_t* ksrc = key + token_idx * key_stride;
-  const scalar_t* vsrc = value + token_idx * value_stride;
-  cache_t* kdst = key_cache + block_idx * (int64_t)n * block_size;
-  cache_t* vdst = value_cache + block_idx * (int64_t)n * block_size + block_offset;
+  scatter_token_paged<scalar_t, FP8>(key + token_idx * key_stride, value + token_idx * value_stride, key_cache_,
+                                     value_cache_, slot_idx, num_heads, head_size, block_size, x, k_scale, v_scale,
+                                     vec_ok);
+}
 
-  if (vec_ok) {
-    // K: one x-run (x * sizeof(cache_t) == 16 bytes) per thread-iteration.
-    const int runs = n / x;
-    const int runs_per_head = head_size / x;
-    for (int r = threadIdx.x; r < runs; r += blockDim.x) {
-      const int h = r / runs_per_head;
-      const int xi = r - h * runs_per_head;
-      const scalar_t* s = ksrc + (int64_t)r * x;
-      cache_t* d = kdst + ((int64_t)(h * runs_per_head + xi) * block_size + block_offset) * x;
-      if (!FP8) {
-        *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(s);
-      } else {
-        // x == 16 source elements -> 16 fp8 bytes
-        union { uint4 u; uint8_t b[16]; } o;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) o.b[j] = float_to_e4m3(to_float<scalar_t>(s[j]) / k_scale);
-        *reinterpret_cast<uint4*>(d) = o.u;
-      }
-    }
-  } else {
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const int h = i / head_size;
-      const int ho = i - h * head_size;
-      const int xi = ho / x, xo = ho - xi * x;
-      const int64_t t =
-          ((int64_t)(h * (head_size / x) + xi) * block_size + block_offset) * x + xo;
-      if (!FP8) {
-        kdst[t] = *reinterpret_cast<const cache_t*>(&ksrc[i]);
-      } else {
-        reinterpret_cast<uint8_t*>(kdst)[t] = float_to_e4m3(to_float<scalar_t>(ksrc[i]) / k_scale);
-      }
-    }
+// RoPE + KV-cache write in ONE launch: rotary_embedding(positions, q, k) in place, then
+// reshape_and_cache(k, v) of the same token.  Reference: /root/reference/csrc/pos_encoding_kernels.cu:77-101 followed
+// by /root/reference/csrc/cache_kernels.cu:210-262, two launches; the arithmetic (and so every bit of q, k and both
+// caches) is that of the two kernels run back to back -- the CTA that rotated a token's K re-reads it (bar.sync makes
+// its own global writes visible to all its threads) and scatters it.
+template <typename scalar_t, bool NEOX, bool FP8>
+__global__ void __launch_bounds__(256) rope_reshape_and_cache_kernel(
+    const int64_t* __restrict__ positions, scalar_t* query, scalar_t* key, const scalar_t* value,
+    const scalar_t* __restrict__ cos_sin_cache, void* __restrict__ key_cache_, void* __restrict__ value_cache_,
+    const int64_t* __restrict__ slot_mapping, int rot_dim, int64_t query_stride, int64_t key_stride,
+    int64_t value_stride, int num_heads, int num_kv_heads, int head_size, int block_size, int x,
+    const float* __restrict__ k_scale_p, const float* __restrict__ v_scale_p, bool vec_ok) {
+  pdl_wait();
+  pdl_trigger();
+  const int token = blockIdx.x;
+  rotate_token<scalar_t, NEOX>(token, positions, query, key, cos_sin_cache, rot_dim, query_stride, key_stride,
+                               (int64_t)head_size, num_heads, num_kv_heads);
+  const int64_t slot_idx = slot_mapping[token];
+  if (slot_idx < 0) return;  // padding token: rotated, not cached (what the two kernels would do)
+  __syncthreads();
+  float k_scale = 1.f, v_scale = 1.f;
+  if (FP8) {
+    k_scale = *k_scale_p;
+    v_scale = *v_scale_p;
   }
-  // V: element (h, d) lands at stride block_size -- inherent to the layout.
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    if (!FP8) {
-      vdst[(int64_t)i * block_size] = *reinterpret_cast<const cache_t*>(&vsrc[i]);
-    } else {
-      reinterpret_cast<uint8_t*>(vdst)[(int64_t)i * block_size] =
-          float_to_e4m3(to_float<scalar_t>(vsrc[i]) / v_scale);
-    }
-  }
+  scatter_token_paged<scalar_t, FP8>(key + token * key_stride, value + token * value_stride, key_cache_, value_cache_,
+                                     slot_idx, num_kv_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -97,6 +79,8 @@ __global__ void __launch_bounds__(256) reshape_and_cache_flash_kernel(
     int64_t head_stride, int64_t key_stride, int64_t value_stride, int num_heads, int head_size,
     int block_size, const float* __restrict__ k_scale_p, const float* __restrict__ v_scale_p,
     bool vec_ok) {
+  pdl_wait();
+  pdl_trigger();
   using cache_t = typename std::conditional<FP8, uint8_t, scalar_t>::type;
   cache_t* key_cache = reinterpret_cast<cache_t*>(key_cache_);
   cache_t* value_cache = reinterpret_cast<cache_t*>(value_cache_);
@@ -159,6 +143,8 @@ __global__ void __launch_bounds__(256) reshape_and_cache_flash_kernel(
 template <typename T>
 __global__ void to_fp8_kernel(uint8_t* __restrict__ dst, const T* __restrict__ src, int64_t n,
                               float scale) {
+  pdl_wait();
+  pdl_trigger();
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = float_to_e4m3(to_float<T>(src[i]) / scale);
@@ -166,6 +152,8 @@ __global__ void to_fp8_kernel(uint8_t* __restrict__ dst, const T* __restrict__ s
 template <typename T>
 __global__ void from_fp8_kernel(T* __restrict__ dst, const uint8_t* __restrict__ src, int64_t n,
                                 float scale) {
+  pdl_wait();
+  pdl_trigger();
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = from_float<T>(e4m3_to_float(src[i]) * scale);
@@ -209,14 +197,58 @@ extern "C" int vb200_reshape_and_cache(const void* key, const void* value, void*
   const int threads = n >= 1024 ? 256 : (n >= 256 ? 128 : 64);
   DISPATCH_SRC(src_dtype, {
     if (fp8)
-      reshape_and_cache_kernel<scalar_t, true><<<num_tokens, threads, 0, stream>>>(
-          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
-          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
+      VB_CUDA_CHECK(launch_k(reshape_and_cache_kernel<scalar_t, true>, dim3(num_tokens), dim3(threads), 0, stream, (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok));
     else
-      reshape_and_cache_kernel<scalar_t, false><<<num_tokens, threads, 0, stream>>>(
-          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
-          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
+      VB_CUDA_CHECK(launch_k(reshape_and_cache_kernel<scalar_t, false>, dim3(num_tokens), dim3(threads), 0, stream, (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+          key_stride, value_stride, num_heads, head_size, block_size, x, k_scale, v_scale, vec_ok));
   });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_rotary_embedding_reshape_and_cache(
+    const int64_t* positions, void* query, void* key, const void* value, const void* cos_sin_cache, void* key_cache,
+    void* value_cache, const int64_t* slot_mapping, int num_tokens, int num_heads, int num_kv_heads, int head_size,
+    int rot_dim, int is_neox, int block_size, int x, int64_t query_stride, int64_t key_stride, int64_t value_stride,
+    int src_dtype, int kv_dtype, const float* k_scale, const float* v_scale, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(src_dtype == VB200_F16 || src_dtype == VB200_BF16,
+           "rotary_embedding_reshape_and_cache: dtype must be f16 or bf16");
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3,
+           "Unsupported data type of kv cache: %d", kv_dtype);
+  VB_CHECK(rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_size,
+           "rotary_embedding_reshape_and_cache: rot_dim %d must be even and <= head_size %d", rot_dim, head_size);
+  VB_CHECK(x > 0 && head_size % x == 0, "head_size %d must be a multiple of x %d", head_size, x);
+  VB_CHECK(key != nullptr && value != nullptr, "rotary_embedding_reshape_and_cache: key and value are required");
+  if (num_tokens <= 0) return 0;
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (k_scale && v_scale), "fp8 kv cache needs k_scale and v_scale");
+  const int cache_elt = fp8 ? 1 : 2;
+  bool vec_ok = (x * cache_elt == 16) && aligned16(key) && aligned16(key_cache) && ((key_stride * 2) % 16 == 0);
+  if (fp8) vec_ok = vec_ok && (x == 16);
+  const int work = (num_heads + num_kv_heads) * rot_dim / 2;
+  const int threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
+#define VB_ROPE_CACHE(T, NEOX, FP8)                                                                                  \
+  VB_CUDA_CHECK(launch_k(rope_reshape_and_cache_kernel<T, NEOX, FP8>, dim3(num_tokens), dim3(threads), 0, stream,     \
+                         positions, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, key_cache,          \
+                         value_cache, slot_mapping, rot_dim, query_stride, key_stride, value_stride, num_heads,       \
+                         num_kv_heads, head_size, block_size, x, k_scale, v_scale, vec_ok))
+#define VB_ROPE_CACHE_T(T)                          \
+  if (is_neox) {                                    \
+    if (fp8) VB_ROPE_CACHE(T, true, true);          \
+    else VB_ROPE_CACHE(T, true, false);             \
+  } else {                                          \
+    if (fp8) VB_ROPE_CACHE(T, false, true);         \
+    else VB_ROPE_CACHE(T, false, false);            \
+  }
+  if (src_dtype == VB200_F16) {
+    VB_ROPE_CACHE_T(__half)
+  } else {
+    VB_ROPE_CACHE_T(__nv_bfloat16)
+  }
+#undef VB_ROPE_CACHE_T
+#undef VB_ROPE_CACHE
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -247,15 +279,13 @@ extern "C" int vb200_reshape_and_cache_flash(const void* key, const void* value,
   const int threads = n >= 1024 ? 256 : (n >= 256 ? 128 : 64);
   DISPATCH_SRC(src_dtype, {
     if (fp8)
-      reshape_and_cache_flash_kernel<scalar_t, true><<<num_tokens, threads, 0, stream>>>(
-          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+      VB_CUDA_CHECK(launch_k(reshape_and_cache_flash_kernel<scalar_t, true>, dim3(num_tokens), dim3(threads), 0, stream, (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
           block_stride, page_stride, head_stride, key_stride, value_stride, num_heads, head_size,
-          block_size, k_scale, v_scale, vec_ok);
+          block_size, k_scale, v_scale, vec_ok));
     else
-      reshape_and_cache_flash_kernel<scalar_t, false><<<num_tokens, threads, 0, stream>>>(
-          (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
+      VB_CUDA_CHECK(launch_k(reshape_and_cache_flash_kernel<scalar_t, false>, dim3(num_tokens), dim3(threads), 0, stream, (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping,
           block_stride, page_stride, head_stride, key_stride, value_stride, num_heads, head_size,
-          block_size, k_scale, v_scale, vec_ok);
+          block_size, k_scale, v_scale, vec_ok));
   });
   VB_LAUNCH_CHECK();
   return 0;
@@ -271,15 +301,13 @@ extern "C" int vb200_convert_fp8(void* dst, const void* src, int64_t numel, int 
                                : 148 * 16);
   if (dst_dtype == VB200_FP8_E4M3) {
     DISPATCH_SRC(src_dtype, {
-      to_fp8_kernel<scalar_t>
-          <<<blocks, threads, 0, stream>>>((uint8_t*)dst, (const scalar_t*)src, numel, scale);
+      VB_CUDA_CHECK(launch_k(to_fp8_kernel<scalar_t>, dim3(blocks), dim3(threads), 0, stream, (uint8_t*)dst, (const scalar_t*)src, numel, scale));
     });
   } else {
     VB_CHECK(src_dtype == VB200_FP8_E4M3, "convert_fp8: one side must be fp8 (src %d dst %d)",
              src_dtype, dst_dtype);
     DISPATCH_SRC(dst_dtype, {
-      from_fp8_kernel<scalar_t>
-          <<<blocks, threads, 0, stream>>>((scalar_t*)dst, (const uint8_t*)src, numel, scale);
+      VB_CUDA_CHECK(launch_k(from_fp8_kernel<scalar_t>, dim3(blocks), dim3(threads), 0, stream, (scalar_t*)dst, (const uint8_t*)src, numel, scale));
     });
   }
   VB_LAUNCH_CHECK();

@@ -47,6 +47,56 @@ inline int num_sms() {
   return n;
 }
 
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------
+// Every kernel of the library starts with pdl_wait() (griddepcontrol.wait: the grids it depends on have completed
+// and their memory is visible) before it touches global memory, then pdl_trigger() (the NEXT kernel on the stream
+// may be scheduled; its CTAs park at their own pdl_wait()).  Host side, launch_k() adds
+// cudaLaunchAttributeProgrammaticStreamSerialization, so the launch latency and the prologue (barrier init, TMEM
+// allocation, tensor-map prefetch) of kernel i+1 overlap the tail of kernel i -- also inside captured CUDA graphs,
+// where the attribute becomes a programmatic dependency edge.  Both instructions are no-ops for a kernel that was
+// launched without the attribute.  VB200_PDL=0 turns the attribute off.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // runtime.cu
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// Same, for a kernel whose CTAs form clusters of `cluster_x` along x (grid.x must be a multiple of it).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k_cluster(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                    unsigned cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster_x;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ---- scalar conversions ----------------------------------------------------------------------
 template <typename T>
 __device__ __forceinline__ float to_float(T v);

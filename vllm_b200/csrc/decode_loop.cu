@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256) advance_step_kernel(
     const int64_t* __restrict__ sampled_token_ids, int64_t* __restrict__ input_positions,
     int* __restrict__ seq_lens, int64_t* __restrict__ slot_mapping, const int* __restrict__ block_tables,
     int64_t block_tables_stride) {
+  pdl_wait();
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= num_seqs) return;
   if (i >= num_queries) {  // CUDA-graph padding rows (advance_step.cu:21-30)
@@ -39,6 +41,8 @@ __global__ void __launch_bounds__(128) merge_attn_states_kernel(
     T* __restrict__ output, float* __restrict__ output_lse, const T* __restrict__ prefix_output,
     const float* __restrict__ prefix_lse, const T* __restrict__ suffix_output,
     const float* __restrict__ suffix_lse, unsigned num_tokens, unsigned num_heads, unsigned head_size) {
+  pdl_wait();
+  pdl_trigger();
   constexpr unsigned kPack = 16 / sizeof(T);
   const unsigned threads_per_head = head_size / kPack;
   const unsigned gid = blockIdx.x * 128u + threadIdx.x;
@@ -83,9 +87,8 @@ extern "C" int vb200_advance_step_flashattn(int num_seqs, int num_queries, int b
   VB_CHECK(num_queries >= 0 && num_seqs >= num_queries, "advance_step_flashattn: need 0 <= num_queries <= num_seqs");
   VB_CHECK(block_size > 0, "advance_step_flashattn: bad block_size %d", block_size);
   if (num_seqs == 0) return 0;
-  advance_step_kernel<<<(num_seqs + 255) / 256, 256, 0, stream>>>(
-      num_seqs, num_queries, block_size, input_tokens, sampled_token_ids, input_positions, seq_lens, slot_mapping,
-      block_tables, block_tables_stride);
+  VB_CUDA_CHECK(launch_k(advance_step_kernel, dim3((num_seqs + 255) / 256), dim3(256), 0, stream, num_seqs, num_queries, block_size, input_tokens, sampled_token_ids, input_positions, seq_lens, slot_mapping,
+      block_tables, block_tables_stride));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -106,9 +109,9 @@ extern "C" int vb200_merge_attn_states(void* output, float* output_lse, const vo
   const long total = (long)num_tokens * num_heads * (head_size / pack);
   const unsigned grid = (unsigned)((total + 127) / 128);
 #define VB_MERGE(T)                                                                                       \
-  merge_attn_states_kernel<T><<<grid, 128, 0, stream>>>((T*)output, output_lse, (const T*)prefix_output, \
+  VB_CUDA_CHECK(launch_k(merge_attn_states_kernel<T>, dim3(grid), dim3(128), 0, stream, (T*)output, output_lse, (const T*)prefix_output, \
                                                         prefix_lse, (const T*)suffix_output, suffix_lse, \
-                                                        num_tokens, num_heads, head_size)
+                                                        num_tokens, num_heads, head_size))
   if (dtype == VB200_F32) VB_MERGE(float);
   else if (dtype == VB200_F16) VB_MERGE(__half);
   else VB_MERGE(__nv_bfloat16);

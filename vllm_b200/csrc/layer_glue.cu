@@ -14,6 +14,7 @@
 // three), which is what makes these launch-latency-bound rather than bandwidth-bound at decode
 // batch sizes.
 #include "common.cuh"
+#include "token_ops.cuh"
 
 namespace vb200 {
 
@@ -51,6 +52,8 @@ __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
     void* __restrict__ out_, T* __restrict__ input, T* __restrict__ residual,
     const T* __restrict__ weight, float* __restrict__ scales, const float* __restrict__ scale_ub,
     float eps, int hidden, int64_t input_stride) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sm[8];
   const int64_t row = blockIdx.x;
   T* in = input + row * input_stride;
@@ -131,45 +134,41 @@ __global__ void __launch_bounds__(256) rotary_kernel(
     const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
     const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride, int64_t key_stride,
     int64_t head_stride, int num_heads, int num_kv_heads) {
-  const int token = blockIdx.x;
-  const int64_t pos = positions[token];
-  const T* cache = cos_sin_cache + pos * rot_dim;
-  const int embed = rot_dim >> 1;
-  const int total = (num_heads + (key ? num_kv_heads : 0)) * embed;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int head = i / embed;
-    const int off = i - head * embed;
-    T* arr = head < num_heads ? query + token * query_stride + head * head_stride
-                              : key + token * key_stride + (head - num_heads) * head_stride;
-    const int xi = NEOX ? off : 2 * off;
-    const int yi = NEOX ? embed + off : 2 * off + 1;
-    const float c = to_float<T>(cache[off]);
-    const float s = to_float<T>(cache[embed + off]);
-    const float x = to_float<T>(arr[xi]);
-    const float y = to_float<T>(arr[yi]);
-    const float xc = to_float<T>(from_float<T>(x * c)), ys = to_float<T>(from_float<T>(y * s));
-    const float yc = to_float<T>(from_float<T>(y * c)), xs = to_float<T>(from_float<T>(x * s));
-    arr[xi] = from_float<T>(xc - ys);
-    arr[yi] = from_float<T>(yc + xs);
-  }
+  pdl_wait();
+  pdl_trigger();
+  rotate_token<T, NEOX>(blockIdx.x, positions, query, key, cos_sin_cache, rot_dim, query_stride, key_stride,
+                        head_stride, num_heads, num_kv_heads);
 }
 
 // silu_and_mul followed by dynamic per-token fp8 quant in ONE pass: act = T(T(silu(x)) * y) is
 // kept in registers, amax reduced, then quantised with the true division of common.cu:74.
 // Bit-identical to silu_and_mul -> dynamic_per_token_scaled_fp8_quant run back to back.
-template <typename T>
+// The kernel is INSTRUCTION-bound, not bandwidth-bound (precise expf + two IEEE divisions per element, ~50
+// instructions each; round 1 measured 1.3 TB/s with one CTA per row: 256 rows on 148 SMs leave 40 SMs with twice the
+// work).  A row is therefore cut into SPLIT column slices, one CTA each, the SPLIT CTAs of a row forming a thread-
+// block cluster that exchanges its slice maxima through distributed shared memory (one st.shared::cluster per peer +
+// one cluster barrier) -- rows x SPLIT CTAs spread evenly over all SMs.
+template <typename T, int SPLIT>
 __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
     uint8_t* __restrict__ out, float* __restrict__ scales, const T* __restrict__ in,
     const float* __restrict__ scale_ub, int d) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sm[8];
-  const int64_t row = blockIdx.x;
-  const T* x = in + row * 2 * d;
+  __shared__ float peer_max[8];
+  // "I have started" (non-blocking): a peer may write my shared memory only once I am running
+  if (SPLIT > 1) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  const int64_t row = blockIdx.x / SPLIT;
+  const int part = blockIdx.x % SPLIT;     // == %cluster_ctarank (clusters are SPLIT consecutive CTAs along x)
+  const int dpart = d / SPLIT;             // host guarantees d % (8 * SPLIT) == 0
+  const T* x = in + row * 2 * d + part * dpart;
   const T* y = x + d;
-  const int nvec = d >> 3;
-  float act[kMaxVecPerThread][8];
+  const int nvec = dpart >> 3;
+  constexpr int kVec = kMaxVecPerThread / (SPLIT > 1 ? 2 : 1);
+  float act[kVec][8];
   float amax = 0.f;
 #pragma unroll
-  for (int k = 0; k < kMaxVecPerThread; ++k) {
+  for (int k = 0; k < kVec; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
       Vec8<T> a, b;
@@ -185,12 +184,25 @@ __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
     }
   }
   amax = block_reduce<true>(amax, sm);
+  if (SPLIT > 1) {
+    // every CTA of the cluster posts its slice maximum into slot `part` of every CTA's peer_max[]
+    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // all peers have started
+    if (threadIdx.x < SPLIT) {
+      uint32_t local = static_cast<uint32_t>(__cvta_generic_to_shared(&peer_max[part])), remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(amax) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+#pragma unroll
+    for (int r = 0; r < SPLIT; ++r) amax = fmaxf(amax, peer_max[r]);
+  }
   float s = scale_ub ? fminf(amax, *scale_ub) : amax;
   s = fmaxf(s / kFp8MaxG, 1.0f / (kFp8MaxG * 512.0f));
-  if (threadIdx.x == 0) scales[row] = s;
-  uint8_t* o = out + row * d;
+  if (threadIdx.x == 0 && part == 0) scales[row] = s;
+  uint8_t* o = out + row * d + part * dpart;
 #pragma unroll
-  for (int k = 0; k < kMaxVecPerThread; ++k) {
+  for (int k = 0; k < kVec; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
       union { uint2 u; uint8_t b[8]; } q;
@@ -230,8 +242,7 @@ extern "C" int vb200_rms_norm(void* out, const void* input, const void* weight, 
   if (num_tokens <= 0) return 0;
   if (check_row("rms_norm", hidden_size, dtype, out, input)) return 1;
   VB_CHECK(input_stride % 8 == 0, "rms_norm: input stride must be a multiple of 8");
-  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 0><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
-                         out, (scalar_t*)input, nullptr, (const scalar_t*)weight, nullptr, nullptr,
+  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 0>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, nullptr, (const scalar_t*)weight, nullptr, nullptr,
                          epsilon, hidden_size, input_stride)));
   VB_LAUNCH_CHECK();
   return 0;
@@ -243,8 +254,7 @@ extern "C" int vb200_fused_add_rms_norm(void* input, void* residual, const void*
   if (num_tokens <= 0) return 0;
   if (check_row("fused_add_rms_norm", hidden_size, dtype, input, residual)) return 1;
   VB_CHECK(input_stride % 8 == 0, "fused_add_rms_norm: input stride must be a multiple of 8");
-  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 1><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
-                         nullptr, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight,
+  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 1>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, nullptr, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight,
                          nullptr, nullptr, epsilon, hidden_size, input_stride)));
   VB_LAUNCH_CHECK();
   return 0;
@@ -259,8 +269,7 @@ extern "C" int vb200_rms_norm_dynamic_per_token_quant(void* out, const void* inp
   if (num_tokens <= 0) return 0;
   if (check_row("rms_norm_dynamic_per_token_quant", hidden_size, dtype, input, residual)) return 1;
   VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "rms_norm_dynamic_per_token_quant: out must be 8-byte aligned");
-  DISPATCH_16(dtype, (rms_norm_kernel<scalar_t, 2><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
-                         out, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, scales,
+  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 2>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, scales,
                          scale_ub, epsilon, hidden_size, (int64_t)hidden_size)));
   VB_LAUNCH_CHECK();
   return 0;
@@ -279,13 +288,11 @@ extern "C" int vb200_rotary_embedding(const int64_t* positions, void* query, voi
   const int threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
   DISPATCH_16(dtype, {
     if (is_neox)
-      rotary_kernel<scalar_t, true><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
-          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
-          query_stride, key_stride, head_stride, num_heads, num_kv_heads);
+      VB_CUDA_CHECK(launch_k(rotary_kernel<scalar_t, true>, dim3(num_tokens), dim3(threads), 0, (cudaStream_t)stream, positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
+          query_stride, key_stride, head_stride, num_heads, num_kv_heads));
     else
-      rotary_kernel<scalar_t, false><<<num_tokens, threads, 0, (cudaStream_t)stream>>>(
-          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
-          query_stride, key_stride, head_stride, num_heads, num_kv_heads);
+      VB_CUDA_CHECK(launch_k(rotary_kernel<scalar_t, false>, dim3(num_tokens), dim3(threads), 0, (cudaStream_t)stream, positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim,
+          query_stride, key_stride, head_stride, num_heads, num_kv_heads));
   });
   VB_LAUNCH_CHECK();
   return 0;
@@ -299,8 +306,25 @@ extern "C" int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scal
   if (num_tokens <= 0) return 0;
   if (check_row("silu_and_mul_dynamic_per_token_quant", d, dtype, input, input)) return 1;
   VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "silu_and_mul_dynamic_per_token_quant: out must be 8-byte aligned");
-  DISPATCH_16(dtype, (silu_mul_quant_kernel<scalar_t><<<num_tokens, kGlueThreads, 0, (cudaStream_t)stream>>>(
-                         (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, d)));
+  // column slices per row: enough CTAs to give every SM about six (see the kernel comment); a slice must keep whole
+  // 16-byte vectors and, when split, fit half the register budget of an unsplit row
+  int split = 1;
+  const int want = (6 * num_sms() + num_tokens - 1) / num_tokens;
+  for (int s = 2; s <= 8; s *= 2)
+    if (s <= want && d % (8 * s) == 0 && d / s >= 1024) split = s;
+  const dim3 grid((unsigned)num_tokens * split), block(kGlueThreads);
+#define VB_SILU_Q(S)                                                                                               \
+  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k_cluster(silu_mul_quant_kernel<scalar_t, S>, grid, block, 0,             \
+                                                    (cudaStream_t)stream, S, (uint8_t*)out, scales,                 \
+                                                    (const scalar_t*)input, scale_ub, d)))
+  if (split == 8) { VB_SILU_Q(8); }
+  else if (split == 4) { VB_SILU_Q(4); }
+  else if (split == 2) { VB_SILU_Q(2); }
+  else {
+    DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(silu_mul_quant_kernel<scalar_t, 1>, grid, block, 0, (cudaStream_t)stream,
+                                              (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, d)));
+  }
+#undef VB_SILU_Q
   VB_LAUNCH_CHECK();
   return 0;
 }

@@ -55,6 +55,8 @@ __global__ void __launch_bounds__(256) moe_gather_rows_kernel(
     uint8_t* __restrict__ a_sorted, const uint8_t* __restrict__ a,
     const int32_t* __restrict__ sorted_token_ids, const int32_t* __restrict__ num_tokens_post_pad,
     int num_valid_tokens, int top_k, int K, int sorted_capacity) {
+  pdl_wait();
+  pdl_trigger();
   const int npost = min(*num_tokens_post_pad, sorted_capacity);
   const int vec_per_row = K >> 4;
   for (int r = blockIdx.x; r < npost; r += gridDim.x) {
@@ -70,6 +72,8 @@ template <typename OutT>
 __global__ void __launch_bounds__(kMoeThreads, 2)
     moe_grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w,
                             const __grid_constant__ CUtensorMap tmap_a, const MoeParams p) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -311,11 +315,11 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
   if (out_dtype == VB200_BF16) {
     auto kern = moe_grouped_gemm_kernel<__nv_bfloat16>;
     VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+    VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kMoeThreads), smem, stream, tw, ta, p));
   } else {
     auto kern = moe_grouped_gemm_kernel<__half>;
     VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    kern<<<grid, kMoeThreads, smem, stream>>>(tw, ta, p);
+    VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kMoeThreads), smem, stream, tw, ta, p));
   }
   VB_LAUNCH_CHECK();
   return 0;
@@ -353,9 +357,8 @@ extern "C" int vb200_moe_grouped_gemm_fp8(
   VB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0, "moe_grouped_gemm_fp8: A must be 16-byte aligned");
   {
     int grid = sorted_capacity < num_sms() * 8 ? sorted_capacity : num_sms() * 8;
-    moe_gather_rows_kernel<<<grid, K >= 4096 ? 256 : 128, 0, stream>>>(
-        a_sorted, reinterpret_cast<const uint8_t*>(a), sorted_token_ids, num_tokens_post_pad,
-        num_valid_tokens, top_k, K, sorted_capacity);
+    VB_CUDA_CHECK(launch_k(moe_gather_rows_kernel, dim3(grid), dim3(K >= 4096 ? 256 : 128), 0, stream, a_sorted, reinterpret_cast<const uint8_t*>(a), sorted_token_ids, num_tokens_post_pad,
+        num_valid_tokens, top_k, K, sorted_capacity));
     VB_LAUNCH_CHECK();
   }
   const int m_blocks = (sorted_capacity + block_m - 1) / block_m;

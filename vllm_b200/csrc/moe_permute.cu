@@ -19,6 +19,8 @@ __global__ void __launch_bounds__(kDataThreads) moe_mm_data_kernel(
     int* __restrict__ expert_offsets, int* __restrict__ problem_sizes1, int* __restrict__ problem_sizes2,
     int* __restrict__ input_permutation, int* __restrict__ output_permutation,
     int* __restrict__ blockscale_offsets) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ int sm[];
   int* hist = sm;
   int* start = hist + num_experts;
@@ -104,6 +106,8 @@ __global__ void moe_pplx_data_kernel(int* __restrict__ expert_offsets, int* __re
                                      int* __restrict__ problem_sizes2,
                                      const int* __restrict__ expert_num_tokens, int num_local_experts,
                                      int padded_m, int n, int k) {
+  pdl_wait();
+  pdl_trigger();
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= num_local_experts) return;
   expert_offsets[e] = e * padded_m;
@@ -122,6 +126,8 @@ __global__ void __launch_bounds__(256) shuffle_rows_kernel(uint8_t* __restrict__
                                                            const uint8_t* __restrict__ in,
                                                            const int* __restrict__ dst2src, int num_dst,
                                                            int num_src, int64_t row_bytes) {
+  pdl_wait();
+  pdl_trigger();
   const int64_t nvec = row_bytes / (int64_t)sizeof(V);
   for (int r = blockIdx.x; r < num_dst; r += gridDim.x) {
     const int s = dst2src[r];
@@ -152,10 +158,10 @@ extern "C" int vb200_get_cutlass_moe_mm_data(const int32_t* topk_ids, int num_to
   if (smem > 48 * 1024)
     VB_CUDA_CHECK(cudaFuncSetAttribute(moe_mm_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-  moe_mm_data_kernel<<<1, kDataThreads, smem, stream>>>(topk_ids, numel, topk, num_experts, n, k, swap_ab,
+  VB_CUDA_CHECK(launch_k(moe_mm_data_kernel, dim3(1), dim3(kDataThreads), smem, stream, topk_ids, numel, topk, num_experts, n, k, swap_ab,
                                                         expert_offsets, problem_sizes1, problem_sizes2,
                                                         input_permutation, output_permutation,
-                                                        blockscale_offsets);
+                                                        blockscale_offsets));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -166,8 +172,7 @@ extern "C" int vb200_get_cutlass_pplx_moe_mm_data(int32_t* expert_offsets, int32
                                                   int padded_m, int n, int k, vb200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   VB_CHECK(num_local_experts >= 1, "get_cutlass_pplx_moe_mm_data: no experts");
-  moe_pplx_data_kernel<<<(num_local_experts + 127) / 128, 128, 0, stream>>>(
-      expert_offsets, problem_sizes1, problem_sizes2, expert_num_tokens, num_local_experts, padded_m, n, k);
+  VB_CUDA_CHECK(launch_k(moe_pplx_data_kernel, dim3((num_local_experts + 127) / 128), dim3(128), 0, stream, expert_offsets, problem_sizes1, problem_sizes2, expert_num_tokens, num_local_experts, padded_m, n, k));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -183,11 +188,10 @@ extern "C" int vb200_shuffle_rows(void* out, const void* in, const int32_t* dst2
   uint8_t* o = reinterpret_cast<uint8_t*>(out);
   const uint8_t* i = reinterpret_cast<const uint8_t*>(in);
   if (vec)
-    shuffle_rows_kernel<uint4><<<grid, row_bytes >= 4096 ? 256 : 128, 0, stream>>>(
-        o, i, dst2src_map, num_dst_rows, num_src_rows, row_bytes);
+    VB_CUDA_CHECK(launch_k(shuffle_rows_kernel<uint4>, dim3(grid), dim3(row_bytes >= 4096 ? 256 : 128), 0, stream, o, i, dst2src_map, num_dst_rows, num_src_rows, row_bytes));
   else
-    shuffle_rows_kernel<uint8_t><<<grid, 256, 0, stream>>>(o, i, dst2src_map, num_dst_rows, num_src_rows,
-                                                           row_bytes);
+    VB_CUDA_CHECK(launch_k(shuffle_rows_kernel<uint8_t>, dim3(grid), dim3(256), 0, stream, o, i, dst2src_map, num_dst_rows, num_src_rows,
+                                                           row_bytes));
   VB_LAUNCH_CHECK();
   return 0;
 }

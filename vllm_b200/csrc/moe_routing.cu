@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(128) topk_softmax_kernel(
     float* __restrict__ topk_weights, IndT* __restrict__ topk_indices,
     int* __restrict__ token_expert_indices, const float* __restrict__ gating, int num_tokens,
     int num_experts, int topk) {
+  pdl_wait();
+  pdl_trigger();
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= num_tokens) return;
   const int lane = threadIdx.x & 31;
@@ -91,6 +93,8 @@ __global__ void __launch_bounds__(kAlignThreads) moe_align_kernel(
     const int* __restrict__ topk_ids, int numel, int num_experts, int block_size,
     int* __restrict__ sorted_token_ids, int sorted_capacity, int* __restrict__ expert_ids,
     int expert_ids_capacity, int* __restrict__ num_tokens_post_pad) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ int sm[];
   int* hist = sm;                          // [E]
   int* start = hist + num_experts;         // [E + 1] padded exclusive prefix
@@ -193,6 +197,8 @@ __global__ void __launch_bounds__(kAlignThreads) moe_align_kernel(
 template <typename T, int TOPK>
 __global__ void __launch_bounds__(256) moe_sum_kernel(T* __restrict__ out,
                                                       const T* __restrict__ in, int topk, int d) {
+  pdl_wait();
+  pdl_trigger();
   const int64_t t = blockIdx.x;
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
     if (TOPK > 0) {
@@ -222,7 +228,7 @@ static int launch_topk(float* w, void* idx, int* tei, const float* g, int T, int
   const int vpt = (E + 31) / 32;
 #define TOPK_CASE(V)                                                                      \
   if (vpt <= V) {                                                                         \
-    topk_softmax_kernel<V, IndT><<<grid, 128, 0, s>>>(w, (IndT*)idx, tei, g, T, E, k);    \
+    VB_CUDA_CHECK(launch_k(topk_softmax_kernel<V, IndT>, dim3(grid), dim3(128), 0, s, w, (IndT*)idx, tei, g, T, E, k));    \
     VB_LAUNCH_CHECK();                                                                    \
     return 0;                                                                             \
   }
@@ -279,10 +285,10 @@ extern "C" int vb200_moe_align_block_size(const int32_t* topk_ids, int numel, in
     VB_CUDA_CHECK(cudaFuncSetAttribute(moe_align_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
-  moe_align_kernel<<<1, kAlignThreads, smem, stream>>>(topk_ids, numel, num_experts, block_size,
+  VB_CUDA_CHECK(launch_k(moe_align_kernel, dim3(1), dim3(kAlignThreads), smem, stream, topk_ids, numel, num_experts, block_size,
                                                        sorted_token_ids, sorted_capacity,
                                                        expert_ids, expert_ids_capacity,
-                                                       num_tokens_post_pad);
+                                                       num_tokens_post_pad));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -304,10 +310,10 @@ extern "C" int vb200_moe_sum(void* out, const void* input, int num_tokens, int t
     scalar_t* o = (scalar_t*)out;
     const scalar_t* in = (const scalar_t*)input;
     switch (topk) {
-      case 2: moe_sum_kernel<scalar_t, 2><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
-      case 3: moe_sum_kernel<scalar_t, 3><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
-      case 4: moe_sum_kernel<scalar_t, 4><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
-      default: moe_sum_kernel<scalar_t, 0><<<num_tokens, threads, 0, stream>>>(o, in, topk, hidden); break;
+      case 2: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 2>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
+      case 3: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 3>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
+      case 4: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 4>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
+      default: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 0>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
     }
   });
   VB_LAUNCH_CHECK();

@@ -99,6 +99,8 @@ constexpr float kLn2 = 0.6931471805599453f;
 template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE, int NWARPS>
 __global__ void __launch_bounds__(NWARPS * 32, (HEAD_SIZE <= 128 ? (FP8 ? 3 : 2) : 1))
     paged_attention_kernel(const PagedAttnParams p) {
+  pdl_wait();
+  pdl_trigger();
   using MT = typename std::conditional<FP8, __half, QT>::type;  // tensor-core operand type
   using M = MmaType<MT>;
   constexpr int X = FP8 ? 16 : 8;                 // elements per 16-byte K run
@@ -457,6 +459,8 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
     QT* __restrict__ out, const float* __restrict__ exp_sums, const float* __restrict__ max_logits,
     const QT* __restrict__ tmp_out, const int* __restrict__ seq_lens, int num_heads,
     int max_num_partitions, int partition_size, int total_rows) {
+  pdl_wait();
+  pdl_trigger();
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);  // seq * num_heads + head
   if (row >= total_rows) return;
   const int lane = threadIdx.x & 31;
@@ -550,13 +554,12 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     if (smem_t > 48 * 1024)
       VB_CUDA_CHECK(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
     dim3 grid_t(p.num_kv_heads * ((q_per_kv_ + 7) / 8), num_seqs, num_partitions);
-    kt<<<grid_t, (kWarps + 1) * 32, smem_t, stream>>>(p, stages);
+    VB_CUDA_CHECK(launch_k(kt, dim3(grid_t), dim3((kWarps + 1) * 32), smem_t, stream, p, stages));
     VB_LAUNCH_CHECK();
     if (p.max_num_partitions > 1 || p.force_partials) {
       const int rows = num_seqs * p.num_heads;
-      paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
-          (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-          p.max_num_partitions, p.partition_size, rows);
+      VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream, (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
+          p.max_num_partitions, p.partition_size, rows));
       VB_LAUNCH_CHECK();
     }
     return 0;
@@ -570,13 +573,12 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
   const int q_per_kv = p.num_heads / p.num_kv_heads;
   const int groups = (q_per_kv + 7) / 8;
   dim3 grid(p.num_kv_heads * groups, num_seqs, num_partitions);
-  kern<<<grid, kWarps * 32, smem, stream>>>(p);
+  VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kWarps * 32), smem, stream, p));
   VB_LAUNCH_CHECK();
   if (p.max_num_partitions > 1 || p.force_partials) {
     const int rows = num_seqs * p.num_heads;
-    paged_attention_reduce_kernel<QT, HEAD_SIZE><<<(rows + 3) / 4, 128, 0, stream>>>(
-        (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-        p.max_num_partitions, p.partition_size, rows);
+    VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream, (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
+        p.max_num_partitions, p.partition_size, rows));
     VB_LAUNCH_CHECK();
   }
   return 0;

@@ -73,6 +73,8 @@ constexpr int kPaMaxStages = 32;
 template <typename QT, bool FP8, int HEAD_SIZE, int NWARPS, int MIN_CTAS>
 __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
     paged_attention_tma_kernel(const PagedAttnParams p, const int num_stages) {
+  pdl_wait();
+  pdl_trigger();
   using MT = typename std::conditional<FP8, __half, QT>::type;  // tensor-core operand type
   using M = MmaType<MT>;
   constexpr int CE = FP8 ? 1 : 2;                  // cache element bytes

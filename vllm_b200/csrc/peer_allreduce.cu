@@ -34,10 +34,15 @@ constexpr float kFp8MaxA = 448.f;
 struct ArSignal {
   uint32_t self_counter[kArMaxBlocks][kArMaxRanks];
   uint32_t peer_counter[2][kArMaxBlocks][kArMaxRanks];
+  // two-shot kernel: grid-wide "my shard is reduced" hand-shake
+  uint32_t grid_arrive;                  // CTAs of this rank that finished the reduce-scatter (atomicInc, wraps to 0)
+  uint32_t grid_epoch;                   // two-shot launches completed by this rank (every rank agrees on it)
+  uint32_t done_flag[kArMaxRanks];       // [r]: last epoch whose shard rank r has published (written by rank r)
 };
 
 struct ArParams {
   const void* data[kArMaxRanks];   // peer partial sums (this process's mapping), [rows, hidden] contiguous
+  void* gather[kArMaxRanks];       // two-shot: peer buffers holding each rank's REDUCED shard (same shape as data)
   ArSignal* signals[kArMaxRanks];  // peer signal blocks; signals[rank] is ours
   int rank;
   void* out;                       // MODE 0/1: T [rows, hidden]; MODE 2: fp8 [rows, hidden]
@@ -129,9 +134,80 @@ __device__ __forceinline__ void ar_sum8(const ArParams& p, int64_t off, float (&
   }
 }
 
+// residual add + RMSNorm (+ per-token fp8 quant) of one row whose all-reduced values `fetch(i, x)` delivers as 8 fp32
+// numbers (already rounded to T) for 16-byte vector i of the row.  Arithmetic = rms_norm_kernel in layer_glue.cu.
+template <typename T, int MODE, typename Fetch>
+__device__ __forceinline__ void ar_norm_row(const ArParams& p, int row, float* sm, Fetch fetch) {
+  const int nvec = p.hidden >> 3;
+  const T* weight = reinterpret_cast<const T*>(p.weight);
+  T* res = reinterpret_cast<T*>(p.residual) + (int64_t)row * p.hidden;
+  float zf[kArMaxVec][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < kArMaxVec; ++k) {
+    const int i = threadIdx.x + k * kArThreads;
+    if (i < nvec) {
+      float x[8];
+      fetch(i, x);
+      ArVec8<T> b, z;
+      b.u = *reinterpret_cast<const uint4*>(res + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float s = x[j] + to_float<T>(b.e[j]);
+        z.e[j] = from_float<T>(s);
+        zf[k][j] = (MODE == 1) ? to_float<T>(z.e[j]) : s;
+        ss = fmaf(zf[k][j], zf[k][j], ss);
+      }
+      *reinterpret_cast<uint4*>(res + i * 8) = z.u;
+    }
+  }
+  ss = ar_block_reduce<false>(ss, sm);
+  const float inv = rsqrtf(ss / (float)p.hidden + p.eps);
+  float amax = 0.f;
+#pragma unroll
+  for (int k = 0; k < kArMaxVec; ++k) {
+    const int i = threadIdx.x + k * kArThreads;
+    if (i < nvec) {
+      ArVec8<T> w, y;
+      w.u = *reinterpret_cast<const uint4*>(weight + i * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const T n = from_float<T>(zf[k][j] * inv);
+        y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(w.e[j]));
+        if (MODE == 2) {
+          zf[k][j] = to_float<T>(y.e[j]);
+          amax = fmaxf(amax, fabsf(zf[k][j]));
+        }
+      }
+      if (MODE == 1)
+        *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.out) + (int64_t)row * p.hidden + i * 8) = y.u;
+    }
+  }
+  if (MODE == 2) {
+    amax = ar_block_reduce<true>(amax, sm);
+    float s = p.scale_ub ? fminf(amax, *p.scale_ub) : amax;
+    s = fmaxf(s / kFp8MaxA, 1.0f / (kFp8MaxA * 512.0f));
+    if (threadIdx.x == 0) p.scales[row] = s;
+    uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + (int64_t)row * p.hidden;
+#pragma unroll
+    for (int k = 0; k < kArMaxVec; ++k) {
+      const int i = threadIdx.x + k * kArThreads;
+      if (i < nvec) {
+        union { uint2 u; uint8_t b[8]; } q;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          q.b[j] = float_to_e4m3(fmaxf(-kFp8MaxA, fminf(zf[k][j] / s, kFp8MaxA)));
+        *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+      }
+    }
+  }
+}
+
 template <typename T, int N, int MODE>
 __global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_kernel(const ArParams p) {
   __shared__ float sm[kArThreads / 32];
+  pdl_wait();   // the partial sums come from the previous kernel on the stream: flags only after it has completed
+  pdl_trigger();
   ar_barrier<N>(p);
   if (MODE == 0) {
     const int64_t nvec = (int64_t)p.rows * p.hidden / 8;
@@ -144,73 +220,107 @@ __global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_kernel(const ArP
       *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.out) + i * 8) = o.u;
     }
   } else {
-    const int nvec = p.hidden >> 3;
-    const T* weight = reinterpret_cast<const T*>(p.weight);
-    for (int row = blockIdx.x; row < p.rows; row += gridDim.x) {
-      T* res = reinterpret_cast<T*>(p.residual) + (int64_t)row * p.hidden;
-      float zf[kArMaxVec][8];
-      float ss = 0.f;
+    for (int row = blockIdx.x; row < p.rows; row += gridDim.x)
+      ar_norm_row<T, MODE>(p, row, sm,
+                           [&](int i, float (&x)[8]) { ar_sum8<T, N>(p, (int64_t)row * p.hidden + i * 8, x); });
+  }
+  ar_barrier<N>(p);
+}
+
+// ---- two-shot (reduce-scatter + all-gather) variant ---------------------------------------------------------------
+// The one-shot kernel pulls (N-1) copies of the whole tensor into every GPU: 14 MiB per GPU for [256 x 4096] bf16 at 8
+// ranks, ~19 us of NVLink time alone.  Here rank r first reduces only ITS shard (rows [r R/N, (r+1) R/N), a contiguous
+// range of 16-byte vectors dealt out to all CTAs in warp-sized chunks: one NVLink round trip, (N-1)/N of the tensor
+// pulled) into its peer-visible gather buffer, then every rank reads each row ONCE from its owner and goes on with the
+// residual add / norm / quant: 2 (N-1)/N of the tensor per GPU instead of (N-1).  The reference makes the same
+// switch above 256 KB at 8 ranks (/root/reference/csrc/custom_all_reduce.cuh:320-360 cross_device_reduce_2stage,
+// :560-572 dispatch).  Synchronisation:
+//   start   per-CTA-index flag barrier, unfenced (partials come from the previous kernel; also: every peer has left
+//           the previous all-reduce, so my gather buffer is free to overwrite)
+//   middle  grid-wide: each CTA fences (sys) and bumps a local counter; the last one pushes epoch e into every peer's
+//           done_flag[rank]; everybody spins locally until all N ranks show e, then fences (acquire)
+//   end     none: peers read my partials only before `middle`, and my gather buffer only until they enter the next
+//           all-reduce's `start`.
+template <typename T, int N, int MODE>
+__global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_2shot_kernel(const ArParams p) {
+  __shared__ float sm[kArThreads / 32];
+  pdl_wait();
+  pdl_trigger();
+  ArSignal* self = p.signals[p.rank];
+  ar_barrier<N>(p);
+  const int nvec = p.hidden >> 3;
+  // ---- reduce-scatter: my shard as a contiguous vector range [v0, v1) ----
+  int64_t v0, v1;
+  int rows_per = 0;
+  if (MODE == 0) {
+    const int64_t total = (int64_t)p.rows * nvec;
+    const int64_t per = ((total + N - 1) / N + 31) & ~(int64_t)31;
+    v0 = min((int64_t)p.rank * per, total);
+    v1 = min(v0 + per, total);
+  } else {
+    rows_per = (p.rows + N - 1) / N;
+    v0 = (int64_t)min(p.rank * rows_per, p.rows) * nvec;
+    v1 = (int64_t)min((p.rank + 1) * rows_per, p.rows) * nvec;
+  }
+  {
+    T* mine = reinterpret_cast<T*>(p.gather[p.rank]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t nchunk = (v1 - v0 + 31) >> 5;
+    for (int64_t c = blockIdx.x + (int64_t)gridDim.x * warp; c < nchunk; c += (int64_t)gridDim.x * (kArThreads / 32)) {
+      const int64_t i = v0 + (c << 5) + lane;
+      if (i < v1) {
+        float acc[8];
+        ar_sum8<T, N>(p, i * 8, acc);
+        ArVec8<T> o;
 #pragma unroll
-      for (int k = 0; k < kArMaxVec; ++k) {
-        const int i = threadIdx.x + k * kArThreads;
-        if (i < nvec) {
-          float x[8];
-          ar_sum8<T, N>(p, (int64_t)row * p.hidden + i * 8, x);
-          ArVec8<T> b, z;
-          b.u = *reinterpret_cast<const uint4*>(res + i * 8);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float s = x[j] + to_float<T>(b.e[j]);
-            z.e[j] = from_float<T>(s);
-            zf[k][j] = (MODE == 1) ? to_float<T>(z.e[j]) : s;
-            ss = fmaf(zf[k][j], zf[k][j], ss);
-          }
-          *reinterpret_cast<uint4*>(res + i * 8) = z.u;
-        }
-      }
-      ss = ar_block_reduce<false>(ss, sm);
-      const float inv = rsqrtf(ss / (float)p.hidden + p.eps);
-      float amax = 0.f;
-#pragma unroll
-      for (int k = 0; k < kArMaxVec; ++k) {
-        const int i = threadIdx.x + k * kArThreads;
-        if (i < nvec) {
-          ArVec8<T> w, y;
-          w.u = *reinterpret_cast<const uint4*>(weight + i * 8);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const T n = from_float<T>(zf[k][j] * inv);
-            y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(w.e[j]));
-            if (MODE == 2) {
-              zf[k][j] = to_float<T>(y.e[j]);
-              amax = fmaxf(amax, fabsf(zf[k][j]));
-            }
-          }
-          if (MODE == 1)
-            *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.out) + (int64_t)row * p.hidden + i * 8) = y.u;
-        }
-      }
-      if (MODE == 2) {
-        amax = ar_block_reduce<true>(amax, sm);
-        float s = p.scale_ub ? fminf(amax, *p.scale_ub) : amax;
-        s = fmaxf(s / kFp8MaxA, 1.0f / (kFp8MaxA * 512.0f));
-        if (threadIdx.x == 0) p.scales[row] = s;
-        uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + (int64_t)row * p.hidden;
-#pragma unroll
-        for (int k = 0; k < kArMaxVec; ++k) {
-          const int i = threadIdx.x + k * kArThreads;
-          if (i < nvec) {
-            union { uint2 u; uint8_t b[8]; } q;
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              q.b[j] = float_to_e4m3(fmaxf(-kFp8MaxA, fminf(zf[k][j] / s, kFp8MaxA)));
-            *reinterpret_cast<uint2*>(o + i * 8) = q.u;
-          }
-        }
+        for (int j = 0; j < 8; ++j) o.e[j] = from_float<T>(acc[j]);
+        *reinterpret_cast<uint4*>(mine + i * 8) = o.u;
       }
     }
   }
-  ar_barrier<N>(p);
+  // ---- middle barrier ----
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // every CTA reads the epoch BEFORE it arrives and only the last arrival advances it: all CTAs see the same e,
+    // whatever grids earlier launches used
+    const uint32_t e = ld_flag(&self->grid_epoch) + 1;
+    __threadfence_system();   // release: this CTA's gather stores (ordered before by the bar.sync) before the count
+    if (atomicInc(&self->grid_arrive, gridDim.x - 1) == gridDim.x - 1) {
+      __threadfence_system();   // acquire the other CTAs' counts (and with them their stores), then publish
+      st_flag(&self->grid_epoch, e);
+#pragma unroll
+      for (int r = 0; r < N; ++r) st_flag(&p.signals[r]->done_flag[p.rank], e);
+    }
+    sm[0] = __uint_as_float(e);
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    const uint32_t e = __float_as_uint(sm[0]);
+    while ((int32_t)(ld_flag(&self->done_flag[threadIdx.x]) - e) < 0) {
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+  // ---- all-gather fused with the consumer ----
+  if (MODE == 0) {
+    const int64_t total = (int64_t)p.rows * nvec;
+    const int64_t per = ((total + N - 1) / N + 31) & ~(int64_t)31;
+    for (int64_t i = (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kArThreads) {
+      const int owner = (int)(i / per);
+      const uint4 v = ld_peer_v4(reinterpret_cast<const T*>(p.gather[owner]) + i * 8);
+      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.out) + i * 8) = v;
+    }
+  } else {
+    for (int row = blockIdx.x; row < p.rows; row += gridDim.x) {
+      const T* src = reinterpret_cast<const T*>(p.gather[row / rows_per]) + (int64_t)row * p.hidden;
+      ar_norm_row<T, MODE>(p, row, sm, [&](int i, float (&x)[8]) {
+        ArVec8<T> v;
+        v.u = ld_peer_v4(src + i * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x[j] = to_float<T>(v.e[j]);
+      });
+    }
+  }
 }
 
 // Staged variant of MODE 1 / 2 (kept as a tuning option, off by default -- see g_ar_staged): a CTA owns rows blockIdx.x, blockIdx.x + grid, ... and
@@ -226,6 +336,8 @@ __global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_staged_kernel(co
   const int stage_bytes = N * row_bytes;
   const T* weight = reinterpret_cast<const T*>(p.weight);
   const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
+  pdl_wait();
+  pdl_trigger();
   ar_barrier<N>(p);
   auto issue = [&](int k) {
     const int row = blockIdx.x + k * gridDim.x;
@@ -320,35 +432,39 @@ static int g_ar_blocks = 0;       // 0 = default; debug / tuning hook below
 static int g_ar_staged = 0;       // measured: direct loads win at 8 ranks (33 vs 52 us) and tie at 2 (14.6 vs 15.1 us)
 
 template <typename T, int N>
-static int launch_mode(int mode, int grid, const ArParams& p, cudaStream_t stream) {
+static int launch_mode(int mode, int grid, const ArParams& p, bool two_shot, cudaStream_t stream) {
   const int stage_bytes = N * p.hidden * (int)sizeof(T);
+  if (two_shot) {
+    if (mode == 0) VB_CUDA_CHECK(launch_k(peer_allreduce_2shot_kernel<T, N, 0>, dim3(grid), dim3(kArThreads), 0, stream, p));
+    else if (mode == 1) VB_CUDA_CHECK(launch_k(peer_allreduce_2shot_kernel<T, N, 1>, dim3(grid), dim3(kArThreads), 0, stream, p));
+    else VB_CUDA_CHECK(launch_k(peer_allreduce_2shot_kernel<T, N, 2>, dim3(grid), dim3(kArThreads), 0, stream, p));
+    return 0;
+  }
   if (mode != 0 && g_ar_staged && stage_bytes <= kArMaxStageBytes) {
     const size_t smem = (size_t)kArStages * stage_bytes;
     if (mode == 1) {
       auto kern = peer_allreduce_staged_kernel<T, N, 1>;
       VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kArStages * kArMaxStageBytes));
-      kern<<<grid, kArThreads, smem, stream>>>(p);
+      VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kArThreads), smem, stream, p));
     } else {
       auto kern = peer_allreduce_staged_kernel<T, N, 2>;
       VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kArStages * kArMaxStageBytes));
-      kern<<<grid, kArThreads, smem, stream>>>(p);
+      VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kArThreads), smem, stream, p));
     }
-    VB_LAUNCH_CHECK();
     return 0;
   }
-  if (mode == 0) peer_allreduce_kernel<T, N, 0><<<grid, kArThreads, 0, stream>>>(p);
-  else if (mode == 1) peer_allreduce_kernel<T, N, 1><<<grid, kArThreads, 0, stream>>>(p);
-  else peer_allreduce_kernel<T, N, 2><<<grid, kArThreads, 0, stream>>>(p);
-  VB_LAUNCH_CHECK();
+  if (mode == 0) VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 0>, dim3(grid), dim3(kArThreads), 0, stream, p));
+  else if (mode == 1) VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 1>, dim3(grid), dim3(kArThreads), 0, stream, p));
+  else VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 2>, dim3(grid), dim3(kArThreads), 0, stream, p));
   return 0;
 }
 
 template <typename T>
-static int launch_ranks(int n, int mode, int grid, const ArParams& p, cudaStream_t stream) {
+static int launch_ranks(int n, int mode, int grid, const ArParams& p, bool two_shot, cudaStream_t stream) {
   switch (n) {
-    case 2: return launch_mode<T, 2>(mode, grid, p, stream);
-    case 4: return launch_mode<T, 4>(mode, grid, p, stream);
-    case 8: return launch_mode<T, 8>(mode, grid, p, stream);
+    case 2: return launch_mode<T, 2>(mode, grid, p, two_shot, stream);
+    case 4: return launch_mode<T, 4>(mode, grid, p, two_shot, stream);
+    case 8: return launch_mode<T, 8>(mode, grid, p, two_shot, stream);
     default: VB_CHECK(false, "peer_allreduce: world size %d not in {2, 4, 8}", n);
   }
   return 1;
@@ -363,12 +479,12 @@ extern "C" size_t vb200_peer_allreduce_signal_bytes(void) { return sizeof(ArSign
 // mode 0: plain sum; 1: + residual add + RMSNorm; 2: + residual add + RMSNorm + dynamic per-token fp8 quant.
 // peer_data / peer_signals: HOST arrays of `world` device pointers (this process's mappings of every rank's
 // partial-sum buffer and zero-initialised signal block; entry `rank` is this rank's own).  Every rank must call
-// with the same rows / hidden / mode, in the same order.
-extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer_data,
-                                    void* const* peer_signals, int rank, int world, int rows, int hidden,
-                                    int dtype, void* residual, const void* weight, float epsilon,
-                                    float* scales, const float* scale_ub, vb200_stream_t stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+// with the same rows / hidden / mode, in the same order.  peer_gather (two-shot only): the same for every rank's
+// gather buffer (at least rows * hidden elements, 16-byte aligned).
+static int run_peer_allreduce(int mode, void* out, const void* const* peer_data, void* const* peer_gather,
+                              void* const* peer_signals, int rank, int world, int rows, int hidden, int dtype,
+                              void* residual, const void* weight, float epsilon, float* scales,
+                              const float* scale_ub, cudaStream_t stream) {
   VB_CHECK(mode >= 0 && mode <= 2, "peer_allreduce: bad mode %d", mode);
   VB_CHECK(dtype == VB200_BF16 || dtype == VB200_F16, "peer_allreduce: dtype must be bf16 or f16");
   VB_CHECK(rank >= 0 && rank < world && world <= kArMaxRanks, "peer_allreduce: bad rank %d / world %d", rank, world);
@@ -376,12 +492,16 @@ extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer
   VB_CHECK(mode == 0 || hidden <= kArThreads * kArMaxVec * 8, "peer_allreduce: hidden %d too large for the fused modes", hidden);
   VB_CHECK(mode == 0 || (residual != nullptr && weight != nullptr), "peer_allreduce: fused modes need residual and weight");
   VB_CHECK(mode != 2 || scales != nullptr, "peer_allreduce: mode 2 needs scales");
+  const bool two_shot = peer_gather != nullptr;
   ArParams p;
   for (int r = 0; r < kArMaxRanks; ++r) {
     p.data[r] = r < world ? peer_data[r] : nullptr;
+    p.gather[r] = (two_shot && r < world) ? peer_gather[r] : nullptr;
     p.signals[r] = r < world ? reinterpret_cast<ArSignal*>(peer_signals[r]) : nullptr;
     VB_CHECK(r >= world || (p.data[r] != nullptr && p.signals[r] != nullptr), "peer_allreduce: null peer pointer");
     VB_CHECK(r >= world || (reinterpret_cast<uintptr_t>(p.data[r]) & 15) == 0, "peer_allreduce: peer buffers must be 16-byte aligned");
+    VB_CHECK(!two_shot || r >= world || (p.gather[r] != nullptr && (reinterpret_cast<uintptr_t>(p.gather[r]) & 15) == 0),
+             "peer_allreduce: gather buffers must be non-null and 16-byte aligned");
   }
   p.rank = rank;
   p.out = out;
@@ -392,7 +512,7 @@ extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer
   p.eps = epsilon;
   p.rows = rows;
   p.hidden = hidden;
-  // Grid: every CTA pays two system-scope barriers, and the same-index CTAs of all ranks must be co-resident
+  // Grid: every CTA pays the system-scope barriers, and all CTAs of all ranks must be co-resident
   // (1 CTA/SM, grid <= #SMs).  More CTAs = fewer rows per CTA = fewer serialised NVLink round trips (measured).
   int cap = g_ar_blocks > 0 ? g_ar_blocks : num_sms();
   if (cap > num_sms()) cap = num_sms();
@@ -405,8 +525,26 @@ extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer
     grid = rows;
   }
   if (grid > cap) grid = cap;
-  if (dtype == VB200_BF16) return launch_ranks<__nv_bfloat16>(world, mode, grid, p, stream);
-  return launch_ranks<__half>(world, mode, grid, p, stream);
+  if (dtype == VB200_BF16) return launch_ranks<__nv_bfloat16>(world, mode, grid, p, two_shot, stream);
+  return launch_ranks<__half>(world, mode, grid, p, two_shot, stream);
+}
+
+extern "C" int vb200_peer_allreduce(int mode, void* out, const void* const* peer_data,
+                                    void* const* peer_signals, int rank, int world, int rows, int hidden,
+                                    int dtype, void* residual, const void* weight, float epsilon,
+                                    float* scales, const float* scale_ub, vb200_stream_t stream_) {
+  return run_peer_allreduce(mode, out, peer_data, nullptr, peer_signals, rank, world, rows, hidden, dtype, residual,
+                            weight, epsilon, scales, scale_ub, (cudaStream_t)stream_);
+}
+
+extern "C" int vb200_peer_allreduce_2shot(int mode, void* out, const void* const* peer_data,
+                                          void* const* peer_gather, void* const* peer_signals, int rank, int world,
+                                          int rows, int hidden, int dtype, void* residual, const void* weight,
+                                          float epsilon, float* scales, const float* scale_ub,
+                                          vb200_stream_t stream_) {
+  VB_CHECK(peer_gather != nullptr, "peer_allreduce_2shot: peer_gather is required");
+  return run_peer_allreduce(mode, out, peer_data, peer_gather, peer_signals, rank, world, rows, hidden, dtype,
+                            residual, weight, epsilon, scales, scale_ub, (cudaStream_t)stream_);
 }
 
 // ---- peer-visible buffers (CUDA IPC) ----------------------------------------------------------------------------

@@ -51,6 +51,8 @@ __global__ void __launch_bounds__(256) static_quant_kernel(uint8_t* __restrict__
                                                            const T* __restrict__ in,
                                                            const float* __restrict__ scale,
                                                            int64_t n) {
+  pdl_wait();
+  pdl_trigger();
   const float inv = 1.0f / (*scale);  // common.cu:23
   quant_row<T, true>(out, in, n, inv, blockIdx.x * blockDim.x + threadIdx.x,
                      gridDim.x * blockDim.x);
@@ -89,6 +91,8 @@ __device__ __forceinline__ float block_max_256(float v, float* sm) {
 template <typename T>
 __global__ void __launch_bounds__(256) absmax_scale_kernel(float* __restrict__ scale,
                                                            const T* __restrict__ in, int64_t n) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sm[8];
   float m = thread_absmax<T>(in, n, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
   m = block_max_256(m, sm);
@@ -104,6 +108,8 @@ __global__ void __launch_bounds__(256) per_token_quant_kernel(uint8_t* __restric
                                                               const T* __restrict__ in,
                                                               const float* __restrict__ scale_ub,
                                                               int hidden) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sm[8];
   const int64_t row = blockIdx.x;
   const T* rin = in + row * hidden;
@@ -128,6 +134,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) silu_and_mul_kernel(T* __restrict__ out,
                                                            const T* __restrict__ in, int d,
                                                            bool vec) {
+  pdl_wait();
+  pdl_trigger();
   const int64_t row = blockIdx.x;
   const T* x = in + row * 2 * d;
   const T* y = x + d;
@@ -174,8 +182,7 @@ extern "C" int vb200_static_scaled_fp8_quant(void* out, const void* input, const
   const int64_t n = num_tokens * hidden_size;
   if (n <= 0) return 0;
   DISPATCH_IN(in_dtype, {
-    static_quant_kernel<scalar_t><<<stream_grid(n, 8), 256, 0, stream>>>(
-        (uint8_t*)out, (const scalar_t*)input, scale, n);
+    VB_CUDA_CHECK(launch_k(static_quant_kernel<scalar_t>, dim3(stream_grid(n, 8)), dim3(256), 0, stream, (uint8_t*)out, (const scalar_t*)input, scale, n));
   });
   VB_LAUNCH_CHECK();
   return 0;
@@ -188,10 +195,8 @@ extern "C" int vb200_dynamic_scaled_fp8_quant(void* out, const void* input, floa
   const int64_t n = num_tokens * hidden_size;
   if (n <= 0) return 0;
   DISPATCH_IN(in_dtype, {
-    absmax_scale_kernel<scalar_t>
-        <<<stream_grid(n, 8), 256, 0, stream>>>(scale, (const scalar_t*)input, n);
-    static_quant_kernel<scalar_t><<<stream_grid(n, 8), 256, 0, stream>>>(
-        (uint8_t*)out, (const scalar_t*)input, scale, n);
+    VB_CUDA_CHECK(launch_k(absmax_scale_kernel<scalar_t>, dim3(stream_grid(n, 8)), dim3(256), 0, stream, scale, (const scalar_t*)input, n));
+    VB_CUDA_CHECK(launch_k(static_quant_kernel<scalar_t>, dim3(stream_grid(n, 8)), dim3(256), 0, stream, (uint8_t*)out, (const scalar_t*)input, scale, n));
   });
   VB_LAUNCH_CHECK();
   return 0;
@@ -204,8 +209,7 @@ extern "C" int vb200_dynamic_per_token_scaled_fp8_quant(void* out, const void* i
   cudaStream_t stream = (cudaStream_t)stream_;
   if (num_tokens <= 0 || hidden_size <= 0) return 0;
   DISPATCH_IN(in_dtype, {
-    per_token_quant_kernel<scalar_t><<<(unsigned)num_tokens, 256, 0, stream>>>(
-        (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, hidden_size);
+    VB_CUDA_CHECK(launch_k(per_token_quant_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(256), 0, stream, (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, hidden_size));
   });
   VB_LAUNCH_CHECK();
   return 0;
@@ -221,8 +225,7 @@ extern "C" int vb200_silu_and_mul(void* out, const void* input, int64_t num_toke
                    ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
   const int threads = d / ve >= 256 ? 256 : (d / ve >= 128 ? 128 : 64);
   DISPATCH_IN(dtype, {
-    silu_and_mul_kernel<scalar_t><<<(unsigned)num_tokens, threads, 0, stream>>>(
-        (scalar_t*)out, (const scalar_t*)input, d, vec);
+    VB_CUDA_CHECK(launch_k(silu_and_mul_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(threads), 0, stream, (scalar_t*)out, (const scalar_t*)input, d, vec));
   });
   VB_LAUNCH_CHECK();
   return 0;

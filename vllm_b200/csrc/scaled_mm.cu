@@ -24,7 +24,6 @@
 //     (deterministic).  Only used when all units are co-resident (units <= #SM/2), so the wait
 //     cannot deadlock.
 #include "tc_common.cuh"
-#include "scaled_mm_1cta.cuh"
 
 #include <cstdlib>
 
@@ -153,6 +152,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   cluster_sync_all();  // barrier inits + TMEM allocation visible in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail; from here on the
+  // kernel reads what that kernel wrote (activations, scales) and writes buffers it may still be reading
+  pdl_wait();
+  pdl_trigger();
   if (threadIdx.x == 0) stamp(p, 1);
 
   if (warp == 0) {
@@ -494,13 +497,15 @@ static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, c
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = g.smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   VB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tw, ta, p));
   return 0;
 }
@@ -567,17 +572,8 @@ extern "C" void vb200_debug_scaled_mm_trace(void* buf) { v2::g_trace = (unsigned
 
 extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
 
-static bool use_v1() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("VB200_GEMM_V1");
-    v = (e && e[0] == '1') ? 1 : 0;
-  }
-  return v == 1;
-}
-
 extern "C" size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K) {
-  if (M <= 0 || N <= 0 || K <= 0 || use_v1()) return 0;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
   return v2::make_plan(M, N, K).ws_bytes;
 }
 
@@ -596,33 +592,6 @@ extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
   VB_CHECK(b_scales_numel == 1 || b_scales_numel == N, "b_scales must have 1 or N entries");
   if (M <= 0 || N <= 0) return 0;
   VB_CHECK(K > 0, "cutlass_scaled_mm: K must be positive");
-  if (!use_v1())
-    return v2::run(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
-                   b_scales_numel, out_dtype, workspace, workspace_bytes, stream);
-  v1::GemmPlan g = v1::plan_gemm(M, N, K);
-  VB_CHECK(g.m_tiles <= 65535, "cutlass_scaled_mm: M too large");
-  CUtensorMap tw, ta;
-  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, v1::kBlockN)) return 1;
-  if (tc::make_tmap_2d_u8(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, (uint32_t)g.tok_tile))
-    return 1;
-  v1::GemmParams p;
-  p.out = out;
-  p.a_scales = a_scales;
-  p.b_scales = b_scales;
-  p.bias = bias;
-  p.M = M;
-  p.N = N;
-  p.K = K;
-  p.ldc = ldc;
-  p.a_per_token = a_scales_numel > 1 ? 1 : 0;
-  p.b_per_channel = b_scales_numel > 1 ? 1 : 0;
-  p.tok_tile = g.tok_tile;
-  p.stages = g.stages;
-  p.splits = g.splits;
-  p.kb_per_split = g.kb_per_split;
-  p.num_kb = g.num_kb;
-  p.col_chunk = g.col_chunk;
-  p.tmem_cols = g.tmem_cols;
-  if (out_dtype == VB200_BF16) return v1::launch_gemm<__nv_bfloat16>(g, tw, ta, p, stream);
-  return v1::launch_gemm<__half>(g, tw, ta, p, stream);
+  return v2::run(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                 b_scales_numel, out_dtype, workspace, workspace_bytes, stream);
 }

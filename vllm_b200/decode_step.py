@@ -5,8 +5,8 @@ reference's model definition + model runner stand (/root/reference/vllm/model_ex
 is the minimum of them needed to measure the path end to end.
 
 Per layer (FP8 w8a8, dynamic per-token activation scales, per-channel weight scales):
-  rms_norm_dynamic_per_token_quant(+residual) -> cutlass_scaled_mm (qkv, column-parallel) -> rotary_embedding ->
-  AttentionImpl.forward (reshape_and_cache + paged_attention) -> scaled_fp8_quant -> cutlass_scaled_mm (o,
+  rms_norm_dynamic_per_token_quant(+residual) -> cutlass_scaled_mm (qkv, column-parallel) ->
+  rotary_embedding_reshape_and_cache (one launch) -> AttentionImpl.forward (paged_attention) -> scaled_fp8_quant -> cutlass_scaled_mm (o,
   row-parallel) -> all-reduce -> rms_norm_dynamic_per_token_quant(+residual) -> cutlass_scaled_mm (gate_up) ->
   silu_and_mul_dynamic_per_token_quant -> cutlass_scaled_mm (down, row-parallel) -> all-reduce
 or, for Mixtral layers, the MoE block: router GEMM -> fused_topk -> fused_experts -> all-reduce.
@@ -21,6 +21,7 @@ import torch
 
 from . import _custom_ops as ops
 from .attention import B200PagedAttentionBackend, B200PagedAttentionMetadata
+from .attention.paged_attn import PagedAttention
 from .distributed import (get_peer_allreduce, get_tensor_model_parallel_rank,
                           get_tensor_model_parallel_world_size, tensor_model_parallel_all_reduce)
 
@@ -51,7 +52,11 @@ MIXTRAL_8X7B = DecoderConfig("Mixtral-8x7B", 4096, 32, 32, 8, 128, 14336, 32000,
 TINY = DecoderConfig("tiny-llama", 256, 2, 8, 2, 32, 512, 1024, rope_theta=10000.0, max_position=4096)
 TINY_MOE = DecoderConfig("tiny-mixtral", 256, 2, 8, 2, 32, 512, 1024, rope_theta=10000.0, max_position=4096,
                          num_experts=4, top_k=2)
-CONFIGS = {c.name: c for c in (LLAMA_3_1_8B, LLAMA_3_1_70B, MIXTRAL_8X7B, TINY, TINY_MOE)}
+# big enough to shard 8 ways (per-rank K of the row-parallel GEMMs >= 128), small enough for a TP-N == TP-1 test
+SMALL = DecoderConfig("small-llama", 1024, 2, 16, 8, 64, 4096, 2048, rope_theta=10000.0, max_position=4096)
+SMALL_MOE = DecoderConfig("small-mixtral", 1024, 2, 16, 8, 64, 2048, 2048, rope_theta=10000.0, max_position=4096,
+                          num_experts=4, top_k=2)
+CONFIGS = {c.name: c for c in (LLAMA_3_1_8B, LLAMA_3_1_70B, MIXTRAL_8X7B, TINY, TINY_MOE, SMALL, SMALL_MOE)}
 
 
 def _dummy_fp8_weight(n: int, k: int, device, gen: torch.Generator, std: float = 0.02):
@@ -61,6 +66,23 @@ def _dummy_fp8_weight(n: int, k: int, device, gen: torch.Generator, std: float =
     scale = amax / 448.0
     q = (w.float() / scale).clamp_(-448.0, 448.0).to(FP8)
     return q, scale
+
+
+def _dummy_weight(n: int, k: int, device, dtype, quant: str, gen: torch.Generator, rows=None, cols=None):
+    """ONE seeded [N, K] weight of the unsharded model, quantised (fp8: per output channel over the FULL row, as a
+    checkpoint would carry it), then cut to this rank's shard: `rows` = list of (start, stop) row ranges that are
+    concatenated (column-parallel layers), `cols` = (start, stop) column range (row-parallel layers).  Every rank
+    draws the same numbers, so a TP-N step computes the same function as the TP-1 step."""
+    if quant == "fp8":
+        w, scale = _dummy_fp8_weight(n, k, device, gen)
+    else:
+        w, scale = torch.empty(n, k, device=device, dtype=dtype).normal_(0.0, 0.02, generator=gen), None
+    if rows is not None and not (len(rows) == 1 and rows[0] == (0, n)):
+        w = torch.cat([w[a:b] for a, b in rows], dim=0)
+        scale = None if scale is None else torch.cat([scale[a:b] for a, b in rows], dim=0)
+    if cols is not None and cols != (0, k):
+        w = w[:, cols[0]:cols[1]].contiguous()
+    return w, scale
 
 
 def make_cos_sin_cache(rot_dim: int, max_position: int, base: float, dtype, device) -> torch.Tensor:
@@ -124,17 +146,21 @@ class DecoderLayer:
         self.inter = shard["inter_size"]
         self.input_ln = torch.ones(H, device=device, dtype=dtype)
         self.post_ln = torch.ones(H, device=device, dtype=dtype)
-        mk = (lambda n, k: _dummy_fp8_weight(n, k, device, gen)) if quant == "fp8" else (
-            lambda n, k: (torch.empty(n, k, device=device, dtype=dtype).normal_(0.0, 0.02, generator=gen), None))
-        self.w_qkv, self.s_qkv = mk(self.q_size + 2 * self.kv_size, H)
-        self.w_o, self.s_o = mk(H, self.q_size)
+        mk = lambda n, k, rows=None, cols=None: _dummy_weight(n, k, device, dtype, quant, gen, rows, cols)  # noqa: E731
+        (q0, q1), (kv0, kv1), (i0, i1) = shard["q_heads"], shard["kv_heads"], shard["inter"]
+        nq, nk, I = cfg.num_heads * D, cfg.num_kv_heads * D, cfg.intermediate_size
+        # QKVParallelLinear: this rank's q heads, then its k heads, then its v heads of the full [q | k | v] weight
+        self.w_qkv, self.s_qkv = mk(nq + 2 * nk, H, rows=[(q0 * D, q1 * D), (nq + kv0 * D, nq + kv1 * D),
+                                                           (nq + nk + kv0 * D, nq + nk + kv1 * D)])
+        self.w_o, self.s_o = mk(H, nq, cols=(q0 * D, q1 * D))
         if cfg.num_experts:
             from .fused_moe import make_dummy_experts
             self.w_gate = torch.empty(cfg.num_experts, H, device=device, dtype=dtype).normal_(0.0, 0.02, generator=gen)
-            self.experts = make_dummy_experts(cfg.num_experts, H, self.inter, device, dtype, quant, gen)
+            self.experts = make_dummy_experts(cfg.num_experts, H, I, device, dtype, quant, gen, inter_range=(i0, i1))
         else:
-            self.w_gate_up, self.s_gate_up = mk(2 * self.inter, H)
-            self.w_down, self.s_down = mk(H, self.inter)
+            # MergedColumnParallelLinear: [gate | up], each cut to this rank's intermediate columns
+            self.w_gate_up, self.s_gate_up = mk(2 * I, H, rows=[(i0, i1), (I + i0, I + i1)])
+            self.w_down, self.s_down = mk(H, I, cols=(i0, i1))
         impl_cls = B200PagedAttentionBackend.get_impl_cls()
         self.attn = impl_cls(self.nh, D, D ** -0.5, self.nkv, None, None, kv_cache_dtype)
         self.kv_scales = _KVScales(device, 0.05 if kv_cache_dtype != "auto" else 1.0,
@@ -184,8 +210,12 @@ class DecoderLayer:
         q = qkv[:, :self.q_size]
         k = qkv[:, self.q_size:self.q_size + self.kv_size]
         v = qkv[:, self.q_size + self.kv_size:]
-        ops.rotary_embedding(positions, q, k, cfg.head_dim, cos_sin, True)
-        attn_out = self.attn.forward(self.kv_scales, q, k, v, kv_cache, meta)
+        # RoPE + this token's K/V into the paged cache: one launch; the backend then only attends (key = value = None)
+        key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.nkv, cfg.head_dim)
+        ops.rotary_embedding_reshape_and_cache(positions, q, k, v, cfg.head_dim, cos_sin, True, key_cache, value_cache,
+                                               meta.slot_mapping, self.attn.kv_cache_dtype, self.kv_scales._k_scale,
+                                               self.kv_scales._v_scale)
+        attn_out = self.attn.forward(self.kv_scales, q, None, None, kv_cache, meta)
         T = attn_out.shape[0]
         fused_ar = fp8 and par is not None   # o_proj's all-reduce is fused into the post-attention norm
         if fp8:
@@ -240,8 +270,9 @@ class Decoder:
         tp = get_tensor_model_parallel_world_size()
         self.tp, self.tp_rank = tp, get_tensor_model_parallel_rank()
         assert cfg.num_heads % tp == 0 and cfg.intermediate_size % tp == 0
+        # ONE weight set for every TP degree: each rank draws the full tensors from the same seed and keeps its shard
         gen = torch.Generator(device=self.device)
-        gen.manual_seed(seed + 1000 * self.tp_rank)
+        gen.manual_seed(seed)
         self.num_layers = cfg.num_layers if num_layers is None else num_layers
         self.layers: List[DecoderLayer] = [DecoderLayer(cfg, tp, self.device, dtype, quant, kv_cache_dtype, gen)
                                            for _ in range(self.num_layers)]
@@ -252,8 +283,10 @@ class Decoder:
         self.final_ln = torch.ones(cfg.hidden_size, device=self.device, dtype=dtype)
         assert cfg.vocab_size % tp == 0
         self.vocab_shard = cfg.vocab_size // tp
-        self.lm_head = torch.empty(self.vocab_shard, cfg.hidden_size, device=self.device, dtype=dtype).normal_(
+        lm_head = torch.empty(cfg.vocab_size, cfg.hidden_size, device=self.device, dtype=dtype).normal_(
             0.0, 0.02, generator=gen)
+        self.lm_head = lm_head[self.tp_rank * self.vocab_shard:(self.tp_rank + 1) * self.vocab_shard].clone()
+        del lm_head
         self.cos_sin = make_cos_sin_cache(cfg.head_dim, cfg.max_position, cfg.rope_theta, dtype, self.device)
         nkv = self.layers[0].nkv
         shape = B200PagedAttentionBackend.get_kv_cache_shape(num_blocks, block_size, nkv, cfg.head_dim)
@@ -263,7 +296,7 @@ class Decoder:
     def fill_kv_cache_random(self, seed: int = 1) -> None:
         """Synthetic cache contents (finite values only), so that attention reads realistic bytes."""
         gen = torch.Generator(device=self.device)
-        gen.manual_seed(seed + self.tp_rank)
+        gen.manual_seed(seed + self.tp_rank)   # synthetic cache contents: per rank (not a shard of one cache)
         for kv in self.kv_caches:
             if kv.dtype == torch.uint8:
                 flat = kv.view(-1)

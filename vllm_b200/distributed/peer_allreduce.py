@@ -12,6 +12,7 @@ pull + sum -> residual add -> RMSNorm (-> quant) -> barrier.  Everything is issu
 CUDA-graph capturable (the barrier counters live in device memory).
 """
 import ctypes
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -31,7 +32,8 @@ class _RawCudaBuffer:
 
 
 class PeerAllReduce:
-    def __init__(self, group: Optional["dist.ProcessGroup"], device: torch.device, max_bytes: int = 8 << 20):
+    def __init__(self, group: Optional["dist.ProcessGroup"], device: torch.device, max_bytes: int = 8 << 20,
+                 algo: Optional[str] = None):
         self.group = group if group is not None else dist.group.WORLD
         self.rank = dist.get_rank(self.group)
         self.world = dist.get_world_size(self.group)
@@ -48,7 +50,8 @@ class PeerAllReduce:
         # (and the caller falls back to NCCL on all ranks together).
         payload, err = None, None
         self._own_ptr, self._peer_ptrs = None, []
-        total = self._sig_bytes + self.max_bytes
+        # layout of the allocation: [signal block | staging (partial sums) | gather (two-shot: reduced shards)]
+        total = self._sig_bytes + 2 * self.max_bytes
         try:
             with torch.cuda.device(self.device):
                 p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
@@ -81,6 +84,13 @@ class PeerAllReduce:
             raise RuntimeError(f"PeerAllReduce set-up failed on some rank ({err or 'peer failure'})")
         self._sig_ptrs = (ctypes.c_void_p * self.world)(*bases)
         self._data_ptrs = (ctypes.c_void_p * self.world)(*[b + self._sig_bytes for b in bases])
+        self._gather_ptrs = (ctypes.c_void_p * self.world)(*[b + self._sig_bytes + self.max_bytes for b in bases])
+        # "auto": the reference's switch (custom_all_reduce.cuh:560-572): one-shot for 2 ranks and small messages,
+        # two-shot (reduce-scatter + all-gather) from 512 KB at 4 ranks / 256 KB at 8 ranks.  VB200_PEER_AR_ALGO / `algo` pins it (same on every rank);
+        # the choice depends only on (world, bytes), so every rank takes the same kernel.
+        self.algo = algo if algo is not None else os.environ.get("VB200_PEER_AR_ALGO", "auto")
+        if self.algo not in ("auto", "1shot", "2shot"):
+            raise RuntimeError(f"VB200_PEER_AR_ALGO={self.algo}: expected auto, 1shot or 2shot")
         # this rank's staging area as a torch tensor over the raw allocation (the GEMM writes into it)
         self._own = torch.as_tensor(_RawCudaBuffer(self._own_ptr + self._sig_bytes, self.max_bytes), device=self.device)
 
@@ -101,10 +111,25 @@ class PeerAllReduce:
             raise RuntimeError("PeerAllReduce: the input must be the tensor returned by staging()")
         return x.shape[0], x.shape[1]
 
+    def two_shot(self, nbytes: int) -> bool:
+        """Which kernel a message of `nbytes` takes (same answer on every rank)."""
+        if self.algo != "auto":
+            return self.algo == "2shot"
+        return (self.world == 4 and nbytes >= 512 * 1024) or (self.world == 8 and nbytes >= 256 * 1024)
+
+    def algo_name(self, rows: int, hidden: int, dtype: torch.dtype) -> str:
+        return "peer-2shot" if self.two_shot(rows * hidden * torch.empty((), dtype=dtype).element_size()) else "peer-1shot"
+
     def _call(self, mode, out, rows, hidden, dtype, residual, weight, eps, scales, scale_ub):
-        check(load().vb200_peer_allreduce(mode, ptr(out), self._data_ptrs, self._sig_ptrs, self.rank, self.world, rows,
-                                          hidden, dtype_enum(dtype), ptr(residual), ptr(weight), float(eps),
-                                          ptr(scales), ptr(scale_ub), stream()))
+        lib = load()
+        if self.two_shot(rows * hidden * torch.empty((), dtype=dtype).element_size()):
+            check(lib.vb200_peer_allreduce_2shot(mode, ptr(out), self._data_ptrs, self._gather_ptrs, self._sig_ptrs,
+                                                 self.rank, self.world, rows, hidden, dtype_enum(dtype), ptr(residual),
+                                                 ptr(weight), float(eps), ptr(scales), ptr(scale_ub), stream()))
+            return
+        check(lib.vb200_peer_allreduce(mode, ptr(out), self._data_ptrs, self._sig_ptrs, self.rank, self.world, rows,
+                                       hidden, dtype_enum(dtype), ptr(residual), ptr(weight), float(eps),
+                                       ptr(scales), ptr(scale_ub), stream()))
 
     # ---- the three fused forms ---------------------------------------------------------------------------------
     def all_reduce(self, staged: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -136,17 +136,31 @@ def fused_moe(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tensor, g
 
 
 # ---- dummy-weight helpers for the decode-step driver ---------------------------------------------------
-def make_dummy_experts(E: int, hidden: int, inter: int, device, dtype, quant: str, gen: torch.Generator):
-    """Random fp8 expert weights with per-tensor (per-expert) scales, as Mixtral FP8 checkpoints carry."""
+def make_dummy_experts(E: int, hidden: int, inter: int, device, dtype, quant: str, gen: torch.Generator,
+                       inter_range=None):
+    """Random fp8 expert weights with per-tensor (per-expert) scales, as Mixtral FP8 checkpoints carry.  `inter` is
+    the UNSHARDED intermediate size; `inter_range` = (start, stop) keeps this tensor-parallel rank's slice of it
+    (w13 rows of gate and up, w2 columns) of the one seeded weight set, scales taken over the full expert."""
     if quant != "fp8":
         raise RuntimeError("the MoE path is built for fp8 w8a8 experts")
-    def mk(n, k):
-        w = torch.empty(E, n, k, device=device, dtype=torch.bfloat16).normal_(0.0, 0.02, generator=gen)
-        amax = w.abs().amax(dim=(1, 2)).float().clamp_(min=1e-8)
-        scale = amax / 448.0
-        return (w.float() / scale.view(E, 1, 1)).clamp_(-448.0, 448.0).to(FP8), scale
-    w13, s13 = mk(2 * inter, hidden)
-    w2, s2 = mk(hidden, inter)
+    i0, i1 = (0, inter) if inter_range is None else inter_range
+
+    def mk(n, k, rows=None, cols=None):
+        q = torch.empty(E, n if rows is None else sum(b - a for a, b in rows), k if cols is None else cols[1] - cols[0],
+                        device=device, dtype=FP8)
+        scale = torch.empty(E, device=device, dtype=torch.float32)
+        for e in range(E):   # one expert at a time: the unsharded bf16 / fp32 temporaries stay small
+            w = torch.empty(n, k, device=device, dtype=torch.bfloat16).normal_(0.0, 0.02, generator=gen)
+            sc = w.abs().amax().float().clamp_(min=1e-8) / 448.0
+            if rows is not None:
+                w = torch.cat([w[a:b] for a, b in rows], dim=0)
+            if cols is not None:
+                w = w[:, cols[0]:cols[1]]
+            q[e] = (w.float() / sc).clamp_(-448.0, 448.0).to(FP8)
+            scale[e] = sc
+        return q, scale
+    w13, s13 = mk(2 * inter, hidden, rows=[(i0, i1), (inter + i0, inter + i1)])
+    w2, s2 = mk(hidden, inter, cols=(i0, i1))
     return {"w13": w13, "w13_scale": s13, "w2": w2, "w2_scale": s2}
 
 
