@@ -324,14 +324,14 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     return bool(load().vb200_cutlass_scaled_mm_supports_fp8(int(cuda_device_capability)))
 
 
-_GEMM_WS = {}       # (device index, stream handle) -> zero-initialised workspace (split-K tickets + partials)
+_GEMM_WS = {}       # (device index, stream handle) -> zero-initialised workspace (stream-K flags + partial tiles)
 _GEMM_WS_KEEP = []  # superseded buffers stay alive: captured CUDA graphs may still point at them
 
 
 def _gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Scratch of the tcgen05 GEMMs (split-K arrival tickets + fp32 partials).  The first 16 KiB (tickets) must be
-    zero on first use and are left zero by every launch, so a buffer is allocated once with torch.zeros and only
-    ever grown.  One workspace per (device, stream): launches on ONE stream are ordered, so they may share it;
+    """Scratch of the tcgen05 GEMM's stream-K plan (arrival flags + fp32 partial tiles; split-K itself reduces through
+    DSMEM and needs none).  The first 4 KiB (flags) must be zero on first use and are left zero by every launch, so a
+    buffer is allocated once with torch.zeros and only ever grown.  One workspace per (device, stream): launches on ONE stream are ordered, so they may share it;
     launches on different streams (or a graph replay on a side stream next to eager work) get different buffers.
     include/vllm_b200.h states the same rule for direct callers of the C ABI."""
     key = (device.index, stream())
@@ -339,7 +339,7 @@ def _gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
     if ws is None or ws.numel() < nbytes:
         if ws is not None:
             _GEMM_WS_KEEP.append(ws)
-        ws = torch.zeros(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 24 << 20), dtype=torch.uint8, device=device)
         _GEMM_WS[key] = ws
     return ws
 
@@ -371,7 +371,7 @@ def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, s
         raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of the output dtype")
     with _device_of(a):
         lib = load()
-        ws_bytes = lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k)   # 0: split-K reduces through DSMEM
+        ws_bytes = lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k)   # 0 unless the stream-K plan applies
         ws = _gemm_workspace(a.device, ws_bytes) if ws_bytes else None
         check(lib.vb200_cutlass_scaled_mm(
             ptr(out), ptr(a), ptr(b), ptr(scale_a), ptr(scale_b), ptr(bias), m, n, k, a.stride(0),

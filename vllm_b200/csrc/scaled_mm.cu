@@ -17,12 +17,23 @@
 //     of stages; both CTAs signal the LEADER's full barrier), warp 1 = MMA issuer (leader CTA only,
 //     one thread; tcgen05.commit multicasts "stage free" / "accumulator ready" to both CTAs),
 //     warps 2-5 = epilogue (tcgen05.ld -> a_scale * (b_scale * acc) (+ bias) -> bf16/f16 -> global).
-//   * Split-K when the tile count cannot fill the machine (decode o_proj / down_proj / qkv): the S
-//     pairs that share an output tile each accumulate a K slice; partial columns a CTA does not own
-//     go to an L2-resident fp32 workspace, a per-tile arrival counter (release/acquire at gpu scope)
-//     orders them, and every CTA reduces + writes 1/S of the token columns in split order
-//     (deterministic).  Only used when all units are co-resident (units <= #SM/2), so the wait
-//     cannot deadlock.
+//   * Split-K when the tile count cannot fill the machine (decode o_proj / down_proj / qkv): the S pairs that share
+//     an output tile form ONE thread-block cluster of 2 S CTAs (cluster rank = 2 * slice + half), each pair
+//     accumulates a K slice, and the partial accumulators are exchanged through DISTRIBUTED SHARED MEMORY: after a
+//     cluster barrier ("my MMAs are done, my stage ring is idle") every CTA pushes the token columns it does not own
+//     into the owner's ring with st.shared::cluster.v4 (TMEM -> registers -> peer SM, nothing goes through L2), a
+//     second cluster barrier publishes them, and every CTA reduces + writes 1/S of the token columns in slice order
+//     (deterministic).  No global workspace, no tickets, no spin-wait: the hardware co-schedules a cluster, so there
+//     is nothing to deadlock on and nothing shared between streams.
+//   * Stream-K when there are MORE tiles than pairs but not a whole number of rounds (gate_up: 112 tiles on 74
+//     pairs = 2 rounds at 76 % occupancy): the tiles' k-blocks are laid end to end and cut into one equal range per
+//     pair, so a tile that straddles a cut is accumulated by two pairs.  The pair that gets there first parks its
+//     fp32 partial in a workspace and raises a flag; the second one (an arrival counter decides who is who) adds it
+//     to its own accumulator and writes the tile.  The waiter only ever waits for a pair that has ALREADY arrived
+//     (bounded, deadlock-free in any schedule); a + b is order-independent, so the result is deterministic.
+//   * Programmatic dependent launch: barrier init, TMEM allocation, tensor-map prefetch AND the first ring-full of
+//     WEIGHT tiles (which no earlier kernel writes) are issued BEFORE griddepcontrol.wait, so they overlap the tail
+//     of whatever ran before; only the activation loads, the scale / bias reads and the stores wait.
 #include "tc_common.cuh"
 
 #include <cstdlib>
@@ -37,21 +48,22 @@ constexpr int kBlockK = 128;    // fp8 elements (= bytes) of K per stage: one 12
 constexpr int kUmmaK = 32;      // K per tcgen05.mma for 8-bit inputs
 constexpr int kMaxTokTile = 256;
 constexpr int kMaxStages = 12;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 4;   // one per TMEM lane quarter.  (8 = two per quarter taking alternate column chunks was
+                               // measured SLOWER, profiles/r02_scaled_mm_plan_sweep_s34.jsonl: the epilogue is bound
+                               // by the store / DSMEM paths, not by instruction issue)
+constexpr int kWpq = kEpiWarps / 4;   // warps per lane quarter
+constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kWTileBytes = kCtaRows * kBlockK;  // 16 KiB
 constexpr int kTmemCols = 512;                   // two accumulator stages of <= 256 columns
 constexpr int kAccStride = 256;                  // TMEM column offset of accumulator stage 1
-constexpr int kMaxSplits = 8;
-constexpr int kCounterBytes = 16 * 1024;         // head of the workspace: arrival / departure counters
-constexpr int kEpiBarrier = 1;                   // named barrier id of the 4 epilogue warps
+constexpr int kMaxSplits = 8;                    // cluster of 2 * 8 = 16 CTAs (non-portable size above 4 slices)
+constexpr int kEpiBarrier = 1;                   // named barrier id of the epilogue warps
 
 struct Params {
   void* out;              // [M, N] out_t, row stride ldc
   const float* a_scales;  // 1 or M
   const float* b_scales;  // 1 or N
   const void* bias;       // nullptr or [N] out_t
-  uint32_t* counters;     // split-K: arrive[2 * tiles], zero between launches (self re-arming)
-  float* partials;        // split-K: [tiles * 2][owner][source slice][col_chunk / 4][128][4] fp32
   int M, N, K;
   int64_t ldc;
   int a_per_token, b_per_channel;
@@ -60,12 +72,14 @@ struct Params {
   int tiles;         // m_tiles * ceil(N / 256)
   int stages;        // shared-memory pipeline depth
   int stage_bytes;   // per CTA: 16 KiB of W + the half token tile rounded up to 1 KiB
-  int splits;        // K slices per tile (1 = none)
+  int splits;        // K slices per tile (1 = none) = pairs per cluster; a cluster works on one tile at a time
   int kb_per_split;  // k-blocks per slice
   int num_kb;        // total k-blocks
   int col_chunk;     // split-K: token columns reduced + written by one slice (multiple of 16)
-  int units;         // tiles * splits
   uint32_t main_bytes;  // bytes of the stage ring (barriers follow)
+  int streamk;           // 1: pairs work on equal k-block ranges of the flattened (tile, k-block) space
+  uint32_t* sk_flags;    // stream-K: [cut][half]{arrival counter, flag}, zero between launches (self re-arming)
+  float* sk_partials;    // stream-K: [cut][half][tok_tile / 4][128 rows][4] fp32
   uint64_t hint_w, hint_a;
   unsigned long long* trace;  // debug: [grid][16] %globaltimer stamps (nullptr = off)
 };
@@ -108,6 +122,37 @@ __device__ __forceinline__ void store_chunk16(OutT* orow, int64_t ldc, const flo
   }
 }
 
+// The work list of one pair (cluster): whole tiles cluster_id, cluster_id + num_clusters, ... restricted to the
+// pair's K slice [kb0, kb1) -- or, stream-K, the segments of its range [u0, u1) of the flattened (tile, k-block) space.
+struct SegIter {
+  int state, end;
+  __device__ __forceinline__ void init(const Params& p, int cluster_id, int num_clusters) {
+    if (p.streamk) {
+      const long long U = (long long)p.tiles * p.num_kb;
+      state = (int)((cluster_id * U) / num_clusters);
+      end = (int)(((cluster_id + 1) * U) / num_clusters);
+    } else {
+      state = cluster_id;
+      end = p.tiles;
+    }
+  }
+  __device__ __forceinline__ bool next(const Params& p, int num_clusters, int kb0, int kb1, int& tile, int& lo, int& hi) {
+    if (state >= end) return false;
+    if (p.streamk) {
+      tile = state / p.num_kb;
+      lo = state - tile * p.num_kb;
+      hi = min(p.num_kb, lo + (end - state));
+      state += hi - lo;
+    } else {
+      tile = state;
+      lo = kb0;
+      hi = kb1;
+      state += num_clusters;
+    }
+    return true;
+  }
+};
+
 template <typename OutT>
 __global__ void __launch_bounds__(kThreads, 1)
     scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_w,
@@ -121,16 +166,22 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* acc_full = empty_bar + kMaxStages;  // [2] accumulator stage ready (both CTAs)
   uint64_t* acc_empty = acc_full + 2;           // [2] accumulator stage drained (leader's is used)
-  uint64_t* red_bar = acc_empty + 2;             // split-K: bulk fetch of the foreign partials
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(red_bar + 1);
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 3);
+  uint32_t* sk_role = tmem_ptr + 1;   // stream-K: broadcast of the arrival order to the epilogue warps
   float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 6);  // [2][256], 16-byte aligned (offset 256 past the ring)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();  // 0 = leader (issues the MMAs)
-  const int pair = blockIdx.x >> 1;
-  const int num_pairs = gridDim.x >> 1;
+  const uint32_t crank = cluster_ctarank();  // 2 * K-slice + half
+  const uint32_t rank = crank & 1u;          // half of the pair; 0 = leader (issues the MMAs)
+  const uint32_t leader = crank & ~1u;       // cluster rank of this pair's leader
+  const int split = (int)(crank >> 1);       // K slice of this pair (0 when splits == 1)
+  const int cluster_ctas = 2 * p.splits;
+  const int cluster_id = blockIdx.x / cluster_ctas;
+  const int num_clusters = gridDim.x / cluster_ctas;
   const int tok_half = p.tok_tile >> 1;
+  const int kb0 = split * p.kb_per_split;                  // this pair's K slice (the same for every tile)
+  const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
   if (threadIdx.x == 0) stamp(p, 0);
 
   if (warp == 0 && lane == 0) {
@@ -142,46 +193,62 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&acc_full[s], 1);   // one multicast tcgen05.commit
-      mbar_init(&acc_empty[s], 8);  // 4 epilogue warps x 2 CTAs
+      mbar_init(&acc_empty[s], 2 * kEpiWarps);  // epilogue warps x 2 CTAs
     }
-    mbar_init(red_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_2cta(tmem_ptr, kTmemCols);
   tc_fence_before();
-  cluster_sync_all();  // barrier inits + TMEM allocation visible in both CTAs
+  cluster_sync_all();  // barrier inits + TMEM allocation visible in the whole cluster
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail; from here on the
-  // kernel reads what that kernel wrote (activations, scales) and writes buffers it may still be reading
-  pdl_wait();
-  pdl_trigger();
+  pdl_trigger();       // the next kernel on the stream may start its own prologue
   if (threadIdx.x == 0) stamp(p, 1);
 
   if (warp == 0) {
     // ===== TMA producer (both CTAs; one thread) =====
     if (lane == 0) {
+      const uint32_t bar_base = map_to_cta(smem_u32(&full_bar[0]), leader);
+      const uint32_t tx_bytes = 2u * (uint32_t)(kWTileBytes + tok_half * kBlockK);
+      // ---- before the grid dependency resolves: the first ring-full of WEIGHT tiles of the first tile.  Weights
+      // are not written by any kernel, so streaming them may overlap the previous kernel's tail; the barrier of each
+      // stage is armed for W + A bytes here, the activation half follows after griddepcontrol.wait.
+      uint32_t npre = 0;
+      SegIter si;
+      si.init(p, cluster_id, num_clusters);
+      int tile, lo, hi;
+      {
+        SegIter s0 = si;
+        if (s0.next(p, num_clusters, kb0, kb1, tile, lo, hi)) {
+          const int n_pt = tile / p.m_tiles;
+          const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
+          npre = (uint32_t)min(hi - lo, p.stages);
+          for (uint32_t i = 0; i < npre; ++i) {
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[i], tx_bytes);
+            tma_load_2d_2cta(smem + (size_t)i * p.stage_bytes, &tmap_w, bar_base + 8u * i, (lo + (int)i) * kBlockK, n0,
+                             p.hint_w);
+          }
+          stamp(p, 2);
+        }
+      }
+      pdl_wait();   // activations (and everything else the previous kernels wrote) are visible from here on
       uint32_t it = 0;
-      for (int u = pair; u < p.units; u += num_pairs) {
-        const int tile = u / p.splits, split = u - tile * p.splits;
+      while (si.next(p, num_clusters, kb0, kb1, tile, lo, hi)) {
         const int n_pt = tile / p.m_tiles, m_t = tile - n_pt * p.m_tiles;
         const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
         const int tok0 = m_t * p.tok_tile + (int)rank * tok_half;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        for (int kb = lo; kb < hi; ++kb, ++it) {
           const int stage = it % p.stages;
-          const uint32_t phase = (it / p.stages) & 1;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sw = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sa = sw + kWTileBytes;
-          if (rank == 0)
-            mbar_arrive_expect_tx(&full_bar[stage],
-                                  2u * (uint32_t)(kWTileBytes + tok_half * kBlockK));
-          const uint32_t bar = map_to_cta(smem_u32(&full_bar[stage]), 0);
-          tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
+          const uint32_t bar = bar_base + 8u * (uint32_t)stage;
+          if (it >= npre) {
+            const uint32_t phase = (it / p.stages) & 1;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+            tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
+          }
           tma_load_2d_2cta(sa, &tmap_a, bar, kb * kBlockK, tok0, p.hint_a);
-          if (it == 0) stamp(p, 2);
         }
       }
       // tail: every stage this CTA filled has been released, i.e. all multicast arrivals aimed at
@@ -195,14 +262,16 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA, one thread) =====
+    // ===== MMA issuer (leader CTA of each pair, one thread) =====
     if (rank == 0 && lane == 0) {
       const uint32_t idesc = make_idesc_f8(kPairRows, p.tok_tile);
+      const uint16_t pair_mask = (uint16_t)(0x3u << leader);   // the two CTAs of this pair, as cluster ranks
       uint32_t it = 0, lt = 0;
-      for (int u = pair; u < p.units; u += num_pairs, ++lt) {
-        const int tile = u / p.splits, split = u - tile * p.splits;
-        const int kb0 = split * p.kb_per_split;
-        const int nkb = min(kb0 + p.kb_per_split, p.num_kb) - kb0;
+      SegIter si;
+      si.init(p, cluster_id, num_clusters);
+      int tile, lo, hi;
+      for (; si.next(p, num_clusters, kb0, kb1, tile, lo, hi); ++lt) {
+        const int nkb = hi - lo;
         const uint32_t as = lt & 1, aphase = (lt >> 1) & 1;
         mbar_wait(&acc_empty[as], aphase ^ 1);  // both CTAs' epilogues drained this stage
         tc_fence_after();
@@ -222,41 +291,51 @@ __global__ void __launch_bounds__(kThreads, 1)
             umma_f8_2cta(d_tmem, adesc + (uint64_t)(k * (kUmmaK >> 4)),
                          bdesc + (uint64_t)(k * (kUmmaK >> 4)), idesc, (kb | k) != 0);
           }
-          umma_commit_2cta(&empty_bar[stage], 0x3);  // frees the stage in both CTAs
+          umma_commit_2cta(&empty_bar[stage], pair_mask);  // frees the stage in both CTAs
         }
-        umma_commit_2cta(&acc_full[as], 0x3);  // accumulator complete, both CTAs' epilogues may read
+        umma_commit_2cta(&acc_full[as], pair_mask);  // accumulator complete, both CTAs' epilogues may read
         stamp(p, 4);
       }
     }
     __syncwarp();
   }
+  if (warp < 2 && p.splits > 1) {
+    // split-K: the two cluster barriers of the DSMEM exchange are executed by every thread of the cluster
+    cluster_sync_all();
+    cluster_sync_all();
+  }
 
   if (warp >= 2) {
-    // ===== epilogue (4 warps of each CTA; TMEM lane quarter = warp % 4) =====
+    // ===== epilogue (kEpiWarps warps of each CTA; TMEM lane quarter = warp % 4, the kWpq warps of a quarter take
+    // alternate column chunks) =====
     const int q = warp & 3;
+    const int h = (warp - 2) >> 2;  // which of the quarter's two warps
     const int row = q * 32 + lane;  // weight row inside this CTA's 128
     const int tid_e = threadIdx.x - 64;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     OutT* outp = reinterpret_cast<OutT*>(p.out);
     const bool has_bias = p.bias != nullptr;
-    const uint32_t acc_empty_leader = map_to_cta(smem_u32(&acc_empty[0]), 0);
+    const uint32_t acc_empty_leader = map_to_cta(smem_u32(&acc_empty[0]), leader);
     uint32_t lt = 0;
-    for (int u = pair; u < p.units; u += num_pairs, ++lt) {
-      const int tile = u / p.splits, split = u - tile * p.splits;
+    pdl_wait();   // scales / bias may come from the previous kernel; `out` may still be read by it
+    SegIter si;
+    si.init(p, cluster_id, num_clusters);
+    int tile, seg_lo, seg_hi;
+    for (; si.next(p, num_clusters, kb0, kb1, tile, seg_lo, seg_hi); ++lt) {
       const int n_pt = tile / p.m_tiles, m_t = tile - n_pt * p.m_tiles;
       const int n = n_pt * kPairRows + (int)rank * kCtaRows + row;  // output column of this thread
       const bool n_ok = n < p.N;
       const int tok0 = m_t * p.tok_tile;  // accumulator column c <-> token tok0 + c
       const uint32_t as = lt & 1, aphase = (lt >> 1) & 1;
       float* asc = s_ascale + as * kMaxTokTile;
-      for (int i = tid_e; i < p.tok_tile; i += 128) {
+      for (int i = tid_e; i < p.tok_tile; i += 32 * kEpiWarps) {
         const int t = tok0 + i;
         asc[i] = p.a_per_token ? (t < p.M ? p.a_scales[t] : 0.f) : p.a_scales[0];
       }
       const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[n] : 0.f) : p.b_scales[0];
       float biasf = 0.f;
       if (has_bias && n_ok) biasf = to_float<OutT>(reinterpret_cast<const OutT*>(p.bias)[n]);
-      named_bar_sync(kEpiBarrier, 128);  // a_scale tile staged (and the previous use of `asc` is over)
+      named_bar_sync(kEpiBarrier, 32 * kEpiWarps);  // a_scale tile staged (and the previous use of `asc` is over)
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
       if (tid_e == 0) stamp(p, 5);
@@ -273,44 +352,128 @@ __global__ void __launch_bounds__(kThreads, 1)
           store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
                         ncols - c);
       };
-      if (p.splits == 1) {
+      const bool sk_partial = p.streamk && (seg_lo > 0 || seg_hi < p.num_kb);
+      if (sk_partial) {
+        // ---- stream-K: this pair holds only part of the tile's K range; the other part is one neighbour's ----
+        // cut index: the tail of a tile is shared with the previous pair, the head with the next one
+        const int cut = seg_lo > 0 ? cluster_id - 1 : cluster_id;
+        uint32_t* cnt = p.sk_flags + 2 * (cut * 2 + (int)rank);
+        uint32_t* flag = cnt + 1;
+        float4* part = reinterpret_cast<float4*>(p.sk_partials) +
+                       (size_t)(cut * 2 + (int)rank) * (size_t)(p.tok_tile >> 2) * kCtaRows + row;
+        if (tid_e == 0) *sk_role = atomicInc(cnt, 1u);   // 0: first of the two to get here, 1: second (counter wraps to 0)
+        named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
+        const uint32_t role = *sk_role;
+        const int tpc = (ncols + 15) >> 4;
+        uint32_t ra[16], rb[16];
+        if (role == 0) {
+          // first: park the fp32 partial ([col / 4][row][4], 512 contiguous bytes per warp store), then raise the flag
+          auto park16 = [&](const uint32_t* r, int jc) {
+            float4* dst = part + (size_t)(jc << 2) * kCtaRows;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+              __stcg(dst + (size_t)jj * kCtaRows,
+                     make_float4(__uint_as_float(r[4 * jj]), __uint_as_float(r[4 * jj + 1]),
+                                 __uint_as_float(r[4 * jj + 2]), __uint_as_float(r[4 * jj + 3])));
+          };
+          tmem_ld_x16(taddr, ra);
+          for (int jc = 0; jc < tpc; jc += 2) {
+            tmem_ld_wait();
+            if (jc + 1 < tpc) tmem_ld_x16(taddr + ((jc + 1) << 4), rb);
+            park16(ra, jc);
+            if (jc + 1 < tpc) {
+              tmem_ld_wait();
+              if (jc + 2 < tpc) tmem_ld_x16(taddr + ((jc + 2) << 4), ra);
+              park16(rb, jc + 1);
+            }
+          }
+          __threadfence();
+          named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
+          if (tid_e == 0) st_release_gpu(flag, 1u);
+        } else {
+          // second: the first has arrived (it incremented the counter), so its flag is coming: bounded wait
+          if (tid_e == 0) {
+            while (ld_acquire_gpu(flag) == 0u) {
+            }
+            *flag = 0u;   // re-armed for the next launch (nobody touches this cut again in this one)
+          }
+          named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
+          auto fix16 = [&](const uint32_t* r, int jc) {
+            float f[16];
+            const float4* src = part + (size_t)(jc << 2) * kCtaRows;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              const float4 v = __ldcg(src + (size_t)jj * kCtaRows);
+              f[4 * jj] = __uint_as_float(r[4 * jj]) + v.x;
+              f[4 * jj + 1] = __uint_as_float(r[4 * jj + 1]) + v.y;
+              f[4 * jj + 2] = __uint_as_float(r[4 * jj + 2]) + v.z;
+              f[4 * jj + 3] = __uint_as_float(r[4 * jj + 3]) + v.w;
+            }
+            const int c = jc << 4;
+            if (n_ok)
+              store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
+                            ncols - c);
+          };
+          tmem_ld_x16(taddr, ra);
+          for (int jc = 0; jc < tpc; jc += 2) {
+            tmem_ld_wait();
+            if (jc + 1 < tpc) tmem_ld_x16(taddr + ((jc + 1) << 4), rb);
+            fix16(ra, jc);
+            if (jc + 1 < tpc) {
+              tmem_ld_wait();
+              if (jc + 2 < tpc) tmem_ld_x16(taddr + ((jc + 2) << 4), ra);
+              fix16(rb, jc + 1);
+            }
+          }
+        }
+      } else if (p.splits == 1) {
         // tcgen05.ld is warp-collective (never under a per-lane predicate) and asynchronous: the load of the
         // next 32 columns is in flight while the current 32 are converted and stored
         uint32_t ra[32], rb[32];
-        tmem_ld_x32(taddr, ra);
-        for (int c = 0; c < ncols; c += 64) {
+        int c = 32 * h;   // this warp: 32-column blocks h, h + kWpq, h + 2 kWpq, ...
+        if (c < ncols) tmem_ld_x32(taddr + c, ra);
+        for (; c < ncols; c += 64 * kWpq) {
           tmem_ld_wait();
-          const bool more1 = c + 32 < ncols;
-          if (more1) tmem_ld_x32(taddr + c + 32, rb);
+          const int c2 = c + 32 * kWpq;
+          if (c2 < ncols) tmem_ld_x32(taddr + c2, rb);
           emit16(ra, c);
           if (c + 16 < ncols) emit16(ra + 16, c + 16);
-          if (more1) {
+          if (c2 < ncols) {
             tmem_ld_wait();
-            if (c + 64 < ncols) tmem_ld_x32(taddr + c + 64, ra);
-            emit16(rb, c + 32);
-            if (c + 48 < ncols) emit16(rb + 16, c + 48);
+            if (c2 + 32 * kWpq < ncols) tmem_ld_x32(taddr + c2 + 32 * kWpq, ra);
+            emit16(rb, c2);
+            if (c2 + 16 < ncols) emit16(rb + 16, c2 + 16);
           }
         }
       } else {
-        // ---- split-K: park the columns other slices own, wait for all slices, reduce own columns ----
-        // workspace of this (tile, CTA): [owner][source slice][col / 4][128 rows][4] fp32
+        // ---- split-K through distributed shared memory (one tile per cluster in this mode) ----
+        // receive buffer of a CTA = its (now idle) stage ring: [source slot][col / 4][128 rows][4] fp32, source slot
+        // = the sending slice's index among the S - 1 foreign slices, in slice order
         const int cw = p.col_chunk, S = p.splits;
-        const size_t R = (size_t)cw * kCtaRows;  // floats per (owner, source) region
-        float* base = p.partials + (size_t)(tile * 2 + (int)rank) * S * S * R;
+        const int cq = cw >> 2;
         const int tpc = p.tok_tile >> 4;  // 16-column chunks of the tile
+        const uint32_t ring_u32 = smem_u32(smem);
+        // barrier 1: every CTA of the cluster has seen its accumulator complete => all MMAs that read the rings are
+        // done and all TMA loads have landed: the rings may be overwritten by peers
+        cluster_sync_all();
+        // foreign 16-column chunks (everything but my own slice's columns), dealt alternately to the two warps
+        const int own_lo = (split * cw) >> 4, own_n = cw >> 4;
         auto next_foreign = [&](int jc) {
-          while (jc < tpc && (jc << 4) / cw == split) ++jc;
+          for (; jc < tpc; ++jc) {
+            if (jc >= own_lo && jc < own_lo + own_n) continue;
+            const int fi = jc < own_lo ? jc : jc - own_n;
+            if (fi % kWpq == h) break;
+          }
           return jc;
         };
-        auto park16 = [&](const uint32_t* r, int jc) {
+        auto push16 = [&](const uint32_t* r, int jc) {
           const int c = jc << 4, o = c / cw;
-          float4* dst = reinterpret_cast<float4*>(base + ((size_t)o * S + split) * R) +
-                        (size_t)((c - o * cw) >> 2) * kCtaRows + row;
+          const int slot = split < o ? split : split - 1;
+          const uint32_t dst = map_to_cta(ring_u32, (uint32_t)(2 * o) + rank) +
+                               (uint32_t)(((slot * cq + ((c - o * cw) >> 2)) * kCtaRows + row) * 16);
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj)
-            __stcg(dst + (size_t)jj * kCtaRows,
-                   make_float4(__uint_as_float(r[4 * jj]), __uint_as_float(r[4 * jj + 1]),
-                               __uint_as_float(r[4 * jj + 2]), __uint_as_float(r[4 * jj + 3])));
+            st_cluster_v4(dst + (uint32_t)(jj * kCtaRows * 16), r[4 * jj], r[4 * jj + 1], r[4 * jj + 2], r[4 * jj + 3]);
         };
         {
           uint32_t ra[16], rb[16];
@@ -320,74 +483,54 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int j1 = next_foreign(j0 + 1);
             tmem_ld_wait();
             if (j1 < tpc) tmem_ld_x16(taddr + (j1 << 4), rb);
-            park16(ra, j0);
+            push16(ra, j0);
             if (j1 >= tpc) break;
             const int j2 = next_foreign(j1 + 1);
             tmem_ld_wait();
             if (j2 < tpc) tmem_ld_x16(taddr + (j2 << 4), ra);
-            park16(rb, j1);
+            push16(rb, j1);
             j0 = j2;
           }
         }
-        __threadfence();
         if (tid_e == 0) stamp(p, 6);
-        named_bar_sync(kEpiBarrier, 128);
-        // arrival counter that re-arms itself: atomicInc wraps to 0 on the S-th arrival, and 0 is what every
-        // waiter (who has incremented it itself) waits for; it is 0 again for the next launch
-        uint32_t* arrive = p.counters + tile * 2 + (int)rank;
         const int nc = min(cw, p.tok_tile - split * cw);  // columns this slice reduces and writes
         const int c_own = split * cw;
         uint32_t ra[16], rb[16];
-        if (nc > 0) tmem_ld_x16(taddr + c_own, ra);  // own columns: in flight during the wait below
-        if (tid_e == 0) {
-          atomicInc(arrive, (uint32_t)S - 1u);
-          while (ld_acquire_gpu(arrive) != 0u) {
-          }
-          stamp(p, 7);
-          if (nc > 0) {
-            // every slice's partials are visible: pull the S-1 foreign regions of my columns into the
-            // (now idle) pipeline stages with two bulk copies (the regions left and right of my own)
-            fence_proxy_async_all();
-            const uint32_t lo = (uint32_t)(split * R * 4), hi = (uint32_t)((S - 1 - split) * R * 4);
-            mbar_arrive_expect_tx(red_bar, lo + hi);
-            const float* reg = base + (size_t)split * S * R;
-            if (lo) bulk_load_1d(smem, reg, lo, red_bar);
-            if (hi) bulk_load_1d(smem + lo, reg + (size_t)(split + 1) * R, hi, red_bar);
-          }
-        }
-        if (nc > 0) {
-          mbar_wait(red_bar, 0);
-          if (tid_e == 0) stamp(p, 8);
-          const uint32_t sp = smem_u32(smem) + (uint32_t)row * 16u;
-          const int cq = cw >> 2;
-          auto reduce16 = [&](const uint32_t* r, int c) {  // c: column offset inside my chunk
+        int c = 16 * h;   // this warp: 16-column chunks h, h + kWpq, ... of my slice's columns
+        if (c < nc) tmem_ld_x16(taddr + c_own + c, ra);  // in flight across the barrier
+        // barrier 2 (release / acquire at cluster scope): the peers' partials of my columns are in my ring
+        cluster_sync_all();
+        if (tid_e == 0) stamp(p, 7);
+        {
+          const uint32_t sp = ring_u32 + (uint32_t)row * 16u;
+          auto reduce16 = [&](const uint32_t* r, int cc0) {  // cc0: column offset inside my chunk
             float f[16];
 #pragma unroll
             for (int jx = 0; jx < 16; ++jx) f[jx] = __uint_as_float(r[jx]);
             for (int s2 = 0; s2 < S - 1; ++s2) {  // own slice first, then the others in slice order
 #pragma unroll
               for (int jj = 0; jj < 4; ++jj) {
-                const float4 v = lds_f4(sp + (uint32_t)((s2 * cq + (c >> 2) + jj) * kCtaRows * 16));
+                const float4 v = lds_f4(sp + (uint32_t)((s2 * cq + (cc0 >> 2) + jj) * kCtaRows * 16));
                 f[4 * jj] += v.x;
                 f[4 * jj + 1] += v.y;
                 f[4 * jj + 2] += v.z;
                 f[4 * jj + 3] += v.w;
               }
             }
-            const int cc = c_own + c;
+            const int cc = c_own + cc0;
             if (n_ok)
               store_chunk16(outp + (int64_t)(tok0 + cc) * p.ldc + n, p.ldc, f, asc_u32 + 4 * cc, bsc, biasf, has_bias,
                             p.M - tok0 - cc);
           };
-          for (int c = 0; c < nc; c += 32) {
+          for (; c < nc; c += 32 * kWpq) {
             tmem_ld_wait();
-            const bool more1 = c + 16 < nc;
-            if (more1) tmem_ld_x16(taddr + c_own + c + 16, rb);
+            const int c2 = c + 16 * kWpq;
+            if (c2 < nc) tmem_ld_x16(taddr + c_own + c2, rb);
             reduce16(ra, c);
-            if (more1) {
+            if (c2 < nc) {
               tmem_ld_wait();
-              if (c + 32 < nc) tmem_ld_x16(taddr + c_own + c + 32, ra);
-              reduce16(rb, c + 16);
+              if (c2 + 16 * kWpq < nc) tmem_ld_x16(taddr + c_own + c2 + 16 * kWpq, ra);
+              reduce16(rb, c2);
             }
           }
         }
@@ -402,7 +545,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   // teardown: nobody leaves (or frees TMEM) while the peer may still touch this CTA
   tc_fence_before();
-  cluster_sync_all();
+  cluster_sync_relaxed();   // execution order only: no need to drain the output stores before arriving
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_2cta(tmem_base, kTmemCols);
@@ -415,91 +558,148 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static unsigned long long* g_trace = nullptr;  // set through vb200_debug_scaled_mm_trace()
 
 struct Plan {
-  int tok_tile, m_tiles, n_ptiles, tiles, stages, stage_bytes, splits, kb_per_split, num_kb, col_chunk,
-      units, pairs;
-  size_t smem, ws_bytes, main_bytes;
+  int tok_tile, m_tiles, n_ptiles, tiles, stages, stage_bytes, splits, kb_per_split, num_kb, col_chunk, clusters;
+  int streamk;
+  size_t smem, main_bytes, ws_bytes;
 };
+constexpr size_t kSkFlagBytes = 4096;   // head of the stream-K workspace: [cut][half]{counter, flag}
 
-// Cost model (microseconds) of one (token tiles, K splits) choice for a problem whose units are all co-resident
-// or run in whole rounds.  Constants are read off the per-phase trace (benchmarks/trace_scaled_mm.py,
-// profiles/r01_scaled_mm_trace_s18.txt): a CTA pulls ~90 GB/s from L2, a pair retires one 256 x 256 x 128 k-block
-// in 0.28 us, the split-K exchange (park partials in L2, wait, fetch, store) costs ~9 us per 256 token columns and
-// the plain epilogue ~2.6 us, HBM streams the weights at ~6.4 TB/s.
-static float plan_cost(int tok_tile, int tiles, int splits, int num_kb, int max_pairs, double w_bytes) {
+// Cost model (microseconds) of one (token tiles, K splits) choice.  Constants are read off the per-phase traces
+// (benchmarks/trace_scaled_mm.py, profiles/r01_scaled_mm_trace_s18.txt / _s19.txt): an SM pulls ~85 GB/s from L2 and
+// all of them together ~11 TB/s (the L2 slice throughput cap), a pair retires one 256 x 256 x 128 k-block in 0.28 us,
+// HBM streams the weights at ~6.4 TB/s, the plain epilogue stores 256 token columns in ~2.6 us; the split-K exchange
+// adds two cluster barriers (~0.5 us each) and the partial columns pushed through DSMEM at about the L2 feed rate.
+static float plan_cost(int tok_tile, int m_tiles, int n_ptiles, int splits, int num_kb, int max_pairs, double w_bytes,
+                       double a_bytes) {
+  const int tiles = m_tiles * n_ptiles;
   const int kbps = ceil_div(num_kb, splits);
   const int rounds = ceil_div(tiles * splits, max_pairs);
-  const float feed = kbps * (kWTileBytes + tok_tile / 2 * kBlockK) / 90e3f;
+  const float feed = kbps * (kWTileBytes + tok_tile / 2 * kBlockK) / 85e3f;
   const float mma = kbps * tok_tile * 0.0011f;
   const float hbm = (float)(w_bytes / 6.4e6);
-  const float main_us = fmaxf(rounds * fmaxf(feed, mma), hbm);
-  return main_us + (splits > 1 ? 0.035f : 0.010f) * tok_tile;
+  // bytes every SM pulls through the L2 fabric: the weights once per token tile, the activations once per row tile
+  const float fabric = (float)((w_bytes * m_tiles + a_bytes * n_ptiles) / 11e6);
+  const float main_us = fmaxf(fmaxf(rounds * fmaxf(feed, mma), hbm), fabric);
+  float epi = 0.010f * tok_tile / splits;
+  if (splits > 1) epi += 1.0f + 0.006f * tok_tile * (splits - 1) / splits;
+  return main_us + epi;
 }
+
+static int max_clusters_cached(int cluster_ctas, size_t smem);
 
 static Plan make_plan(int M, int N, int K) {
   Plan g;
-  g.m_tiles = ceil_div(M, kMaxTokTile);
   g.n_ptiles = ceil_div(N, kPairRows);
   g.num_kb = ceil_div(K, kBlockK);
   const int max_pairs = num_sms() / 2;
-  // split-K only when every unit gets its own CTA pair (co-residency makes the in-kernel wait safe)
-  int splits = 1;
-  for (int s = 2; s <= kMaxSplits; ++s)
-    if (g.m_tiles * g.n_ptiles * s <= max_pairs && g.num_kb / s >= 4) splits = s;
-  if (M > 128 && M <= kMaxTokTile && 2 * g.n_ptiles <= max_pairs) {
-    // one token tile of 129..256 columns: splitting the TOKENS over two pairs (weights re-read from L2, no
-    // partial-sum traffic) can beat splitting K, whose exchange moves M x N x 4 bytes per slice through L2
-    const double w_bytes = (double)N * K;
-    float best = plan_cost((M + 15) / 16 * 16, g.n_ptiles, splits, g.num_kb, max_pairs, w_bytes);
-    const int tok2 = (ceil_div(M, 2) + 15) / 16 * 16;
+  const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
+  const int budget = 227 * 1024 - 1024 /*alignment slack*/ - tail;
+  const double w_bytes = (double)N * K, a_bytes = (double)M * K;
+  // candidates: token tiles of <= 256 columns (one more split of a single 129..256-token tile in two), K slices
+  // 1..8 as long as a slice keeps >= 4 k-blocks and all clusters of the tile grid are resident at once
+  const int mt_min = ceil_div(M, kMaxTokTile);
+  float best = -1.f;
+  g.m_tiles = mt_min;
+  g.splits = 1;
+  for (int mt = mt_min; mt <= mt_min + ((M > 128 && M <= kMaxTokTile) ? 1 : 0); ++mt) {
+    const int tok = (ceil_div(M, mt) + 15) / 16 * 16;
     for (int s = 1; s <= kMaxSplits; ++s) {
-      if (s > 1 && !(2 * g.n_ptiles * s <= max_pairs && g.num_kb / s >= 4)) break;
-      const float c = plan_cost(tok2, 2 * g.n_ptiles, s, g.num_kb, max_pairs, w_bytes);
-      if (c < best * 0.95f) {
+      if (s > 1) {
+        if (g.num_kb / s < 4) break;
+        if (mt * g.n_ptiles * s > max_pairs) break;
+        if (ceil_div(g.num_kb, ceil_div(g.num_kb, s)) != s) continue;   // this s does not give s non-empty slices
+        if (max_clusters_cached(2 * s, (size_t)227 * 1024) < mt * g.n_ptiles) continue;   // cluster shape not placeable
+      }
+      const float c = plan_cost(tok, mt, g.n_ptiles, s, g.num_kb, max_pairs, w_bytes, a_bytes);
+      if (best < 0.f || c < best * (mt > mt_min ? 0.95f : 1.0f) - 1e-6f) {
         best = c;
-        g.m_tiles = 2;
-        splits = s;
+        g.m_tiles = mt;
+        g.splits = s;
       }
     }
   }
   g.tok_tile = (ceil_div(M, g.m_tiles) + 15) / 16 * 16;
   g.tiles = g.m_tiles * g.n_ptiles;
-  const int a_bytes = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
-  g.stage_bytes = kWTileBytes + a_bytes;
-  const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
-  const int budget = 227 * 1024 - 1024 /*alignment slack*/ - tail;
+  const int a_tile = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
+  g.stage_bytes = kWTileBytes + a_tile;
   g.stages = budget / g.stage_bytes;
   if (g.stages > kMaxStages) g.stages = kMaxStages;
-  g.kb_per_split = ceil_div(g.num_kb, splits);
-  g.splits = ceil_div(g.num_kb, g.kb_per_split);
+  g.kb_per_split = ceil_div(g.num_kb, g.splits);
   g.col_chunk = (ceil_div(g.tok_tile, g.splits) + 15) / 16 * 16;
-  g.units = g.tiles * g.splits;
-  g.pairs = g.units < max_pairs ? g.units : max_pairs;
-  if (g.stages > g.kb_per_split && g.units <= g.pairs) g.stages = g.kb_per_split < 2 ? 2 : g.kb_per_split;
+  g.clusters = g.splits > 1 ? g.tiles : (g.tiles < max_pairs ? g.tiles : max_pairs);
+  if (g.stages > g.kb_per_split && g.tiles <= g.clusters) g.stages = g.kb_per_split < 2 ? 2 : g.kb_per_split;
   size_t main_bytes = (size_t)g.stages * g.stage_bytes;
-  const size_t region = (size_t)g.col_chunk * kCtaRows * 4;  // one (owner, source) region
+  const size_t region = (size_t)g.col_chunk * kCtaRows * 4;  // one source slot of the DSMEM receive buffer
   if (g.splits > 1 && (g.splits - 1) * region > main_bytes)
     main_bytes = ((g.splits - 1) * region + 1023) / 1024 * 1024;
   g.main_bytes = main_bytes;
   g.smem = 1024 + main_bytes + tail;
-  g.ws_bytes = g.splits > 1
-                   ? (size_t)kCounterBytes + (size_t)g.tiles * 2 * g.splits * g.splits * region
-                   : 0;
+  // stream-K: more tiles than pairs and a ragged last round -- every pair takes ceil(U / P) k-blocks instead of
+  // `rounds` whole tiles.  Needs ranges of at least one tile (a tile is then cut at most once).
+  g.streamk = 0;
+  g.ws_bytes = 0;
+  if (g.splits == 1 && g.tiles > max_pairs) {
+    const int rounds = ceil_div(g.tiles, max_pairs);
+    const long long U = (long long)g.tiles * g.num_kb;
+    const long long per_pair = (U + max_pairs - 1) / max_pairs;
+    if (per_pair >= g.num_kb && per_pair * 100 <= (long long)rounds * g.num_kb * 92) {
+      g.streamk = 1;
+      g.ws_bytes = kSkFlagBytes + (size_t)max_pairs * 2 * g.tok_tile * kCtaRows * 4;
+    }
+  }
   return g;
+}
+
+template <typename OutT>
+static cudaError_t prepare_kernel(int cluster_ctas) {
+  auto kern = scaled_mm_kernel<OutT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e == cudaSuccess && cluster_ctas > 8)
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  return e;
+}
+
+// How many clusters of `cluster_ctas` CTAs (one CTA per SM: the kernel takes the whole shared memory) the device
+// can hold at once; 0 when the shape cannot be placed at all.  Asked once per cluster size.
+static int max_clusters_cached(int cluster_ctas, size_t smem) {
+  static int cache[2 * kMaxSplits + 1];   // 0 = not asked yet, -1 = not placeable
+  if (cluster_ctas <= 2) return num_sms() / 2;
+  if (cache[cluster_ctas] == 0) {
+    int n = 0;
+    if (prepare_kernel<__nv_bfloat16>(cluster_ctas) == cudaSuccess) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(cluster_ctas * 64, 1, 1);
+      cfg.blockDim = dim3(kThreads);
+      cfg.dynamicSmemBytes = smem;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = cluster_ctas;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&n, scaled_mm_kernel<__nv_bfloat16>, &cfg) != cudaSuccess) n = 0;
+    }
+    (void)cudaGetLastError();
+    cache[cluster_ctas] = n > 0 ? n : -1;
+  }
+  return cache[cluster_ctas] > 0 ? cache[cluster_ctas] : 0;
 }
 
 template <typename OutT>
 static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, const Params& p,
                   cudaStream_t stream) {
   auto kern = scaled_mm_kernel<OutT>;
-  VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  const int cluster_ctas = 2 * g.splits;
+  VB_CUDA_CHECK(prepare_kernel<OutT>(cluster_ctas));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * g.pairs, 1, 1);
+  cfg.gridDim = dim3(cluster_ctas * g.clusters, 1, 1);
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = g.smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.x = cluster_ctas;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -510,17 +710,40 @@ static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, c
   return 0;
 }
 
+static int g_force_splits = 0;   // debug / tuning hook (vb200_debug_scaled_mm_plan): 0 = planner's choice
+static int g_force_mtiles = 0;
+static int g_no_streamk = 0;     // debug: 1 = whole tiles per pair even when stream-K applies
+
 static int run(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
-               int a_scales_numel, int b_scales_numel, int out_dtype, void* workspace,
-               size_t workspace_bytes, cudaStream_t stream) {
+               int a_scales_numel, int b_scales_numel, int out_dtype, void* workspace, size_t workspace_bytes,
+               cudaStream_t stream) {
   Plan g = make_plan(M, N, K);
-  if (g.splits > 1 && (workspace == nullptr || workspace_bytes < g.ws_bytes)) {
-    // no (or too small a) workspace: run unsplit rather than fail
-    g.splits = 1;
-    g.kb_per_split = g.num_kb;
-    g.units = g.tiles;
-    g.pairs = g.units < num_sms() / 2 ? g.units : num_sms() / 2;
+  // stream-K parks partial tiles in the caller's workspace; without one (or with the debug switch) whole tiles
+  if (g.streamk && (g_no_streamk || workspace == nullptr || workspace_bytes < g.ws_bytes)) g.streamk = 0;
+  if (g_force_splits > 0 || g_force_mtiles > 0) {
+    g.streamk = 0;
+    // re-derive the plan for a forced (token tiles, K slices) pair -- same arithmetic as make_plan's tail
+    if (g_force_mtiles > 0) g.m_tiles = g_force_mtiles;
+    if (g_force_splits > 0) g.splits = g_force_splits;
+    VB_CHECK(ceil_div(M, g.m_tiles) <= kMaxTokTile, "scaled_mm debug plan: token tile too large");
+    g.tok_tile = (ceil_div(M, g.m_tiles) + 15) / 16 * 16;
+    g.tiles = g.m_tiles * g.n_ptiles;
+    g.kb_per_split = ceil_div(g.num_kb, g.splits);
+    VB_CHECK(ceil_div(g.num_kb, g.kb_per_split) == g.splits, "scaled_mm debug plan: empty K slice");
+    const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;
+    const int a_tile = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
+    g.stage_bytes = kWTileBytes + a_tile;
+    g.stages = (227 * 1024 - 1024 - tail) / g.stage_bytes;
+    if (g.stages > kMaxStages) g.stages = kMaxStages;
+    g.col_chunk = (ceil_div(g.tok_tile, g.splits) + 15) / 16 * 16;
+    const int max_pairs = num_sms() / 2;
+    g.clusters = g.splits > 1 ? g.tiles : (g.tiles < max_pairs ? g.tiles : max_pairs);
+    size_t main_bytes = (size_t)g.stages * g.stage_bytes;
+    const size_t region = (size_t)g.col_chunk * kCtaRows * 4;
+    if (g.splits > 1 && (g.splits - 1) * region > main_bytes) main_bytes = ((g.splits - 1) * region + 1023) / 1024 * 1024;
+    g.main_bytes = main_bytes;
+    g.smem = 1024 + main_bytes + tail;
   }
   CUtensorMap tw, ta;
   if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kCtaRows)) return 1;
@@ -531,9 +754,6 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
   p.a_scales = a_scales;
   p.b_scales = b_scales;
   p.bias = bias;
-  p.counters = reinterpret_cast<uint32_t*>(workspace);
-  p.partials = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kCounterBytes)
-                         : nullptr;
   p.M = M;
   p.N = N;
   p.K = K;
@@ -549,8 +769,10 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
   p.kb_per_split = g.kb_per_split;
   p.num_kb = g.num_kb;
   p.col_chunk = g.col_chunk;
-  p.units = g.units;
   p.main_bytes = (uint32_t)g.main_bytes;
+  p.streamk = g.streamk;
+  p.sk_flags = reinterpret_cast<uint32_t*>(workspace);
+  p.sk_partials = g.streamk ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kSkFlagBytes) : nullptr;
   // weights are streamed once when there is a single token tile; otherwise they are re-read from L2
   p.hint_w = g.m_tiles == 1 ? kEvictFirst : kEvictNormal;
   p.hint_a = g.m_tiles == 1 ? kEvictLast : kEvictNormal;
@@ -572,6 +794,29 @@ extern "C" void vb200_debug_scaled_mm_trace(void* buf) { v2::g_trace = (unsigned
 
 extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100 ? 1 : 0; }
 
+// Debug / tuning hook (not part of the drop-in surface): force the number of K slices and / or token tiles of the
+// following launches (0 = planner's choice); plan[0..5] (if non-NULL) receives the planner's choice for (M, N, K):
+// token tile, token tiles, K slices, cluster CTAs, clusters, pipeline stages, stream-K (plan[0..6]).
+extern "C" void vb200_debug_scaled_mm_plan(int force_splits, int force_mtiles, int M, int N, int K, int* plan) {
+  v2::g_no_streamk = force_splits < 0 ? 1 : 0;     // force_splits = -1: planner's choice, but no stream-K
+  if (force_splits < 0) force_splits = 0;
+  v2::g_force_splits = force_splits;
+  v2::g_force_mtiles = force_mtiles;
+  if (plan != nullptr && M > 0 && N > 0 && K > 0) {
+    const v2::Plan g = v2::make_plan(M, N, K);
+    plan[0] = g.tok_tile;
+    plan[1] = g.m_tiles;
+    plan[2] = g.splits;
+    plan[3] = 2 * g.splits;
+    plan[4] = g.clusters;
+    plan[5] = g.stages;
+    plan[6] = g.streamk;
+  }
+}
+
+// Split-K reduces through distributed shared memory inside a cluster and needs no workspace; only the stream-K plan
+// (more tiles than CTA pairs, ragged last round) parks partial tiles in one.  0 = none needed.  The first 4 KiB must be
+// zero before the first launch (the kernel re-arms them); one workspace per stream.
 extern "C" size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   return v2::make_plan(M, N, K).ws_bytes;
