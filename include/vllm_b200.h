@@ -330,6 +330,26 @@ int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, const float* a
                          const int32_t* problem_sizes, int num_rows, int E, int N, int K,
                          int per_act_token, int per_out_ch, int out_dtype, vb200_stream_t stream);
 
+/* The two ends of the permuted MoE pipeline as single launches (B200 path of cutlass_moe_fp8; the reference runs
+ * scaled_fp8_quant + shuffle_rows (+ shuffle_rows of the scales) before GEMM 1 and shuffle_rows + mul_ + moe_sum after
+ * GEMM 2: fused_moe/cutlass_moe.py:142-150,205-214, topk_weight_and_reduce.py:60-100).
+ * moe_gather_quant_fp8: for sorted row r < *num_routed (all rows when num_routed == NULL):
+ *   out[r, :] = fp8(input[src_row[r], :] quantised per row) -- dynamic per-token (static_scale == NULL; scales[r]
+ *   receives the row's scale, fp8/common.cu:28-83 arithmetic) or static per-tensor (*static_scale, common.cu:14-26).
+ *   Same bytes as quantising `input` first and gathering rows afterwards.  input bf16/f16 [num_src_rows, hidden],
+ *   hidden % 8 == 0. */
+int vb200_moe_gather_quant_fp8(void* out, float* scales, const void* input, const int32_t* src_row,
+                               const int32_t* num_routed, const float* static_scale, const float* scale_ub,
+                               int num_dst_rows, int num_src_rows, int hidden, int in_dtype, vb200_stream_t stream);
+/* moe_unpermute_reduce: out[t, :] = sum_j T(float(c[dst_row[t*topk + j], :]) * topk_weights[t, j]); rows with
+ * dst_row >= *num_routed (ids no local expert owns, moe_data.cu:92-99) contribute zero; topk_weights == NULL skips
+ * the multiply.  Rounding points = `fused_out.mul_(topk_weights)` followed by moe_sum (accumulation in T in j order
+ * for topk 2..4, fp32 otherwise: moe_align_sum_kernels.cu:109-123,277-318).  c [*, hidden], out [num_tokens, hidden]
+ * bf16/f16, hidden % 8 == 0. */
+int vb200_moe_unpermute_reduce(void* out, const void* c, const int32_t* dst_row, const float* topk_weights,
+                               const int32_t* num_routed, int num_tokens, int topk, int hidden, int dtype,
+                               vb200_stream_t stream);
+
 /* ---- callers either side of the path --------------------------------- */
 
 /* advance_step_flashattn: csrc/prepare_inputs/advance_step.cu:176-232 (kernel :13-65), schema

@@ -328,3 +328,155 @@ def test_cutlass_moe_fp8_matches_fused_experts():
     scale = max(y.float().abs().max().item(), 1.0)
     torch.testing.assert_close(x.float(), y.float(), rtol=2e-2, atol=2e-2 * scale)
     assert (x.float() - y.float()).abs().mean().item() <= 3e-3 * scale
+
+
+# ---- the fused ends of the permuted pipeline (one launch each) vs the stand-alone ops they replace --------------
+@pytest.mark.parametrize("T,k,E,hidden", [(1, 2, 8, 128), (33, 2, 8, 1024), (128, 2, 8, 4096), (64, 6, 64, 256),
+                                          (200, 4, 16, 2048)])
+@pytest.mark.parametrize("mode", ["per_token", "static"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("invalid", [0.0, 0.3])
+def test_gather_quant_matches_quant_then_shuffle(T, k, E, hidden, mode, dtype, invalid):
+    """moe_gather_quant_fp8 == scaled_fp8_quant followed by shuffle_rows of codes and scales (cutlass_moe.py:142-150),
+    bit for bit, on every routed row; rows past the routed count are not written."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(T * 7 + hidden)
+    a = (torch.randn(T, hidden) * 2).to(dtype).to(DEV)
+    ids = _ids(T, k, E, invalid).to(DEV)
+    rows = T * k
+    eo = torch.empty(E + 1, dtype=torch.int32, device=DEV)
+    ps = torch.empty(E, 3, dtype=torch.int32, device=DEV)
+    a_map = torch.zeros(rows, dtype=torch.int32, device=DEV)
+    c_map = torch.empty(rows, dtype=torch.int32, device=DEV)
+    ops.get_cutlass_moe_mm_data(ids, eo, ps, ps.clone(), a_map, c_map, E, 64, hidden)
+    static = torch.tensor([0.03], device=DEV) if mode == "static" else None
+    q, s = ops.scaled_fp8_quant(a, static, use_per_token_if_dynamic=mode == "per_token")
+    want_q = ops.shuffle_rows(q, a_map)
+    got_q, got_s = ops.moe_gather_quant_fp8(a, a_map, eo[-1:], scale=static)
+    torch.cuda.synchronize()
+    n = int(eo[-1])
+    assert n == int((ids >= 0).sum())
+    assert torch.equal(got_q[:n].view(torch.uint8), want_q[:n].view(torch.uint8))
+    if mode == "per_token":
+        want_s = ops.shuffle_rows(s.view(T, 1), a_map)
+        assert torch.equal(got_s[:n], want_s[:n])
+    else:
+        assert got_s.data_ptr() == static.data_ptr()
+    # without the bound every row is written (a_map is zero-filled past the routed rows)
+    got_q2, _ = ops.moe_gather_quant_fp8(a, a_map, None, scale=static)
+    torch.cuda.synchronize()
+    assert torch.equal(got_q2.view(torch.uint8), want_q.view(torch.uint8))
+
+
+@pytest.mark.parametrize("T,k,hidden", [(1, 1, 128), (33, 2, 1024), (128, 2, 4096), (64, 3, 256), (50, 4, 512),
+                                        (40, 6, 256)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("weighted", [True, False])
+@pytest.mark.parametrize("invalid", [0.0, 0.3])
+def test_unpermute_reduce_matches_shuffle_mul_sum(T, k, hidden, dtype, weighted, invalid):
+    """moe_unpermute_reduce == shuffle_rows(c3, c_map) -> mul_(topk_weights) -> moe_sum (cutlass_moe.py:205-214,
+    topk_weight_and_reduce.py:60-100), bit for bit; (token, j) pairs of foreign experts contribute zero."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(T + k + hidden)
+    E = 8
+    ids = _ids(T, k, E, invalid).to(DEV)
+    rows = T * k
+    eo = torch.empty(E + 1, dtype=torch.int32, device=DEV)
+    ps = torch.empty(E, 3, dtype=torch.int32, device=DEV)
+    a_map = torch.zeros(rows, dtype=torch.int32, device=DEV)
+    c_map = torch.empty(rows, dtype=torch.int32, device=DEV)
+    ops.get_cutlass_moe_mm_data(ids, eo, ps, ps.clone(), a_map, c_map, E, 64, hidden)
+    torch.cuda.synchronize()
+    n = int(eo[-1])
+    c3 = torch.randn(rows, hidden, device=DEV).to(dtype)
+    c3_ref = c3.clone()
+    c3_ref[n:] = 0            # the reference zero-fills c3 so that row `n` reads as zero (cutlass_moe.py:196-197)
+    c3[n:] = float("nan")     # the fused kernel must never read those rows
+    w = torch.softmax(torch.randn(T, k, device=DEV), -1)
+    fused = ops.shuffle_rows(c3_ref, c_map.clamp(max=rows - 1)).view(T, k, hidden)
+    if weighted:
+        fused.mul_(w.view(T, k, 1))
+    want = torch.empty(T, hidden, device=DEV, dtype=dtype)
+    ops.moe_sum(fused, want)
+    got = ops.moe_unpermute_reduce(c3, c_map, w if weighted else None, eo[-1:], T, k)
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
+@pytest.mark.parametrize("per_act_token,per_out_ch", [(False, False), (True, True)])
+@pytest.mark.parametrize("use_expert_map", [False, True])
+def test_run_cutlass_moe_fp8_reference_entry(per_act_token, per_out_ch, use_expert_map):
+    """run_cutlass_moe_fp8 called the way the reference's CutlassExpertsFp8.apply does (cutlass_moe.py:287-321):
+    pre-quantised activations, caller-owned workspaces, un-weighted [M*topk, K] output in (token, j) order; its
+    weighted top-k sum must equal cutlass_moe_fp8 on the same inputs."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.fused_moe import cutlass_moe_fp8, run_cutlass_moe_fp8
+    seed_all(5)
+    T, k, E, inter, hidden = 96, 2, 8, 512, 256
+    w1q, w1s = _fp8_weights(E, 2 * inter, hidden, per_out_ch)
+    w2q, w2s = _fp8_weights(E, hidden, inter, per_out_ch)
+    a = (torch.randn(T, hidden) / 2).bfloat16().to(DEV)
+    ids = _ids(T, k, E).to(DEV)
+    tw = torch.softmax(torch.randn(T, k), -1).to(DEV)
+    emap = None
+    if use_expert_map:
+        emap = torch.full((E,), -1, dtype=torch.int32)
+        emap[:E // 2] = torch.arange(E // 2, dtype=torch.int32)
+        emap = emap.to(DEV)
+        w1q, w1s, w2q, w2s = w1q[:E // 2], w1s[:E // 2], w2q[:E // 2], w2s[:E // 2]
+    w1q, w2q, w1s, w2s = (t.contiguous().to(DEV) for t in (w1q, w2q, w1s, w2s))
+    a1q, a1s = ops.scaled_fp8_quant(a, None, use_per_token_if_dynamic=per_act_token)
+    ws13 = torch.empty(T * k * max(2 * inter, hidden), dtype=a.dtype, device=DEV)
+    ws2 = torch.empty(T * k * inter, dtype=a.dtype, device=DEV)
+    out = torch.full((T * k, hidden), float("nan"), dtype=a.dtype, device=DEV)
+
+    def act(o, i):
+        ops.silu_and_mul(o, i)
+    run_cutlass_moe_fp8(out, a1q, w1q, w2q, ids, act, E, emap, w1s, w2s, a1s, None, ws13, ws2, None, a.dtype,
+                        per_act_token, per_out_ch, False)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    if use_expert_map:   # (token, j) pairs of foreign experts read as zero rows
+        foreign = (emap[ids.long()] < 0).view(-1)
+        assert (out[foreign] == 0).all() and foreign.any()
+    x = (out.view(T, k, hidden).float() * tw.view(T, k, 1)).to(a.dtype)
+    got = torch.empty(T, hidden, dtype=a.dtype, device=DEV)
+    ops.moe_sum(x, got)
+    want = cutlass_moe_fp8(a, w1q, w2q, tw, ids, w1s, w2s, per_act_token=per_act_token, expert_map=emap,
+                           global_num_experts=E)
+    torch.cuda.synchronize()
+    scale = max(want.float().abs().max().item(), 1.0)
+    # the same ops in the same order on both routes
+    torch.testing.assert_close(got.float(), want.float(), rtol=0, atol=1e-3 * scale)
+
+
+def test_run_cutlass_moe_fp8_batched_format():
+    """Batched-experts format (cutlass_moe.py:105-126): hidden_states [E, padded_M, K], expert_num_tokens rows valid
+    per expert; valid rows equal the per-expert dense computation of the oracle."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.fused_moe import run_cutlass_moe_fp8
+    seed_all(9)
+    E, padded_M, inter, hidden = 4, 32, 256, 128
+    counts = torch.tensor([32, 0, 7, 19], dtype=torch.int32)
+    w1q, w1s = _fp8_weights(E, 2 * inter, hidden, True)
+    w2q, w2s = _fp8_weights(E, hidden, inter, True)
+    a = (torch.randn(E, padded_M, hidden) / 2).bfloat16()
+    a1q, a1s = oq.dynamic_per_token_scaled_fp8_quant(a.view(-1, hidden))
+    out = torch.zeros(E, padded_M, hidden, dtype=torch.bfloat16, device=DEV)
+    ws13 = torch.empty(E * padded_M * max(2 * inter, hidden), dtype=torch.bfloat16, device=DEV)
+    ws2 = torch.empty(E * padded_M * inter, dtype=torch.bfloat16, device=DEV)
+    run_cutlass_moe_fp8(out, a1q.view(E, padded_M, hidden).to(DEV), w1q.to(DEV), w2q.to(DEV), None,
+                        lambda o, i: ops.silu_and_mul(o, i), E, None, w1s.view(E, -1, 1).to(DEV),
+                        w2s.view(E, -1, 1).to(DEV), a1s.view(E, padded_M, 1).to(DEV), None, ws13, ws2, counts.to(DEV),
+                        torch.bfloat16, True, True, True)
+    torch.cuda.synchronize()
+    offs = torch.arange(E, dtype=torch.int32) * padded_M
+    c1 = omoe.cutlass_moe_mm(a1q, w1q, a1s.view(-1), w1s, offs, counts, torch.bfloat16)
+    c2 = omoe.silu_and_mul(c1)
+    a2q, a2s = oq.dynamic_per_token_scaled_fp8_quant(c2)
+    c3 = omoe.cutlass_moe_mm(a2q, w2q, a2s.view(-1), w2s, offs, counts, torch.bfloat16).view(E, padded_M, hidden)
+    for e in range(E):
+        m = int(counts[e])
+        if m:
+            g, w = out[e, :m].cpu().float(), c3[e, :m].float()
+            torch.testing.assert_close(g, w, rtol=2e-2, atol=2e-2 * max(w.abs().max().item(), 1.0))

@@ -487,19 +487,28 @@ def get_cutlass_pplx_moe_mm_data(expert_offsets: torch.Tensor, problem_sizes1: t
             num_local_experts, padded_m, n, k, stream()))
 
 
-def shuffle_rows(input_tensor: torch.Tensor, dst2src_map: torch.Tensor) -> torch.Tensor:
-    """vllm/_custom_ops.py:912-922: output[r] = input[dst2src_map[r]] (allocates the output like the reference)."""
-    require_cuda(input_tensor, dst2src_map)
+def shuffle_rows_into(out: torch.Tensor, input_tensor: torch.Tensor, dst2src_map: torch.Tensor) -> torch.Tensor:
+    """shuffle_rows into a caller-owned contiguous [len(dst2src_map), cols] tensor (no allocation)."""
+    require_cuda(input_tensor, dst2src_map, out)
     _i32c("shuffle_rows", dst2src_map)
     if input_tensor.dim() != 2 or not input_tensor.is_contiguous():
         raise RuntimeError("shuffle_rows: input must be a contiguous 2-D tensor")
-    out = torch.empty((dst2src_map.shape[0], input_tensor.shape[1]), device=input_tensor.device,
-                      dtype=input_tensor.dtype)
+    if out.shape != (dst2src_map.shape[0], input_tensor.shape[1]) or out.dtype != input_tensor.dtype or \
+            not out.is_contiguous():
+        raise RuntimeError("shuffle_rows: out must be a contiguous [len(dst2src_map), cols] tensor of the input dtype")
     with _device_of(input_tensor):
         check(load().vb200_shuffle_rows(ptr(out), ptr(input_tensor), ptr(dst2src_map), out.size(0),
                                         input_tensor.size(0), input_tensor.size(1) * input_tensor.element_size(),
                                         stream()))
     return out
+
+
+def shuffle_rows(input_tensor: torch.Tensor, dst2src_map: torch.Tensor) -> torch.Tensor:
+    """vllm/_custom_ops.py:912-922: output[r] = input[dst2src_map[r]] (allocates the output like the reference)."""
+    require_cuda(input_tensor, dst2src_map)
+    out = torch.empty((dst2src_map.shape[0], input_tensor.shape[1]), device=input_tensor.device,
+                      dtype=input_tensor.dtype)
+    return shuffle_rows_into(out, input_tensor, dst2src_map)
 
 
 def cutlass_moe_mm(out_tensors: torch.Tensor, a_tensors: torch.Tensor, b_tensors: torch.Tensor,
@@ -545,6 +554,53 @@ def cutlass_moe_mm(out_tensors: torch.Tensor, a_tensors: torch.Tensor, b_tensors
             ptr(expert_offsets), ptr(problem_sizes), a_tensors.size(0), E, N, K, int(per_act_token),
             int(per_out_ch), dtype_enum(out_tensors.dtype), stream()))
 
+
+def moe_gather_quant_fp8(input: torch.Tensor, src_row: torch.Tensor, num_routed: Optional[torch.Tensor] = None,
+                         scale: Optional[torch.Tensor] = None, scale_ub: Optional[torch.Tensor] = None):
+    """B200 path of the CUTLASS-style MoE front end: ONE launch for `scaled_fp8_quant` followed by `shuffle_rows`
+    (of the codes and of the per-token scales; fused_moe/cutlass_moe.py:142-150).  Row r of the result is row
+    `src_row[r]` of `input` quantised to fp8 -- with `scale` (static per-tensor, [1] fp32) or, when `scale` is None,
+    with the row's own dynamic scale, returned as `[rows, 1]` fp32.  `num_routed` (int32 [1] on the device, e.g.
+    `expert_offsets[-1:]`) bounds the rows that are written.  Returns (codes, scales)."""
+    require_cuda(input, src_row, num_routed, scale, scale_ub)
+    _i32c("moe_gather_quant_fp8", src_row, num_routed)
+    if input.dim() != 2 or not input.is_contiguous() or input.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("moe_gather_quant_fp8: input must be a contiguous 2-D bf16 / f16 tensor")
+    rows = src_row.numel()
+    out = torch.empty((rows, input.size(1)), device=input.device, dtype=torch.float8_e4m3fn)
+    scales = scale if scale is not None else torch.empty((rows, 1), device=input.device, dtype=torch.float32)
+    with _device_of(input):
+        check(load().vb200_moe_gather_quant_fp8(
+            ptr(out), None if scale is not None else ptr(scales), ptr(input), ptr(src_row), ptr(num_routed),
+            ptr(scale), ptr(scale_ub), rows, input.size(0), input.size(1), dtype_enum(input.dtype), stream()))
+    return out, scales
+
+
+def moe_unpermute_reduce(c: torch.Tensor, dst_row: torch.Tensor, topk_weights: Optional[torch.Tensor],
+                         num_routed: torch.Tensor, num_tokens: int, topk: int,
+                         out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """B200 path of the CUTLASS-style MoE back end: ONE launch for `shuffle_rows(c, c_map)`, the in-place multiply by
+    the routing weights and `moe_sum` (cutlass_moe.py:205-214, topk_weight_and_reduce.py:60-100) with the same
+    rounding points.  c [rows, hidden]; dst_row int32 [num_tokens*topk] (flat (token, j) -> row of c; rows >=
+    *num_routed count as zero); topk_weights fp32 [num_tokens, topk] or None."""
+    require_cuda(c, dst_row, topk_weights, num_routed, out)
+    _i32c("moe_unpermute_reduce", dst_row, num_routed)
+    if c.dim() != 2 or not c.is_contiguous() or c.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("moe_unpermute_reduce: c must be a contiguous 2-D bf16 / f16 tensor")
+    if dst_row.numel() < num_tokens * topk:
+        raise RuntimeError("moe_unpermute_reduce: dst_row needs num_tokens * topk entries")
+    if topk_weights is not None:
+        if topk_weights.dtype != torch.float32 or topk_weights.numel() != num_tokens * topk:
+            raise RuntimeError("moe_unpermute_reduce: topk_weights must be fp32 [num_tokens, topk]")
+        topk_weights = topk_weights.contiguous()
+    if out is None:
+        out = torch.empty((num_tokens, c.size(1)), device=c.device, dtype=c.dtype)
+    elif out.dtype != c.dtype or not out.is_contiguous() or out.numel() != num_tokens * c.size(1):
+        raise RuntimeError("moe_unpermute_reduce: out must be a contiguous [num_tokens, hidden] tensor of c's dtype")
+    with _device_of(c):
+        check(load().vb200_moe_unpermute_reduce(ptr(out), ptr(c), ptr(dst_row), ptr(topk_weights), ptr(num_routed),
+                                                num_tokens, topk, c.size(1), dtype_enum(c.dtype), stream()))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------

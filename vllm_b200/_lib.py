@@ -86,6 +86,8 @@ SIGNATURES = {
     "vb200_get_cutlass_moe_mm_data": (c_int, [_P, c_int, c_int, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P]),
     "vb200_get_cutlass_pplx_moe_mm_data": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_shuffle_rows": (c_int, [_P, _P, _P, c_int, c_int, c_int64, _P]),
+    "vb200_moe_gather_quant_fp8": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
+    "vb200_moe_unpermute_reduce": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_advance_step_flashattn": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int64, _P]),
     "vb200_merge_attn_states": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
     "vb200_peer_allreduce_signal_bytes": (c_size_t, []),

@@ -138,6 +138,133 @@ __global__ void __launch_bounds__(256) shuffle_rows_kernel(uint8_t* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// The two ends of the permuted pipeline as single launches (what the B200 path of cutlass_moe_fp8 uses instead of
+// "quantise, then shuffle_rows" and "shuffle_rows, multiply by the routing weights, moe_sum"):
+//   gather + quantise   a_q[r, :] = fp8(a[src_row[r], :] / s_r)   s_r = the row's dynamic per-token scale
+//                       (/root/reference/csrc/quantization/fp8/common.cu:28-83) or the static *scale (:14-26);
+//                       per-token quantisation is row-wise, so quantising the gathered row gives the same bytes as
+//                       gathering the quantised row (cutlass_moe.py:142-150 `_fp8_perm`).
+//   un-permute + weight + reduce   out[t, :] = sum_j T(float(c[dst_row[t*k+j], :]) * w[t, j]), accumulated like
+//                       moe_sum (in T, j order for k in 2..4; fp32 otherwise), rows past *num_routed count as zero
+//                       (TopKWeightAndReduceContiguous, topk_weight_and_reduce.py:60-100 + moe_data.cu:92-99).
+// ---------------------------------------------------------------------------------------------
+constexpr float kE4m3Max = 448.f;
+
+template <typename T>
+__global__ void __launch_bounds__(256) moe_gather_quant_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
+                                                               const T* __restrict__ in,
+                                                               const int* __restrict__ src_row,
+                                                               const int* __restrict__ num_routed,
+                                                               const float* __restrict__ static_scale,
+                                                               const float* __restrict__ scale_ub, int num_src,
+                                                               int hidden) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float sm[8];
+  const int r = blockIdx.x;
+  if (num_routed != nullptr && r >= *num_routed) return;   // rows no local expert owns: never read downstream
+  const int s_row = src_row[r];
+  if (s_row < 0 || s_row >= num_src) return;
+  constexpr int VE = 16 / sizeof(T);
+  const T* rin = in + (int64_t)s_row * hidden;
+  uint8_t* rout = out + (int64_t)r * hidden;
+  const int nvec = hidden / VE;   // host guarantees hidden % VE == 0 and 16-byte aligned rows
+  float s;
+  if (static_scale != nullptr) {
+    s = 1.0f / *static_scale;     // common.cu:23: multiply by the reciprocal
+  } else {
+    float m = 0.f;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      union { uint4 u; T e[VE]; } v;
+      v.u = *reinterpret_cast<const uint4*>(rin + (int64_t)i * VE);
+#pragma unroll
+      for (int j = 0; j < VE; ++j) m = fmaxf(m, fabsf(to_float<T>(v.e[j])));
+    }
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = warp_max((threadIdx.x & 31) < (blockDim.x >> 5) ? sm[threadIdx.x & 31] : 0.f);
+    s = scale_ub ? fminf(m, *scale_ub) : m;
+    s = fmaxf(s / kE4m3Max, 1.0f / (kE4m3Max * 512.0f));   // common.cu:66-68
+    if (threadIdx.x == 0) scales[r] = s;
+  }
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    union { uint4 u; T e[VE]; } v;
+    v.u = *reinterpret_cast<const uint4*>(rin + (int64_t)i * VE);   // second pass hits L1/L2
+    union { uint2 u2; uint8_t b[8]; } o;
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      const float x = to_float<T>(v.e[j]);
+      const float q = static_scale != nullptr ? x * s : x / s;      // true division on the per-token path (:74)
+      o.b[j] = float_to_e4m3(fmaxf(-kE4m3Max, fminf(q, kE4m3Max)));
+    }
+    *reinterpret_cast<uint2*>(rout + (int64_t)i * VE) = o.u2;
+  }
+}
+
+template <typename T, int TOPK>
+__global__ void __launch_bounds__(256) moe_unpermute_reduce_kernel(T* __restrict__ out, const T* __restrict__ c,
+                                                                   const int* __restrict__ dst_row,
+                                                                   const float* __restrict__ weights,
+                                                                   const int* __restrict__ num_routed, int topk,
+                                                                   int hidden) {
+  pdl_wait();
+  pdl_trigger();
+  constexpr int VE = 16 / sizeof(T);
+  constexpr int KMAX = TOPK > 0 ? TOPK : 1;
+  const int64_t t = blockIdx.x;
+  const int limit = *num_routed;
+  const int nvec = hidden / VE;
+  if (TOPK > 0) {
+    int rows[KMAX];
+    float w[KMAX];
+#pragma unroll
+    for (int j = 0; j < KMAX; ++j) {
+      rows[j] = dst_row[t * TOPK + j];
+      w[j] = weights ? weights[t * TOPK + j] : 1.f;
+    }
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      union { uint4 u; T e[VE]; } acc, v;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) acc.e[e] = from_float<T>(0.f);
+#pragma unroll
+      for (int j = 0; j < KMAX; ++j) {
+        if (rows[j] >= 0 && rows[j] < limit) v.u = ldg_stream_v4(c + (int64_t)rows[j] * hidden + (int64_t)i * VE);
+        else v.u = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) {
+          // fused_out.mul_(w): fp32 product rounded once to T; moe_sum: adds in T, j order, from 0
+          const float p = weights ? to_float<T>(from_float<T>(to_float<T>(v.e[e]) * w[j])) : to_float<T>(v.e[e]);
+          acc.e[e] = from_float<T>(to_float<T>(acc.e[e]) + p);
+        }
+      }
+      *reinterpret_cast<uint4*>(out + t * hidden + (int64_t)i * VE) = acc.u;
+    }
+  } else {
+    // other top-k: at::sum_out semantics (fp32 accumulation of the T-rounded products, one final rounding)
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      float acc[VE];
+#pragma unroll
+      for (int e = 0; e < VE; ++e) acc[e] = 0.f;
+      for (int j = 0; j < topk; ++j) {
+        const int row = dst_row[t * topk + j];
+        if (row < 0 || row >= limit) continue;
+        const float wj = weights ? weights[t * topk + j] : 1.f;
+        union { uint4 u; T e[VE]; } v;
+        v.u = ldg_stream_v4(c + (int64_t)row * hidden + (int64_t)i * VE);
+#pragma unroll
+        for (int e = 0; e < VE; ++e)
+          acc[e] += weights ? to_float<T>(from_float<T>(to_float<T>(v.e[e]) * wj)) : to_float<T>(v.e[e]);
+      }
+      union { uint4 u; T e[VE]; } o;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) o.e[e] = from_float<T>(acc[e]);
+      *reinterpret_cast<uint4*>(out + t * hidden + (int64_t)i * VE) = o.u;
+    }
+  }
+}
+
 }  // namespace vb200
 
 using namespace vb200;
@@ -194,4 +321,59 @@ extern "C" int vb200_shuffle_rows(void* out, const void* in, const int32_t* dst2
                                                            row_bytes));
   VB_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int vb200_moe_gather_quant_fp8(void* out, float* scales, const void* input, const int32_t* src_row,
+                                          const int32_t* num_routed, const float* static_scale,
+                                          const float* scale_ub, int num_dst_rows, int num_src_rows, int hidden,
+                                          int in_dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (num_dst_rows <= 0 || hidden <= 0) return 0;
+  VB_CHECK(in_dtype == VB200_BF16 || in_dtype == VB200_F16, "moe_gather_quant_fp8: input must be bf16 or f16");
+  VB_CHECK(hidden % 8 == 0 && (reinterpret_cast<uintptr_t>(input) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+           "moe_gather_quant_fp8: hidden (%d) must be a multiple of 8 and the rows 16-byte aligned", hidden);
+  VB_CHECK(static_scale != nullptr || scales != nullptr, "moe_gather_quant_fp8: dynamic quantisation needs `scales`");
+  const int threads = hidden >= 2048 ? 256 : 128;
+  if (in_dtype == VB200_BF16)
+    VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__nv_bfloat16>, dim3(num_dst_rows), dim3(threads), 0, stream,
+                           (uint8_t*)out, scales, (const __nv_bfloat16*)input, src_row, num_routed, static_scale,
+                           scale_ub, num_src_rows, hidden));
+  else
+    VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__half>, dim3(num_dst_rows), dim3(threads), 0, stream,
+                           (uint8_t*)out, scales, (const __half*)input, src_row, num_routed, static_scale, scale_ub,
+                           num_src_rows, hidden));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+template <typename T>
+static int launch_unpermute_reduce(void* out, const void* c, const int32_t* dst_row, const float* weights,
+                                   const int32_t* num_routed, int num_tokens, int topk, int hidden,
+                                   cudaStream_t stream) {
+  const int threads = hidden >= 2048 ? 256 : 128;
+  T* o = (T*)out;
+  const T* ci = (const T*)c;
+  switch (topk) {
+    case 1: VB_CUDA_CHECK(launch_k(moe_unpermute_reduce_kernel<T, 1>, dim3(num_tokens), dim3(threads), 0, stream, o, ci, dst_row, weights, num_routed, topk, hidden)); break;
+    case 2: VB_CUDA_CHECK(launch_k(moe_unpermute_reduce_kernel<T, 2>, dim3(num_tokens), dim3(threads), 0, stream, o, ci, dst_row, weights, num_routed, topk, hidden)); break;
+    case 3: VB_CUDA_CHECK(launch_k(moe_unpermute_reduce_kernel<T, 3>, dim3(num_tokens), dim3(threads), 0, stream, o, ci, dst_row, weights, num_routed, topk, hidden)); break;
+    case 4: VB_CUDA_CHECK(launch_k(moe_unpermute_reduce_kernel<T, 4>, dim3(num_tokens), dim3(threads), 0, stream, o, ci, dst_row, weights, num_routed, topk, hidden)); break;
+    default: VB_CUDA_CHECK(launch_k(moe_unpermute_reduce_kernel<T, 0>, dim3(num_tokens), dim3(threads), 0, stream, o, ci, dst_row, weights, num_routed, topk, hidden)); break;
+  }
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_moe_unpermute_reduce(void* out, const void* c, const int32_t* dst_row, const float* topk_weights,
+                                          const int32_t* num_routed, int num_tokens, int topk, int hidden, int dtype,
+                                          vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (num_tokens <= 0 || hidden <= 0) return 0;
+  VB_CHECK(dtype == VB200_BF16 || dtype == VB200_F16, "moe_unpermute_reduce: dtype must be bf16 or f16");
+  VB_CHECK(topk >= 1 && num_routed != nullptr, "moe_unpermute_reduce: bad arguments");
+  VB_CHECK(hidden % 8 == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+           "moe_unpermute_reduce: hidden (%d) must be a multiple of 8 and the rows 16-byte aligned", hidden);
+  if (dtype == VB200_BF16)
+    return launch_unpermute_reduce<__nv_bfloat16>(out, c, dst_row, topk_weights, num_routed, num_tokens, topk, hidden, stream);
+  return launch_unpermute_reduce<__half>(out, c, dst_row, topk_weights, num_routed, num_tokens, topk, hidden, stream);
 }
