@@ -642,7 +642,10 @@ static Plan make_plan(int M, int N, int K) {
     const int rounds = ceil_div(g.tiles, max_pairs);
     const long long U = (long long)g.tiles * g.num_kb;
     const long long per_pair = (U + max_pairs - 1) / max_pairs;
-    if (per_pair >= g.num_kb && per_pair * 100 <= (long long)rounds * g.num_kb * 92) {
+    // ... and to token tiles of <= 128 columns: a cut tile's fp32 partial (tok_tile x 128 x 4 bytes per CTA) travels
+    // through L2 twice, which at 256 columns costs more than the ragged round it removes (gate_up, M = 256: 37.5 us
+    // stream-K vs 33.2 us whole tiles; M = 16: 24.4 vs 27.2; profiles/r02_scaled_mm_plan_sweep_s36.jsonl)
+    if (g.tok_tile <= 128 && per_pair >= g.num_kb && per_pair * 100 <= (long long)rounds * g.num_kb * 92) {
       g.streamk = 1;
       g.ws_bytes = kSkFlagBytes + (size_t)max_pairs * 2 * g.tok_tile * kCtaRows * 4;
     }
