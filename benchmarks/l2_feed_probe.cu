@@ -3,7 +3,10 @@
 // cluster needs the SAME activation tile, does a multicast load (each CTA fetches 1/C of the tile and the fabric
 // replicates it into all C shared memories) relieve the per-SM limit, or is the limit the SM's own inbound port?
 //
-//   l2_feed_probe <grid> <cluster> <multicast 0|1> <source 0=L2-resident 1=HBM stream> [chunk_kb=16] [stages=8]
+//   l2_feed_probe <grid> <cluster> <multicast 0|1> <source 0=L2-resident 1=HBM stream> [chunk_kb=16] [stages=8] [producers=1]
+//
+// `producers` = number of warps (one issuing thread each) that take the chunks round-robin: one thread sustains only
+// one bulk copy per ~170 ns whatever its size, several threads overlap their issue latencies.
 //
 // Every CTA keeps a ring of `stages` chunks in flight; a chunk counts as delivered when all its bytes have landed in
 // THIS CTA's shared memory (mbarrier complete_tx).  Prints delivered GB/s per SM and in total, and the bytes actually
@@ -65,10 +68,10 @@ struct P {
   const uint8_t* src;
   size_t region;      // bytes addressable (power of two)
   size_t stride;      // start offset of cluster i = i * stride
-  int iters, stages, chunk, csize, multicast;
+  int iters, stages, chunk, csize, multicast, producers;
 };
 
-__global__ void __launch_bounds__(64, 1) feed_kernel(P p, unsigned long long* sink) {
+__global__ void __launch_bounds__(288, 1) feed_kernel(P p, unsigned long long* sink) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + 16;
@@ -90,9 +93,9 @@ __global__ void __launch_bounds__(64, 1) feed_kernel(P p, unsigned long long* si
   }
   const size_t mask = p.region - 1;
   const size_t base = (size_t)cluster_id * p.stride;
-  if (threadIdx.x == 0) {
-    // producer
-    for (int it = 0; it < p.iters; ++it) {
+  if ((threadIdx.x & 31) == 0 && (int)(threadIdx.x >> 5) < p.producers) {
+    // producer warp w: chunks w, w + producers, ...
+    for (int it = threadIdx.x >> 5; it < p.iters; it += p.producers) {
       const int s = it % p.stages;
       if (it >= p.stages) mbar_wait(&empty[s], ((it / p.stages) & 1) ^ 1);
       mbar_expect(&full[s], (uint32_t)p.chunk);
@@ -106,7 +109,7 @@ __global__ void __launch_bounds__(64, 1) feed_kernel(P p, unsigned long long* si
         bulk_load_mc(d + crank * part, g + crank * part, part, &full[s], (uint16_t)((1u << p.csize) - 1u));
       }
     }
-  } else if (threadIdx.x == 32) {
+  } else if ((int)threadIdx.x == 32 * p.producers) {
     // consumer: the chunk has landed -> release the stage (in every CTA that may write into it)
     unsigned long long acc = 0;
     for (int it = 0; it < p.iters; ++it) {
@@ -136,6 +139,7 @@ int main(int argc, char** argv) {
   const int grid = atoi(argv[1]), csize = atoi(argv[2]), mc = atoi(argv[3]), source = atoi(argv[4]);
   const int chunk = (argc > 5 ? atoi(argv[5]) : 16) * 1024;
   const int stages = argc > 6 ? atoi(argv[6]) : 8;
+  const int producers = argc > 7 ? atoi(argv[7]) : 1;
   if (grid % csize || stages > 16 || chunk % (16 * csize)) {
     printf("bad arguments\n");
     return 1;
@@ -153,6 +157,7 @@ int main(int argc, char** argv) {
   p.multicast = mc;
   p.chunk = chunk;
   p.stages = stages;
+  p.producers = producers;
   const int clusters = grid / csize;
   // L2-resident: clusters start 1 MiB + 4 KiB apart inside 32 MiB and walk 8 MiB each; HBM: private slices
   p.stride = source ? (region / clusters) / 4096 * 4096 : ((1u << 20) + 4096);
@@ -163,7 +168,7 @@ int main(int argc, char** argv) {
   if (csize > 8) CK(cudaFuncSetAttribute(feed_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(64);
+  cfg.blockDim = dim3(32 * (producers + 1));
   cfg.dynamicSmemBytes = smem;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -189,10 +194,10 @@ int main(int argc, char** argv) {
   }
   const double delivered = (double)p.iters * chunk;            // bytes landed in each CTA's shared memory
   const double requested = mc ? delivered / csize : delivered;  // bytes each CTA asked L2 for
-  printf("{\"grid\": %d, \"cluster\": %d, \"multicast\": %d, \"source\": \"%s\", \"chunk_kb\": %d, \"stages\": %d, "
+  printf("{\"grid\": %d, \"cluster\": %d, \"multicast\": %d, \"source\": \"%s\", \"chunk_kb\": %d, \"stages\": %d, \"producers\": %d, "
          "\"max_active_clusters\": %d, \"ms\": %.3f, \"delivered_GBs_per_sm\": %.1f, \"delivered_TBs_total\": %.2f, "
          "\"requested_TBs_total\": %.2f}\n",
-         grid, csize, mc, source ? "hbm" : "l2", chunk / 1024, stages, maxc, best, delivered / best / 1e6,
+         grid, csize, mc, source ? "hbm" : "l2", chunk / 1024, stages, producers, maxc, best, delivered / best / 1e6,
          delivered * grid / best / 1e9, requested * grid / best / 1e9);
   return 0;
 }

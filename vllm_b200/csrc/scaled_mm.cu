@@ -13,10 +13,11 @@
 //   * Persistent: grid = min(units, #SM/2) pairs; a unit is (256-row weight tile, token tile, K
 //     slice).  The fp32 accumulator (128 lanes x <= 256 columns per CTA) is double-buffered in TMEM
 //     (512 columns), so the epilogue of unit i overlaps the main loop of unit i+1.
-//   * Warp roles per CTA: warp 0 = TMA producer (128-byte-swizzled [rows x 128 B] boxes into a ring
-//     of stages; both CTAs signal the LEADER's full barrier), warp 1 = MMA issuer (leader CTA only,
+//   * Warp roles per CTA: warps 0-2 = TMA producers, k-blocks dealt round-robin (128-byte-swizzled [rows x 128 B]
+//     boxes into a ring of stages; both CTAs signal the LEADER's full barrier; three issuing threads because one
+//     thread sustains only one bulk copy per ~170 ns, see kProdWarps), warp 3 = MMA issuer (leader CTA only,
 //     one thread; tcgen05.commit multicasts "stage free" / "accumulator ready" to both CTAs),
-//     warps 2-5 = epilogue (tcgen05.ld -> a_scale * (b_scale * acc) (+ bias) -> bf16/f16 -> global).
+//     warps 4-7 = epilogue (tcgen05.ld -> a_scale * (b_scale * acc) (+ bias) -> bf16/f16 -> global).
 //   * Split-K when the tile count cannot fill the machine (decode o_proj / down_proj / qkv): the S pairs that share
 //     an output tile form ONE thread-block cluster of 2 S CTAs (cluster rank = 2 * slice + half), each pair
 //     accumulates a K slice, and the partial accumulators are exchanged through DISTRIBUTED SHARED MEMORY: after a
@@ -52,7 +53,17 @@ constexpr int kEpiWarps = 4;   // one per TMEM lane quarter.  (8 = two per quart
                                // measured SLOWER, profiles/r02_scaled_mm_plan_sweep_s34.jsonl: the epilogue is bound
                                // by the store / DSMEM paths, not by instruction issue)
 constexpr int kWpq = kEpiWarps / 4;   // warps per lane quarter
-constexpr int kThreads = 64 + 32 * kEpiWarps;
+// TMA producer warps.  ONE issuing thread sustains one cp.async.bulk(.tensor) per ~170 ns whatever its size up to
+// 16 KiB (benchmarks/l2_feed_probe.cu, profiles/r02_l2_feed_probe_s37.jsonl: 16 / 8 / 4 KiB chunks all land at 5.8 M
+// copies/s per SM, 93 / 47 / 23 GB/s) -- and the main loop of the single-producer kernel ran at exactly two copies
+// (W box + A box) per 340-390 ns k-block (profiles/r02_scaled_mm_trace_s36.txt), i.e. issue-bound at 50-85 GB/s per
+// SM, below both the L2 feed (130 GB/s per SM) and the HBM stream.  Three warps take the k-blocks round-robin
+// (3 + MMA + 4 epilogue = 8 warps = two per scheduler, which keeps the 230-register epilogue free of spills; a ninth
+// warp would cap the kernel at 168 registers).
+constexpr int kProdWarps = 3;
+constexpr int kMmaWarp = kProdWarps;          // warp index of the MMA issuer
+constexpr int kFirstEpiWarp = kProdWarps + 1; // epilogue warps 4..7 -> TMEM lane quarters 0..3 (= warp % 4)
+constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);
 constexpr int kWTileBytes = kCtaRows * kBlockK;  // 16 KiB
 constexpr int kTmemCols = 512;                   // two accumulator stages of <= 256 columns
 constexpr int kAccStride = 256;                  // TMEM column offset of accumulator stage 1
@@ -197,7 +208,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc_2cta(tmem_ptr, kTmemCols);
+  if (warp == kMmaWarp) tmem_alloc_2cta(tmem_ptr, kTmemCols);
   tc_fence_before();
   cluster_sync_all();  // barrier inits + TMEM allocation visible in the whole cluster
   tc_fence_after();
@@ -205,8 +216,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   pdl_trigger();       // the next kernel on the stream may start its own prologue
   if (threadIdx.x == 0) stamp(p, 1);
 
-  if (warp == 0) {
-    // ===== TMA producer (both CTAs; one thread) =====
+  if (warp < kProdWarps) {
+    // ===== TMA producers (both CTAs; one thread of each of kProdWarps warps; warp w owns k-block iterations
+    // it = w, w + kProdWarps, ... of this CTA's work list: the barrier protocol is per stage, so the warps never
+    // have to order themselves against each other) =====
     if (lane == 0) {
       const uint32_t bar_base = map_to_cta(smem_u32(&full_bar[0]), leader);
       const uint32_t tx_bytes = 2u * (uint32_t)(kWTileBytes + tok_half * kBlockK);
@@ -223,12 +236,12 @@ __global__ void __launch_bounds__(kThreads, 1)
           const int n_pt = tile / p.m_tiles;
           const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
           npre = (uint32_t)min(hi - lo, p.stages);
-          for (uint32_t i = 0; i < npre; ++i) {
+          for (uint32_t i = (uint32_t)warp; i < npre; i += kProdWarps) {
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[i], tx_bytes);
             tma_load_2d_2cta(smem + (size_t)i * p.stage_bytes, &tmap_w, bar_base + 8u * i, (lo + (int)i) * kBlockK, n0,
                              p.hint_w);
           }
-          stamp(p, 2);
+          if (warp == 0) stamp(p, 2);
         }
       }
       pdl_wait();   // activations (and everything else the previous kernels wrote) are visible from here on
@@ -238,6 +251,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
         const int tok0 = m_t * p.tok_tile + (int)rank * tok_half;
         for (int kb = lo; kb < hi; ++kb, ++it) {
+          if ((int)(it % kProdWarps) != warp) continue;
           const int stage = it % p.stages;
           uint8_t* sw = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sa = sw + kWTileBytes;
@@ -252,16 +266,17 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       // tail: every stage this CTA filled has been released, i.e. all multicast arrivals aimed at
-      // this CTA's barriers have landed before it can exit
+      // this CTA's barriers have landed before it can exit (each warp drains the iterations it owns)
       const uint32_t n_tail = it < (uint32_t)p.stages ? it : (uint32_t)p.stages;
       for (uint32_t i = 0; i < n_tail; ++i, ++it) {
+        if ((int)(it % kProdWarps) != warp) continue;
         const int stage = it % p.stages;
         const uint32_t phase = (it / p.stages) & 1;
         mbar_wait(&empty_bar[stage], phase ^ 1);
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ===== MMA issuer (leader CTA of each pair, one thread) =====
     if (rank == 0 && lane == 0) {
       const uint32_t idesc = make_idesc_f8(kPairRows, p.tok_tile);
@@ -299,19 +314,19 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     __syncwarp();
   }
-  if (warp < 2 && p.splits > 1) {
+  if (warp < kFirstEpiWarp && p.splits > 1) {
     // split-K: the two cluster barriers of the DSMEM exchange are executed by every thread of the cluster
     cluster_sync_all();
     cluster_sync_all();
   }
 
-  if (warp >= 2) {
+  if (warp >= kFirstEpiWarp) {
     // ===== epilogue (kEpiWarps warps of each CTA; TMEM lane quarter = warp % 4, the kWpq warps of a quarter take
     // alternate column chunks) =====
     const int q = warp & 3;
-    const int h = (warp - 2) >> 2;  // which of the quarter's two warps
+    const int h = (warp - kFirstEpiWarp) >> 2;  // which of the quarter's warps
     const int row = q * 32 + lane;  // weight row inside this CTA's 128
-    const int tid_e = threadIdx.x - 64;
+    const int tid_e = threadIdx.x - 32 * kFirstEpiWarp;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     OutT* outp = reinterpret_cast<OutT*>(p.out);
     const bool has_bias = p.bias != nullptr;
@@ -546,7 +561,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   // teardown: nobody leaves (or frees TMEM) while the peer may still touch this CTA
   tc_fence_before();
   cluster_sync_relaxed();   // execution order only: no need to drain the output stores before arriving
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     tc_fence_after();
     tmem_dealloc_2cta(tmem_base, kTmemCols);
   }
