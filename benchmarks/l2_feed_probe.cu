@@ -3,7 +3,7 @@
 // cluster needs the SAME activation tile, does a multicast load (each CTA fetches 1/C of the tile and the fabric
 // replicates it into all C shared memories) relieve the per-SM limit, or is the limit the SM's own inbound port?
 //
-//   l2_feed_probe <grid> <cluster> <multicast 0|1> <source 0=L2-resident 1=HBM stream> [chunk_kb=16] [stages=8] [producers=1]
+//   l2_feed_probe <grid> <cluster> <multicast 0|1> <source 0=L2-resident 1=HBM stream> [chunk_kb=16] [stages=8] [producers=1] [consumers=1]
 //
 // `producers` = number of warps (one issuing thread each) that take the chunks round-robin: one thread sustains only
 // one bulk copy per ~170 ns whatever its size, several threads overlap their issue latencies.
@@ -68,7 +68,7 @@ struct P {
   const uint8_t* src;
   size_t region;      // bytes addressable (power of two)
   size_t stride;      // start offset of cluster i = i * stride
-  int iters, stages, chunk, csize, multicast, producers;
+  int iters, stages, chunk, csize, multicast, producers, consumers;
 };
 
 __global__ void __launch_bounds__(288, 1) feed_kernel(P p, unsigned long long* sink) {
@@ -109,10 +109,11 @@ __global__ void __launch_bounds__(288, 1) feed_kernel(P p, unsigned long long* s
         bulk_load_mc(d + crank * part, g + crank * part, part, &full[s], (uint16_t)((1u << p.csize) - 1u));
       }
     }
-  } else if ((int)threadIdx.x == 32 * p.producers) {
-    // consumer: the chunk has landed -> release the stage (in every CTA that may write into it)
+  } else if ((threadIdx.x & 31) == 0 && (int)(threadIdx.x >> 5) < p.producers + p.consumers) {
+    // consumer warp c: chunks c, c + consumers, ...: the chunk has landed -> release the stage (in every CTA that may
+    // write into it)
     unsigned long long acc = 0;
-    for (int it = 0; it < p.iters; ++it) {
+    for (int it = (threadIdx.x >> 5) - p.producers; it < p.iters; it += p.consumers) {
       const int s = it % p.stages;
       mbar_wait(&full[s], (it / p.stages) & 1);
       acc += ring[(size_t)s * p.chunk + (it & 63)];
@@ -140,6 +141,7 @@ int main(int argc, char** argv) {
   const int chunk = (argc > 5 ? atoi(argv[5]) : 16) * 1024;
   const int stages = argc > 6 ? atoi(argv[6]) : 8;
   const int producers = argc > 7 ? atoi(argv[7]) : 1;
+  const int consumers = argc > 8 ? atoi(argv[8]) : 1;
   if (grid % csize || stages > 16 || chunk % (16 * csize)) {
     printf("bad arguments\n");
     return 1;
@@ -158,6 +160,7 @@ int main(int argc, char** argv) {
   p.chunk = chunk;
   p.stages = stages;
   p.producers = producers;
+  p.consumers = consumers;
   const int clusters = grid / csize;
   // L2-resident: clusters start 1 MiB + 4 KiB apart inside 32 MiB and walk 8 MiB each; HBM: private slices
   p.stride = source ? (region / clusters) / 4096 * 4096 : ((1u << 20) + 4096);
@@ -168,7 +171,7 @@ int main(int argc, char** argv) {
   if (csize > 8) CK(cudaFuncSetAttribute(feed_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(32 * (producers + 1));
+  cfg.blockDim = dim3(32 * (producers + consumers));
   cfg.dynamicSmemBytes = smem;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -194,10 +197,10 @@ int main(int argc, char** argv) {
   }
   const double delivered = (double)p.iters * chunk;            // bytes landed in each CTA's shared memory
   const double requested = mc ? delivered / csize : delivered;  // bytes each CTA asked L2 for
-  printf("{\"grid\": %d, \"cluster\": %d, \"multicast\": %d, \"source\": \"%s\", \"chunk_kb\": %d, \"stages\": %d, \"producers\": %d, "
+  printf("{\"grid\": %d, \"cluster\": %d, \"multicast\": %d, \"source\": \"%s\", \"chunk_kb\": %d, \"stages\": %d, \"producers\": %d, \"consumers\": %d, "
          "\"max_active_clusters\": %d, \"ms\": %.3f, \"delivered_GBs_per_sm\": %.1f, \"delivered_TBs_total\": %.2f, "
          "\"requested_TBs_total\": %.2f}\n",
-         grid, csize, mc, source ? "hbm" : "l2", chunk / 1024, stages, producers, maxc, best, delivered / best / 1e6,
+         grid, csize, mc, source ? "hbm" : "l2", chunk / 1024, stages, producers, consumers, maxc, best, delivered / best / 1e6,
          delivered * grid / best / 1e9, requested * grid / best / 1e9);
   return 0;
 }
