@@ -45,10 +45,15 @@ def main():
             rel = (t - t0) / 1e3
             med = rel.median(dim=0).values
             mx = rel.max(dim=0).values
-            cols = [i for i in range(11) if (t[:, i] > 0).any()]
+            cols = [i for i in range(11) if (t[:, i] > 1e15).any()]
             print(f"{name} M={M}: ctas={int(used.sum())} span={span:.1f}us")
             print("   median us since first entry: " + " ".join(f"{NAMES[i]}={med[i]:.1f}" for i in cols))
             print("   max    us since first entry: " + " ".join(f"{NAMES[i]}={mx[i]:.1f}" for i in cols))
+            lead = t[t[:, 14] > 0]   # leader CTAs: the MMA issuer's own counters
+            if len(lead):
+                kb = lead[:, 14].median()
+                print(f"   MMA issuer (median over {len(lead)} leaders): k-blocks={kb:.0f}, whole loop "
+                      f"{lead[:, 15].median():.0f} cycles = {lead[:, 15].median() / kb:.0f} per k-block (first wait included)")
 
 
 if __name__ == "__main__":

@@ -245,19 +245,29 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       pdl_wait();   // activations (and everything else the previous kernels wrote) are visible from here on
+      // (stage, phase, owner) are carried as running counters: this is single-thread, latency-bound code, and a
+      // runtime `it % stages` / `it / stages` pair costs more cycles than the TMA issue itself
       uint32_t it = 0;
+      int stage = 0, owner = 0;
+      uint32_t phase = 0;
+      auto advance = [&]() {
+        ++it;
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+        if (++owner == kProdWarps) owner = 0;
+      };
       while (si.next(p, num_clusters, kb0, kb1, tile, lo, hi)) {
         const int n_pt = tile / p.m_tiles, m_t = tile - n_pt * p.m_tiles;
         const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
         const int tok0 = m_t * p.tok_tile + (int)rank * tok_half;
-        for (int kb = lo; kb < hi; ++kb, ++it) {
-          if ((int)(it % kProdWarps) != warp) continue;
-          const int stage = it % p.stages;
+        for (int kb = lo; kb < hi; ++kb, advance()) {
+          if (owner != warp) continue;
           uint8_t* sw = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sa = sw + kWTileBytes;
           const uint32_t bar = bar_base + 8u * (uint32_t)stage;
           if (it >= npre) {
-            const uint32_t phase = (it / p.stages) & 1;
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
             tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
@@ -268,10 +278,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       // tail: every stage this CTA filled has been released, i.e. all multicast arrivals aimed at
       // this CTA's barriers have landed before it can exit (each warp drains the iterations it owns)
       const uint32_t n_tail = it < (uint32_t)p.stages ? it : (uint32_t)p.stages;
-      for (uint32_t i = 0; i < n_tail; ++i, ++it) {
-        if ((int)(it % kProdWarps) != warp) continue;
-        const int stage = it % p.stages;
-        const uint32_t phase = (it / p.stages) & 1;
+      for (uint32_t i = 0; i < n_tail; ++i, advance()) {
+        if (owner != warp) continue;
         mbar_wait(&empty_bar[stage], phase ^ 1);
       }
     }
@@ -282,6 +290,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       const uint32_t idesc = make_idesc_f8(kPairRows, p.tok_tile);
       const uint16_t pair_mask = (uint16_t)(0x3u << leader);   // the two CTAs of this pair, as cluster ranks
       uint32_t it = 0, lt = 0;
+      int stage = 0;
+      uint32_t phase = 0;
+      const long long loop_c0 = p.trace != nullptr ? clock64() : 0;
       SegIter si;
       si.init(p, cluster_id, num_clusters);
       int tile, lo, hi;
@@ -292,12 +303,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * kAccStride;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int stage = it % p.stages;
-          const uint32_t phase = (it / p.stages) & 1;
           mbar_wait(&full_bar[stage], phase);  // both CTAs' boxes have landed
           tc_fence_after();
           if (it == 0) stamp(p, 3);
-          const uint32_t sw = smem_u32(smem + (size_t)stage * p.stage_bytes);
+          const uint32_t sw = smem_u32(smem) + (uint32_t)stage * (uint32_t)p.stage_bytes;
           const uint64_t adesc = make_smem_desc_sw128(sw);
           const uint64_t bdesc = make_smem_desc_sw128(sw + kWTileBytes);
 #pragma unroll
@@ -307,9 +316,18 @@ __global__ void __launch_bounds__(kThreads, 1)
                          bdesc + (uint64_t)(k * (kUmmaK >> 4)), idesc, (kb | k) != 0);
           }
           umma_commit_2cta(&empty_bar[stage], pair_mask);  // frees the stage in both CTAs
+          // running (stage, phase): no runtime division in this single-thread, latency-bound loop
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
         umma_commit_2cta(&acc_full[as], pair_mask);  // accumulator complete, both CTAs' epilogues may read
         stamp(p, 4);
+      }
+      if (p.trace != nullptr) {   // debug: the issuer's k-block count and its whole-loop cycle count
+        p.trace[(size_t)blockIdx.x * 16 + 14] = (unsigned long long)it;
+        p.trace[(size_t)blockIdx.x * 16 + 15] = (unsigned long long)(clock64() - loop_c0);
       }
     }
     __syncwarp();
