@@ -146,6 +146,27 @@ int vb200_paged_attention_v1(void* out, const void* query, const void* key_cache
                              int partition_size, void* workspace, size_t workspace_bytes,
                              vb200_stream_t stream);
 
+/* Decode attention over the FLASH cache layout: the cache vLLM's V1 backends allocate,
+ * kv_cache [2, num_blocks, block_size, num_kv_heads, head_size] (vllm/v1/attention/backends/flash_attn.py:79-102),
+ * in NHD order or as the HND-permuted view Blackwell uses (vllm/platforms/cuda.py:264-290) -- the layout
+ * vb200_reshape_and_cache_flash writes.  key_cache / value_cache are the two halves (kv_cache.unbind(0)); element
+ * (block, token, head, d) lives at block*block_stride + token*token_stride + head*head_stride + d (elements; both
+ * halves share the strides).  Same math, query/out shapes, scales, alibi and split-K workspace contract as
+ * vb200_paged_attention_v1 (one query token per sequence, seq_lens = context length including it); it is the decode
+ * case of the reference's flash_attn_varlen_func(q, k=key_cache, v=value_cache, block_table=..., seqused_k=...)
+ * call (flash_attn.py:497-519) with max_seqlen_q == 1.  block_size must be 16; head_size * sizeof(cache element) must
+ * be a multiple of 128 (f16/bf16: 64, 128, 192, 256; fp8: 128, 256); strides * element size must be multiples of 16
+ * bytes.  The kernel builds two TMA tensor maps on the host per call (no allocation, graph-capturable). */
+size_t vb200_paged_attention_flash_workspace_size(int num_seqs, int num_heads, int head_size, int max_seq_len,
+                                                  int q_dtype, int partition_size);
+int vb200_paged_attention_flash(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                int num_seqs, int num_heads, int head_size, int num_kv_heads, float scale,
+                                const int32_t* block_tables, const int32_t* seq_lens, int block_size, int num_blocks,
+                                int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype,
+                                int kv_dtype, const float* k_scale, const float* v_scale, int64_t q_stride,
+                                int64_t block_stride, int64_t token_stride, int64_t head_stride, int partition_size,
+                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------ */
 /* FP8 activation quantisation + activation                                                    */
 /* ------------------------------------------------------------------------------------------ */

@@ -106,6 +106,66 @@ def paged_attention_v1(
             max(partition_size, 0), ptr(ws), ws_bytes, stream()))
 
 
+def paged_attention_flash(
+    out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: Optional[torch.Tensor],
+    v_scale: Optional[torch.Tensor],
+    partition_size: int = 0,
+) -> None:
+    """Decode attention over the flash cache layout (include/vllm_b200.h
+    vb200_paged_attention_flash): key_cache / value_cache are the `[num_blocks, block_size, num_kv_heads, head_size]`
+    halves of the V1 cache (`kv_cache.unbind(0)`, vllm/v1/attention/backends/flash_attn.py:465), NHD-contiguous or
+    the HND-permuted view -- addressed through their strides like reshape_and_cache_flash.  query / out
+    [num_seqs, num_heads, head_size]; one query token per sequence; seq_lens int32 = context length."""
+    kvd = kv_dtype_enum(kv_cache_dtype)
+    require_cuda(out, query, key_cache, value_cache, block_tables, seq_lens, alibi_slopes, k_scale, v_scale)
+    if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
+        raise RuntimeError("query must be [num_seqs, num_heads, head_size] with contiguous heads")
+    if key_cache.dim() != 4 or key_cache.shape != value_cache.shape or key_cache.stride() != value_cache.stride():
+        raise RuntimeError("paged_attention_flash: key_cache / value_cache must be [num_blocks, block_size, num_kv_heads, "
+                           "head_size] views with equal strides")
+    if key_cache.stride(3) != 1:
+        raise RuntimeError("paged_attention_flash: the head dimension of the cache must be contiguous")
+    if block_tables.dtype != torch.int32 or seq_lens.dtype != torch.int32:
+        raise RuntimeError("block_tables and seq_lens must be int32")
+    if kvd == _lib.KV_AUTO and key_cache.dtype != query.dtype:
+        raise RuntimeError(f"kv_cache_dtype 'auto' needs cache dtype == query dtype ({key_cache.dtype} vs {query.dtype})")
+    if kvd == _lib.KV_FP8_E4M3 and key_cache.element_size() != 1:
+        raise RuntimeError("fp8 kv cache must be a 1-byte tensor (uint8 / float8_e4m3fn)")
+    if out.shape != query.shape or out.dtype != query.dtype or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous tensor of query's shape and dtype")
+    num_blocks, block_size, num_kv_heads, head_size = key_cache.shape
+    num_seqs, num_heads, hs = query.shape
+    if hs != head_size:
+        raise RuntimeError(f"head size mismatch: query {hs}, cache {head_size}")
+    lib = load()
+    qd = dtype_enum(query.dtype)
+    with _device_of(query):
+        ws, ws_bytes = None, 0
+        if partition_size >= 0:
+            if partition_size == 0:
+                partition_size = lib.vb200_paged_attention_v1_partition_size(
+                    num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size, kvd)
+            ws_bytes = lib.vb200_paged_attention_flash_workspace_size(num_seqs, num_heads, head_size, max_seq_len, qd,
+                                                                      partition_size)
+            if ws_bytes > 0:
+                ws = torch.empty(ws_bytes, dtype=torch.uint8, device=query.device)
+        check(lib.vb200_paged_attention_flash(
+            ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), num_seqs, num_heads, head_size, num_kv_heads,
+            float(scale), ptr(block_tables), ptr(seq_lens), block_size, num_blocks, max_seq_len, block_tables.stride(0),
+            ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0), key_cache.stride(0),
+            key_cache.stride(1), key_cache.stride(2), max(partition_size, 0), ptr(ws), ws_bytes, stream()))
+
+
 def paged_attention_v2(
     out: torch.Tensor,
     exp_sum: torch.Tensor,

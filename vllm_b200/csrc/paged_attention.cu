@@ -21,6 +21,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace vb200 {
 
@@ -505,6 +506,7 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
 
 }  // namespace vb200
 #include "paged_attention_tma.cuh"
+#include "paged_attention_flash.cuh"
 namespace vb200 {
 
 constexpr int kWarps = 4;
@@ -639,6 +641,69 @@ static int run_paged_attention(PagedAttnParams& p, int num_seqs, int head_size, 
   }
   return fp8 ? dispatch_head<__nv_bfloat16, true>(p, head_size, block_size, num_seqs, np, stream)
              : dispatch_head<__nv_bfloat16, false>(p, head_size, block_size, num_seqs, np, stream);
+}
+
+// ---- flash cache layout (NHD / HND views through strides): paged_attention_flash.cuh ---------------------------
+struct FlashLayout {
+  int64_t block_stride, token_stride, head_stride;  // elements
+  int num_blocks;
+};
+
+template <typename QT, bool FP8, int HEAD_SIZE>
+static int launch_pa_flash(const PagedAttnParams& p, const FlashLayout& L, int num_seqs, int num_partitions,
+                           cudaStream_t stream) {
+  constexpr int CE = FP8 ? 1 : 2;
+  static_assert((HEAD_SIZE * CE) % 128 == 0, "flash-layout kernel: head bytes must be a multiple of 128");
+  auto kt = paged_attention_flash_kernel<QT, FP8, HEAD_SIZE, kWarps, (HEAD_SIZE <= 128 ? 4 : 2)>;
+  // same ring sizing as the paged-layout kernel, minus the 1 KiB the swizzled boxes need for alignment
+  int stages = pa_tma_stages<HEAD_SIZE>(CE, p.partition_size);
+  size_t smem = pa_flash_smem_bytes<HEAD_SIZE, kWarps>(stages, CE, p.partition_size);
+  const size_t per_cta = (size_t)(227 * 1024) / pa_tma_ctas_per_sm(HEAD_SIZE) - 1024;
+  while (smem > per_cta && stages > kWarps) {
+    stages -= kWarps;
+    smem = pa_flash_smem_bytes<HEAD_SIZE, kWarps>(stages, CE, p.partition_size);
+  }
+  VB_CHECK(smem <= 227 * 1024, "paged attention (flash layout): partition of %d tokens needs too much shared memory",
+           p.partition_size);
+  CUtensorMap tk, tv;
+  const uint64_t dims[4] = {(uint64_t)HEAD_SIZE * CE, 16, (uint64_t)p.num_kv_heads, (uint64_t)L.num_blocks};
+  const uint64_t strides[3] = {(uint64_t)L.token_stride * CE, (uint64_t)L.head_stride * CE,
+                               (uint64_t)L.block_stride * CE};
+  if (tc::make_tmap_4d_u8(&tk, p.k_cache, dims, strides, 16)) return 1;
+  if (tc::make_tmap_4d_u8(&tv, p.v_cache, dims, strides, 16)) return 1;
+  if (smem > 48 * 1024)
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int q_per_kv = p.num_heads / p.num_kv_heads;
+  dim3 grid(p.num_kv_heads * ((q_per_kv + 7) / 8), num_seqs, num_partitions);
+  VB_CUDA_CHECK(launch_k(kt, grid, dim3((kWarps + 1) * 32), smem, stream, tk, tv, p, stages));
+  VB_LAUNCH_CHECK();
+  if (p.max_num_partitions > 1 || p.force_partials) {
+    const int rows = num_seqs * p.num_heads;
+    VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream,
+                           (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
+                           p.max_num_partitions, p.partition_size, rows));
+    VB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+template <typename QT>
+static int dispatch_flash(const PagedAttnParams& p, const FlashLayout& L, int head_size, bool fp8, int num_seqs, int np,
+                          cudaStream_t s) {
+  if (fp8) {
+    if (head_size == 128) return launch_pa_flash<QT, true, 128>(p, L, num_seqs, np, s);
+    if (head_size == 256) return launch_pa_flash<QT, true, 256>(p, L, num_seqs, np, s);
+    VB_CHECK(false, "paged_attention_flash: fp8 KV cache supports head sizes 128 and 256 (got %d)", head_size);
+  }
+  switch (head_size) {
+    case 64: return launch_pa_flash<QT, false, 64>(p, L, num_seqs, np, s);
+    case 128: return launch_pa_flash<QT, false, 128>(p, L, num_seqs, np, s);
+    case 192: return launch_pa_flash<QT, false, 192>(p, L, num_seqs, np, s);
+    case 256: return launch_pa_flash<QT, false, 256>(p, L, num_seqs, np, s);
+    default: break;
+  }
+  VB_CHECK(false, "paged_attention_flash: head size %d is not supported (64, 128, 192, 256)", head_size);
+  return 0;
 }
 
 }  // namespace vb200
@@ -798,4 +863,72 @@ extern "C" int vb200_paged_attention_v1(
   p.prefetch_dist = pa_prefetch_dist();
   return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype,
                              (cudaStream_t)stream);
+}
+
+// Decode attention over the flash cache layout (see include/vllm_b200.h).
+extern "C" size_t vb200_paged_attention_flash_workspace_size(int num_seqs, int num_heads, int head_size, int max_seq_len,
+                                                             int q_dtype, int partition_size) {
+  return vb200_paged_attention_v1_workspace_size(num_seqs, num_heads, head_size, max_seq_len, q_dtype, partition_size);
+}
+
+extern "C" int vb200_paged_attention_flash(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+    int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+    int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
+    const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, vb200_stream_t stream) {
+  VB_CHECK(block_size == 16, "paged_attention_flash: block size must be 16 (got %d)", block_size);
+  VB_CHECK(q_dtype == VB200_F16 || q_dtype == VB200_BF16, "paged_attention_flash: query dtype must be f16 or bf16");
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3, "Unsupported data type of kv cache: %d", kv_dtype);
+  VB_CHECK(num_kv_heads > 0 && num_heads % num_kv_heads == 0, "num_heads %d must be a multiple of num_kv_heads %d",
+           num_heads, num_kv_heads);
+  VB_CHECK(num_blocks > 0, "paged_attention_flash: the cache holds no blocks");
+  if (num_seqs <= 0) return 0;
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (k_scale && v_scale), "fp8 kv cache needs k_scale and v_scale");
+  int part = partition_size;
+  if (workspace == nullptr) {
+    part = 0;
+  } else if (part <= 0) {
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size,
+                                                   kv_dtype);
+  }
+  int np = 1;
+  if (part > 0 && max_seq_len > part) np = (max_seq_len + part - 1) / part;
+  if (np == 1) part = round_up(max_seq_len > 0 ? max_seq_len : 16, 32);
+  VB_CHECK(part % 16 == 0, "paged_attention_flash: partition size %d must be a multiple of 16", part);
+  PagedAttnParams p;
+  p.out = out;
+  p.exp_sums = nullptr;
+  p.max_logits = nullptr;
+  p.tmp_out = nullptr;
+  if (np > 1) {
+    const size_t need = vb200_paged_attention_v1_workspace_size(num_seqs, num_heads, head_size, max_seq_len, q_dtype, part);
+    VB_CHECK(workspace_bytes >= need, "paged_attention_flash workspace too small: %zu < %zu", workspace_bytes, need);
+    const size_t rows = (size_t)num_seqs * num_heads * np;
+    p.exp_sums = reinterpret_cast<float*>(workspace);
+    p.max_logits = p.exp_sums + rows;
+    p.tmp_out = reinterpret_cast<void*>(p.max_logits + rows);
+  }
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  p.partition_size = part;
+  p.max_num_partitions = np;
+  p.q_stride = q_stride;
+  p.kv_block_stride = block_stride;
+  p.kv_head_stride = head_stride;
+  p.scale = scale;
+  p.prefetch_dist = 0;
+  FlashLayout L{block_stride, token_stride, head_stride, num_blocks};
+  if (q_dtype == VB200_F16) return dispatch_flash<__half>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
+  return dispatch_flash<__nv_bfloat16>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
 }

@@ -45,5 +45,27 @@ int make_tmap_2d_u8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return 0;
 }
 
+// 4-D byte tensor {inner bytes, dim1, dim2, dim3} with byte strides for dims 1..3 (any order of magnitudes: this is how
+// one map covers both the NHD and the HND-permuted KV-cache views); box = {128 bytes, box1, 1, 1}, 128-byte swizzle.
+int make_tmap_4d_u8(CUtensorMap* map, const void* base, const uint64_t dims[4], const uint64_t strides_bytes[3],
+                    uint32_t box1) {
+  EncodeTiledFn enc = get_encode();
+  VB_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+  VB_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA operands need a 16-byte aligned base (%p)", base);
+  for (int i = 0; i < 3; ++i)
+    VB_CHECK((strides_bytes[i] & 15) == 0 && strides_bytes[i] > 0, "TMA strides must be positive multiples of 16 bytes (%llu)",
+             (unsigned long long)strides_bytes[i]);
+  VB_CHECK(dims[0] >= 128 && box1 >= 1 && box1 <= 256, "TMA box out of range");
+  const cuuint64_t d[4] = {dims[0], dims[1], dims[2], dims[3]};
+  const cuuint64_t st[3] = {strides_bytes[0], strides_bytes[1], strides_bytes[2]};
+  const cuuint32_t box[4] = {128, box1, 1, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(base), d, st, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (4-D) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 }  // namespace tc
 }  // namespace vb200
