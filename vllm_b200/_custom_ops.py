@@ -130,7 +130,8 @@ def paged_attention_flash(
     require_cuda(out, query, key_cache, value_cache, block_tables, seq_lens, alibi_slopes, k_scale, v_scale)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
         raise RuntimeError("query must be [num_seqs, num_heads, head_size] with contiguous heads")
-    if key_cache.dim() != 4 or key_cache.shape != value_cache.shape or key_cache.stride() != value_cache.stride():
+    if key_cache.dim() != 4 or key_cache.shape != value_cache.shape or any(
+            key_cache.size(i) > 1 and key_cache.stride(i) != value_cache.stride(i) for i in range(4)):
         raise RuntimeError("paged_attention_flash: key_cache / value_cache must be [num_blocks, block_size, num_kv_heads, "
                            "head_size] views with equal strides")
     if key_cache.stride(3) != 1:
@@ -147,6 +148,8 @@ def paged_attention_flash(
     num_seqs, num_heads, hs = query.shape
     if hs != head_size:
         raise RuntimeError(f"head size mismatch: query {hs}, cache {head_size}")
+    # the stride of a size-1 dimension is arbitrary in torch; the tensor map wants a well-formed one
+    strides = [key_cache.stride(i) if key_cache.size(i) > 1 else head_size for i in range(3)]
     lib = load()
     qd = dtype_enum(query.dtype)
     with _device_of(query):
@@ -162,8 +165,8 @@ def paged_attention_flash(
         check(lib.vb200_paged_attention_flash(
             ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), num_seqs, num_heads, head_size, num_kv_heads,
             float(scale), ptr(block_tables), ptr(seq_lens), block_size, num_blocks, max_seq_len, block_tables.stride(0),
-            ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0), key_cache.stride(0),
-            key_cache.stride(1), key_cache.stride(2), max(partition_size, 0), ptr(ws), ws_bytes, stream()))
+            ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0), *strides,
+            max(partition_size, 0), ptr(ws), ws_bytes, stream()))
 
 
 def paged_attention_v2(
