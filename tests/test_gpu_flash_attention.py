@@ -128,7 +128,7 @@ def test_flash_backend_decode_step(layout, kvd):
     try:
         S, H, Hkv, D, bs = 4, 16, 4, 128, 16
         seq_lens = [5, 64, 333, 1000]
-        nb = sum((L + bs - 1) // bs for L in seq_lens) + 3
+        nb = S * ((max(seq_lens) + bs - 1) // bs) + 3
         dtype = torch.bfloat16
         cache_dtype = torch.uint8 if kvd == "fp8" else dtype
         kv_cache = B200FlashAttentionBackend.allocate_kv_cache(nb, bs, Hkv, D, cache_dtype, DEV)
