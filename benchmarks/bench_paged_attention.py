@@ -2,7 +2,9 @@
 """Micro-benchmark of paged-attention decode at the BASELINE configs: achieved HBM GB/s (algorithmic bytes,
 SURVEY.md 8d) vs the measured copy peak, next to the reference's own CUDA kernel (torch.ops._ref_C, test infra).
 Inputs are larger than L2 (126 MB) and block tables are random permutations, so every iteration streams from HBM.
-Usage: python benchmarks/bench_paged_attention.py [--cfg 2|3|5|all] [--iters 20] [--partition N] [--no-ref]"""
+`--flash` adds the flash-layout kernel (vb200_paged_attention_flash) on the SAME cache contents re-laid out as
+[num_blocks, 16, Hkv, D] in NHD and HND order.
+Usage: python benchmarks/bench_paged_attention.py [--cfg 2|3|5|all] [--iters 20] [--partition N] [--no-ref] [--flash]"""
 import argparse
 import json
 import os
@@ -96,6 +98,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--partition", type=int, default=0)
     ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--flash", action="store_true")
     a = ap.parse_args()
     from vllm_b200 import _custom_ops as ops
     from parity_utils import load_ref_cuda
@@ -127,6 +130,26 @@ def main():
             row.update(ref_v1_us=round(medr * 1e6, 1), ref_v1_GBs=round(nbytes / medr / 1e9, 1),
                        speedup_vs_ref=round(medr / med, 2),
                        max_abs_diff_vs_ref=float((out.float() - out_r.float()).abs().max()))
+        if a.flash:
+            nbk, Hk, Dx, bsz, xx = kc.shape
+            for layout in ("HND", "NHD"):
+                kf = kc.permute(0, 3, 1, 2, 4).reshape(nbk, bsz, Hk, Dx * xx)
+                vf = vc.permute(0, 3, 1, 2)
+                if layout == "NHD":
+                    kf, vf = kf.contiguous(), vf.contiguous()
+                else:
+                    kf = kf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+                    vf = vf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+                out_f = torch.empty_like(q)
+
+                def flash():
+                    ops.paged_attention_flash(out_f, q, kf, vf, scale, bt, sl, max_len, None, cfg["kvd"], sc, sc,
+                                              partition_size=a.partition)
+                medf, bestf = timeit(flash, a.iters)
+                row.update({f"flash_{layout}_us": round(medf * 1e6, 1), f"flash_{layout}_GBs": round(nbytes / medf / 1e9, 1),
+                            f"flash_{layout}_frac_of_peak": round(nbytes / medf / 1e9 / peak, 3),
+                            f"flash_{layout}_max_abs_diff_vs_paged": float((out_f.float() - out.float()).abs().max())})
+                del kf, vf
         print(json.dumps(row), flush=True)
         del q, kc, vc, bt, sl
         torch.cuda.empty_cache()
