@@ -220,7 +220,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ===== TMA producers (both CTAs; one thread of each of kProdWarps warps; warp w owns k-block iterations
     // it = w, w + kProdWarps, ... of this CTA's work list: the barrier protocol is per stage, so the warps never
     // have to order themselves against each other) =====
-    if (lane == 0) {
+    // (the whole warp runs the loops and waits; one elected lane issues -- see the MMA issuer below for why)
+    {
       const uint32_t bar_base = map_to_cta(smem_u32(&full_bar[0]), leader);
       const uint32_t tx_bytes = 2u * (uint32_t)(kWTileBytes + tok_half * kBlockK);
       // ---- before the grid dependency resolves: the first ring-full of WEIGHT tiles of the first tile.  Weights
@@ -237,16 +238,19 @@ __global__ void __launch_bounds__(kThreads, 1)
           const int n0 = n_pt * kPairRows + (int)rank * kCtaRows;
           npre = (uint32_t)min(hi - lo, p.stages);
           for (uint32_t i = (uint32_t)warp; i < npre; i += kProdWarps) {
-            if (rank == 0) mbar_arrive_expect_tx(&full_bar[i], tx_bytes);
-            tma_load_2d_2cta(smem + (size_t)i * p.stage_bytes, &tmap_w, bar_base + 8u * i, (lo + (int)i) * kBlockK, n0,
-                             p.hint_w);
+            if (elect_one()) {
+              if (rank == 0) mbar_arrive_expect_tx(&full_bar[i], tx_bytes);
+              tma_load_2d_2cta(smem + (size_t)i * p.stage_bytes, &tmap_w, bar_base + 8u * i, (lo + (int)i) * kBlockK,
+                               n0, p.hint_w);
+            }
+            __syncwarp();
           }
-          if (warp == 0) stamp(p, 2);
+          if (warp == 0 && lane == 0) stamp(p, 2);
         }
       }
       pdl_wait();   // activations (and everything else the previous kernels wrote) are visible from here on
-      // (stage, phase, owner) are carried as running counters: this is single-thread, latency-bound code, and a
-      // runtime `it % stages` / `it / stages` pair costs more cycles than the TMA issue itself
+      // (stage, phase, owner) are carried as running counters: this is latency-bound code, and a runtime
+      // `it % stages` / `it / stages` pair costs more cycles than the TMA issue itself
       uint32_t it = 0;
       int stage = 0, owner = 0;
       uint32_t phase = 0;
@@ -267,12 +271,16 @@ __global__ void __launch_bounds__(kThreads, 1)
           uint8_t* sw = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sa = sw + kWTileBytes;
           const uint32_t bar = bar_base + 8u * (uint32_t)stage;
-          if (it >= npre) {
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-            tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
+          const bool fresh = it >= npre;   // W of the first `npre` k-blocks is already in flight
+          if (fresh) mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (elect_one()) {
+            if (fresh) {
+              if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d_2cta(sw, &tmap_w, bar, kb * kBlockK, n0, p.hint_w);
+            }
+            tma_load_2d_2cta(sa, &tmap_a, bar, kb * kBlockK, tok0, p.hint_a);
           }
-          tma_load_2d_2cta(sa, &tmap_a, bar, kb * kBlockK, tok0, p.hint_a);
+          __syncwarp();
         }
       }
       // tail: every stage this CTA filled has been released, i.e. all multicast arrivals aimed at
@@ -285,10 +293,16 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     __syncwarp();
   } else if (warp == kMmaWarp) {
-    // ===== MMA issuer (leader CTA of each pair, one thread) =====
-    if (rank == 0 && lane == 0) {
+    // ===== MMA issuer (leader CTA of each pair).  The WHOLE warp runs the loop and waits on the barriers; one
+    // elected lane issues the tcgen05 instructions.  Keeping the warp converged is what lets the compiler hold the
+    // descriptors / TMEM addresses / barrier addresses in uniform registers: issued from a `lane == 0` branch, every
+    // UTCQMMA and UTCBAR was wrapped in an ELECT + 5 x R2UR.BROADCAST "waterfall" loop (69 cycles per MMA, 440 per
+    // k-block measured in the issuer: profiles/r02_scaled_mm_trace_s42.txt) =====
+    if (rank == 0) {
       const uint32_t idesc = make_idesc_f8(kPairRows, p.tok_tile);
       const uint16_t pair_mask = (uint16_t)(0x3u << leader);   // the two CTAs of this pair, as cluster ranks
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);   // warp-uniform copy of the TMEM base
+      const uint32_t smem_base_u = smem_u32(smem);
       uint32_t it = 0, lt = 0;
       int stage = 0;
       uint32_t phase = 0;
@@ -301,31 +315,35 @@ __global__ void __launch_bounds__(kThreads, 1)
         const uint32_t as = lt & 1, aphase = (lt >> 1) & 1;
         mbar_wait(&acc_empty[as], aphase ^ 1);  // both CTAs' epilogues drained this stage
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * kAccStride;
+        const uint32_t d_tmem = tmem_u + as * kAccStride;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           mbar_wait(&full_bar[stage], phase);  // both CTAs' boxes have landed
           tc_fence_after();
-          if (it == 0) stamp(p, 3);
-          const uint32_t sw = smem_u32(smem) + (uint32_t)stage * (uint32_t)p.stage_bytes;
+          if (it == 0 && lane == 0) stamp(p, 3);
+          const uint32_t sw = smem_base_u + (uint32_t)stage * (uint32_t)p.stage_bytes;
           const uint64_t adesc = make_smem_desc_sw128(sw);
           const uint64_t bdesc = make_smem_desc_sw128(sw + kWTileBytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // advance both descriptors by 32 bytes of K inside the swizzle row (address field >> 4)
-            umma_f8_2cta(d_tmem, adesc + (uint64_t)(k * (kUmmaK >> 4)),
-                         bdesc + (uint64_t)(k * (kUmmaK >> 4)), idesc, (kb | k) != 0);
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // advance both descriptors by 32 bytes of K inside the swizzle row (address field >> 4)
+              umma_f8_2cta(d_tmem, adesc + (uint64_t)(k * (kUmmaK >> 4)),
+                           bdesc + (uint64_t)(k * (kUmmaK >> 4)), idesc, (kb | k) != 0);
+            }
+            umma_commit_2cta(&empty_bar[stage], pair_mask);  // frees the stage in both CTAs
           }
-          umma_commit_2cta(&empty_bar[stage], pair_mask);  // frees the stage in both CTAs
-          // running (stage, phase): no runtime division in this single-thread, latency-bound loop
+          __syncwarp();
+          // running (stage, phase): no runtime division in this latency-bound loop
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit_2cta(&acc_full[as], pair_mask);  // accumulator complete, both CTAs' epilogues may read
-        stamp(p, 4);
+        if (elect_one()) umma_commit_2cta(&acc_full[as], pair_mask);  // accumulator complete: epilogues may read
+        __syncwarp();
+        if (lane == 0) stamp(p, 4);
       }
-      if (p.trace != nullptr) {   // debug: the issuer's k-block count and its whole-loop cycle count
+      if (p.trace != nullptr && lane == 0) {   // debug: the issuer's k-block count and its whole-loop cycle count
         p.trace[(size_t)blockIdx.x * 16 + 14] = (unsigned long long)it;
         p.trace[(size_t)blockIdx.x * 16 + 15] = (unsigned long long)(clock64() - loop_c0);
       }
