@@ -69,15 +69,6 @@ constexpr int kTmemCols = 512;                   // two accumulator stages of <=
 constexpr int kAccStride = 256;                  // TMEM column offset of accumulator stage 1
 constexpr int kMaxSplits = 8;                    // cluster of 2 * 8 = 16 CTAs (non-portable size above 4 slices)
 constexpr int kEpiBarrier = 1;                   // named barrier id of the epilogue warps
-// Output staging for the TMA-store epilogue: a ring of kOutBufs buffers of [16 tokens][128 weight rows] out_t.  A
-// thread owns ONE weight row (TMEM lane) and 16 token columns, i.e. 16 elements that are `ldc` apart in `out`:
-// written directly they are 2-byte stores, 64 contiguous bytes per warp instruction, and the epilogue of a
-// 256-token tile took 3.3 us (profiles/r02_scaled_mm_trace_s46.txt: acc_rdy -> epi_end).  Staged through shared
-// memory the same stores cost one st.shared each and leave as 4 KiB bulk tensor stores.
-constexpr int kOutBufs = 4;
-constexpr int kOutBufBytes = 16 * kCtaRows * 2;
-constexpr int kOutStageBytes = kOutBufs * kOutBufBytes;   // 16 KiB
-constexpr int kTailBytes = kOutStageBytes + 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // + barriers, tmem ptr, a_scale
 
 struct Params {
   void* out;              // [M, N] out_t, row stride ldc
@@ -102,24 +93,7 @@ struct Params {
   float* sk_partials;    // stream-K: [cut][half][tok_tile / 4][128 rows][4] fp32
   uint64_t hint_w, hint_a;
   unsigned long long* trace;  // debug: [grid][16] %globaltimer stamps (nullptr = off)
-  int tma_store;              // 1: epilogue leaves through shared-memory staging + bulk tensor stores (tmap_c)
 };
-
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t smem_src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                   reinterpret_cast<uint64_t>(map)),
-               "r"(smem_src), "r"(c0), "r"(c1)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_group_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void sts_b16(uint32_t addr, uint16_t v) {
-  asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
-}
 
 __device__ __forceinline__ void stamp(const Params& p, int slot) {
   if (p.trace != nullptr) {
@@ -159,28 +133,6 @@ __device__ __forceinline__ void store_chunk16(OutT* orow, int64_t ldc, const flo
   }
 }
 
-// Same arithmetic, results written into a [16 tokens][128 rows] staging buffer (row stride 256 bytes) instead.
-template <typename OutT>
-__device__ __forceinline__ void stage_chunk16(uint32_t sbuf_row, const float (&acc)[16], uint32_t asc_smem, float bsc,
-                                              float biasf, bool has_bias) {
-  float a[16];
-#pragma unroll
-  for (int q4 = 0; q4 < 4; ++q4) {
-    const float4 v = lds_f4(asc_smem + 16 * q4);
-    a[4 * q4] = v.x;
-    a[4 * q4 + 1] = v.y;
-    a[4 * q4 + 2] = v.z;
-    a[4 * q4 + 3] = v.w;
-  }
-#pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float sv = bsc * acc[j];
-    const float v = has_bias ? fmaf(a[j], sv, biasf) : a[j] * sv;
-    const OutT o = from_float<OutT>(v);
-    sts_b16(sbuf_row + (uint32_t)(j * kCtaRows * 2), *reinterpret_cast<const uint16_t*>(&o));
-  }
-}
-
 // The work list of one pair (cluster): whole tiles cluster_id, cluster_id + num_clusters, ... restricted to the
 // pair's K slice [kb0, kb1) -- or, stream-K, the segments of its range [u0, u1) of the flattened (tile, k-block) space.
 struct SegIter {
@@ -214,15 +166,14 @@ struct SegIter {
 
 template <typename OutT>
 __global__ void __launch_bounds__(kThreads, 1)
-    scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_a,
-                     const __grid_constant__ CUtensorMap tmap_c, const Params p) {
+    scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                     const __grid_constant__ CUtensorMap tmap_a, const Params p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: [stages][W 16 KiB | A half tile] | output staging 16 KiB | barriers | tmem ptr | a_scale[2][256]
+  // carve: [stages][W 16 KiB | A half tile] | barriers | tmem ptr | a_scale[2][256]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   const size_t main_bytes = p.main_bytes;  // >= stages * stage_bytes (and >= the split-K reduce buffer)
-  uint8_t* s_outbuf = smem + main_bytes;   // output staging ring (main_bytes is a multiple of 1 KiB)
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(s_outbuf + kOutStageBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + main_bytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* acc_full = empty_bar + kMaxStages;  // [2] accumulator stage ready (both CTAs)
   uint64_t* acc_empty = acc_full + 2;           // [2] accumulator stage drained (leader's is used)
@@ -247,7 +198,6 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmap_w);
     prefetch_tensormap(&tmap_a);
-    if (p.tma_store) prefetch_tensormap(&tmap_c);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);   // leader's producer arrive (+ transaction bytes of both CTAs)
       mbar_init(&empty_bar[s], 1);  // one multicast tcgen05.commit
@@ -418,7 +368,6 @@ __global__ void __launch_bounds__(kThreads, 1)
     const bool has_bias = p.bias != nullptr;
     const uint32_t acc_empty_leader = map_to_cta(smem_u32(&acc_empty[0]), leader);
     uint32_t lt = 0;
-    uint32_t out_chunk = 0;   // running index into the output staging ring
     pdl_wait();   // scales / bias may come from the previous kernel; `out` may still be read by it
     SegIter si;
     si.init(p, cluster_id, num_clusters);
@@ -445,31 +394,14 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int ncols = min(p.tok_tile, p.M - tok0);  // valid token columns of this tile
 
       const uint32_t asc_u32 = smem_u32(asc);
-      const int n_cta0 = n_pt * kPairRows + (int)rank * kCtaRows;   // first output column of this CTA's 128
-      // 16 scaled token columns c .. c + 15 of this thread's weight row -> `out`.  Every epilogue thread calls this the
-      // same number of times in the same order (the staged path synchronises the four warps per 16-column chunk).
-      auto out16 = [&](const float (&f)[16], int c, int nvalid) {
-        if (!p.tma_store) {
-          if (n_ok) store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias, nvalid);
-          return;
-        }
-        const uint32_t sbuf = smem_u32(s_outbuf) + (out_chunk % kOutBufs) * kOutBufBytes;
-        ++out_chunk;
-        stage_chunk16<OutT>(sbuf + (uint32_t)row * 2u, f, asc_u32 + 4 * c, bsc, biasf, has_bias);
-        fence_proxy_async();                                   // my staging writes -> visible to the bulk-copy engine
-        if (tid_e == 0) bulk_wait_group_read<kOutBufs - 2>();  // the buffer the NEXT chunk will overwrite has been read
-        named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
-        if (tid_e == 0) {
-          tma_store_2d(&tmap_c, sbuf, n_cta0, tok0 + c);       // rows past M and columns past N are clipped
-          bulk_commit_group();
-        }
-      };
       // 16 accumulator columns (registers r[off .. off+15]) -> scaled, converted, stored
       auto emit16 = [&](const uint32_t* r, int c) {
         float f[16];
 #pragma unroll
         for (int jx = 0; jx < 16; ++jx) f[jx] = __uint_as_float(r[jx]);
-        out16(f, c, ncols - c);
+        if (n_ok)
+          store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
+                        ncols - c);
       };
       const bool sk_partial = p.streamk && (seg_lo > 0 || seg_hi < p.num_kb);
       if (sk_partial) {
@@ -529,7 +461,9 @@ __global__ void __launch_bounds__(kThreads, 1)
               f[4 * jj + 3] = __uint_as_float(r[4 * jj + 3]) + v.w;
             }
             const int c = jc << 4;
-            out16(f, c, ncols - c);
+            if (n_ok)
+              store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
+                            ncols - c);
           };
           tmem_ld_x16(taddr, ra);
           for (int jc = 0; jc < tpc; jc += 2) {
@@ -635,7 +569,9 @@ __global__ void __launch_bounds__(kThreads, 1)
               }
             }
             const int cc = c_own + cc0;
-            out16(f, cc, p.M - tok0 - cc);
+            if (n_ok)
+              store_chunk16(outp + (int64_t)(tok0 + cc) * p.ldc + n, p.ldc, f, asc_u32 + 4 * cc, bsc, biasf, has_bias,
+                            p.M - tok0 - cc);
           };
           for (; c < nc; c += 32 * kWpq) {
             tmem_ld_wait();
@@ -656,7 +592,6 @@ __global__ void __launch_bounds__(kThreads, 1)
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(acc_empty_leader + as * 8u);
     }
-    if (p.tma_store && tid_e == 0) bulk_wait_group_all();   // every bulk store of this CTA has been written
   }
 
   // teardown: nobody leaves (or frees TMEM) while the peer may still touch this CTA
@@ -708,7 +643,7 @@ static Plan make_plan(int M, int N, int K) {
   g.n_ptiles = ceil_div(N, kPairRows);
   g.num_kb = ceil_div(K, kBlockK);
   const int max_pairs = num_sms() / 2;
-  const int tail = kTailBytes;
+  const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;  // barriers, tmem ptr, a_scale
   const int budget = 227 * 1024 - 1024 /*alignment slack*/ - tail;
   const double w_bytes = (double)N * K, a_bytes = (double)M * K;
   // candidates: token tiles of <= 256 columns (one more split of a single 129..256-token tile in two), K slices
@@ -806,7 +741,7 @@ static int max_clusters_cached(int cluster_ctas, size_t smem) {
 }
 
 template <typename OutT>
-static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, const CUtensorMap& tc_, const Params& p,
+static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, const Params& p,
                   cudaStream_t stream) {
   auto kern = scaled_mm_kernel<OutT>;
   const int cluster_ctas = 2 * g.splits;
@@ -825,14 +760,13 @@ static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, c
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  VB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tw, ta, tc_, p));
+  VB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tw, ta, p));
   return 0;
 }
 
 static int g_force_splits = 0;   // debug / tuning hook (vb200_debug_scaled_mm_plan): 0 = planner's choice
 static int g_force_mtiles = 0;
 static int g_no_streamk = 0;     // debug: 1 = whole tiles per pair even when stream-K applies
-static int g_no_tma_store = getenv("VB200_GEMM_TMA_STORE") && getenv("VB200_GEMM_TMA_STORE")[0] == '0';  // debug: direct stores
 
 static int run(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
@@ -851,7 +785,7 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
     g.tiles = g.m_tiles * g.n_ptiles;
     g.kb_per_split = ceil_div(g.num_kb, g.splits);
     VB_CHECK(ceil_div(g.num_kb, g.kb_per_split) == g.splits, "scaled_mm debug plan: empty K slice");
-    const int tail = kTailBytes;
+    const int tail = 2 * kMaxStages * 8 + 5 * 8 + 24 + 2 * kMaxTokTile * 4;
     const int a_tile = ((g.tok_tile / 2) * kBlockK + 1023) / 1024 * 1024;
     g.stage_bytes = kWTileBytes + a_tile;
     g.stages = (227 * 1024 - 1024 - tail) / g.stage_bytes;
@@ -897,12 +831,8 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
   p.hint_w = g.m_tiles == 1 ? kEvictFirst : kEvictNormal;
   p.hint_a = g.m_tiles == 1 ? kEvictLast : kEvictNormal;
   p.trace = g_trace;
-  // bulk tensor stores need a 16-byte aligned base and row pitch; anything else keeps the direct stores
-  CUtensorMap tcm = tw;
-  p.tma_store = g_no_tma_store ? 0 : (((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (ldc * 2) % 16 == 0) ? 1 : 0);
-  if (p.tma_store && tc::make_tmap_2d_out16(&tcm, out, (uint64_t)M, (uint64_t)N, (uint64_t)ldc * 2, kCtaRows, 16)) return 1;
-  if (out_dtype == VB200_BF16) return launch<__nv_bfloat16>(g, tw, ta, tcm, p, stream);
-  return launch<__half>(g, tw, ta, tcm, p, stream);
+  if (out_dtype == VB200_BF16) return launch<__nv_bfloat16>(g, tw, ta, p, stream);
+  return launch<__half>(g, tw, ta, p, stream);
 }
 
 }  // namespace v2

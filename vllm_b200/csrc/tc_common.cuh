@@ -272,9 +272,6 @@ __device__ __forceinline__ void fence_proxy_async_all() {
 // 128-byte swizzle; out-of-bounds elements read as zero.  Returns 0 on success.
 int make_tmap_2d_u8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows);
-// 2-D matrix of 16-bit elements, box {box_cols, box_rows}, no swizzle: bulk tensor stores of GEMM outputs.
-int make_tmap_2d_out16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_bytes,
-                       uint32_t box_cols, uint32_t box_rows);
 // 4-D byte tensor {inner bytes, dim1, dim2, dim3}, byte strides of dims 1..3; box {128 B, box1, 1, 1}; 128-byte swizzle.
 int make_tmap_4d_u8(CUtensorMap* map, const void* base, const uint64_t dims[4], const uint64_t strides_bytes[3],
                     uint32_t box1);

@@ -45,25 +45,6 @@ int make_tmap_2d_u8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return 0;
 }
 
-// 2-D row-major matrix of 16-bit elements [rows, cols], row pitch `ld_bytes`; box = {box_cols, box_rows}, no swizzle
-// (shared-memory image = box_rows rows of box_cols * 2 contiguous bytes); used for bulk tensor STORES of GEMM outputs.
-int make_tmap_2d_out16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_bytes,
-                       uint32_t box_cols, uint32_t box_rows) {
-  EncodeTiledFn enc = get_encode();
-  VB_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
-  VB_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld_bytes & 15) == 0,
-           "TMA stores need a 16-byte aligned base and row pitch (base %p, pitch %llu)", base, (unsigned long long)ld_bytes);
-  const cuuint64_t dims[2] = {cols, rows};
-  const cuuint64_t strides[1] = {ld_bytes};
-  const cuuint32_t box[2] = {box_cols, box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  VB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (output) failed with CUresult %d", (int)r);
-  return 0;
-}
-
 // 4-D byte tensor {inner bytes, dim1, dim2, dim3} with byte strides for dims 1..3 (any order of magnitudes: this is how
 // one map covers both the NHD and the HND-permuted KV-cache views); box = {128 bytes, box1, 1, 1}, 128-byte swizzle.
 int make_tmap_4d_u8(CUtensorMap* map, const void* base, const uint64_t dims[4], const uint64_t strides_bytes[3],
