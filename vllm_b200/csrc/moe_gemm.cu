@@ -164,46 +164,55 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // Producer and MMA issuer: the WHOLE warp runs the loop and waits on the barriers, one elected lane issues.  With the
+  // warp converged the compiler keeps descriptors and barrier addresses in uniform registers; issued from a
+  // `lane == 0` branch every UTCQMMA / UTCBAR / UTMALDG was wrapped in an ELECT + R2UR.BROADCAST waterfall loop
+  // (measured on the dense GEMM: 69 cycles per MMA issue, profiles/r02_scaled_mm_trace_s42.txt vs _s46.txt).
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const int wrow = expert * p.N + n0;  // row of the [E*N, K] weight matrix
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sw = smem + (size_t)stage * stage_bytes;
+    int stage = 0;
+    uint32_t phase = 0;
+    const int wrow = expert * p.N + n0;  // row of the [E*N, K] weight matrix
+    for (int kb = 0; kb < p.num_kb; ++kb) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* sw = smem + (size_t)stage * stage_bytes;
+      if (elect_one()) {
         mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
         tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * kMoeBlockK, wrow, kEvictFirst);
         tma_load_2d(sw + kMoeWTile, &tmap_a, &full_bar[stage], kb * kMoeBlockK, row0, kEvictLast);
-        if (++stage == p.stages) {
-          stage = 0;
-          phase ^= 1;
-        }
+      }
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_f8(kMoeBlockN, umma_n);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t sw = smem_u32(smem + (size_t)stage * stage_bytes);
-        const uint64_t adesc = make_smem_desc_sw128(sw);
-        const uint64_t bdesc = make_smem_desc_sw128(sw + kMoeWTile);
+    const uint32_t idesc = make_idesc_f8(kMoeBlockN, umma_n);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t smem_base_u = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < p.num_kb; ++kb) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      const uint32_t sw = smem_base_u + (uint32_t)stage * (uint32_t)stage_bytes;
+      const uint64_t adesc = make_smem_desc_sw128(sw);
+      const uint64_t bdesc = make_smem_desc_sw128(sw + kMoeWTile);
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
-          umma_f8(tmem_base, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+          umma_f8(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
                   bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
         umma_commit(&empty_bar[stage]);
-        if (++stage == p.stages) {
-          stage = 0;
-          phase ^= 1;
-        }
       }
-      umma_commit(acc_bar);
+      __syncwarp();
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
     }
+    if (elect_one()) umma_commit(acc_bar);
+    __syncwarp();
   } else {
     // ===== epilogue warps 2..5 =====
     const int q = warp & 3;
