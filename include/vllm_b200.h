@@ -428,6 +428,17 @@ int vb200_peer_allreduce_2shot(int mode, void* out, const void* const* peer_data
                                void* residual, const void* weight, float epsilon, float* scales,
                                const float* scale_ub, vb200_stream_t stream);
 
+/* Split variant: reduce-scatter fused with the consumer (each rank reduces, norms and quantises ONLY its rows) followed
+ * by an all-gather of the finished rows, as two launches -- the single-kernel two-shot pays a fenced grid-wide barrier in
+ * the middle that costs more than the NVLink time it saves (profiles/r02_multi_gpu_tp8_s44.txt); here that barrier is a
+ * kernel boundary and both kernels start with the cheap unfenced flag barrier.  peer_gather: HOST array of `world`
+ * device pointers, each at least 2 * rows * hidden * sizeof(T) + 4 * rows bytes, peer-visible.  Results (out, residual,
+ * scales on every rank) are bit-identical to vb200_peer_allreduce. */
+int vb200_peer_allreduce_split(int mode, void* out, const void* const* peer_data, void* const* peer_gather,
+                               void* const* peer_signals, int rank, int world, int rows, int hidden, int dtype,
+                               void* residual, const void* weight, float epsilon, float* scales,
+                               const float* scale_ub, vb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,6 +103,8 @@ SIGNATURES = {
                                      _P]),
     "vb200_peer_allreduce_2shot": (c_int, [c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_float, _P,
                                            _P, _P]),
+    "vb200_peer_allreduce_split": (c_int, [c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, c_float, _P,
+                                           _P, _P]),
     "vb200_cutlass_moe_mm": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_int, _P]),
 }

@@ -428,6 +428,92 @@ __global__ void __launch_bounds__(kArThreads, 1) peer_allreduce_staged_kernel(co
   ar_barrier<N>(p);
 }
 
+// ---- split variant: reduce-scatter + consumer | all-gather, as TWO kernels -------------------------------------------
+// What the measurements said about the single-kernel two-shot above (profiles/r02_multi_gpu_tp8_s44.txt: 34.8 us at
+// 8 ranks vs 33.2 us one-shot; 27.8 vs 14.3 us at 2 ranks): its grid-wide + cross-GPU MIDDLE barrier, which has to be
+// fenced at system scope because it publishes data written inside the same kernel, costs more than the NVLink time
+// the shard-wise reduction saves.  Splitting at that point turns the middle barrier into a kernel boundary: kernel 1
+// (start barrier, unfenced as before) reduces ONLY this rank's rows, runs the residual add / RMSNorm (/ quant) on
+// them -- the consumer's work is sharded N ways too -- and leaves normed rows, updated residual rows and scales in its
+// peer-visible gather buffer; kernel 2 starts with the same unfenced flag barrier (what it announces was written by
+// the peer's PREVIOUS kernel) and copies every row from its owner.  Per GPU (N-1)/N of the partial sums are pulled
+// once, and the gathered bytes are the fp8 rows + residual rows instead of N-1 copies of the bf16 tensor.
+//   gather buffer of a rank: [out rows | residual rows | scales], each region sized for ALL rows (only the owner's
+//   rows are valid): offsets rows*hidden*sizeof(T), 2*rows*hidden*sizeof(T).
+template <typename T, int N, int MODE>
+__global__ void __launch_bounds__(kArThreads, 1) peer_reduce_scatter_kernel(const ArParams p) {
+  __shared__ float sm[kArThreads / 32];
+  pdl_wait();
+  pdl_trigger();
+  ar_barrier<N>(p);
+  const int rows_per = (p.rows + N - 1) / N;
+  const int r0 = min(p.rank * rows_per, p.rows), r1 = min(r0 + rows_per, p.rows);
+  uint8_t* g = reinterpret_cast<uint8_t*>(p.gather[p.rank]);
+  const size_t region = (size_t)p.rows * p.hidden * sizeof(T);
+  if (MODE == 0) {
+    const int nvec = p.hidden >> 3;
+    T* dst = reinterpret_cast<T*>(g);
+    for (int64_t i = (int64_t)r0 * nvec + (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < (int64_t)r1 * nvec;
+         i += (int64_t)gridDim.x * kArThreads) {
+      float acc[8];
+      ar_sum8<T, N>(p, i * 8, acc);
+      ArVec8<T> o;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.e[j] = from_float<T>(acc[j]);
+      *reinterpret_cast<uint4*>(dst + i * 8) = o.u;
+    }
+    return;
+  }
+  ArParams q = p;
+  q.out = g;                                                  // normed (/ quantised) rows, indexed by global row
+  q.scales = reinterpret_cast<float*>(g + 2 * region);
+  T* res_copy = reinterpret_cast<T*>(g + region);
+  const int nvec = p.hidden >> 3;
+  for (int row = r0 + blockIdx.x; row < r1; row += gridDim.x) {
+    ar_norm_row<T, MODE>(q, row, sm,
+                         [&](int i, float (&x)[8]) { ar_sum8<T, N>(p, (int64_t)row * p.hidden + i * 8, x); });
+    // the updated residual row travels too: every rank ends with the whole residual, as after the reference's op
+    __syncthreads();
+    const T* res = reinterpret_cast<const T*>(p.residual) + (int64_t)row * p.hidden;
+    for (int i = threadIdx.x; i < nvec; i += kArThreads)
+      *reinterpret_cast<uint4*>(res_copy + (int64_t)row * p.hidden + i * 8) = *reinterpret_cast<const uint4*>(res + i * 8);
+  }
+}
+
+template <typename T, int N, int MODE>
+__global__ void __launch_bounds__(kArThreads, 1) peer_all_gather_kernel(const ArParams p) {
+  pdl_wait();     // this rank's kernel 1 has completed (and with it everything it wrote)
+  pdl_trigger();
+  ar_barrier<N>(p);   // every peer is past ITS kernel 1 as well
+  const int rows_per = (p.rows + N - 1) / N;
+  const size_t region = (size_t)p.rows * p.hidden * sizeof(T);
+  const int out_row_bytes = MODE == 2 ? p.hidden : p.hidden * (int)sizeof(T);
+  const int ovec = out_row_bytes >> 4, rvec = (p.hidden * (int)sizeof(T)) >> 4;
+  const int per_row = ovec + (MODE == 0 ? 0 : rvec);
+  const int64_t total = (int64_t)p.rows * per_row;
+  for (int64_t i = (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kArThreads) {
+    const int row = (int)(i / per_row);
+    const int v = (int)(i - (int64_t)row * per_row);
+    const uint8_t* g = reinterpret_cast<const uint8_t*>(p.gather[row / rows_per]);
+    if (v < ovec) {
+      const uint4 x = ld_peer_v4(g + (int64_t)row * out_row_bytes + v * 16);
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.out) + (int64_t)row * out_row_bytes + v * 16) = x;
+    } else if (row / rows_per != p.rank) {   // my own residual rows are already in place
+      const int vv = v - ovec;
+      const uint4 x = ld_peer_v4(g + region + (int64_t)row * p.hidden * sizeof(T) + vv * 16);
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.residual) + (int64_t)row * p.hidden * sizeof(T) + vv * 16) = x;
+    }
+  }
+  if (MODE == 2) {
+    for (int row = blockIdx.x * kArThreads + threadIdx.x; row < p.rows; row += gridDim.x * kArThreads) {
+      const float* sc = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(p.gather[row / rows_per]) + 2 * region);
+      float v;
+      asm volatile("ld.global.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(sc + row) : "memory");
+      p.scales[row] = v;
+    }
+  }
+}
+
 static int g_ar_blocks = 0;       // 0 = default; debug / tuning hook below
 static int g_ar_staged = 0;       // measured: direct loads win at 8 ranks (33 vs 52 us) and tie at 2 (14.6 vs 15.1 us)
 
@@ -456,6 +542,32 @@ static int launch_mode(int mode, int grid, const ArParams& p, bool two_shot, cud
   if (mode == 0) VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 0>, dim3(grid), dim3(kArThreads), 0, stream, p));
   else if (mode == 1) VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 1>, dim3(grid), dim3(kArThreads), 0, stream, p));
   else VB_CUDA_CHECK(launch_k(peer_allreduce_kernel<T, N, 2>, dim3(grid), dim3(kArThreads), 0, stream, p));
+  return 0;
+}
+
+template <typename T, int N>
+static int launch_split(int mode, const ArParams& p, cudaStream_t stream) {
+  const int rows_per = (p.rows + N - 1) / N;
+  int cap = g_ar_blocks > 0 ? g_ar_blocks : num_sms();
+  if (cap > num_sms()) cap = num_sms();
+  if (cap > kArMaxBlocks) cap = kArMaxBlocks;
+  int g1 = mode == 0 ? (int)(((int64_t)rows_per * p.hidden / 8 + kArThreads - 1) / kArThreads) : rows_per;
+  if (g1 > cap) g1 = cap;
+  if (g1 < 1) g1 = 1;
+  const int64_t vecs = (int64_t)p.rows * p.hidden * (mode == 2 ? 3 : (mode == 1 ? 4 : 2)) / 16;
+  int g2 = (int)((vecs + kArThreads - 1) / kArThreads);
+  if (g2 > cap) g2 = cap;
+  if (g2 < 1) g2 = 1;
+  if (mode == 0) {
+    VB_CUDA_CHECK(launch_k(peer_reduce_scatter_kernel<T, N, 0>, dim3(g1), dim3(kArThreads), 0, stream, p));
+    VB_CUDA_CHECK(launch_k(peer_all_gather_kernel<T, N, 0>, dim3(g2), dim3(kArThreads), 0, stream, p));
+  } else if (mode == 1) {
+    VB_CUDA_CHECK(launch_k(peer_reduce_scatter_kernel<T, N, 1>, dim3(g1), dim3(kArThreads), 0, stream, p));
+    VB_CUDA_CHECK(launch_k(peer_all_gather_kernel<T, N, 1>, dim3(g2), dim3(kArThreads), 0, stream, p));
+  } else {
+    VB_CUDA_CHECK(launch_k(peer_reduce_scatter_kernel<T, N, 2>, dim3(g1), dim3(kArThreads), 0, stream, p));
+    VB_CUDA_CHECK(launch_k(peer_all_gather_kernel<T, N, 2>, dim3(g2), dim3(kArThreads), 0, stream, p));
+  }
   return 0;
 }
 
@@ -545,6 +657,51 @@ extern "C" int vb200_peer_allreduce_2shot(int mode, void* out, const void* const
   VB_CHECK(peer_gather != nullptr, "peer_allreduce_2shot: peer_gather is required");
   return run_peer_allreduce(mode, out, peer_data, peer_gather, peer_signals, rank, world, rows, hidden, dtype,
                             residual, weight, epsilon, scales, scale_ub, (cudaStream_t)stream_);
+}
+
+// Split variant (reduce-scatter + consumer | all-gather, two launches; see the kernels).  peer_gather: every rank's
+// gather buffer, at least 2 * rows * hidden * sizeof(T) + 4 * rows bytes.  Same results as vb200_peer_allreduce.
+extern "C" int vb200_peer_allreduce_split(int mode, void* out, const void* const* peer_data, void* const* peer_gather,
+                                          void* const* peer_signals, int rank, int world, int rows, int hidden,
+                                          int dtype, void* residual, const void* weight, float epsilon, float* scales,
+                                          const float* scale_ub, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(mode >= 0 && mode <= 2, "peer_allreduce_split: bad mode %d", mode);
+  VB_CHECK(dtype == VB200_BF16 || dtype == VB200_F16, "peer_allreduce_split: dtype must be bf16 or f16");
+  VB_CHECK(rank >= 0 && rank < world && world <= kArMaxRanks, "peer_allreduce_split: bad rank %d / world %d", rank, world);
+  VB_CHECK(rows > 0 && hidden > 0 && hidden % 16 == 0, "peer_allreduce_split: hidden (%d) must be a positive multiple of 16", hidden);
+  VB_CHECK(mode == 0 || hidden <= kArThreads * kArMaxVec * 8, "peer_allreduce_split: hidden %d too large for the fused modes", hidden);
+  VB_CHECK(mode == 0 || (residual != nullptr && weight != nullptr), "peer_allreduce_split: fused modes need residual and weight");
+  VB_CHECK(mode != 2 || scales != nullptr, "peer_allreduce_split: mode 2 needs scales");
+  VB_CHECK(peer_gather != nullptr, "peer_allreduce_split: peer_gather is required");
+  ArParams p;
+  for (int r = 0; r < kArMaxRanks; ++r) {
+    p.data[r] = r < world ? peer_data[r] : nullptr;
+    p.gather[r] = r < world ? peer_gather[r] : nullptr;
+    p.signals[r] = r < world ? reinterpret_cast<ArSignal*>(peer_signals[r]) : nullptr;
+    VB_CHECK(r >= world || (p.data[r] && p.gather[r] && p.signals[r]), "peer_allreduce_split: null peer pointer");
+    VB_CHECK(r >= world || ((reinterpret_cast<uintptr_t>(p.data[r]) | reinterpret_cast<uintptr_t>(p.gather[r])) & 15) == 0,
+             "peer_allreduce_split: peer buffers must be 16-byte aligned");
+  }
+  p.rank = rank;
+  p.out = out;
+  p.residual = residual;
+  p.weight = weight;
+  p.scales = scales;
+  p.scale_ub = scale_ub;
+  p.eps = epsilon;
+  p.rows = rows;
+  p.hidden = hidden;
+#define VB_SPLIT(T_)                                                     \
+  switch (world) {                                                       \
+    case 2: return launch_split<T_, 2>(mode, p, stream);                 \
+    case 4: return launch_split<T_, 4>(mode, p, stream);                 \
+    case 8: return launch_split<T_, 8>(mode, p, stream);                 \
+    default: VB_CHECK(false, "peer_allreduce_split: world size %d not in {2, 4, 8}", world); \
+  }
+  if (dtype == VB200_BF16) { VB_SPLIT(__nv_bfloat16) } else { VB_SPLIT(__half) }
+#undef VB_SPLIT
+  return 1;
 }
 
 // ---- peer-visible buffers (CUDA IPC) ----------------------------------------------------------------------------

@@ -50,8 +50,10 @@ class PeerAllReduce:
         # (and the caller falls back to NCCL on all ranks together).
         payload, err = None, None
         self._own_ptr, self._peer_ptrs = None, []
-        # layout of the allocation: [signal block | staging (partial sums) | gather (two-shot: reduced shards)]
-        total = self._sig_bytes + 2 * self.max_bytes
+        # layout of the allocation: [signal block | staging (partial sums) | gather (two-shot: reduced shards; split:
+        # finished rows + residual rows + scales)]
+        self._gather_bytes = 2 * self.max_bytes + (64 << 10)
+        total = self._sig_bytes + self.max_bytes + self._gather_bytes
         try:
             with torch.cuda.device(self.device):
                 p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
@@ -89,8 +91,8 @@ class PeerAllReduce:
         # two-shot (reduce-scatter + all-gather) from 512 KB at 4 ranks / 256 KB at 8 ranks.  VB200_PEER_AR_ALGO / `algo` pins it (same on every rank);
         # the choice depends only on (world, bytes), so every rank takes the same kernel.
         self.algo = algo if algo is not None else os.environ.get("VB200_PEER_AR_ALGO", "auto")
-        if self.algo not in ("auto", "1shot", "2shot"):
-            raise RuntimeError(f"VB200_PEER_AR_ALGO={self.algo}: expected auto, 1shot or 2shot")
+        if self.algo not in ("auto", "1shot", "2shot", "split"):
+            raise RuntimeError(f"VB200_PEER_AR_ALGO={self.algo}: expected auto, 1shot, 2shot or split")
         # this rank's staging area as a torch tensor over the raw allocation (the GEMM writes into it)
         self._own = torch.as_tensor(_RawCudaBuffer(self._own_ptr + self._sig_bytes, self.max_bytes), device=self.device)
 
@@ -111,18 +113,37 @@ class PeerAllReduce:
             raise RuntimeError("PeerAllReduce: the input must be the tensor returned by staging()")
         return x.shape[0], x.shape[1]
 
-    def two_shot(self, nbytes: int) -> bool:
-        """Which kernel a message of `nbytes` takes (same answer on every rank)."""
+    def pick(self, rows: int, hidden: int, dtype: torch.dtype) -> str:
+        """Which kernel(s) a [rows, hidden] message takes: "1shot", "2shot" or "split" (same answer on every rank: it
+        depends only on world size and shape).  auto = what the 8-GPU measurements say
+        (profiles/r02_multi_gpu_tp8_s44.txt, r02_peer_allreduce_split_*.txt): one-shot at 2 ranks and for small
+        messages; from 4 ranks and 256 KB on, the split form (reduce-scatter + consumer | all-gather, two launches).  The
+        single-kernel two-shot never won (its fenced middle barrier) and is kept for comparison only."""
+        nbytes = rows * hidden * torch.empty((), dtype=dtype).element_size()
+        split_ok = hidden % 16 == 0 and rows >= self.world and 2 * nbytes + 4 * rows <= self._gather_bytes
+        if self.algo == "split":
+            return "split" if split_ok else "1shot"
         if self.algo != "auto":
-            return self.algo == "2shot"
-        return (self.world == 4 and nbytes >= 512 * 1024) or (self.world == 8 and nbytes >= 256 * 1024)
+            return self.algo
+        if self.world >= 4 and nbytes >= 256 * 1024 and split_ok:
+            return "split"
+        return "1shot"
+
+    def two_shot(self, nbytes: int) -> bool:
+        return self.algo == "2shot"
 
     def algo_name(self, rows: int, hidden: int, dtype: torch.dtype) -> str:
-        return "peer-2shot" if self.two_shot(rows * hidden * torch.empty((), dtype=dtype).element_size()) else "peer-1shot"
+        return "peer-" + self.pick(rows, hidden, dtype)
 
     def _call(self, mode, out, rows, hidden, dtype, residual, weight, eps, scales, scale_ub):
         lib = load()
-        if self.two_shot(rows * hidden * torch.empty((), dtype=dtype).element_size()):
+        algo = self.pick(rows, hidden, dtype)
+        if algo == "split":
+            check(lib.vb200_peer_allreduce_split(mode, ptr(out), self._data_ptrs, self._gather_ptrs, self._sig_ptrs,
+                                                 self.rank, self.world, rows, hidden, dtype_enum(dtype), ptr(residual),
+                                                 ptr(weight), float(eps), ptr(scales), ptr(scale_ub), stream()))
+            return
+        if algo == "2shot":
             check(lib.vb200_peer_allreduce_2shot(mode, ptr(out), self._data_ptrs, self._gather_ptrs, self._sig_ptrs,
                                                  self.rank, self.world, rows, hidden, dtype_enum(dtype), ptr(residual),
                                                  ptr(weight), float(eps), ptr(scales), ptr(scale_ub), stream()))
