@@ -74,10 +74,10 @@ def main():
             finally:
                 co._TP_GROUP, co._TP_WORLD, co._TP_RANK, co._PEER_AR = saved
             scale = ref.abs().max().item()
-            for ar in ("gloo",) if one_gpu else ("nccl", "1shot", "2shot"):
+            for ar in ("gloo",) if one_gpu else ("nccl", "1shot", "2shot", "split"):
                 co._PEER_AR = None if ar in ("nccl", "gloo") else par
                 if par is not None:
-                    par.algo = ar if ar in ("1shot", "2shot") else "auto"
+                    par.algo = ar if ar in ("1shot", "2shot", "split") else "auto"
                 got = run_decoder(Decoder(cfg, nb, bs, kvd, "fp8", device=dev, seed=5), cfg, B, bs, nb, dev, gather_vocab)
                 err = (got - ref).abs()
                 # TP-N is not bit-identical to TP-1 even with a perfect all-reduce: the row-parallel GEMMs (o_proj,

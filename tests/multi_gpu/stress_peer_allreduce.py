@@ -71,7 +71,7 @@ def main():
     t0 = time.perf_counter()
     for it in range(ITERS):
         shape = SHAPES[rng_plan.randrange(len(SHAPES))]
-        algo = ("1shot", "2shot")[rng_plan.randrange(2)]
+        algo = ("1shot", "2shot", "split")[rng_plan.randrange(3)]
         mode = (0, 0, 0, 1, 2)[rng_plan.randrange(5)]
         if rng_delay.random() < 0.03:
             torch.cuda._sleep(rng_delay.randrange(1, 2_000_000))   # up to ~1 ms at 1.9 GHz
@@ -82,7 +82,7 @@ def main():
     # ---- graph: 8 mixed calls per replay, REPLAYS replays, a replicated scalar input changes between replays --------
     bad.zero_()
     shift = torch.zeros((), device=dev, dtype=dt)
-    plan = [(SHAPES[rng_plan.randrange(len(SHAPES))], ("1shot", "2shot")[i % 2]) for i in range(8)]
+    plan = [(SHAPES[rng_plan.randrange(len(SHAPES))], ("1shot", "2shot", "split")[i % 3]) for i in range(8)]
 
     def body():
         for shape, algo in plan:
