@@ -116,8 +116,8 @@ class PeerAllReduce:
     def pick(self, rows: int, hidden: int, dtype: torch.dtype) -> str:
         """Which kernel(s) a [rows, hidden] message takes: "1shot", "2shot" or "split" (same answer on every rank: it
         depends only on world size and shape).  auto = what the 8-GPU measurements say
-        (profiles/r02_multi_gpu_tp8_s44.txt, r02_peer_allreduce_split_*.txt): one-shot at 2 ranks and for small
-        messages; from 4 ranks and 256 KB on, the split form (reduce-scatter + consumer | all-gather, two launches).  The
+        (profiles/r02_multi_gpu_tp8_s44.txt, r02_peer_allreduce_split_*.txt): one-shot at 2 and 4 ranks and for small
+        messages; at 8 ranks from 256 KB on, the split form (reduce-scatter + consumer | all-gather, two launches).  The
         single-kernel two-shot never won (its fenced middle barrier) and is kept for comparison only."""
         nbytes = rows * hidden * torch.empty((), dtype=dtype).element_size()
         split_ok = hidden % 16 == 0 and rows >= self.world and 2 * nbytes + 4 * rows <= self._gather_bytes
@@ -125,7 +125,10 @@ class PeerAllReduce:
             return "split" if split_ok else "1shot"
         if self.algo != "auto":
             return self.algo
-        if self.world >= 4 and nbytes >= 256 * 1024 and split_ok:
+        # measured per fused op at [256 x 4096] bf16 (us, one-shot / split): 2 ranks 14.2 / 18.3, 4 ranks 19.6 / 23.9,
+        # 8 ranks 33.3 / 24.6 -- the split form pays a second launch + barrier and wins once (N-1) copies of the
+        # tensor per GPU outweigh them
+        if self.world >= 8 and nbytes >= 256 * 1024 and split_ok:
             return "split"
         return "1shot"
 
