@@ -310,6 +310,17 @@ int vb200_moe_grouped_gemm_fp8(void* c, const void* a, const void* b, const floa
                                int b_scales_per_channel, int mul_routed_weight, int out_dtype,
                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
 
+/* Unquantised (f16 / bf16) experts: the same grouped GEMM for fused_experts with use_fp8_w8a8 = False
+ * (fused_moe.py:1349-1563; the bf16-weights case of tests/kernels/moe/test_moe.py:117-233):
+ *   C[token_id, n] = OutT( (sum_k A[token_id / top_k, k] * B[e, n, k]) * [topk_weights[token_id]] ), fp32 accumulate.
+ * a [num_a_rows, K], b [E, N, K], c [num_valid_tokens, N] all of `dtype` (F16 / BF16), contiguous; K % 8 == 0.
+ * workspace: vb200_moe_grouped_gemm_workspace_size(sorted_capacity, 2 * K) bytes. */
+int vb200_moe_grouped_gemm_16(void* c, const void* a, const void* b, const float* topk_weights,
+                              const int32_t* sorted_token_ids, const int32_t* expert_ids,
+                              const int32_t* num_tokens_post_pad, int num_valid_tokens, int num_a_rows, int top_k,
+                              int E, int N, int K, int block_m, int sorted_capacity, int mul_routed_weight, int dtype,
+                              void* workspace, size_t workspace_bytes, vb200_stream_t stream);
+
 /* ---- CUTLASS-style fused-MoE API ----------------------------------------- */
 
 /* get_cutlass_moe_mm_data: csrc/quantization/cutlass_w8a8/moe/moe_data.cu:103-159, schema

@@ -129,3 +129,38 @@ def test_fused_experts_cuda_graph():
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, eager)
+
+
+@pytest.mark.parametrize("T,k,E,H,I", [(1, 2, 8, 256, 512), (33, 2, 8, 128, 1024), (128, 2, 8, 512, 1024),
+                                        (33, 6, 64, 256, 256), (222, 2, 8, 1024, 896), (64, 2, 8, 2048, 200)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_fused_experts_unquantised(T, k, E, H, I, dtype):
+    """The bf16 / f16-weights variant of fused_experts (tests/kernels/moe/test_moe.py:117-233 compares
+    fused_moe with torch_moe on randn / 10 weights at atol 2e-2): same tcgen05 grouped GEMM with kind::f16 MMAs."""
+    from vllm_b200.fused_moe import fused_experts, fused_topk
+    seed_all(T + H + I)
+    w1 = (torch.randn(E, 2 * I, H) / 10).to(dtype)
+    w2 = (torch.randn(E, H, I) / 10).to(dtype)
+    x = (torch.randn(T, H) / 10).to(dtype)
+    gate = torch.randn(T, E)
+    tw_o, ids_o, _ = omoe.topk_softmax(gate, k)
+    tw_o = tw_o / tw_o.sum(-1, keepdim=True)
+    want = omoe.fused_experts_bf16(x, w1, w2, tw_o, ids_o)
+    tw, ids, _ = fused_topk(x.to(DEV), gate.to(DEV), k, True)
+    assert torch.equal(ids.cpu(), ids_o), "top-k ids must be bit-exact"
+    out = fused_experts(x.to(DEV), w1.to(DEV), w2.to(DEV), tw, ids)
+    torch.cuda.synchronize()
+    assert out.dtype == dtype and out.shape == (T, H)
+    torch.testing.assert_close(out.cpu().float(), want.float(), rtol=1e-2, atol=2e-2)
+
+
+def test_grouped_gemm_16_rejects_mixed_dtypes():
+    from vllm_b200.fused_moe.fused_moe import invoke_fused_moe_kernel
+    from vllm_b200.fused_moe import moe_align_block_size
+    ids = torch.zeros(4, 2, dtype=torch.int32, device=DEV)
+    s, e, n = moe_align_block_size(ids, 16, 2)
+    a = torch.zeros(4, 64, dtype=torch.bfloat16, device=DEV)
+    b = torch.zeros(2, 128, 64, dtype=torch.float16, device=DEV)
+    c = torch.zeros(4, 2, 128, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(RuntimeError):
+        invoke_fused_moe_kernel(a, b, c, None, None, None, s, e, n, False, 2, 16, False)

@@ -86,6 +86,8 @@ SIGNATURES = {
     "vb200_moe_grouped_gemm_fp8": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                            c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t,
                                            _P]),
+    "vb200_moe_grouped_gemm_16": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                          c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_moe_grouped_gemm_workspace_size": (c_size_t, [c_int, c_int]),
     "vb200_get_cutlass_moe_mm_data": (c_int, [_P, c_int, c_int, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P]),
     "vb200_get_cutlass_pplx_moe_mm_data": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),

@@ -47,6 +47,8 @@ struct MoeParams {
   const int32_t* expert_offsets;   // [E] first row of expert e
   const int32_t* problem_sizes;    // [E, 3] = (m_e, N, K), or (N, m_e, K) when the producer swapped A/B
   int ragged;
+  int in16;                        // 0: fp8 e4m3 operands; 1: f16; 2: bf16 (unquantised experts, test_moe.py:117-233).  K
+                                   // and the tile sizes are in BYTES throughout, so only the MMA kind differs
 };
 
 // A_sorted[r, :] = A[sorted_token_ids[r] / top_k, :] for valid r < num_tokens_post_pad (16-byte
@@ -187,7 +189,7 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc_f8(kMoeBlockN, umma_n);
+    const uint32_t idesc = p.in16 ? make_idesc_16(kMoeBlockN, umma_n, p.in16 == 2) : make_idesc_f8(kMoeBlockN, umma_n);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t smem_base_u = smem_u32(smem);
     int stage = 0;
@@ -199,10 +201,18 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
       const uint64_t adesc = make_smem_desc_sw128(sw);
       const uint64_t bdesc = make_smem_desc_sw128(sw + kMoeWTile);
       if (elect_one()) {
+        // 32 bytes of K per MMA either way: 32 e4m3 or 16 f16 / bf16 elements
+        if (p.in16) {
 #pragma unroll
-        for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
-          umma_f8(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
-                  bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+          for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
+            umma_f16(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+                     bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+        } else {
+#pragma unroll
+          for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
+            umma_f8(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+                    bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+        }
         umma_commit(&empty_bar[stage]);
       }
       __syncwarp();
@@ -223,14 +233,15 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
       const bool ok = tok >= 0 && tok < p.num_valid_tokens;
       s_rowscale[i] = (ok && p.topk_weights) ? p.topk_weights[tok] : 1.f;
       s_rowscale[kMoeMaxBlockM + i] =
-          p.a_per_token ? (ok ? p.a_scales[tok / p.top_k] : 0.f) : p.a_scales[0];
+          p.a_scales == nullptr ? 1.f : (p.a_per_token ? (ok ? p.a_scales[tok / p.top_k] : 0.f) : p.a_scales[0]);
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
     const int nl = q * 32 + lane;
     const int n = n0 + nl;
     const bool n_ok = n < p.N;
-    const float bsc = p.b_per_channel ? (n_ok ? p.b_scales[(int64_t)expert * p.N + n] : 0.f)
-                                      : p.b_scales[expert];
+    const float bsc = p.b_scales == nullptr ? 1.f
+                                            : (p.b_per_channel ? (n_ok ? p.b_scales[(int64_t)expert * p.N + n] : 0.f)
+                                                               : p.b_scales[expert]);
     const bool mul_w = p.topk_weights != nullptr;
     mbar_wait(acc_bar, 0);
     tc_fence_after();
@@ -395,7 +406,69 @@ extern "C" int vb200_moe_grouped_gemm_fp8(
   p.expert_offsets = nullptr;
   p.problem_sizes = nullptr;
   p.ragged = 0;
+  p.in16 = 0;
   return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
+}
+
+// Unquantised (f16 / bf16) experts: the bf16-weights variant of fused_experts (fused_moe.py:1349-1563 with
+// use_fp8_w8a8 = False; reference test tests/kernels/moe/test_moe.py:117-233).  Same kernel -- tiles, TMA boxes and the
+// pipeline are sized in bytes -- with kind::f16 MMAs and no scales:
+//   C[token_id, n] = OutT( (sum_k A[token_id / top_k, k] * B[e, n, k]) * [topk_weights[token_id]] ),   fp32 accumulate.
+// a [num_a_rows, K], b [E, N, K] of `dtype` (F16 / BF16), K % 8 == 0; c [num_valid_tokens, N] of the same dtype.
+// workspace: vb200_moe_grouped_gemm_workspace_size(sorted_capacity, 2 * K) bytes.
+extern "C" int vb200_moe_grouped_gemm_16(
+    void* c, const void* a, const void* b, const float* topk_weights, const int32_t* sorted_token_ids,
+    const int32_t* expert_ids, const int32_t* num_tokens_post_pad, int num_valid_tokens, int num_a_rows, int top_k, int E,
+    int N, int K, int block_m, int sorted_capacity, int mul_routed_weight, int dtype, void* workspace,
+    size_t workspace_bytes, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(dtype == VB200_BF16 || dtype == VB200_F16, "moe_grouped_gemm_16: dtype must be bf16 or f16");
+  VB_CHECK(K > 0 && K % 8 == 0, "moe_grouped_gemm_16: K (%d) must be a positive multiple of 8", K);
+  VB_CHECK(block_m >= 16 && block_m <= kMoeMaxBlockM && block_m % 16 == 0,
+           "moe_grouped_gemm_16: block_m (%d) must be a multiple of 16 in [16, 256]", block_m);
+  VB_CHECK(top_k >= 1 && E >= 1 && N >= 1, "moe_grouped_gemm_16: bad top_k / E / N");
+  VB_CHECK(!mul_routed_weight || topk_weights != nullptr, "moe_grouped_gemm_16: mul_routed_weight needs topk_weights");
+  (void)num_a_rows;
+  if (num_valid_tokens <= 0 || sorted_capacity <= 0) return 0;
+  const int kb = 2 * K;   // bytes per row
+  const size_t need = vb200_moe_grouped_gemm_workspace_size(sorted_capacity, kb);
+  VB_CHECK(workspace != nullptr && workspace_bytes >= need, "moe_grouped_gemm_16: workspace too small (%zu < %zu)",
+           workspace_bytes, need);
+  uint8_t* a_sorted = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~static_cast<uintptr_t>(255));
+  VB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0,
+           "moe_grouped_gemm_16: A and B must be 16-byte aligned");
+  {
+    int grid = sorted_capacity < num_sms() * 8 ? sorted_capacity : num_sms() * 8;
+    VB_CUDA_CHECK(launch_k(moe_gather_rows_kernel, dim3(grid), dim3(kb >= 4096 ? 256 : 128), 0, stream, a_sorted,
+                           reinterpret_cast<const uint8_t*>(a), sorted_token_ids, num_tokens_post_pad, num_valid_tokens,
+                           top_k, kb, sorted_capacity));
+    VB_LAUNCH_CHECK();
+  }
+  const int m_blocks = (sorted_capacity + block_m - 1) / block_m;
+  CUtensorMap tw, ta;
+  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)kb, (uint64_t)kb, kMoeBlockN)) return 1;
+  if (tc::make_tmap_2d_u8(&ta, a_sorted, (uint64_t)m_blocks * block_m, (uint64_t)kb, (uint64_t)kb, (uint32_t)block_m)) return 1;
+  MoeParams p;
+  p.c = c;
+  p.a_scales = nullptr;
+  p.b_scales = nullptr;
+  p.topk_weights = mul_routed_weight ? topk_weights : nullptr;
+  p.sorted_token_ids = sorted_token_ids;
+  p.expert_ids = expert_ids;
+  p.num_tokens_post_pad = num_tokens_post_pad;
+  p.num_valid_tokens = num_valid_tokens;
+  p.top_k = top_k;
+  p.E = E;
+  p.N = N;
+  p.K = kb;
+  p.block_m = block_m;
+  p.a_per_token = 0;
+  p.b_per_channel = 0;
+  p.expert_offsets = nullptr;
+  p.problem_sizes = nullptr;
+  p.ragged = 0;
+  p.in16 = dtype == VB200_BF16 ? 2 : 1;
+  return launch_moe_gemm(p, tw, ta, m_blocks, dtype, stream);
 }
 
 
@@ -449,5 +522,6 @@ extern "C" int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, con
   p.expert_offsets = expert_offsets;
   p.problem_sizes = problem_sizes;
   p.ragged = 1;
+  p.in16 = 0;
   return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
 }

@@ -1,8 +1,9 @@
 """Mirror of the decode-relevant part of /root/reference/vllm/model_executor/layers/fused_moe/fused_moe.py:
 fused_topk (:882-915), invoke_fused_moe_kernel (:478-647, the Triton kernel :267-475 replaced by the tcgen05
 grouped GEMM), fused_experts / fused_experts_impl (:1253-1346, :1349-1563), fused_moe (:1566-1670).
-FP8 w8a8 experts only (per-tensor or per-channel weight scales; static / dynamic per-tensor / per-token
-activation scales): that is what BASELINE config 4 (Mixtral-8x7B FP8) runs."""
+FP8 w8a8 experts (per-tensor or per-channel weight scales; static / dynamic per-tensor / per-token activation scales:
+what BASELINE config 4, Mixtral-8x7B FP8, runs) and unquantised f16 / bf16 experts (SURVEY 8d's bf16-weights variant,
+tests/kernels/moe/test_moe.py:117-233) on the same tcgen05 grouped GEMM."""
 from typing import Optional
 
 import torch
@@ -55,13 +56,24 @@ def invoke_fused_moe_kernel(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, A
                             block_m: int, use_fp8_w8a8: bool = True, per_channel_quant: bool = False) -> None:
     """fused_moe.py:478-647.  A fp8 [rows, K] (row = token_id // top_k); B fp8 [E, N, K]; C [num_pairs, N]
     (any leading shape, contiguous); A_scale [1] or [rows, 1]; B_scale [E] or [E, N(,1)]."""
-    if not use_fp8_w8a8 or A.dtype != FP8 or B.dtype != FP8:
-        raise RuntimeError("invoke_fused_moe_kernel: only the fp8 w8a8 grouped GEMM is built")
     assert sorted_token_ids.stride(0) == 1 and B.stride(-1) == 1 and A.stride(-1) == 1
     assert A.is_contiguous() and B.is_contiguous() and C.is_contiguous()
     E, N, K = B.shape
     num_pairs = C.numel() // N
     lib = load()
+    if not use_fp8_w8a8:
+        # unquantised experts: f16 / bf16 operands, no scales (fused_moe.py:1349-1563 with every use_* flag off)
+        if A.dtype not in (torch.float16, torch.bfloat16) or B.dtype != A.dtype or C.dtype != A.dtype:
+            raise RuntimeError("invoke_fused_moe_kernel: unquantised experts need f16 / bf16 A, B and C of one dtype")
+        ws_bytes = lib.vb200_moe_grouped_gemm_workspace_size(sorted_token_ids.numel(), 2 * K)
+        ws = _moe_workspace(A.device, ws_bytes)
+        check(lib.vb200_moe_grouped_gemm_16(
+            ptr(C), ptr(A), ptr(B), ptr(topk_weights) if mul_routed_weight else None, ptr(sorted_token_ids),
+            ptr(expert_ids), ptr(num_tokens_post_padded), num_pairs, A.shape[0], top_k, E, N, K, block_m,
+            sorted_token_ids.numel(), int(bool(mul_routed_weight)), dtype_enum(A.dtype), ptr(ws), ws.numel(), stream()))
+        return
+    if A.dtype != FP8 or B.dtype != FP8:
+        raise RuntimeError("invoke_fused_moe_kernel: use_fp8_w8a8 needs float8_e4m3fn A and B")
     ws_bytes = lib.vb200_moe_grouped_gemm_workspace_size(sorted_token_ids.numel(), K)
     ws = _moe_workspace(A.device, ws_bytes)
     a_per_token = 1 if A_scale.numel() > 1 else 0
@@ -88,8 +100,8 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
     """fused_moe.py:1253-1346 / fused_experts_impl :1349-1563 for use_fp8_w8a8 (Mixtral FP8):
       quant(hidden) -> align -> GEMM1 [T, k, 2I] -> silu_and_mul -> quant -> GEMM2 (x routed weight) [T, k, H]
       -> moe_sum.  w1 [E, 2I, H], w2 [E, H, I] fp8 with K contiguous."""
-    if not use_fp8_w8a8 or use_int8_w8a8 or use_int8_w8a16 or use_int4_w4a16 or use_mxfp4_w4a4:
-        raise RuntimeError("fused_experts: only use_fp8_w8a8=True is built in vllm_b200")
+    if use_int8_w8a8 or use_int8_w8a16 or use_int4_w4a16 or use_mxfp4_w4a4:
+        raise RuntimeError("fused_experts: fp8 w8a8 and unquantised f16 / bf16 experts are built in vllm_b200")
     if activation != "silu" or not is_act_and_mul or apply_router_weight_on_input or block_shape is not None:
         raise RuntimeError("fused_experts: only silu-and-mul experts with per-tensor / per-channel scales are built")
     assert hidden_states.size(1) == w1.size(2), f"Hidden size mismatch {hidden_states.size(1)} != {w1.size(2)}"
@@ -97,7 +109,7 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
     assert hidden_states.is_contiguous(), "Hidden_states must be contiguous"
     assert w1.stride(-1) == 1 and w2.stride(-1) == 1, "Stride of last dimension must be 1"
     assert hidden_states.dtype in (torch.float16, torch.bfloat16)
-    assert w1_scale is not None and w2_scale is not None
+    assert not use_fp8_w8a8 or (w1_scale is not None and w2_scale is not None)
     T, H = hidden_states.shape
     E, N, _ = w1.shape
     if global_num_experts == -1:
@@ -106,12 +118,25 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
     dev, dt = hidden_states.device, hidden_states.dtype
     if topk_ids.dtype != torch.int32:
         topk_ids = topk_ids.to(torch.int32)
-    # activation quant: per-token when per_channel_quant, static when a scale is given, else dynamic per-tensor
-    # (moe_kernel_quantize_input, fused_moe/utils.py)
-    a1q, a1s = ops.scaled_fp8_quant(hidden_states, a1_scale, use_per_token_if_dynamic=per_channel_quant)
     block_m = get_block_m(T * k, global_num_experts)
     sorted_ids, expert_ids, num_post = moe_align_block_size(topk_ids, block_m, global_num_experts, expert_map)
     cache1 = torch.empty((T, k, N), device=dev, dtype=dt)
+    if not use_fp8_w8a8:
+        # unquantised experts: GEMM 1 -> silu_and_mul -> GEMM 2 (x routed weight) -> moe_sum, all in the activation dtype
+        assert w1.dtype == dt and w2.dtype == dt, "unquantised experts must have the activation dtype"
+        invoke_fused_moe_kernel(hidden_states, w1, cache1, None, None, None, sorted_ids, expert_ids, num_post, False, k,
+                                block_m, False)
+        cache2 = torch.empty((T * k, N // 2), device=dev, dtype=dt)
+        ops.silu_and_mul(cache2, cache1.view(T * k, N))
+        cache3 = torch.empty((T, k, w2.shape[1]), device=dev, dtype=dt)
+        invoke_fused_moe_kernel(cache2, w2, cache3, None, None, topk_weights.contiguous(), sorted_ids, expert_ids,
+                                num_post, True, 1, block_m, False)
+        out = hidden_states if inplace else torch.empty_like(hidden_states)
+        ops.moe_sum(cache3, out)
+        return out
+    # activation quant: per-token when per_channel_quant, static when a scale is given, else dynamic per-tensor
+    # (moe_kernel_quantize_input, fused_moe/utils.py)
+    a1q, a1s = ops.scaled_fp8_quant(hidden_states, a1_scale, use_per_token_if_dynamic=per_channel_quant)
     invoke_fused_moe_kernel(a1q, w1, cache1, a1s, w1_scale, None, sorted_ids, expert_ids, num_post, False, k,
                             block_m, True, per_channel_quant)
     if per_channel_quant and a2_scale is None:
