@@ -164,3 +164,64 @@ def test_grouped_gemm_16_rejects_mixed_dtypes():
     c = torch.zeros(4, 2, 128, dtype=torch.bfloat16, device=DEV)
     with pytest.raises(RuntimeError):
         invoke_fused_moe_kernel(a, b, c, None, None, None, s, e, n, False, 2, 16, False)
+
+
+@pytest.mark.parametrize("quant", ["fp8", "bf16"])
+@pytest.mark.parametrize("mode", ["single", "tp2", "ep2"])
+def test_fused_moe_layer(quant, mode):
+    """FusedMoE.forward_impl + Fp8MoEMethod.apply / UnquantizedFusedMoEMethod (layer.py:611-1533, fp8.py:918-1010):
+    the layer equals fused_experts on its weights; two tensor-parallel (intermediate split) or expert-parallel
+    (expert_map) halves, built as the ranks of a TP-2 group would build them, sum to the unsharded layer."""
+    from vllm_b200.distributed import communication_op as co
+    from vllm_b200.fused_moe import fused_experts, fused_topk
+    from vllm_b200.fused_moe.layer import Fp8MoEMethod, FusedMoE
+    seed_all(17)
+    T, E, k, H, I = 48, 8, 2, 256, 512
+    dt = torch.bfloat16
+    x = (torch.randn(T, H) / 4).to(dt).to(DEV)
+    logits = torch.randn(T, E).to(dt).to(DEV)
+    if quant == "fp8":
+        w13, s13 = _fp8_weights(E, 2 * I, H, False)
+        w2, s2 = _fp8_weights(E, H, I, False)
+    else:
+        w13, s13 = (torch.randn(E, 2 * I, H) / 10).to(dt), None
+        w2, s2 = (torch.randn(E, H, I) / 10).to(dt), None
+    tw, ids, _ = fused_topk(x, logits, k, True)
+    kw = dict(use_fp8_w8a8=True, w1_scale=s13.to(DEV), w2_scale=s2.to(DEV)) if quant == "fp8" else {}
+    want = fused_experts(x, w13.to(DEV), w2.to(DEV), tw, ids, **kw)
+
+    def build(world, rank, ep):
+        saved = (co._TP_WORLD, co._TP_RANK)
+        co._TP_WORLD, co._TP_RANK = world, rank
+        try:
+            layer = FusedMoE(E, k, H, I, params_dtype=dt, reduce_results=False, renormalize=True,
+                             quant_method=Fp8MoEMethod() if quant == "fp8" else None, ep_size=world if ep else None)
+        finally:
+            co._TP_WORLD, co._TP_RANK = saved
+        layer = layer.to(DEV)
+        if ep:
+            e0 = rank * (E // world)
+            sl_e, i0, i1 = slice(e0, e0 + E // world), 0, I
+        else:
+            per = I // world
+            sl_e, i0, i1 = slice(0, E), rank * per, (rank + 1) * per
+        assert layer.w13_weight.shape == (sl_e.stop - sl_e.start, 2 * (i1 - i0), H)
+        layer.w13_weight.data.copy_(torch.cat([w13[sl_e, i0:i1], w13[sl_e, I + i0:I + i1]], dim=1).to(DEV))
+        layer.w2_weight.data.copy_(w2[sl_e, :, i0:i1].to(DEV))
+        if quant == "fp8":
+            layer.w13_weight_scale.data.copy_(s13[sl_e].to(DEV))
+            layer.w2_weight_scale.data.copy_(s2[sl_e].to(DEV))
+        layer.quant_method.process_weights_after_loading(layer)
+        return layer
+
+    if mode == "single":
+        got = build(1, 0, False)(x, logits)
+        assert torch.equal(got, want)
+        return
+    parts = [build(2, r, mode == "ep2")(x, logits).float() for r in range(2)]
+    got = parts[0] + parts[1]
+    scale = max(want.float().abs().max().item(), 1.0)
+    # ep2: each (token, expert) pair is computed by exactly one rank with the same arithmetic -> only the final bf16
+    # sums differ; tp2 (fp8): the second quantisation sees half of the intermediate row, so its per-tensor scale differs
+    torch.testing.assert_close(got, want.float(), rtol=2e-2, atol=2e-2 * scale)
+    assert (got - want.float()).abs().mean().item() <= 4e-3 * scale
