@@ -56,14 +56,16 @@ def peaks():
 
 def kernel_traffic(config, world):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel from the committed
-    `ncu --set full` capture of this command (profiles/r01_kernel_traffic.json); None when no capture exists for
+    `ncu --set full` capture of this command (profiles/r02_kernel_traffic.json); None when no capture exists for
     the configuration (ncu cannot run inside a timed bench)."""
     if world != 1:
         return None
-    try:
-        return json.load(open(os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")))[config]["traffic"]
-    except Exception:
-        return None
+    for name in ("r02_kernel_traffic.json", "r01_kernel_traffic.json"):   # newest capture first
+        try:
+            return json.load(open(os.path.join(ROOT, "profiles", name)))[config]["traffic"]
+        except Exception:
+            continue
+    return None
 
 
 # ---------------------------------------------------------------------------------------------------
