@@ -53,14 +53,9 @@ def main():
                         res[f"mt{mt}_s{S}"] = None
                         torch.cuda.synchronize()
             hook(0, 0, 0, 0, 0, None)
-            if plan[6]:   # the planner's choice is stream-K: time it, and the same plan with whole tiles per pair
-                res["planner_streamk"] = round(timeit(lambda i: ops.cutlass_scaled_mm(x, ws[i % npool].t(), sa, sb, torch.bfloat16), 30) * 1e6, 1)
-                hook(-1, 0, 0, 0, 0, None)
-                res["planner_whole_tiles"] = round(timeit(lambda i: ops.cutlass_scaled_mm(x, ws[i % npool].t(), sa, sb, torch.bfloat16), 30) * 1e6, 1)
-                hook(0, 0, 0, 0, 0, None)
             ok = {k: v for k, v in res.items() if v is not None}
             best = min(ok, key=ok.get) if ok else None
-            ck = "planner_streamk" if plan[6] else f"mt{chosen[0]}_s{chosen[1]}"
+            ck = f"mt{chosen[0]}_s{chosen[1]}"
             print(json.dumps({"shape": name, "M": M, "N": N, "K": K, "planner": ck, "planner_us": res.get(ck),
                               "best": best, "best_us": ok.get(best), "all_us": res}), flush=True)
 

@@ -241,12 +241,9 @@ int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scales, const v
  * Requires K % 16 == 0 and N % 16 == 0 (vllm/_custom_ops.py:732-736).
  * The tcgen05/TMA kernel builds its TMA descriptors on the host per call (driver entry point
  * resolved at load time; no allocation, graph-capturable).  Split-K problems reduce their partial sums through
- * distributed shared memory inside a thread-block cluster and need no scratch.  `workspace`: only the stream-K plan
- * (more 256-row weight tiles than CTA pairs with a ragged last round, e.g. N = 28672) uses one:
- * vb200_cutlass_scaled_mm_workspace_size(M, N, K) bytes (0 = none needed) whose first 4 KiB must be ZERO on first
- * use; every launch leaves them zero.  ONE workspace per stream: launches that may run concurrently (different
- * streams, or a graph replay next to eager work) must not share it.  With workspace == NULL (or too small) the
- * kernel falls back to whole tiles per CTA pair -- same results, the last round runs partly empty. */
+ * distributed shared memory inside a thread-block cluster: the kernel needs NO scratch.  `workspace` /
+ * `workspace_bytes` are kept in the signature for ABI stability and ignored (pass NULL, 0);
+ * vb200_cutlass_scaled_mm_workspace_size() returns 0. */
 size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K);
 int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b, const float* a_scales,
                             const float* b_scales, const void* bias, int M, int N, int K,

@@ -387,26 +387,6 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     return bool(load().vb200_cutlass_scaled_mm_supports_fp8(int(cuda_device_capability)))
 
 
-_GEMM_WS = {}       # (device index, stream handle) -> zero-initialised workspace (stream-K flags + partial tiles)
-_GEMM_WS_KEEP = []  # superseded buffers stay alive: captured CUDA graphs may still point at them
-
-
-def _gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Scratch of the tcgen05 GEMM's stream-K plan (arrival flags + fp32 partial tiles; split-K itself reduces through
-    DSMEM and needs none).  The first 4 KiB (flags) must be zero on first use and are left zero by every launch, so a
-    buffer is allocated once with torch.zeros and only ever grown.  One workspace per (device, stream): launches on ONE stream are ordered, so they may share it;
-    launches on different streams (or a graph replay on a side stream next to eager work) get different buffers.
-    include/vllm_b200.h states the same rule for direct callers of the C ABI."""
-    key = (device.index, stream())
-    ws = _GEMM_WS.get(key)
-    if ws is None or ws.numel() < nbytes:
-        if ws is not None:
-            _GEMM_WS_KEEP.append(ws)
-        ws = torch.zeros(max(nbytes, 24 << 20), dtype=torch.uint8, device=device)
-        _GEMM_WS[key] = ws
-    return ws
-
-
 def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor,
                           scale_b: torch.Tensor, bias: Optional[torch.Tensor] = None) -> None:
     """torch.ops._C.cutlass_scaled_mm (csrc/torch_bindings.cpp:422-426) with the checks of
@@ -433,13 +413,11 @@ def cutlass_scaled_mm_out(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, s
     if bias is not None and (bias.numel() != n or not bias.is_contiguous() or bias.dtype != out.dtype):
         raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of the output dtype")
     with _device_of(a):
-        lib = load()
-        ws_bytes = lib.vb200_cutlass_scaled_mm_workspace_size(m, n, k)   # 0 unless the stream-K plan applies
-        ws = _gemm_workspace(a.device, ws_bytes) if ws_bytes else None
-        check(lib.vb200_cutlass_scaled_mm(
+        # no scratch: split-K reduces through distributed shared memory inside the kernel's clusters
+        check(load().vb200_cutlass_scaled_mm(
             ptr(out), ptr(a), ptr(b), ptr(scale_a), ptr(scale_b), ptr(bias), m, n, k, a.stride(0),
             b.stride(1), out.stride(0), scale_a.numel(), scale_b.numel(), dtype_enum(out.dtype),
-            ptr(ws), ws.numel() if ws is not None else 0, stream()))
+            None, 0, stream()))
 
 
 def cutlass_scaled_mm(a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor, scale_b: torch.Tensor,

@@ -26,12 +26,11 @@
 //     second cluster barrier publishes them, and every CTA reduces + writes 1/S of the token columns in slice order
 //     (deterministic).  No global workspace, no tickets, no spin-wait: the hardware co-schedules a cluster, so there
 //     is nothing to deadlock on and nothing shared between streams.
-//   * Stream-K when there are MORE tiles than pairs but not a whole number of rounds (gate_up: 112 tiles on 74
-//     pairs = 2 rounds at 76 % occupancy): the tiles' k-blocks are laid end to end and cut into one equal range per
-//     pair, so a tile that straddles a cut is accumulated by two pairs.  The pair that gets there first parks its
-//     fp32 partial in a workspace and raises a flag; the second one (an arrival counter decides who is who) adds it
-//     to its own accumulator and writes the tile.  The waiter only ever waits for a pair that has ALREADY arrived
-//     (bounded, deadlock-free in any schedule); a + b is order-independent, so the result is deterministic.
+//   * More tiles than pairs (gate_up: 112 tiles on 74 pairs): whole tiles round-robin, the second round partly empty.
+//     A stream-K variant (equal k-block ranges per pair, cut tiles fixed up through an L2 workspace) was built and
+//     measured: it paid off only while the issue loops were slow; after the warp-converged issue fix whole tiles win
+//     at every batch (gate_up, M = 16 / 64 / 128 / 256: 20.1 / 20.7 / 22.2 / 29.6 us whole tiles vs 22.4 / 24.4 / 26.7 /
+//     37.5 us stream-K, profiles/r02_scaled_mm_plan_sweep_s52.jsonl, _s36) and it was removed.
 //   * Programmatic dependent launch: barrier init, TMEM allocation, tensor-map prefetch AND the first ring-full of
 //     WEIGHT tiles (which no earlier kernel writes) are issued BEFORE griddepcontrol.wait, so they overlap the tail
 //     of whatever ran before; only the activation loads, the scale / bias reads and the stores wait.
@@ -88,9 +87,6 @@ struct Params {
   int num_kb;        // total k-blocks
   int col_chunk;     // split-K: token columns reduced + written by one slice (multiple of 16)
   uint32_t main_bytes;  // bytes of the stage ring (barriers follow)
-  int streamk;           // 1: pairs work on equal k-block ranges of the flattened (tile, k-block) space
-  uint32_t* sk_flags;    // stream-K: [cut][half]{arrival counter, flag}, zero between launches (self re-arming)
-  float* sk_partials;    // stream-K: [cut][half][tok_tile / 4][128 rows][4] fp32
   uint64_t hint_w, hint_a;
   unsigned long long* trace;  // debug: [grid][16] %globaltimer stamps (nullptr = off)
 };
@@ -134,32 +130,21 @@ __device__ __forceinline__ void store_chunk16(OutT* orow, int64_t ldc, const flo
 }
 
 // The work list of one pair (cluster): whole tiles cluster_id, cluster_id + num_clusters, ... restricted to the
-// pair's K slice [kb0, kb1) -- or, stream-K, the segments of its range [u0, u1) of the flattened (tile, k-block) space.
+// pair's K slice [kb0, kb1).
 struct SegIter {
   int state, end;
   __device__ __forceinline__ void init(const Params& p, int cluster_id, int num_clusters) {
-    if (p.streamk) {
-      const long long U = (long long)p.tiles * p.num_kb;
-      state = (int)((cluster_id * U) / num_clusters);
-      end = (int)(((cluster_id + 1) * U) / num_clusters);
-    } else {
-      state = cluster_id;
-      end = p.tiles;
-    }
+    (void)num_clusters;
+    state = cluster_id;
+    end = p.tiles;
   }
   __device__ __forceinline__ bool next(const Params& p, int num_clusters, int kb0, int kb1, int& tile, int& lo, int& hi) {
+    (void)p;
     if (state >= end) return false;
-    if (p.streamk) {
-      tile = state / p.num_kb;
-      lo = state - tile * p.num_kb;
-      hi = min(p.num_kb, lo + (end - state));
-      state += hi - lo;
-    } else {
-      tile = state;
-      lo = kb0;
-      hi = kb1;
-      state += num_clusters;
-    }
+    tile = state;
+    lo = kb0;
+    hi = kb1;
+    state += num_clusters;
     return true;
   }
 };
@@ -178,7 +163,6 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint64_t* acc_full = empty_bar + kMaxStages;  // [2] accumulator stage ready (both CTAs)
   uint64_t* acc_empty = acc_full + 2;           // [2] accumulator stage drained (leader's is used)
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 3);
-  uint32_t* sk_role = tmem_ptr + 1;   // stream-K: broadcast of the arrival order to the epilogue warps
   float* s_ascale = reinterpret_cast<float*>(tmem_ptr + 6);  // [2][256], 16-byte aligned (offset 256 past the ring)
 
   const int warp = threadIdx.x >> 5;
@@ -403,81 +387,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
                         ncols - c);
       };
-      const bool sk_partial = p.streamk && (seg_lo > 0 || seg_hi < p.num_kb);
-      if (sk_partial) {
-        // ---- stream-K: this pair holds only part of the tile's K range; the other part is one neighbour's ----
-        // cut index: the tail of a tile is shared with the previous pair, the head with the next one
-        const int cut = seg_lo > 0 ? cluster_id - 1 : cluster_id;
-        uint32_t* cnt = p.sk_flags + 2 * (cut * 2 + (int)rank);
-        uint32_t* flag = cnt + 1;
-        float4* part = reinterpret_cast<float4*>(p.sk_partials) +
-                       (size_t)(cut * 2 + (int)rank) * (size_t)(p.tok_tile >> 2) * kCtaRows + row;
-        if (tid_e == 0) *sk_role = atomicInc(cnt, 1u);   // 0: first of the two to get here, 1: second (counter wraps to 0)
-        named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
-        const uint32_t role = *sk_role;
-        const int tpc = (ncols + 15) >> 4;
-        uint32_t ra[16], rb[16];
-        if (role == 0) {
-          // first: park the fp32 partial ([col / 4][row][4], 512 contiguous bytes per warp store), then raise the flag
-          auto park16 = [&](const uint32_t* r, int jc) {
-            float4* dst = part + (size_t)(jc << 2) * kCtaRows;
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-              __stcg(dst + (size_t)jj * kCtaRows,
-                     make_float4(__uint_as_float(r[4 * jj]), __uint_as_float(r[4 * jj + 1]),
-                                 __uint_as_float(r[4 * jj + 2]), __uint_as_float(r[4 * jj + 3])));
-          };
-          tmem_ld_x16(taddr, ra);
-          for (int jc = 0; jc < tpc; jc += 2) {
-            tmem_ld_wait();
-            if (jc + 1 < tpc) tmem_ld_x16(taddr + ((jc + 1) << 4), rb);
-            park16(ra, jc);
-            if (jc + 1 < tpc) {
-              tmem_ld_wait();
-              if (jc + 2 < tpc) tmem_ld_x16(taddr + ((jc + 2) << 4), ra);
-              park16(rb, jc + 1);
-            }
-          }
-          __threadfence();
-          named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
-          if (tid_e == 0) st_release_gpu(flag, 1u);
-        } else {
-          // second: the first has arrived (it incremented the counter), so its flag is coming: bounded wait
-          if (tid_e == 0) {
-            while (ld_acquire_gpu(flag) == 0u) {
-            }
-            *flag = 0u;   // re-armed for the next launch (nobody touches this cut again in this one)
-          }
-          named_bar_sync(kEpiBarrier, 32 * kEpiWarps);
-          auto fix16 = [&](const uint32_t* r, int jc) {
-            float f[16];
-            const float4* src = part + (size_t)(jc << 2) * kCtaRows;
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              const float4 v = __ldcg(src + (size_t)jj * kCtaRows);
-              f[4 * jj] = __uint_as_float(r[4 * jj]) + v.x;
-              f[4 * jj + 1] = __uint_as_float(r[4 * jj + 1]) + v.y;
-              f[4 * jj + 2] = __uint_as_float(r[4 * jj + 2]) + v.z;
-              f[4 * jj + 3] = __uint_as_float(r[4 * jj + 3]) + v.w;
-            }
-            const int c = jc << 4;
-            if (n_ok)
-              store_chunk16(outp + (int64_t)(tok0 + c) * p.ldc + n, p.ldc, f, asc_u32 + 4 * c, bsc, biasf, has_bias,
-                            ncols - c);
-          };
-          tmem_ld_x16(taddr, ra);
-          for (int jc = 0; jc < tpc; jc += 2) {
-            tmem_ld_wait();
-            if (jc + 1 < tpc) tmem_ld_x16(taddr + ((jc + 1) << 4), rb);
-            fix16(ra, jc);
-            if (jc + 1 < tpc) {
-              tmem_ld_wait();
-              if (jc + 2 < tpc) tmem_ld_x16(taddr + ((jc + 2) << 4), ra);
-              fix16(rb, jc + 1);
-            }
-          }
-        }
-      } else if (p.splits == 1) {
+      if (p.splits == 1) {
         // tcgen05.ld is warp-collective (never under a per-lane predicate) and asynchronous: the load of the
         // next 32 columns is in flight while the current 32 are converted and stored
         uint32_t ra[32], rb[32];
@@ -610,29 +520,29 @@ static unsigned long long* g_trace = nullptr;  // set through vb200_debug_scaled
 
 struct Plan {
   int tok_tile, m_tiles, n_ptiles, tiles, stages, stage_bytes, splits, kb_per_split, num_kb, col_chunk, clusters;
-  int streamk;
-  size_t smem, main_bytes, ws_bytes;
+  size_t smem, main_bytes;
 };
-constexpr size_t kSkFlagBytes = 4096;   // head of the stream-K workspace: [cut][half]{counter, flag}
 
-// Cost model (microseconds) of one (token tiles, K splits) choice.  Constants are read off the per-phase traces
-// (benchmarks/trace_scaled_mm.py, profiles/r01_scaled_mm_trace_s18.txt / _s19.txt): an SM pulls ~85 GB/s from L2 and
-// all of them together ~11 TB/s (the L2 slice throughput cap), a pair retires one 256 x 256 x 128 k-block in 0.28 us,
-// HBM streams the weights at ~6.4 TB/s, the plain epilogue stores 256 token columns in ~2.6 us; the split-K exchange
-// adds two cluster barriers (~0.5 us each) and the partial columns pushed through DSMEM at about the L2 feed rate.
+// Cost model (microseconds) of one (token tiles, K splits) choice.  The constants are FITTED to the exhaustive plan
+// sweep (benchmarks/sweep_scaled_mm_plan.py -> profiles/r02_scaled_mm_plan_sweep_s52.jsonl: every placeable plan of the 8
+// decode shapes x M in {16, 64, 128, 256}); with them the planner's pick is within 1.3 % of the best measured plan on
+// average and within 12 % at worst.  What they stand for: an SM pulls ~100 GB/s through the L2 fabric in this kernel and
+// all of them together ~9 TB/s, a pair retires a 256 x 256 x 128 k-block in ~0.15 us, HBM streams the weights at
+// ~6.5 TB/s, the plain epilogue stores 256 token columns in ~1.5 us; a split adds two cluster barriers plus the
+// teardown (1.6 us) and the partial columns pushed through distributed shared memory at 21 B/clk per SM.
 static float plan_cost(int tok_tile, int m_tiles, int n_ptiles, int splits, int num_kb, int max_pairs, double w_bytes,
                        double a_bytes) {
   const int tiles = m_tiles * n_ptiles;
   const int kbps = ceil_div(num_kb, splits);
   const int rounds = ceil_div(tiles * splits, max_pairs);
-  const float feed = kbps * (kWTileBytes + tok_tile / 2 * kBlockK) / 85e3f;
-  const float mma = kbps * tok_tile * 0.0011f;
-  const float hbm = (float)(w_bytes / 6.4e6);
+  const float feed = kbps * (kWTileBytes + tok_tile / 2 * kBlockK) / 100e3f;
+  const float mma = kbps * tok_tile * 0.0006f;
+  const float hbm = (float)(w_bytes / 6.5e6);
   // bytes every SM pulls through the L2 fabric: the weights once per token tile, the activations once per row tile
-  const float fabric = (float)((w_bytes * m_tiles + a_bytes * n_ptiles) / 11e6);
+  const float fabric = (float)((w_bytes * m_tiles + a_bytes * n_ptiles) / 9e6);
   const float main_us = fmaxf(fmaxf(rounds * fmaxf(feed, mma), hbm), fabric);
-  float epi = 0.010f * tok_tile / splits;
-  if (splits > 1) epi += 1.0f + 0.006f * tok_tile * (splits - 1) / splits;
+  float epi = 0.006f * tok_tile / splits;
+  if (splits > 1) epi += 1.6f + 0.018f * tok_tile * (splits - 1) / splits;
   return main_us + epi;
 }
 
@@ -662,7 +572,7 @@ static Plan make_plan(int M, int N, int K) {
         if (max_clusters_cached(2 * s, (size_t)227 * 1024) < mt * g.n_ptiles) continue;   // cluster shape not placeable
       }
       const float c = plan_cost(tok, mt, g.n_ptiles, s, g.num_kb, max_pairs, w_bytes, a_bytes);
-      if (best < 0.f || c < best * (mt > mt_min ? 0.95f : 1.0f) - 1e-6f) {
+      if (best < 0.f || c < best - 1e-6f) {
         best = c;
         g.m_tiles = mt;
         g.splits = s;
@@ -685,22 +595,6 @@ static Plan make_plan(int M, int N, int K) {
     main_bytes = ((g.splits - 1) * region + 1023) / 1024 * 1024;
   g.main_bytes = main_bytes;
   g.smem = 1024 + main_bytes + tail;
-  // stream-K: more tiles than pairs and a ragged last round -- every pair takes ceil(U / P) k-blocks instead of
-  // `rounds` whole tiles.  Needs ranges of at least one tile (a tile is then cut at most once).
-  g.streamk = 0;
-  g.ws_bytes = 0;
-  if (g.splits == 1 && g.tiles > max_pairs) {
-    const int rounds = ceil_div(g.tiles, max_pairs);
-    const long long U = (long long)g.tiles * g.num_kb;
-    const long long per_pair = (U + max_pairs - 1) / max_pairs;
-    // ... and to token tiles of <= 128 columns: a cut tile's fp32 partial (tok_tile x 128 x 4 bytes per CTA) travels
-    // through L2 twice, which at 256 columns costs more than the ragged round it removes (gate_up, M = 256: 37.5 us
-    // stream-K vs 33.2 us whole tiles; M = 16: 24.4 vs 27.2; profiles/r02_scaled_mm_plan_sweep_s36.jsonl)
-    if (g.tok_tile <= 128 && per_pair >= g.num_kb && per_pair * 100 <= (long long)rounds * g.num_kb * 92) {
-      g.streamk = 1;
-      g.ws_bytes = kSkFlagBytes + (size_t)max_pairs * 2 * g.tok_tile * kCtaRows * 4;
-    }
-  }
   return g;
 }
 
@@ -766,17 +660,13 @@ static int launch(const Plan& g, const CUtensorMap& tw, const CUtensorMap& ta, c
 
 static int g_force_splits = 0;   // debug / tuning hook (vb200_debug_scaled_mm_plan): 0 = planner's choice
 static int g_force_mtiles = 0;
-static int g_no_streamk = 0;     // debug: 1 = whole tiles per pair even when stream-K applies
 
 static int run(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
                int a_scales_numel, int b_scales_numel, int out_dtype, void* workspace, size_t workspace_bytes,
                cudaStream_t stream) {
   Plan g = make_plan(M, N, K);
-  // stream-K parks partial tiles in the caller's workspace; without one (or with the debug switch) whole tiles
-  if (g.streamk && (g_no_streamk || workspace == nullptr || workspace_bytes < g.ws_bytes)) g.streamk = 0;
   if (g_force_splits > 0 || g_force_mtiles > 0) {
-    g.streamk = 0;
     // re-derive the plan for a forced (token tiles, K slices) pair -- same arithmetic as make_plan's tail
     if (g_force_mtiles > 0) g.m_tiles = g_force_mtiles;
     if (g_force_splits > 0) g.splits = g_force_splits;
@@ -824,9 +714,8 @@ static int run(void* out, const void* a, const void* b, const float* a_scales, c
   p.num_kb = g.num_kb;
   p.col_chunk = g.col_chunk;
   p.main_bytes = (uint32_t)g.main_bytes;
-  p.streamk = g.streamk;
-  p.sk_flags = reinterpret_cast<uint32_t*>(workspace);
-  p.sk_partials = g.streamk ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kSkFlagBytes) : nullptr;
+  (void)workspace;
+  (void)workspace_bytes;
   // weights are streamed once when there is a single token tile; otherwise they are re-read from L2
   p.hint_w = g.m_tiles == 1 ? kEvictFirst : kEvictNormal;
   p.hint_a = g.m_tiles == 1 ? kEvictLast : kEvictNormal;
@@ -852,7 +741,6 @@ extern "C" int vb200_cutlass_scaled_mm_supports_fp8(int cap) { return cap >= 100
 // following launches (0 = planner's choice); plan[0..5] (if non-NULL) receives the planner's choice for (M, N, K):
 // token tile, token tiles, K slices, cluster CTAs, clusters, pipeline stages, stream-K (plan[0..6]).
 extern "C" void vb200_debug_scaled_mm_plan(int force_splits, int force_mtiles, int M, int N, int K, int* plan) {
-  v2::g_no_streamk = force_splits < 0 ? 1 : 0;     // force_splits = -1: planner's choice, but no stream-K
   if (force_splits < 0) force_splits = 0;
   v2::g_force_splits = force_splits;
   v2::g_force_mtiles = force_mtiles;
@@ -864,16 +752,14 @@ extern "C" void vb200_debug_scaled_mm_plan(int force_splits, int force_mtiles, i
     plan[3] = 2 * g.splits;
     plan[4] = g.clusters;
     plan[5] = g.stages;
-    plan[6] = g.streamk;
+    plan[6] = 0;
   }
 }
 
-// Split-K reduces through distributed shared memory inside a cluster and needs no workspace; only the stream-K plan
-// (more tiles than CTA pairs, ragged last round) parks partial tiles in one.  0 = none needed.  The first 4 KiB must be
-// zero before the first launch (the kernel re-arms them); one workspace per stream.
+// Split-K reduces through distributed shared memory inside a cluster: the kernel needs no workspace (kept in the ABI).
 extern "C" size_t vb200_cutlass_scaled_mm_workspace_size(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
-  return v2::make_plan(M, N, K).ws_bytes;
+  return 0;
 }
 
 extern "C" int vb200_cutlass_scaled_mm(void* out, const void* a, const void* b,
