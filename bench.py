@@ -333,15 +333,27 @@ def gemm_rooflines(dec, batch, hbm_peak, hbm_src):
         def sweep():
             for l in layers:
                 ops.cutlass_scaled_mm_out(c, a, getattr(l, wattr).t(), a_s, getattr(l, sattr).view(1, -1))
-        sweep()
+        # one pass captured in a CUDA graph (as in the timed step): eager launches of a ~10 us kernel would time the
+        # host's launch path (ctypes + two tensor-map encodes, ~16 us per call), not the kernel
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            sweep()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            sweep()
+        g.replay()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(3):
-            sweep()
+            g.replay()
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / (3 * len(layers))
+        del g
         byts = N * K + batch * K + batch * N * 2 + 4 * (batch + N)
         flops = 2.0 * batch * N * K
         gbs, tfs = byts / us / 1e3, flops / us / 1e6
@@ -357,8 +369,8 @@ def gemm_rooflines(dec, batch, hbm_peak, hbm_src):
                     "flops_per_launch": flops, "traffic": None})
     return {"gemms": out, "sum_us_per_layer": round(sum(g["avg_launch_us"] for g in out), 2),
             "hbm_peak_source": hbm_src, "tensor_peak_source": tensor_src,
-            "how": "CUDA events around 3 passes of back-to-back launches over all layers' weights (PDL on, as in the "
-                   "captured step), per-launch average"}
+            "how": "CUDA events around 3 replays of one CUDA graph holding back-to-back launches over all layers' weights "
+                   "(PDL on, as in the captured step), per-launch average"}
 
 
 
