@@ -491,8 +491,6 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
 #pragma unroll
   for (int i = 0; i < PER; ++i) acc[i] = 0.f;
   for (int j = 0; j < np; ++j) {
-    // exp_sum == 0: a partition the persistent kernel folded into its run's first partial (its tmp_out row is unwritten)
-    if (es[j] == 0.f) continue;
     const float w = es[j] * __expf(ml[j] - mg) * inv;
 #pragma unroll
     for (int i = 0; i < PER; ++i) {

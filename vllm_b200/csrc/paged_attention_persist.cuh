@@ -7,21 +7,17 @@
 // (profiles/r01_paged_attention_cfg5_ncu_summary_s28.txt: 0.76 of the HBM peak).  Finer partitions even the load out but
 // every CTA pays its own fill / drain bubble (block table, barriers, first bytes ~2 us after the first copy is issued,
 // merge), which costs what the balance gains (profiles/r01_paged_attention_cfg5_partition_sweep_s29.txt).
-// Here the grid is exactly the resident slots (4 CTAs per SM) and every CTA owns a CONTIGUOUS range of the fixed-size
-// work items (sequence, kv-head group, 512-token partition), items ordered partition-fastest.  Consecutive items of a
-// range mostly belong to the same (sequence, head group): the consumer warps then simply keep their online-softmax
-// state running across them -- no merge, no query reload -- and write ONE partial for the whole run (at the run's first
-// partition index; the other indices of the run get exp_sum = 0 / max_logit = -inf, which the reduce kernel skips).
-// A CTA therefore merges and writes once or twice in its life instead of once per 512 tokens, the producer warp never
-// stops at item boundaries (the next item's sequence length and block ids are fetched while the current item's copies
-// are being issued), and per-SM work differs by at most one item.
+// Here the grid is exactly the resident slots (4 CTAs per SM) and every CTA walks a static round-robin list of
+// fixed-size work items (sequence, kv-head group, 512-token partition).  The producer warp does not stop at item
+// boundaries: while the consumer warps merge and write item i it is already streaming item i + 1 into the ring, so
+// there is one fill bubble per CTA instead of one per item, and per-SM work differs by at most one small item.
 //   * ring, barriers, fragment loads and math: identical to paged_attention_tma_kernel (same stage <-> consumer warp
 //     binding: global tile g of the CTA belongs to warp g % NWARPS and stage g % num_stages, num_stages % NWARPS == 0);
-//   * block ids: the producer warp loads the (<= 32) ids of an item with one coalesced load and hands them to the
-//     issuing lane by shuffle -- no shared-memory block table, nothing to synchronise with the consumers;
-//   * merge of the 4 warps' (m, l, O) through its own shared-memory area (the ring stays live), bracketed by a named
-//     barrier of the 128 consumer threads only;
-//   * outputs: the reference's v2 partial formats, then paged_attention_reduce_kernel.
+//   * block ids: the producer warp loads 32 at a time (one coalesced load per 512 tokens) and hands them to the issuing
+//     lane by shuffle -- no shared-memory block table, nothing to synchronise with the consumers;
+//   * per-item merge of the 4 warps' (m, l, O) through its own shared-memory area (the ring stays live), bracketed by a
+//     named barrier of the 128 consumer threads only;
+//   * outputs: the reference's v2 partial formats, then paged_attention_reduce_kernel -- unchanged.
 #pragma once
 
 namespace vb200 {
@@ -90,55 +86,39 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
     return ntok > 0 || (seq_len <= 0 && part_idx == 0);
   };
 
-  // contiguous item range of this CTA
-  const int item_lo = (int)(((long long)blockIdx.x * total_items) / gridDim.x);
-  const int item_hi = (int)(((long long)(blockIdx.x + 1) * total_items) / gridDim.x);
-
   if (warp == NWARPS) {
-    // ===== producer warp: all lanes fetch block ids, lane 0 issues two bulk copies per 16-token block.  The metadata
-    // of item i + 1 (sequence length, block ids) is loaded before item i's copies are issued, so its latency hides
-    // behind them (an item is <= 32 blocks: partition_size == 512) =====
+    // ===== producer warp: all lanes fetch block ids, lane 0 issues two bulk copies per 16-token block =====
     int stage = 0;
     uint32_t phase = 0;
-    const int64_t blk_stride_b = p.kv_block_stride * CE;
-    auto fetch = [&](int item, int& ntiles, int& kv_head, int& mine) {
-      ntiles = 0;
-      kv_head = 0;
-      mine = 0;
-      if (item >= item_hi) return;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
       int seq_idx, hg, part_idx, seq_len, tok_begin, ntok;
-      if (!decode(item, seq_idx, hg, part_idx, seq_len, tok_begin, ntok)) return;
-      ntiles = (ntok + 15) >> 4;
-      kv_head = hg / groups_per_kv;
-      const int* bt = p.block_tables + (int64_t)seq_idx * p.max_num_blocks_per_seq + (tok_begin >> 4);
-      mine = lane < ntiles ? bt[lane] : 0;
-    };
-    int ntiles, kv_head, mine;
-    fetch(item_lo, ntiles, kv_head, mine);
-    for (int item = item_lo; item < item_hi; ++item) {
-      int n_ntiles, n_kv_head, n_mine;
-      fetch(item + 1, n_ntiles, n_kv_head, n_mine);
+      if (!decode(item, seq_idx, hg, part_idx, seq_len, tok_begin, ntok)) continue;
+      const int ntiles = (ntok + 15) >> 4;
+      const int kv_head = hg / groups_per_kv;
       const unsigned char* kbase = reinterpret_cast<const unsigned char*>(p.k_cache) + (int64_t)kv_head * p.kv_head_stride * CE;
       const unsigned char* vbase = reinterpret_cast<const unsigned char*>(p.v_cache) + (int64_t)kv_head * p.kv_head_stride * CE;
-      for (int j = 0; j < ntiles; ++j) {
-        const int blk = __shfl_sync(0xffffffffu, mine, j);
-        if (lane == 0) {
-          pa_mbar_wait(&empty_bar[stage], phase ^ 1);
-          const int64_t off = (int64_t)blk * blk_stride_b;
-          unsigned char* dst = ring + stage * STAGE;
-          pa_mbar_expect_tx(&full_bar[stage], STAGE);
-          pa_bulk_load(dst, kbase + off, KBYTES, &full_bar[stage]);
-          pa_bulk_load(dst + KBYTES, vbase + off, KBYTES, &full_bar[stage]);
+      const int64_t blk_stride_b = p.kv_block_stride * CE;
+      const int* bt = p.block_tables + (int64_t)seq_idx * p.max_num_blocks_per_seq + (tok_begin >> 4);
+      for (int t0 = 0; t0 < ntiles; t0 += 32) {
+        const int mine = (t0 + lane < ntiles) ? bt[t0 + lane] : 0;
+        const int n = min(32, ntiles - t0);
+        for (int j = 0; j < n; ++j) {
+          const int blk = __shfl_sync(0xffffffffu, mine, j);
+          if (lane == 0) {
+            pa_mbar_wait(&empty_bar[stage], phase ^ 1);
+            const int64_t off = (int64_t)blk * blk_stride_b;
+            unsigned char* dst = ring + stage * STAGE;
+            pa_mbar_expect_tx(&full_bar[stage], STAGE);
+            pa_bulk_load(dst, kbase + off, KBYTES, &full_bar[stage]);
+            pa_bulk_load(dst + KBYTES, vbase + off, KBYTES, &full_bar[stage]);
+          }
+          if (++stage == num_stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
-        if (++stage == num_stages) {
-          stage = 0;
-          phase ^= 1u;
-        }
+        __syncwarp();
       }
-      __syncwarp();
-      ntiles = n_ntiles;
-      kv_head = n_kv_head;
-      mine = n_mine;
     }
     return;
   }
@@ -154,88 +134,18 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
   int stage = warp % num_stages;
   uint32_t phase = 0;
 
-  // state of the current run = consecutive items of one (sequence, head group)
-  int run_seq = -1, run_hg = -1, run_first = 0, run_last = 0, head0 = 0, nheads = 0;
-  uint32_t qf[NQK][2];
-  float alibi2[2] = {0.f, 0.f};
-  float o[NJ][4];
-  float m_run[2] = {-INFINITY, -INFINITY};
-  float l_run[2] = {0.f, 0.f};
-  const float sl2 = p.scale * kLog2e * k_scale;
-
-  // merge the NWARPS partial (m, l, O) of the finished run and write its partial / output (consumer threads only)
-  auto flush = [&]() {
-#pragma unroll
-    for (int off = 4; off < 32; off <<= 1) {
-      l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], off);
-      l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], off);
-    }
-    pa_named_bar(2, NWARPS * 32);   // the previous flush's reads of the merge area are over
-    if (r == 0) {
-      sm_m[warp * 8 + 2 * c] = m_run[0];
-      sm_m[warp * 8 + 2 * c + 1] = m_run[1];
-      sm_l[warp * 8 + 2 * c] = l_run[0];
-      sm_l[warp * 8 + 2 * c + 1] = l_run[1];
-    }
-    float* so = sm_o + warp * 8 * HEAD_SIZE;
-#pragma unroll
-    for (int j = 0; j < NJ; ++j) {
-      const int da = 16 * j + r, db = da + 8;
-      so[(2 * c) * HEAD_SIZE + da] = o[j][0];
-      so[(2 * c + 1) * HEAD_SIZE + da] = o[j][1];
-      so[(2 * c) * HEAD_SIZE + db] = o[j][2];
-      so[(2 * c + 1) * HEAD_SIZE + db] = o[j][3];
-    }
-    pa_named_bar(2, NWARPS * 32);
-    for (int idx = tid; idx < nheads * HEAD_SIZE; idx += NWARPS * 32) {
-      const int h = idx / HEAD_SIZE;
-      const int d = idx - h * HEAD_SIZE;
-      float mg = -INFINITY;
-#pragma unroll
-      for (int w = 0; w < NWARPS; ++w) mg = fmaxf(mg, sm_m[w * 8 + h]);
-      float lsum = 0.f, acc = 0.f;
-#pragma unroll
-      for (int w = 0; w < NWARPS; ++w) {
-        const float f = (sm_m[w * 8 + h] == -INFINITY) ? 0.f : fast_exp2(sm_m[w * 8 + h] - mg);
-        lsum = fmaf(sm_l[w * 8 + h], f, lsum);
-        acc = fmaf(sm_o[(w * 8 + h) * HEAD_SIZE + d], f, acc);
-      }
-      const float res = acc * v_scale * __fdividef(1.f, lsum + 1e-6f);
-      const int head = head0 + h;
-      if (partitioned) {
-        const int64_t o2 = ((int64_t)run_seq * p.num_heads + head) * P + run_first;
-        reinterpret_cast<QT*>(p.tmp_out)[o2 * HEAD_SIZE + d] = from_float<QT>(res);
-        if (d == 0) {
-          p.exp_sums[o2] = lsum;
-          p.max_logits[o2] = mg * kLn2;
-        }
-        // the other partitions of the run are folded into this partial: mark them empty for the reduce kernel
-        for (int e = d; e <= run_last - run_first; e += HEAD_SIZE) {
-          if (e > 0) {
-            p.exp_sums[o2 + e] = 0.f;
-            p.max_logits[o2 + e] = -INFINITY;
-          }
-        }
-      } else {
-        reinterpret_cast<QT*>(p.out)[((int64_t)run_seq * p.num_heads + head) * HEAD_SIZE + d] = from_float<QT>(res);
-      }
-    }
-  };
-
-  for (int item = item_lo; item < item_hi; ++item) {
+  for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
     int seq_idx, hg, part_idx, seq_len, tok_begin, ntok;
     if (!decode(item, seq_idx, hg, part_idx, seq_len, tok_begin, ntok)) continue;
     const int ntiles = (ntok + 15) >> 4;
-    if (seq_idx != run_seq || hg != run_hg) {
-      if (run_seq >= 0) flush();
-      run_seq = seq_idx;
-      run_hg = hg;
-      run_first = part_idx;
-      const int kv_head = hg / groups_per_kv;
-      const int hgroup = hg - kv_head * groups_per_kv;
-      head0 = kv_head * num_q_per_kv + hgroup * 8;
-      nheads = min(8, num_q_per_kv - hgroup * 8);
-      // query fragments (B operand of QK^T), as in paged_attention_tma_kernel
+    const int kv_head = hg / groups_per_kv;
+    const int hgroup = hg - kv_head * groups_per_kv;
+    const int head0 = kv_head * num_q_per_kv + hgroup * 8;
+    const int nheads = min(8, num_q_per_kv - hgroup * 8);
+
+    // query fragments (B operand of QK^T), as in paged_attention_tma_kernel
+    uint32_t qf[NQK][2];
+    {
       const QT* qp = reinterpret_cast<const QT*>(p.q) + (int64_t)seq_idx * p.q_stride + (int64_t)(head0 + r) * HEAD_SIZE;
       const bool hvalid = r < nheads;
 #pragma unroll
@@ -260,18 +170,19 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
         qf[i][0] = w0;
         qf[i][1] = w1;
       }
-      alibi2[0] = alibi2[1] = 0.f;
-      if (p.alibi_slopes != nullptr) {
-#pragma unroll
-        for (int h = 0; h < 2; ++h)
-          if (2 * c + h < nheads) alibi2[h] = p.alibi_slopes[head0 + 2 * c + h] * kLog2e;
-      }
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
-      m_run[0] = m_run[1] = -INFINITY;
-      l_run[0] = l_run[1] = 0.f;
     }
-    run_last = part_idx;
+    const float sl2 = p.scale * kLog2e * k_scale;
+    float alibi2[2] = {0.f, 0.f};
+    if (p.alibi_slopes != nullptr) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        if (2 * c + h < nheads) alibi2[h] = p.alibi_slopes[head0 + 2 * c + h] * kLog2e;
+    }
+    float o[NJ][4];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY};
+    float l_run[2] = {0.f, 0.f};
 
     const uint32_t g_end = g + (uint32_t)ntiles;
     for (; my_g < g_end; my_g += NWARPS) {
@@ -318,7 +229,6 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
       }
       const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
-      // (mn can stay -inf only if every row of the tile is masked, which a tile with >= 1 valid token never is)
       const float corr0 = fast_exp2(m_run[0] - mn0), corr1 = fast_exp2(m_run[1] - mn1);
       m_run[0] = mn0;
       m_run[1] = mn1;
@@ -371,8 +281,57 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
       }
     }
     g = g_end;
+
+    // ---- per-item merge of the NWARPS partial (m, l, O) and write-out (consumer threads only) ----
+#pragma unroll
+    for (int off = 4; off < 32; off <<= 1) {
+      l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], off);
+      l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], off);
+    }
+    pa_named_bar(2, NWARPS * 32);   // the previous item's merge reads are over
+    if (r == 0) {
+      sm_m[warp * 8 + 2 * c] = m_run[0];
+      sm_m[warp * 8 + 2 * c + 1] = m_run[1];
+      sm_l[warp * 8 + 2 * c] = l_run[0];
+      sm_l[warp * 8 + 2 * c + 1] = l_run[1];
+    }
+    float* so = sm_o + warp * 8 * HEAD_SIZE;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int da = 16 * j + r, db = da + 8;
+      so[(2 * c) * HEAD_SIZE + da] = o[j][0];
+      so[(2 * c + 1) * HEAD_SIZE + da] = o[j][1];
+      so[(2 * c) * HEAD_SIZE + db] = o[j][2];
+      so[(2 * c + 1) * HEAD_SIZE + db] = o[j][3];
+    }
+    pa_named_bar(2, NWARPS * 32);
+    for (int idx = tid; idx < nheads * HEAD_SIZE; idx += NWARPS * 32) {
+      const int h = idx / HEAD_SIZE;
+      const int d = idx - h * HEAD_SIZE;
+      float mg = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < NWARPS; ++w) mg = fmaxf(mg, sm_m[w * 8 + h]);
+      float lsum = 0.f, acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < NWARPS; ++w) {
+        const float f = (sm_m[w * 8 + h] == -INFINITY) ? 0.f : fast_exp2(sm_m[w * 8 + h] - mg);
+        lsum = fmaf(sm_l[w * 8 + h], f, lsum);
+        acc = fmaf(sm_o[(w * 8 + h) * HEAD_SIZE + d], f, acc);
+      }
+      const float res = acc * v_scale * __fdividef(1.f, lsum + 1e-6f);
+      const int head = head0 + h;
+      if (partitioned) {
+        const int64_t o2 = ((int64_t)seq_idx * p.num_heads + head) * P + part_idx;
+        reinterpret_cast<QT*>(p.tmp_out)[o2 * HEAD_SIZE + d] = from_float<QT>(res);
+        if (d == 0) {
+          p.exp_sums[o2] = lsum;
+          p.max_logits[o2] = mg * kLn2;
+        }
+      } else {
+        reinterpret_cast<QT*>(p.out)[((int64_t)seq_idx * p.num_heads + head) * HEAD_SIZE + d] = from_float<QT>(res);
+      }
+    }
   }
-  if (run_seq >= 0) flush();
 }
 
 template <int HEAD_SIZE, int NWARPS>
