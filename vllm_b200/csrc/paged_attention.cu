@@ -45,7 +45,6 @@ struct PagedAttnParams {
   int64_t q_stride, kv_block_stride, kv_head_stride;
   float scale;
   int prefetch_dist;  // tiles (per warp) ahead of the register double buffer that are pulled into L2; 0 = off
-  int persist = 0;    // host only: run the persistent kernel (paged_attention_persist.cuh) on this launch
 };
 
 template <typename T>
@@ -508,7 +507,6 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
 }  // namespace vb200
 #include "paged_attention_tma.cuh"
 #include "paged_attention_flash.cuh"
-#include "paged_attention_persist.cuh"
 namespace vb200 {
 
 constexpr int kWarps = 4;
@@ -543,47 +541,10 @@ static inline int pa_tma_stages(int cache_elem_bytes, int partition_tokens) {
   return st;
 }
 
-// persistent kernel: VB200_PA_PERSIST = 0 never, 1 whenever it applies (tests), unset = the wave-fill heuristic below
-static int pa_persist_mode() {
-  static int v = -2;
-  if (v == -2) {
-    const char* e = getenv("VB200_PA_PERSIST");
-    v = e ? (e[0] == '0' ? 0 : 1) : -1;
-  }
-  return v;
-}
-constexpr int kPaPersistPartition = 512;   // tokens per work item of the persistent kernel
-
 template <typename QT, bool FP8, int HEAD_SIZE, int BLOCK_SIZE>
 static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
                      cudaStream_t stream) {
   const int q_per_kv_ = p.num_heads / p.num_kv_heads;
-  if (BLOCK_SIZE == 16 && HEAD_SIZE % 16 == 0 && pa_use_tma() && p.persist) {
-    constexpr int HS = HEAD_SIZE % 16 == 0 ? HEAD_SIZE : 128;
-    constexpr int kCtas = HS <= 128 ? 4 : 2;
-    auto kp = paged_attention_persist_kernel<QT, FP8, HS, kWarps, kCtas>;
-    const int ce = FP8 ? 1 : 2;
-    const size_t per_cta = (size_t)(227 * 1024) / kCtas - 1024;
-    int stages = kPaMaxStages;
-    while (stages > kWarps && pa_persist_smem_bytes<HS, kWarps>(stages, ce) > per_cta) stages -= kWarps;
-    const size_t smem_p = pa_persist_smem_bytes<HS, kWarps>(stages, ce);
-    VB_CHECK(smem_p <= 227 * 1024, "paged attention (persistent): head size %d needs too much shared memory", HEAD_SIZE);
-    if (smem_p > 48 * 1024)
-      VB_CUDA_CHECK(cudaFuncSetAttribute(kp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-    const long items = (long)num_seqs * p.num_kv_heads * ((q_per_kv_ + 7) / 8) * num_partitions;
-    const long slots = (long)num_sms() * kCtas;
-    const int grid_p = (int)(items < slots ? items : slots);
-    VB_CUDA_CHECK(launch_k(kp, dim3(grid_p), dim3((kWarps + 1) * 32), smem_p, stream, p, stages, (int)items));
-    VB_LAUNCH_CHECK();
-    if (p.max_num_partitions > 1 || p.force_partials) {
-      const int rows = num_seqs * p.num_heads;
-      VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream,
-                             (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-                             p.max_num_partitions, p.partition_size, rows));
-      VB_LAUNCH_CHECK();
-    }
-    return 0;
-  }
   if (BLOCK_SIZE == 16 && HEAD_SIZE % 16 == 0 && pa_use_tma()) {
     constexpr int HS = HEAD_SIZE % 16 == 0 ? HEAD_SIZE : 128;  // (only instantiated for multiples of 16)
     auto kt = paged_attention_tma_kernel<QT, FP8, HS, kWarps, (HS <= 128 ? 4 : 2)>;
@@ -805,15 +766,13 @@ static inline int pa_ctas_per_sm(int head_size, int kv_dtype) {
   return head_size <= 128 ? (kv_dtype == VB200_KV_FP8_E4M3 ? 3 : 2) : 1;
 }
 
-// Split-K plan of paged_attention_v1: tokens per partition, and whether the persistent kernel takes the launch.
-// Cost model of the one-CTA-per-partition kernel: time ~ waves(np) * (tokens per partition + fixed per-CTA overhead),
-// where a wave is num_sms x resident CTAs; it picks the np (not only powers of two) that fills whole waves, no split
-// when the unsplit grid already covers the machine.  When even the best such grid leaves its last wave < 92 % full
-// (config 5: 512 CTAs on 592 slots) and there are enough 512-token items to go round, the persistent kernel runs
-// instead (partition = 512 tokens, grid = the resident slots).
-static int pa_plan(int num_seqs, int num_heads, int num_kv_heads, int head_size, int max_seq_len, int block_size,
-                   int kv_dtype, bool* persist) {
-  *persist = false;
+extern "C" int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads,
+                                                       int num_kv_heads, int head_size,
+                                                       int max_seq_len, int block_size,
+                                                       int kv_dtype) {
+  // Split-K cost model: time ~ waves(np) * (tokens per partition + fixed per-CTA overhead), where
+  // a wave is num_sms x resident CTAs.  Picks the np (not only powers of two) that fills whole
+  // waves; no split when the unsplit grid already covers the machine.
   if (num_seqs <= 0 || num_kv_heads <= 0) return 0;
   const int q_per_kv = num_heads / num_kv_heads;
   const int groups = (q_per_kv + 7) / 8;
@@ -823,7 +782,7 @@ static int pa_plan(int num_seqs, int num_heads, int num_kv_heads, int head_size,
   const int align = block_size > 32 ? block_size : 32;
   const int len = max_seq_len > 0 ? max_seq_len : 16;
   const long kOverheadTokens = 256;
-  long best_cost = -1, best_ctas = base_ctas;
+  long best_cost = -1;
   int best_part = round_up(len, align);
   for (int np = 1; np <= 64; ++np) {
     const int part = round_up((len + np - 1) / np, align);
@@ -834,28 +793,9 @@ static int pa_plan(int num_seqs, int num_heads, int num_kv_heads, int head_size,
     if (best_cost < 0 || cost < best_cost) {
       best_cost = cost;
       best_part = part;
-      best_ctas = base_ctas * np_eff;
-    }
-  }
-  const int mode = pa_persist_mode();
-  if (tma && mode != 0) {
-    const long items = base_ctas * ((len + kPaPersistPartition - 1) / kPaPersistPartition);
-    const long waves = (best_ctas + resident - 1) / resident;
-    const bool ragged_wave = best_ctas * 100 < waves * resident * 92;
-    if (mode == 1 || (ragged_wave && items >= resident)) {
-      *persist = true;
-      return kPaPersistPartition;
     }
   }
   return best_part;
-}
-
-extern "C" int vb200_paged_attention_v1_partition_size(int num_seqs, int num_heads,
-                                                       int num_kv_heads, int head_size,
-                                                       int max_seq_len, int block_size,
-                                                       int kv_dtype) {
-  bool persist;
-  return pa_plan(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size, kv_dtype, &persist);
 }
 
 extern "C" size_t vb200_paged_attention_v1_workspace_size(int num_seqs, int num_heads,
@@ -876,23 +816,19 @@ extern "C" int vb200_paged_attention_v1(
     const float* v_scale, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
     int partition_size, void* workspace, size_t workspace_bytes, vb200_stream_t stream) {
   int part = partition_size;
-  bool persist = false;
   if (workspace == nullptr) {
     part = 0;
-  } else {
-    // the persistent kernel runs when the plan asks for it and the caller did not impose a different partition
-    const int plan_part = pa_plan(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size, kv_dtype, &persist);
-    if (part <= 0) part = plan_part;
-    else if (part != plan_part) persist = false;
+  } else if (part <= 0) {
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size,
+                                                   max_seq_len, block_size, kv_dtype);
   }
   int np = 1;
   if (part > 0 && max_seq_len > part) np = (max_seq_len + part - 1) / part;
-  if (np == 1 && !persist) {
+  if (np == 1) {
     part = round_up(max_seq_len > 0 ? max_seq_len : 16, 32);
     if (part % block_size) part = round_up(part, block_size);
   }
   PagedAttnParams p;
-  p.persist = persist ? 1 : 0;
   p.out = out;
   p.exp_sums = nullptr;
   p.max_logits = nullptr;
