@@ -146,6 +146,23 @@ int vb200_paged_attention_v1(void* out, const void* query, const void* key_cache
                              int partition_size, void* workspace, size_t workspace_bytes,
                              vb200_stream_t stream);
 
+/* paged_attention_v1 with the dynamic per-token fp8 quantisation of its output fused into the split-K reduce kernel
+ * (SURVEY.md 8f row 1): out_q fp8 [num_seqs, num_heads*head_size] and out_scales fp32 [num_seqs] are exactly what
+ * vb200_paged_attention_v1 followed by vb200_dynamic_per_token_scaled_fp8_quant (fp8/common.cu:28-83) produce on the
+ * same partition plan -- the activation the FP8 o_proj consumes -- in one launch fewer and without the bf16 round trip
+ * through HBM.  Needs block_size 16, head_size % 32 == 0, num_heads <= 128 and a workspace of
+ * vb200_paged_attention_v1_quant_workspace_size() bytes (the partials are always materialised). */
+size_t vb200_paged_attention_v1_quant_workspace_size(int num_seqs, int num_heads, int head_size, int max_seq_len,
+                                                     int q_dtype, int partition_size);
+int vb200_paged_attention_v1_quant(void* out_q, float* out_scales, const float* scale_ub, const void* query,
+                                   const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+                                   int head_size, int num_kv_heads, float scale, const int32_t* block_tables,
+                                   const int32_t* seq_lens, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+                                   const float* alibi_slopes, int q_dtype, int kv_dtype, const float* k_scale,
+                                   const float* v_scale, int64_t q_stride, int64_t kv_block_stride,
+                                   int64_t kv_head_stride, int partition_size, void* workspace, size_t workspace_bytes,
+                                   vb200_stream_t stream);
+
 /* Decode attention over the FLASH cache layout: the cache vLLM's V1 backends allocate,
  * kv_cache [2, num_blocks, block_size, num_kv_heads, head_size] (vllm/v1/attention/backends/flash_attn.py:79-102),
  * in NHD order or as the HND-permuted view Blackwell uses (vllm/platforms/cuda.py:264-290) -- the layout

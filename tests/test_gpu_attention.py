@@ -198,3 +198,33 @@ def test_paged_attention_cuda_graph_capture():
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, eager)
+
+
+@pytest.mark.parametrize("kvd", ["auto", "fp8"])
+@pytest.mark.parametrize("case", [(7, 32, 8, 128, [1, 15, 16, 17, 511, 513, 1300]), (3, 8, 8, 64, [33, 700, 2]),
+                                  (2, 40, 1, 128, [77, 640]), (2, 4, 2, 256, [40, 300]), (2, 64, 8, 128, [5000, 300]),
+                                  (4, 16, 2, 128, [100, 90, 80, 70])], ids=lambda c: f"S{c[0]}H{c[1]}kv{c[2]}D{c[3]}")
+def test_paged_attention_v1_quant_matches_unfused(kvd, case):
+    """paged_attention_v1_quant (per-token fp8 quantisation inside the split-K reduce kernel) == paged_attention_v1
+    followed by scaled_fp8_quant(use_per_token_if_dynamic=True), bit for bit (codes and scales)."""
+    from vllm_b200 import _custom_ops as ops
+    S, H, Hkv, D, seq_lens = case
+    bs, dtype = 16, torch.bfloat16
+    seed_all(S + H + D)
+    nb = S * ((max(seq_lens) + bs - 1) // bs) + 4
+    ksc, vsc = (0.043, 0.029) if kvd == "fp8" else (1.0, 1.0)
+    kc, vc = make_paged_kv(nb, bs, Hkv, D, dtype, kvd, dist="normal", k_scale=ksc, v_scale=vsc)
+    q = (torch.randn(S, H, D) * 0.5).to(dtype).to(DEV)
+    bt = make_block_tables(S, seq_lens, bs, nb).to(DEV)
+    sl = torch.tensor(seq_lens, dtype=torch.int32, device=DEV)
+    ks, vs = torch.tensor([ksc], device=DEV), torch.tensor([vsc], device=DEV)
+    kc, vc = kc.to(DEV), vc.to(DEV)
+    scale = float(D ** -0.5)
+    out = torch.empty_like(q)
+    ops.paged_attention_v1(out, q, kc, vc, Hkv, scale, bt, sl, bs, max(seq_lens), None, kvd, ks, vs)
+    want_q, want_s = ops.scaled_fp8_quant(out.view(S, H * D), None, use_per_token_if_dynamic=True)
+    got_q, got_s = ops.paged_attention_v1_quant(q, kc, vc, Hkv, scale, bt, sl, bs, max(seq_lens), None, kvd, ks, vs)
+    torch.cuda.synchronize()
+    assert got_q.shape == (S, H * D) and got_s.shape == (S, 1)
+    assert torch.equal(got_s, want_s.view(S, 1))
+    assert torch.equal(got_q.view(torch.uint8), want_q.view(torch.uint8))

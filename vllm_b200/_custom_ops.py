@@ -106,6 +106,46 @@ def paged_attention_v1(
             max(partition_size, 0), ptr(ws), ws_bytes, stream()))
 
 
+def paged_attention_v1_quant(
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: Optional[torch.Tensor],
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+    scale_ub: Optional[torch.Tensor] = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """paged_attention_v1 followed by scaled_fp8_quant(use_per_token_if_dynamic=True) of its output, with the
+    quantisation fused into the split-K reduce kernel: returns (fp8 [num_seqs, num_heads *
+    head_size], fp32 scales [num_seqs, 1]), bit-identical to the two ops run back to back.  Block size 16,
+    head_size % 32 == 0."""
+    kvd = _pa_common(query, key_cache, value_cache, block_tables, seq_lens, kv_cache_dtype)
+    require_cuda(alibi_slopes, k_scale, v_scale, scale_ub)
+    lib = load()
+    num_seqs, num_heads, head_size = query.shape
+    qd = dtype_enum(query.dtype)
+    out_q = torch.empty((num_seqs, num_heads * head_size), dtype=FP8_DTYPE, device=query.device)
+    scales = torch.empty((num_seqs, 1), dtype=torch.float32, device=query.device)
+    with _device_of(query):
+        part = lib.vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len,
+                                                           block_size, kvd)
+        ws_bytes = lib.vb200_paged_attention_v1_quant_workspace_size(num_seqs, num_heads, head_size, max_seq_len, qd, part)
+        ws = torch.empty(max(ws_bytes, 64), dtype=torch.uint8, device=query.device)
+        check(lib.vb200_paged_attention_v1_quant(
+            ptr(out_q), ptr(scales), ptr(scale_ub), ptr(query), ptr(key_cache), ptr(value_cache), num_seqs, num_heads,
+            head_size, num_kv_heads, float(scale), ptr(block_tables), ptr(seq_lens), block_size, max_seq_len,
+            block_tables.stride(0), ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0),
+            key_cache.stride(0), key_cache.stride(1), part, ptr(ws), ws.numel(), stream()))
+    return out_q, scales
+
+
 def paged_attention_flash(
     out: torch.Tensor,
     query: torch.Tensor,

@@ -135,6 +135,28 @@ class B200PagedAttentionImpl:
                                           layer._k_scale, layer._v_scale, output=out3)
         return output.view(-1, self.num_heads * self.head_size)
 
+    def supports_fused_output_quant(self, block_size: int) -> bool:
+        return block_size == 16 and self.head_size % 32 == 0 and self.num_heads <= 128
+
+    def forward_quant(self, layer, query: torch.Tensor, kv_cache: torch.Tensor,
+                      attn_metadata: B200PagedAttentionMetadata, scale_ub: Optional[torch.Tensor] = None):
+        """Decode attention whose output leaves as the dynamically per-token quantised fp8 activation of the FP8
+        o_proj: (fp8 [T, H*D], scales [T, 1]).  The quantisation runs inside the split-K reduce kernel
+        (ops.paged_attention_v1_quant); results are bit-identical to forward() followed by
+        scaled_fp8_quant(use_per_token_if_dynamic=True).  The new token's K / V must already be in the cache."""
+        from .. import _custom_ops as ops
+        if attn_metadata.prefill_metadata is not None:
+            raise NotImplementedError("the B200 paged-attention backend implements the decode path only")
+        query = query.view(-1, self.num_heads, self.head_size)
+        key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads, self.head_size)
+        meta = attn_metadata.decode_metadata
+        if self.alibi_slopes is not None and self.alibi_slopes.device != query.device:
+            self.alibi_slopes = self.alibi_slopes.to(query.device)
+        return ops.paged_attention_v1_quant(query, key_cache, value_cache, self.num_kv_heads, self.scale,
+                                            meta.block_tables, meta.seq_lens_tensor, value_cache.shape[3],
+                                            meta.max_decode_seq_len, self.alibi_slopes, self.kv_cache_dtype,
+                                            layer._k_scale, layer._v_scale, scale_ub)
+
 
 class B200PagedAttentionBackend:
     """abstract.AttentionBackend (:37-107)."""

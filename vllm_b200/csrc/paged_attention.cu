@@ -45,6 +45,10 @@ struct PagedAttnParams {
   int64_t q_stride, kv_block_stride, kv_head_stride;
   float scale;
   int prefetch_dist;  // tiles (per warp) ahead of the register double buffer that are pulled into L2; 0 = off
+  // fused output quantisation (vb200_paged_attention_v1_quant): the split-K reduce kernel writes fp8 + per-token scales
+  void* out_q = nullptr;
+  float* out_scales = nullptr;
+  const float* scale_ub = nullptr;
 };
 
 template <typename T>
@@ -504,6 +508,80 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
   }
 }
 
+// v2 reduce fused with dynamic_per_token_scaled_fp8_quant of the attention output (the activation quantisation in
+// front of o_proj; /root/reference/csrc/quantization/fp8/common.cu:28-83): one CTA per sequence, one warp per head
+// (heads beyond 32 loop), the reduced row stays in registers between the reduction, the row amax and the fp8 write.
+// Same arithmetic and rounding points as paged_attention_reduce_kernel followed by per_token_quant_kernel: the reduced
+// value is rounded to QT first (what the unfused kernel stores), then amax / scale / true division.
+template <typename QT, int HEAD_SIZE>
+__global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
+    uint8_t* __restrict__ out_q, float* __restrict__ out_scales, const float* __restrict__ scale_ub,
+    const float* __restrict__ exp_sums, const float* __restrict__ max_logits, const QT* __restrict__ tmp_out,
+    const int* __restrict__ seq_lens, int num_heads, int max_num_partitions, int partition_size) {
+  pdl_wait();
+  pdl_trigger();
+  constexpr int PER = HEAD_SIZE / 32;
+  constexpr int MAXH = 4;   // heads per warp (<= 128 query heads)
+  __shared__ float sm[32];
+  const int seq_idx = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int seq_len = seq_lens[seq_idx];
+  const int np = min(max(1, (seq_len + partition_size - 1) / partition_size), max_num_partitions);
+  float y[MAXH][PER];
+  float amax = 0.f;
+#pragma unroll
+  for (int hh = 0; hh < MAXH; ++hh) {
+    const int head = warp + hh * nw;
+    if (head < num_heads) {
+      const int64_t row = (int64_t)seq_idx * num_heads + head;
+      const float* ml = max_logits + row * max_num_partitions;
+      const float* es = exp_sums + row * max_num_partitions;
+      const QT* tp = tmp_out + row * max_num_partitions * HEAD_SIZE;
+      if (np == 1) {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(tp[lane + 32 * i]);
+      } else {
+        float mg = -INFINITY;
+        for (int j = lane; j < np; j += 32) mg = fmaxf(mg, ml[j]);
+        mg = warp_max(mg);
+        float gsum = 0.f;
+        for (int j = lane; j < np; j += 32) gsum += es[j] * __expf(ml[j] - mg);
+        gsum = warp_sum(gsum);
+        const float inv = __fdividef(1.f, gsum + 1e-6f);
+        float acc[PER];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) acc[i] = 0.f;
+        for (int j = 0; j < np; ++j) {
+          const float w = es[j] * __expf(ml[j] - mg) * inv;
+#pragma unroll
+          for (int i = 0; i < PER; ++i) acc[i] = fmaf(to_float<QT>(tp[(int64_t)j * HEAD_SIZE + lane + 32 * i]), w, acc[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(from_float<QT>(acc[i]));
+      }
+#pragma unroll
+      for (int i = 0; i < PER; ++i) amax = fmaxf(amax, fabsf(y[hh][i]));
+    }
+  }
+  amax = warp_max(amax);
+  if (lane == 0) sm[warp] = amax;
+  __syncthreads();
+  amax = warp_max(lane < nw ? sm[lane] : 0.f);
+  float s = scale_ub ? fminf(amax, *scale_ub) : amax;
+  s = fmaxf(s / 448.f, 1.0f / (448.f * 512.0f));
+  if (threadIdx.x == 0) out_scales[seq_idx] = s;
+#pragma unroll
+  for (int hh = 0; hh < MAXH; ++hh) {
+    const int head = warp + hh * nw;
+    if (head < num_heads) {
+      uint8_t* o = out_q + ((int64_t)seq_idx * num_heads + head) * HEAD_SIZE;
+#pragma unroll
+      for (int i = 0; i < PER; ++i)
+        o[lane + 32 * i] = float_to_e4m3(fmaxf(-448.f, fminf(y[hh][i] / s, 448.f)));
+    }
+  }
+}
+
 }  // namespace vb200
 #include "paged_attention_tma.cuh"
 #include "paged_attention_flash.cuh"
@@ -558,6 +636,20 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     dim3 grid_t(p.num_kv_heads * ((q_per_kv_ + 7) / 8), num_seqs, num_partitions);
     VB_CUDA_CHECK(launch_k(kt, dim3(grid_t), dim3((kWarps + 1) * 32), smem_t, stream, p, stages));
     VB_LAUNCH_CHECK();
+    if (p.out_q != nullptr) {
+      // fused output quantisation: always through the partials (force_partials is set by the entry point)
+      if constexpr (HEAD_SIZE % 32 == 0) {
+        const int warps = p.num_heads < 32 ? p.num_heads : 32;
+        VB_CHECK(p.num_heads <= 128, "paged_attention_v1_quant: at most 128 query heads (got %d)", p.num_heads);
+        VB_CUDA_CHECK(launch_k(paged_attention_reduce_quant_kernel<QT, HEAD_SIZE>, dim3(num_seqs), dim3(32 * warps), 0,
+                               stream, (uint8_t*)p.out_q, p.out_scales, p.scale_ub, p.exp_sums, p.max_logits,
+                               (const QT*)p.tmp_out, p.seq_lens, p.num_heads, p.max_num_partitions, p.partition_size));
+        VB_LAUNCH_CHECK();
+        return 0;
+      } else {
+        VB_CHECK(false, "paged_attention_v1_quant: head size %d must be a multiple of 32", HEAD_SIZE);
+      }
+    }
     if (p.max_num_partitions > 1 || p.force_partials) {
       const int rows = num_seqs * p.num_heads;
       VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream, (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
@@ -566,6 +658,7 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     }
     return 0;
   }
+  VB_CHECK(p.out_q == nullptr, "paged_attention_v1_quant: needs block size 16 and a head size that is a multiple of 32");
   auto kern = paged_attention_kernel<QT, FP8, HEAD_SIZE, BLOCK_SIZE, kWarps>;
   const int nblk = (p.partition_size + BLOCK_SIZE - 1) / BLOCK_SIZE;
   const size_t smem = (size_t)kWarps * 8 * HEAD_SIZE * 4 + 2 * kWarps * 8 * 4 + (size_t)nblk * 4;
@@ -931,4 +1024,66 @@ extern "C" int vb200_paged_attention_flash(
   FlashLayout L{block_stride, token_stride, head_stride, num_blocks};
   if (q_dtype == VB200_F16) return dispatch_flash<__half>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
   return dispatch_flash<__nv_bfloat16>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
+}
+
+// paged_attention_v1 + dynamic per-token fp8 quantisation of its output in the split-K reduce kernel (SURVEY.md 8f
+// row 1; see include/vllm_b200.h).
+extern "C" size_t vb200_paged_attention_v1_quant_workspace_size(int num_seqs, int num_heads, int head_size, int max_seq_len,
+                                                                int q_dtype, int partition_size) {
+  (void)q_dtype;
+  if (partition_size <= 0) return 0;
+  size_t np = (size_t)(max_seq_len + partition_size - 1) / partition_size;
+  if (np < 1) np = 1;
+  const size_t rows = (size_t)num_seqs * num_heads * np;
+  return rows * 4 * 2 + rows * head_size * 2 + 64;
+}
+
+extern "C" int vb200_paged_attention_v1_quant(
+    void* out_q, float* out_scales, const float* scale_ub, const void* query, const void* key_cache,
+    const void* value_cache, int num_seqs, int num_heads, int head_size, int num_kv_heads, float scale,
+    const int32_t* block_tables, const int32_t* seq_lens, int block_size, int max_seq_len, int max_num_blocks_per_seq,
+    const float* alibi_slopes, int q_dtype, int kv_dtype, const float* k_scale, const float* v_scale, int64_t q_stride,
+    int64_t kv_block_stride, int64_t kv_head_stride, int partition_size, void* workspace, size_t workspace_bytes,
+    vb200_stream_t stream) {
+  VB_CHECK(out_q != nullptr && out_scales != nullptr, "paged_attention_v1_quant: out_q and out_scales are required");
+  VB_CHECK(block_size == 16 && head_size % 32 == 0, "paged_attention_v1_quant: block size 16 and head size %% 32 == 0");
+  VB_CHECK(workspace != nullptr, "paged_attention_v1_quant: a workspace is required");
+  int part = partition_size;
+  if (part <= 0)
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size,
+                                                   kv_dtype);
+  if (part <= 0) return 0;
+  int np = (max_seq_len + part - 1) / part;
+  if (np < 1) np = 1;
+  const size_t need = vb200_paged_attention_v1_quant_workspace_size(num_seqs, num_heads, head_size, max_seq_len, q_dtype, part);
+  VB_CHECK(workspace_bytes >= need, "paged_attention_v1_quant workspace too small: %zu < %zu", workspace_bytes, need);
+  const size_t rows = (size_t)num_seqs * num_heads * np;
+  PagedAttnParams p;
+  p.out = nullptr;
+  p.exp_sums = reinterpret_cast<float*>(workspace);
+  p.max_logits = p.exp_sums + rows;
+  p.tmp_out = reinterpret_cast<void*>(p.max_logits + rows);
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_tables = block_tables;
+  p.seq_lens = seq_lens;
+  p.alibi_slopes = alibi_slopes;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_num_blocks_per_seq = max_num_blocks_per_seq;
+  p.partition_size = part;
+  p.max_num_partitions = np;
+  p.force_partials = 1;
+  p.q_stride = q_stride;
+  p.kv_block_stride = kv_block_stride;
+  p.kv_head_stride = kv_head_stride;
+  p.scale = scale;
+  p.prefetch_dist = 0;
+  p.out_q = out_q;
+  p.out_scales = out_scales;
+  p.scale_ub = scale_ub;
+  return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype, (cudaStream_t)stream);
 }

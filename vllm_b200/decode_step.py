@@ -17,6 +17,8 @@ library GEMM (torch.matmul -> cuBLAS) for the projections: only its attention/ca
 from dataclasses import dataclass
 from typing import List, Optional
 
+import os
+
 import torch
 
 from . import _custom_ops as ops
@@ -215,14 +217,19 @@ class DecoderLayer:
         ops.rotary_embedding_reshape_and_cache(positions, q, k, v, cfg.head_dim, cos_sin, True, key_cache, value_cache,
                                                meta.slot_mapping, self.attn.kv_cache_dtype, self.kv_scales._k_scale,
                                                self.kv_scales._v_scale)
-        attn_out = self.attn.forward(self.kv_scales, q, None, None, kv_cache, meta)
-        T = attn_out.shape[0]
+        T = q.shape[0]
         fused_ar = fp8 and par is not None   # o_proj's all-reduce is fused into the post-attention norm
         if fp8:
-            aq, a_s = ops.scaled_fp8_quant(attn_out, use_per_token_if_dynamic=True)
+            if self.attn.supports_fused_output_quant(value_cache.shape[3]) and os.environ.get("VB200_ATTN_QUANT", "1") != "0":
+                # the per-token fp8 quantisation of the attention output happens inside the split-K reduce kernel
+                aq, a_s = self.attn.forward_quant(self.kv_scales, q, kv_cache, meta)
+            else:
+                attn_out = self.attn.forward(self.kv_scales, q, None, None, kv_cache, meta)
+                aq, a_s = ops.scaled_fp8_quant(attn_out, use_per_token_if_dynamic=True)
             hidden = self._linear_q(aq, a_s, self.w_o, self.s_o,
                                     par.staging(T, cfg.hidden_size, self.dtype) if fused_ar else None)
         else:
+            attn_out = self.attn.forward(self.kv_scales, q, None, None, kv_cache, meta)
             hidden = torch.matmul(attn_out, self.w_o.t())
         if not fused_ar:
             hidden = tensor_model_parallel_all_reduce(hidden)
