@@ -426,7 +426,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     # ---- count launches of OUR kernels in one step (host-side counter around the C ABI) -------------
     lib = _lib.load()
     counter = {"n": 0}
-    per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_dynamic_scaled_fp8_quant": 2,
+    per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_paged_attention_v1_quant": 2,
+                "vb200_dynamic_scaled_fp8_quant": 2,
                 "vb200_moe_grouped_gemm_fp8": 2}
     wrapped = {}
     for name in _lib.SIGNATURES:
@@ -527,6 +528,18 @@ def run_gpu_arm(args, rank, world, local_rank):
         evs.append((s, e))
         return r
     real_fd.forward_decode = staticmethod(timed_forward_decode)
+    # fp8 layers take the attention through forward_quant (output quantisation fused into the split-K reduce kernel)
+    impl_cls = __import__("vllm_b200.attention.backend", fromlist=["B200PagedAttentionImpl"]).B200PagedAttentionImpl
+    orig_fq = impl_cls.forward_quant
+
+    def timed_forward_quant(self, *a, **k):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        r = orig_fq(self, *a, **k)
+        e.record()
+        evs.append((s, e))
+        return r
+    impl_cls.forward_quant = timed_forward_quant
     try:
         inp.upload()
         for _ in range(max(2, min(args.steps, 5))):
@@ -534,6 +547,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         torch.cuda.synchronize()
     finally:
         real_fd.forward_decode = staticmethod(orig)
+        impl_cls.forward_quant = orig_fq
     attn_ms = [s.elapsed_time(e) for s, e in evs[len(dec.layers):]]  # drop the first step
     attn_s = statistics.mean(attn_ms) * 1e-3
     cache_bytes = 1 if kvd != "auto" else 2
@@ -558,7 +572,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                 "d2h_bytes_per_step": inp.d2h_bytes, "ms_per_step": round(e2e_s * 1e3, 4)},
         "gpu_launches": launches_per_step * args.steps,
         "gpu_launches_per_step": launches_per_step,
-        "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel (+ split-K reduce)",
+        "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel (+ split-K reduce with the fused per-token fp8 output quant)" if quant == "fp8" else "paged_attention_kernel (+ split-K reduce)",
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": kernel_traffic(args.config, world), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo, "avg_launch_us": round(attn_s * 1e6, 2),
