@@ -282,6 +282,14 @@ int vb200_topk_softmax(float* topk_weights, void* topk_indices, int32_t* token_e
                        const float* gating_output, int num_tokens, int num_experts, int topk,
                        int indices_dtype, vb200_stream_t stream);
 
+/* fused_topk (vllm/model_executor/layers/fused_moe/fused_moe.py:882-915) in ONE launch: the reference casts the router
+ * logits to fp32 on the host, calls topk_softmax and renormalises with two more torch ops (:869-870, :908); here the
+ * kernel reads the logits in their own dtype (F32 / F16 / BF16; widening is exact), and divides the k winners by their
+ * sum (accumulated in k order) when `renormalize` is set.  topk_indices / token_expert_indices int32. */
+int vb200_fused_topk(float* topk_weights, int32_t* topk_indices, int32_t* token_expert_indices,
+                     const void* gating_output, int num_tokens, int num_experts, int topk, int renormalize,
+                     int in_dtype, vb200_stream_t stream);
+
 /* moe_align_block_size: csrc/moe/moe_align_sum_kernels.cu:204-275, schema
  * csrc/moe/torch_bindings.cpp:18-22.  topk_ids int32 [numel]; sorted_token_ids int32
  * [numel + num_experts*(block_size-1)] (caller may pre-fill; this call writes every entry:

@@ -93,3 +93,24 @@ def test_moe_sum(dtype, T, k, H):
         outr = torch.empty_like(out)
         ref.moe_sum(x.to(DEV), outr)
         assert torch.equal(out, outr)
+
+
+@pytest.mark.parametrize("T,E,k", [(1, 8, 2), (128, 8, 2), (33, 64, 6), (257, 16, 4), (64, 160, 8)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("renorm", [False, True])
+def test_fused_topk_one_launch(T, E, k, dtype, renorm):
+    """fused_topk (fused_moe.py:882-915): the single-launch path (logits read in their own dtype, renormalisation in the
+    kernel) gives the ids of the explicit arg-max oracle bit for bit and the weights of `softmax -> topk -> w / sum(w)`
+    to fp32 rounding."""
+    from vllm_b200.fused_moe import fused_topk
+    seed_all(T + E + k)
+    gate = torch.randn(T, E).to(dtype)
+    hidden = torch.zeros(T, 16, dtype=torch.bfloat16, device=DEV)
+    w_o, ids_o, _ = omoe.topk_softmax(gate.float(), k)
+    if renorm:
+        w_o = w_o / w_o.sum(-1, keepdim=True)
+    w, ids, tei = fused_topk(hidden, gate.to(DEV), k, renorm)
+    torch.cuda.synchronize()
+    assert ids.dtype == torch.int32 and torch.equal(ids.cpu(), ids_o.to(torch.int32))
+    torch.testing.assert_close(w.cpu(), w_o, rtol=2e-6, atol=1e-7)
+    assert torch.equal(tei.cpu(), (torch.arange(k)[None, :] * T + torch.arange(T)[:, None]).to(torch.int32))

@@ -83,6 +83,7 @@ SIGNATURES = {
                                         c_int64, c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_cutlass_scaled_mm_supports_fp8": (c_int, [c_int]),
     "vb200_topk_softmax": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),
+    "vb200_fused_topk": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "vb200_moe_align_workspace_size": (c_size_t, [c_int, c_int]),
     "vb200_moe_align_block_size": (c_int, [_P, c_int, c_int, c_int, _P, c_int, _P, c_int, _P, _P,
                                            c_size_t, _P]),

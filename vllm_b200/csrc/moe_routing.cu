@@ -12,23 +12,26 @@ namespace vb200 {
 // ---------------------------------------------------------------------------------------------
 // topk_softmax: one warp per row; lane l holds experts l, l+32, ...
 // ---------------------------------------------------------------------------------------------
-template <int VPT, typename IndT>
+// InT: dtype of the router logits (the reference casts them to fp32 on the host first, fused_moe.py:908; reading
+// bf16 / f16 here and widening is the same values).  RENORM: w /= sum(w) over the k winners, summed in k order
+// (fused_moe.py:869-870 does it as two torch ops on the [T, k] tensor).
+template <int VPT, typename IndT, typename InT = float, bool RENORM = false>
 __global__ void __launch_bounds__(128) topk_softmax_kernel(
     float* __restrict__ topk_weights, IndT* __restrict__ topk_indices,
-    int* __restrict__ token_expert_indices, const float* __restrict__ gating, int num_tokens,
+    int* __restrict__ token_expert_indices, const InT* __restrict__ gating, int num_tokens,
     int num_experts, int topk) {
   pdl_wait();
   pdl_trigger();
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= num_tokens) return;
   const int lane = threadIdx.x & 31;
-  const float* g = gating + (int64_t)row * num_experts;
+  const InT* g = gating + (int64_t)row * num_experts;
   float v[VPT];
   float mx = -FLT_MAX;
 #pragma unroll
   for (int i = 0; i < VPT; ++i) {
     const int e = lane + 32 * i;
-    v[i] = e < num_experts ? g[e] : -FLT_MAX;
+    v[i] = e < num_experts ? to_float<InT>(g[e]) : -FLT_MAX;
     mx = fmaxf(mx, v[i]);
   }
   mx = warp_max(mx);
@@ -46,6 +49,7 @@ __global__ void __launch_bounds__(128) topk_softmax_kernel(
     const int e = lane + 32 * i;
     v[i] = e < num_experts ? v[i] * inv : -1.f;  // probabilities are >= 0; -1 never wins
   }
+  float wsum = 0.f;   // lane 0: sum of the winners' probabilities
   // k rounds of arg-max, lowest index wins ties (topk_softmax_kernels.cu:336-358)
   for (int k = 0; k < topk; ++k) {
     float best = -2.f;
@@ -70,6 +74,7 @@ __global__ void __launch_bounds__(128) topk_softmax_kernel(
     if (lane == 0) {
       const int64_t o = (int64_t)row * topk + k;
       topk_weights[o] = best;
+      wsum += best;
       topk_indices[o] = (IndT)bidx;
       token_expert_indices[o] = k * num_tokens + row;  // :373
     }
@@ -78,6 +83,12 @@ __global__ void __launch_bounds__(128) topk_softmax_kernel(
 #pragma unroll
       for (int i = 0; i < VPT; ++i)
         if (lane + 32 * i == bidx) v[i] = -1.f;
+    }
+  }
+  if (RENORM && lane == 0) {
+    for (int k = 0; k < topk; ++k) {
+      const int64_t o = (int64_t)row * topk + k;
+      topk_weights[o] = topk_weights[o] / wsum;   // this lane wrote them: program order makes its own stores visible
     }
   }
 }
@@ -196,10 +207,28 @@ __global__ void __launch_bounds__(kAlignThreads) moe_align_kernel(
 // ---------------------------------------------------------------------------------------------
 template <typename T, int TOPK>
 __global__ void __launch_bounds__(256) moe_sum_kernel(T* __restrict__ out,
-                                                      const T* __restrict__ in, int topk, int d) {
+                                                      const T* __restrict__ in, int topk, int d, bool vec) {
   pdl_wait();
   pdl_trigger();
   const int64_t t = blockIdx.x;
+  constexpr int VE = 16 / sizeof(T);
+  if (TOPK > 0 && vec) {
+    // 16-byte vectors: the kernel is a 3 MB stream at decode sizes and was latency-bound with scalar accesses
+    // (11.7 us for [128, 2, 4096] bf16, profiles/r02_launches_cfg4_2steps_s56.txt).  Same arithmetic per element.
+    for (int i = threadIdx.x; i < d / VE; i += blockDim.x) {
+      union V { uint4 u; T e[VE]; } acc, v;
+#pragma unroll
+      for (int e = 0; e < VE; ++e) acc.e[e] = from_float<T>(0.f);
+#pragma unroll
+      for (int k = 0; k < TOPK; ++k) {
+        v.u = ldg_stream_v4(in + (t * TOPK + k) * d + (int64_t)i * VE);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) acc.e[e] = from_float<T>(to_float<T>(acc.e[e]) + to_float<T>(v.e[e]));
+      }
+      *reinterpret_cast<uint4*>(out + t * d + (int64_t)i * VE) = acc.u;
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
     if (TOPK > 0) {
       // accumulate in T, in j order, starting from 0 (moe_align_sum_kernels.cu:116-121)
@@ -221,14 +250,14 @@ __global__ void __launch_bounds__(256) moe_sum_kernel(T* __restrict__ out,
 
 using namespace vb200;
 
-template <typename IndT>
-static int launch_topk(float* w, void* idx, int* tei, const float* g, int T, int E, int k,
+template <typename IndT, typename InT = float, bool RENORM = false>
+static int launch_topk(float* w, void* idx, int* tei, const InT* g, int T, int E, int k,
                        cudaStream_t s) {
   const int grid = (T + 3) / 4;
   const int vpt = (E + 31) / 32;
 #define TOPK_CASE(V)                                                                      \
   if (vpt <= V) {                                                                         \
-    VB_CUDA_CHECK(launch_k(topk_softmax_kernel<V, IndT>, dim3(grid), dim3(128), 0, s, w, (IndT*)idx, tei, g, T, E, k));    \
+    VB_CUDA_CHECK(launch_k(topk_softmax_kernel<V, IndT, InT, RENORM>, dim3(grid), dim3(128), 0, s, w, (IndT*)idx, tei, g, T, E, k));    \
     VB_LAUNCH_CHECK();                                                                    \
     return 0;                                                                             \
   }
@@ -258,6 +287,29 @@ extern "C" int vb200_topk_softmax(float* topk_weights, void* topk_indices,
                                   num_tokens, num_experts, topk, stream);
     default:
       VB_CHECK(false, "topk_softmax: indices must be int32, uint32 or int64");
+  }
+  return 0;
+}
+
+// fused_topk (fused_moe.py:882-915) as ONE launch: softmax over the router logits in their own dtype, top-k, optional
+// renormalisation.  int32 indices.
+template <typename InT>
+static int fused_topk_in(float* w, int32_t* idx, int32_t* tei, const void* g, int T, int E, int k, int renorm, cudaStream_t s) {
+  if (renorm) return launch_topk<int32_t, InT, true>(w, idx, tei, (const InT*)g, T, E, k, s);
+  return launch_topk<int32_t, InT, false>(w, idx, tei, (const InT*)g, T, E, k, s);
+}
+
+extern "C" int vb200_fused_topk(float* topk_weights, int32_t* topk_indices, int32_t* token_expert_indices,
+                                const void* gating_output, int num_tokens, int num_experts, int topk, int renormalize,
+                                int in_dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(topk >= 1 && topk <= num_experts, "fused_topk: topk %d must be in [1, num_experts %d]", topk, num_experts);
+  if (num_tokens <= 0) return 0;
+  switch (in_dtype) {
+    case VB200_F32: return fused_topk_in<float>(topk_weights, topk_indices, token_expert_indices, gating_output, num_tokens, num_experts, topk, renormalize, stream);
+    case VB200_F16: return fused_topk_in<__half>(topk_weights, topk_indices, token_expert_indices, gating_output, num_tokens, num_experts, topk, renormalize, stream);
+    case VB200_BF16: return fused_topk_in<__nv_bfloat16>(topk_weights, topk_indices, token_expert_indices, gating_output, num_tokens, num_experts, topk, renormalize, stream);
+    default: VB_CHECK(false, "fused_topk: router logits must be fp32, f16 or bf16");
   }
   return 0;
 }
@@ -305,15 +357,19 @@ extern "C" int vb200_moe_sum(void* out, const void* input, int num_tokens, int t
                              int dtype, vb200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (num_tokens <= 0 || hidden <= 0) return 0;
-  const int threads = hidden >= 256 ? 256 : 64;
+  const int esz = dtype == VB200_F32 ? 4 : 2;
+  const bool vec = hidden % (16 / esz) == 0 && (reinterpret_cast<uintptr_t>(input) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  const int work = vec ? hidden / (16 / esz) : hidden;
+  const int threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
   DISPATCH_T(dtype, {
     scalar_t* o = (scalar_t*)out;
     const scalar_t* in = (const scalar_t*)input;
     switch (topk) {
-      case 2: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 2>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
-      case 3: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 3>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
-      case 4: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 4>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
-      default: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 0>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden)); break;
+      case 2: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 2>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden, vec)); break;
+      case 3: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 3>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden, vec)); break;
+      case 4: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 4>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden, vec)); break;
+      default: VB_CUDA_CHECK(launch_k(moe_sum_kernel<scalar_t, 0>, dim3(num_tokens), dim3(threads), 0, stream, o, in, topk, hidden, vec)); break;
     }
   });
   VB_LAUNCH_CHECK();

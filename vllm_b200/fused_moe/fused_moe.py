@@ -25,6 +25,14 @@ def fused_topk(hidden_states: torch.Tensor, gating_output: torch.Tensor, topk: i
     topk_weights = torch.empty(M, topk, dtype=torch.float32, device=dev)
     topk_ids = torch.empty(M, topk, dtype=torch.int32 if indices_type is None else indices_type, device=dev)
     token_expert_indices = torch.empty(M, topk, dtype=torch.int32, device=dev)
+    if topk_ids.dtype == torch.int32 and gating_output.is_cuda and gating_output.is_contiguous() and \
+            gating_output.dtype in (torch.float32, torch.float16, torch.bfloat16):
+        # one launch: logits read in their own dtype (the host-side .float() of fused_moe.py:908 is exact), softmax,
+        # top-k and the renormalisation of :869-870
+        check(load().vb200_fused_topk(ptr(topk_weights), ptr(topk_ids), ptr(token_expert_indices), ptr(gating_output),
+                                      M, gating_output.size(-1), topk, int(bool(renormalize)),
+                                      dtype_enum(gating_output.dtype), stream()))
+        return topk_weights, topk_ids, token_expert_indices
     ops.topk_softmax(topk_weights, topk_ids, token_expert_indices, gating_output.float().contiguous())
     if renormalize:
         topk_weights = topk_weights / topk_weights.sum(dim=-1, keepdim=True)
