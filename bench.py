@@ -261,40 +261,62 @@ def workload_config(name: str, n_gpus: int):
 # ---------------------------------------------------------------------------------------------------
 class StepInputs:
     """Host (pinned) and device copies of the decode inputs.  The context ADVANCES: every step appends one token per
-    sequence (device side: advance_step_flashattn inside the captured graph; host side: `advance_host` for the e2e
-    leg, which uploads the step's inputs), starting at `ctx` tokens; block tables hold `headroom` extra tokens."""
+    sequence (device side: advance_step_flashattn inside the captured graph; host side: `set_host_context` for the e2e
+    leg, which uploads the step's inputs), starting at `ctx` tokens; block tables hold `headroom` extra tokens.
+
+    All five inputs live in ONE packed buffer (ids | positions | slots | seq_lens | block tables) so that a step's
+    upload is one pinned-host -> device copy; the host side is double-buffered so that the next step's positions /
+    seq_lens / slots can be written while the device still runs the current step."""
 
     def __init__(self, batch, ctx, block_size, num_blocks, vocab, device, headroom):
         g = torch.Generator().manual_seed(0)
         bps = (ctx + headroom + block_size - 1) // block_size
         self.bs, self.bps = block_size, bps
-        self.h_ids = torch.randint(0, vocab, (batch,), generator=g, dtype=torch.int64).pin_memory()
-        self.h_pos = torch.empty((batch,), dtype=torch.int64).pin_memory()
-        self.h_sl = torch.empty((batch,), dtype=torch.int32).pin_memory()
-        self.h_bt = torch.randperm(num_blocks, generator=g)[:batch * bps].to(torch.int32).reshape(batch, bps).pin_memory()
-        self.h_slots = torch.empty((batch,), dtype=torch.int64).pin_memory()
-        self.h_out = torch.empty(batch, dtype=torch.int64).pin_memory()
         self.batch, self.ctx, self.max_len = batch, ctx, ctx + headroom
+        o_ids, o_pos, o_slots = 0, 8 * batch, 16 * batch
+        o_sl, o_bt = 24 * batch, 28 * batch
+        nbytes = o_bt + 4 * batch * bps
+
+        def views(buf):
+            return (buf[o_ids:o_pos].view(torch.int64), buf[o_pos:o_slots].view(torch.int64),
+                    buf[o_slots:o_sl].view(torch.int64), buf[o_sl:o_bt].view(torch.int32),
+                    buf[o_bt:nbytes].view(torch.int32).view(batch, bps))
+        self._host = [torch.empty(nbytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self._hviews = [views(h) for h in self._host]
+        self._cur_buf = 0
+        ids = torch.randint(0, vocab, (batch,), generator=g, dtype=torch.int64)
+        bt = torch.randperm(num_blocks, generator=g)[:batch * bps].to(torch.int32).reshape(batch, bps)
+        for v in self._hviews:
+            v[0].copy_(ids)
+            v[4].copy_(bt)
+        self.bt64 = bt.to(torch.int64)
+        self.h_out = torch.empty(batch, dtype=torch.int64).pin_memory()
         self.set_host_context(ctx)
-        self.d_ids, self.d_pos, self.d_sl = (t.to(device) for t in (self.h_ids, self.h_pos, self.h_sl))
-        self.d_bt, self.d_slots = self.h_bt.to(device), self.h_slots.to(device)
-        self.h2d_bytes = sum(t.numel() * t.element_size() for t in (self.h_ids, self.h_pos, self.h_sl, self.h_bt, self.h_slots))
+        self._dev = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        self.d_ids, self.d_pos, self.d_slots, self.d_sl, self.d_bt = views(self._dev)
+        self.upload()
+        self.h2d_bytes = nbytes
         self.d2h_bytes = self.h_out.numel() * self.h_out.element_size()
+
+    @property
+    def h_ids(self):
+        return self._hviews[self._cur_buf][0]
+
+    def flip(self):
+        """Switch to the other host buffer (the previous one may still be in flight to the device)."""
+        self._cur_buf ^= 1
 
     def set_host_context(self, seq_len):
         """Host copies for a step whose sequences hold `seq_len` tokens (the last one is the token being decoded)."""
         assert seq_len <= self.max_len, "bench context outgrew the block tables"
         self.cur = seq_len
-        self.h_pos.fill_(seq_len - 1)
-        self.h_sl.fill_(seq_len)
-        self.h_slots.copy_(self.h_bt[:, (seq_len - 1) // self.bs].to(torch.int64) * self.bs + (seq_len - 1) % self.bs)
+        _, pos, slots, sl, _ = self._hviews[self._cur_buf]
+        pos.fill_(seq_len - 1)
+        sl.fill_(seq_len)
+        torch.add(self.bt64[:, (seq_len - 1) // self.bs] * self.bs, (seq_len - 1) % self.bs, out=slots)
 
     def upload(self):
-        self.d_ids.copy_(self.h_ids, non_blocking=True)
-        self.d_pos.copy_(self.h_pos, non_blocking=True)
-        self.d_sl.copy_(self.h_sl, non_blocking=True)
-        self.d_bt.copy_(self.h_bt, non_blocking=True)
-        self.d_slots.copy_(self.h_slots, non_blocking=True)
+        self._dev.copy_(self._host[self._cur_buf], non_blocking=True)
 
 
 def attention_algorithmic_bytes(batch, ctx, H, Hkv, D, cache_bytes, q_bytes=2, block_size=16):
@@ -491,21 +513,49 @@ def run_gpu_arm(args, rank, world, local_rank):
         torch.cuda.profiler.stop()
     ms = e0.elapsed_time(e1) / args.steps
     # ---- e2e: host inputs every step, sampled ids back to the host every step -------------------------
+    dev_evs = []
+    host_t = {"upload_call": 0.0, "replay_call": 0.0, "d2h_call": 0.0, "next_context": 0.0, "wait": 0.0, "ids": 0.0}
+
     def e2e_step():
-        inp.upload()                       # H2D: ids, positions, seq_lens, block tables, slots of THIS step
+        pc = time.perf_counter
+        evs4 = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        t_0 = pc()
+        evs4[0].record()
+        inp.upload()                       # H2D: ids, positions, seq_lens, block tables, slots of THIS step (one copy)
+        evs4[1].record()
+        t_1 = pc()
         graph.replay()
+        t_2 = pc()
+        evs4[2].record()
         inp.h_out.copy_(d_next.view(-1), non_blocking=True)   # D2H: sampled ids
-        torch.cuda.current_stream().synchronize()
-        inp.h_ids.copy_(inp.h_out)         # the host owns the loop: next ids / context from what came back
+        evs4[3].record()
+        t_3 = pc()
+        dev_evs.append(evs4)
+        # while the device runs: the host writes the NEXT step's context into its other pinned buffer
+        inp.flip()
         inp.set_host_context(inp.cur + 1)
+        t_4 = pc()
+        torch.cuda.current_stream().synchronize()
+        t_5 = pc()
+        inp.h_ids.copy_(inp.h_out)         # the host owns the loop: next ids are what came back
+        t_6 = pc()
+        for k, v in zip(host_t, (t_1 - t_0, t_2 - t_1, t_3 - t_2, t_4 - t_3, t_5 - t_4, t_6 - t_5)):
+            host_t[k] += v
     inp.set_host_context(ctx + args.warmup + args.steps)   # carry on where the device loop stopped
     for _ in range(min(args.warmup, 3)):
         e2e_step()
     barrier()
+    for k in host_t:
+        host_t[k] = 0.0
+    dev_evs.clear()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
     e2e_s = (time.perf_counter() - t0) / args.steps
+    host_us = {k: round(v / args.steps * 1e6, 1) for k, v in host_t.items()}
+    # where the device spent the step (CUDA events on the stream): the H2D copy, the captured step, the D2H copy
+    dev_us = {name: round(statistics.mean(e[i].elapsed_time(e[i + 1]) for e in dev_evs) * 1e3, 1)
+              for i, name in enumerate(("h2d", "graph", "d2h"))}
     barrier()
     clk = clocks.stop() if rank == 0 else None
     if world > 1:
@@ -569,7 +619,8 @@ def run_gpu_arm(args, rank, world, local_rank):
         "data": "synthetic", "config": workload_config(args.config, world),
         "tokens_per_s_per_gpu": round(tps / world, 1),
         "e2e": {"value": round(batch / e2e_s, 1), "unit": "tokens/s", "h2d_bytes_per_step": inp.h2d_bytes,
-                "d2h_bytes_per_step": inp.d2h_bytes, "ms_per_step": round(e2e_s * 1e3, 4)},
+                "d2h_bytes_per_step": inp.d2h_bytes, "ms_per_step": round(e2e_s * 1e3, 4),
+                "host_us_per_step": host_us, "device_us_per_step": dev_us},
         "gpu_launches": launches_per_step * args.steps,
         "gpu_launches_per_step": launches_per_step,
         "roofline": {"bound": "hbm", "kernel": "paged_attention_kernel (+ split-K reduce with the fused per-token fp8 output quant)" if quant == "fp8" else "paged_attention_kernel (+ split-K reduce)",

@@ -417,6 +417,13 @@ int vb200_advance_step_flashattn(int num_seqs, int num_queries, int block_size, 
                                  int32_t* seq_lens, int64_t* slot_mapping, const int32_t* block_tables,
                                  int64_t block_tables_stride, vb200_stream_t stream);
 
+/* greedy_argmax: the greedy branch of vllm/v1/sample/sampler.py:87-96 (`logits.argmax(dim=-1)`), additive (the
+ * reference runs torch's reduction on an fp32 copy of the logits).  logits [num_rows, vocab] of `dtype`
+ * (F32/F16/BF16), rows `row_stride` elements apart; out_idx int64 [num_rows]; out_val fp32 [num_rows] or NULL (the
+ * row maximum, for the vocab-parallel merge).  First index wins a tie; NaN counts as the largest value. */
+int vb200_greedy_argmax(int64_t* out_idx, float* out_val, const void* logits, int num_rows, int vocab,
+                        int64_t row_stride, int dtype, vb200_stream_t stream);
+
 /* merge_attn_states: csrc/attention/merge_attn_states.cu:121-178 (kernel :12-89), schema
  * csrc/torch_bindings.cpp:75-83.  output/prefix_output/suffix_output [num_tokens, num_heads, head_size] of
  * `dtype` (F32/F16/BF16), contiguous; *_lse fp32 [num_heads, num_tokens]; output_lse may be NULL.

@@ -151,3 +151,36 @@ def test_decode_loop_in_one_graph():
     a, sla = run(False)
     b, slb = run(True)
     assert torch.equal(a, b) and torch.equal(sla, slb) and int(sla[0]) == ctx0 + steps
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("rows,vocab", [(1, 7), (3, 1000), (16, 32000), (256, 128256), (5, 50257), (2, 151936)])
+def test_greedy_argmax_matches_numpy_first_max(rows, vocab, dtype):
+    """Bit-exact index parity with `logits.argmax(dim=-1)` under its documented rule (first index among equal maxima),
+    checked against numpy on the host; bf16 logits tie often, so the rule is exercised at every size."""
+    from vllm_b200 import _custom_ops as ops
+    seed_all(rows * 31 + vocab)
+    logits = (torch.randn(rows, vocab) * 4).to(dtype)
+    idx, val = ops.greedy_argmax(logits.to(DEV), return_max=True)
+    torch.cuda.synchronize()
+    ref = logits.float().numpy()
+    assert idx.cpu().tolist() == ref.argmax(axis=1).tolist()
+    assert torch.equal(val.cpu(), logits.float().max(dim=1).values)
+    assert torch.equal(ops.greedy_argmax(logits.to(DEV)), idx)
+
+
+def test_greedy_argmax_ties_nan_and_strided_rows():
+    from vllm_b200 import _custom_ops as ops
+    x = torch.zeros(4, 4099, dtype=torch.bfloat16)
+    x[0, 17] = x[0, 4000] = 3.0                 # tie: the lower index
+    x[1, :] = -float("inf")                     # all equal: index 0
+    x[2, 5] = 9.0
+    x[2, 77] = float("nan")                     # NaN beats every number
+    x[3, 4098] = 1.0                            # last element of an odd-length row (scalar path: stride not 16 B)
+    got = ops.greedy_argmax(x.to(DEV)).cpu().tolist()
+    assert got == [17, 0, 77, 4098]
+    wide = torch.randn(6, 2 * 4096, device=DEV, dtype=torch.float16)
+    view = wide[:, :4096]                       # row stride 8192, vector path
+    assert torch.equal(ops.greedy_argmax(view).cpu(), torch.from_numpy(view.float().cpu().numpy().argmax(axis=1)))
+    with pytest.raises(RuntimeError, match="contiguous last"):
+        ops.greedy_argmax(wide.t())

@@ -161,7 +161,8 @@ def test_silu_and_mul_per_token_quant(dtype, T, d):
 @pytest.mark.parametrize("neox", [True, False])
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
 @pytest.mark.parametrize("T,H,Hkv,D,rot,bs", [(1, 32, 8, 128, 128, 16), (256, 32, 8, 128, 128, 16), (37, 12, 12, 64, 64, 32),
-                                              (9, 8, 2, 80, 32, 16), (4, 8, 1, 256, 128, 8)])
+                                              (9, 8, 2, 80, 32, 16), (4, 8, 1, 256, 128, 8), (5, 64, 8, 128, 128, 16),
+                                              (3, 4, 4, 32, 32, 16), (7, 4, 1, 256, 256, 16), (6, 8, 2, 96, 96, 16)])
 def test_rotary_embedding_reshape_and_cache(dtype, neox, kv_cache_dtype, T, H, Hkv, D, rot, bs):
     """The fused RoPE + KV-cache-write launch == rotary_embedding followed by reshape_and_cache, bit for bit, in q, k
     and both caches (ours back to back, and the oracle); padding tokens (slot -1) are rotated but not cached."""

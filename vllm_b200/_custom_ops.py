@@ -850,6 +850,22 @@ def advance_step_flashattn(num_seqs: int, num_queries: int, block_size: int, inp
             ptr(seq_lens), ptr(slot_mapping), ptr(block_tables), block_tables.stride(0), stream()))
 
 
+def greedy_argmax(logits: torch.Tensor, return_max: bool = False):
+    """Greedy sampling (`logits.argmax(dim=-1)`, vllm/v1/sample/sampler.py:87-96) on the logits as the lm_head GEMM
+    wrote them -- no fp32 copy of the [tokens, vocab] matrix.  logits [T, vocab] f32 / f16 / bf16 with a contiguous
+    last dimension.  Returns int64 [T], plus the fp32 row maxima when `return_max` (vocab-parallel merge)."""
+    require_cuda(logits)
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise RuntimeError("greedy_argmax: logits must be [num_tokens, vocab] with a contiguous last dimension")
+    t, v = logits.shape
+    idx = torch.empty(t, dtype=torch.int64, device=logits.device)
+    val = torch.empty(t, dtype=torch.float32, device=logits.device) if return_max else None
+    with _device_of(logits):
+        check(load().vb200_greedy_argmax(ptr(idx), ptr(val), ptr(logits), t, v, logits.stride(0) if t > 1 else v,
+                                         dtype_enum(logits.dtype), stream()))
+    return (idx, val) if return_max else idx
+
+
 def merge_attn_states(output: torch.Tensor, prefix_output: torch.Tensor, prefix_lse: torch.Tensor,
                       suffix_output: torch.Tensor, suffix_lse: torch.Tensor,
                       output_lse: Optional[torch.Tensor] = None) -> None:

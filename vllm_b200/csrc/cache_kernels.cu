@@ -68,6 +68,130 @@ __global__ void __launch_bounds__(256) rope_reshape_and_cache_kernel(
                                      slot_idx, num_kv_heads, head_size, block_size, x, k_scale, v_scale, vec_ok);
 }
 
+// The same operation for the shapes a decode step has (full rotary: rot_dim == head_size, 16-byte-aligned rows,
+// K runs of x * sizeof(cache_t) == 16 bytes): every thread owns ONE 16-byte piece of the token -- 8 (x, y) pairs of a
+// q / k head, or 8 elements of a v head -- so all of a token's loads are in flight at once (the per-element kernel
+// above does ten dependent rounds of 2-byte loads and stores per thread), and the rotated K goes to the cache from
+// registers instead of being re-read.  Same arithmetic, element for element: every product and sum rounded to T, the
+// cache quantised from the rounded K.
+template <typename scalar_t, bool FP8>
+__device__ __forceinline__ void store_cache8(void* dst, const scalar_t (&v)[8], float scale) {
+  if (!FP8) {
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+  } else {
+    union { uint2 u; uint8_t b[8]; } o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.b[j] = float_to_e4m3(to_float<scalar_t>(v[j]) / scale);
+    *reinterpret_cast<uint2*>(dst) = o.u;
+  }
+}
+
+template <typename scalar_t, bool NEOX, bool FP8>
+__global__ void __launch_bounds__(512) rope_reshape_and_cache_vec_kernel(
+    const int64_t* __restrict__ positions, scalar_t* query, scalar_t* key, const scalar_t* __restrict__ value,
+    const scalar_t* __restrict__ cos_sin_cache, void* __restrict__ key_cache_, void* __restrict__ value_cache_,
+    const int64_t* __restrict__ slot_mapping, int64_t query_stride, int64_t key_stride, int64_t value_stride,
+    int num_heads, int num_kv_heads, int head_size, int block_size, int x, const float* __restrict__ k_scale_p,
+    const float* __restrict__ v_scale_p) {
+  pdl_wait();
+  pdl_trigger();
+  using cache_t = typename std::conditional<FP8, uint8_t, scalar_t>::type;
+  const int64_t token = blockIdx.x;
+  const int64_t pos = positions[token];
+  const int64_t slot_idx = slot_mapping[token];
+  const bool cached = slot_idx >= 0;           // padding token: rotated, not cached
+  float k_scale = 1.f, v_scale = 1.f;
+  if (FP8) {
+    k_scale = *k_scale_p;
+    v_scale = *v_scale_p;
+  }
+  const int embed = head_size >> 1;
+  const int rot_per_head = NEOX ? embed >> 3 : head_size >> 3;
+  const int nrot = (num_heads + num_kv_heads) * rot_per_head;
+  const int v_per_head = head_size >> 3;
+  const int nv = cached ? num_kv_heads * v_per_head : 0;
+  const scalar_t* cache = cos_sin_cache + pos * head_size;
+  const int64_t block_idx = cached ? slot_idx / block_size : 0;
+  const int block_offset = cached ? (int)(slot_idx % block_size) : 0;
+  const int64_t n = (int64_t)num_kv_heads * head_size;
+  cache_t* kdst = reinterpret_cast<cache_t*>(key_cache_) + block_idx * n * block_size;
+  cache_t* vdst = reinterpret_cast<cache_t*>(value_cache_) + block_idx * n * block_size + block_offset;
+  const int runs_per_head = head_size / x;
+
+  for (int t = threadIdx.x; t < nrot + nv; t += blockDim.x) {
+    if (t < nrot) {
+      const int head = t / rot_per_head, r = t - head * rot_per_head;
+      const bool is_k = head >= num_heads;
+      const int hk = head - num_heads;
+      scalar_t* arr = is_k ? key + token * key_stride + (int64_t)hk * head_size
+                           : query + token * query_stride + (int64_t)head * head_size;
+      Vec16<scalar_t> a, b, c, sn;
+      if (NEOX) {   // x = arr[off .. off+8), y = arr[embed + off ..), cos = cache[off ..), sin = cache[embed + off ..)
+        const int off = r * 8;
+        *reinterpret_cast<uint4*>(&a) = *reinterpret_cast<const uint4*>(arr + off);
+        *reinterpret_cast<uint4*>(&b) = *reinterpret_cast<const uint4*>(arr + embed + off);
+        *reinterpret_cast<uint4*>(&c) = *reinterpret_cast<const uint4*>(cache + off);
+        *reinterpret_cast<uint4*>(&sn) = *reinterpret_cast<const uint4*>(cache + embed + off);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float cf = to_float<scalar_t>(c.v[j]), sf = to_float<scalar_t>(sn.v[j]);
+          const float xf = to_float<scalar_t>(a.v[j]), yf = to_float<scalar_t>(b.v[j]);
+          const float xc = to_float<scalar_t>(from_float<scalar_t>(xf * cf));
+          const float ys = to_float<scalar_t>(from_float<scalar_t>(yf * sf));
+          const float yc = to_float<scalar_t>(from_float<scalar_t>(yf * cf));
+          const float xs = to_float<scalar_t>(from_float<scalar_t>(xf * sf));
+          a.v[j] = from_float<scalar_t>(xc - ys);
+          b.v[j] = from_float<scalar_t>(yc + xs);
+        }
+        *reinterpret_cast<uint4*>(arr + off) = *reinterpret_cast<const uint4*>(&a);
+        *reinterpret_cast<uint4*>(arr + embed + off) = *reinterpret_cast<const uint4*>(&b);
+        if (is_k && cached) {
+          const int d0 = off, d1 = embed + off;
+          store_cache8<scalar_t, FP8>(
+              kdst + ((int64_t)(hk * runs_per_head + d0 / x) * block_size + block_offset) * x + d0 % x, a.v, k_scale);
+          store_cache8<scalar_t, FP8>(
+              kdst + ((int64_t)(hk * runs_per_head + d1 / x) * block_size + block_offset) * x + d1 % x, b.v, k_scale);
+        }
+      } else {      // pairs (arr[2i], arr[2i+1]) for i in [r*4, r*4+4): cos = cache[i], sin = cache[embed + i]
+        const int off = r * 4;
+        *reinterpret_cast<uint4*>(&a) = *reinterpret_cast<const uint4*>(arr + 2 * off);
+        *reinterpret_cast<uint2*>(&c) = *reinterpret_cast<const uint2*>(cache + off);
+        *reinterpret_cast<uint2*>(&sn) = *reinterpret_cast<const uint2*>(cache + embed + off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float cf = to_float<scalar_t>(c.v[j]), sf = to_float<scalar_t>(sn.v[j]);
+          const float xf = to_float<scalar_t>(a.v[2 * j]), yf = to_float<scalar_t>(a.v[2 * j + 1]);
+          const float xc = to_float<scalar_t>(from_float<scalar_t>(xf * cf));
+          const float ys = to_float<scalar_t>(from_float<scalar_t>(yf * sf));
+          const float yc = to_float<scalar_t>(from_float<scalar_t>(yf * cf));
+          const float xs = to_float<scalar_t>(from_float<scalar_t>(xf * sf));
+          a.v[2 * j] = from_float<scalar_t>(xc - ys);
+          a.v[2 * j + 1] = from_float<scalar_t>(yc + xs);
+        }
+        *reinterpret_cast<uint4*>(arr + 2 * off) = *reinterpret_cast<const uint4*>(&a);
+        if (is_k && cached) {
+          const int d0 = 2 * off;
+          store_cache8<scalar_t, FP8>(
+              kdst + ((int64_t)(hk * runs_per_head + d0 / x) * block_size + block_offset) * x + d0 % x, a.v, k_scale);
+        }
+      }
+    } else {        // 8 elements of a v head: element (h, d) lands at stride block_size -- inherent to the layout
+      const int i = (t - nrot) * 8;   // h * head_size + d
+      Vec16<scalar_t> a;
+      *reinterpret_cast<uint4*>(&a) = *reinterpret_cast<const uint4*>(value + token * value_stride + i);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (!FP8) {
+          vdst[(int64_t)(i + j) * block_size] = *reinterpret_cast<const cache_t*>(&a.v[j]);
+        } else {
+          reinterpret_cast<uint8_t*>(vdst)[(int64_t)(i + j) * block_size] =
+              float_to_e4m3(to_float<scalar_t>(a.v[j]) / v_scale);
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Flash layout through runtime strides: cache[blk*block_stride + off*page_stride + h*head_stride + d]
 // ---------------------------------------------------------------------------------------------
@@ -227,6 +351,35 @@ extern "C" int vb200_rotary_embedding_reshape_and_cache(
   const int cache_elt = fp8 ? 1 : 2;
   bool vec_ok = (x * cache_elt == 16) && aligned16(key) && aligned16(key_cache) && ((key_stride * 2) % 16 == 0);
   if (fp8) vec_ok = vec_ok && (x == 16);
+  // decode shapes: one 16-byte piece of the token per thread (rope_reshape_and_cache_vec_kernel)
+  const bool pieces = vec_ok && rot_dim == head_size && head_size % 16 == 0 && x % 8 == 0 && aligned16(query) &&
+                      aligned16(value) && aligned16(cos_sin_cache) && query_stride % 8 == 0 && value_stride % 8 == 0;
+  if (pieces) {
+    const int tasks = (num_heads + num_kv_heads) * (is_neox ? head_size / 16 : head_size / 8) + num_kv_heads * head_size / 8;
+    const int threads = tasks >= 512 ? 512 : (tasks + 31) / 32 * 32;
+#define VB_ROPE_VEC(T, NEOX, FP8)                                                                                     \
+  VB_CUDA_CHECK(launch_k(rope_reshape_and_cache_vec_kernel<T, NEOX, FP8>, dim3(num_tokens), dim3(threads), 0, stream, \
+                         positions, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, key_cache,          \
+                         value_cache, slot_mapping, query_stride, key_stride, value_stride, num_heads, num_kv_heads,  \
+                         head_size, block_size, x, k_scale, v_scale))
+#define VB_ROPE_VEC_T(T)                          \
+  if (is_neox) {                                  \
+    if (fp8) VB_ROPE_VEC(T, true, true);          \
+    else VB_ROPE_VEC(T, true, false);             \
+  } else {                                        \
+    if (fp8) VB_ROPE_VEC(T, false, true);         \
+    else VB_ROPE_VEC(T, false, false);            \
+  }
+    if (src_dtype == VB200_F16) {
+      VB_ROPE_VEC_T(__half)
+    } else {
+      VB_ROPE_VEC_T(__nv_bfloat16)
+    }
+#undef VB_ROPE_VEC_T
+#undef VB_ROPE_VEC
+    VB_LAUNCH_CHECK();
+    return 0;
+  }
   const int work = (num_heads + num_kv_heads) * rot_dim / 2;
   const int threads = work >= 256 ? 256 : (work >= 128 ? 128 : 64);
 #define VB_ROPE_CACHE(T, NEOX, FP8)                                                                                  \

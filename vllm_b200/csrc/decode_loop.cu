@@ -4,7 +4,10 @@
 //       replays one CUDA graph with no host round trip;
 //   merge_attn_states       /root/reference/csrc/attention/merge_attn_states.cu:12-89,121-178
 //       log-sum-exp merge of two partial attention results (split-KV / cascade attention).
-// Both are HBM-trivial; one launch each, 16-byte accesses.
+//   greedy_argmax           the greedy branch of /root/reference/vllm/v1/sample/sampler.py:87-96 (`logits.argmax(dim=-1)`)
+//       on the logits in the dtype the lm_head GEMM wrote them (no fp32 copy of a [tokens, vocab] matrix): arg-max
+//       and max per row, first index on ties, NaN counts as the largest value (torch.argmax's rules).
+// All are HBM-trivial; one launch each, 16-byte accesses.
 #include <cmath>
 #include <limits>
 
@@ -74,9 +77,95 @@ __global__ void __launch_bounds__(128) merge_attn_states_kernel(
   if (output_lse != nullptr && pack == 0) output_lse[(size_t)head * num_tokens + token] = logf(out_se) + max_lse;
 }
 
+// One CTA per row of logits.  (value, index) pairs are compared as torch.argmax does: larger value wins, NaN beats
+// every number, the lower index wins a tie.
+__device__ __forceinline__ bool argmax_better(float v, int i, float bv, int bi) {
+  const bool vn = v != v, bn = bv != bv;
+  if (vn || bn) return vn && (!bn || i < bi);
+  return v > bv || (v == bv && i < bi);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) greedy_argmax_kernel(int64_t* __restrict__ out_idx, float* __restrict__ out_val,
+                                                            const T* __restrict__ logits, int vocab,
+                                                            int64_t row_stride, int vec_ok) {
+  pdl_wait();
+  pdl_trigger();
+  constexpr int kPack = 16 / sizeof(T);
+  const T* row = logits + (int64_t)blockIdx.x * row_stride;
+  float bv = -std::numeric_limits<float>::infinity();
+  int bi = 0x7fffffff;
+  if (vec_ok) {
+    const int nvec = vocab / kPack;
+#pragma unroll 4
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      const uint4 u = ldg_stream_v4(row + (int64_t)i * kPack);
+      const T* e = reinterpret_cast<const T*>(&u);
+#pragma unroll
+      for (int j = 0; j < kPack; ++j) {
+        const float v = to_float<T>(e[j]);
+        if (argmax_better(v, i * kPack + j, bv, bi)) { bv = v; bi = i * kPack + j; }
+      }
+    }
+    for (int i = nvec * kPack + threadIdx.x; i < vocab; i += blockDim.x) {
+      const float v = to_float<T>(row[i]);
+      if (argmax_better(v, i, bv, bi)) { bv = v; bi = i; }
+    }
+  } else {
+    for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+      const float v = to_float<T>(row[i]);
+      if (argmax_better(v, i, bv, bi)) { bv = v; bi = i; }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (argmax_better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+  }
+  __shared__ float sv[16];
+  __shared__ int si[16];
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int nw = blockDim.x >> 5;
+    bv = threadIdx.x < nw ? sv[threadIdx.x] : -std::numeric_limits<float>::infinity();
+    bi = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (argmax_better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    if (threadIdx.x == 0) {
+      out_idx[blockIdx.x] = bi;
+      if (out_val != nullptr) out_val[blockIdx.x] = bv;
+    }
+  }
+}
+
 }  // namespace vb200
 
 using namespace vb200;
+
+extern "C" int vb200_greedy_argmax(int64_t* out_idx, float* out_val, const void* logits, int num_rows, int vocab,
+                                   int64_t row_stride, int dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(dtype == VB200_F32 || dtype == VB200_F16 || dtype == VB200_BF16, "greedy_argmax: unsupported logits dtype %d", dtype);
+  VB_CHECK(vocab > 0 && row_stride >= vocab, "greedy_argmax: need vocab > 0 and row_stride >= vocab");
+  if (num_rows <= 0) return 0;
+  const int esz = dtype == VB200_F32 ? 4 : 2;
+  const int vec_ok = ((reinterpret_cast<uintptr_t>(logits) & 15) == 0 && (row_stride * esz) % 16 == 0) ? 1 : 0;
+#define VB_ARGMAX(T)                                                                                               \
+  VB_CUDA_CHECK(launch_k(greedy_argmax_kernel<T>, dim3(num_rows), dim3(512), 0, stream, out_idx, out_val,          \
+                         (const T*)logits, vocab, row_stride, vec_ok))
+  if (dtype == VB200_F32) VB_ARGMAX(float);
+  else if (dtype == VB200_F16) VB_ARGMAX(__half);
+  else VB_ARGMAX(__nv_bfloat16);
+#undef VB_ARGMAX
+  VB_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int vb200_advance_step_flashattn(int num_seqs, int num_queries, int block_size,
                                             int64_t* input_tokens, const int64_t* sampled_token_ids,

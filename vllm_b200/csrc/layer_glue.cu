@@ -13,6 +13,8 @@
 // reduction pass and the write pass (one HBM read per element instead of the reference's two or
 // three), which is what makes these launch-latency-bound rather than bandwidth-bound at decode
 // batch sizes.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "token_ops.cuh"
 
@@ -21,10 +23,6 @@ namespace vb200 {
 constexpr float kFp8MaxG = 448.f;
 constexpr int kGlueThreads = 256;
 constexpr int kMaxVecPerThread = 8;  // rows up to 256 * 8 * 8 = 16384 16-bit elements stay in registers
-
-__device__ __forceinline__ uint8_t quant_clamped_g(float x) {
-  return float_to_e4m3(fmaxf(-kFp8MaxG, fminf(x, kFp8MaxG)));
-}
 
 template <bool IS_MAX>
 __device__ __forceinline__ float block_reduce(float v, float* sm) {
@@ -113,14 +111,15 @@ __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
     s = fmaxf(s / kFp8MaxG, 1.0f / (kFp8MaxG * 512.0f));
     if (threadIdx.x == 0) scales[row] = s;
     uint8_t* o = reinterpret_cast<uint8_t*>(out_) + row * hidden;
+    const RowDivider div(s, amax);
 #pragma unroll
     for (int k = 0; k < kMaxVecPerThread; ++k) {
       const int i = threadIdx.x + k * kGlueThreads;
       if (i < nvec) {
-        union { uint2 u; uint8_t b[8]; } q;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) q.b[j] = quant_clamped_g(zf[k][j] / s);
-        *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+        uint2 q;
+        q.x = e4m3x4_clamped(div(zf[k][0]), div(zf[k][1]), div(zf[k][2]), div(zf[k][3]));
+        q.y = e4m3x4_clamped(div(zf[k][4]), div(zf[k][5]), div(zf[k][6]), div(zf[k][7]));
+        *reinterpret_cast<uint2*>(o + i * 8) = q;
       }
     }
   }
@@ -201,14 +200,15 @@ __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
   s = fmaxf(s / kFp8MaxG, 1.0f / (kFp8MaxG * 512.0f));
   if (threadIdx.x == 0 && part == 0) scales[row] = s;
   uint8_t* o = out + row * d + part * dpart;
+  const RowDivider div(s, amax);
 #pragma unroll
   for (int k = 0; k < kVec; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
-      union { uint2 u; uint8_t b[8]; } q;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) q.b[j] = quant_clamped_g(act[k][j] / s);
-      *reinterpret_cast<uint2*>(o + i * 8) = q.u;
+      uint2 q;
+      q.x = e4m3x4_clamped(div(act[k][0]), div(act[k][1]), div(act[k][2]), div(act[k][3]));
+      q.y = e4m3x4_clamped(div(act[k][4]), div(act[k][5]), div(act[k][6]), div(act[k][7]));
+      *reinterpret_cast<uint2*>(o + i * 8) = q;
     }
   }
 }
@@ -312,6 +312,11 @@ extern "C" int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scal
   const int want = (6 * num_sms() + num_tokens - 1) / num_tokens;
   for (int s = 2; s <= 8; s *= 2)
     if (s <= want && d % (8 * s) == 0 && d / s >= 1024) split = s;
+  static const char* force = getenv("VB200_SILU_SPLIT");   // experiments (benchmarks/bench_layer_glue.py)
+  if (force != nullptr) {
+    const int f = atoi(force);
+    if ((f == 1 || f == 2 || f == 4 || f == 8) && d % (8 * f) == 0 && d / f <= kGlueThreads * (f > 1 ? 4 : 8) * 8) split = f;
+  }
   const dim3 grid((unsigned)num_tokens * split), block(kGlueThreads);
 #define VB_SILU_Q(S)                                                                                               \
   DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k_cluster(silu_mul_quant_kernel<scalar_t, S>, grid, block, 0,             \

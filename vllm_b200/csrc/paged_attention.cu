@@ -513,6 +513,32 @@ __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
 // (heads beyond 32 loop), the reduced row stays in registers between the reduction, the row amax and the fp8 write.
 // Same arithmetic and rounding points as paged_attention_reduce_kernel followed by per_token_quant_kernel: the reduced
 // value is rounded to QT first (what the unfused kernel stores), then amax / scale / true division.
+// A lane owns PER = HEAD_SIZE / 32 CONSECUTIVE elements of its head (one 8-byte load per partition at head size 128,
+// one 4-byte store of the quantised row piece).
+template <typename QT, int PER>
+__device__ __forceinline__ void load_lane_piece(float (&v)[PER], const QT* p) {
+  if constexpr (PER % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < PER; i += 4) {
+      const uint2 u = *reinterpret_cast<const uint2*>(p + i);
+      const QT* e = reinterpret_cast<const QT*>(&u);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[i + j] = to_float<QT>(e[j]);
+    }
+  } else if constexpr (PER % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < PER; i += 2) {
+      const uint32_t u = *reinterpret_cast<const uint32_t*>(p + i);
+      const QT* e = reinterpret_cast<const QT*>(&u);
+      v[i] = to_float<QT>(e[0]);
+      v[i + 1] = to_float<QT>(e[1]);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < PER; ++i) v[i] = to_float<QT>(p[i]);
+  }
+}
+
 template <typename QT, int HEAD_SIZE>
 __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
     uint8_t* __restrict__ out_q, float* __restrict__ out_scales, const float* __restrict__ scale_ub,
@@ -536,10 +562,9 @@ __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
       const int64_t row = (int64_t)seq_idx * num_heads + head;
       const float* ml = max_logits + row * max_num_partitions;
       const float* es = exp_sums + row * max_num_partitions;
-      const QT* tp = tmp_out + row * max_num_partitions * HEAD_SIZE;
+      const QT* tp = tmp_out + row * max_num_partitions * HEAD_SIZE + lane * PER;
       if (np == 1) {
-#pragma unroll
-        for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(tp[lane + 32 * i]);
+        load_lane_piece<QT, PER>(y[hh], tp);
       } else {
         float mg = -INFINITY;
         for (int j = lane; j < np; j += 32) mg = fmaxf(mg, ml[j]);
@@ -551,10 +576,13 @@ __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
         float acc[PER];
 #pragma unroll
         for (int i = 0; i < PER; ++i) acc[i] = 0.f;
+#pragma unroll 4
         for (int j = 0; j < np; ++j) {
           const float w = es[j] * __expf(ml[j] - mg) * inv;
+          float t[PER];
+          load_lane_piece<QT, PER>(t, tp + (int64_t)j * HEAD_SIZE);
 #pragma unroll
-          for (int i = 0; i < PER; ++i) acc[i] = fmaf(to_float<QT>(tp[(int64_t)j * HEAD_SIZE + lane + 32 * i]), w, acc[i]);
+          for (int i = 0; i < PER; ++i) acc[i] = fmaf(t[i], w, acc[i]);
         }
 #pragma unroll
         for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(from_float<QT>(acc[i]));
@@ -570,14 +598,21 @@ __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
   float s = scale_ub ? fminf(amax, *scale_ub) : amax;
   s = fmaxf(s / 448.f, 1.0f / (448.f * 512.0f));
   if (threadIdx.x == 0) out_scales[seq_idx] = s;
+  const RowDivider div(s, amax);
 #pragma unroll
   for (int hh = 0; hh < MAXH; ++hh) {
     const int head = warp + hh * nw;
     if (head < num_heads) {
-      uint8_t* o = out_q + ((int64_t)seq_idx * num_heads + head) * HEAD_SIZE;
+      uint8_t* o = out_q + ((int64_t)seq_idx * num_heads + head) * HEAD_SIZE + lane * PER;
+      if constexpr (PER % 4 == 0) {
 #pragma unroll
-      for (int i = 0; i < PER; ++i)
-        o[lane + 32 * i] = float_to_e4m3(fmaxf(-448.f, fminf(y[hh][i] / s, 448.f)));
+        for (int i = 0; i < PER; i += 4)
+          *reinterpret_cast<uint32_t*>(o + i) =
+              e4m3x4_clamped(div(y[hh][i]), div(y[hh][i + 1]), div(y[hh][i + 2]), div(y[hh][i + 3]));
+      } else {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) o[i] = float_to_e4m3(fmaxf(-448.f, fminf(div(y[hh][i]), 448.f)));
+      }
     }
   }
 }

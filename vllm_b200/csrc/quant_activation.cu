@@ -16,33 +16,42 @@ __device__ __forceinline__ uint8_t quant_clamped(float x) {
   return float_to_e4m3(r);
 }
 
+// INVERTED: x * s (s = 1 / scale, the static path).  Otherwise x / s, through RowDivider when T is a 16-bit type
+// (`row_absmax` finite); fp32 inputs carry 24 significant bits and keep the plain division.
 template <typename T, bool INVERTED>
 __device__ __forceinline__ void quant_row(uint8_t* __restrict__ out, const T* __restrict__ in,
-                                          int64_t n, float s, int tid, int nthreads) {
+                                          int64_t n, float s, int tid, int nthreads, float row_absmax = 0.f) {
   // 16-byte vector path when both pointers are aligned
   constexpr int VE = 16 / sizeof(T);  // elements per 16-byte load (8 for 16-bit, 4 for fp32)
   const bool vec = ((reinterpret_cast<uintptr_t>(in) & 15) == 0) &&
                    ((reinterpret_cast<uintptr_t>(out) & (VE - 1)) == 0);
+  const RowDivider div(s, (sizeof(T) == 2 && !INVERTED) ? row_absmax : __int_as_float(0x7f800000));
   int64_t done = 0;
   if (vec) {
     const int64_t nvec = n / VE;
     for (int64_t i = tid; i < nvec; i += nthreads) {
       union { uint4 u; T e[VE]; } v;
       v.u = *reinterpret_cast<const uint4*>(in + i * VE);
-      union { uint2 u2; uint32_t u1; uint8_t b[8]; } o;
+      float q[VE];
 #pragma unroll
       for (int j = 0; j < VE; ++j) {
         const float x = to_float<T>(v.e[j]);
-        o.b[j] = quant_clamped(INVERTED ? x * s : x / s);
+        q[j] = INVERTED ? x * s : div(x);
       }
-      if (VE == 8) *reinterpret_cast<uint2*>(out + i * VE) = o.u2;
-      else *reinterpret_cast<uint32_t*>(out + i * VE) = o.u1;
+      if (VE == 8) {
+        uint2 o;
+        o.x = e4m3x4_clamped(q[0], q[1], q[2], q[3]);
+        o.y = e4m3x4_clamped(q[VE - 4], q[VE - 3], q[VE - 2], q[VE - 1]);
+        *reinterpret_cast<uint2*>(out + i * VE) = o;
+      } else {
+        *reinterpret_cast<uint32_t*>(out + i * VE) = e4m3x4_clamped(q[0], q[1], q[2], q[3]);
+      }
     }
     done = nvec * VE;
   }
   for (int64_t i = done + tid; i < n; i += nthreads) {
     const float x = to_float<T>(in[i]);
-    out[i] = quant_clamped(INVERTED ? x * s : x / s);
+    out[i] = quant_clamped(INVERTED ? x * s : div(x));
   }
 }
 
@@ -119,7 +128,7 @@ __global__ void __launch_bounds__(256) per_token_quant_kernel(uint8_t* __restric
   float s = scale_ub ? fminf(m, *scale_ub) : m;
   s = fmaxf(s / kFp8Max, 1.0f / (kFp8Max * 512.0f));  // common.cu:66-68, utils.cuh:49-51
   if (threadIdx.x == 0) scales[row] = s;
-  quant_row<T, false>(rout, rin, hidden, s, threadIdx.x, blockDim.x);  // true division (:74)
+  quant_row<T, false>(rout, rin, hidden, s, threadIdx.x, blockDim.x, m);  // the quotient of a true division (:74)
 }
 
 // silu_and_mul: out = T(silu_f32(x)) *_T y

@@ -332,7 +332,8 @@ class Decoder:
 
     def greedy_step(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
         """One decode step with greedy sampling: next token ids [T] int64 (vocab-parallel arg-max)."""
-        logits = self.forward(input_ids, positions, meta).float()
-        val, idx = logits.max(dim=-1)
-        idx = idx + self.tp_rank * self.vocab_shard
-        return merge_vocab_parallel_argmax(val, idx, self.tp)
+        logits = self.forward(input_ids, positions, meta)
+        if self.tp == 1:
+            return ops.greedy_argmax(logits)
+        idx, val = ops.greedy_argmax(logits, return_max=True)
+        return merge_vocab_parallel_argmax(val, idx + self.tp_rank * self.vocab_shard, self.tp)
