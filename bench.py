@@ -557,6 +557,30 @@ def run_gpu_arm(args, rank, world, local_rank):
     dev_us = {name: round(statistics.mean(e[i].elapsed_time(e[i + 1]) for e in dev_evs) * 1e3, 1)
               for i, name in enumerate(("h2d", "graph", "d2h"))}
     barrier()
+    if os.environ.get("VB200_E2E_PROBE") == "1" and rank == 0:
+        # what an isolated replay (the device idle before it) costs over a queued one
+        def timed(n_per_sync, reps, sleep_s=0.0):
+            tot = 0.0
+            for _ in range(reps):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                if sleep_s:
+                    time.sleep(sleep_s)
+                a.record()
+                for _ in range(n_per_sync):
+                    graph.replay()
+                b.record()
+                torch.cuda.synchronize()
+                tot += a.elapsed_time(b)
+            return tot / (reps * n_per_sync)
+        inp.set_host_context(ctx)
+        inp.upload()
+        for name, n, r, sl in (("queued x10", 10, 1, 0.0), ("1 per sync", 1, 8, 0.0), ("2 per sync", 2, 4, 0.0),
+                               ("4 per sync", 4, 2, 0.0), ("1 per sync after 2 ms idle", 1, 6, 0.002)):
+            inp.upload()   # reset the context so that every probe attends over the same lengths
+            torch.cuda.synchronize()
+            print(f"[e2e-probe] {name}: {timed(n, r, sl):.3f} ms per replay", file=sys.stderr, flush=True)
+        inp.set_host_context(ctx + args.warmup + 2 * args.steps + 3)
+        inp.upload()
     clk = clocks.stop() if rank == 0 else None
     if world > 1:
         t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
