@@ -190,8 +190,9 @@ def test_flash_attn_varlen_func_rejects_what_is_not_built():
     bt = torch.zeros(2, 2, dtype=torch.int32, device=DEV)
     sl = torch.ones(2, dtype=torch.int32, device=DEV)
     cu = torch.arange(3, dtype=torch.int32, device=DEV)
-    with pytest.raises(NotImplementedError):
-        flash_attn_varlen_func(q, kc, kc, 2, cu, 16, sl, block_table=bt)           # prefill
+    with pytest.raises(NotImplementedError):                                       # prefill over an fp8 cache
+        flash_attn_varlen_func(q, kc.view(torch.uint8)[..., :128], kc.view(torch.uint8)[..., :128], 2, cu, 16, sl,
+                               block_table=bt, k_descale=torch.ones(1, device=DEV), v_descale=torch.ones(1, device=DEV))
     with pytest.raises(NotImplementedError):
         flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, softcap=30.0)
     with pytest.raises(NotImplementedError):
@@ -201,3 +202,103 @@ def test_flash_attn_varlen_func_rejects_what_is_not_built():
         ops.paged_attention_flash(torch.empty_like(q), q, torch.zeros(4, 32, 2, 128, dtype=torch.bfloat16, device=DEV),
                                   torch.zeros(4, 32, 2, 128, dtype=torch.bfloat16, device=DEV), 0.1, bt, sl, 16, None,
                                   "auto", None, None)                               # block size 32
+
+
+# ---- prefill / chunked prefill / mixed batches over the paged flash-layout cache (csrc/paged_prefill.cu) ----------
+# (query_len, kv_len) per sequence; the first two lists are the reference test's own
+# (/root/reference/tests/kernels/attention/test_flash_attn.py:192-194), tolerances from there (:316-318).
+VARLEN_CASES = [
+    [(1, 1328), (5, 18), (129, 463)],
+    [(1, 523), (1, 37), (1, 2011)],
+    [(64, 64), (65, 65), (200, 200), (1, 1)],            # pure prefill, tile edges
+    [(128, 1024), (63, 127), (300, 4000), (17, 17)],     # chunked prefill deep into a long context
+    [(700, 700)],
+]
+
+
+def _varlen_inputs(seq_lens, H, Hkv, D, bs, dtype, layout, nb=2048):
+    query_lens = [x[0] for x in seq_lens]
+    kv_lens = [x[1] for x in seq_lens]
+    q = torch.randn(sum(query_lens), H, D).to(dtype)
+    kc = torch.randn(nb, bs, Hkv, D).to(dtype)
+    vc = torch.randn(nb, bs, Hkv, D).to(dtype)
+    maxb = (max(kv_lens) + bs - 1) // bs
+    bt = torch.randint(0, nb, (len(seq_lens), maxb), dtype=torch.int32)
+    cu = torch.tensor([0] + query_lens, dtype=torch.int32).cumsum(0).to(torch.int32)
+    kd, vd = kc.to(DEV), vc.to(DEV)
+    if layout == "HND":   # physical [nb, H, bs, D], logical view [nb, bs, H, D]
+        kd = kd.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        vd = vd.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+    return q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens
+
+
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("block_size", [16, 32])
+@pytest.mark.parametrize("heads", [(4, 4), (8, 2), (16, 2)])
+@pytest.mark.parametrize("head_size", [64, 128, 256])
+@pytest.mark.parametrize("seq_lens", VARLEN_CASES, ids=lambda c: f"n{len(c)}q{max(x[0] for x in c)}")
+def test_flash_attn_varlen_paged(seq_lens, head_size, heads, block_size, dtype, layout):
+    from vllm_b200 import _custom_ops as ops
+    H, Hkv = heads
+    seed_all(len(seq_lens) * 100 + head_size + H)
+    q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens = _varlen_inputs(seq_lens, H, Hkv, head_size, block_size, dtype, layout)
+    scale = float(head_size ** -0.5)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    kvl = torch.tensor(kv_lens, dtype=torch.int32, device=DEV)
+    ops.flash_attn_varlen_paged(out, q.to(DEV), kd, vd, cu.to(DEV), kvl, bt.to(DEV), scale, True, max(query_lens))
+    torch.cuda.synchronize()
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+    if max(query_lens) <= 64:   # the same batch on the 128-row tiles (max_seqlen_q unknown)
+        out2 = torch.full_like(q, float("nan"), device=DEV)
+        ops.flash_attn_varlen_paged(out2, q.to(DEV), kd, vd, cu.to(DEV), kvl, bt.to(DEV), scale, True)
+        torch.testing.assert_close(out2.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+
+
+def test_flash_attn_varlen_paged_non_causal_and_backend_prefill():
+    """causal=False attends every cached key; the V1-style backend routes a mixed prefill + decode batch through
+    flash_attn_varlen_func (reshape_and_cache_flash first, then the variable-length kernel)."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.attention.flash_backend import (B200FlashAttentionBackend, B200FlashAttentionImpl,
+                                                   B200FlashAttentionMetadata)
+    seed_all(5)
+    H, Hkv, D, bs, dtype = 8, 2, 128, 16, torch.bfloat16
+    seq_lens = [(70, 300), (9, 9)]
+    q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens = _varlen_inputs(seq_lens, H, Hkv, D, bs, dtype, "NHD", nb=256)
+    scale = float(D ** -0.5)
+    out = torch.empty_like(q, device=DEV)
+    ops.flash_attn_varlen_paged(out, q.to(DEV), kd, vd, cu.to(DEV), torch.tensor(kv_lens, dtype=torch.int32, device=DEV),
+                                bt.to(DEV), scale, False)
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale, causal=False)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+
+    # backend: sequence 0 prefills 40 new tokens on top of 100 cached ones, sequence 1 decodes one token at 57
+    nb = 64
+    kv = B200FlashAttentionBackend.allocate_kv_cache(nb, bs, Hkv, D, dtype, DEV)
+    kv.copy_(torch.randn(2, nb, bs, Hkv, D).to(dtype))
+    lens = [(40, 140), (1, 57)]
+    T = sum(x[0] for x in lens)
+    perm = torch.randperm(nb)
+    bt2 = torch.stack([perm[:16], perm[16:32]]).to(torch.int32)
+    qkv = torch.randn(T, H + 2 * Hkv, D).to(dtype)
+    slots = []
+    for s, (ql, kl) in enumerate(lens):
+        for pos in range(kl - ql, kl):
+            slots.append(int(bt2[s, pos // bs]) * bs + pos % bs)
+    meta = B200FlashAttentionMetadata(
+        num_actual_tokens=T, max_query_len=40, query_start_loc=torch.tensor([0, 40, 41], dtype=torch.int32, device=DEV),
+        max_seq_len=140, seq_lens=torch.tensor([140, 57], dtype=torch.int32, device=DEV), block_table=bt2.to(DEV),
+        slot_mapping=torch.tensor(slots, dtype=torch.int64, device=DEV))
+    impl = B200FlashAttentionImpl(H, D, scale, Hkv)
+
+    class _Layer:
+        _k_scale = torch.ones(1, device=DEV)
+        _v_scale = torch.ones(1, device=DEV)
+    qd = qkv.to(DEV)
+    out2 = torch.empty(T, H, D, dtype=dtype, device=DEV)
+    impl.forward(_Layer(), qd[:, :H], qd[:, H:H + Hkv], qd[:, H + Hkv:], kv, meta, output=out2)
+    torch.cuda.synchronize()
+    kc2, vc2 = kv[0].cpu(), kv[1].cpu()   # after the write: what the oracle gathers from
+    want2 = oattn.flash_attn_varlen_paged(qkv[:, :H].contiguous(), kc2, vc2, [40, 1], [140, 57], bt2, scale)
+    torch.testing.assert_close(out2.cpu().float(), want2.float(), atol=1.5e-2, rtol=1e-2)

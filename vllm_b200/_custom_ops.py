@@ -106,6 +106,47 @@ def paged_attention_v1(
             max(partition_size, 0), ptr(ws), ws_bytes, stream()))
 
 
+def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                            cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, block_table: torch.Tensor,
+                            scale: float, causal: bool = True, max_seqlen_q: int = 0) -> None:
+    """Variable-length causal attention over the flash cache layout (include/vllm_b200.h
+    vb200_flash_attn_varlen_paged): prefill / chunked prefill / mixed batches of the V1 backend's
+    flash_attn_varlen_func call (vllm/v1/attention/backends/flash_attn.py:497-519).  query / out [total_q, num_heads,
+    head_size]; key_cache / value_cache the `[num_blocks, block_size, num_kv_heads, head_size]` halves (NHD or HND
+    strides) holding every sequence's tokens, the new ones included; cu_seqlens_q int32 [num_seqs + 1]; seqused_k
+    int32 [num_seqs]; block_table int32 [num_seqs, max_blocks]; max_seqlen_q the longest query length when the caller
+    knows it (0 = unknown)."""
+    require_cuda(out, query, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table)
+    if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
+        raise RuntimeError("query must be [total_q, num_heads, head_size] with contiguous heads")
+    if out.shape != query.shape or out.dtype != query.dtype or out.stride(2) != 1 or out.stride(1) != out.shape[2]:
+        raise RuntimeError("out must have query's shape and dtype, with contiguous heads")
+    if key_cache.dim() != 4 or key_cache.shape != value_cache.shape or key_cache.stride(3) != 1 or any(
+            key_cache.size(i) > 1 and key_cache.stride(i) != value_cache.stride(i) for i in range(4)):
+        raise RuntimeError("flash_attn_varlen_paged: key_cache / value_cache must be [num_blocks, block_size, "
+                           "num_kv_heads, head_size] views with equal strides and a contiguous head dimension")
+    if key_cache.dtype != query.dtype:
+        raise NotImplementedError("flash_attn_varlen_paged: the cache must have the query's dtype (fp8 caches are "
+                                  "read by the decode kernel only)")
+    for name, t in (("cu_seqlens_q", cu_seqlens_q), ("seqused_k", seqused_k), ("block_table", block_table)):
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise RuntimeError(f"{name} must be a contiguous int32 tensor")
+    num_seqs = seqused_k.shape[0]
+    if cu_seqlens_q.numel() != num_seqs + 1 or block_table.dim() != 2 or block_table.shape[0] != num_seqs:
+        raise RuntimeError("cu_seqlens_q must hold num_seqs + 1 offsets and block_table num_seqs rows")
+    num_blocks, block_size, num_kv_heads, head_size = key_cache.shape
+    total_q, num_heads, hs = query.shape
+    if hs != head_size:
+        raise RuntimeError(f"head size mismatch: query {hs}, cache {head_size}")
+    strides = [key_cache.stride(i) if key_cache.size(i) > 1 else head_size for i in range(3)]
+    with _device_of(query):
+        check(load().vb200_flash_attn_varlen_paged(
+            ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), ptr(cu_seqlens_q), ptr(seqused_k), ptr(block_table),
+            num_seqs, total_q, num_heads, num_kv_heads, head_size, block_size, block_table.stride(0), int(max_seqlen_q),
+            float(scale), 1 if causal else 0, dtype_enum(query.dtype), query.stride(0) if total_q > 1 else num_heads * head_size,
+            out.stride(0) if total_q > 1 else num_heads * head_size, strides[0], strides[1], strides[2], stream()))
+
+
 def paged_attention_v1_quant(
     query: torch.Tensor,
     key_cache: torch.Tensor,

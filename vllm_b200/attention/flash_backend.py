@@ -12,8 +12,8 @@ Mirrors the pieces of /root/reference/vllm/v1/attention/backends/flash_attn.py a
   * `flash_attn_varlen_func`         that call's signature for the decode case (max_seqlen_q == 1), on this package's
                                      vb200_paged_attention_flash kernel (TMA tensor-map loads of the cache as it lies,
                                      csrc/paged_attention_flash.cuh).
-Prefill (max_seqlen_q > 1), sliding windows, soft-capping and cascade attention are outside the decode hot path and
-raise.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3, :478-486); this kernel keeps the query in
+Prefill / chunked prefill / mixed batches (max_seqlen_q > 1) run on the variable-length kernel of
+csrc/paged_prefill.cu (16-bit caches).  Sliding windows, soft-capping and cascade attention raise.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3, :478-486); this kernel keeps the query in
 bf16/f16 and folds the per-tensor k / v descales into the fp32 logits / output, which is the dequantised result the
 parity bar is stated against.
 """
@@ -47,17 +47,16 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
                            q_descale=None, k_descale: Optional[torch.Tensor] = None,
                            v_descale: Optional[torch.Tensor] = None, scheduler_metadata=None, fa_version: int = 3,
                            num_splits: int = 0, cu_seqlens_k=None) -> torch.Tensor:
-    """The decode case of vllm.vllm_flash_attn.flash_attn_varlen_func as flash_attn.py:497-519 calls it: q
-    [num_seqs, num_heads, head_size] (one token per sequence, cu_seqlens_q = 0..num_seqs), k / v the two halves of the
+    """vllm.vllm_flash_attn.flash_attn_varlen_func as flash_attn.py:497-519 calls it.  Decode (max_seqlen_q == 1): q
+    [num_seqs, num_heads, head_size] (one token per sequence, cu_seqlens_q = 0..num_seqs) on the HBM-roofline decode
+    kernel; anything else (prefill, chunked prefill, mixed batches: q [total_q, ...] split by cu_seqlens_q, bottom-right
+    aligned causal mask against seqused_k) on the variable-length tensor-core kernel.  k / v the two halves of the
     paged cache `[num_blocks, block_size, num_kv_heads, head_size]` (any stride order with a contiguous head
     dimension), block_table int32 [num_seqs, max_blocks], seqused_k int32 [num_seqs].  k_descale / v_descale: fp32
     per-tensor scales of an fp8 cache (the reference passes them expanded to [num_seqs, num_kv_heads]; element 0 is
     used)."""
     if block_table is None:
         raise NotImplementedError("flash_attn_varlen_func: only the paged-KV (block_table) form is built")
-    if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0]:
-        raise NotImplementedError("flash_attn_varlen_func: decode only (one query token per sequence); prefill is "
-                                  "outside the hot path")
     if softcap:
         raise NotImplementedError("flash_attn_varlen_func: logits soft-capping is not built")
     if window_size is not None and tuple(window_size) not in ((-1, -1), (-1, 0)):
@@ -71,6 +70,17 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         softmax_scale = q.shape[-1] ** -0.5
     if out is None:
         out = torch.empty_like(q)
+    if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0]:
+        # prefill / chunked prefill / mixed batch: the variable-length kernel (csrc/paged_prefill.cu)
+        if fp8:
+            raise NotImplementedError("flash_attn_varlen_func: prefill over an fp8 cache is not built (decode is)")
+        if alibi_slopes is not None:
+            raise NotImplementedError("flash_attn_varlen_func: ALiBi is built for the decode case only")
+        if cu_seqlens_q is None:
+            raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
+        ops.flash_attn_varlen_paged(out, q, k, v, cu_seqlens_q, seqused_k, block_table, softmax_scale, causal,
+                                    int(max_seqlen_q))
+        return out
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None
     ops.paged_attention_flash(out, q, k, v, softmax_scale, block_table, seqused_k, int(max_seqlen_k), alibi_slopes,

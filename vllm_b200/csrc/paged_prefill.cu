@@ -1,0 +1,397 @@
+// Variable-length (prefill / chunked-prefill / mixed) causal attention over the paged FLASH-layout KV cache
+// ("prefill-with-paged-KV"): the general case of the call the reference's V1 backend makes,
+//   flash_attn_varlen_func(q, k=key_cache, v=value_cache, cu_seqlens_q, seqused_k, block_table, causal=True)
+//   /root/reference/vllm/v1/attention/backends/flash_attn.py:497-519
+// q holds every sequence's NEW tokens back to back (cu_seqlens_q), the cache already holds ALL of a sequence's keys
+// and values including the new ones (reshape_and_cache_flash runs first, :448-463), and query token i of a
+// sequence with q_len new tokens out of kv_len attends keys 0 .. kv_len - q_len + i (bottom-right aligned causal
+// mask, flash-attn's convention).  The decode case (q_len == 1 everywhere) has its own HBM-roofline kernel
+// (paged_attention_flash.cuh); this one is the compute-shaped case.
+//
+// One CTA = 128 (or 64, for short chunks) query rows of one sequence x one query head; 4 warps x 32 (16) rows.
+// FlashAttention-2 structure on the warp-level tensor-core path (mma.sync m16n8k16, fp32 accumulate): K / V tiles
+// of 64 tokens are gathered page by page through the block table with cp.async (16-byte chunks, XOR-swizzled
+// rows, two stages), every K / V fragment read from shared memory feeds both of a warp's row tiles, S = Q K^T and
+// O += P V never leave registers, online softmax in the exp2 domain.  Tiles that lie entirely above the causal
+// diagonal are never loaded; a sequence's tiles are issued deepest-context first.
+#include <cmath>
+
+#include "common.cuh"
+
+namespace vb200 {
+
+namespace prefill {
+
+constexpr int BN = 64, NWARPS = 4, NTHREADS = NWARPS * 32;
+
+struct Params {
+  void* out;
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int* block_table;
+  const int* cu_seqlens_q;
+  const int* seqused_k;
+  int num_seqs, num_heads, num_kv_heads, max_blocks_per_seq, block_size;
+  int64_t q_stride, o_stride;                       // elements between consecutive tokens
+  int64_t block_stride, token_stride, head_stride;  // cache, elements
+  float scale_log2;                                 // softmax scale * log2(e)
+  int causal;
+};
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int n = valid ? 16 : 0;   // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+
+template <typename T>
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma16816<__half>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0,
+                                                        uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi);
+template <>
+__device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// byte offset of 16-byte chunk `c` of row `r` in a tile whose rows hold D 16-bit elements
+template <int D>
+__device__ __forceinline__ uint32_t swz(int r, int c) {
+  return (uint32_t)(r * (D * 2) + ((c ^ (r & 7)) << 4));
+}
+
+template <typename T, int D, int MT>
+__global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Params p) {
+  pdl_wait();
+  pdl_trigger();
+  constexpr int BM = 16 * MT * NWARPS;             // query rows per CTA: every warp owns MT 16-row tiles
+  constexpr int CPR = D / 8;                       // 16-byte chunks per row
+  constexpr int KV_PASSES = BN * CPR / NTHREADS;   // chunks of one K (or V) tile per thread
+  constexpr int Q_PASSES = BM * CPR / NTHREADS;
+  static_assert(BN * CPR % NTHREADS == 0 && D % 16 == 0, "tile / head size");
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t sQ = (uint32_t)__cvta_generic_to_shared(smem);
+  const uint32_t sK = sQ + BM * D * 2;             // 2 stages
+  const uint32_t sV = sK + 2 * BN * D * 2;         // 2 stages
+
+  // which (sequence, BM-row tile) is this CTA?  grid.x covers an upper bound of the tile count
+  int t = blockIdx.x, seq = 0, q0 = 0, q_len = 0;
+  for (; seq < p.num_seqs; ++seq) {
+    q0 = p.cu_seqlens_q[seq];
+    q_len = p.cu_seqlens_q[seq + 1] - q0;
+    const int nt = (q_len + BM - 1) / BM;
+    if (t < nt) {
+      t = nt - 1 - t;                              // the tiles with the most keys first
+      break;
+    }
+    t -= nt;
+  }
+  if (seq >= p.num_seqs) return;
+  const int m0 = t * BM;
+  const int kv_len = p.seqused_k[seq];
+  const int head = blockIdx.y;
+  const int kvh = head / (p.num_heads / p.num_kv_heads);
+  const int shift = kv_len - q_len;                // query row i sees keys 0 .. shift + i
+  const int rows_here = min(BM, q_len - m0);
+  // keys this tile can see at all
+  int n_keys = p.causal ? min(kv_len, shift + m0 + rows_here) : kv_len;
+  if (n_keys < 0) n_keys = 0;
+  const int n_tiles = (n_keys + BN - 1) / BN;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, tq = lane & 3;
+  const T* qg = reinterpret_cast<const T*>(p.q) + (int64_t)q0 * p.q_stride + (int64_t)head * D;
+  const T* kc = reinterpret_cast<const T*>(p.k_cache) + (int64_t)kvh * p.head_stride;
+  const T* vc = reinterpret_cast<const T*>(p.v_cache) + (int64_t)kvh * p.head_stride;
+  const int* bt = p.block_table + (int64_t)seq * p.max_blocks_per_seq;
+
+  // ---- Q tile -> shared memory
+#pragma unroll
+  for (int i = 0; i < Q_PASSES; ++i) {
+    const int idx = tid + i * NTHREADS;
+    const int r = idx / CPR, c = idx % CPR;
+    const bool ok = m0 + r < q_len;
+    cp_async16(sQ + swz<D>(r, c), qg + (int64_t)(ok ? m0 + r : 0) * p.q_stride + c * 8, ok);
+  }
+  auto load_kv = [&](int j, int stage) {
+    const uint32_t dk = sK + stage * (BN * D * 2), dv = sV + stage * (BN * D * 2);
+#pragma unroll
+    for (int i = 0; i < KV_PASSES; ++i) {
+      const int idx = tid + i * NTHREADS;
+      const int r = idx / CPR, c = idx % CPR;
+      const int n = j * BN + r;
+      const bool ok = n < n_keys;
+      int64_t off = 0;
+      if (ok) {
+        const int page = bt[n / p.block_size];
+        off = (int64_t)page * p.block_stride + (int64_t)(n % p.block_size) * p.token_stride + c * 8;
+      }
+      cp_async16(dk + swz<D>(r, c), kc + off, ok);
+      cp_async16(dv + swz<D>(r, c), vc + off, ok);
+    }
+  };
+  if (n_tiles > 0) load_kv(0, 0);
+  cp_commit();
+
+  float o[MT][D / 8][4];
+  float row_max[MT][2], row_sum[MT][2];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) o[mt][i][0] = o[mt][i][1] = o[mt][i][2] = o[mt][i][3] = 0.f;
+    row_max[mt][0] = row_max[mt][1] = -INFINITY;
+    row_sum[mt][0] = row_sum[mt][1] = 0.f;
+  }
+  // Q fragments stay in registers when one 16-row tile per warp leaves room; otherwise they are re-read per k-step
+  constexpr bool QREG = MT == 1 && D <= 128;
+  uint32_t qf[QREG ? D / 16 : 1][4];
+  const int wrow = warp * 16 * MT;                 // first row of this warp inside the CTA tile
+
+  for (int j = 0; j < n_tiles; ++j) {
+    const int stage = j & 1;
+    if (j + 1 < n_tiles) load_kv(j + 1, stage ^ 1);
+    cp_commit();
+    cp_wait<1>();
+    __syncthreads();
+    if (QREG && j == 0) {
+#pragma unroll
+      for (int ks = 0; ks < (QREG ? D / 16 : 1); ++ks)
+        ldsm_x4(sQ + swz<D>(wrow + (lane & 15), ks * 2 + (lane >> 4)), qf[ks]);
+    }
+    const uint32_t tk = sK + stage * (BN * D * 2), tv = sV + stage * (BN * D * 2);
+    // ---- S = Q K^T  (16 * MT rows x 64 keys per warp): a K fragment feeds MT row tiles
+    float s[MT][BN / 8][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int i = 0; i < BN / 8; ++i) s[mt][i][0] = s[mt][i][1] = s[mt][i][2] = s[mt][i][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+      uint32_t qa[MT][4];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        if (QREG) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) qa[mt][e] = qf[QREG ? ks : 0][e];
+        } else {
+          ldsm_x4(sQ + swz<D>(wrow + mt * 16 + (lane & 15), ks * 2 + (lane >> 4)), qa[mt]);
+        }
+      }
+#pragma unroll
+      for (int np = 0; np < BN / 16; ++np) {
+        uint32_t b[4];
+        ldsm_x4(tk + swz<D>(np * 16 + (lane & 7) + ((lane >> 4) << 3), ks * 2 + ((lane >> 3) & 1)), b);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          mma16816<T>(s[mt][2 * np], qa[mt], b[0], b[1]);
+          mma16816<T>(s[mt][2 * np + 1], qa[mt], b[2], b[3]);
+        }
+      }
+    }
+    // ---- mask (only tiles that touch the diagonal or the end of the sequence)
+    const int n_base = j * BN;
+    const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + m0 + wrow);
+    if (need_mask) {
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int i = 0; i < BN / 8; ++i)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int n = n_base + i * 8 + 2 * tq + (e & 1);
+            const int row = m0 + wrow + mt * 16 + g + ((e >> 1) << 3);
+            const bool vis = n < kv_len && (!p.causal || n <= shift + row);
+            if (!vis) s[mt][i][e] = -INFINITY;
+          }
+    }
+    // ---- online softmax (exp2 domain)
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      float mx[2] = {row_max[mt][0], row_max[mt][1]};
+#pragma unroll
+      for (int i = 0; i < BN / 8; ++i) {
+        mx[0] = fmaxf(mx[0], fmaxf(s[mt][i][0], s[mt][i][1]));
+        mx[1] = fmaxf(mx[1], fmaxf(s[mt][i][2], s[mt][i][3]));
+      }
+      float alpha[2], mscaled[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+        mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
+        mscaled[h] = mx[h] == -INFINITY ? 0.f : mx[h] * p.scale_log2;     // a fully masked row so far: exp2(-inf) = 0
+        alpha[h] = exp2f(row_max[mt][h] * p.scale_log2 - mscaled[h]);     // row_max = -inf -> 0
+        row_max[mt][h] = mx[h];
+        row_sum[mt][h] *= alpha[h];
+      }
+#pragma unroll
+      for (int i = 0; i < D / 8; ++i) {
+        o[mt][i][0] *= alpha[0];
+        o[mt][i][1] *= alpha[0];
+        o[mt][i][2] *= alpha[1];
+        o[mt][i][3] *= alpha[1];
+      }
+#pragma unroll
+      for (int i = 0; i < BN / 8; ++i) {
+        s[mt][i][0] = exp2f(fmaf(s[mt][i][0], p.scale_log2, -mscaled[0]));
+        s[mt][i][1] = exp2f(fmaf(s[mt][i][1], p.scale_log2, -mscaled[0]));
+        s[mt][i][2] = exp2f(fmaf(s[mt][i][2], p.scale_log2, -mscaled[1]));
+        s[mt][i][3] = exp2f(fmaf(s[mt][i][3], p.scale_log2, -mscaled[1]));
+        row_sum[mt][0] += s[mt][i][0] + s[mt][i][1];
+        row_sum[mt][1] += s[mt][i][2] + s[mt][i][3];
+      }
+    }
+    // ---- O += P V: a V fragment feeds MT row tiles
+#pragma unroll
+    for (int kk = 0; kk < BN / 16; ++kk) {
+      uint32_t a[MT][4];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        a[mt][0] = pack2<T>(s[mt][2 * kk][0], s[mt][2 * kk][1]);
+        a[mt][1] = pack2<T>(s[mt][2 * kk][2], s[mt][2 * kk][3]);
+        a[mt][2] = pack2<T>(s[mt][2 * kk + 1][0], s[mt][2 * kk + 1][1]);
+        a[mt][3] = pack2<T>(s[mt][2 * kk + 1][2], s[mt][2 * kk + 1][3]);
+      }
+#pragma unroll
+      for (int dp = 0; dp < D / 16; ++dp) {
+        uint32_t b[4];
+        ldsm_x4_trans(tv + swz<D>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), dp * 2 + (lane >> 4)), b);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          mma16816<T>(o[mt][2 * dp], a[mt], b[0], b[1]);
+          mma16816<T>(o[mt][2 * dp + 1], a[mt], b[2], b[3]);
+        }
+      }
+    }
+    __syncthreads();   // every warp is done with this stage before the next iteration's loads overwrite it
+  }
+  cp_wait<0>();
+
+  // ---- epilogue: O / l  ->  out
+  T* og = reinterpret_cast<T*>(p.out) + (int64_t)q0 * p.o_stride + (int64_t)head * D;
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      float l = row_sum[mt][h];
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
+      const int row = m0 + wrow + mt * 16 + g + h * 8;
+      if (row < q_len) {
+        const float inv = l > 0.f ? 1.f / l : 0.f;
+        T* orow = og + (int64_t)row * p.o_stride;
+#pragma unroll
+        for (int i = 0; i < D / 8; ++i)
+          *reinterpret_cast<uint32_t*>(orow + i * 8 + 2 * tq) =
+              pack2<T>(o[mt][i][2 * h] * inv, o[mt][i][2 * h + 1] * inv);
+      }
+    }
+  }
+}
+
+template <typename T, int D, int MT>
+static int launch(const Params& p, int total_q, cudaStream_t stream) {
+  auto kern = paged_prefill_flash_kernel<T, D, MT>;
+  constexpr int BM = 16 * MT * NWARPS;
+  const size_t smem = (size_t)(BM + 4 * BN) * D * 2;
+  if (smem > 48 * 1024)
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // every sequence adds at most one partial tile: an upper bound that needs no host read of cu_seqlens_q
+  const int max_tiles = total_q / BM + p.num_seqs;
+  VB_CUDA_CHECK(launch_k(kern, dim3(max_tiles, p.num_heads), dim3(NTHREADS), smem, stream, p));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+// 128-row tiles (two 16-row tiles per warp: every K / V fragment read from shared memory feeds two MMAs' worth of
+// rows) once some sequence has more than 64 new tokens; 64-row tiles for short chunks and for head size 256, whose
+// accumulators leave no room for the second tile.
+template <typename T>
+static int dispatch(const Params& p, int head_size, int total_q, int max_seqlen_q, cudaStream_t stream) {
+  const bool big = max_seqlen_q > 64;
+  switch (head_size) {
+    case 64: return big ? launch<T, 64, 2>(p, total_q, stream) : launch<T, 64, 1>(p, total_q, stream);
+    case 128: return big ? launch<T, 128, 2>(p, total_q, stream) : launch<T, 128, 1>(p, total_q, stream);
+    case 256: return launch<T, 256, 1>(p, total_q, stream);
+    default: break;
+  }
+  VB_CHECK(false, "flash_attn_varlen_paged: head size %d is not supported (64, 128, 256)", head_size);
+  return 0;
+}
+
+}  // namespace prefill
+}  // namespace vb200
+
+using namespace vb200;
+
+extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                             const int32_t* cu_seqlens_q, const int32_t* seqused_k,
+                                             const int32_t* block_table, int num_seqs, int total_q, int num_heads,
+                                             int num_kv_heads, int head_size, int block_size,
+                                             int max_num_blocks_per_seq, int max_seqlen_q, float scale, int causal,
+                                             int dtype,
+                                             int64_t q_stride, int64_t out_stride, int64_t block_stride,
+                                             int64_t token_stride, int64_t head_stride, vb200_stream_t stream) {
+  VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "flash_attn_varlen_paged: dtype must be f16 or bf16");
+  VB_CHECK(num_kv_heads > 0 && num_heads % num_kv_heads == 0, "flash_attn_varlen_paged: num_heads %% num_kv_heads != 0");
+  VB_CHECK(block_size > 0, "flash_attn_varlen_paged: bad block_size %d", block_size);
+  VB_CHECK(((q_stride | out_stride | block_stride | token_stride | head_stride) & 7) == 0,
+           "flash_attn_varlen_paged: strides must be multiples of 8 elements (16 bytes)");
+  VB_CHECK(((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(query) |
+             reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15) == 0,
+           "flash_attn_varlen_paged: tensors must be 16-byte aligned");
+  if (num_seqs <= 0 || total_q <= 0) return 0;
+  prefill::Params p;
+  p.out = out;
+  p.q = query;
+  p.k_cache = key_cache;
+  p.v_cache = value_cache;
+  p.block_table = block_table;
+  p.cu_seqlens_q = cu_seqlens_q;
+  p.seqused_k = seqused_k;
+  p.num_seqs = num_seqs;
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.max_blocks_per_seq = max_num_blocks_per_seq;
+  p.block_size = block_size;
+  p.q_stride = q_stride;
+  p.o_stride = out_stride;
+  p.block_stride = block_stride;
+  p.token_stride = token_stride;
+  p.head_stride = head_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.causal = causal;
+  if (max_seqlen_q <= 0) max_seqlen_q = total_q;   // unknown: assume long chunks
+  if (dtype == VB200_F16) return prefill::dispatch<__half>(p, head_size, total_q, max_seqlen_q, (cudaStream_t)stream);
+  return prefill::dispatch<__nv_bfloat16>(p, head_size, total_q, max_seqlen_q, (cudaStream_t)stream);
+}
