@@ -235,7 +235,7 @@ def _varlen_inputs(seq_lens, H, Hkv, D, bs, dtype, layout, nb=2048):
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("block_size", [16, 32])
-@pytest.mark.parametrize("heads", [(4, 4), (8, 2), (16, 2)])
+@pytest.mark.parametrize("heads", [(4, 4), (8, 2), (16, 2), (14, 2)])
 @pytest.mark.parametrize("head_size", [64, 128, 256])
 @pytest.mark.parametrize("seq_lens", VARLEN_CASES, ids=lambda c: f"n{len(c)}q{max(x[0] for x in c)}")
 def test_flash_attn_varlen_paged(seq_lens, head_size, heads, block_size, dtype, layout):

@@ -61,7 +61,7 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         raise NotImplementedError("flash_attn_varlen_func: logits soft-capping is not built")
     if window_size is not None and tuple(window_size) not in ((-1, -1), (-1, 0)):
         raise NotImplementedError("flash_attn_varlen_func: sliding windows are not built")
-    if cu_seqlens_q is not None and cu_seqlens_q.numel() != q.shape[0] + 1:
+    if cu_seqlens_q is not None and cu_seqlens_q.numel() != seqused_k.shape[0] + 1:
         raise RuntimeError("cu_seqlens_q must hold num_seqs + 1 offsets")
     fp8 = k.element_size() == 1
     if fp8 and (k_descale is None or v_descale is None):

@@ -8,7 +8,8 @@
 // mask, flash-attn's convention).  The decode case (q_len == 1 everywhere) has its own HBM-roofline kernel
 // (paged_attention_flash.cuh); this one is the compute-shaped case.
 //
-// One CTA = 128 (or 64, for short chunks) query rows of one sequence x one query head; 4 warps x 32 (16) rows.
+// One CTA = 128 (or 64, for short chunks) rows of one sequence x one KV head, a row being a (token, query head of
+// that KV head's GQA group) pair; 4 warps x 32 (16) rows.
 // FlashAttention-2 structure on the warp-level tensor-core path (mma.sync m16n8k16, fp32 accumulate): K / V tiles
 // of 64 tokens are gathered page by page through the block table with cp.async (16-byte chunks, XOR-swizzled
 // rows, two stages), every K / V fragment read from shared memory feeds both of a warp's row tiles, S = Q K^T and
@@ -32,7 +33,9 @@ struct Params {
   const int* block_table;
   const int* cu_seqlens_q;
   const int* seqused_k;
-  int num_seqs, num_heads, num_kv_heads, max_blocks_per_seq, block_size;
+  int num_seqs, num_heads, num_kv_heads, max_blocks_per_seq;
+  int block_shift;                                  // log2(block_size)
+  int group;                                        // query heads per kv head
   int64_t q_stride, o_stride;                       // elements between consecutive tokens
   int64_t block_stride, token_stride, head_stride;  // cache, elements
   float scale_log2;                                 // softmax scale * log2(e)
@@ -85,6 +88,12 @@ __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // byte offset of 16-byte chunk `c` of row `r` in a tile whose rows hold D 16-bit elements
 template <int D>
 __device__ __forceinline__ uint32_t swz(int r, int c) {
@@ -105,12 +114,16 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   const uint32_t sK = sQ + BM * D * 2;             // 2 stages
   const uint32_t sV = sK + 2 * BN * D * 2;         // 2 stages
 
+  // The rows of a tile are (token, query head of this kv head's group) pairs, token-major: row r of a sequence is
+  // token r / G, head kvh * G + r % G -- a K / V tile is loaded once for the whole GQA group, and a decode row of a
+  // mixed batch brings G rows instead of one.
   // which (sequence, BM-row tile) is this CTA?  grid.x covers an upper bound of the tile count
+  const int G = p.group;
   int t = blockIdx.x, seq = 0, q0 = 0, q_len = 0;
   for (; seq < p.num_seqs; ++seq) {
     q0 = p.cu_seqlens_q[seq];
     q_len = p.cu_seqlens_q[seq + 1] - q0;
-    const int nt = (q_len + BM - 1) / BM;
+    const int nt = (q_len * G + BM - 1) / BM;
     if (t < nt) {
       t = nt - 1 - t;                              // the tiles with the most keys first
       break;
@@ -119,30 +132,32 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   }
   if (seq >= p.num_seqs) return;
   const int m0 = t * BM;
+  const int n_rows = q_len * G;
   const int kv_len = p.seqused_k[seq];
-  const int head = blockIdx.y;
-  const int kvh = head / (p.num_heads / p.num_kv_heads);
-  const int shift = kv_len - q_len;                // query row i sees keys 0 .. shift + i
-  const int rows_here = min(BM, q_len - m0);
+  const int kvh = blockIdx.y;
+  const int shift = kv_len - q_len;                // query token i sees keys 0 .. shift + i
+  const int last_tok = (min(m0 + BM, n_rows) - 1) / G;
   // keys this tile can see at all
-  int n_keys = p.causal ? min(kv_len, shift + m0 + rows_here) : kv_len;
+  int n_keys = p.causal ? min(kv_len, shift + last_tok + 1) : kv_len;
   if (n_keys < 0) n_keys = 0;
   const int n_tiles = (n_keys + BN - 1) / BN;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, tq = lane & 3;
-  const T* qg = reinterpret_cast<const T*>(p.q) + (int64_t)q0 * p.q_stride + (int64_t)head * D;
+  const T* qg = reinterpret_cast<const T*>(p.q) + (int64_t)q0 * p.q_stride + (int64_t)kvh * G * D;
   const T* kc = reinterpret_cast<const T*>(p.k_cache) + (int64_t)kvh * p.head_stride;
   const T* vc = reinterpret_cast<const T*>(p.v_cache) + (int64_t)kvh * p.head_stride;
   const int* bt = p.block_table + (int64_t)seq * p.max_blocks_per_seq;
+  const int bmask = (1 << p.block_shift) - 1;
 
   // ---- Q tile -> shared memory
 #pragma unroll
   for (int i = 0; i < Q_PASSES; ++i) {
     const int idx = tid + i * NTHREADS;
     const int r = idx / CPR, c = idx % CPR;
-    const bool ok = m0 + r < q_len;
-    cp_async16(sQ + swz<D>(r, c), qg + (int64_t)(ok ? m0 + r : 0) * p.q_stride + c * 8, ok);
+    const bool ok = m0 + r < n_rows;
+    const int tok = ok ? (m0 + r) / G : 0, hd = ok ? (m0 + r) % G : 0;
+    cp_async16(sQ + swz<D>(r, c), qg + (int64_t)tok * p.q_stride + hd * D + c * 8, ok);
   }
   auto load_kv = [&](int j, int stage) {
     const uint32_t dk = sK + stage * (BN * D * 2), dv = sV + stage * (BN * D * 2);
@@ -154,8 +169,8 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       const bool ok = n < n_keys;
       int64_t off = 0;
       if (ok) {
-        const int page = bt[n / p.block_size];
-        off = (int64_t)page * p.block_stride + (int64_t)(n % p.block_size) * p.token_stride + c * 8;
+        const int page = bt[n >> p.block_shift];
+        off = (int64_t)page * p.block_stride + (int64_t)(n & bmask) * p.token_stride + c * 8;
       }
       cp_async16(dk + swz<D>(r, c), kc + off, ok);
       cp_async16(dv + swz<D>(r, c), vc + off, ok);
@@ -177,6 +192,12 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   constexpr bool QREG = MT == 1 && D <= 128;
   uint32_t qf[QREG ? D / 16 : 1][4];
   const int wrow = warp * 16 * MT;                 // first row of this warp inside the CTA tile
+  int tok_of[MT][2];                               // token (within the sequence) of this thread's rows
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) tok_of[mt][h] = (m0 + wrow + mt * 16 + g + h * 8) / G;
+  const int warp_first_tok = (m0 + wrow) / G;
 
   for (int j = 0; j < n_tiles; ++j) {
     const int stage = j & 1;
@@ -221,7 +242,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
     }
     // ---- mask (only tiles that touch the diagonal or the end of the sequence)
     const int n_base = j * BN;
-    const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + m0 + wrow);
+    const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + warp_first_tok);
     if (need_mask) {
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
@@ -230,8 +251,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int n = n_base + i * 8 + 2 * tq + (e & 1);
-            const int row = m0 + wrow + mt * 16 + g + ((e >> 1) << 3);
-            const bool vis = n < kv_len && (!p.causal || n <= shift + row);
+            const bool vis = n < kv_len && (!p.causal || n <= shift + tok_of[mt][e >> 1]);
             if (!vis) s[mt][i][e] = -INFINITY;
           }
     }
@@ -250,7 +270,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
         mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
         mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
         mscaled[h] = mx[h] == -INFINITY ? 0.f : mx[h] * p.scale_log2;     // a fully masked row so far: exp2(-inf) = 0
-        alpha[h] = exp2f(row_max[mt][h] * p.scale_log2 - mscaled[h]);     // row_max = -inf -> 0
+        alpha[h] = ex2(row_max[mt][h] * p.scale_log2 - mscaled[h]);     // row_max = -inf -> 0
         row_max[mt][h] = mx[h];
         row_sum[mt][h] *= alpha[h];
       }
@@ -263,10 +283,10 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       }
 #pragma unroll
       for (int i = 0; i < BN / 8; ++i) {
-        s[mt][i][0] = exp2f(fmaf(s[mt][i][0], p.scale_log2, -mscaled[0]));
-        s[mt][i][1] = exp2f(fmaf(s[mt][i][1], p.scale_log2, -mscaled[0]));
-        s[mt][i][2] = exp2f(fmaf(s[mt][i][2], p.scale_log2, -mscaled[1]));
-        s[mt][i][3] = exp2f(fmaf(s[mt][i][3], p.scale_log2, -mscaled[1]));
+        s[mt][i][0] = ex2(fmaf(s[mt][i][0], p.scale_log2, -mscaled[0]));
+        s[mt][i][1] = ex2(fmaf(s[mt][i][1], p.scale_log2, -mscaled[0]));
+        s[mt][i][2] = ex2(fmaf(s[mt][i][2], p.scale_log2, -mscaled[1]));
+        s[mt][i][3] = ex2(fmaf(s[mt][i][3], p.scale_log2, -mscaled[1]));
         row_sum[mt][0] += s[mt][i][0] + s[mt][i][1];
         row_sum[mt][1] += s[mt][i][2] + s[mt][i][3];
       }
@@ -298,7 +318,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   cp_wait<0>();
 
   // ---- epilogue: O / l  ->  out
-  T* og = reinterpret_cast<T*>(p.out) + (int64_t)q0 * p.o_stride + (int64_t)head * D;
+  T* og = reinterpret_cast<T*>(p.out) + (int64_t)q0 * p.o_stride + (int64_t)kvh * G * D;
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt) {
 #pragma unroll
@@ -307,9 +327,9 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       l += __shfl_xor_sync(0xffffffffu, l, 1);
       l += __shfl_xor_sync(0xffffffffu, l, 2);
       const int row = m0 + wrow + mt * 16 + g + h * 8;
-      if (row < q_len) {
+      if (row < n_rows) {
         const float inv = l > 0.f ? 1.f / l : 0.f;
-        T* orow = og + (int64_t)row * p.o_stride;
+        T* orow = og + (int64_t)tok_of[mt][h] * p.o_stride + (row - tok_of[mt][h] * G) * D;
 #pragma unroll
         for (int i = 0; i < D / 8; ++i)
           *reinterpret_cast<uint32_t*>(orow + i * 8 + 2 * tq) =
@@ -327,8 +347,8 @@ static int launch(const Params& p, int total_q, cudaStream_t stream) {
   if (smem > 48 * 1024)
     VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // every sequence adds at most one partial tile: an upper bound that needs no host read of cu_seqlens_q
-  const int max_tiles = total_q / BM + p.num_seqs;
-  VB_CUDA_CHECK(launch_k(kern, dim3(max_tiles, p.num_heads), dim3(NTHREADS), smem, stream, p));
+  const int max_tiles = (int)(((int64_t)total_q * p.group) / BM) + p.num_seqs;
+  VB_CUDA_CHECK(launch_k(kern, dim3(max_tiles, p.num_kv_heads), dim3(NTHREADS), smem, stream, p));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -338,7 +358,7 @@ static int launch(const Params& p, int total_q, cudaStream_t stream) {
 // accumulators leave no room for the second tile.
 template <typename T>
 static int dispatch(const Params& p, int head_size, int total_q, int max_seqlen_q, cudaStream_t stream) {
-  const bool big = max_seqlen_q > 64;
+  const bool big = (int64_t)max_seqlen_q * p.group > 64;
   switch (head_size) {
     case 64: return big ? launch<T, 64, 2>(p, total_q, stream) : launch<T, 64, 1>(p, total_q, stream);
     case 128: return big ? launch<T, 128, 2>(p, total_q, stream) : launch<T, 128, 1>(p, total_q, stream);
@@ -364,7 +384,8 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
                                              int64_t token_stride, int64_t head_stride, vb200_stream_t stream) {
   VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "flash_attn_varlen_paged: dtype must be f16 or bf16");
   VB_CHECK(num_kv_heads > 0 && num_heads % num_kv_heads == 0, "flash_attn_varlen_paged: num_heads %% num_kv_heads != 0");
-  VB_CHECK(block_size > 0, "flash_attn_varlen_paged: bad block_size %d", block_size);
+  VB_CHECK(block_size > 0 && (block_size & (block_size - 1)) == 0,
+           "flash_attn_varlen_paged: block_size %d must be a power of two", block_size);
   VB_CHECK(((q_stride | out_stride | block_stride | token_stride | head_stride) & 7) == 0,
            "flash_attn_varlen_paged: strides must be multiples of 8 elements (16 bytes)");
   VB_CHECK(((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(query) |
@@ -383,7 +404,9 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
   p.num_heads = num_heads;
   p.num_kv_heads = num_kv_heads;
   p.max_blocks_per_seq = max_num_blocks_per_seq;
-  p.block_size = block_size;
+  p.block_shift = 0;
+  while ((1 << p.block_shift) < block_size) ++p.block_shift;
+  p.group = num_heads / num_kv_heads;
   p.q_stride = q_stride;
   p.o_stride = out_stride;
   p.block_stride = block_stride;
