@@ -45,7 +45,9 @@ union Vec8 {
 // MODE 2: rms_norm_dynamic_per_token_quant (optional residual): z = float(x) + float(r) unrounded,
 //         residual = T(z); y = T(T(z * inv) * w); s = max(min(amax|y|, ub) / 448, 1/(448*512));
 //         out = fp8(clamp(y / s)); scales[token] = s
-template <typename T, int MODE>
+// KV: 16-byte vectors per thread, sized to the row by the launcher (hidden <= KV * 256 * 8) so that the registers
+// holding the row between the passes do not cap the CTAs per SM.
+template <typename T, int MODE, int KV>
 __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
     void* __restrict__ out_, T* __restrict__ input, T* __restrict__ residual,
     const T* __restrict__ weight, float* __restrict__ scales, const float* __restrict__ scale_ub,
@@ -57,10 +59,16 @@ __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
   T* in = input + row * input_stride;
   T* res = residual ? residual + row * hidden : nullptr;
   const int nvec = hidden >> 3;
-  float zf[kMaxVecPerThread][8];  // the (residual-added) row, fp32
+  float zf[KV][8];  // the (residual-added) row, fp32
+  Vec8<T> wv[KV];   // the weight: fetched with the row, not after the reduction that needs no weight
   float ss = 0.f;
 #pragma unroll
-  for (int k = 0; k < kMaxVecPerThread; ++k) {
+  for (int k = 0; k < KV; ++k) {
+    const int i = threadIdx.x + k * kGlueThreads;
+    if (i < nvec) wv[k].u = *reinterpret_cast<const uint4*>(weight + i * 8);
+  }
+#pragma unroll
+  for (int k = 0; k < KV; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
       Vec8<T> a;
@@ -87,15 +95,14 @@ __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
   const float inv = rsqrtf(ss / (float)hidden + eps);
   float amax = 0.f;
 #pragma unroll
-  for (int k = 0; k < kMaxVecPerThread; ++k) {
+  for (int k = 0; k < KV; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
-      Vec8<T> w, y;
-      w.u = *reinterpret_cast<const uint4*>(weight + i * 8);
+      Vec8<T> y;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const T n = from_float<T>(zf[k][j] * inv);
-        y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(w.e[j]));
+        y.e[j] = from_float<T>(to_float<T>(n) * to_float<T>(wv[k].e[j]));
         if (MODE == 2) {
           zf[k][j] = to_float<T>(y.e[j]);
           amax = fmaxf(amax, fabsf(zf[k][j]));
@@ -113,7 +120,7 @@ __global__ void __launch_bounds__(kGlueThreads) rms_norm_kernel(
     uint8_t* o = reinterpret_cast<uint8_t*>(out_) + row * hidden;
     const RowDivider div(s, amax);
 #pragma unroll
-    for (int k = 0; k < kMaxVecPerThread; ++k) {
+    for (int k = 0; k < KV; ++k) {
       const int i = threadIdx.x + k * kGlueThreads;
       if (i < nvec) {
         uint2 q;
@@ -147,7 +154,26 @@ __global__ void __launch_bounds__(256) rotary_kernel(
 // work).  A row is therefore cut into SPLIT column slices, one CTA each, the SPLIT CTAs of a row forming a thread-
 // block cluster that exchanges its slice maxima through distributed shared memory (one st.shared::cluster per peer +
 // one cluster barrier) -- rows x SPLIT CTAs spread evenly over all SMs.
-template <typename T, int SPLIT>
+// Two floats rounded to T (round-to-nearest-even each, as from_float<T>) by ONE pack instruction, returned as floats.
+template <typename T>
+__device__ __forceinline__ void round_pair(float& a, float& b);
+template <>
+__device__ __forceinline__ void round_pair<__half>(float& a, float& b) {
+  const float2 f = __half22float2(__floats2half2_rn(a, b));
+  a = f.x;
+  b = f.y;
+}
+template <>
+__device__ __forceinline__ void round_pair<__nv_bfloat16>(float& a, float& b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  const uint32_t u = *reinterpret_cast<const uint32_t*>(&h);
+  a = __uint_as_float(u << 16);
+  b = __uint_as_float(u & 0xffff0000u);
+}
+
+// KV: 16-byte vectors per thread (the slice is at most KV * 256 vectors) -- sized to the slice so that the registers
+// holding the activations between the two passes do not cap the CTAs per SM (rows x SPLIT CTAs should be ONE wave).
+template <typename T, int SPLIT, int KV>
 __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
     uint8_t* __restrict__ out, float* __restrict__ scales, const T* __restrict__ in,
     const float* __restrict__ scale_ub, int d) {
@@ -163,22 +189,25 @@ __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
   const T* x = in + row * 2 * d + part * dpart;
   const T* y = x + d;
   const int nvec = dpart >> 3;
-  constexpr int kVec = kMaxVecPerThread / (SPLIT > 1 ? 2 : 1);
-  float act[kVec][8];
+  float act[KV][8];
   float amax = 0.f;
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
+  for (int k = 0; k < KV; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
       Vec8<T> a, b;
       a.u = ldg_stream_v4(x + i * 8);
       b.u = ldg_stream_v4(y + i * 8);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float xf = to_float<T>(a.e[j]);
-        const T sl = from_float<T>(xf / (1.0f + expf(-xf)));
-        act[k][j] = to_float<T>(from_float<T>(to_float<T>(sl) * to_float<T>(b.e[j])));
-        amax = fmaxf(amax, fabsf(act[k][j]));
+      for (int j = 0; j < 8; j += 2) {
+        const float x0 = to_float<T>(a.e[j]), x1 = to_float<T>(a.e[j + 1]);
+        float s0 = x0 / (1.0f + expf(-x0)), s1 = x1 / (1.0f + expf(-x1));
+        round_pair<T>(s0, s1);                                   // T(silu(x))
+        float p0 = s0 * to_float<T>(b.e[j]), p1 = s1 * to_float<T>(b.e[j + 1]);
+        round_pair<T>(p0, p1);                                   // T(T(silu(x)) * y)
+        act[k][j] = p0;
+        act[k][j + 1] = p1;
+        amax = fmaxf(amax, fmaxf(fabsf(p0), fabsf(p1)));
       }
     }
   }
@@ -202,7 +231,7 @@ __global__ void __launch_bounds__(kGlueThreads) silu_mul_quant_kernel(
   uint8_t* o = out + row * d + part * dpart;
   const RowDivider div(s, amax);
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) {
+  for (int k = 0; k < KV; ++k) {
     const int i = threadIdx.x + k * kGlueThreads;
     if (i < nvec) {
       uint2 q;
@@ -236,14 +265,33 @@ using namespace vb200;
     __VA_ARGS__;                                                 \
   }
 
+// vectors per thread for a row of `hidden` 16-bit elements: 1, 2, 4 or 8
+#define VB_NORM_KV(hidden, ...)                                    \
+  do {                                                             \
+    const int vpt_ = ((hidden) / 8 + kGlueThreads - 1) / kGlueThreads; \
+    if (vpt_ <= 1) {                                               \
+      constexpr int KV = 1;                                        \
+      __VA_ARGS__;                                                 \
+    } else if (vpt_ <= 2) {                                        \
+      constexpr int KV = 2;                                        \
+      __VA_ARGS__;                                                 \
+    } else if (vpt_ <= 4) {                                        \
+      constexpr int KV = 4;                                        \
+      __VA_ARGS__;                                                 \
+    } else {                                                       \
+      constexpr int KV = 8;                                        \
+      __VA_ARGS__;                                                 \
+    }                                                              \
+  } while (0)
+
 extern "C" int vb200_rms_norm(void* out, const void* input, const void* weight, float epsilon,
                               int num_tokens, int hidden_size, int64_t input_stride, int dtype,
                               vb200_stream_t stream) {
   if (num_tokens <= 0) return 0;
   if (check_row("rms_norm", hidden_size, dtype, out, input)) return 1;
   VB_CHECK(input_stride % 8 == 0, "rms_norm: input stride must be a multiple of 8");
-  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 0>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, nullptr, (const scalar_t*)weight, nullptr, nullptr,
-                         epsilon, hidden_size, input_stride)));
+  VB_NORM_KV(hidden_size, DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 0, KV>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, nullptr, (const scalar_t*)weight, nullptr, nullptr,
+                         epsilon, hidden_size, input_stride))));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -254,8 +302,8 @@ extern "C" int vb200_fused_add_rms_norm(void* input, void* residual, const void*
   if (num_tokens <= 0) return 0;
   if (check_row("fused_add_rms_norm", hidden_size, dtype, input, residual)) return 1;
   VB_CHECK(input_stride % 8 == 0, "fused_add_rms_norm: input stride must be a multiple of 8");
-  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 1>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, nullptr, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight,
-                         nullptr, nullptr, epsilon, hidden_size, input_stride)));
+  VB_NORM_KV(hidden_size, DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 1, KV>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, nullptr, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight,
+                         nullptr, nullptr, epsilon, hidden_size, input_stride))));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -269,8 +317,8 @@ extern "C" int vb200_rms_norm_dynamic_per_token_quant(void* out, const void* inp
   if (num_tokens <= 0) return 0;
   if (check_row("rms_norm_dynamic_per_token_quant", hidden_size, dtype, input, residual)) return 1;
   VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "rms_norm_dynamic_per_token_quant: out must be 8-byte aligned");
-  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 2>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, scales,
-                         scale_ub, epsilon, hidden_size, (int64_t)hidden_size)));
+  VB_NORM_KV(hidden_size, DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(rms_norm_kernel<scalar_t, 2, KV>, dim3(num_tokens), dim3(kGlueThreads), 0, (cudaStream_t)stream, out, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, scales,
+                         scale_ub, epsilon, hidden_size, (int64_t)hidden_size))));
   VB_LAUNCH_CHECK();
   return 0;
 }
@@ -306,29 +354,43 @@ extern "C" int vb200_silu_and_mul_dynamic_per_token_quant(void* out, float* scal
   if (num_tokens <= 0) return 0;
   if (check_row("silu_and_mul_dynamic_per_token_quant", d, dtype, input, input)) return 1;
   VB_CHECK((reinterpret_cast<uintptr_t>(out) & 7) == 0, "silu_and_mul_dynamic_per_token_quant: out must be 8-byte aligned");
-  // column slices per row: enough CTAs to give every SM about six (see the kernel comment); a slice must keep whole
-  // 16-byte vectors and, when split, fit half the register budget of an unsplit row
+  // column slices per row: enough CTAs for about two waves of light CTAs (measured at 256 x 14336: 1 / 2 / 4 / 8 slices
+  // 13.2 / 11.4 / 11.0 / 9.5 us -- a second wave's loads overlap the first wave's arithmetic); whole 16-byte vectors
   int split = 1;
-  const int want = (6 * num_sms() + num_tokens - 1) / num_tokens;
+  const int want = (14 * num_sms() + num_tokens - 1) / num_tokens;
   for (int s = 2; s <= 8; s *= 2)
     if (s <= want && d % (8 * s) == 0 && d / s >= 1024) split = s;
   static const char* force = getenv("VB200_SILU_SPLIT");   // experiments (benchmarks/bench_layer_glue.py)
   if (force != nullptr) {
     const int f = atoi(force);
-    if ((f == 1 || f == 2 || f == 4 || f == 8) && d % (8 * f) == 0 && d / f <= kGlueThreads * (f > 1 ? 4 : 8) * 8) split = f;
+    if ((f == 1 || f == 2 || f == 4 || f == 8) && d % (8 * f) == 0) split = f;
   }
   const dim3 grid((unsigned)num_tokens * split), block(kGlueThreads);
-#define VB_SILU_Q(S)                                                                                               \
-  DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k_cluster(silu_mul_quant_kernel<scalar_t, S>, grid, block, 0,             \
-                                                    (cudaStream_t)stream, S, (uint8_t*)out, scales,                 \
-                                                    (const scalar_t*)input, scale_ub, d)))
-  if (split == 8) { VB_SILU_Q(8); }
-  else if (split == 4) { VB_SILU_Q(4); }
-  else if (split == 2) { VB_SILU_Q(2); }
-  else {
-    DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(silu_mul_quant_kernel<scalar_t, 1>, grid, block, 0, (cudaStream_t)stream,
-                                              (uint8_t*)out, scales, (const scalar_t*)input, scale_ub, d)));
-  }
+  const int vec_per_thread = (d / split / 8 + kGlueThreads - 1) / kGlueThreads;
+#define VB_SILU_Q(S, KV)                                                                                           \
+  do {                                                                                                             \
+    if (S > 1) {                                                                                                   \
+      DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k_cluster(silu_mul_quant_kernel<scalar_t, S, KV>, grid, block, 0,    \
+                                                        (cudaStream_t)stream, S, (uint8_t*)out, scales,            \
+                                                        (const scalar_t*)input, scale_ub, d)));                    \
+    } else {                                                                                                       \
+      DISPATCH_16(dtype, VB_CUDA_CHECK(launch_k(silu_mul_quant_kernel<scalar_t, S, KV>, grid, block, 0,            \
+                                                (cudaStream_t)stream, (uint8_t*)out, scales,                       \
+                                                (const scalar_t*)input, scale_ub, d)));                            \
+    }                                                                                                              \
+  } while (0)
+#define VB_SILU_Q_KV(S)                                   \
+  do {                                                    \
+    if (vec_per_thread <= 1) VB_SILU_Q(S, 1);             \
+    else if (vec_per_thread <= 2) VB_SILU_Q(S, 2);        \
+    else if (vec_per_thread <= 4) VB_SILU_Q(S, 4);        \
+    else VB_SILU_Q(S, 8);                                 \
+  } while (0)
+  if (split == 8) VB_SILU_Q_KV(8);
+  else if (split == 4) VB_SILU_Q_KV(4);
+  else if (split == 2) VB_SILU_Q_KV(2);
+  else VB_SILU_Q_KV(1);
+#undef VB_SILU_Q_KV
 #undef VB_SILU_Q
   VB_LAUNCH_CHECK();
   return 0;
