@@ -203,7 +203,9 @@ def test_paged_attention_cuda_graph_capture():
 @pytest.mark.parametrize("kvd", ["auto", "fp8"])
 @pytest.mark.parametrize("case", [(7, 32, 8, 128, [1, 15, 16, 17, 511, 513, 1300]), (3, 8, 8, 64, [33, 700, 2]),
                                   (2, 40, 1, 128, [77, 640]), (2, 4, 2, 256, [40, 300]), (2, 64, 8, 128, [5000, 300]),
-                                  (4, 16, 2, 128, [100, 90, 80, 70])], ids=lambda c: f"S{c[0]}H{c[1]}kv{c[2]}D{c[3]}")
+                                  (4, 16, 2, 128, [100, 90, 80, 70]), (2, 128, 8, 128, [600, 40]),
+                                  (2, 72, 8, 128, [700, 30]), (3, 24, 8, 64, [1500, 2, 513])],
+                         ids=lambda c: f"S{c[0]}H{c[1]}kv{c[2]}D{c[3]}")
 def test_paged_attention_v1_quant_matches_unfused(kvd, case):
     """paged_attention_v1_quant (per-token fp8 quantisation inside the split-K reduce kernel) == paged_attention_v1
     followed by scaled_fp8_quant(use_per_token_if_dynamic=True), bit for bit (codes and scales)."""

@@ -539,7 +539,10 @@ __device__ __forceinline__ void load_lane_piece(float (&v)[PER], const QT* p) {
   }
 }
 
-template <typename QT, int HEAD_SIZE>
+// HPW: heads per warp.  A warp walks its HPW heads TOGETHER, phase by phase (maxima, sums, partials), so that the
+// loads of all its heads are in flight at once; fewer, busier warps keep the CTA small enough for every sequence's
+// CTA to be resident in one wave (32 heads: 16 warps, two CTAs per SM).
+template <typename QT, int HEAD_SIZE, int HPW>
 __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
     uint8_t* __restrict__ out_q, float* __restrict__ out_scales, const float* __restrict__ scale_ub,
     const float* __restrict__ exp_sums, const float* __restrict__ max_logits, const QT* __restrict__ tmp_out,
@@ -547,50 +550,85 @@ __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
   pdl_wait();
   pdl_trigger();
   constexpr int PER = HEAD_SIZE / 32;
-  constexpr int MAXH = 4;   // heads per warp (<= 128 query heads)
+  constexpr int JB = HPW == 4 ? 2 : 4;     // partitions fetched per round
   __shared__ float sm[32];
   const int seq_idx = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
   const int seq_len = seq_lens[seq_idx];
   const int np = min(max(1, (seq_len + partition_size - 1) / partition_size), max_num_partitions);
-  float y[MAXH][PER];
+  float y[HPW][PER];
+  const float* ml[HPW];
+  const float* es[HPW];
+  const QT* tp[HPW];
+  bool live[HPW];
+#pragma unroll
+  for (int hh = 0; hh < HPW; ++hh) {
+    const int head = warp + hh * nw;
+    live[hh] = head < num_heads;
+    const int64_t row = (int64_t)seq_idx * num_heads + (live[hh] ? head : 0);
+    ml[hh] = max_logits + row * max_num_partitions;
+    es[hh] = exp_sums + row * max_num_partitions;
+    tp[hh] = tmp_out + row * max_num_partitions * HEAD_SIZE + lane * PER;
+  }
+  if (np == 1) {
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh)
+      if (live[hh]) load_lane_piece<QT, PER>(y[hh], tp[hh]);
+  } else {
+    float mg[HPW], gsum[HPW], inv[HPW];
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh) {
+      mg[hh] = -INFINITY;
+      if (live[hh])
+        for (int j = lane; j < np; j += 32) mg[hh] = fmaxf(mg[hh], ml[hh][j]);
+    }
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh) mg[hh] = warp_max(mg[hh]);
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh) {
+      gsum[hh] = 0.f;
+      if (live[hh])
+        for (int j = lane; j < np; j += 32) gsum[hh] += es[hh][j] * __expf(ml[hh][j] - mg[hh]);
+    }
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh) {
+      gsum[hh] = warp_sum(gsum[hh]);
+      inv[hh] = __fdividef(1.f, gsum[hh] + 1e-6f);
+    }
+    float acc[HPW][PER];
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh)
+#pragma unroll
+      for (int i = 0; i < PER; ++i) acc[hh][i] = 0.f;
+    for (int j0 = 0; j0 < np; j0 += JB) {
+      float t[HPW][JB][PER];
+#pragma unroll
+      for (int hh = 0; hh < HPW; ++hh)
+#pragma unroll
+        for (int jj = 0; jj < JB; ++jj)
+          if (live[hh] && j0 + jj < np) load_lane_piece<QT, PER>(t[hh][jj], tp[hh] + (int64_t)(j0 + jj) * HEAD_SIZE);
+#pragma unroll
+      for (int hh = 0; hh < HPW; ++hh)
+#pragma unroll
+        for (int jj = 0; jj < JB; ++jj)
+          if (live[hh] && j0 + jj < np) {   // same order of accumulation as the unfused reduce kernel: j ascending
+            const float w = es[hh][j0 + jj] * __expf(ml[hh][j0 + jj] - mg[hh]) * inv[hh];
+#pragma unroll
+            for (int i = 0; i < PER; ++i) acc[hh][i] = fmaf(t[hh][jj][i], w, acc[hh][i]);
+          }
+    }
+#pragma unroll
+    for (int hh = 0; hh < HPW; ++hh)
+#pragma unroll
+      for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(from_float<QT>(acc[hh][i]));
+  }
   float amax = 0.f;
 #pragma unroll
-  for (int hh = 0; hh < MAXH; ++hh) {
-    const int head = warp + hh * nw;
-    if (head < num_heads) {
-      const int64_t row = (int64_t)seq_idx * num_heads + head;
-      const float* ml = max_logits + row * max_num_partitions;
-      const float* es = exp_sums + row * max_num_partitions;
-      const QT* tp = tmp_out + row * max_num_partitions * HEAD_SIZE + lane * PER;
-      if (np == 1) {
-        load_lane_piece<QT, PER>(y[hh], tp);
-      } else {
-        float mg = -INFINITY;
-        for (int j = lane; j < np; j += 32) mg = fmaxf(mg, ml[j]);
-        mg = warp_max(mg);
-        float gsum = 0.f;
-        for (int j = lane; j < np; j += 32) gsum += es[j] * __expf(ml[j] - mg);
-        gsum = warp_sum(gsum);
-        const float inv = __fdividef(1.f, gsum + 1e-6f);
-        float acc[PER];
-#pragma unroll
-        for (int i = 0; i < PER; ++i) acc[i] = 0.f;
-#pragma unroll 4
-        for (int j = 0; j < np; ++j) {
-          const float w = es[j] * __expf(ml[j] - mg) * inv;
-          float t[PER];
-          load_lane_piece<QT, PER>(t, tp + (int64_t)j * HEAD_SIZE);
-#pragma unroll
-          for (int i = 0; i < PER; ++i) acc[i] = fmaf(t[i], w, acc[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < PER; ++i) y[hh][i] = to_float<QT>(from_float<QT>(acc[i]));
-      }
+  for (int hh = 0; hh < HPW; ++hh)
+    if (live[hh]) {
 #pragma unroll
       for (int i = 0; i < PER; ++i) amax = fmaxf(amax, fabsf(y[hh][i]));
     }
-  }
   amax = warp_max(amax);
   if (lane == 0) sm[warp] = amax;
   __syncthreads();
@@ -600,9 +638,9 @@ __global__ void __launch_bounds__(1024) paged_attention_reduce_quant_kernel(
   if (threadIdx.x == 0) out_scales[seq_idx] = s;
   const RowDivider div(s, amax);
 #pragma unroll
-  for (int hh = 0; hh < MAXH; ++hh) {
+  for (int hh = 0; hh < HPW; ++hh) {
     const int head = warp + hh * nw;
-    if (head < num_heads) {
+    if (live[hh]) {
       uint8_t* o = out_q + ((int64_t)seq_idx * num_heads + head) * HEAD_SIZE + lane * PER;
       if constexpr (PER % 4 == 0) {
 #pragma unroll
@@ -674,11 +712,17 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     if (p.out_q != nullptr) {
       // fused output quantisation: always through the partials (force_partials is set by the entry point)
       if constexpr (HEAD_SIZE % 32 == 0) {
-        const int warps = p.num_heads < 32 ? p.num_heads : 32;
         VB_CHECK(p.num_heads <= 128, "paged_attention_v1_quant: at most 128 query heads (got %d)", p.num_heads);
-        VB_CUDA_CHECK(launch_k(paged_attention_reduce_quant_kernel<QT, HEAD_SIZE>, dim3(num_seqs), dim3(32 * warps), 0,
-                               stream, (uint8_t*)p.out_q, p.out_scales, p.scale_ub, p.exp_sums, p.max_logits,
-                               (const QT*)p.tmp_out, p.seq_lens, p.num_heads, p.max_num_partitions, p.partition_size));
+        const int hpw = p.num_heads <= 8 ? 1 : (p.num_heads <= 64 ? 2 : 4);
+        const int warps = (p.num_heads + hpw - 1) / hpw;
+#define VB_REDUCE_Q(HPW)                                                                                              \
+  VB_CUDA_CHECK(launch_k(paged_attention_reduce_quant_kernel<QT, HEAD_SIZE, HPW>, dim3(num_seqs), dim3(32 * warps), 0, \
+                         stream, (uint8_t*)p.out_q, p.out_scales, p.scale_ub, p.exp_sums, p.max_logits,                \
+                         (const QT*)p.tmp_out, p.seq_lens, p.num_heads, p.max_num_partitions, p.partition_size))
+        if (hpw == 1) VB_REDUCE_Q(1);
+        else if (hpw == 2) VB_REDUCE_Q(2);
+        else VB_REDUCE_Q(4);
+#undef VB_REDUCE_Q
         VB_LAUNCH_CHECK();
         return 0;
       } else {
