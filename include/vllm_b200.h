@@ -189,17 +189,19 @@ int vb200_paged_attention_flash(void* out, const void* query, const void* key_ca
  * block_table=..., causal=True) as vllm/v1/attention/backends/flash_attn.py:497-519 calls it -- prefill, chunked
  * prefill and mixed prefill / decode batches.  query / out [total_q, num_heads, head_size] (f16 / bf16; token rows
  * q_stride / out_stride elements apart), sequence s owning rows cu_seqlens_q[s] .. cu_seqlens_q[s+1] (int32
- * [num_seqs + 1]); the cache (layout and strides as vb200_paged_attention_flash, dtype == query dtype, any
- * block_size) already holds all seqused_k[s] tokens of the sequence, the new ones last; row i of a sequence with
+ * [num_seqs + 1]); the cache (layout and strides as vb200_paged_attention_flash; kv_dtype AUTO = the query's dtype,
+ * FP8_E4M3 = bytes with per-tensor k_scale / v_scale as there; any power-of-two block_size) already holds all
+ * seqused_k[s] tokens of the sequence, the new ones last; row i of a sequence with
  * q_len new tokens attends keys 0 .. seqused_k[s] - q_len + i when `causal`, all seqused_k[s] keys otherwise.
  * max_seqlen_q: the longest q_len (the reference call's argument; picks 64- or 128-row tiles, <= 0 = unknown).
- * head_size 64 / 128 / 256; strides multiples of 8 elements; no workspace, no host read of the device arrays. */
+ * head_size 64 / 128 / 256; strides multiples of 16 bytes; no workspace, no host read of the device arrays. */
 int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_cache, const void* value_cache,
                                   const int32_t* cu_seqlens_q, const int32_t* seqused_k, const int32_t* block_table,
                                   int num_seqs, int total_q, int num_heads, int num_kv_heads, int head_size,
                                   int block_size, int max_num_blocks_per_seq, int max_seqlen_q, float scale, int causal,
-                                  int dtype, int64_t q_stride, int64_t out_stride, int64_t block_stride,
-                                  int64_t token_stride, int64_t head_stride, vb200_stream_t stream);
+                                  int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
+                                  int64_t q_stride, int64_t out_stride, int64_t block_stride, int64_t token_stride,
+                                  int64_t head_stride, vb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------ */
 /* FP8 activation quantisation + activation                                                    */

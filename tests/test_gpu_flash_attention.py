@@ -190,9 +190,8 @@ def test_flash_attn_varlen_func_rejects_what_is_not_built():
     bt = torch.zeros(2, 2, dtype=torch.int32, device=DEV)
     sl = torch.ones(2, dtype=torch.int32, device=DEV)
     cu = torch.arange(3, dtype=torch.int32, device=DEV)
-    with pytest.raises(NotImplementedError):                                       # prefill over an fp8 cache
-        flash_attn_varlen_func(q, kc.view(torch.uint8)[..., :128], kc.view(torch.uint8)[..., :128], 2, cu, 16, sl,
-                               block_table=bt, k_descale=torch.ones(1, device=DEV), v_descale=torch.ones(1, device=DEV))
+    with pytest.raises(NotImplementedError):                                       # ALiBi outside the decode case
+        flash_attn_varlen_func(q, kc, kc, 2, cu, 16, sl, block_table=bt, alibi_slopes=torch.ones(8, device=DEV))
     with pytest.raises(NotImplementedError):
         flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, softcap=30.0)
     with pytest.raises(NotImplementedError):
@@ -302,3 +301,41 @@ def test_flash_attn_varlen_paged_non_causal_and_backend_prefill():
     kc2, vc2 = kv[0].cpu(), kv[1].cpu()   # after the write: what the oracle gathers from
     want2 = oattn.flash_attn_varlen_paged(qkv[:, :H].contiguous(), kc2, vc2, [40, 1], [140, 57], bt2, scale)
     torch.testing.assert_close(out2.cpu().float(), want2.float(), atol=1.5e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("heads", [(8, 2), (4, 4), (14, 2)])
+@pytest.mark.parametrize("head_size", [64, 128, 256])
+@pytest.mark.parametrize("seq_lens", VARLEN_CASES[:1] + VARLEN_CASES[2:4], ids=lambda c: f"n{len(c)}q{max(x[0] for x in c)}")
+def test_flash_attn_varlen_paged_fp8_cache(seq_lens, head_size, heads, dtype, layout):
+    """fp8 (e4m3) cache: the oracle attends over the DEQUANTISED cache (bytes -> half -> x scale -> query dtype, as
+    quant_utils.cuh:348-359), the kernel folds the per-tensor scales into the logits / output."""
+    from oracle.fp8 import dequant_e4m3
+    from vllm_b200 import _custom_ops as ops
+    H, Hkv = heads
+    bs, nb = 16, 1024
+    seed_all(len(seq_lens) * 7 + head_size + H)
+    query_lens = [x[0] for x in seq_lens]
+    kv_lens = [x[1] for x in seq_lens]
+    q = torch.randn(sum(query_lens), H, head_size).to(dtype)
+    ksc, vsc = 0.043, 0.029
+    k8 = (torch.randn(nb, bs, Hkv, head_size) / ksc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+    v8 = (torch.randn(nb, bs, Hkv, head_size) / vsc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+    maxb = (max(kv_lens) + bs - 1) // bs
+    bt = torch.randint(0, nb, (len(seq_lens), maxb), dtype=torch.int32)
+    cu = torch.tensor([0] + query_lens, dtype=torch.int32).cumsum(0).to(torch.int32)
+    kd, vd = k8.to(DEV), v8.to(DEV)
+    if layout == "HND":
+        kd = kd.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        vd = vd.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+    scale = float(head_size ** -0.5)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    ops.flash_attn_varlen_paged(out, q.to(DEV), kd, vd, cu.to(DEV), torch.tensor(kv_lens, dtype=torch.int32, device=DEV),
+                                bt.to(DEV), scale, True, max(query_lens), "fp8", torch.tensor([ksc], device=DEV),
+                                torch.tensor([vsc], device=DEV))
+    torch.cuda.synchronize()
+    kc = dequant_e4m3(k8, ksc, dtype)
+    vc = dequant_e4m3(v8, vsc, dtype)
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2, rtol=1e-2)

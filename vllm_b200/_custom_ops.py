@@ -108,14 +108,15 @@ def paged_attention_v1(
 
 def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                             cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, block_table: torch.Tensor,
-                            scale: float, causal: bool = True, max_seqlen_q: int = 0) -> None:
+                            scale: float, causal: bool = True, max_seqlen_q: int = 0, kv_cache_dtype: str = "auto",
+                            k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
     """Variable-length causal attention over the flash cache layout (include/vllm_b200.h
     vb200_flash_attn_varlen_paged): prefill / chunked prefill / mixed batches of the V1 backend's
     flash_attn_varlen_func call (vllm/v1/attention/backends/flash_attn.py:497-519).  query / out [total_q, num_heads,
     head_size]; key_cache / value_cache the `[num_blocks, block_size, num_kv_heads, head_size]` halves (NHD or HND
     strides) holding every sequence's tokens, the new ones included; cu_seqlens_q int32 [num_seqs + 1]; seqused_k
     int32 [num_seqs]; block_table int32 [num_seqs, max_blocks]; max_seqlen_q the longest query length when the caller
-    knows it (0 = unknown)."""
+    knows it (0 = unknown); kv_cache_dtype "auto" or "fp8" (e4m3 bytes + fp32 per-tensor k_scale / v_scale)."""
     require_cuda(out, query, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
         raise RuntimeError("query must be [total_q, num_heads, head_size] with contiguous heads")
@@ -125,9 +126,12 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
             key_cache.size(i) > 1 and key_cache.stride(i) != value_cache.stride(i) for i in range(4)):
         raise RuntimeError("flash_attn_varlen_paged: key_cache / value_cache must be [num_blocks, block_size, "
                            "num_kv_heads, head_size] views with equal strides and a contiguous head dimension")
-    if key_cache.dtype != query.dtype:
-        raise NotImplementedError("flash_attn_varlen_paged: the cache must have the query's dtype (fp8 caches are "
-                                  "read by the decode kernel only)")
+    kvd = kv_dtype_enum(kv_cache_dtype)
+    require_cuda(k_scale, v_scale)
+    if kvd == _lib.KV_AUTO and key_cache.dtype != query.dtype:
+        raise RuntimeError(f"kv_cache_dtype 'auto' needs cache dtype == query dtype ({key_cache.dtype} vs {query.dtype})")
+    if kvd == _lib.KV_FP8_E4M3 and (key_cache.element_size() != 1 or k_scale is None or v_scale is None):
+        raise RuntimeError("fp8 kv cache must be a 1-byte tensor (uint8 / float8_e4m3fn) with k_scale and v_scale")
     for name, t in (("cu_seqlens_q", cu_seqlens_q), ("seqused_k", seqused_k), ("block_table", block_table)):
         if t.dtype != torch.int32 or not t.is_contiguous():
             raise RuntimeError(f"{name} must be a contiguous int32 tensor")
@@ -143,7 +147,8 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
         check(load().vb200_flash_attn_varlen_paged(
             ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), ptr(cu_seqlens_q), ptr(seqused_k), ptr(block_table),
             num_seqs, total_q, num_heads, num_kv_heads, head_size, block_size, block_table.stride(0), int(max_seqlen_q),
-            float(scale), 1 if causal else 0, dtype_enum(query.dtype), query.stride(0) if total_q > 1 else num_heads * head_size,
+            float(scale), 1 if causal else 0, dtype_enum(query.dtype), kvd, ptr(k_scale), ptr(v_scale),
+            query.stride(0) if total_q > 1 else num_heads * head_size,
             out.stride(0) if total_q > 1 else num_heads * head_size, strides[0], strides[1], strides[2], stream()))
 
 

@@ -13,7 +13,7 @@ Mirrors the pieces of /root/reference/vllm/v1/attention/backends/flash_attn.py a
                                      vb200_paged_attention_flash kernel (TMA tensor-map loads of the cache as it lies,
                                      csrc/paged_attention_flash.cuh).
 Prefill / chunked prefill / mixed batches (max_seqlen_q > 1) run on the variable-length kernel of
-csrc/paged_prefill.cu (16-bit caches).  Sliding windows, soft-capping and cascade attention raise.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3, :478-486); this kernel keeps the query in
+csrc/paged_prefill.cu (16-bit and fp8 caches).  Sliding windows, soft-capping and cascade attention raise.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3, :478-486); this kernel keeps the query in
 bf16/f16 and folds the per-tensor k / v descales into the fp32 logits / output, which is the dequantised result the
 parity bar is stated against.
 """
@@ -72,14 +72,14 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         out = torch.empty_like(q)
     if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0]:
         # prefill / chunked prefill / mixed batch: the variable-length kernel (csrc/paged_prefill.cu)
-        if fp8:
-            raise NotImplementedError("flash_attn_varlen_func: prefill over an fp8 cache is not built (decode is)")
         if alibi_slopes is not None:
             raise NotImplementedError("flash_attn_varlen_func: ALiBi is built for the decode case only")
         if cu_seqlens_q is None:
             raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
+        ks = k_descale.reshape(-1)[:1].float().contiguous() if fp8 else None
+        vs = v_descale.reshape(-1)[:1].float().contiguous() if fp8 else None
         ops.flash_attn_varlen_paged(out, q, k, v, cu_seqlens_q, seqused_k, block_table, softmax_scale, causal,
-                                    int(max_seqlen_q))
+                                    int(max_seqlen_q), "fp8" if fp8 else "auto", ks, vs)
         return out
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None

@@ -40,6 +40,8 @@ struct Params {
   int64_t block_stride, token_stride, head_stride;  // cache, elements
   float scale_log2;                                 // softmax scale * log2(e)
   int causal;
+  const float* k_scale;                             // fp8 cache: per-tensor dequantisation scales (device)
+  const float* v_scale;
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
@@ -94,25 +96,46 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// two e4m3 bytes (low byte first) -> two T values packed in 32 bits; exact (e4m3 fits f16 and bf16)
+template <typename T>
+__device__ __forceinline__ uint32_t e4m3x2_to(uint16_t v);
+template <>
+__device__ __forceinline__ uint32_t e4m3x2_to<__half>(uint16_t v) { return e4m3x2_to_f16x2(v); }
+template <>
+__device__ __forceinline__ uint32_t e4m3x2_to<__nv_bfloat16>(uint16_t v) {
+  const uint32_t h = e4m3x2_to_f16x2(v);
+  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h));
+  return pack2<__nv_bfloat16>(f.x, f.y);
+}
+
 // byte offset of 16-byte chunk `c` of row `r` in a tile whose rows hold D 16-bit elements
 template <int D>
 __device__ __forceinline__ uint32_t swz(int r, int c) {
   return (uint32_t)(r * (D * 2) + ((c ^ (r & 7)) << 4));
 }
 
-template <typename T, int D, int MT>
+// FP8: the cache holds e4m3 bytes.  Tiles arrive as bytes in a two-stage staging ring and are expanded (exactly) to T
+// into ONE 16-bit tile pair in front of the MMAs; the per-tensor scales are folded into the logits (k) and the output
+// (v), as the decode kernel does.
+template <typename T, int D, int MT, bool FP8>
 __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Params p) {
   pdl_wait();
   pdl_trigger();
   constexpr int BM = 16 * MT * NWARPS;             // query rows per CTA: every warp owns MT 16-row tiles
-  constexpr int CPR = D / 8;                       // 16-byte chunks per row
-  constexpr int KV_PASSES = BN * CPR / NTHREADS;   // chunks of one K (or V) tile per thread
+  constexpr int CPR = D / 8;                       // 16-byte chunks per row of 16-bit elements
+  constexpr int CPR_KV = FP8 ? D / 16 : D / 8;     // 16-byte chunks per cache row as it is loaded
+  constexpr int KV_PASSES = BN * CPR_KV / NTHREADS;   // chunks of one K (or V) tile per thread
   constexpr int Q_PASSES = BM * CPR / NTHREADS;
-  static_assert(BN * CPR % NTHREADS == 0 && D % 16 == 0, "tile / head size");
+  constexpr int TILE16 = BN * D * 2, TILE_LD = FP8 ? BN * D : TILE16;
+  static_assert(BN * CPR_KV % NTHREADS == 0 && D % 16 == 0, "tile / head size");
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t sQ = (uint32_t)__cvta_generic_to_shared(smem);
-  const uint32_t sK = sQ + BM * D * 2;             // 2 stages
-  const uint32_t sV = sK + 2 * BN * D * 2;         // 2 stages
+  const uint32_t sK = sQ + BM * D * 2;             // 2 stages (as loaded)
+  const uint32_t sV = sK + 2 * TILE_LD;            // 2 stages
+  const uint32_t sK16 = sV + 2 * TILE_LD;          // FP8 only: the expanded tiles
+  const uint32_t sV16 = sK16 + TILE16;
+  const uint8_t* smem_k8 = smem + BM * D * 2;      // generic views of the staging ring (FP8)
+  const uint8_t* smem_v8 = smem_k8 + 2 * TILE_LD;
 
   // The rows of a tile are (token, query head of this kv head's group) pairs, token-major: row r of a sequence is
   // token r / G, head kvh * G + r % G -- a K / V tile is loaded once for the whole GQA group, and a decode row of a
@@ -145,8 +168,10 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, tq = lane & 3;
   const T* qg = reinterpret_cast<const T*>(p.q) + (int64_t)q0 * p.q_stride + (int64_t)kvh * G * D;
-  const T* kc = reinterpret_cast<const T*>(p.k_cache) + (int64_t)kvh * p.head_stride;
-  const T* vc = reinterpret_cast<const T*>(p.v_cache) + (int64_t)kvh * p.head_stride;
+  const T* kc = reinterpret_cast<const T*>(p.k_cache) + (FP8 ? 0 : (int64_t)kvh * p.head_stride);   // 16-bit caches
+  const T* vc = reinterpret_cast<const T*>(p.v_cache) + (FP8 ? 0 : (int64_t)kvh * p.head_stride);
+  const float scale_log2 = FP8 ? p.scale_log2 * *p.k_scale : p.scale_log2;
+  const float out_scale = FP8 ? *p.v_scale : 1.f;
   const int* bt = p.block_table + (int64_t)seq * p.max_blocks_per_seq;
   const int bmask = (1 << p.block_shift) - 1;
 
@@ -160,20 +185,50 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
     cp_async16(sQ + swz<D>(r, c), qg + (int64_t)tok * p.q_stride + hd * D + c * 8, ok);
   }
   auto load_kv = [&](int j, int stage) {
-    const uint32_t dk = sK + stage * (BN * D * 2), dv = sV + stage * (BN * D * 2);
+    const uint32_t dk = sK + stage * TILE_LD, dv = sV + stage * TILE_LD;
 #pragma unroll
     for (int i = 0; i < KV_PASSES; ++i) {
       const int idx = tid + i * NTHREADS;
-      const int r = idx / CPR, c = idx % CPR;
+      const int r = idx / CPR_KV, c = idx % CPR_KV;
       const int n = j * BN + r;
       const bool ok = n < n_keys;
       int64_t off = 0;
       if (ok) {
         const int page = bt[n >> p.block_shift];
-        off = (int64_t)page * p.block_stride + (int64_t)(n & bmask) * p.token_stride + c * 8;
+        off = (int64_t)page * p.block_stride + (int64_t)(n & bmask) * p.token_stride + c * (FP8 ? 16 : 8);
       }
-      cp_async16(dk + swz<D>(r, c), kc + off, ok);
-      cp_async16(dv + swz<D>(r, c), vc + off, ok);
+      if (FP8) {   // bytes, rows as they lie (the expansion pass reads them 16 bytes per thread: conflict-free)
+        cp_async16(dk + r * D + c * 16, reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * p.head_stride + off, ok);
+        cp_async16(dv + r * D + c * 16, reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * p.head_stride + off, ok);
+      } else {
+        cp_async16(dk + swz<D>(r, c), kc + off, ok);
+        cp_async16(dv + swz<D>(r, c), vc + off, ok);
+      }
+    }
+  };
+  // FP8: bytes of stage `stage` -> the swizzled 16-bit tiles
+  auto expand_kv = [&](int stage) {
+#pragma unroll
+    for (int i = 0; i < KV_PASSES; ++i) {
+      const int idx = tid + i * NTHREADS;
+      const int r = idx / CPR_KV, c = idx % CPR_KV;
+#pragma unroll
+      for (int which = 0; which < 2; ++which) {
+        const uint8_t* src = (which ? smem_v8 : smem_k8) + stage * TILE_LD + r * D + c * 16;
+        const uint4 b = *reinterpret_cast<const uint4*>(src);
+        const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+        uint32_t o[8];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          o[2 * k] = e4m3x2_to<T>((uint16_t)(w[k] & 0xffffu));
+          o[2 * k + 1] = e4m3x2_to<T>((uint16_t)(w[k] >> 16));
+        }
+        const uint32_t dst = which ? sV16 : sK16;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + swz<D>(r, 2 * c)), "r"(o[0]), "r"(o[1]),
+                     "r"(o[2]), "r"(o[3]) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + swz<D>(r, 2 * c + 1)), "r"(o[4]), "r"(o[5]),
+                     "r"(o[6]), "r"(o[7]) : "memory");
+      }
     }
   };
   if (n_tiles > 0) load_kv(0, 0);
@@ -210,7 +265,11 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       for (int ks = 0; ks < (QREG ? D / 16 : 1); ++ks)
         ldsm_x4(sQ + swz<D>(wrow + (lane & 15), ks * 2 + (lane >> 4)), qf[ks]);
     }
-    const uint32_t tk = sK + stage * (BN * D * 2), tv = sV + stage * (BN * D * 2);
+    if (FP8) {
+      expand_kv(stage);
+      __syncthreads();
+    }
+    const uint32_t tk = FP8 ? sK16 : sK + stage * TILE16, tv = FP8 ? sV16 : sV + stage * TILE16;
     // ---- S = Q K^T  (16 * MT rows x 64 keys per warp): a K fragment feeds MT row tiles
     float s[MT][BN / 8][4];
 #pragma unroll
@@ -269,8 +328,8 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       for (int h = 0; h < 2; ++h) {
         mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
         mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
-        mscaled[h] = mx[h] == -INFINITY ? 0.f : mx[h] * p.scale_log2;     // a fully masked row so far: exp2(-inf) = 0
-        alpha[h] = ex2(row_max[mt][h] * p.scale_log2 - mscaled[h]);     // row_max = -inf -> 0
+        mscaled[h] = mx[h] == -INFINITY ? 0.f : mx[h] * scale_log2;     // a fully masked row so far: exp2(-inf) = 0
+        alpha[h] = ex2(row_max[mt][h] * scale_log2 - mscaled[h]);     // row_max = -inf -> 0
         row_max[mt][h] = mx[h];
         row_sum[mt][h] *= alpha[h];
       }
@@ -283,10 +342,10 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       }
 #pragma unroll
       for (int i = 0; i < BN / 8; ++i) {
-        s[mt][i][0] = ex2(fmaf(s[mt][i][0], p.scale_log2, -mscaled[0]));
-        s[mt][i][1] = ex2(fmaf(s[mt][i][1], p.scale_log2, -mscaled[0]));
-        s[mt][i][2] = ex2(fmaf(s[mt][i][2], p.scale_log2, -mscaled[1]));
-        s[mt][i][3] = ex2(fmaf(s[mt][i][3], p.scale_log2, -mscaled[1]));
+        s[mt][i][0] = ex2(fmaf(s[mt][i][0], scale_log2, -mscaled[0]));
+        s[mt][i][1] = ex2(fmaf(s[mt][i][1], scale_log2, -mscaled[0]));
+        s[mt][i][2] = ex2(fmaf(s[mt][i][2], scale_log2, -mscaled[1]));
+        s[mt][i][3] = ex2(fmaf(s[mt][i][3], scale_log2, -mscaled[1]));
         row_sum[mt][0] += s[mt][i][0] + s[mt][i][1];
         row_sum[mt][1] += s[mt][i][2] + s[mt][i][3];
       }
@@ -313,7 +372,10 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
         }
       }
     }
-    __syncthreads();   // every warp is done with this stage before the next iteration's loads overwrite it
+    // 16-bit caches: every warp is done with this stage before the next iteration's loads overwrite it.  FP8: the
+    // expanded tiles are next written after the following iteration's first barrier, which every warp reaches
+    // only after these MMAs.
+    if (!FP8) __syncthreads();
   }
   cp_wait<0>();
 
@@ -328,7 +390,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       l += __shfl_xor_sync(0xffffffffu, l, 2);
       const int row = m0 + wrow + mt * 16 + g + h * 8;
       if (row < n_rows) {
-        const float inv = l > 0.f ? 1.f / l : 0.f;
+        const float inv = l > 0.f ? out_scale / l : 0.f;
         T* orow = og + (int64_t)tok_of[mt][h] * p.o_stride + (row - tok_of[mt][h] * G) * D;
 #pragma unroll
         for (int i = 0; i < D / 8; ++i)
@@ -339,11 +401,11 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   }
 }
 
-template <typename T, int D, int MT>
+template <typename T, int D, int MT, bool FP8>
 static int launch(const Params& p, int total_q, cudaStream_t stream) {
-  auto kern = paged_prefill_flash_kernel<T, D, MT>;
+  auto kern = paged_prefill_flash_kernel<T, D, MT, FP8>;
   constexpr int BM = 16 * MT * NWARPS;
-  const size_t smem = (size_t)(BM + 4 * BN) * D * 2;
+  const size_t smem = (size_t)BM * D * 2 + (FP8 ? (size_t)4 * BN * D + (size_t)2 * BN * D * 2 : (size_t)4 * BN * D * 2);
   if (smem > 48 * 1024)
     VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // every sequence adds at most one partial tile: an upper bound that needs no host read of cu_seqlens_q
@@ -354,15 +416,15 @@ static int launch(const Params& p, int total_q, cudaStream_t stream) {
 }
 
 // 128-row tiles (two 16-row tiles per warp: every K / V fragment read from shared memory feeds two MMAs' worth of
-// rows) once some sequence has more than 64 new tokens; 64-row tiles for short chunks and for head size 256, whose
+// rows) once some sequence has more than 64 rows; 64-row tiles for short chunks and for head size 256, whose
 // accumulators leave no room for the second tile.
-template <typename T>
+template <typename T, bool FP8>
 static int dispatch(const Params& p, int head_size, int total_q, int max_seqlen_q, cudaStream_t stream) {
   const bool big = (int64_t)max_seqlen_q * p.group > 64;
   switch (head_size) {
-    case 64: return big ? launch<T, 64, 2>(p, total_q, stream) : launch<T, 64, 1>(p, total_q, stream);
-    case 128: return big ? launch<T, 128, 2>(p, total_q, stream) : launch<T, 128, 1>(p, total_q, stream);
-    case 256: return launch<T, 256, 1>(p, total_q, stream);
+    case 64: return big ? launch<T, 64, 2, FP8>(p, total_q, stream) : launch<T, 64, 1, FP8>(p, total_q, stream);
+    case 128: return big ? launch<T, 128, 2, FP8>(p, total_q, stream) : launch<T, 128, 1, FP8>(p, total_q, stream);
+    case 256: return launch<T, 256, 1, FP8>(p, total_q, stream);
     default: break;
   }
   VB_CHECK(false, "flash_attn_varlen_paged: head size %d is not supported (64, 128, 256)", head_size);
@@ -379,15 +441,18 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
                                              const int32_t* block_table, int num_seqs, int total_q, int num_heads,
                                              int num_kv_heads, int head_size, int block_size,
                                              int max_num_blocks_per_seq, int max_seqlen_q, float scale, int causal,
-                                             int dtype,
+                                             int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
                                              int64_t q_stride, int64_t out_stride, int64_t block_stride,
                                              int64_t token_stride, int64_t head_stride, vb200_stream_t stream) {
   VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "flash_attn_varlen_paged: dtype must be f16 or bf16");
   VB_CHECK(num_kv_heads > 0 && num_heads % num_kv_heads == 0, "flash_attn_varlen_paged: num_heads %% num_kv_heads != 0");
   VB_CHECK(block_size > 0 && (block_size & (block_size - 1)) == 0,
            "flash_attn_varlen_paged: block_size %d must be a power of two", block_size);
-  VB_CHECK(((q_stride | out_stride | block_stride | token_stride | head_stride) & 7) == 0,
-           "flash_attn_varlen_paged: strides must be multiples of 8 elements (16 bytes)");
+  VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3, "Unsupported data type of kv cache: %d", kv_dtype);
+  const bool fp8 = kv_dtype == VB200_KV_FP8_E4M3;
+  VB_CHECK(!fp8 || (k_scale && v_scale), "fp8 kv cache needs k_scale and v_scale");
+  VB_CHECK(((q_stride | out_stride) & 7) == 0 && ((block_stride | token_stride | head_stride) & (fp8 ? 15 : 7)) == 0,
+           "flash_attn_varlen_paged: strides must be multiples of 16 bytes");
   VB_CHECK(((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(query) |
              reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15) == 0,
            "flash_attn_varlen_paged: tensors must be 16-byte aligned");
@@ -414,7 +479,13 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
   p.head_stride = head_stride;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.causal = causal;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
   if (max_seqlen_q <= 0) max_seqlen_q = total_q;   // unknown: assume long chunks
-  if (dtype == VB200_F16) return prefill::dispatch<__half>(p, head_size, total_q, max_seqlen_q, (cudaStream_t)stream);
-  return prefill::dispatch<__nv_bfloat16>(p, head_size, total_q, max_seqlen_q, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == VB200_F16)
+    return fp8 ? prefill::dispatch<__half, true>(p, head_size, total_q, max_seqlen_q, st)
+               : prefill::dispatch<__half, false>(p, head_size, total_q, max_seqlen_q, st);
+  return fp8 ? prefill::dispatch<__nv_bfloat16, true>(p, head_size, total_q, max_seqlen_q, st)
+             : prefill::dispatch<__nv_bfloat16, false>(p, head_size, total_q, max_seqlen_q, st);
 }
