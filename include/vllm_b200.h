@@ -146,6 +146,25 @@ int vb200_paged_attention_v1(void* out, const void* query, const void* key_cache
                              int partition_size, void* workspace, size_t workspace_bytes,
                              vb200_stream_t stream);
 
+/* paged_attention_v1 that allocates nothing and takes no workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, partition plan, kernels and results as
+ * vb200_paged_attention_v1 given a workspace of vb200_paged_attention_v1_workspace_size() bytes; the split-K partials
+ * live in a library-owned static device array of vb200_paged_attention_v1_static_max_bytes() = 16 MiB, resident on
+ * every GPU that loads the library until the process exits.  A call whose partials need more (num_seqs * num_heads *
+ * partitions * (8 + 2 * head_size) + 64 bytes) is rejected with an error; use the workspace form for it.  No
+ * cudaMalloc / cudaFree or allocating library routine is called.  All calls on a device share the array and it keeps
+ * the last call's contents (nothing in it has to start at zero: every slot read is written first by the same call);
+ * calls that overlap on the GPU -- different streams, or a graph replay beside eager work -- race on it. */
+size_t vb200_paged_attention_v1_static_max_bytes(void);
+int vb200_paged_attention_v1_static(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                    int num_seqs, int num_heads, int head_size, int num_kv_heads, float scale,
+                                    const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+                                    int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype,
+                                    int kv_dtype, const float* k_scale, const float* v_scale, int64_t q_stride,
+                                    int64_t kv_block_stride, int64_t kv_head_stride, int partition_size,
+                                    vb200_stream_t stream);
+
 /* paged_attention_v1 with the dynamic per-token fp8 quantisation of its output fused into the split-K reduce kernel
  * (SURVEY.md 8f row 1): out_q fp8 [num_seqs, num_heads*head_size] and out_scales fp32 [num_seqs] are exactly what
  * vb200_paged_attention_v1 followed by vb200_dynamic_per_token_scaled_fp8_quant (fp8/common.cu:28-83) produce on the

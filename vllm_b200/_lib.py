@@ -60,6 +60,10 @@ SIGNATURES = {
     "vb200_paged_attention_v1": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P,
                                          c_int, c_int, c_int, _P, c_int, c_int, _P, _P, c_int64, c_int64,
                                          c_int64, c_int, _P, c_size_t, _P]),
+    "vb200_paged_attention_v1_static_max_bytes": (c_size_t, []),
+    "vb200_paged_attention_v1_static": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P,
+                                                c_int, c_int, c_int, _P, c_int, c_int, _P, _P, c_int64, c_int64,
+                                                c_int64, c_int, _P]),
     "vb200_paged_attention_v1_quant_workspace_size": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "vb200_paged_attention_v1_quant": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, c_int,
                                                c_int, c_int, _P, c_int, c_int, _P, _P, c_int64, c_int64, c_int64, c_int,

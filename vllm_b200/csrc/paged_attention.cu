@@ -19,6 +19,7 @@
 //    either the final output or the v2 partials (normalised tmp_out, exp_sums, max_logits) with
 //    the reference's +1e-6 normalisers (attention_kernels.cuh:337,647).
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -1165,4 +1166,62 @@ extern "C" int vb200_paged_attention_v1_quant(
   p.out_scales = out_scales;
   p.scale_ub = scale_ub;
   return run_paged_attention(p, num_seqs, head_size, block_size, max_seq_len, q_dtype, kv_dtype, (cudaStream_t)stream);
+}
+
+// ---- paged_attention_v1 over library-owned scratch: an entry point that allocates nothing ------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The split-K partials
+// (exp_sums | max_logits | tmp_out) live in a file-scope device array instead of a caller workspace.  Every GPU that
+// loads the library holds the array until exit; every call on a device shares it, so calls that overlap on the GPU
+// (two streams, or a graph replay next to eager work) race on it.  Nothing in it has to start at zero: the main
+// kernel writes every (sequence, head, partition) slot the reduce kernel reads, so the previous call's contents are
+// never observed and no clearing launch is needed.
+#define VB200_PA_STATIC_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) unsigned char g_pa_static_scratch[VB200_PA_STATIC_SCRATCH_BYTES];
+
+// In host code `g_pa_static_scratch` is a host-side stand-in, not a device address: the address a kernel may use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int pa_static_scratch_ptr(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  VB_CUDA_CHECK(cudaGetDevice(&dev));
+  VB_CHECK(dev >= 0 && dev < kMaxDevices, "paged_attention_v1_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    VB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_pa_static_scratch));
+    VB_CHECK(p != nullptr, "paged_attention_v1_static: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+extern "C" size_t vb200_paged_attention_v1_static_max_bytes(void) { return VB200_PA_STATIC_SCRATCH_BYTES; }
+
+extern "C" int vb200_paged_attention_v1_static(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+    int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+    int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
+    const float* k_scale, const float* v_scale, int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride,
+    int partition_size, vb200_stream_t stream) {
+  int part = partition_size;
+  if (part <= 0)
+    part = vb200_paged_attention_v1_partition_size(num_seqs, num_heads, num_kv_heads, head_size, max_seq_len, block_size,
+                                                   kv_dtype);
+  const size_t need = vb200_paged_attention_v1_workspace_size(num_seqs, num_heads, head_size, max_seq_len, q_dtype, part);
+  VB_CHECK(need <= (size_t)VB200_PA_STATIC_SCRATCH_BYTES,
+           "paged_attention_v1_static: the split-K partials of this call need %zu bytes, the library-owned scratch "
+           "holds %zu (num_seqs %d x num_heads %d x partitions of %d tokens over max_seq_len %d); use "
+           "vb200_paged_attention_v1 with a caller workspace",
+           need, (size_t)VB200_PA_STATIC_SCRATCH_BYTES, num_seqs, num_heads, part, max_seq_len);
+  void* scratch = nullptr;
+  if (int rc = pa_static_scratch_ptr(&scratch)) return rc;
+  // same partition plan, kernels and arithmetic as vb200_paged_attention_v1 given a caller workspace of `need` bytes
+  return vb200_paged_attention_v1(out, query, key_cache, value_cache, num_seqs, num_heads, head_size, num_kv_heads, scale,
+                                  block_tables, seq_lens, block_size, max_seq_len, max_num_blocks_per_seq, alibi_slopes,
+                                  q_dtype, kv_dtype, k_scale, v_scale, q_stride, kv_block_stride, kv_head_stride, part,
+                                  scratch, (size_t)VB200_PA_STATIC_SCRATCH_BYTES, stream);
 }
