@@ -38,9 +38,14 @@ def main():
     dev = torch.device("cuda")
     dtype = torch.bfloat16
     H, Hkv, D, bs = 32, 8, 128, 16
-    cases = [("prefill 8 x 2048", [(2048, 2048)] * 8), ("prefill 1 x 8192", [(8192, 8192)]),
-             ("chunked 16 x 512 @ 4096", [(512, 4096)] * 16), ("mixed 4 x 1024 + 64 decodes @ 2048", [(1024, 1024)] * 4 + [(1, 2048)] * 64)]
-    for name, sl in cases:
+    # (name, [(query_len, kv_len)], sliding_window or None, soft_cap or 0)
+    cases = [("prefill 8 x 2048", [(2048, 2048)] * 8, None, 0.0), ("prefill 1 x 8192", [(8192, 8192)], None, 0.0),
+             ("chunked 16 x 512 @ 4096", [(512, 4096)] * 16, None, 0.0),
+             ("mixed 4 x 1024 + 64 decodes @ 2048", [(1024, 1024)] * 4 + [(1, 2048)] * 64, None, 0.0),
+             ("prefill 1 x 8192, window 1024", [(8192, 8192)], 1024, 0.0),
+             ("prefill 8 x 2048, soft cap 50", [(2048, 2048)] * 8, None, 50.0),
+             ("chunked 16 x 512 @ 4096, window 1024 + soft cap 30", [(512, 4096)] * 16, 1024, 30.0)]
+    for name, sl, window, cap in cases:
         ql = [x[0] for x in sl]
         kl = [x[1] for x in sl]
         nb = sum((k + bs - 1) // bs for k in kl) + 8
@@ -59,14 +64,18 @@ def main():
         kv_lens = torch.tensor(kl, dtype=torch.int32, device=dev)
         out = torch.empty_like(q)
         scale = D ** -0.5
-        flops = 4.0 * D * H * sum(sum(range(k - qq + 1, k + 1)) for qq, k in sl)
-        us = timed(lambda: ops.flash_attn_varlen_paged(out, q, kc, vc, cu, kv_lens, bt, scale, True, max(ql)))
+        vis = lambda p: p if window is None else min(p, window)   # noqa: E731  keys a query at 1-based position p sees
+        flops = 4.0 * D * H * sum(sum(vis(p) for p in range(k - qq + 1, k + 1)) for qq, k in sl)
+        wl = -1 if window is None else window - 1
+        us = timed(lambda: ops.flash_attn_varlen_paged(out, q, kc, vc, cu, kv_lens, bt, scale, True, max(ql),
+                                                       window_left=wl, softcap=cap))
         line = {"case": name, "H": H, "Hkv": Hkv, "D": D, "ours_us": round(us, 1), "ours_TFLOPs": round(flops / us / 1e6, 1)}
         if lib_fa is not None:
             try:
                 out2 = torch.empty_like(q)
                 f = lambda: lib_fa(q=q, k=kc, v=vc, out=out2, cu_seqlens_q=cu, max_seqlen_q=max(ql), seqused_k=kv_lens,  # noqa: E731
-                                   max_seqlen_k=max(kl), softmax_scale=scale, causal=True, block_table=bt, fa_version=2)
+                                   max_seqlen_k=max(kl), softmax_scale=scale, causal=True, block_table=bt, fa_version=2,
+                                   window_size=(wl, 0) if window is not None else (-1, -1), softcap=cap)
                 lus = timed(f)
                 line.update({"library_us": round(lus, 1), "library_TFLOPs": round(flops / lus / 1e6, 1),
                              "max_abs_diff_vs_library": float((out.float() - out2.float()).abs().max())})

@@ -213,7 +213,7 @@ int vb200_paged_attention_flash(void* out, const void* query, const void* key_ca
  * seqused_k[s] tokens of the sequence, the new ones last; row i of a sequence with
  * q_len new tokens attends keys 0 .. seqused_k[s] - q_len + i when `causal`, all seqused_k[s] keys otherwise.
  * max_seqlen_q: the longest q_len (the reference call's argument; picks 64- or 128-row tiles, <= 0 = unknown).
- * head_size 64 / 128 / 256; strides multiples of 16 bytes; no workspace, no host read of the device arrays. */
+ * head_size 64 / 128 / 192 / 256; strides multiples of 16 bytes; no workspace, no host read of the device arrays. */
 int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_cache, const void* value_cache,
                                   const int32_t* cu_seqlens_q, const int32_t* seqused_k, const int32_t* block_table,
                                   int num_seqs, int total_q, int num_heads, int num_kv_heads, int head_size,
@@ -221,6 +221,25 @@ int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_
                                   int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
                                   int64_t q_stride, int64_t out_stride, int64_t block_stride, int64_t token_stride,
                                   int64_t head_stride, vb200_stream_t stream);
+/* The same call with the two remaining arguments the reference backend passes (flash_attn.py:342-350,507-510):
+ *   window_left: sliding window, flash-attn's window_size = (window_left, 0) = (sliding_window - 1, 0): a query at
+ *                absolute position p attends keys p - window_left .. p only (needs causal); < 0 = no window;
+ *   softcap:     logits soft-capping, logits = softcap * tanh(logits / softcap) before the mask; 0 = off.
+ * Golden: ref_paged_attn, tests/kernels/attention/test_flash_attn.py:25-77 (sliding_window :62-67, soft_cap :68-69);
+ * the reference test runs sliding_window in {None, 256} and soft_cap in {None, 10, 50} (:86-88,:201-203).
+ *   softmax_lse: optional fp32 [num_heads, lse_stride >= total_q]: the natural-log sum of exponentials of every
+ *                query row's (scaled, capped, masked) logits -- flash_attn_varlen_func(return_softmax_lse=True), what
+ *                cascade_attention (flash_attn.py:674-764) feeds to merge_attn_states; -inf for a row without a
+ *                visible key; NULL = not wanted.
+ * K / V tiles that lie left of every row's window are never loaded.  Decode batches (q_len 1) are accepted. */
+int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                       const int32_t* cu_seqlens_q, const int32_t* seqused_k,
+                                       const int32_t* block_table, int num_seqs, int total_q, int num_heads,
+                                       int num_kv_heads, int head_size, int block_size, int max_num_blocks_per_seq,
+                                       int max_seqlen_q, float scale, int causal, int dtype, int kv_dtype,
+                                       const float* k_scale, const float* v_scale, int64_t q_stride, int64_t out_stride,
+                                       int64_t block_stride, int64_t token_stride, int64_t head_stride, int window_left,
+                                       float softcap, float* softmax_lse, int64_t lse_stride, vb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------ */
 /* FP8 activation quantisation + activation                                                    */

@@ -106,13 +106,16 @@ def paged_attention_v2(query, key_cache, value_cache, num_kv_heads, scale, block
     return out, exp_sums, max_logits, tmp_out
 
 
-def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, block_tables, scale, causal=True):
+def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, block_tables, scale, causal=True,
+                            sliding_window=None, soft_cap=None):
     """Variable-length attention over the FLASH cache layout (prefill / chunked prefill / mixed batches): the golden of
     the reference's own test, /root/reference/tests/kernels/attention/test_flash_attn.py:25-77 (`ref_paged_attn`),
     restated: per sequence gather its kv_len tokens through the block table from key_cache / value_cache
     `[num_blocks, block_size, num_kv_heads, head_size]` (:48-54), repeat kv heads for GQA (:56-58), fp32 logits of the
     scaled query (:46,59), bottom-right aligned causal mask `triu(diagonal = kv_len - query_len + 1)` (:60-61,70),
-    softmax rounded to the value dtype (:71), times V (:72).  query [sum(query_lens), H, D] -> same shape."""
+    softmax rounded to the value dtype (:71), times V (:72).  query [sum(query_lens), H, D] -> same shape.
+    sliding_window (:62-67): a query at absolute position p sees keys p - sliding_window + 1 .. p only; soft_cap
+    (:68-69): logits become soft_cap * tanh(logits / soft_cap) before the mask."""
     nb, bs, Hkv, D = key_cache.shape
     outs, start = [], 0
     for i, (ql, kl) in enumerate(zip(query_lens, kv_lens)):
@@ -125,9 +128,15 @@ def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, 
             k = torch.repeat_interleave(k, q.shape[1] // Hkv, dim=1)
             v = torch.repeat_interleave(v, q.shape[1] // Hkv, dim=1)
         attn = torch.einsum("qhd,khd->hqk", q, k.float())
+        if soft_cap:
+            attn = soft_cap * torch.tanh(attn / soft_cap)
         if causal:
             mask = torch.triu(torch.ones(ql, kl), diagonal=kl - ql + 1).bool()
+            if sliding_window is not None:
+                mask |= torch.triu(torch.ones(ql, kl), diagonal=kl - (ql + sliding_window) + 1).bool().logical_not()
             attn.masked_fill_(mask, float("-inf"))
+        elif sliding_window is not None:
+            raise ValueError("a sliding window needs the causal mask")
         attn = torch.softmax(attn, dim=-1).to(v.dtype)
         outs.append(torch.einsum("hqk,khd->qhd", attn.float(), v.float()).to(query.dtype))
         start += ql

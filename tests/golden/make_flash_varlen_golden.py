@@ -31,6 +31,12 @@ def main():
         # the reference test's first seq_lens list (:192-193) at one of its head configurations
         "flash_varlen_ref_case": dict(seq_lens=[(1, 1328), (5, 18), (129, 463)], H=8, Hkv=2, D=128, bs=16, nb=32, seed=0),
         "flash_varlen_prefill_gqa7": dict(seq_lens=[(70, 70), (33, 200), (1, 97)], H=14, Hkv=2, D=64, bs=32, nb=16, seed=1),
+        # the reference test's sliding_window / soft_cap parameters (:86-88, :201-203)
+        "flash_varlen_window256": dict(seq_lens=[(1, 523), (130, 400), (5, 18)], H=4, Hkv=2, D=64, bs=16, nb=24, seed=2,
+                                       sliding_window=256),
+        "flash_varlen_softcap10_window": dict(seq_lens=[(1, 300), (90, 333)], H=4, Hkv=4, D=64, bs=16, nb=24, seed=3,
+                                              sliding_window=100, soft_cap=10.0),
+        "flash_varlen_softcap50": dict(seq_lens=[(40, 200), (1, 77)], H=8, Hkv=2, D=64, bs=16, nb=16, seed=4, soft_cap=50.0),
     }
     for name, c in cases.items():
         torch.manual_seed(c["seed"])
@@ -42,11 +48,14 @@ def main():
         maxb = (max(kl) + c["bs"] - 1) // c["bs"]
         bt = torch.randint(0, c["nb"], (len(ql), maxb), dtype=torch.int32)
         scale = c["D"] ** -0.5
-        out = ref(query=q.clone(), key_cache=kc, value_cache=vc, query_lens=ql, kv_lens=kl, block_tables=bt, scale=scale)
+        out = ref(query=q.clone(), key_cache=kc, value_cache=vc, query_lens=ql, kv_lens=kl, block_tables=bt, scale=scale,
+                  sliding_window=c.get("sliding_window"), soft_cap=c.get("soft_cap"))
         as_i16 = lambda t: t.contiguous().view(torch.int16).numpy()  # noqa: E731
         np.savez_compressed(os.path.join(HERE, name + ".npz"), q=as_i16(q), key_cache=as_i16(kc), value_cache=as_i16(vc),
                             block_tables=bt.numpy(), query_lens=np.array(ql), kv_lens=np.array(kl),
-                            scale=np.float32(scale), out=as_i16(out.to(torch.bfloat16)))
+                            scale=np.float32(scale), out=as_i16(out.to(torch.bfloat16)),
+                            sliding_window=np.int64(c.get("sliding_window") or -1),
+                            soft_cap=np.float32(c.get("soft_cap") or 0.0))
         print(name, tuple(out.shape), os.path.getsize(os.path.join(HERE, name + ".npz")))
 
 

@@ -230,3 +230,67 @@ def test_paged_attention_v1_quant_matches_unfused(kvd, case):
     assert got_q.shape == (S, H * D) and got_s.shape == (S, 1)
     assert torch.equal(got_s, want_s.view(S, 1))
     assert torch.equal(got_q.view(torch.uint8), want_q.view(torch.uint8))
+
+
+# ---- BASELINE.json-sized problems: the per-layer attention call of configs[1], [2], [4] (per-GPU shard at TP 8) and a
+# ragged batch.  Too big for the CPU oracle, so the checks are (1) the reference's own CUDA kernel on the same inputs
+# when oracle/_ref is present, (2) size-independent properties: the split-K plan does not change the result, v2 == v1,
+# a sequence's output does not depend on its batch neighbours (a sub-batch at oracle size reproduces its rows), and
+# that sub-batch against the CPU oracle. ------------------------------------------------------------------------------
+BASELINE_SHAPES = [
+    # name, S, H, Hkv, D, kv dtype, sequence lengths
+    ("cfg2_bf16_64x2k", 64, 32, 8, 128, "auto", [2048] * 64),
+    ("cfg3_fp8_256x4k", 256, 32, 8, 128, "fp8", [4096] * 256),
+    ("cfg5_tp8_shard_fp8_128x8k", 128, 8, 1, 128, "fp8", [8192] * 128),
+    ("ragged_bf16_64", 64, 32, 8, 128, "auto", [1 + (i * 977) % 2048 for i in range(64)]),
+]
+
+
+def _device_paged_kv(nb, bs, Hkv, D, dtype, kvd, ksc, vsc):
+    """Caches in the reference paged layout generated on the GPU (the CPU helper would take minutes at these sizes)."""
+    x = 16 if kvd == "fp8" else 8
+    k = torch.randn(nb, Hkv, D // x, bs, x, device=DEV)
+    v = torch.randn(nb, Hkv, D, bs, device=DEV)
+    if kvd == "fp8":
+        return ((k / ksc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8),
+                (v / vsc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8))
+    return k.to(dtype), v.to(dtype)
+
+
+@pytest.mark.parametrize("shape", BASELINE_SHAPES, ids=lambda s: s[0])
+def test_paged_attention_baseline_sized(shape):
+    name, S, H, Hkv, D, kvd, seq_lens = shape
+    bs, dtype = 16, torch.bfloat16
+    seed_all(len(name))
+    blocks_per_seq = (max(seq_lens) + bs - 1) // bs
+    nb = S * blocks_per_seq
+    ksc, vsc = (0.043, 0.029) if kvd == "fp8" else (1.0, 1.0)
+    kc, vc = _device_paged_kv(nb, bs, Hkv, D, dtype, kvd, ksc, vsc)
+    q = (torch.randn(S, H, D, device=DEV) * 0.5).to(dtype)
+    bt = torch.randperm(nb, device=DEV).to(torch.int32).view(S, blocks_per_seq)
+    sl = torch.tensor(seq_lens, dtype=torch.int32, device=DEV)
+    scale = float(D ** -0.5)
+    ks, vs = torch.tensor(ksc, device=DEV), torch.tensor(vsc, device=DEV)
+    args = (q, kc, vc, Hkv, scale, bt, sl, bs, None, kvd, ks, vs)
+    got, _ = _run_ours("v1", *args)                       # the library's own split-K plan
+    torch.cuda.synchronize()
+    assert torch.isfinite(got.float()).all()
+    ref_out = _run_ref(*args)
+    if ref_out is not None:
+        torch.testing.assert_close(got.float(), ref_out.float(), rtol=RTOL, atol=ATOL)
+    unsplit, _ = _run_ours("v1", *args, partition_size=-1)
+    torch.testing.assert_close(got.float(), unsplit.float(), rtol=RTOL, atol=ATOL)
+    v2, _ = _run_ours("v2", *args)
+    torch.testing.assert_close(got.float(), v2.float(), rtol=RTOL, atol=ATOL)
+    # three sequences on their own (the longest, the shortest, the last): same rows, and equal to the CPU oracle
+    pick = sorted({max(range(S), key=lambda i: seq_lens[i]), min(range(S), key=lambda i: seq_lens[i]), S - 1})
+    idx = torch.tensor(pick, device=DEV)
+    sub_args = (q[idx].contiguous(), kc, vc, Hkv, scale, bt[idx].contiguous(), sl[idx].contiguous(), bs, None, kvd, ks, vs)
+    sub, _ = _run_ours("v1", *sub_args)
+    torch.testing.assert_close(sub.float(), got[idx].float(), rtol=RTOL, atol=ATOL)
+    # the oracle gathers through the block table: hand it only the blocks these sequences own, renumbered
+    own = bt[idx].reshape(-1).long()
+    kc_s, vc_s = kc[own].cpu(), vc[own].cpu()
+    bt_s = torch.arange(own.numel(), dtype=torch.int32).view(len(pick), blocks_per_seq)
+    want = oattn.paged_attention(q[idx].cpu(), kc_s, vc_s, Hkv, scale, bt_s, sl[idx].cpu(), None, kvd, ksc, vsc)
+    torch.testing.assert_close(sub.cpu().float(), want.float(), rtol=RTOL, atol=ATOL)

@@ -192,10 +192,11 @@ def test_flash_attn_varlen_func_rejects_what_is_not_built():
     cu = torch.arange(3, dtype=torch.int32, device=DEV)
     with pytest.raises(NotImplementedError):                                       # ALiBi outside the decode case
         flash_attn_varlen_func(q, kc, kc, 2, cu, 16, sl, block_table=bt, alibi_slopes=torch.ones(8, device=DEV))
-    with pytest.raises(NotImplementedError):
-        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, softcap=30.0)
-    with pytest.raises(NotImplementedError):
-        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, window_size=(128, 0))
+    with pytest.raises(NotImplementedError):                                       # a window needs the causal mask
+        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, window_size=(128, 0), causal=False)
+    with pytest.raises(NotImplementedError):                                       # ALiBi with a soft cap
+        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, softcap=30.0,
+                               alibi_slopes=torch.ones(8, device=DEV))
     with pytest.raises(RuntimeError):
         from vllm_b200 import _custom_ops as ops
         ops.paged_attention_flash(torch.empty_like(q), q, torch.zeros(4, 32, 2, 128, dtype=torch.bfloat16, device=DEV),
@@ -339,3 +340,191 @@ def test_flash_attn_varlen_paged_fp8_cache(seq_lens, head_size, heads, dtype, la
     vc = dequant_e4m3(v8, vsc, dtype)
     want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale)
     torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2, rtol=1e-2)
+
+
+# ---- sliding window / logits soft-capping (the reference test's grid: sliding_window in {None, 256}, soft_cap in
+# {None, 10, 50}, test_flash_attn.py:86-88,201-203; golden :62-69) -------------------------------------------------
+@pytest.mark.parametrize("dtype_layout", [(torch.float16, "NHD"), (torch.bfloat16, "HND")], ids=["f16-NHD", "bf16-HND"])
+@pytest.mark.parametrize("soft_cap", [None, 10.0, 50.0])
+@pytest.mark.parametrize("sliding_window", [None, 256, 70])
+@pytest.mark.parametrize("heads", [(8, 2), (14, 2)])
+@pytest.mark.parametrize("head_size", [64, 128, 256])
+@pytest.mark.parametrize("seq_lens", VARLEN_CASES[:4], ids=lambda c: f"n{len(c)}q{max(x[0] for x in c)}")
+def test_flash_attn_varlen_paged_window_softcap(seq_lens, head_size, heads, sliding_window, soft_cap, dtype_layout):
+    if sliding_window is None and soft_cap is None:
+        pytest.skip("the plain causal case is test_flash_attn_varlen_paged")
+    dtype, layout = dtype_layout
+    from vllm_b200.attention.flash_backend import flash_attn_varlen_func
+    H, Hkv = heads
+    seed_all(len(seq_lens) * 31 + head_size + H + (sliding_window or 0))
+    q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens = _varlen_inputs(seq_lens, H, Hkv, head_size, 16, dtype, layout)
+    scale = float(head_size ** -0.5)
+    kvl = torch.tensor(kv_lens, dtype=torch.int32, device=DEV)
+    window = (sliding_window - 1, 0) if sliding_window is not None else (-1, -1)      # as test_flash_attn.py:120,237
+    out = torch.full_like(q, float("nan"), device=DEV)
+    flash_attn_varlen_func(q=q.to(DEV), k=kd, v=vd, out=out, cu_seqlens_q=cu.to(DEV), seqused_k=kvl,
+                           max_seqlen_q=max(query_lens), max_seqlen_k=max(kv_lens), softmax_scale=scale, causal=True,
+                           window_size=window, block_table=bt.to(DEV), softcap=soft_cap if soft_cap is not None else 0)
+    torch.cuda.synchronize()
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale, sliding_window=sliding_window,
+                                         soft_cap=soft_cap)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("name", ["flash_varlen_window256", "flash_varlen_softcap10_window", "flash_varlen_softcap50"])
+def test_flash_attn_varlen_window_softcap_vs_reference_test_golden(name):
+    """The kernel against outputs of the reference test suite's own `ref_paged_attn` (tests/golden/
+    make_flash_varlen_golden.py), tolerance as test_flash_attn.py:316-318."""
+    import os
+    import numpy as np
+    from vllm_b200 import _custom_ops as ops
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    bf = lambda a: torch.from_numpy(a).view(torch.bfloat16)  # noqa: E731
+    q, kc, vc, want = bf(g["q"]), bf(g["key_cache"]), bf(g["value_cache"]), bf(g["out"])
+    ql, kl = g["query_lens"].tolist(), g["kv_lens"].tolist()
+    cu = torch.tensor([0] + ql, dtype=torch.int32).cumsum(0).to(torch.int32)
+    sw, cap = int(g["sliding_window"]), float(g["soft_cap"])
+    out = torch.full_like(q, float("nan"), device=DEV)
+    ops.flash_attn_varlen_paged(out, q.to(DEV), kc.to(DEV), vc.to(DEV), cu.to(DEV),
+                                torch.tensor(kl, dtype=torch.int32, device=DEV),
+                                torch.from_numpy(g["block_tables"]).to(DEV), float(g["scale"]), True, max(ql),
+                                window_left=sw - 1 if sw >= 0 else -1, softcap=cap)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+
+
+def test_flash_backend_decode_with_window_and_softcap_fp8():
+    """B200FlashAttentionImpl with sliding_window / logits_soft_cap (flash_attn.py:366-374) on a decode batch over an
+    fp8 cache: routed to the variable-length kernel."""
+    from oracle.fp8 import dequant_e4m3
+    from vllm_b200.attention.flash_backend import B200FlashAttentionImpl, B200FlashAttentionMetadata
+    seed_all(77)
+    H, Hkv, D, bs, nb, dtype = 8, 2, 128, 16, 128, torch.bfloat16
+    kv_lens = [300, 17, 129]
+    S = len(kv_lens)
+    ksc, vsc = 0.05, 0.03
+    kv8 = (torch.randn(2, nb, bs, Hkv, D) / 0.05).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+    perm = torch.randperm(nb)
+    bt = perm[:S * 20].view(S, 20).to(torch.int32)
+    q = torch.randn(S, H, D).to(dtype)
+    meta = B200FlashAttentionMetadata(
+        num_actual_tokens=S, max_query_len=1, query_start_loc=torch.arange(S + 1, dtype=torch.int32, device=DEV),
+        max_seq_len=max(kv_lens), seq_lens=torch.tensor(kv_lens, dtype=torch.int32, device=DEV), block_table=bt.to(DEV),
+        slot_mapping=torch.zeros(S, dtype=torch.int64, device=DEV))
+    impl = B200FlashAttentionImpl(H, D, D ** -0.5, Hkv, sliding_window=64, kv_cache_dtype="fp8", logits_soft_cap=30.0,
+                                  kv_sharing_target_layer_name="previous layer wrote the cache")
+
+    class _Layer:
+        _k_scale = torch.tensor([ksc], device=DEV)
+        _v_scale = torch.tensor([vsc], device=DEV)
+    out = torch.empty(S, H, D, dtype=dtype, device=DEV)
+    impl.forward(_Layer(), q.to(DEV), None, None, kv8.to(DEV), meta, output=out)
+    torch.cuda.synchronize()
+    kc, vc = dequant_e4m3(kv8[0], ksc, dtype), dequant_e4m3(kv8[1], vsc, dtype)
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, [1] * S, kv_lens, bt, D ** -0.5, sliding_window=64, soft_cap=30.0)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2, rtol=1e-2)
+
+
+# ---- cascade attention (shared prefix + per-query suffix merged through the log-sum-exps), modelled on
+# /root/reference/tests/kernels/attention/test_cascade_flash_attn.py:70-200 (cases :70-76, tolerance :200) -------------
+CASCADE_CASES = [
+    ([(129, 871), (18, 280), (37, 988), (1023, 2304), (1, 257)], 256),     # the reference's general case
+    ([(1, 1023), (1, 879), (1, 778), (1, 1777)] * 100, 512),               # its flash-decoding case
+    ([(5, 40), (1, 33)], 16),
+]
+
+
+@pytest.mark.parametrize("soft_cap", [None, 50])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("head_size", [128, 192, 256])
+@pytest.mark.parametrize("heads", [(4, 4), (8, 2), (16, 2)])
+@pytest.mark.parametrize("case", CASCADE_CASES, ids=["general", "decode400", "tiny"])
+def test_cascade_attention(case, heads, head_size, dtype, soft_cap):
+    from vllm_b200.attention.flash_backend import cascade_attention, flash_attn_varlen_func
+    seq_lens, common_prefix_len = case
+    H, Hkv = heads
+    bs, nb = 16, 2048
+    seed_all(0)
+    query_lens = [x[0] for x in seq_lens]
+    kv_lens = [x[1] for x in seq_lens]
+    kc = torch.randn(nb, bs, Hkv, head_size).to(dtype)
+    vc = torch.randn(nb, bs, Hkv, head_size).to(dtype)
+    q = torch.randn(sum(query_lens), H, head_size).to(dtype)
+    cu = torch.tensor([0] + query_lens, dtype=torch.int32).cumsum(0).to(torch.int32)
+    maxb = (max(kv_lens) + bs - 1) // bs
+    bt = torch.randint(0, nb, (len(seq_lens), maxb), dtype=torch.int32)
+    ncb = common_prefix_len // bs
+    bt[:, :ncb] = bt[0, :ncb]
+    scale = float(head_size ** -0.5)
+    cap = float(soft_cap or 0)
+    qd, kd, vd, btd, cud = q.to(DEV), kc.to(DEV), vc.to(DEV), bt.to(DEV), cu.to(DEV)
+    kvl = torch.tensor(kv_lens, dtype=torch.int32, device=DEV)
+    ref_out = flash_attn_varlen_func(q=qd, k=kd, v=vd, cu_seqlens_q=cud, seqused_k=kvl, max_seqlen_q=max(query_lens),
+                                     max_seqlen_k=max(kv_lens), softmax_scale=scale, causal=True, window_size=(-1, -1),
+                                     block_table=btd, softcap=cap)
+    out = torch.full_like(qd, float("nan"))
+    cascade_attention(output=out, query=qd, key_cache=kd, value_cache=vd, cu_query_lens=cud,
+                      max_query_len=max(query_lens),
+                      cu_prefix_query_lens=torch.tensor([0, sum(query_lens)], dtype=torch.int32, device=DEV),
+                      prefix_kv_lens=torch.tensor([common_prefix_len], dtype=torch.int32, device=DEV),
+                      suffix_kv_lens=kvl - common_prefix_len, max_kv_len=max(kv_lens), softmax_scale=scale,
+                      alibi_slopes=None, sliding_window=(-1, -1), logits_soft_cap=cap, block_table=btd,
+                      common_prefix_len=common_prefix_len)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(out.float(), ref_out.float(), atol=1e-2, rtol=1e-2)      # the reference test's check
+    if len(seq_lens) <= 8:                                                              # and the oracle on the whole sequences
+        want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale, soft_cap=soft_cap)
+        torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+
+
+def test_flash_attn_varlen_softmax_lse_and_cascade_backend():
+    """return_softmax_lse against the oracle's logits; B200FlashAttentionImpl.forward with use_cascade metadata
+    (flash_attn.py:520-545) on an fp8 cache."""
+    from oracle.fp8 import dequant_e4m3
+    from vllm_b200.attention.flash_backend import (B200FlashAttentionImpl, B200FlashAttentionMetadata,
+                                                   flash_attn_varlen_func)
+    seed_all(9)
+    H, Hkv, D, bs, nb, dtype = 8, 2, 128, 16, 256, torch.bfloat16
+    seq_lens = [(33, 100), (1, 57), (70, 70)]
+    q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens = _varlen_inputs(seq_lens, H, Hkv, D, bs, dtype, "NHD", nb=nb)
+    scale = float(D ** -0.5)
+    kvl = torch.tensor(kv_lens, dtype=torch.int32, device=DEV)
+    out, lse = flash_attn_varlen_func(q=q.to(DEV), k=kd, v=vd, cu_seqlens_q=cu.to(DEV), seqused_k=kvl,
+                                      max_seqlen_q=max(query_lens), max_seqlen_k=max(kv_lens), softmax_scale=scale,
+                                      causal=True, block_table=bt.to(DEV), return_softmax_lse=True)
+    assert lse.shape == (H, sum(query_lens)) and lse.dtype == torch.float32
+    want_lse = torch.empty(H, sum(query_lens))
+    o = 0
+    for i, (ql, kl) in enumerate(seq_lens):
+        idx = bt[i, :(kl + bs - 1) // bs].long()
+        k = torch.repeat_interleave(kc[idx].reshape(-1, Hkv, D)[:kl].float(), H // Hkv, dim=1)
+        logits = torch.einsum("qhd,khd->hqk", q[o:o + ql].float() * scale, k)
+        logits.masked_fill_(torch.triu(torch.ones(ql, kl), diagonal=kl - ql + 1).bool(), float("-inf"))
+        want_lse[:, o:o + ql] = torch.logsumexp(logits, dim=-1)
+        o += ql
+    torch.testing.assert_close(lse.cpu(), want_lse, atol=2e-3, rtol=2e-3)
+
+    # backend: two sequences sharing a 32-token prefix, fp8 cache, the cache already written (KV sharing flag)
+    ksc, vsc = 0.05, 0.03
+    kv8 = (torch.randn(2, nb, bs, Hkv, D) / 0.05).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+    lens = [(4, 90), (1, 45)]
+    bt2 = torch.randint(0, nb, (2, 6), dtype=torch.int32)
+    bt2[:, :2] = bt2[0, :2]
+    T = sum(x[0] for x in lens)
+    q2 = torch.randn(T, H, D).to(dtype)
+    sl = torch.tensor([x[1] for x in lens], dtype=torch.int32, device=DEV)
+    meta = B200FlashAttentionMetadata(
+        num_actual_tokens=T, max_query_len=4, query_start_loc=torch.tensor([0, 4, 5], dtype=torch.int32, device=DEV),
+        max_seq_len=90, seq_lens=sl, block_table=bt2.to(DEV), slot_mapping=torch.zeros(T, dtype=torch.int64, device=DEV),
+        use_cascade=True, common_prefix_len=32, cu_prefix_query_lens=torch.tensor([0, T], dtype=torch.int32, device=DEV),
+        prefix_kv_lens=torch.tensor([32], dtype=torch.int32, device=DEV), suffix_kv_lens=sl - 32)
+    impl = B200FlashAttentionImpl(H, D, scale, Hkv, kv_cache_dtype="fp8", kv_sharing_target_layer_name="written already")
+
+    class _Layer:
+        _k_scale = torch.tensor([ksc], device=DEV)
+        _v_scale = torch.tensor([vsc], device=DEV)
+    out2 = torch.empty(T, H, D, dtype=dtype, device=DEV)
+    impl.forward(_Layer(), q2.to(DEV), None, None, kv8.to(DEV), meta, output=out2)
+    torch.cuda.synchronize()
+    want2 = oattn.flash_attn_varlen_paged(q2, dequant_e4m3(kv8[0], ksc, dtype), dequant_e4m3(kv8[1], vsc, dtype),
+                                          [x[0] for x in lens], [x[1] for x in lens], bt2, scale)
+    torch.testing.assert_close(out2.cpu().float(), want2.float(), atol=2e-2, rtol=1e-2)

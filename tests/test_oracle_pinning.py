@@ -182,7 +182,8 @@ def test_cutlass_moe_data_oracle_known_answer():
         torch.testing.assert_close(got[o:o + m], want, rtol=1e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("name", ["flash_varlen_ref_case", "flash_varlen_prefill_gqa7"])
+@pytest.mark.parametrize("name", ["flash_varlen_ref_case", "flash_varlen_prefill_gqa7", "flash_varlen_window256",
+                                  "flash_varlen_softcap10_window", "flash_varlen_softcap50"])
 def test_flash_varlen_oracle_matches_reference_test_golden(name):
     """oracle.attention.flash_attn_varlen_paged == the reference test suite's own `ref_paged_attn`
     (tests/kernels/attention/test_flash_attn.py:25-77) run in the build container on seeded inputs
@@ -192,7 +193,9 @@ def test_flash_varlen_oracle_matches_reference_test_golden(name):
     g = np.load(os.path.join(GOLD, name + ".npz"))
     q, kc, vc = _bf16(g["q"]), _bf16(g["key_cache"]), _bf16(g["value_cache"])
     out = oattn.flash_attn_varlen_paged(q, kc, vc, g["query_lens"].tolist(), g["kv_lens"].tolist(),
-                                        torch.from_numpy(g["block_tables"]), float(g["scale"]))
+                                        torch.from_numpy(g["block_tables"]), float(g["scale"]),
+                                        sliding_window=int(g["sliding_window"]) if int(g["sliding_window"]) >= 0 else None,
+                                        soft_cap=float(g["soft_cap"]) or None)
     want = _bf16(g["out"])
     assert out.shape == want.shape
     torch.testing.assert_close(out.float(), want.float(), rtol=1e-2, atol=1.5e-2)

@@ -109,14 +109,19 @@ def paged_attention_v1(
 def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                             cu_seqlens_q: torch.Tensor, seqused_k: torch.Tensor, block_table: torch.Tensor,
                             scale: float, causal: bool = True, max_seqlen_q: int = 0, kv_cache_dtype: str = "auto",
-                            k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
+                            k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None,
+                            window_left: int = -1, softcap: float = 0.0,
+                            softmax_lse: Optional[torch.Tensor] = None) -> None:
     """Variable-length causal attention over the flash cache layout (include/vllm_b200.h
     vb200_flash_attn_varlen_paged): prefill / chunked prefill / mixed batches of the V1 backend's
     flash_attn_varlen_func call (vllm/v1/attention/backends/flash_attn.py:497-519).  query / out [total_q, num_heads,
     head_size]; key_cache / value_cache the `[num_blocks, block_size, num_kv_heads, head_size]` halves (NHD or HND
     strides) holding every sequence's tokens, the new ones included; cu_seqlens_q int32 [num_seqs + 1]; seqused_k
     int32 [num_seqs]; block_table int32 [num_seqs, max_blocks]; max_seqlen_q the longest query length when the caller
-    knows it (0 = unknown); kv_cache_dtype "auto" or "fp8" (e4m3 bytes + fp32 per-tensor k_scale / v_scale)."""
+    knows it (0 = unknown); kv_cache_dtype "auto" or "fp8" (e4m3 bytes + fp32 per-tensor k_scale / v_scale);
+    window_left >= 0: sliding window (flash-attn's window_size = (window_left, 0), i.e. sliding_window - 1); softcap > 0:
+    logits soft-capping (flash_attn.py:342-350); softmax_lse: optional fp32 [num_heads, total_q] output, the log-sum-exp
+    of every query row (return_softmax_lse=True of the reference call, used by cascade attention)."""
     require_cuda(out, query, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
         raise RuntimeError("query must be [total_q, num_heads, head_size] with contiguous heads")
@@ -132,9 +137,17 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
         raise RuntimeError(f"kv_cache_dtype 'auto' needs cache dtype == query dtype ({key_cache.dtype} vs {query.dtype})")
     if kvd == _lib.KV_FP8_E4M3 and (key_cache.element_size() != 1 or k_scale is None or v_scale is None):
         raise RuntimeError("fp8 kv cache must be a 1-byte tensor (uint8 / float8_e4m3fn) with k_scale and v_scale")
-    for name, t in (("cu_seqlens_q", cu_seqlens_q), ("seqused_k", seqused_k), ("block_table", block_table)):
+    for name, t in (("cu_seqlens_q", cu_seqlens_q), ("seqused_k", seqused_k)):
         if t.dtype != torch.int32 or not t.is_contiguous():
             raise RuntimeError(f"{name} must be a contiguous int32 tensor")
+    # block_table may be a row / column slice of the full table (cascade attention: block_table[:1] and
+    # block_table[:, num_common_kv_blocks:], flash_attn.py:722,749)
+    if block_table.dtype != torch.int32 or block_table.dim() != 2 or (block_table.shape[1] > 1 and block_table.stride(1) != 1):
+        raise RuntimeError("block_table must be an int32 [num_seqs, max_blocks] tensor with contiguous rows")
+    require_cuda(softmax_lse)
+    if softmax_lse is not None and (softmax_lse.dtype != torch.float32 or tuple(softmax_lse.shape) != (query.shape[1], query.shape[0])
+                                    or not softmax_lse.is_contiguous()):
+        raise RuntimeError("softmax_lse must be a contiguous fp32 [num_heads, total_q] tensor")
     num_seqs = seqused_k.shape[0]
     if cu_seqlens_q.numel() != num_seqs + 1 or block_table.dim() != 2 or block_table.shape[0] != num_seqs:
         raise RuntimeError("cu_seqlens_q must hold num_seqs + 1 offsets and block_table num_seqs rows")
@@ -144,12 +157,13 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
         raise RuntimeError(f"head size mismatch: query {hs}, cache {head_size}")
     strides = [key_cache.stride(i) if key_cache.size(i) > 1 else head_size for i in range(3)]
     with _device_of(query):
-        check(load().vb200_flash_attn_varlen_paged(
+        check(load().vb200_flash_attn_varlen_paged_opts(
             ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), ptr(cu_seqlens_q), ptr(seqused_k), ptr(block_table),
             num_seqs, total_q, num_heads, num_kv_heads, head_size, block_size, block_table.stride(0), int(max_seqlen_q),
             float(scale), 1 if causal else 0, dtype_enum(query.dtype), kvd, ptr(k_scale), ptr(v_scale),
             query.stride(0) if total_q > 1 else num_heads * head_size,
-            out.stride(0) if total_q > 1 else num_heads * head_size, strides[0], strides[1], strides[2], stream()))
+            out.stride(0) if total_q > 1 else num_heads * head_size, strides[0], strides[1], strides[2],
+            int(window_left), float(softcap or 0.0), ptr(softmax_lse), total_q, stream()))
 
 
 def paged_attention_v1_quant(

@@ -13,7 +13,11 @@ Mirrors the pieces of /root/reference/vllm/v1/attention/backends/flash_attn.py a
                                      vb200_paged_attention_flash kernel (TMA tensor-map loads of the cache as it lies,
                                      csrc/paged_attention_flash.cuh).
 Prefill / chunked prefill / mixed batches (max_seqlen_q > 1) run on the variable-length kernel of
-csrc/paged_prefill.cu (16-bit and fp8 caches).  Sliding windows, soft-capping and cascade attention raise.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3, :478-486); this kernel keeps the query in
+csrc/paged_prefill.cu (16-bit and fp8 caches); so does every batch with a sliding window (`window_size = (left, 0)`)
+or logits soft-capping, decode batches included (that kernel skips the tiles left of the window and applies the cap
+in front of the mask).  Cascade attention (`cascade_attention`, flash_attn.py:674-764: shared prefix non-causal + per-query
+suffix, both returning the log-sum-exp, merged by merge_attn_states) runs on the same kernel.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3,
+:478-486); this kernel keeps the query in
 bf16/f16 and folds the per-tensor k / v descales into the fp32 logits / output, which is the dequantised result the
 parity bar is stated against.
 """
@@ -46,7 +50,7 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
                            block_table: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
                            q_descale=None, k_descale: Optional[torch.Tensor] = None,
                            v_descale: Optional[torch.Tensor] = None, scheduler_metadata=None, fa_version: int = 3,
-                           num_splits: int = 0, cu_seqlens_k=None) -> torch.Tensor:
+                           num_splits: int = 0, cu_seqlens_k=None, return_softmax_lse: bool = False):
     """vllm.vllm_flash_attn.flash_attn_varlen_func as flash_attn.py:497-519 calls it.  Decode (max_seqlen_q == 1): q
     [num_seqs, num_heads, head_size] (one token per sequence, cu_seqlens_q = 0..num_seqs) on the HBM-roofline decode
     kernel; anything else (prefill, chunked prefill, mixed batches: q [total_q, ...] split by cu_seqlens_q, bottom-right
@@ -54,13 +58,18 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
     paged cache `[num_blocks, block_size, num_kv_heads, head_size]` (any stride order with a contiguous head
     dimension), block_table int32 [num_seqs, max_blocks], seqused_k int32 [num_seqs].  k_descale / v_descale: fp32
     per-tensor scales of an fp8 cache (the reference passes them expanded to [num_seqs, num_kv_heads]; element 0 is
-    used)."""
+    used).  return_softmax_lse: also return the fp32 [num_heads, total_q] log-sum-exp (variable-length kernel)."""
     if block_table is None:
         raise NotImplementedError("flash_attn_varlen_func: only the paged-KV (block_table) form is built")
-    if softcap:
-        raise NotImplementedError("flash_attn_varlen_func: logits soft-capping is not built")
+    softcap = float(softcap or 0.0)
+    window_left = -1
     if window_size is not None and tuple(window_size) not in ((-1, -1), (-1, 0)):
-        raise NotImplementedError("flash_attn_varlen_func: sliding windows are not built")
+        # (left, 0) is what the reference backend passes: (sliding_window - 1, 0), flash_attn.py:366-369; a causal call
+        # ignores the right side (keys right of the diagonal are masked anyway)
+        left, right = (int(x) for x in window_size)
+        if not causal or left < 0:
+            raise NotImplementedError("flash_attn_varlen_func: only causal (left, 0) sliding windows are built")
+        window_left = left
     if cu_seqlens_q is not None and cu_seqlens_q.numel() != seqused_k.shape[0] + 1:
         raise RuntimeError("cu_seqlens_q must hold num_seqs + 1 offsets")
     fp8 = k.element_size() == 1
@@ -70,17 +79,21 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         softmax_scale = q.shape[-1] ** -0.5
     if out is None:
         out = torch.empty_like(q)
-    if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0]:
-        # prefill / chunked prefill / mixed batch: the variable-length kernel (csrc/paged_prefill.cu)
+    if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0] or window_left >= 0 or softcap > 0 or return_softmax_lse:
+        # prefill / chunked prefill / mixed batch, or any batch with a window / soft-cap: the variable-length kernel
+        # (csrc/paged_prefill.cu)
         if alibi_slopes is not None:
-            raise NotImplementedError("flash_attn_varlen_func: ALiBi is built for the decode case only")
+            raise NotImplementedError("flash_attn_varlen_func: ALiBi is built for the plain decode case only")
         if cu_seqlens_q is None:
-            raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
+            if max_seqlen_q != 1:
+                raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
+            cu_seqlens_q = torch.arange(q.shape[0] + 1, dtype=torch.int32, device=q.device)
         ks = k_descale.reshape(-1)[:1].float().contiguous() if fp8 else None
         vs = v_descale.reshape(-1)[:1].float().contiguous() if fp8 else None
+        lse = torch.empty((q.shape[1], q.shape[0]), dtype=torch.float32, device=q.device) if return_softmax_lse else None
         ops.flash_attn_varlen_paged(out, q, k, v, cu_seqlens_q, seqused_k, block_table, softmax_scale, causal,
-                                    int(max_seqlen_q), "fp8" if fp8 else "auto", ks, vs)
-        return out
+                                    int(max_seqlen_q), "fp8" if fp8 else "auto", ks, vs, window_left, softcap, lse)
+        return (out, lse) if return_softmax_lse else out
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None
     ops.paged_attention_flash(out, q, k, v, softmax_scale, block_table, seqused_k, int(max_seqlen_k), alibi_slopes,
@@ -100,7 +113,45 @@ class B200FlashAttentionMetadata:
     slot_mapping: torch.Tensor        # int64 [num_tokens]
     use_cascade: bool = False
     common_prefix_len: int = 0
+    cu_prefix_query_lens: Optional[torch.Tensor] = None   # int32 [2] = [0, num_actual_tokens]   (:121-123)
+    prefix_kv_lens: Optional[torch.Tensor] = None         # int32 [1] = [common_prefix_len]
+    suffix_kv_lens: Optional[torch.Tensor] = None         # int32 [num_seqs] = seq_lens - common_prefix_len
     causal: bool = True
+
+
+def cascade_attention(output: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                      cu_query_lens: torch.Tensor, max_query_len: int, cu_prefix_query_lens: torch.Tensor,
+                      prefix_kv_lens: torch.Tensor, suffix_kv_lens: torch.Tensor, max_kv_len: int, softmax_scale: float,
+                      alibi_slopes: Optional[torch.Tensor], sliding_window: tuple, logits_soft_cap: float,
+                      block_table: torch.Tensor, common_prefix_len: int, fa_version: int = 3,
+                      prefix_scheduler_metadata=None, suffix_scheduler_metadata=None, q_descale=None,
+                      k_descale: Optional[torch.Tensor] = None, v_descale: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """cascade_attention (flash_attn.py:674-764): every query attends the batch's SHARED prefix (the first
+    common_prefix_len tokens, i.e. the first blocks of sequence 0's table) as one non-causal problem over all tokens, then
+    its own suffix causally through the remaining block-table columns; the two partial results are merged through their
+    log-sum-exps.  Same restrictions as the reference (:698-707): no ALiBi, no sliding window, the prefix a whole number
+    of blocks."""
+    if alibi_slopes is not None:
+        raise AssertionError("Cascade attention does not support ALiBi.")
+    if tuple(sliding_window) != (-1, -1):
+        raise AssertionError("Cascade attention does not support sliding window.")
+    num_tokens = query.shape[0]
+    block_size = key_cache.shape[-3]
+    if common_prefix_len % block_size != 0 or common_prefix_len < block_size:
+        raise AssertionError("common_prefix_len must be a positive multiple of the block size")
+    num_common_kv_blocks = common_prefix_len // block_size
+    prefix_output, prefix_lse = flash_attn_varlen_func(
+        q=query, k=key_cache, v=value_cache, cu_seqlens_q=cu_prefix_query_lens, seqused_k=prefix_kv_lens,
+        max_seqlen_q=num_tokens, max_seqlen_k=common_prefix_len, softmax_scale=softmax_scale, causal=False,
+        window_size=sliding_window, block_table=block_table[:1], softcap=logits_soft_cap, return_softmax_lse=True,
+        k_descale=k_descale, v_descale=v_descale)
+    suffix_output, suffix_lse = flash_attn_varlen_func(
+        q=query, k=key_cache, v=value_cache, cu_seqlens_q=cu_query_lens, seqused_k=suffix_kv_lens,
+        max_seqlen_q=max_query_len, max_seqlen_k=max_kv_len - common_prefix_len, softmax_scale=softmax_scale, causal=True,
+        window_size=sliding_window, block_table=block_table[:, num_common_kv_blocks:], softcap=logits_soft_cap,
+        return_softmax_lse=True, k_descale=k_descale, v_descale=v_descale)
+    ops.merge_attn_states(output, prefix_output, prefix_lse, suffix_output, suffix_lse)
+    return output
 
 
 class B200FlashAttentionImpl:
@@ -110,8 +161,9 @@ class B200FlashAttentionImpl:
                  alibi_slopes: Optional[list] = None, sliding_window: Optional[int] = None,
                  kv_cache_dtype: str = "auto", logits_soft_cap: Optional[float] = None,
                  attn_type: str = "decoder", kv_sharing_target_layer_name: Optional[str] = None) -> None:
-        if sliding_window is not None or logits_soft_cap:
-            raise NotImplementedError("B200FlashAttentionImpl: sliding window / soft cap are not built")
+        # flash_attn.py:366-374: flash-attn's window is (sliding_window - 1, 0); a soft cap of 0 means none
+        self.sliding_window = (-1, -1) if sliding_window is None else (sliding_window - 1, 0)
+        self.logits_soft_cap = float(logits_soft_cap or 0.0)
         if attn_type != "decoder":
             raise NotImplementedError("B200FlashAttentionImpl: decoder self-attention only")
         B200FlashAttentionBackend.validate_head_size(head_size)
@@ -132,8 +184,6 @@ class B200FlashAttentionImpl:
             raise NotImplementedError("fused output quantization is not yet supported for B200FlashAttentionImpl")
         if attn_metadata is None:   # profiling run
             return output
-        if attn_metadata.use_cascade:
-            raise NotImplementedError("cascade attention is outside the decode hot path")
         n = attn_metadata.num_actual_tokens
         key_cache, value_cache = kv_cache.unbind(0)
         if self.kv_sharing_target_layer_name is None:
@@ -141,10 +191,25 @@ class B200FlashAttentionImpl:
                                         self.kv_cache_dtype, layer._k_scale, layer._v_scale)
         if self.alibi_slopes is not None and self.alibi_slopes.device != query.device:
             self.alibi_slopes = self.alibi_slopes.to(query.device)
+        fp8 = self.kv_cache_dtype.startswith("fp8")
+        if attn_metadata.use_cascade:   # flash_attn.py:520-545
+            if not output[:n].is_contiguous():
+                raise RuntimeError("cascade attention needs a contiguous output")
+            cascade_attention(output[:n], query[:n], key_cache, value_cache, cu_query_lens=attn_metadata.query_start_loc,
+                              max_query_len=attn_metadata.max_query_len,
+                              cu_prefix_query_lens=attn_metadata.cu_prefix_query_lens,
+                              prefix_kv_lens=attn_metadata.prefix_kv_lens, suffix_kv_lens=attn_metadata.suffix_kv_lens,
+                              max_kv_len=attn_metadata.max_seq_len, softmax_scale=self.scale,
+                              alibi_slopes=self.alibi_slopes, sliding_window=self.sliding_window,
+                              logits_soft_cap=self.logits_soft_cap, block_table=attn_metadata.block_table,
+                              common_prefix_len=attn_metadata.common_prefix_len,
+                              k_descale=layer._k_scale if fp8 else None, v_descale=layer._v_scale if fp8 else None)
+            return output
         flash_attn_varlen_func(q=query[:n], k=key_cache, v=value_cache, out=output[:n],
                                cu_seqlens_q=attn_metadata.query_start_loc, max_seqlen_q=attn_metadata.max_query_len,
                                seqused_k=attn_metadata.seq_lens, max_seqlen_k=attn_metadata.max_seq_len,
                                softmax_scale=self.scale, causal=attn_metadata.causal, alibi_slopes=self.alibi_slopes,
+                               window_size=self.sliding_window, softcap=self.logits_soft_cap,
                                block_table=attn_metadata.block_table,
                                k_descale=layer._k_scale if self.kv_cache_dtype.startswith("fp8") else None,
                                v_descale=layer._v_scale if self.kv_cache_dtype.startswith("fp8") else None)

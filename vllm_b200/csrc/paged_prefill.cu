@@ -42,6 +42,11 @@ struct Params {
   int causal;
   const float* k_scale;                             // fp8 cache: per-tensor dequantisation scales (device)
   const float* v_scale;
+  // EXTRA kernels only (sliding window / logits soft-cap / log-sum-exp output, flash_attn.py:342-350,507-510,711-760):
+  int window_left;                                  // keys p - window_left .. p of a query at position p; < 0: no window
+  float cap_pre;                                    // soft-cap: softmax scale / cap (then scale_log2 = cap * log2(e)); 0: none
+  float* lse;                                       // optional fp32 [num_heads, lse_stride]: log-sum-exp of every row's logits
+  int64_t lse_stride;
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
@@ -95,6 +100,11 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// tanh(x) = 1 - 2 / (e^(2x) + 1): two MUFU operations, absolute error ~1e-7 (tanh.approx's 2^-11 relative error times a
+// cap of 50 would move a logit by 0.02)
+__device__ __forceinline__ float tanh_2mufu(float x) {
+  return 1.f - __fdividef(2.f, ex2(x * 2.8853900817779268f) + 1.f);
+}
 
 // two e4m3 bytes (low byte first) -> two T values packed in 32 bits; exact (e4m3 fits f16 and bf16)
 template <typename T>
@@ -117,7 +127,10 @@ __device__ __forceinline__ uint32_t swz(int r, int c) {
 // FP8: the cache holds e4m3 bytes.  Tiles arrive as bytes in a two-stage staging ring and are expanded (exactly) to T
 // into ONE 16-bit tile pair in front of the MMAs; the per-tensor scales are folded into the logits (k) and the output
 // (v), as the decode kernel does.
-template <typename T, int D, int MT, bool FP8>
+// EXTRA: sliding window (tiles left of every row's window are never loaded; the left edge is masked like the diagonal)
+// and logits soft-capping (cap * tanh(logit / cap) in front of the mask), and the optional log-sum-exp output; a
+// separate instantiation so that the plain causal kernel keeps its registers and instruction stream.
+template <typename T, int D, int MT, bool FP8, bool EXTRA>
 __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Params p) {
   pdl_wait();
   pdl_trigger();
@@ -164,13 +177,21 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   int n_keys = p.causal ? min(kv_len, shift + last_tok + 1) : kv_len;
   if (n_keys < 0) n_keys = 0;
   const int n_tiles = (n_keys + BN - 1) / BN;
+  const int wl = EXTRA && p.causal ? p.window_left : -1;
+  int j0 = 0;                                      // first tile any row of this CTA can see
+  if (EXTRA && wl >= 0) {
+    const int lo = shift + m0 / G - wl;
+    if (lo > 0) j0 = min(lo / BN, n_tiles);
+  }
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, tq = lane & 3;
   const T* qg = reinterpret_cast<const T*>(p.q) + (int64_t)q0 * p.q_stride + (int64_t)kvh * G * D;
   const T* kc = reinterpret_cast<const T*>(p.k_cache) + (FP8 ? 0 : (int64_t)kvh * p.head_stride);   // 16-bit caches
   const T* vc = reinterpret_cast<const T*>(p.v_cache) + (FP8 ? 0 : (int64_t)kvh * p.head_stride);
-  const float scale_log2 = FP8 ? p.scale_log2 * *p.k_scale : p.scale_log2;
+  const bool capped = EXTRA && p.cap_pre != 0.f;
+  const float scale_log2 = FP8 && !capped ? p.scale_log2 * *p.k_scale : p.scale_log2;
+  const float cap_pre = !capped ? 0.f : FP8 ? p.cap_pre * *p.k_scale : p.cap_pre;
   const float out_scale = FP8 ? *p.v_scale : 1.f;
   const int* bt = p.block_table + (int64_t)seq * p.max_blocks_per_seq;
   const int bmask = (1 << p.block_shift) - 1;
@@ -231,7 +252,7 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       }
     }
   };
-  if (n_tiles > 0) load_kv(0, 0);
+  if (n_tiles > j0) load_kv(j0, 0);
   cp_commit();
 
   float o[MT][D / 8][4];
@@ -253,14 +274,15 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
 #pragma unroll
     for (int h = 0; h < 2; ++h) tok_of[mt][h] = (m0 + wrow + mt * 16 + g + h * 8) / G;
   const int warp_first_tok = (m0 + wrow) / G;
+  const int warp_last_tok = (m0 + wrow + 16 * MT - 1) / G;
 
-  for (int j = 0; j < n_tiles; ++j) {
-    const int stage = j & 1;
+  for (int j = j0; j < n_tiles; ++j) {
+    const int stage = (j - j0) & 1;
     if (j + 1 < n_tiles) load_kv(j + 1, stage ^ 1);
     cp_commit();
     cp_wait<1>();
     __syncthreads();
-    if (QREG && j == 0) {
+    if (QREG && j == j0) {
 #pragma unroll
       for (int ks = 0; ks < (QREG ? D / 16 : 1); ++ks)
         ldsm_x4(sQ + swz<D>(wrow + (lane & 15), ks * 2 + (lane >> 4)), qf[ks]);
@@ -299,9 +321,18 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
         }
       }
     }
-    // ---- mask (only tiles that touch the diagonal or the end of the sequence)
+    if (EXTRA && capped) {
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int i = 0; i < BN / 8; ++i)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s[mt][i][e] = tanh_2mufu(s[mt][i][e] * cap_pre);
+    }
+    // ---- mask (only tiles that touch the diagonal, the left edge of the window or the end of the sequence)
     const int n_base = j * BN;
-    const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + warp_first_tok);
+    const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + warp_first_tok) ||
+                           (EXTRA && wl >= 0 && n_base < shift + warp_last_tok - wl);
     if (need_mask) {
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
@@ -310,7 +341,8 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int n = n_base + i * 8 + 2 * tq + (e & 1);
-            const bool vis = n < kv_len && (!p.causal || n <= shift + tok_of[mt][e >> 1]);
+            const bool vis = n < kv_len && (!p.causal || n <= shift + tok_of[mt][e >> 1]) &&
+                             (!(EXTRA && wl >= 0) || n >= shift + tok_of[mt][e >> 1] - wl);
             if (!vis) s[mt][i][e] = -INFINITY;
           }
     }
@@ -392,6 +424,9 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
       if (row < n_rows) {
         const float inv = l > 0.f ? out_scale / l : 0.f;
         T* orow = og + (int64_t)tok_of[mt][h] * p.o_stride + (row - tok_of[mt][h] * G) * D;
+        if (EXTRA && p.lse != nullptr && tq == 0)   // natural log; a row without a visible key: -inf (merge_attn_states' empty state)
+          p.lse[(int64_t)(kvh * G + row - tok_of[mt][h] * G) * p.lse_stride + q0 + tok_of[mt][h]] =
+              l > 0.f ? (row_max[mt][h] * scale_log2 + log2f(l)) * 0.6931471805599453f : -INFINITY;
 #pragma unroll
         for (int i = 0; i < D / 8; ++i)
           *reinterpret_cast<uint32_t*>(orow + i * 8 + 2 * tq) =
@@ -401,9 +436,9 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
   }
 }
 
-template <typename T, int D, int MT, bool FP8>
+template <typename T, int D, int MT, bool FP8, bool EXTRA>
 static int launch(const Params& p, int total_q, cudaStream_t stream) {
-  auto kern = paged_prefill_flash_kernel<T, D, MT, FP8>;
+  auto kern = paged_prefill_flash_kernel<T, D, MT, FP8, EXTRA>;
   constexpr int BM = 16 * MT * NWARPS;
   const size_t smem = (size_t)BM * D * 2 + (FP8 ? (size_t)4 * BN * D + (size_t)2 * BN * D * 2 : (size_t)4 * BN * D * 2);
   if (smem > 48 * 1024)
@@ -417,17 +452,20 @@ static int launch(const Params& p, int total_q, cudaStream_t stream) {
 
 // 128-row tiles (two 16-row tiles per warp: every K / V fragment read from shared memory feeds two MMAs' worth of
 // rows) once some sequence has more than 64 rows; 64-row tiles for short chunks and for head size 256, whose
-// accumulators leave no room for the second tile.
-template <typename T, bool FP8>
+// accumulators leave no room for the second tile (192 likewise).
+template <typename T, bool FP8, bool EXTRA>
 static int dispatch(const Params& p, int head_size, int total_q, int max_seqlen_q, cudaStream_t stream) {
   const bool big = (int64_t)max_seqlen_q * p.group > 64;
   switch (head_size) {
-    case 64: return big ? launch<T, 64, 2, FP8>(p, total_q, stream) : launch<T, 64, 1, FP8>(p, total_q, stream);
-    case 128: return big ? launch<T, 128, 2, FP8>(p, total_q, stream) : launch<T, 128, 1, FP8>(p, total_q, stream);
-    case 256: return launch<T, 256, 1, FP8>(p, total_q, stream);
+    case 64:
+      return big ? launch<T, 64, 2, FP8, EXTRA>(p, total_q, stream) : launch<T, 64, 1, FP8, EXTRA>(p, total_q, stream);
+    case 128:
+      return big ? launch<T, 128, 2, FP8, EXTRA>(p, total_q, stream) : launch<T, 128, 1, FP8, EXTRA>(p, total_q, stream);
+    case 192: return launch<T, 192, 1, FP8, EXTRA>(p, total_q, stream);
+    case 256: return launch<T, 256, 1, FP8, EXTRA>(p, total_q, stream);
     default: break;
   }
-  VB_CHECK(false, "flash_attn_varlen_paged: head size %d is not supported (64, 128, 256)", head_size);
+  VB_CHECK(false, "flash_attn_varlen_paged: head size %d is not supported (64, 128, 192, 256)", head_size);
   return 0;
 }
 
@@ -436,14 +474,18 @@ static int dispatch(const Params& p, int head_size, int total_q, int max_seqlen_
 
 using namespace vb200;
 
-extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_cache, const void* value_cache,
-                                             const int32_t* cu_seqlens_q, const int32_t* seqused_k,
-                                             const int32_t* block_table, int num_seqs, int total_q, int num_heads,
-                                             int num_kv_heads, int head_size, int block_size,
-                                             int max_num_blocks_per_seq, int max_seqlen_q, float scale, int causal,
-                                             int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
-                                             int64_t q_stride, int64_t out_stride, int64_t block_stride,
-                                             int64_t token_stride, int64_t head_stride, vb200_stream_t stream) {
+extern "C" int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, const void* key_cache,
+                                                  const void* value_cache, const int32_t* cu_seqlens_q,
+                                                  const int32_t* seqused_k, const int32_t* block_table, int num_seqs,
+                                                  int total_q, int num_heads, int num_kv_heads, int head_size,
+                                                  int block_size, int max_num_blocks_per_seq, int max_seqlen_q,
+                                                  float scale, int causal, int dtype, int kv_dtype, const float* k_scale,
+                                                  const float* v_scale, int64_t q_stride, int64_t out_stride,
+                                                  int64_t block_stride, int64_t token_stride, int64_t head_stride,
+                                                  int window_left, float softcap, float* softmax_lse,
+                                                  int64_t lse_stride, vb200_stream_t stream) {
+  VB_CHECK(window_left < 0 || causal, "flash_attn_varlen_paged: a sliding window (left, 0) needs causal attention");
+  VB_CHECK(softcap >= 0.f && softcap == softcap, "flash_attn_varlen_paged: softcap must be >= 0");
   VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "flash_attn_varlen_paged: dtype must be f16 or bf16");
   VB_CHECK(num_kv_heads > 0 && num_heads % num_kv_heads == 0, "flash_attn_varlen_paged: num_heads %% num_kv_heads != 0");
   VB_CHECK(block_size > 0 && (block_size & (block_size - 1)) == 0,
@@ -481,11 +523,42 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
   p.causal = causal;
   p.k_scale = k_scale;
   p.v_scale = v_scale;
+  VB_CHECK(softmax_lse == nullptr || lse_stride >= total_q, "flash_attn_varlen_paged: lse_stride < total_q");
+  p.lse = softmax_lse;
+  p.lse_stride = lse_stride;
+  p.window_left = window_left < 0 ? -1 : window_left;
+  p.cap_pre = 0.f;
+  if (softcap > 0.f) {   // logits = softcap * tanh(q.k * scale / softcap): the tanh takes q.k * cap_pre, the exponent scale is the cap
+    p.cap_pre = scale / softcap;
+    p.scale_log2 = softcap * 1.4426950408889634f;
+  }
   if (max_seqlen_q <= 0) max_seqlen_q = total_q;   // unknown: assume long chunks
   cudaStream_t st = (cudaStream_t)stream;
+  if (p.window_left >= 0 || p.cap_pre != 0.f || p.lse != nullptr) {
+    if (dtype == VB200_F16)
+      return fp8 ? prefill::dispatch<__half, true, true>(p, head_size, total_q, max_seqlen_q, st)
+                 : prefill::dispatch<__half, false, true>(p, head_size, total_q, max_seqlen_q, st);
+    return fp8 ? prefill::dispatch<__nv_bfloat16, true, true>(p, head_size, total_q, max_seqlen_q, st)
+               : prefill::dispatch<__nv_bfloat16, false, true>(p, head_size, total_q, max_seqlen_q, st);
+  }
   if (dtype == VB200_F16)
-    return fp8 ? prefill::dispatch<__half, true>(p, head_size, total_q, max_seqlen_q, st)
-               : prefill::dispatch<__half, false>(p, head_size, total_q, max_seqlen_q, st);
-  return fp8 ? prefill::dispatch<__nv_bfloat16, true>(p, head_size, total_q, max_seqlen_q, st)
-             : prefill::dispatch<__nv_bfloat16, false>(p, head_size, total_q, max_seqlen_q, st);
+    return fp8 ? prefill::dispatch<__half, true, false>(p, head_size, total_q, max_seqlen_q, st)
+               : prefill::dispatch<__half, false, false>(p, head_size, total_q, max_seqlen_q, st);
+  return fp8 ? prefill::dispatch<__nv_bfloat16, true, false>(p, head_size, total_q, max_seqlen_q, st)
+             : prefill::dispatch<__nv_bfloat16, false, false>(p, head_size, total_q, max_seqlen_q, st);
+}
+
+extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_cache, const void* value_cache,
+                                             const int32_t* cu_seqlens_q, const int32_t* seqused_k,
+                                             const int32_t* block_table, int num_seqs, int total_q, int num_heads,
+                                             int num_kv_heads, int head_size, int block_size,
+                                             int max_num_blocks_per_seq, int max_seqlen_q, float scale, int causal,
+                                             int dtype, int kv_dtype, const float* k_scale, const float* v_scale,
+                                             int64_t q_stride, int64_t out_stride, int64_t block_stride,
+                                             int64_t token_stride, int64_t head_stride, vb200_stream_t stream) {
+  return vb200_flash_attn_varlen_paged_opts(out, query, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table,
+                                            num_seqs, total_q, num_heads, num_kv_heads, head_size, block_size,
+                                            max_num_blocks_per_seq, max_seqlen_q, scale, causal, dtype, kv_dtype, k_scale,
+                                            v_scale, q_stride, out_stride, block_stride, token_stride, head_stride, -1,
+                                            0.f, nullptr, 0, stream);
 }
