@@ -231,6 +231,9 @@ int vb200_flash_attn_varlen_paged(void* out, const void* query, const void* key_
  *                query row's (scaled, capped, masked) logits -- flash_attn_varlen_func(return_softmax_lse=True), what
  *                cascade_attention (flash_attn.py:674-764) feeds to merge_attn_states; -inf for a row without a
  *                visible key; NULL = not wanted.
+ *   alibi_slopes: optional fp32 [num_heads]: -slope * |key position - query position| is added to the scaled
+ *                (and capped) logit -- flash-attn's -slope * |i + seqlen_k - seqlen_q - j|, which for one query token
+ *                is paged_attention_v1's slope * (token - seq_len + 1) (attention_kernels.cuh:283-285); NULL = none.
  * K / V tiles that lie left of every row's window are never loaded.  Decode batches (q_len 1) are accepted. */
 int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, const void* key_cache, const void* value_cache,
                                        const int32_t* cu_seqlens_q, const int32_t* seqused_k,
@@ -239,7 +242,8 @@ int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, const void*
                                        int max_seqlen_q, float scale, int causal, int dtype, int kv_dtype,
                                        const float* k_scale, const float* v_scale, int64_t q_stride, int64_t out_stride,
                                        int64_t block_stride, int64_t token_stride, int64_t head_stride, int window_left,
-                                       float softcap, float* softmax_lse, int64_t lse_stride, vb200_stream_t stream);
+                                       float softcap, float* softmax_lse, int64_t lse_stride,
+                                       const float* alibi_slopes, vb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------ */
 /* FP8 activation quantisation + activation                                                    */

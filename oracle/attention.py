@@ -107,7 +107,7 @@ def paged_attention_v2(query, key_cache, value_cache, num_kv_heads, scale, block
 
 
 def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, block_tables, scale, causal=True,
-                            sliding_window=None, soft_cap=None):
+                            sliding_window=None, soft_cap=None, alibi_slopes=None):
     """Variable-length attention over the FLASH cache layout (prefill / chunked prefill / mixed batches): the golden of
     the reference's own test, /root/reference/tests/kernels/attention/test_flash_attn.py:25-77 (`ref_paged_attn`),
     restated: per sequence gather its kv_len tokens through the block table from key_cache / value_cache
@@ -115,7 +115,9 @@ def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, 
     scaled query (:46,59), bottom-right aligned causal mask `triu(diagonal = kv_len - query_len + 1)` (:60-61,70),
     softmax rounded to the value dtype (:71), times V (:72).  query [sum(query_lens), H, D] -> same shape.
     sliding_window (:62-67): a query at absolute position p sees keys p - sliding_window + 1 .. p only; soft_cap
-    (:68-69): logits become soft_cap * tanh(logits / soft_cap) before the mask."""
+    (:68-69): logits become soft_cap * tanh(logits / soft_cap) before the mask.  alibi_slopes [H] (not in the reference
+    test; flash-attn's documented bias -slope * |i + kv_len - query_len - j|, which for query_len 1 is the paged
+    kernels' slope * (j - kv_len + 1), attention_kernels.cuh:283-285) is added after the cap."""
     nb, bs, Hkv, D = key_cache.shape
     outs, start = [], 0
     for i, (ql, kl) in enumerate(zip(query_lens, kv_lens)):
@@ -130,6 +132,9 @@ def flash_attn_varlen_paged(query, key_cache, value_cache, query_lens, kv_lens, 
         attn = torch.einsum("qhd,khd->hqk", q, k.float())
         if soft_cap:
             attn = soft_cap * torch.tanh(attn / soft_cap)
+        if alibi_slopes is not None:
+            dist = (torch.arange(kl)[None, :] - (torch.arange(ql)[:, None] + kl - ql)).abs().float()
+            attn = attn - alibi_slopes.float()[:, None, None] * dist[None]
         if causal:
             mask = torch.triu(torch.ones(ql, kl), diagonal=kl - ql + 1).bool()
             if sliding_window is not None:

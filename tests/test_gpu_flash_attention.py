@@ -190,13 +190,10 @@ def test_flash_attn_varlen_func_rejects_what_is_not_built():
     bt = torch.zeros(2, 2, dtype=torch.int32, device=DEV)
     sl = torch.ones(2, dtype=torch.int32, device=DEV)
     cu = torch.arange(3, dtype=torch.int32, device=DEV)
-    with pytest.raises(NotImplementedError):                                       # ALiBi outside the decode case
-        flash_attn_varlen_func(q, kc, kc, 2, cu, 16, sl, block_table=bt, alibi_slopes=torch.ones(8, device=DEV))
     with pytest.raises(NotImplementedError):                                       # a window needs the causal mask
         flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, window_size=(128, 0), causal=False)
-    with pytest.raises(NotImplementedError):                                       # ALiBi with a soft cap
-        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl, block_table=bt, softcap=30.0,
-                               alibi_slopes=torch.ones(8, device=DEV))
+    with pytest.raises(NotImplementedError):                                       # no paged cache
+        flash_attn_varlen_func(q, kc, kc, 1, cu, 16, sl)
     with pytest.raises(RuntimeError):
         from vllm_b200 import _custom_ops as ops
         ops.paged_attention_flash(torch.empty_like(q), q, torch.zeros(4, 32, 2, 128, dtype=torch.bfloat16, device=DEV),
@@ -528,3 +525,37 @@ def test_flash_attn_varlen_softmax_lse_and_cascade_backend():
     want2 = oattn.flash_attn_varlen_paged(q2, dequant_e4m3(kv8[0], ksc, dtype), dequant_e4m3(kv8[1], vsc, dtype),
                                           [x[0] for x in lens], [x[1] for x in lens], bt2, scale)
     torch.testing.assert_close(out2.cpu().float(), want2.float(), atol=2e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("soft_cap", [None, 30.0])
+@pytest.mark.parametrize("heads", [(8, 2), (6, 6)])
+@pytest.mark.parametrize("head_size", [64, 128])
+def test_flash_attn_varlen_alibi(head_size, heads, soft_cap):
+    """ALiBi on the variable-length kernel: against the oracle (flash-attn's documented bias) on a mixed batch, and, for
+    one query token per sequence, against the decode kernel, whose ALiBi is pinned by the reference CPU kernel's golden
+    (tests/golden/pa_mha_normal_alibi.npz)."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.attention.flash_backend import flash_attn_varlen_func
+    H, Hkv = heads
+    seed_all(head_size + H)
+    dtype, bs = torch.bfloat16, 16
+    seq_lens = [(40, 300), (1, 77), (130, 130)]
+    q, kc, vc, kd, vd, bt, cu, query_lens, kv_lens = _varlen_inputs(seq_lens, H, Hkv, head_size, bs, dtype, "NHD", nb=256)
+    slopes = torch.rand(H) * 0.3
+    scale = float(head_size ** -0.5)
+    kvl = torch.tensor(kv_lens, dtype=torch.int32, device=DEV)
+    out = flash_attn_varlen_func(q=q.to(DEV), k=kd, v=vd, cu_seqlens_q=cu.to(DEV), seqused_k=kvl,
+                                 max_seqlen_q=max(query_lens), max_seqlen_k=max(kv_lens), softmax_scale=scale,
+                                 causal=True, block_table=bt.to(DEV), alibi_slopes=slopes.to(DEV),
+                                 softcap=soft_cap or 0.0)
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, query_lens, kv_lens, bt, scale, soft_cap=soft_cap, alibi_slopes=slopes)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=1.5e-2, rtol=1e-2)
+    if soft_cap is None:
+        S = 3
+        qd = torch.randn(S, H, head_size).to(dtype).to(DEV)
+        cu1 = torch.arange(S + 1, dtype=torch.int32, device=DEV)
+        out_v = torch.empty_like(qd)
+        ops.flash_attn_varlen_paged(out_v, qd, kd, vd, cu1, kvl, bt.to(DEV), scale, True, 1, alibi_slopes=slopes.to(DEV))
+        out_d = torch.empty_like(qd)
+        ops.paged_attention_flash(out_d, qd, kd, vd, scale, bt.to(DEV), kvl, max(kv_lens), slopes.to(DEV), "auto", None, None)
+        torch.testing.assert_close(out_v.float(), out_d.float(), atol=1.5e-2, rtol=1e-2)

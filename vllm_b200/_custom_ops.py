@@ -111,7 +111,8 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
                             scale: float, causal: bool = True, max_seqlen_q: int = 0, kv_cache_dtype: str = "auto",
                             k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None,
                             window_left: int = -1, softcap: float = 0.0,
-                            softmax_lse: Optional[torch.Tensor] = None) -> None:
+                            softmax_lse: Optional[torch.Tensor] = None,
+                            alibi_slopes: Optional[torch.Tensor] = None) -> None:
     """Variable-length causal attention over the flash cache layout (include/vllm_b200.h
     vb200_flash_attn_varlen_paged): prefill / chunked prefill / mixed batches of the V1 backend's
     flash_attn_varlen_func call (vllm/v1/attention/backends/flash_attn.py:497-519).  query / out [total_q, num_heads,
@@ -121,7 +122,8 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
     knows it (0 = unknown); kv_cache_dtype "auto" or "fp8" (e4m3 bytes + fp32 per-tensor k_scale / v_scale);
     window_left >= 0: sliding window (flash-attn's window_size = (window_left, 0), i.e. sliding_window - 1); softcap > 0:
     logits soft-capping (flash_attn.py:342-350); softmax_lse: optional fp32 [num_heads, total_q] output, the log-sum-exp
-    of every query row (return_softmax_lse=True of the reference call, used by cascade attention)."""
+    of every query row (return_softmax_lse=True of the reference call, used by cascade attention); alibi_slopes: optional
+    fp32 [num_heads], bias -slope * |key position - query position|."""
     require_cuda(out, query, key_cache, value_cache, cu_seqlens_q, seqused_k, block_table)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
         raise RuntimeError("query must be [total_q, num_heads, head_size] with contiguous heads")
@@ -144,7 +146,10 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
     # block_table[:, num_common_kv_blocks:], flash_attn.py:722,749)
     if block_table.dtype != torch.int32 or block_table.dim() != 2 or (block_table.shape[1] > 1 and block_table.stride(1) != 1):
         raise RuntimeError("block_table must be an int32 [num_seqs, max_blocks] tensor with contiguous rows")
-    require_cuda(softmax_lse)
+    require_cuda(softmax_lse, alibi_slopes)
+    if alibi_slopes is not None and (alibi_slopes.dtype != torch.float32 or alibi_slopes.numel() != query.shape[1]
+                                     or not alibi_slopes.is_contiguous()):
+        raise RuntimeError("alibi_slopes must be a contiguous fp32 [num_heads] tensor")
     if softmax_lse is not None and (softmax_lse.dtype != torch.float32 or tuple(softmax_lse.shape) != (query.shape[1], query.shape[0])
                                     or not softmax_lse.is_contiguous()):
         raise RuntimeError("softmax_lse must be a contiguous fp32 [num_heads, total_q] tensor")
@@ -163,7 +168,7 @@ def flash_attn_varlen_paged(out: torch.Tensor, query: torch.Tensor, key_cache: t
             float(scale), 1 if causal else 0, dtype_enum(query.dtype), kvd, ptr(k_scale), ptr(v_scale),
             query.stride(0) if total_q > 1 else num_heads * head_size,
             out.stride(0) if total_q > 1 else num_heads * head_size, strides[0], strides[1], strides[2],
-            int(window_left), float(softcap or 0.0), ptr(softmax_lse), total_q, stream()))
+            int(window_left), float(softcap or 0.0), ptr(softmax_lse), total_q, ptr(alibi_slopes), stream()))
 
 
 def paged_attention_v1_quant(

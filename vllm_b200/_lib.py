@@ -108,7 +108,7 @@ SIGNATURES = {
                                               c_int64, _P]),
     "vb200_flash_attn_varlen_paged_opts": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                                    c_int, c_int, c_float, c_int, c_int, c_int, _P, _P, c_int64, c_int64,
-                                                   c_int64, c_int64, c_int64, c_int, c_float, _P, c_int64, _P]),
+                                                   c_int64, c_int64, c_int64, c_int, c_float, _P, c_int64, _P, _P]),
     "vb200_greedy_argmax": (c_int, [_P, _P, _P, c_int, c_int, c_int64, c_int, _P]),
     "vb200_advance_step_flashattn": (c_int, [c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int64, _P]),
     "vb200_merge_attn_states": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P]),

@@ -82,8 +82,6 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
     if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0] or window_left >= 0 or softcap > 0 or return_softmax_lse:
         # prefill / chunked prefill / mixed batch, or any batch with a window / soft-cap: the variable-length kernel
         # (csrc/paged_prefill.cu)
-        if alibi_slopes is not None:
-            raise NotImplementedError("flash_attn_varlen_func: ALiBi is built for the plain decode case only")
         if cu_seqlens_q is None:
             if max_seqlen_q != 1:
                 raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
@@ -92,7 +90,8 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         vs = v_descale.reshape(-1)[:1].float().contiguous() if fp8 else None
         lse = torch.empty((q.shape[1], q.shape[0]), dtype=torch.float32, device=q.device) if return_softmax_lse else None
         ops.flash_attn_varlen_paged(out, q, k, v, cu_seqlens_q, seqused_k, block_table, softmax_scale, causal,
-                                    int(max_seqlen_q), "fp8" if fp8 else "auto", ks, vs, window_left, softcap, lse)
+                                    int(max_seqlen_q), "fp8" if fp8 else "auto", ks, vs, window_left, softcap, lse,
+                                    alibi_slopes)
         return (out, lse) if return_softmax_lse else out
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None

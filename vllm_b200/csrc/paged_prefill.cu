@@ -47,6 +47,7 @@ struct Params {
   float cap_pre;                                    // soft-cap: softmax scale / cap (then scale_log2 = cap * log2(e)); 0: none
   float* lse;                                       // optional fp32 [num_heads, lse_stride]: log-sum-exp of every row's logits
   int64_t lse_stride;
+  const float* alibi_slopes;                        // optional fp32 [num_heads]: logit -= slope * |key - query position|
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
@@ -275,6 +276,16 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
     for (int h = 0; h < 2; ++h) tok_of[mt][h] = (m0 + wrow + mt * 16 + g + h * 8) / G;
   const int warp_first_tok = (m0 + wrow) / G;
   const int warp_last_tok = (m0 + wrow + 16 * MT - 1) / G;
+  // ALiBi in the units of the raw logits: (s + b / scale) * scale = s * scale + b
+  float alibi_c[MT][2];
+  const bool use_alibi = EXTRA && p.alibi_slopes != nullptr;
+  if (use_alibi) {
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        alibi_c[mt][h] = p.alibi_slopes[kvh * G + (m0 + wrow + mt * 16 + g + h * 8) % G] * 1.4426950408889634f / scale_log2;
+  }
 
   for (int j = j0; j < n_tiles; ++j) {
     const int stage = (j - j0) & 1;
@@ -329,8 +340,18 @@ __global__ void __launch_bounds__(NTHREADS) paged_prefill_flash_kernel(const Par
 #pragma unroll
           for (int e = 0; e < 4; ++e) s[mt][i][e] = tanh_2mufu(s[mt][i][e] * cap_pre);
     }
-    // ---- mask (only tiles that touch the diagonal, the left edge of the window or the end of the sequence)
     const int n_base = j * BN;
+    if (use_alibi) {
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int i = 0; i < BN / 8; ++i)
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            s[mt][i][e] = fmaf(-alibi_c[mt][e >> 1],
+                               fabsf((float)(n_base + i * 8 + 2 * tq + (e & 1) - shift - tok_of[mt][e >> 1])), s[mt][i][e]);
+    }
+    // ---- mask (only tiles that touch the diagonal, the left edge of the window or the end of the sequence)
     const bool need_mask = n_base + BN > n_keys || (p.causal && n_base + BN - 1 > shift + warp_first_tok) ||
                            (EXTRA && wl >= 0 && n_base < shift + warp_last_tok - wl);
     if (need_mask) {
@@ -483,7 +504,8 @@ extern "C" int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, 
                                                   const float* v_scale, int64_t q_stride, int64_t out_stride,
                                                   int64_t block_stride, int64_t token_stride, int64_t head_stride,
                                                   int window_left, float softcap, float* softmax_lse,
-                                                  int64_t lse_stride, vb200_stream_t stream) {
+                                                  int64_t lse_stride, const float* alibi_slopes,
+                                                  vb200_stream_t stream) {
   VB_CHECK(window_left < 0 || causal, "flash_attn_varlen_paged: a sliding window (left, 0) needs causal attention");
   VB_CHECK(softcap >= 0.f && softcap == softcap, "flash_attn_varlen_paged: softcap must be >= 0");
   VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "flash_attn_varlen_paged: dtype must be f16 or bf16");
@@ -526,6 +548,7 @@ extern "C" int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, 
   VB_CHECK(softmax_lse == nullptr || lse_stride >= total_q, "flash_attn_varlen_paged: lse_stride < total_q");
   p.lse = softmax_lse;
   p.lse_stride = lse_stride;
+  p.alibi_slopes = alibi_slopes;
   p.window_left = window_left < 0 ? -1 : window_left;
   p.cap_pre = 0.f;
   if (softcap > 0.f) {   // logits = softcap * tanh(q.k * scale / softcap): the tanh takes q.k * cap_pre, the exponent scale is the cap
@@ -534,7 +557,7 @@ extern "C" int vb200_flash_attn_varlen_paged_opts(void* out, const void* query, 
   }
   if (max_seqlen_q <= 0) max_seqlen_q = total_q;   // unknown: assume long chunks
   cudaStream_t st = (cudaStream_t)stream;
-  if (p.window_left >= 0 || p.cap_pre != 0.f || p.lse != nullptr) {
+  if (p.window_left >= 0 || p.cap_pre != 0.f || p.lse != nullptr || p.alibi_slopes != nullptr) {
     if (dtype == VB200_F16)
       return fp8 ? prefill::dispatch<__half, true, true>(p, head_size, total_q, max_seqlen_q, st)
                  : prefill::dispatch<__half, false, true>(p, head_size, total_q, max_seqlen_q, st);
@@ -560,5 +583,5 @@ extern "C" int vb200_flash_attn_varlen_paged(void* out, const void* query, const
                                             num_seqs, total_q, num_heads, num_kv_heads, head_size, block_size,
                                             max_num_blocks_per_seq, max_seqlen_q, scale, causal, dtype, kv_dtype, k_scale,
                                             v_scale, q_stride, out_stride, block_stride, token_stride, head_stride, -1,
-                                            0.f, nullptr, 0, stream);
+                                            0.f, nullptr, 0, nullptr, stream);
 }
