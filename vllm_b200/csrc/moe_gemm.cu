@@ -18,6 +18,8 @@
 // overlaps the other's weight stream.
 // The activation rows of a block are not contiguous in A (row = token_id / top_k): a small gather
 // kernel first writes them in sorted order into the workspace, so the GEMM loads A with plain TMA.
+#include <cstdlib>
+
 #include "tc_common.cuh"
 
 namespace vb200 {
@@ -49,6 +51,7 @@ struct MoeParams {
   int ragged;
   int in16;                        // 0: fp8 e4m3 operands; 1: f16; 2: bf16 (unquantised experts, test_moe.py:117-233).  K
                                    // and the tile sizes are in BYTES throughout, so only the MMA kind differs
+  int m_fastest;                   // CTA launch order: 1 = all M-blocks of a weight-row tile back to back (see the kernel)
 };
 
 // A_sorted[r, :] = A[sorted_token_ids[r] / top_k, :] for valid r < num_tokens_post_pad (16-byte
@@ -91,8 +94,17 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int n_tile = blockIdx.x;
-  const int pblk = blockIdx.y;
+  // Launch order.  CTAs start in the order x fastest.  With (n_tile, pblk) = (x, y) the M-blocks of one expert -- an
+  // expert with more rows than block_m has several -- read the same weight tile a whole sweep of n tiles apart, and
+  // the evict-first weight stream has left L2 by then: the expert's weights come from HBM once per M-block.  With
+  // m_fastest the M-blocks of a weight-row tile run back to back, so the second read of a tile meets the first in
+  // L2 and the weights cross HBM once whatever the routing skew.
+  int n_tile = blockIdx.x, pblk = blockIdx.y;
+  if (p.m_fastest) {
+    const int lin = blockIdx.y * gridDim.x + blockIdx.x;
+    n_tile = lin / (int)gridDim.y;
+    pblk = lin - n_tile * (int)gridDim.y;
+  }
   const int n0 = n_tile * kMoeBlockN;
   int row0, expert;
   if (p.ragged) {
@@ -315,6 +327,10 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
   VB_CHECK(block_m >= 16 && block_m <= kMoeMaxBlockM && block_m % 16 == 0,
            "moe grouped GEMM: block_m (%d) must be a multiple of 16 in [16, %d]", block_m, kMoeMaxBlockM);
   p.num_kb = (K + kMoeBlockK - 1) / kMoeBlockK;
+  {
+    const char* e = getenv("VB200_MOE_ORDER");   // A/B switch for benchmarks: 0 = n tiles fastest (the old order)
+    p.m_fastest = (e && e[0] == '0') ? 0 : 1;
+  }
   const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
   const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
   // two CTAs per SM when the stages fit in half of the shared memory, else one
@@ -497,6 +513,14 @@ extern "C" int vb200_cutlass_moe_mm(void* out, const void* a, const void* b, con
   // more than reading an expert's weights once (batch 512: 272 -> 259 us); long K (w2) prefers the 256-row block
   // (113 vs 134 us) -- profiles/r01_moe_gemm_sweep_s16.jsonl, r01_moe_gemm_sweep_s31.jsonl
   if (block_m > 128 && K <= 8192) block_m = 128;
+  // more than 256 rows per expert on average: every expert has several M-blocks whatever the block, and with the
+  // M-blocks of a weight tile launched back to back the smaller block (two CTAs per SM) wins (w2, batch 2048: 269 vs
+  // 286 us, profiles/r02_moe_gemm_block_m_s73.txt)
+  if ((num_rows + E - 1) / E > 256) block_m = 128;
+  if (const char* e = getenv("VB200_MOE_RAGGED_BLOCK_M")) {   // benchmark override
+    const int v = atoi(e);
+    if (v >= 16 && v % 16 == 0) block_m = v;
+  }
   if (block_m > kMoeMaxBlockM) block_m = kMoeMaxBlockM;  // s_tok / s_rowscale / TMEM columns / UMMA N all end at 256
   const int m_blocks = E + num_rows / block_m;  // >= sum_e ceil(m_e / block_m)
   CUtensorMap tw, ta;
