@@ -44,6 +44,7 @@ struct MoeParams {
   int num_valid_tokens, top_k, E, N, K, block_m;
   int a_per_token, b_per_channel;
   int stages, num_kb, tmem_cols;
+  int tile_cols;                   // TMEM columns of one weight tile's accumulator (tmem_cols = NT * tile_cols)
   // ragged ("CUTLASS-style") mode: experts own contiguous row ranges of A / C given by expert_offsets and
   // problem_sizes (csrc/quantization/cutlass_w8a8/moe/get_group_starts.cuh:11-31); no sorted_token_ids
   const int32_t* expert_offsets;   // [E] first row of expert e
@@ -73,8 +74,12 @@ __global__ void __launch_bounds__(256) moe_gather_rows_kernel(
   }
 }
 
-template <typename OutT>
-__global__ void __launch_bounds__(kMoeThreads, 2)
+// NT = weight-row tiles per CTA.  NT = 2 (larger batches): one CTA multiplies TWO adjacent 128-row weight tiles with ONE
+// activation tile per k-block -- two accumulators in TMEM -- so the activation bytes, which every CTA pulls from L2
+// for itself, are fetched once per 256 weight rows; one CTA per SM (the stage is 16 KiB larger and TMEM holds 2 x
+// tile_cols columns).  NT = 1 (decode batches): the pure weight stream, two CTAs per SM.
+template <typename OutT, int NT>
+__global__ void __launch_bounds__(kMoeThreads, NT == 1 ? 2 : 1)
     moe_grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w,
                             const __grid_constant__ CUtensorMap tmap_a, const MoeParams p) {
   pdl_wait();
@@ -83,7 +88,7 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   const int a_tile_bytes = p.block_m * kMoeBlockK;
-  const int stage_bytes = kMoeWTile + a_tile_bytes;
+  const int stage_bytes = NT * kMoeWTile + a_tile_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
   uint64_t* empty_bar = full_bar + kMoeMaxStages;
   uint64_t* acc_bar = empty_bar + kMoeMaxStages;
@@ -105,7 +110,8 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
     n_tile = lin / (int)gridDim.y;
     pblk = lin - n_tile * (int)gridDim.y;
   }
-  const int n0 = n_tile * kMoeBlockN;
+  const int n0 = n_tile * kMoeBlockN * NT;
+  const int nt_eff = (NT == 2 && n0 + kMoeBlockN < p.N) ? 2 : 1;   // the last CTA of an odd tile count has one tile
   int row0, expert;
   if (p.ragged) {
     // linear M-block id -> (expert, block inside the expert's row range): experts are walked in order, each owning
@@ -156,7 +162,7 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
     for (int i = 0; i < nvalid; ++i) {
       const int tok = s_tok[i];
       if (tok < 0 || tok >= p.num_valid_tokens) continue;
-      for (int n = n0 + threadIdx.x; n < min(n0 + kMoeBlockN, p.N); n += kMoeThreads)
+      for (int n = n0 + threadIdx.x; n < min(n0 + kMoeBlockN * NT, p.N); n += kMoeThreads)
         outp[(int64_t)tok * p.N + n] = from_float<OutT>(0.f);
     }
     return;
@@ -190,9 +196,11 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
       mbar_wait(&empty_bar[stage], phase ^ 1);
       uint8_t* sw = smem + (size_t)stage * stage_bytes;
       if (elect_one()) {
-        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(nt_eff * kMoeWTile + a_tile_bytes));
         tma_load_2d(sw, &tmap_w, &full_bar[stage], kb * kMoeBlockK, wrow, kEvictFirst);
-        tma_load_2d(sw + kMoeWTile, &tmap_a, &full_bar[stage], kb * kMoeBlockK, row0, kEvictLast);
+        if (NT == 2 && nt_eff == 2)
+          tma_load_2d(sw + kMoeWTile, &tmap_w, &full_bar[stage], kb * kMoeBlockK, wrow + kMoeBlockN, kEvictFirst);
+        tma_load_2d(sw + NT * kMoeWTile, &tmap_a, &full_bar[stage], kb * kMoeBlockK, row0, kEvictLast);
       }
       __syncwarp();
       if (++stage == p.stages) {
@@ -210,20 +218,26 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
       const uint32_t sw = smem_base_u + (uint32_t)stage * (uint32_t)stage_bytes;
-      const uint64_t adesc = make_smem_desc_sw128(sw);
-      const uint64_t bdesc = make_smem_desc_sw128(sw + kMoeWTile);
+      const uint64_t bdesc = make_smem_desc_sw128(sw + NT * kMoeWTile);
       if (elect_one()) {
-        // 32 bytes of K per MMA either way: 32 e4m3 or 16 f16 / bf16 elements
-        if (p.in16) {
 #pragma unroll
-          for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
-            umma_f16(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
-                     bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
-        } else {
+        for (int t = 0; t < NT; ++t) {
+          if (t < nt_eff) {
+            const uint64_t adesc = make_smem_desc_sw128(sw + t * kMoeWTile);
+            const uint32_t acc = tmem_u + (uint32_t)(t * p.tile_cols);
+            // 32 bytes of K per MMA either way: 32 e4m3 or 16 f16 / bf16 elements
+            if (p.in16) {
 #pragma unroll
-          for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
-            umma_f8(tmem_u, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
-                    bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+              for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
+                umma_f16(acc, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+                         bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+            } else {
+#pragma unroll
+              for (int k = 0; k < kMoeBlockK / kMoeUmmaK; ++k)
+                umma_f8(acc, adesc + (uint64_t)(k * (kMoeUmmaK >> 4)),
+                        bdesc + (uint64_t)(k * (kMoeUmmaK >> 4)), idesc, (kb | k) != 0);
+            }
+          }
         }
         umma_commit(&empty_bar[stage]);
       }
@@ -249,16 +263,25 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
     const int nl = q * 32 + lane;
-    const int n = n0 + nl;
-    const bool n_ok = n < p.N;
-    const float bsc = p.b_scales == nullptr ? 1.f
-                                            : (p.b_per_channel ? (n_ok ? p.b_scales[(int64_t)expert * p.N + n] : 0.f)
-                                                               : p.b_scales[expert]);
+    float bsc_t[NT];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const int nn = n0 + t * kMoeBlockN + nl;
+      bsc_t[t] = p.b_scales == nullptr ? 1.f
+                                       : (p.b_per_channel ? (nn < p.N ? p.b_scales[(int64_t)expert * p.N + nn] : 0.f)
+                                                          : p.b_scales[expert]);
+    }
     const bool mul_w = p.topk_weights != nullptr;
     mbar_wait(acc_bar, 0);
     tc_fence_after();
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     OutT* outp = reinterpret_cast<OutT*>(p.c);
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+    if (t >= nt_eff) break;
+    const int n = n0 + t * kMoeBlockN + nl;
+    const bool n_ok = n < p.N;
+    const float bsc = bsc_t[t];
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.tile_cols);
     // token ids and the two per-row factors are read with explicit ld.shared, 16 columns at a time, BEFORE the
     // stores of those columns: a generic load would be ordered behind every earlier global store and serialise
     // the loop on the shared-memory latency
@@ -307,6 +330,7 @@ __global__ void __launch_bounds__(kMoeThreads, 2)
         }
       }
     }
+    }   // weight tile t
   }
   tc_fence_before();
   __syncthreads();
@@ -331,11 +355,20 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
     const char* e = getenv("VB200_MOE_ORDER");   // A/B switch for benchmarks: 0 = n tiles fastest (the old order)
     p.m_fastest = (e && e[0] == '0') ? 0 : 1;
   }
-  const int stage_bytes = kMoeWTile + block_m * kMoeBlockK;
+  // Two weight tiles per CTA once an M-block holds 128 rows or more AND K is long (w2: K = intermediate size): there
+  // the kernel is bound by the L2 -> SM traffic of the activation tiles (see the kernel's NT comment): w2 at batch 512
+  // 128 -> 105 us, at 2048 275 -> 257.  With a short K (w13: 32 k-blocks) a CTA's prologue and epilogue weigh more
+  // than the saved traffic and two CTAs per SM overlapping them win (215 vs 223 us): profiles/r02_moe_gemm_nt2_s74.txt
+  int nt = (block_m >= 128 && N >= 2 * kMoeBlockN && K >= 8192) ? 2 : 1;
+  if (const char* e = getenv("VB200_MOE_NT")) {   // A/B switch for benchmarks
+    if (e[0] == '1') nt = 1;
+    if (e[0] == '2' && N >= 2 * kMoeBlockN) nt = 2;
+  }
+  const int stage_bytes = nt * kMoeWTile + block_m * kMoeBlockK;
   const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
   // two CTAs per SM when the stages fit in half of the shared memory, else one
   int budget = (227 * 1024) / 2 - 1024 - meta;
-  int stages = budget / stage_bytes;
+  int stages = nt == 1 ? budget / stage_bytes : 0;
   if (stages < 3) {
     budget = 227 * 1024 - 1024 - meta;
     stages = budget / stage_bytes;
@@ -345,18 +378,26 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
   p.stages = stages;
   int cols = 32;
   while (cols < block_m) cols <<= 1;
-  p.tmem_cols = cols;
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
-  dim3 grid((N + kMoeBlockN - 1) / kMoeBlockN, m_blocks);
+  p.tile_cols = cols;
+  p.tmem_cols = nt * cols;
+  size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
+  // NT = 2 is compiled for one CTA per SM and may take all 512 TMEM columns: never let two of them share an SM
+  if (nt == 2 && smem < 120 * 1024) smem = 120 * 1024;
+  dim3 grid((N + kMoeBlockN * nt - 1) / (kMoeBlockN * nt), m_blocks);
+#define VB_MOE_LAUNCH(T, NT_)                                                                             \
+  do {                                                                                                    \
+    auto kern = moe_grouped_gemm_kernel<T, NT_>;                                                          \
+    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));   \
+    VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kMoeThreads), smem, stream, tw, ta, p));                \
+  } while (0)
   if (out_dtype == VB200_BF16) {
-    auto kern = moe_grouped_gemm_kernel<__nv_bfloat16>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kMoeThreads), smem, stream, tw, ta, p));
+    if (nt == 2) VB_MOE_LAUNCH(__nv_bfloat16, 2);
+    else VB_MOE_LAUNCH(__nv_bfloat16, 1);
   } else {
-    auto kern = moe_grouped_gemm_kernel<__half>;
-    VB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    VB_CUDA_CHECK(launch_k(kern, dim3(grid), dim3(kMoeThreads), smem, stream, tw, ta, p));
+    if (nt == 2) VB_MOE_LAUNCH(__half, 2);
+    else VB_MOE_LAUNCH(__half, 1);
   }
+#undef VB_MOE_LAUNCH
   VB_LAUNCH_CHECK();
   return 0;
 }
