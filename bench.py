@@ -450,7 +450,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     counter = {"n": 0}
     per_call = {"vb200_paged_attention_v1": 2, "vb200_paged_attention_v2": 2, "vb200_paged_attention_v1_quant": 2,
                 "vb200_dynamic_scaled_fp8_quant": 2,
-                "vb200_moe_grouped_gemm_fp8": 2}
+                "vb200_moe_grouped_gemm_fp8": 2, "vb200_moe_grouped_gemm_fp8_q16": 2, "vb200_moe_grouped_gemm_16": 2}
     wrapped = {}
     for name in _lib.SIGNATURES:
         if name.startswith("vb200_") and not any(s in name for s in ("size", "error", "version", "supports")):

@@ -267,6 +267,15 @@ int vb200_dynamic_per_token_scaled_fp8_quant(void* out, const void* input, float
  * out[t,i] = T(silu_f32(x[t,i])) *_T x[t,d+i]; input [num_tokens, 2d], out [num_tokens, d]. */
 int vb200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, int dtype,
                        vb200_stream_t stream);
+/* The two halves of the dynamic per-tensor quantisation around the MoE activation (fused_moe.py:1506-1527: activation,
+ * then moe_kernel_quantize_input -> scaled_fp8_quant(x, None), fp8/common.cu:113-137) for a pipeline that quantises
+ * while it gathers (vb200_moe_grouped_gemm_fp8_q16): vb200_absmax_scale is the first pass of
+ * vb200_dynamic_scaled_fp8_quant alone (*scale = max(*scale, max|x| / 448), scale pre-zeroed by the caller);
+ * vb200_silu_and_mul_absmax is vb200_silu_and_mul (f16 / bf16, d % 8 == 0) that leaves the same quantity of its
+ * OUTPUT (as rounded to the tensor dtype) in *scale. */
+int vb200_absmax_scale(float* scale, const void* input, int64_t numel, int in_dtype, vb200_stream_t stream);
+int vb200_silu_and_mul_absmax(void* out, float* scale, const void* input, int64_t num_tokens, int d, int dtype,
+                              vb200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------ */
 /* Per-token glue between the contractions                         */
@@ -392,6 +401,17 @@ int vb200_moe_grouped_gemm_fp8(void* c, const void* a, const void* b, const floa
                                int sorted_capacity, int a_scales_per_token,
                                int b_scales_per_channel, int mul_routed_weight, int out_dtype,
                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
+
+/* vb200_moe_grouped_gemm_fp8 fed with the UNQUANTISED activations a [num_a_rows, K] (a_dtype F16 / BF16) and their
+ * per-tensor scale a_scale (device scalar): rows are quantised (fp8(x * (1 / scale)), fp8/common.cu:14-26) while they
+ * are gathered into expert order -- one launch instead of static_scaled_fp8_quant + gather.  Bit-identical to
+ * vb200_static_scaled_fp8_quant followed by vb200_moe_grouped_gemm_fp8 with a per-tensor a_scales. */
+int vb200_moe_grouped_gemm_fp8_q16(void* c, const void* a, int a_dtype, const void* b, const float* a_scale,
+                                   const float* b_scales, const float* topk_weights, const int32_t* sorted_token_ids,
+                                   const int32_t* expert_ids, const int32_t* num_tokens_post_pad, int num_valid_tokens,
+                                   int num_a_rows, int top_k, int E, int N, int K, int block_m, int sorted_capacity,
+                                   int b_scales_per_channel, int mul_routed_weight, int out_dtype, void* workspace,
+                                   size_t workspace_bytes, vb200_stream_t stream);
 
 /* Unquantised (f16 / bf16) experts: the same grouped GEMM for fused_experts with use_fp8_w8a8 = False
  * (fused_moe.py:1349-1563; the bf16-weights case of tests/kernels/moe/test_moe.py:117-233):

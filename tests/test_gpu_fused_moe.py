@@ -225,3 +225,58 @@ def test_fused_moe_layer(quant, mode):
     # sums differ; tp2 (fp8): the second quantisation sees half of the intermediate row, so its per-tensor scale differs
     torch.testing.assert_close(got, want.float(), rtol=2e-2, atol=2e-2 * scale)
     assert (got - want.float()).abs().mean().item() <= 4e-3 * scale
+
+
+@pytest.mark.parametrize("T,k,E,H,I", [(1, 2, 8, 256, 512), (128, 2, 8, 512, 1024), (33, 6, 64, 256, 256),
+                                       (300, 2, 4, 256, 128), (128, 2, 8, 4096, 1792)])
+@pytest.mark.parametrize("static_scales", [False, True])
+def test_fused_experts_per_tensor_pipeline_is_bit_identical_to_the_unfused_ops(T, k, E, H, I, static_scales):
+    """fused_experts with per-tensor activation scales computes only the scales up front (abs-max, fused with
+    silu_and_mul for the second GEMM) and quantises while it gathers (vb200_moe_grouped_gemm_fp8_q16): 8 launches
+    instead of 12.  Same bytes into the GEMMs: the output must equal, bit for bit, the reference's sequence
+    scaled_fp8_quant -> GEMM -> silu_and_mul -> scaled_fp8_quant -> GEMM -> moe_sum (fused_moe.py:1470-1560) run op by op."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.fused_moe import fused_experts, invoke_fused_moe_kernel, moe_align_block_size
+    from vllm_b200.fused_moe.fused_moe import get_block_m
+    seed_all(T + H + I)
+    w1, s1 = _fp8_weights(E, 2 * I, H, False)
+    w2, s2 = _fp8_weights(E, H, I, False)
+    x = (torch.randn(T, H) * 0.7).bfloat16().to(DEV)
+    ids = torch.stack([torch.randperm(E)[:k] for _ in range(T)]).to(torch.int32).to(DEV)
+    tw = (torch.rand(T, k) + 0.1).to(DEV)
+    w1d, s1d, w2d, s2d = w1.to(DEV), s1.to(DEV), w2.to(DEV), s2.to(DEV)
+    a1 = torch.tensor([0.011], device=DEV) if static_scales else None
+    a2 = torch.tensor([0.023], device=DEV) if static_scales else None
+    got = fused_experts(x, w1d, w2d, tw, ids, use_fp8_w8a8=True, w1_scale=s1d, w2_scale=s2d, a1_scale=a1, a2_scale=a2)
+    # the same pipeline op by op
+    bm = get_block_m(T * k, E)
+    sorted_ids, expert_ids, npost = moe_align_block_size(ids, bm, E)
+    a1q, a1s = ops.scaled_fp8_quant(x, a1)
+    c1 = torch.empty(T, k, 2 * I, dtype=torch.bfloat16, device=DEV)
+    invoke_fused_moe_kernel(a1q, w1d, c1, a1s, s1d, None, sorted_ids, expert_ids, npost, False, k, bm, True, False)
+    c2 = torch.empty(T * k, I, dtype=torch.bfloat16, device=DEV)
+    ops.silu_and_mul(c2, c1.view(T * k, 2 * I))
+    a2q, a2s = ops.scaled_fp8_quant(c2, a2)
+    c3 = torch.empty(T, k, H, dtype=torch.bfloat16, device=DEV)
+    invoke_fused_moe_kernel(a2q, w2d, c3, a2s, s2d, tw, sorted_ids, expert_ids, npost, True, 1, bm, True, False)
+    want = torch.empty_like(x)
+    ops.moe_sum(c3, want)
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
+def test_silu_and_mul_absmax_matches_the_two_ops():
+    from vllm_b200 import _custom_ops as ops
+    seed_all(12)
+    x = (torch.randn(77, 2 * 1792) * 2).bfloat16().to(DEV)
+    want = torch.empty(77, 1792, dtype=torch.bfloat16, device=DEV)
+    ops.silu_and_mul(want, x)
+    _, want_scale = ops.scaled_fp8_quant(want, None)
+    out = torch.empty_like(want)
+    scale = torch.zeros(1, dtype=torch.float32, device=DEV)
+    ops.silu_and_mul_absmax(out, scale, x)
+    assert torch.equal(out.view(torch.int16), want.view(torch.int16))
+    assert torch.equal(scale.view(-1), want_scale.view(-1))
+    s2 = torch.zeros(1, dtype=torch.float32, device=DEV)
+    ops.absmax_scale(s2, want)
+    assert torch.equal(s2.view(-1), want_scale.view(-1))

@@ -485,6 +485,30 @@ def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
         check(load().vb200_silu_and_mul(ptr(out), ptr(x), n, d, dtype_enum(x.dtype), stream()))
 
 
+def absmax_scale(scale: torch.Tensor, x: torch.Tensor) -> None:
+    """First pass of the dynamic per-tensor scaled_fp8_quant (fp8/common.cu:113-137) on its own:
+    scale[0] = max(scale[0], max|x| / 448); `scale` is an fp32 tensor the caller zeroed."""
+    require_cuda(scale, x)
+    if scale.dtype != torch.float32 or not x.is_contiguous():
+        raise RuntimeError("absmax_scale: fp32 scale and a contiguous input")
+    with _device_of(x):
+        check(load().vb200_absmax_scale(ptr(scale), ptr(x), x.numel(), dtype_enum(x.dtype), stream()))
+
+
+def silu_and_mul_absmax(out: torch.Tensor, scale: torch.Tensor, x: torch.Tensor) -> None:
+    """silu_and_mul that also leaves max|out| / 448 in scale[0] (pre-zeroed): activation + first pass of the dynamic
+    per-tensor quantisation that follows it in the fp8 MoE pipeline, one launch."""
+    require_cuda(out, scale, x)
+    d = x.shape[-1] // 2
+    if not (x.is_contiguous() and out.is_contiguous()) or out.shape[-1] != d or out.dtype != x.dtype:
+        raise RuntimeError("silu_and_mul_absmax: contiguous x [..., 2d] and out [..., d] of one dtype")
+    if scale.dtype != torch.float32:
+        raise RuntimeError("silu_and_mul_absmax: fp32 scale")
+    n = x.numel() // max(x.shape[-1], 1)
+    with _device_of(x):
+        check(load().vb200_silu_and_mul_absmax(ptr(out), ptr(scale), ptr(x), n, d, dtype_enum(x.dtype), stream()))
+
+
 # ------------------------------------------------------------------------------------------------
 # fp8 w8a8 linear  (reference: vllm/_custom_ops.py:688-741)
 # ------------------------------------------------------------------------------------------------

@@ -76,6 +76,8 @@ SIGNATURES = {
     "vb200_dynamic_scaled_fp8_quant": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_dynamic_per_token_scaled_fp8_quant": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_silu_and_mul": (c_int, [_P, _P, c_int64, c_int, c_int, _P]),
+    "vb200_absmax_scale": (c_int, [_P, _P, c_int64, c_int, _P]),
+    "vb200_silu_and_mul_absmax": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_rms_norm": (c_int, [_P, _P, _P, c_float, c_int, c_int, c_int64, c_int, _P]),
     "vb200_fused_add_rms_norm": (c_int, [_P, _P, _P, c_float, c_int, c_int, c_int64, c_int, _P]),
     "vb200_rms_norm_dynamic_per_token_quant": (c_int, [_P, _P, _P, _P, c_float, _P, _P, c_int, c_int, c_int, _P]),
@@ -95,6 +97,8 @@ SIGNATURES = {
     "vb200_moe_grouped_gemm_fp8": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                            c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t,
                                            _P]),
+    "vb200_moe_grouped_gemm_fp8_q16": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
+                                               c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_moe_grouped_gemm_16": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                           c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_moe_grouped_gemm_workspace_size": (c_size_t, [c_int, c_int]),

@@ -467,6 +467,67 @@ extern "C" int vb200_moe_grouped_gemm_fp8(
   return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
 }
 
+// The fp8 grouped GEMM fed with UNQUANTISED activations and their per-tensor scale: the rows are quantised while they
+// are gathered into expert order (one launch instead of static_scaled_fp8_quant + gather, and no fp8 copy of the
+// activations in token order).  Quantising a row is element-wise with one scale, so the bytes the GEMM reads are those
+// of "quantise the tensor (fp8/common.cu:14-26), then gather": the result is bit-identical to
+// vb200_static_scaled_fp8_quant + vb200_moe_grouped_gemm_fp8 (a_scales_per_token = 0).
+namespace vb200 {
+int launch_moe_gather_quant_sorted(uint8_t* out, const void* input, const int32_t* sorted_token_ids,
+                                   const int32_t* num_tokens_post_pad, const float* static_scale, int sorted_capacity,
+                                   int num_src_rows, int top_k, int hidden, int in_dtype, cudaStream_t stream);
+}
+extern "C" int vb200_moe_grouped_gemm_fp8_q16(
+    void* c, const void* a, int a_dtype, const void* b, const float* a_scale, const float* b_scales,
+    const float* topk_weights, const int32_t* sorted_token_ids, const int32_t* expert_ids,
+    const int32_t* num_tokens_post_pad, int num_valid_tokens, int num_a_rows, int top_k, int E, int N, int K, int block_m,
+    int sorted_capacity, int b_scales_per_channel, int mul_routed_weight, int out_dtype, void* workspace,
+    size_t workspace_bytes, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(out_dtype == VB200_BF16 || out_dtype == VB200_F16, "moe_grouped_gemm_fp8_q16: out dtype must be bf16 or f16");
+  VB_CHECK(a_dtype == VB200_BF16 || a_dtype == VB200_F16, "moe_grouped_gemm_fp8_q16: activations must be bf16 or f16");
+  VB_CHECK(K > 0 && K % 16 == 0, "moe_grouped_gemm_fp8_q16: K (%d) must be a positive multiple of 16", K);
+  VB_CHECK(block_m >= 16 && block_m <= kMoeMaxBlockM && block_m % 16 == 0,
+           "moe_grouped_gemm_fp8_q16: block_m (%d) must be a multiple of 16 in [16, 256]", block_m);
+  VB_CHECK(top_k >= 1 && E >= 1 && N >= 1 && num_a_rows >= 1, "moe_grouped_gemm_fp8_q16: bad top_k / E / N / rows");
+  VB_CHECK(a_scale != nullptr, "moe_grouped_gemm_fp8_q16: the per-tensor activation scale is required");
+  VB_CHECK(!mul_routed_weight || topk_weights != nullptr, "moe_grouped_gemm_fp8_q16: mul_routed_weight needs topk_weights");
+  if (num_valid_tokens <= 0 || sorted_capacity <= 0) return 0;
+  const size_t need = vb200_moe_grouped_gemm_workspace_size(sorted_capacity, K);
+  VB_CHECK(workspace != nullptr && workspace_bytes >= need, "moe_grouped_gemm_fp8_q16: workspace too small (%zu < %zu)",
+           workspace_bytes, need);
+  uint8_t* a_sorted = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~static_cast<uintptr_t>(255));
+  VB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0, "moe_grouped_gemm_fp8_q16: A must be 16-byte aligned");
+  if (int rc = launch_moe_gather_quant_sorted(a_sorted, a, sorted_token_ids, num_tokens_post_pad, a_scale, sorted_capacity,
+                                              num_a_rows, top_k, K, a_dtype, stream))
+    return rc;
+  const int m_blocks = (sorted_capacity + block_m - 1) / block_m;
+  CUtensorMap tw, ta;
+  if (tc::make_tmap_2d_u8(&tw, b, (uint64_t)E * N, (uint64_t)K, (uint64_t)K, kMoeBlockN)) return 1;
+  if (tc::make_tmap_2d_u8(&ta, a_sorted, (uint64_t)m_blocks * block_m, (uint64_t)K, (uint64_t)K, (uint32_t)block_m)) return 1;
+  MoeParams p;
+  p.c = c;
+  p.a_scales = a_scale;
+  p.b_scales = b_scales;
+  p.topk_weights = mul_routed_weight ? topk_weights : nullptr;
+  p.sorted_token_ids = sorted_token_ids;
+  p.expert_ids = expert_ids;
+  p.num_tokens_post_pad = num_tokens_post_pad;
+  p.num_valid_tokens = num_valid_tokens;
+  p.top_k = top_k;
+  p.E = E;
+  p.N = N;
+  p.K = K;
+  p.block_m = block_m;
+  p.a_per_token = 0;
+  p.b_per_channel = b_scales_per_channel ? 1 : 0;
+  p.expert_offsets = nullptr;
+  p.problem_sizes = nullptr;
+  p.ragged = 0;
+  p.in16 = 0;
+  return launch_moe_gemm(p, tw, ta, m_blocks, out_dtype, stream);
+}
+
 // Unquantised (f16 / bf16) experts: the bf16-weights variant of fused_experts (fused_moe.py:1349-1563 with
 // use_fp8_w8a8 = False; reference test tests/kernels/moe/test_moe.py:117-233).  Same kernel -- tiles, TMA boxes and the
 // pipeline are sized in bytes -- with kind::f16 MMAs and no scales:

@@ -158,14 +158,17 @@ __global__ void __launch_bounds__(256) moe_gather_quant_kernel(uint8_t* __restri
                                                                const int* __restrict__ num_routed,
                                                                const float* __restrict__ static_scale,
                                                                const float* __restrict__ scale_ub, int num_src,
-                                                               int hidden) {
+                                                               int hidden, int src_div) {
   pdl_wait();
   pdl_trigger();
   __shared__ float sm[8];
   const int r = blockIdx.x;
   if (num_routed != nullptr && r >= *num_routed) return;   // rows no local expert owns: never read downstream
-  const int s_row = src_row[r];
-  if (s_row < 0 || s_row >= num_src) return;
+  // src_row holds source rows (src_div = 1) or (token, slot) pair ids whose source row is id / top_k (the
+  // sorted_token_ids of moe_align_block_size; its padding ids are >= num_src * src_div)
+  int s_row = src_row[r];
+  if (s_row < 0 || s_row >= num_src * src_div) return;
+  s_row /= src_div;
   constexpr int VE = 16 / sizeof(T);
   const T* rin = in + (int64_t)s_row * hidden;
   uint8_t* rout = out + (int64_t)r * hidden;
@@ -337,14 +340,34 @@ extern "C" int vb200_moe_gather_quant_fp8(void* out, float* scales, const void* 
   if (in_dtype == VB200_BF16)
     VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__nv_bfloat16>, dim3(num_dst_rows), dim3(threads), 0, stream,
                            (uint8_t*)out, scales, (const __nv_bfloat16*)input, src_row, num_routed, static_scale,
-                           scale_ub, num_src_rows, hidden));
+                           scale_ub, num_src_rows, hidden, 1));
   else
     VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__half>, dim3(num_dst_rows), dim3(threads), 0, stream,
                            (uint8_t*)out, scales, (const __half*)input, src_row, num_routed, static_scale, scale_ub,
-                           num_src_rows, hidden));
+                           num_src_rows, hidden, 1));
   VB_LAUNCH_CHECK();
   return 0;
 }
+
+// The same gather + static quantisation driven by moe_align_block_size's sorted_token_ids (pair ids, source row =
+// id / top_k): used by vb200_moe_grouped_gemm_fp8_q16 (moe_gemm.cu) in place of "quantise the tensor, then gather".
+namespace vb200 {
+int launch_moe_gather_quant_sorted(uint8_t* out, const void* input, const int32_t* sorted_token_ids,
+                                   const int32_t* num_tokens_post_pad, const float* static_scale, int sorted_capacity,
+                                   int num_src_rows, int top_k, int hidden, int in_dtype, cudaStream_t stream) {
+  const int threads = hidden >= 2048 ? 256 : 128;
+  if (in_dtype == VB200_BF16)
+    VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__nv_bfloat16>, dim3(sorted_capacity), dim3(threads), 0, stream, out,
+                           (float*)nullptr, (const __nv_bfloat16*)input, sorted_token_ids, num_tokens_post_pad,
+                           static_scale, (const float*)nullptr, num_src_rows, hidden, top_k));
+  else
+    VB_CUDA_CHECK(launch_k(moe_gather_quant_kernel<__half>, dim3(sorted_capacity), dim3(threads), 0, stream, out,
+                           (float*)nullptr, (const __half*)input, sorted_token_ids, num_tokens_post_pad, static_scale,
+                           (const float*)nullptr, num_src_rows, hidden, top_k));
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+}  // namespace vb200
 
 template <typename T>
 static int launch_unpermute_reduce(void* out, const void* c, const int32_t* dst_row, const float* weights,

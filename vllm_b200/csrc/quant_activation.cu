@@ -164,6 +164,36 @@ __global__ void __launch_bounds__(256) silu_and_mul_kernel(T* __restrict__ out,
   }
 }
 
+// silu_and_mul that also leaves max|out| / 448 in *scale (atomic max; pre-zeroed by the caller): the first pass of the
+// dynamic per-tensor quantisation that follows it in the fp8 MoE pipeline (fused_moe.py:1506-1527: activation, then
+// moe_kernel_quantize_input), taken from the values as rounded to T -- what absmax_scale_kernel would read back.
+template <typename T>
+__global__ void __launch_bounds__(256) silu_and_mul_absmax_kernel(T* __restrict__ out, float* __restrict__ scale,
+                                                                  const T* __restrict__ in, int d) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float sm[8];
+  const int64_t row = blockIdx.x;
+  const T* x = in + row * 2 * d;
+  const T* y = x + d;
+  T* o = out + row * d;
+  constexpr int VE = 16 / sizeof(T);
+  float m = 0.f;
+  for (int i = threadIdx.x; i < d / VE; i += blockDim.x) {
+    union { uint4 u; T e[VE]; } a, b, r;
+    a.u = *reinterpret_cast<const uint4*>(x + i * VE);
+    b.u = *reinterpret_cast<const uint4*>(y + i * VE);
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      r.e[j] = silu_mul<T>(a.e[j], b.e[j]);
+      m = fmaxf(m, fabsf(to_float<T>(r.e[j])));
+    }
+    *reinterpret_cast<uint4*>(o + i * VE) = r.u;
+  }
+  m = block_max_256(m, sm);
+  if (threadIdx.x == 0) atomicMax(reinterpret_cast<int*>(scale), __float_as_int(m / kFp8Max));
+}
+
 static inline int stream_grid(int64_t n, int per_thread) {
   int64_t b = (n / per_thread + 255) / 256;
   const int64_t cap = (int64_t)num_sms() * 8;
@@ -235,6 +265,32 @@ extern "C" int vb200_silu_and_mul(void* out, const void* input, int64_t num_toke
   const int threads = d / ve >= 256 ? 256 : (d / ve >= 128 ? 128 : 64);
   DISPATCH_IN(dtype, {
     VB_CUDA_CHECK(launch_k(silu_and_mul_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(threads), 0, stream, (scalar_t*)out, (const scalar_t*)input, d, vec));
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+// First pass of dynamic_scaled_fp8_quant on its own: *scale = max(*scale, max|input| / 448) (scale pre-zeroed by the
+// caller).  The fp8 MoE pipeline quantises while it gathers the rows into expert order, so it needs only the scale.
+extern "C" int vb200_absmax_scale(float* scale, const void* input, int64_t numel, int in_dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (numel <= 0) return 0;
+  DISPATCH_IN(in_dtype, {
+    VB_CUDA_CHECK(launch_k(absmax_scale_kernel<scalar_t>, dim3(stream_grid(numel, 8)), dim3(256), 0, stream, scale, (const scalar_t*)input, numel));
+  });
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int vb200_silu_and_mul_absmax(void* out, float* scale, const void* input, int64_t num_tokens, int d, int dtype,
+                                         vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (num_tokens <= 0 || d <= 0) return 0;
+  VB_CHECK(dtype == VB200_F16 || dtype == VB200_BF16, "silu_and_mul_absmax: dtype must be f16 or bf16");
+  VB_CHECK(d % 8 == 0 && (reinterpret_cast<uintptr_t>(input) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+           "silu_and_mul_absmax: d (%d) must be a multiple of 8 and the tensors 16-byte aligned", d);
+  DISPATCH_IN(dtype, {
+    VB_CUDA_CHECK(launch_k(silu_and_mul_absmax_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(256), 0, stream, (scalar_t*)out, scale, (const scalar_t*)input, d));
   });
   VB_LAUNCH_CHECK();
   return 0;

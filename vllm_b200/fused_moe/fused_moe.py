@@ -80,10 +80,25 @@ def invoke_fused_moe_kernel(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, A
             ptr(expert_ids), ptr(num_tokens_post_padded), num_pairs, A.shape[0], top_k, E, N, K, block_m,
             sorted_token_ids.numel(), int(bool(mul_routed_weight)), dtype_enum(A.dtype), ptr(ws), ws.numel(), stream()))
         return
-    if A.dtype != FP8 or B.dtype != FP8:
-        raise RuntimeError("invoke_fused_moe_kernel: use_fp8_w8a8 needs float8_e4m3fn A and B")
+    if B.dtype != FP8:
+        raise RuntimeError("invoke_fused_moe_kernel: use_fp8_w8a8 needs float8_e4m3fn B")
     ws_bytes = lib.vb200_moe_grouped_gemm_workspace_size(sorted_token_ids.numel(), K)
     ws = _moe_workspace(A.device, ws_bytes)
+    if A.dtype in (torch.float16, torch.bfloat16):
+        # unquantised activations + their per-tensor scale: quantised while they are gathered into expert order
+        # (bit-identical to static_scaled_fp8_quant followed by the fp8 call below)
+        if A_scale is None or A_scale.numel() != 1:
+            raise RuntimeError("invoke_fused_moe_kernel: 16-bit activations need a per-tensor A_scale")
+        check(lib.vb200_moe_grouped_gemm_fp8_q16(
+            ptr(C), ptr(A), dtype_enum(A.dtype), ptr(B), ptr(A_scale), ptr(B_scale),
+            ptr(topk_weights) if mul_routed_weight else None, ptr(sorted_token_ids), ptr(expert_ids),
+            ptr(num_tokens_post_padded), num_pairs, A.shape[0], top_k, E, N, K, block_m, sorted_token_ids.numel(),
+            1 if B_scale.numel() > E else 0, int(bool(mul_routed_weight)), dtype_enum(C.dtype), ptr(ws), ws.numel(),
+            stream()))
+        return
+    if A.dtype != FP8:
+        raise RuntimeError("invoke_fused_moe_kernel: use_fp8_w8a8 needs float8_e4m3fn (or, with a per-tensor scale, "
+                           "f16 / bf16) A")
     a_per_token = 1 if A_scale.numel() > 1 else 0
     b_per_channel = 1 if B_scale.numel() > E else 0
     if a_per_token and A_scale.numel() != A.shape[0]:
@@ -144,6 +159,34 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
         return out
     # activation quant: per-token when per_channel_quant, static when a scale is given, else dynamic per-tensor
     # (moe_kernel_quantize_input, fused_moe/utils.py)
+    if not per_channel_quant and (N // 2) % 16 == 0 and H % 16 == 0:
+        # Per-tensor activation scales (Mixtral-style fp8 checkpoints).  The reference quantises the whole tensor and the
+        # GEMM gathers fp8 rows; here only the SCALE is computed up front (dynamic: one abs-max pass, fused with the
+        # activation for the second GEMM) and the rows are quantised while they are gathered into expert order: 8
+        # launches instead of 12 per layer, same bytes into the GEMMs, bit-identical output.
+        scales = None
+        if a1_scale is None or a2_scale is None:
+            scales = torch.zeros(2, dtype=torch.float32, device=dev)   # one fill for both dynamic scales
+        if a1_scale is None:
+            a1s = scales[0:1]
+            ops.absmax_scale(a1s, hidden_states)
+        else:
+            a1s = a1_scale.reshape(-1)[:1].float()
+        invoke_fused_moe_kernel(hidden_states, w1, cache1, a1s, w1_scale, None, sorted_ids, expert_ids, num_post, False,
+                                k, block_m, True, False)
+        cache2 = torch.empty((T * k, N // 2), device=dev, dtype=dt)
+        if a2_scale is None:
+            a2s = scales[1:2]
+            ops.silu_and_mul_absmax(cache2, a2s, cache1.view(T * k, N))
+        else:
+            a2s = a2_scale.reshape(-1)[:1].float()
+            ops.silu_and_mul(cache2, cache1.view(T * k, N))
+        cache3 = torch.empty((T, k, w2.shape[1]), device=dev, dtype=dt)
+        invoke_fused_moe_kernel(cache2, w2, cache3, a2s, w2_scale, topk_weights.contiguous(), sorted_ids, expert_ids,
+                                num_post, True, 1, block_m, True, False)
+        out = hidden_states if inplace else torch.empty_like(hidden_states)
+        ops.moe_sum(cache3, out)
+        return out
     a1q, a1s = ops.scaled_fp8_quant(hidden_states, a1_scale, use_per_token_if_dynamic=per_channel_quant)
     invoke_fused_moe_kernel(a1q, w1, cache1, a1s, w1_scale, None, sorted_ids, expert_ids, num_post, False, k,
                             block_m, True, per_channel_quant)
