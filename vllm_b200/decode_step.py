@@ -11,8 +11,10 @@ Per layer (FP8 w8a8, dynamic per-token activation scales, per-channel weight sca
   silu_and_mul_dynamic_per_token_quant -> cutlass_scaled_mm (down, row-parallel) -> all-reduce
 or, for Mixtral layers, the MoE block: router GEMM -> fused_topk -> fused_experts -> all-reduce.
 Tensor parallelism: heads / columns / expert-intermediate shards, one all-reduce per row-parallel GEMM
-(/root/reference/vllm/model_executor/layers/linear.py:1389).  The bf16 variant (BASELINE config 2) uses the
-library GEMM (torch.matmul -> cuBLAS) for the projections: only its attention/cache path is ours.
+(/root/reference/vllm/model_executor/layers/linear.py:1389).  The bf16 variant (BASELINE config 2) and every model's
+lm_head use the library GEMM (torch.matmul -> cuBLAS) for their unquantised projections, as the reference does;
+VB200_DENSE16=1 runs them on the tcgen05 grouped GEMM with one expert instead (quantization/unquantized_linear.py:
+correct, but a dense decode GEMM has too few weight-row tiles for that kernel: 8.66 vs 6.22 ms/step on config 2).
 """
 from dataclasses import dataclass
 from typing import List, Optional
@@ -28,6 +30,14 @@ from .distributed import (get_peer_allreduce, get_tensor_model_parallel_rank,
                           get_tensor_model_parallel_world_size, tensor_model_parallel_all_reduce)
 
 FP8 = torch.float8_e4m3fn
+
+
+def _dense(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """Unquantised y = x W^T (UnquantizedLinearMethod.apply, layers/linear.py:221-230)."""
+    if os.environ.get("VB200_DENSE16", "0") == "1" and x.dtype in (torch.float16, torch.bfloat16) and x.shape[1] % 8 == 0:
+        from .quantization.unquantized_linear import linear_16
+        return linear_16(x, w)
+    return torch.matmul(x, w.t())
 
 
 @dataclass
@@ -208,7 +218,7 @@ class DecoderLayer:
             else:
                 ops.fused_add_rms_norm(hidden, residual, self.input_ln, eps)
                 x = hidden
-            qkv = torch.matmul(x, self.w_qkv.t())
+            qkv = _dense(x, self.w_qkv)
         q = qkv[:, :self.q_size]
         k = qkv[:, self.q_size:self.q_size + self.kv_size]
         v = qkv[:, self.q_size + self.kv_size:]
@@ -230,7 +240,7 @@ class DecoderLayer:
                                     par.staging(T, cfg.hidden_size, self.dtype) if fused_ar else None)
         else:
             attn_out = self.attn.forward(self.kv_scales, q, None, None, kv_cache, meta)
-            hidden = torch.matmul(attn_out, self.w_o.t())
+            hidden = _dense(attn_out.view(T, -1), self.w_o)
         if not fused_ar:
             hidden = tensor_model_parallel_all_reduce(hidden)
         # ---- MLP block ----
@@ -258,10 +268,10 @@ class DecoderLayer:
             hidden = self._linear_q(hq, hs, self.w_down, self.s_down)
         else:
             ops.fused_add_rms_norm(hidden, residual, self.post_ln, eps)
-            gu = torch.matmul(hidden, self.w_gate_up.t())
+            gu = _dense(hidden, self.w_gate_up)
             act = torch.empty(gu.shape[0], self.inter, device=gu.device, dtype=gu.dtype)
             ops.silu_and_mul(act, gu)
-            hidden = torch.matmul(act, self.w_down.t())
+            hidden = _dense(act, self.w_down)
         hidden = tensor_model_parallel_all_reduce(hidden)
         return hidden, residual, False
 
@@ -327,8 +337,8 @@ class Decoder:
         return hidden
 
     def forward(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
-        """Returns the logits of this rank's vocabulary shard, [T, vocab/tp] (library GEMM: lm_head is not fp8)."""
-        return torch.matmul(self.hidden_states(input_ids, positions, meta), self.lm_head.t())
+        """Returns the logits of this rank's vocabulary shard, [T, vocab/tp] (lm_head is not quantised: bf16 GEMM)."""
+        return _dense(self.hidden_states(input_ids, positions, meta), self.lm_head)
 
     def greedy_step(self, input_ids, positions, meta: B200PagedAttentionMetadata) -> torch.Tensor:
         """One decode step with greedy sampling: next token ids [T] int64 (vocab-parallel arg-max)."""
