@@ -373,6 +373,20 @@ int vb200_moe_align_block_size(const int32_t* topk_ids, int numel, int num_exper
                                int expert_ids_capacity, int32_t* num_tokens_post_pad,
                                void* workspace, size_t workspace_bytes, vb200_stream_t stream);
 
+/* The router of a MoE layer in one launch: logits = hidden @ w_gate^T (the replicated, unquantised gate Linear,
+ * `router_logits, _ = self.gate(hidden_states)`, vllm/model_executor/models/mixtral.py:105-112), rounded to the
+ * activation dtype as a GEMM output is, then fused_topk (fp32 softmax, top-k with lowest-index ties, optional
+ * renormalisation: fused_moe.py:866-915; identical to vb200_fused_topk on those logits).  hidden [num_tokens,
+ * hidden_size] and w_gate [num_experts, hidden_size] of `dtype` (F16 / BF16), contiguous, 16-byte aligned; num_experts
+ * <= 32; hidden_size % 8 == 0, <= 8192.  topk_weights fp32 / topk_indices int32 [num_tokens, topk];
+ * token_expert_indices int32 [num_tokens, topk] or NULL; logits_out [num_tokens, num_experts] of `dtype` or NULL;
+ * absmax_scale: NULL, or a pre-zeroed fp32 scalar that receives max|hidden| / 448 (atomic max) -- the dynamic
+ * per-tensor fp8 scale of the experts' first GEMM (what vb200_absmax_scale computes), for free while the row is in
+ * registers. */
+int vb200_moe_router_topk(float* topk_weights, int32_t* topk_indices, int32_t* token_expert_indices, void* logits_out,
+                          float* absmax_scale, const void* hidden, const void* w_gate, int num_tokens, int hidden_size,
+                          int num_experts, int topk, int renormalize, int dtype, vb200_stream_t stream);
+
 /* moe_sum: csrc/moe/moe_align_sum_kernels.cu:277-318 (kernel :109-123):
  * out[t,:] = sum_j in[t,j,:], accumulated in the tensor dtype in j order. */
 int vb200_moe_sum(void* out, const void* input, int num_tokens, int topk, int hidden, int dtype,

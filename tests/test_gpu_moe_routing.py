@@ -114,3 +114,29 @@ def test_fused_topk_one_launch(T, E, k, dtype, renorm):
     assert ids.dtype == torch.int32 and torch.equal(ids.cpu(), ids_o.to(torch.int32))
     torch.testing.assert_close(w.cpu(), w_o, rtol=2e-6, atol=1e-7)
     assert torch.equal(tei.cpu(), (torch.arange(k)[None, :] * T + torch.arange(T)[:, None]).to(torch.int32))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("renorm", [True, False])
+@pytest.mark.parametrize("T,H,E,k", [(1, 4096, 8, 2), (128, 4096, 8, 2), (33, 1024, 32, 6), (256, 8192, 16, 1), (7, 136, 3, 3)])
+def test_router_topk_one_launch(T, H, E, k, renorm, dtype):
+    """vb200_moe_router_topk = gate GEMM + fused_topk (+ abs-max of the hidden states).  The logits are a floating-point
+    GEMM: against a plain PyTorch fp32 reference of hidden @ w_gate^T within one unit in the last place of the
+    activation dtype; the routing on THOSE logits is integer / exact work: bit-identical to fused_topk
+    (fused_moe.py:882-915) run on them; the abs-max scale equals scaled_fp8_quant's dynamic per-tensor scale."""
+    from vllm_b200 import _custom_ops as ops
+    from vllm_b200.fused_moe import fused_topk, router_topk
+    seed_all(T + H + E)
+    x = torch.randn(T, H, device=DEV).to(dtype)
+    w = (torch.randn(E, H, device=DEV) / H ** 0.5 * 3).to(dtype)
+    scale = torch.zeros(1, dtype=torch.float32, device=DEV)
+    tw, ids, logits = router_topk(x, w, k, renorm, absmax_scale=scale, return_logits=True)
+    torch.cuda.synchronize()
+    want_logits = x.float() @ w.float().t()
+    ulp = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    assert (logits.float() - want_logits).abs().max() <= ulp * want_logits.abs().clamp_min(1.0).max() * 1.01
+    tw2, ids2, _ = fused_topk(x, logits, k, renorm)
+    assert torch.equal(ids, ids2)
+    assert torch.equal(tw, tw2)
+    _, want_scale = ops.scaled_fp8_quant(x, None)
+    assert torch.equal(scale.view(-1), want_scale.view(-1))

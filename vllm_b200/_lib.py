@@ -97,6 +97,7 @@ SIGNATURES = {
     "vb200_moe_grouped_gemm_fp8": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                            c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t,
                                            _P]),
+    "vb200_moe_router_topk": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "vb200_moe_grouped_gemm_fp8_q16": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                                c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t, _P]),
     "vb200_moe_grouped_gemm_16": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int,

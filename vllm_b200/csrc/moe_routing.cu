@@ -314,6 +314,144 @@ extern "C" int vb200_fused_topk(float* topk_weights, int32_t* topk_indices, int3
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Router in one launch: logits = hidden @ w_gate^T (the replicated, unquantised gate Linear: FusedMoE's
+// `router_logits, _ = self.gate(hidden_states)`, models/mixtral.py:105-112), rounded to the activation dtype as the
+// library GEMM's output would be, then fused_topk (softmax, top-k, renormalisation: fused_moe.py:866-915) -- and, on
+// the way, max|hidden| / 448 for the dynamic per-tensor fp8 scale of the experts' first GEMM, since the row is in
+// registers anyway.  One CTA of 4 warps per token; E <= 32 (lane e of warp 0 owns expert e); H <= 8 * 8 * 128.
+// ---------------------------------------------------------------------------------------------
+namespace vb200 {
+constexpr int kRouterThreads = 128;
+constexpr int kRouterMaxVec = 8;   // 16-byte vectors of the row per thread
+
+template <typename T, bool RENORM>
+__global__ void __launch_bounds__(kRouterThreads) moe_router_topk_kernel(
+    float* __restrict__ topk_weights, int* __restrict__ topk_indices, int* __restrict__ token_expert_indices,
+    T* __restrict__ logits_out, float* __restrict__ absmax_scale, const T* __restrict__ hidden,
+    const T* __restrict__ w_gate, int num_tokens, int H, int E, int topk) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float part[kRouterThreads / 32][32];
+  __shared__ float smax[kRouterThreads / 32];
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nvec = H >> 3;
+  const T* x = hidden + (int64_t)row * H;
+  union V8 { uint4 u; T e[8]; };
+  V8 xv[kRouterMaxVec];
+  float m = 0.f;
+#pragma unroll
+  for (int i = 0; i < kRouterMaxVec; ++i) {
+    const int v = tid + i * kRouterThreads;
+    if (v < nvec) {
+      xv[i].u = *reinterpret_cast<const uint4*>(x + (int64_t)v * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) m = fmaxf(m, fabsf(to_float<T>(xv[i].e[j])));
+    }
+  }
+  for (int e = 0; e < E; ++e) {
+    const T* w = w_gate + (int64_t)e * H;
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < kRouterMaxVec; ++i) {
+      const int v = tid + i * kRouterThreads;
+      if (v < nvec) {
+        V8 wv;
+        wv.u = *reinterpret_cast<const uint4*>(w + (int64_t)v * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc = fmaf(to_float<T>(xv[i].e[j]), to_float<T>(wv.e[j]), acc);
+      }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) part[warp][e] = acc;
+  }
+  m = warp_max(m);
+  if (lane == 0) smax[warp] = m;
+  __syncthreads();
+  if (warp != 0) return;
+  if (absmax_scale != nullptr && lane == 0) {
+    float mm = smax[0];
+#pragma unroll
+    for (int w = 1; w < kRouterThreads / 32; ++w) mm = fmaxf(mm, smax[w]);
+    atomicMax(reinterpret_cast<int*>(absmax_scale), __float_as_int(mm / 448.0f));   // as absmax_scale_kernel
+  }
+  // lane e: logit of expert e, rounded to T like a GEMM output, then fused_topk on it
+  float v = -FLT_MAX;
+  if (lane < E) {
+    float acc = part[0][lane];
+#pragma unroll
+    for (int w = 1; w < kRouterThreads / 32; ++w) acc += part[w][lane];
+    const T r = from_float<T>(acc);
+    if (logits_out != nullptr) logits_out[(int64_t)row * E + lane] = r;
+    v = to_float<T>(r);
+  }
+  const float mx = warp_max(v);
+  float p = lane < E ? expf(v - mx) : 0.f;
+  const float sum = warp_sum(p);
+  const float inv = 1.f / sum;
+  p = lane < E ? p * inv : -1.f;
+  float wsum = 0.f;
+  for (int k = 0; k < topk; ++k) {
+    float best = p;
+    int bidx = lane;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, bidx, off);
+      if (ob > best || (ob == best && oi < bidx)) {
+        best = ob;
+        bidx = oi;
+      }
+    }
+    if (lane == 0) {
+      const int64_t o = (int64_t)row * topk + k;
+      topk_weights[o] = best;
+      wsum += best;
+      topk_indices[o] = bidx;
+      if (token_expert_indices != nullptr) token_expert_indices[o] = k * num_tokens + row;
+    }
+    if (lane == bidx) p = -1.f;
+  }
+  if (RENORM && lane == 0) {
+    for (int k = 0; k < topk; ++k) {
+      const int64_t o = (int64_t)row * topk + k;
+      topk_weights[o] = topk_weights[o] / wsum;
+    }
+  }
+}
+}  // namespace vb200
+
+extern "C" int vb200_moe_router_topk(float* topk_weights, int32_t* topk_indices, int32_t* token_expert_indices,
+                                     void* logits_out, float* absmax_scale, const void* hidden, const void* w_gate,
+                                     int num_tokens, int hidden_size, int num_experts, int topk, int renormalize,
+                                     int dtype, vb200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  VB_CHECK(dtype == VB200_BF16 || dtype == VB200_F16, "moe_router_topk: hidden / w_gate must be bf16 or f16");
+  VB_CHECK(num_experts >= 1 && num_experts <= 32, "moe_router_topk: num_experts %d must be in [1, 32]", num_experts);
+  VB_CHECK(topk >= 1 && topk <= num_experts, "moe_router_topk: topk %d must be in [1, num_experts %d]", topk, num_experts);
+  VB_CHECK(hidden_size % 8 == 0 && hidden_size <= 8 * kRouterMaxVec * kRouterThreads,
+           "moe_router_topk: hidden size %d must be a multiple of 8 and at most %d", hidden_size,
+           8 * kRouterMaxVec * kRouterThreads);
+  VB_CHECK(((reinterpret_cast<uintptr_t>(hidden) | reinterpret_cast<uintptr_t>(w_gate)) & 15) == 0,
+           "moe_router_topk: hidden and w_gate must be 16-byte aligned");
+  if (num_tokens <= 0) return 0;
+#define VB_ROUTER(T, R)                                                                                            \
+  VB_CUDA_CHECK(launch_k(moe_router_topk_kernel<T, R>, dim3(num_tokens), dim3(kRouterThreads), 0, stream, topk_weights, \
+                         topk_indices, token_expert_indices, (T*)logits_out, absmax_scale, (const T*)hidden,       \
+                         (const T*)w_gate, num_tokens, hidden_size, num_experts, topk))
+  if (dtype == VB200_BF16) {
+    if (renormalize) VB_ROUTER(__nv_bfloat16, true);
+    else VB_ROUTER(__nv_bfloat16, false);
+  } else {
+    if (renormalize) VB_ROUTER(__half, true);
+    else VB_ROUTER(__half, false);
+  }
+#undef VB_ROUTER
+  VB_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" size_t vb200_moe_align_workspace_size(int numel, int num_experts) {
   (void)numel;
   (void)num_experts;

@@ -4,6 +4,7 @@ grouped GEMM), fused_experts / fused_experts_impl (:1253-1346, :1349-1563), fuse
 FP8 w8a8 experts (per-tensor or per-channel weight scales; static / dynamic per-tensor / per-token activation scales:
 what BASELINE config 4, Mixtral-8x7B FP8, runs) and unquantised f16 / bf16 experts (SURVEY 8d's bf16-weights variant,
 tests/kernels/moe/test_moe.py:117-233) on the same tcgen05 grouped GEMM."""
+import os
 from typing import Optional
 
 import torch
@@ -37,6 +38,27 @@ def fused_topk(hidden_states: torch.Tensor, gating_output: torch.Tensor, topk: i
     if renormalize:
         topk_weights = topk_weights / topk_weights.sum(dim=-1, keepdim=True)
     return topk_weights, topk_ids, token_expert_indices
+
+
+def router_topk(hidden_states: torch.Tensor, w_gate: torch.Tensor, topk: int, renormalize: bool,
+                absmax_scale: Optional[torch.Tensor] = None, return_logits: bool = False):
+    """The gate Linear + fused_topk in one launch (include/vllm_b200.h vb200_moe_router_topk): router logits =
+    hidden @ w_gate^T rounded to the activation dtype, then exactly fused_topk on them.  absmax_scale: optional pre-zeroed
+    fp32 [1] that receives max|hidden| / 448 (the experts' dynamic per-tensor a1 scale).  Returns (topk_weights fp32
+    [T, k], topk_ids int32 [T, k]) and, with return_logits, the logits [T, E]."""
+    T, H = hidden_states.shape
+    E = w_gate.shape[0]
+    dev = hidden_states.device
+    if not (hidden_states.is_cuda and hidden_states.is_contiguous() and w_gate.is_contiguous()) or \
+            w_gate.dtype != hidden_states.dtype or w_gate.shape[1] != H:
+        raise RuntimeError("router_topk: contiguous CUDA hidden [T, H] and w_gate [E, H] of one dtype")
+    topk_weights = torch.empty(T, topk, dtype=torch.float32, device=dev)
+    topk_ids = torch.empty(T, topk, dtype=torch.int32, device=dev)
+    logits = torch.empty(T, E, dtype=hidden_states.dtype, device=dev) if return_logits else None
+    check(load().vb200_moe_router_topk(ptr(topk_weights), ptr(topk_ids), None, ptr(logits), ptr(absmax_scale),
+                                       ptr(hidden_states), ptr(w_gate), T, H, E, topk, int(bool(renormalize)),
+                                       dtype_enum(hidden_states.dtype), stream()))
+    return (topk_weights, topk_ids, logits) if return_logits else (topk_weights, topk_ids)
 
 
 def get_block_m(num_pairs: int, num_experts: int) -> int:
@@ -119,10 +141,13 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
                   w1_scale: Optional[torch.Tensor] = None, w2_scale: Optional[torch.Tensor] = None,
                   w1_zp=None, w2_zp=None, a1_scale: Optional[torch.Tensor] = None,
                   a2_scale: Optional[torch.Tensor] = None, block_shape=None, allow_deep_gemm: bool = False,
-                  allow_cutlass_block_scaled_grouped_gemm: bool = False) -> torch.Tensor:
+                  allow_cutlass_block_scaled_grouped_gemm: bool = False,
+                  dynamic_scales: Optional[torch.Tensor] = None) -> torch.Tensor:
     """fused_moe.py:1253-1346 / fused_experts_impl :1349-1563 for use_fp8_w8a8 (Mixtral FP8):
       quant(hidden) -> align -> GEMM1 [T, k, 2I] -> silu_and_mul -> quant -> GEMM2 (x routed weight) [T, k, H]
-      -> moe_sum.  w1 [E, 2I, H], w2 [E, H, I] fp8 with K contiguous."""
+      -> moe_sum.  w1 [E, 2I, H], w2 [E, H, I] fp8 with K contiguous.
+    dynamic_scales (B200 extension, per-tensor dynamic quantisation only): an fp32 [2] tensor whose [0] ALREADY holds
+    the abs-max scale of hidden_states (router_topk computed it) and whose [1] is zero."""
     if use_int8_w8a8 or use_int8_w8a16 or use_int4_w4a16 or use_mxfp4_w4a4:
         raise RuntimeError("fused_experts: fp8 w8a8 and unquantised f16 / bf16 experts are built in vllm_b200")
     if activation != "silu" or not is_act_and_mul or apply_router_weight_on_input or block_shape is not None:
@@ -164,12 +189,13 @@ def fused_experts(hidden_states: torch.Tensor, w1: torch.Tensor, w2: torch.Tenso
         # GEMM gathers fp8 rows; here only the SCALE is computed up front (dynamic: one abs-max pass, fused with the
         # activation for the second GEMM) and the rows are quantised while they are gathered into expert order: 8
         # launches instead of 12 per layer, same bytes into the GEMMs, bit-identical output.
-        scales = None
-        if a1_scale is None or a2_scale is None:
+        scales = dynamic_scales
+        if scales is None and (a1_scale is None or a2_scale is None):
             scales = torch.zeros(2, dtype=torch.float32, device=dev)   # one fill for both dynamic scales
         if a1_scale is None:
             a1s = scales[0:1]
-            ops.absmax_scale(a1s, hidden_states)
+            if dynamic_scales is None:
+                ops.absmax_scale(a1s, hidden_states)
         else:
             a1s = a1_scale.reshape(-1)[:1].float()
         invoke_fused_moe_kernel(hidden_states, w1, cache1, a1s, w1_scale, None, sorted_ids, expert_ids, num_post, False,
@@ -243,6 +269,14 @@ def make_dummy_experts(E: int, hidden: int, inter: int, device, dtype, quant: st
 def moe_forward(hidden: torch.Tensor, w_gate: torch.Tensor, experts: dict, top_k: int, renormalize: bool = True):
     """FusedMoE.forward_impl (fused_moe/layer.py:1482-1533) minus the all-reduce (done by the caller):
     router logits via the library GEMM (replicated, unquantised gate), then fused_moe."""
+    E, H = w_gate.shape
+    if E <= 32 and H % 16 == 0 and H <= 8192 and hidden.dtype in (torch.float16, torch.bfloat16) and \
+            os.environ.get("VB200_FUSED_ROUTER", "1") != "0":
+        # gate GEMM + fused_topk + the abs-max of `hidden` (the experts' dynamic a1 scale) in ONE launch
+        scales = torch.zeros(2, dtype=torch.float32, device=hidden.device)
+        topk_weights, topk_ids = router_topk(hidden, w_gate, top_k, renormalize, absmax_scale=scales[0:1])
+        return fused_experts(hidden, experts["w13"], experts["w2"], topk_weights, topk_ids, use_fp8_w8a8=True,
+                             w1_scale=experts["w13_scale"], w2_scale=experts["w2_scale"], dynamic_scales=scales)
     router_logits = torch.matmul(hidden, w_gate.t())
     return fused_moe(hidden, experts["w13"], experts["w2"], router_logits, top_k, renormalize,
                      use_fp8_w8a8=True, w1_scale=experts["w13_scale"], w2_scale=experts["w2_scale"])
