@@ -21,6 +21,9 @@ CFGS = {
     "3": dict(num_seqs=256, ctx=4096, H=32, Hkv=8, D=128, kvd="fp8"),
     "5": dict(num_seqs=128, ctx=8192, H=8, Hkv=1, D=128, kvd="fp8"),
     "2r": dict(num_seqs=64, ctx=2048, H=32, Hkv=8, D=128, kvd="auto", ragged=True),
+    # per-GPU shards of config 3 under tensor parallelism (not in "all")
+    "3tp4": dict(num_seqs=256, ctx=4096, H=8, Hkv=2, D=128, kvd="fp8"),
+    "3tp8": dict(num_seqs=256, ctx=4096, H=4, Hkv=1, D=128, kvd="fp8"),
 }
 
 
@@ -104,7 +107,7 @@ def main():
     from parity_utils import load_ref_cuda
     ref = None if a.no_ref else load_ref_cuda()
     peak, how = peak_gbs()
-    names = list(CFGS) if a.cfg == "all" else a.cfg.split(",")
+    names = [n for n in CFGS if "tp" not in n] if a.cfg == "all" else a.cfg.split(",")
     for name in names:
         cfg = CFGS[name]
         q, kc, vc, bt, sl, sc = make(cfg)
