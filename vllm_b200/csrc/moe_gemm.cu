@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) moe_gather_rows_kernel(
 // for itself, are fetched once per 256 weight rows; one CTA per SM (the stage is 16 KiB larger and TMEM holds 2 x
 // tile_cols columns).  NT = 1 (decode batches): the pure weight stream, two CTAs per SM.
 template <typename OutT, int NT>
-__global__ void __launch_bounds__(kMoeThreads, NT == 1 ? 2 : 1)
+__global__ void __launch_bounds__(kMoeThreads, 2)
     moe_grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w,
                             const __grid_constant__ CUtensorMap tmap_a, const MoeParams p) {
   pdl_wait();
@@ -355,11 +355,17 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
     const char* e = getenv("VB200_MOE_ORDER");   // A/B switch for benchmarks: 0 = n tiles fastest (the old order)
     p.m_fastest = (e && e[0] == '0') ? 0 : 1;
   }
-  // Two weight tiles per CTA once an M-block holds 128 rows or more AND K is long (w2: K = intermediate size): there
-  // the kernel is bound by the L2 -> SM traffic of the activation tiles (see the kernel's NT comment): w2 at batch 512
-  // 128 -> 105 us, at 2048 275 -> 257.  With a short K (w13: 32 k-blocks) a CTA's prologue and epilogue weigh more
-  // than the saved traffic and two CTAs per SM overlapping them win (215 vs 223 us): profiles/r02_moe_gemm_nt2_s74.txt
-  int nt = (block_m >= 128 && N >= 2 * kMoeBlockN && K >= 8192) ? 2 : 1;
+  // Two weight tiles per CTA (the kernel's NT comment) once an M-block holds 128 rows or more -- at those batches the
+  // L2 -> SM traffic of the activation tiles binds -- provided the halved grid still fills the machine.  Long K (w2, K
+  // = intermediate size): always (batch 512: 128 -> 105 us).  Short K (w13, 32 k-blocks): only with two CTAs per SM
+  // (block_m <= 128, two-stage rings), whose overlapped prologues / epilogues one CTA per SM lacks (batch 512: 215 ->
+  // 205 us, batch 2048: 606 -> 547; one CTA per SM: 223 / 635), and only when ceil(N / 256) x M-blocks >= 2 x #SMs
+  // (TP-8 shard at batch 512: 168 CTAs, 39 -> 49 us otherwise).  profiles/r02_moe_gemm_nt2_s74.txt, _s81.txt
+  int nt = 1;
+  if (block_m >= 128 && N >= 2 * kMoeBlockN) {
+    const long ctas2 = (long)((N + 2 * kMoeBlockN - 1) / (2 * kMoeBlockN)) * m_blocks;
+    if (K >= 8192 || (block_m <= 128 && ctas2 >= 2L * num_sms())) nt = 2;
+  }
   if (const char* e = getenv("VB200_MOE_NT")) {   // A/B switch for benchmarks
     if (e[0] == '1') nt = 1;
     if (e[0] == '2' && N >= 2 * kMoeBlockN) nt = 2;
@@ -368,8 +374,12 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
   const int meta = 4096 + kMoeMaxBlockM * 4 * 3;
   // two CTAs per SM when the stages fit in half of the shared memory, else one
   int budget = (227 * 1024) / 2 - 1024 - meta;
-  int stages = nt == 1 ? budget / stage_bytes : 0;
-  if (stages < 3) {
+  int stages = budget / stage_bytes;
+  // NT = 2 with <= 128-row M-blocks: two CTAs per SM still fit (2 x 2 x 128 TMEM columns) with a two-stage ring -- 96 KB
+  // in flight per CTA is what the L2 feed needs, the stage COUNT matters less (VB200_MOE_NT2_2CTA=0: one CTA per SM)
+  const char* e2 = getenv("VB200_MOE_NT2_2CTA");
+  const bool nt2_two_ctas = nt == 2 && block_m <= 128 && stages >= 2 && !(e2 && e2[0] == '0');
+  if ((nt == 1 && stages < 3) || (nt == 2 && !nt2_two_ctas)) {
     budget = 227 * 1024 - 1024 - meta;
     stages = budget / stage_bytes;
   }
@@ -382,7 +392,7 @@ static int launch_moe_gemm(MoeParams p, const CUtensorMap& tw, const CUtensorMap
   p.tmem_cols = nt * cols;
   size_t smem = 1024 + (size_t)stages * stage_bytes + meta;
   // NT = 2 is compiled for one CTA per SM and may take all 512 TMEM columns: never let two of them share an SM
-  if (nt == 2 && smem < 120 * 1024) smem = 120 * 1024;
+  if (nt == 2 && !nt2_two_ctas && smem < 120 * 1024) smem = 120 * 1024;
   dim3 grid((N + kMoeBlockN * nt - 1) / (kMoeBlockN * nt), m_blocks);
 #define VB_MOE_LAUNCH(T, NT_)                                                                             \
   do {                                                                                                    \
