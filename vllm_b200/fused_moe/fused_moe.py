@@ -69,7 +69,9 @@ def get_block_m(num_pairs: int, num_experts: int) -> int:
     for bm in (16, 32, 64, 128):
         if avg * 3 <= bm * 2:
             return bm
-    return 256 if avg > 192 else 128
+    # above 256 rows per expert every expert has several M-blocks whatever the block; with the M-blocks of a weight tile
+    # launched back to back the 128-row block (two CTAs per SM) is the faster one (csrc/moe_gemm.cu, ragged rule)
+    return 256 if 192 < avg <= 256 else 128
 
 
 def _moe_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
