@@ -559,3 +559,38 @@ def test_flash_attn_varlen_alibi(head_size, heads, soft_cap):
         out_d = torch.empty_like(qd)
         ops.paged_attention_flash(out_d, qd, kd, vd, scale, bt.to(DEV), kvl, max(kv_lens), slopes.to(DEV), "auto", None, None)
         torch.testing.assert_close(out_v.float(), out_d.float(), atol=1.5e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("kvd", ["auto", "fp8"])
+@pytest.mark.parametrize("partition_size", [0, 128, -1])
+@pytest.mark.parametrize("window", [1, 16, 100, 1000, 5000])
+def test_paged_attention_flash_decode_with_sliding_window(window, partition_size, kvd):
+    """Sliding window on the HBM-roofline decode kernel (vb200_paged_attention_flash_window): blocks left of the window
+    are skipped, partitions counted from the window's first block; against the oracle (golden
+    test_flash_attn.py:62-67) incl. forced split-K, windows shorter / longer than the sequences, ALiBi, fp8 cache."""
+    from oracle.fp8 import dequant_e4m3
+    from vllm_b200 import _custom_ops as ops
+    seed_all(window + 7)
+    H, Hkv, D, bs, nb, dtype = 8, 2, 128, 16, 700, torch.bfloat16
+    kv_lens = [1, 15, 16, 17, 130, 1029, 2600]
+    S = len(kv_lens)
+    ksc, vsc = (0.05, 0.03) if kvd == "fp8" else (1.0, 1.0)
+    if kvd == "fp8":
+        k8 = (torch.randn(nb, bs, Hkv, D) / ksc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+        v8 = (torch.randn(nb, bs, Hkv, D) / vsc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+        kc, vc, kd, vd = dequant_e4m3(k8, ksc, dtype), dequant_e4m3(v8, vsc, dtype), k8.to(DEV), v8.to(DEV)
+    else:
+        kc, vc = torch.randn(nb, bs, Hkv, D).to(dtype), torch.randn(nb, bs, Hkv, D).to(dtype)
+        kd, vd = kc.to(DEV), vc.to(DEV)
+    maxb = (max(kv_lens) + bs - 1) // bs
+    bt = torch.randint(0, nb, (S, maxb), dtype=torch.int32)
+    q = torch.randn(S, H, D).to(dtype)
+    slopes = torch.rand(H) * 0.05
+    scale = float(D ** -0.5)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    ops.paged_attention_flash(out, q.to(DEV), kd, vd, scale, bt.to(DEV), torch.tensor(kv_lens, dtype=torch.int32, device=DEV),
+                              max(kv_lens), slopes.to(DEV), kvd, torch.tensor([ksc], device=DEV),
+                              torch.tensor([vsc], device=DEV), partition_size=partition_size, window_left=window - 1)
+    torch.cuda.synchronize()
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, [1] * S, kv_lens, bt, scale, sliding_window=window, alibi_slopes=slopes)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2 if kvd == "fp8" else 1.5e-2, rtol=1e-2)

@@ -225,12 +225,15 @@ def paged_attention_flash(
     k_scale: Optional[torch.Tensor],
     v_scale: Optional[torch.Tensor],
     partition_size: int = 0,
+    window_left: int = -1,
 ) -> None:
     """Decode attention over the flash cache layout (include/vllm_b200.h
     vb200_paged_attention_flash): key_cache / value_cache are the `[num_blocks, block_size, num_kv_heads, head_size]`
     halves of the V1 cache (`kv_cache.unbind(0)`, vllm/v1/attention/backends/flash_attn.py:465), NHD-contiguous or
     the HND-permuted view -- addressed through their strides like reshape_and_cache_flash.  query / out
-    [num_seqs, num_heads, head_size]; one query token per sequence; seq_lens int32 = context length."""
+    [num_seqs, num_heads, head_size]; one query token per sequence; seq_lens int32 = context length.  window_left >= 0:
+    sliding window, the query attends its last window_left + 1 keys only (flash-attn's window_size = (window_left, 0));
+    blocks left of the window are never read."""
     kvd = kv_dtype_enum(kv_cache_dtype)
     require_cuda(out, query, key_cache, value_cache, block_tables, seq_lens, alibi_slopes, k_scale, v_scale)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
@@ -257,6 +260,9 @@ def paged_attention_flash(
     strides = [key_cache.stride(i) if key_cache.size(i) > 1 else head_size for i in range(3)]
     lib = load()
     qd = dtype_enum(query.dtype)
+    window_left = int(window_left)
+    if window_left >= 0:   # the split-K plan is made for what a sequence can contribute: the window + its first block's slack
+        max_seq_len = min(max_seq_len, window_left + 16)
     with _device_of(query):
         ws, ws_bytes = None, 0
         if partition_size >= 0:
@@ -267,11 +273,11 @@ def paged_attention_flash(
                                                                       partition_size)
             if ws_bytes > 0:
                 ws = torch.empty(ws_bytes, dtype=torch.uint8, device=query.device)
-        check(lib.vb200_paged_attention_flash(
+        check(lib.vb200_paged_attention_flash_window(
             ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), num_seqs, num_heads, head_size, num_kv_heads,
             float(scale), ptr(block_tables), ptr(seq_lens), block_size, num_blocks, max_seq_len, block_tables.stride(0),
             ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0), *strides,
-            max(partition_size, 0), ptr(ws), ws_bytes, stream()))
+            max(partition_size, 0), ptr(ws), ws_bytes, window_left, stream()))
 
 
 def paged_attention_v2(

@@ -79,8 +79,12 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         softmax_scale = q.shape[-1] ** -0.5
     if out is None:
         out = torch.empty_like(q)
-    if max_seqlen_q != 1 or q.shape[0] != seqused_k.shape[0] or window_left >= 0 or softcap > 0 or return_softmax_lse:
-        # prefill / chunked prefill / mixed batch, or any batch with a window / soft-cap: the variable-length kernel
+    decode = max_seqlen_q == 1 and q.shape[0] == seqused_k.shape[0]
+    head_bytes = q.shape[-1] * k.element_size()
+    # a decode batch with a window stays on the HBM-roofline decode kernel when that kernel takes the shape
+    decode_kernel_ok = decode and softcap == 0 and not return_softmax_lse and k.shape[1] == 16 and head_bytes % 128 == 0
+    if not decode_kernel_ok:
+        # prefill / chunked prefill / mixed batch, or a batch with a soft-cap / LSE output: the variable-length kernel
         # (csrc/paged_prefill.cu)
         if cu_seqlens_q is None:
             if max_seqlen_q != 1:
@@ -96,7 +100,7 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None
     ops.paged_attention_flash(out, q, k, v, softmax_scale, block_table, seqused_k, int(max_seqlen_k), alibi_slopes,
-                              "fp8" if fp8 else "auto", ks, vs)
+                              "fp8" if fp8 else "auto", ks, vs, window_left=window_left)
     return out
 
 

@@ -50,6 +50,10 @@ struct PagedAttnParams {
   void* out_q = nullptr;
   float* out_scales = nullptr;
   const float* scale_ub = nullptr;
+  // flash-layout kernel only: sliding window, a query at position seq_len - 1 attends keys seq_len - 1 - window_left ..
+  // seq_len - 1 (flash-attn's window_size = (window_left, 0)); < 0: none.  Partitions are counted from the 16-token
+  // block that holds the first visible key.
+  int window_left = -1;
 };
 
 template <typename T>
@@ -464,14 +468,16 @@ template <typename QT, int HEAD_SIZE>
 __global__ void __launch_bounds__(128) paged_attention_reduce_kernel(
     QT* __restrict__ out, const float* __restrict__ exp_sums, const float* __restrict__ max_logits,
     const QT* __restrict__ tmp_out, const int* __restrict__ seq_lens, int num_heads,
-    int max_num_partitions, int partition_size, int total_rows) {
+    int max_num_partitions, int partition_size, int total_rows, int window_left) {
   pdl_wait();
   pdl_trigger();
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);  // seq * num_heads + head
   if (row >= total_rows) return;
   const int lane = threadIdx.x & 31;
   const int seq_idx = row / num_heads;
-  const int seq_len = seq_lens[seq_idx];
+  int seq_len = seq_lens[seq_idx];
+  // sliding window (flash-layout kernel): partitions are counted from the block holding the first visible key
+  if (window_left >= 0) seq_len -= max(0, seq_len - 1 - window_left) & ~15;
   // seq_len is read on the device and may have grown past the max_seq_len the buffers were sized from (a replayed
   // graph whose seq_lens advance on device): never walk past the row's max_num_partitions entries
   const int np = min(max(1, (seq_len + partition_size - 1) / partition_size), max_num_partitions);
@@ -733,7 +739,7 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
     if (p.max_num_partitions > 1 || p.force_partials) {
       const int rows = num_seqs * p.num_heads;
       VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream, (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-          p.max_num_partitions, p.partition_size, rows));
+          p.max_num_partitions, p.partition_size, rows, -1));
       VB_LAUNCH_CHECK();
     }
     return 0;
@@ -753,7 +759,7 @@ static int launch_pa(const PagedAttnParams& p, int num_seqs, int num_partitions,
   if (p.max_num_partitions > 1 || p.force_partials) {
     const int rows = num_seqs * p.num_heads;
     VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream, (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-        p.max_num_partitions, p.partition_size, rows));
+        p.max_num_partitions, p.partition_size, rows, -1));
     VB_LAUNCH_CHECK();
   }
   return 0;
@@ -854,7 +860,7 @@ static int launch_pa_flash(const PagedAttnParams& p, const FlashLayout& L, int n
     const int rows = num_seqs * p.num_heads;
     VB_CUDA_CHECK(launch_k(paged_attention_reduce_kernel<QT, HEAD_SIZE>, dim3((rows + 3) / 4), dim3(128), 0, stream,
                            (QT*)p.out, p.exp_sums, p.max_logits, (const QT*)p.tmp_out, p.seq_lens, p.num_heads,
-                           p.max_num_partitions, p.partition_size, rows));
+                           p.max_num_partitions, p.partition_size, rows, p.window_left));
     VB_LAUNCH_CHECK();
   }
   return 0;
@@ -1044,12 +1050,15 @@ extern "C" size_t vb200_paged_attention_flash_workspace_size(int num_seqs, int n
   return vb200_paged_attention_v1_workspace_size(num_seqs, num_heads, head_size, max_seq_len, q_dtype, partition_size);
 }
 
-extern "C" int vb200_paged_attention_flash(
+static int pa_flash_impl(
     void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
     int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
     int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
     const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
-    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, vb200_stream_t stream) {
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left,
+    vb200_stream_t stream) {
+  // with a window a sequence contributes at most window_left + 1 keys plus the 15 that may share their first block
+  if (window_left >= 0 && max_seq_len > window_left + 16) max_seq_len = window_left + 16;
   VB_CHECK(block_size == 16, "paged_attention_flash: block size must be 16 (got %d)", block_size);
   VB_CHECK(q_dtype == VB200_F16 || q_dtype == VB200_BF16, "paged_attention_flash: query dtype must be f16 or bf16");
   VB_CHECK(kv_dtype == VB200_KV_AUTO || kv_dtype == VB200_KV_FP8_E4M3, "Unsupported data type of kv cache: %d", kv_dtype);
@@ -1101,9 +1110,39 @@ extern "C" int vb200_paged_attention_flash(
   p.kv_head_stride = head_stride;
   p.scale = scale;
   p.prefetch_dist = 0;
+  p.window_left = window_left < 0 ? -1 : window_left;
   FlashLayout L{block_stride, token_stride, head_stride, num_blocks};
   if (q_dtype == VB200_F16) return dispatch_flash<__half>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
   return dispatch_flash<__nv_bfloat16>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
+}
+
+extern "C" int vb200_paged_attention_flash(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+    int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+    int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
+    const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, vb200_stream_t stream) {
+  return pa_flash_impl(out, query, key_cache, value_cache, num_seqs, num_heads, head_size, num_kv_heads, scale,
+                       block_tables, seq_lens, block_size, num_blocks, max_seq_len, max_num_blocks_per_seq, alibi_slopes,
+                       q_dtype, kv_dtype, k_scale, v_scale, q_stride, block_stride, token_stride, head_stride,
+                       partition_size, workspace, workspace_bytes, -1, stream);
+}
+
+// The same decode with a sliding window (flash-attn's window_size = (window_left, 0), flash_attn.py:366-369,507-510): the
+// query at position seq_len - 1 attends keys seq_len - 1 - window_left .. seq_len - 1.  Blocks left of the window are
+// never loaded: partitions are counted from the block that holds the first visible key, and the split-K plan is made
+// for window_left + 16 tokens.  Same workspace contract (sized from max_seq_len is always enough).
+extern "C" int vb200_paged_attention_flash_window(
+    void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
+    int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
+    int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
+    const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left,
+    vb200_stream_t stream) {
+  return pa_flash_impl(out, query, key_cache, value_cache, num_seqs, num_heads, head_size, num_kv_heads, scale,
+                       block_tables, seq_lens, block_size, num_blocks, max_seq_len, max_num_blocks_per_seq, alibi_slopes,
+                       q_dtype, kv_dtype, k_scale, v_scale, q_stride, block_stride, token_stride, head_stride,
+                       partition_size, workspace, workspace_bytes, window_left, stream);
 }
 
 // paged_attention_v1 + dynamic per-token fp8 quantisation of its output in the split-K reduce kernel (SURVEY.md 8f

@@ -74,7 +74,9 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
   const int nheads = min(8, num_q_per_kv - hgroup * 8);
 
   const int seq_len = p.seq_lens[seq_idx];
-  const int tok_begin = part_idx * p.partition_size;
+  // sliding window: the first visible key and the 16-token block that holds it; partition 0 starts at that block
+  const int win_start = p.window_left >= 0 ? max(0, seq_len - 1 - p.window_left) : 0;
+  const int tok_begin = (win_start & ~15) + part_idx * p.partition_size;
   if (tok_begin >= seq_len && !(seq_len <= 0 && part_idx == 0)) return;
   const int tok_end = min(tok_begin + p.partition_size, seq_len);
   const int ntok = max(tok_end - tok_begin, 0);
@@ -223,10 +225,13 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
       {
         const float pa = (float)(tok_begin + tok_a - seq_len + 1);
         const float pb = (float)(tok_begin + tok_b - seq_len + 1);
-        s[0] = (tok_a < ntok) ? fmaf(s[0], sl2, alibi2[0] * pa) : -INFINITY;
-        s[1] = (tok_a < ntok) ? fmaf(s[1], sl2, alibi2[1] * pa) : -INFINITY;
-        s[2] = (tok_b < ntok) ? fmaf(s[2], sl2, alibi2[0] * pb) : -INFINITY;
-        s[3] = (tok_b < ntok) ? fmaf(s[3], sl2, alibi2[1] * pb) : -INFINITY;
+        // visible: inside the partition / sequence and not left of the window (only the window's first block has such keys)
+        const bool va = tok_a < ntok && tok_begin + tok_a >= win_start;
+        const bool vb = tok_b < ntok && tok_begin + tok_b >= win_start;
+        s[0] = va ? fmaf(s[0], sl2, alibi2[0] * pa) : -INFINITY;
+        s[1] = va ? fmaf(s[1], sl2, alibi2[1] * pa) : -INFINITY;
+        s[2] = vb ? fmaf(s[2], sl2, alibi2[0] * pb) : -INFINITY;
+        s[3] = vb ? fmaf(s[3], sl2, alibi2[1] * pb) : -INFINITY;
       }
       // ---- online softmax over the 16 token rows (8 r-lanes x 2) --------------------------------------------
       float mx0 = fmaxf(s[0], s[2]), mx1 = fmaxf(s[1], s[3]);
