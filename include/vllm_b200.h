@@ -206,7 +206,8 @@ int vb200_paged_attention_flash(void* out, const void* query, const void* key_ca
  * flash_attn.py:366-369,507-510): the query at position seq_len - 1 attends keys seq_len - 1 - window_left ..
  * seq_len - 1.  Blocks left of the window are never loaded (partitions are counted from the block holding the first
  * visible key; the split-K plan is made for min(max_seq_len, window_left + 16) tokens -- pass that to the workspace /
- * partition helpers).  window_left < 0: no window. */
+ * partition helpers).  window_left < 0: no window.  softcap > 0: logits soft-capping, softcap * tanh(logit / softcap)
+ * before ALiBi and the mask (flash_attn.py:371-374); 0: off. */
 int vb200_paged_attention_flash_window(void* out, const void* query, const void* key_cache, const void* value_cache,
                                        int num_seqs, int num_heads, int head_size, int num_kv_heads, float scale,
                                        const int32_t* block_tables, const int32_t* seq_lens, int block_size,
@@ -214,7 +215,7 @@ int vb200_paged_attention_flash_window(void* out, const void* query, const void*
                                        const float* alibi_slopes, int q_dtype, int kv_dtype, const float* k_scale,
                                        const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
                                        int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes,
-                                       int window_left, vb200_stream_t stream);
+                                       int window_left, float softcap, vb200_stream_t stream);
 
 /* Variable-length causal attention over the FLASH cache layout (prefill with paged KV): the
  * general case of flash_attn_varlen_func(q, k=key_cache, v=value_cache, cu_seqlens_q=..., seqused_k=...,

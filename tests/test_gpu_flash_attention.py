@@ -594,3 +594,38 @@ def test_paged_attention_flash_decode_with_sliding_window(window, partition_size
     torch.cuda.synchronize()
     want = oattn.flash_attn_varlen_paged(q, kc, vc, [1] * S, kv_lens, bt, scale, sliding_window=window, alibi_slopes=slopes)
     torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2 if kvd == "fp8" else 1.5e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("kvd", ["auto", "fp8"])
+@pytest.mark.parametrize("window", [None, 200])
+@pytest.mark.parametrize("soft_cap", [10.0, 50.0])
+def test_paged_attention_flash_decode_softcap(soft_cap, window, kvd):
+    """Logits soft-capping (with and without a window, ALiBi on top) on the decode kernel against the oracle
+    (golden test_flash_attn.py:68-69), split-K forced."""
+    from oracle.fp8 import dequant_e4m3
+    from vllm_b200 import _custom_ops as ops
+    seed_all(int(soft_cap) + (window or 0))
+    H, Hkv, D, bs, nb, dtype = 8, 2, 128, 16, 400, torch.float16
+    kv_lens = [1, 17, 333, 1500]
+    S = len(kv_lens)
+    ksc, vsc = (0.05, 0.03) if kvd == "fp8" else (1.0, 1.0)
+    if kvd == "fp8":
+        k8 = (torch.randn(nb, bs, Hkv, D) * 3 / ksc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+        v8 = (torch.randn(nb, bs, Hkv, D) / vsc).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+        kc, vc, kd, vd = dequant_e4m3(k8, ksc, dtype), dequant_e4m3(v8, vsc, dtype), k8.to(DEV), v8.to(DEV)
+    else:
+        kc, vc = (torch.randn(nb, bs, Hkv, D) * 3).to(dtype), torch.randn(nb, bs, Hkv, D).to(dtype)   # logits past the cap
+        kd, vd = kc.to(DEV), vc.to(DEV)
+    bt = torch.randint(0, nb, (S, (max(kv_lens) + bs - 1) // bs), dtype=torch.int32)
+    q = torch.randn(S, H, D).to(dtype)
+    slopes = torch.rand(H) * 0.02
+    scale = float(D ** -0.5)
+    out = torch.full_like(q, float("nan"), device=DEV)
+    ops.paged_attention_flash(out, q.to(DEV), kd, vd, scale, bt.to(DEV), torch.tensor(kv_lens, dtype=torch.int32, device=DEV),
+                              max(kv_lens), slopes.to(DEV), kvd, torch.tensor([ksc], device=DEV),
+                              torch.tensor([vsc], device=DEV), partition_size=256,
+                              window_left=-1 if window is None else window - 1, softcap=soft_cap)
+    torch.cuda.synchronize()
+    want = oattn.flash_attn_varlen_paged(q, kc, vc, [1] * S, kv_lens, bt, scale, sliding_window=window, soft_cap=soft_cap,
+                                         alibi_slopes=slopes)
+    torch.testing.assert_close(out.cpu().float(), want.float(), atol=2e-2 if kvd == "fp8" else 1.5e-2, rtol=1e-2)

@@ -226,6 +226,7 @@ def paged_attention_flash(
     v_scale: Optional[torch.Tensor],
     partition_size: int = 0,
     window_left: int = -1,
+    softcap: float = 0.0,
 ) -> None:
     """Decode attention over the flash cache layout (include/vllm_b200.h
     vb200_paged_attention_flash): key_cache / value_cache are the `[num_blocks, block_size, num_kv_heads, head_size]`
@@ -233,7 +234,7 @@ def paged_attention_flash(
     the HND-permuted view -- addressed through their strides like reshape_and_cache_flash.  query / out
     [num_seqs, num_heads, head_size]; one query token per sequence; seq_lens int32 = context length.  window_left >= 0:
     sliding window, the query attends its last window_left + 1 keys only (flash-attn's window_size = (window_left, 0));
-    blocks left of the window are never read."""
+    blocks left of the window are never read.  softcap > 0: logits = softcap * tanh(logits / softcap)."""
     kvd = kv_dtype_enum(kv_cache_dtype)
     require_cuda(out, query, key_cache, value_cache, block_tables, seq_lens, alibi_slopes, k_scale, v_scale)
     if query.dim() != 3 or query.stride(2) != 1 or query.stride(1) != query.shape[2]:
@@ -277,7 +278,7 @@ def paged_attention_flash(
             ptr(out), ptr(query), ptr(key_cache), ptr(value_cache), num_seqs, num_heads, head_size, num_kv_heads,
             float(scale), ptr(block_tables), ptr(seq_lens), block_size, num_blocks, max_seq_len, block_tables.stride(0),
             ptr(alibi_slopes), qd, kvd, ptr(k_scale), ptr(v_scale), query.stride(0), *strides,
-            max(partition_size, 0), ptr(ws), ws_bytes, window_left, stream()))
+            max(partition_size, 0), ptr(ws), ws_bytes, window_left, float(softcap or 0.0), stream()))
 
 
 def paged_attention_v2(

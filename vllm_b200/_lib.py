@@ -74,7 +74,7 @@ SIGNATURES = {
                                             c_int, _P, c_size_t, _P]),
     "vb200_paged_attention_flash_window": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, c_int,
                                                    c_int, c_int, c_int, _P, c_int, c_int, _P, _P, c_int64, c_int64,
-                                                   c_int64, c_int64, c_int, _P, c_size_t, c_int, _P]),
+                                                   c_int64, c_int64, c_int, _P, c_size_t, c_int, c_float, _P]),
     "vb200_static_scaled_fp8_quant": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_dynamic_scaled_fp8_quant": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "vb200_dynamic_per_token_scaled_fp8_quant": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P]),

@@ -13,9 +13,9 @@ Mirrors the pieces of /root/reference/vllm/v1/attention/backends/flash_attn.py a
                                      vb200_paged_attention_flash kernel (TMA tensor-map loads of the cache as it lies,
                                      csrc/paged_attention_flash.cuh).
 Prefill / chunked prefill / mixed batches (max_seqlen_q > 1) run on the variable-length kernel of
-csrc/paged_prefill.cu (16-bit and fp8 caches); so does every batch with a sliding window (`window_size = (left, 0)`)
-or logits soft-capping, decode batches included (that kernel skips the tiles left of the window and applies the cap
-in front of the mask).  Cascade attention (`cascade_attention`, flash_attn.py:674-764: shared prefix non-causal + per-query
+csrc/paged_prefill.cu (16-bit and fp8 caches), with a sliding window (`window_size = (left, 0)`: tiles left of the
+window are skipped) and logits soft-capping (in front of the mask); pure decode batches keep the decode kernel with
+both (blocks left of the window are never read).  Cascade attention (`cascade_attention`, flash_attn.py:674-764: shared prefix non-causal + per-query
 suffix, both returning the log-sum-exp, merged by merge_attn_states) runs on the same kernel.  fp8 caches: the reference also quantises the QUERY to fp8 (FA3,
 :478-486); this kernel keeps the query in
 bf16/f16 and folds the per-tensor k / v descales into the fp32 logits / output, which is the dequantised result the
@@ -81,11 +81,11 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         out = torch.empty_like(q)
     decode = max_seqlen_q == 1 and q.shape[0] == seqused_k.shape[0]
     head_bytes = q.shape[-1] * k.element_size()
-    # a decode batch with a window stays on the HBM-roofline decode kernel when that kernel takes the shape
-    decode_kernel_ok = decode and softcap == 0 and not return_softmax_lse and k.shape[1] == 16 and head_bytes % 128 == 0
+    # a decode batch -- window and soft-cap included -- stays on the HBM-roofline decode kernel when that kernel takes
+    # the shape
+    decode_kernel_ok = decode and not return_softmax_lse and k.shape[1] == 16 and head_bytes % 128 == 0
     if not decode_kernel_ok:
-        # prefill / chunked prefill / mixed batch, or a batch with a soft-cap / LSE output: the variable-length kernel
-        # (csrc/paged_prefill.cu)
+        # prefill / chunked prefill / mixed batch, or an LSE output: the variable-length kernel (csrc/paged_prefill.cu)
         if cu_seqlens_q is None:
             if max_seqlen_q != 1:
                 raise RuntimeError("flash_attn_varlen_func: cu_seqlens_q is required")
@@ -100,7 +100,7 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
     ks = k_descale.reshape(-1)[:1].float().contiguous() if k_descale is not None else None
     vs = v_descale.reshape(-1)[:1].float().contiguous() if v_descale is not None else None
     ops.paged_attention_flash(out, q, k, v, softmax_scale, block_table, seqused_k, int(max_seqlen_k), alibi_slopes,
-                              "fp8" if fp8 else "auto", ks, vs, window_left=window_left)
+                              "fp8" if fp8 else "auto", ks, vs, window_left=window_left, softcap=softcap)
     return out
 
 

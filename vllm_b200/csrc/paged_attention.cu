@@ -54,6 +54,7 @@ struct PagedAttnParams {
   // seq_len - 1 (flash-attn's window_size = (window_left, 0)); < 0: none.  Partitions are counted from the 16-token
   // block that holds the first visible key.
   int window_left = -1;
+  float softcap = 0.f;   // flash-layout kernel only: logits = softcap * tanh(logits / softcap); 0: off
 };
 
 template <typename T>
@@ -1055,8 +1056,9 @@ static int pa_flash_impl(
     int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
     int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
     const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
-    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left,
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left, float softcap,
     vb200_stream_t stream) {
+  VB_CHECK(softcap >= 0.f && softcap == softcap, "paged_attention_flash: softcap must be >= 0");
   // with a window a sequence contributes at most window_left + 1 keys plus the 15 that may share their first block
   if (window_left >= 0 && max_seq_len > window_left + 16) max_seq_len = window_left + 16;
   VB_CHECK(block_size == 16, "paged_attention_flash: block size must be 16 (got %d)", block_size);
@@ -1111,6 +1113,7 @@ static int pa_flash_impl(
   p.scale = scale;
   p.prefetch_dist = 0;
   p.window_left = window_left < 0 ? -1 : window_left;
+  p.softcap = softcap;
   FlashLayout L{block_stride, token_stride, head_stride, num_blocks};
   if (q_dtype == VB200_F16) return dispatch_flash<__half>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
   return dispatch_flash<__nv_bfloat16>(p, L, head_size, fp8, num_seqs, np, (cudaStream_t)stream);
@@ -1125,24 +1128,25 @@ extern "C" int vb200_paged_attention_flash(
   return pa_flash_impl(out, query, key_cache, value_cache, num_seqs, num_heads, head_size, num_kv_heads, scale,
                        block_tables, seq_lens, block_size, num_blocks, max_seq_len, max_num_blocks_per_seq, alibi_slopes,
                        q_dtype, kv_dtype, k_scale, v_scale, q_stride, block_stride, token_stride, head_stride,
-                       partition_size, workspace, workspace_bytes, -1, stream);
+                       partition_size, workspace, workspace_bytes, -1, 0.f, stream);
 }
 
 // The same decode with a sliding window (flash-attn's window_size = (window_left, 0), flash_attn.py:366-369,507-510): the
 // query at position seq_len - 1 attends keys seq_len - 1 - window_left .. seq_len - 1.  Blocks left of the window are
 // never loaded: partitions are counted from the block that holds the first visible key, and the split-K plan is made
-// for window_left + 16 tokens.  Same workspace contract (sized from max_seq_len is always enough).
+// for window_left + 16 tokens.  Same workspace contract (sized from max_seq_len is always enough).  softcap > 0: logits
+// soft-capping, softcap * tanh(logit / softcap) (flash_attn.py:371-374, applied before ALiBi and the mask).
 extern "C" int vb200_paged_attention_flash_window(
     void* out, const void* query, const void* key_cache, const void* value_cache, int num_seqs, int num_heads,
     int head_size, int num_kv_heads, float scale, const int32_t* block_tables, const int32_t* seq_lens, int block_size,
     int num_blocks, int max_seq_len, int max_num_blocks_per_seq, const float* alibi_slopes, int q_dtype, int kv_dtype,
     const float* k_scale, const float* v_scale, int64_t q_stride, int64_t block_stride, int64_t token_stride,
-    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left,
+    int64_t head_stride, int partition_size, void* workspace, size_t workspace_bytes, int window_left, float softcap,
     vb200_stream_t stream) {
   return pa_flash_impl(out, query, key_cache, value_cache, num_seqs, num_heads, head_size, num_kv_heads, scale,
                        block_tables, seq_lens, block_size, num_blocks, max_seq_len, max_num_blocks_per_seq, alibi_slopes,
                        q_dtype, kv_dtype, k_scale, v_scale, q_stride, block_stride, token_stride, head_stride,
-                       partition_size, workspace, workspace_bytes, window_left, stream);
+                       partition_size, workspace, workspace_bytes, window_left, softcap, stream);
 }
 
 // paged_attention_v1 + dynamic per-token fp8 quantisation of its output in the split-K reduce kernel (SURVEY.md 8f

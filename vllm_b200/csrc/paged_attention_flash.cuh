@@ -176,6 +176,11 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
     }
     float sl2 = p.scale * kLog2e;
     if (FP8) sl2 *= *p.k_scale;
+    // logits soft-capping (flash_attn.py:371-374): cap * tanh(logit / cap) -- the tanh takes the raw dot product times
+    // scale / cap, the exponent scale becomes cap * log2(e); tanh.approx as in the library kernel
+    const bool capped = p.softcap > 0.f;
+    const float cap_pre = capped ? sl2 / (kLog2e * p.softcap) : 0.f;
+    if (capped) sl2 = p.softcap * kLog2e;
     float alibi2[2] = {0.f, 0.f};
     if (p.alibi_slopes != nullptr) {
 #pragma unroll
@@ -226,6 +231,10 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32, MIN_CTAS)
         const float pa = (float)(tok_begin + tok_a - seq_len + 1);
         const float pb = (float)(tok_begin + tok_b - seq_len + 1);
         // visible: inside the partition / sequence and not left of the window (only the window's first block has such keys)
+        if (capped) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) asm("tanh.approx.f32 %0, %1;" : "=f"(s[e]) : "f"(s[e] * cap_pre));
+        }
         const bool va = tok_a < ntok && tok_begin + tok_a >= win_start;
         const bool vb = tok_b < ntok && tok_begin + tok_b >= win_start;
         s[0] = va ? fmaf(s[0], sl2, alibi2[0] * pa) : -INFINITY;
