@@ -101,3 +101,30 @@ def test_oracle_window_softcap_alibi_against_a_per_row_loop(sliding_window, soft
                 want = w @ v[lo:p + 1, h // 2]
                 torch.testing.assert_close(got[o + i, h], want, rtol=1e-5, atol=1e-5)
         o += n_q
+
+
+def test_decode_window_partition_plan_covers_every_visible_key_once():
+    """The index arithmetic of the windowed flash-layout decode (csrc/paged_attention_flash.cuh: partition 0 starts at
+    the 16-token block of the first visible key; csrc/paged_attention.cu: the reduce kernel counts partitions from the
+    same block, the host plans for window_left + 16 tokens) restated in Python: for every (seq_len, window, partition)
+    the launched partitions cover exactly the keys seq_len - 1 - window_left .. seq_len - 1, each once, the reduce
+    kernel reads exactly the partitions that were written, and none of them lies past the planned grid."""
+    for seq_len in list(range(1, 70)) + [255, 256, 257, 1000, 4097]:
+        for window_left in (0, 1, 15, 16, 17, 99, 511, 512, 5000):
+            for part in (16, 32, 128, 512):
+                max_seq_len = 4097
+                planned = min(max_seq_len, window_left + 16)                  # pa_flash_impl's clamp
+                grid_np = max(1, -(-planned // part))                         # partitions launched per sequence
+                win_start = max(0, seq_len - 1 - window_left)
+                base = win_start & ~15
+                seen, written = [], []
+                for p in range(grid_np):
+                    tok_begin = base + p * part
+                    if tok_begin >= seq_len:
+                        continue                                              # the CTA returns
+                    tok_end = min(tok_begin + part, seq_len)
+                    written.append(p)
+                    seen += [t for t in range(tok_begin, tok_end) if t >= win_start]
+                assert seen == list(range(win_start, seq_len)), (seq_len, window_left, part)
+                reduce_np = min(max(1, -(-(seq_len - base) // part)), grid_np)  # paged_attention_reduce_kernel
+                assert written == list(range(reduce_np)), (seq_len, window_left, part)
